@@ -1,0 +1,258 @@
+"""cms_bwt_b200 -- ctypes binding of libcmsbwt_b200.so (include/cmsbwt_b200.h).
+
+The library is the product; this module only loads it and mirrors the reference's interface for
+the path: `compute_bwt(args, ref_file, coll_file)` stands where the reference's
+`computeBWT(Args, refFile, collFile)` stands (CMS-BWT.h:69, CMS-BWT-functions.cpp:1788-1797), with
+the same Args fields (utils.h:8-14: prefixLength, buffer, format, outname).  There is no CPU
+fallback: importing works without a GPU (so the symbol table can be checked), every compute call
+fails loudly if the shared library or a CUDA device is missing.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcmsbwt_b200.so")
+
+MODE_PLAIN, MODE_RLE = 0, 1
+UINT64_MAX = 2 ** 64 - 1
+
+EXPORTS = [
+    "cmsbwt_ctx_create", "cmsbwt_ctx_destroy", "cmsbwt_last_error", "cmsbwt_get_stats",
+    "cmsbwt_augment", "cmsbwt_read_reference", "cmsbwt_parse_collection", "cmsbwt_build_sa",
+    "cmsbwt_index_upload", "cmsbwt_index_download", "cmsbwt_ms_run", "cmsbwt_ms_run_device",
+    "cmsbwt_set_ms_dump", "cmsbwt_ms_download", "cmsbwt_heads_sort", "cmsbwt_heads_download",
+    "cmsbwt_emit", "cmsbwt_result_device", "cmsbwt_result_download", "cmsbwt_run",
+    "cmsbwt_set_param",
+]
+
+
+class Stats(C.Structure):
+    _fields_ = [("sa_build_ms", C.c_double), ("index_build_ms", C.c_double), ("ms_ms", C.c_double),
+                ("sort_ms", C.c_double), ("emit_ms", C.c_double), ("h2d_ms", C.c_double),
+                ("d2h_ms", C.c_double), ("n_heads", C.c_uint64), ("n_docs", C.c_uint64),
+                ("n_tails", C.c_uint64), ("n_items", C.c_uint64), ("n_runs", C.c_uint64),
+                ("rank_rounds", C.c_uint32), ("kmer_k", C.c_uint32),
+                ("kernel_launches", C.c_uint64)]
+
+    def asdict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class CmsBwtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("cmsbwt error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    """Loads libcmsbwt_b200.so; raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("%s not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "or `make -C cms_bwt_b200/csrc`" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        vp, u64, i64 = C.c_void_p, C.c_uint64, C.c_int64
+        L.cmsbwt_ctx_create.argtypes = [C.c_int, C.POINTER(vp)]
+        L.cmsbwt_ctx_destroy.argtypes = [vp]
+        L.cmsbwt_ctx_destroy.restype = None
+        L.cmsbwt_last_error.argtypes = [vp]
+        L.cmsbwt_last_error.restype = C.c_char_p
+        L.cmsbwt_get_stats.argtypes = [vp, C.POINTER(Stats)]
+        L.cmsbwt_augment.argtypes = [vp, i64, vp]
+        L.cmsbwt_augment.restype = i64
+        L.cmsbwt_read_reference.argtypes = [vp, i64, vp]
+        L.cmsbwt_read_reference.restype = i64
+        L.cmsbwt_parse_collection.argtypes = [vp, i64, u64, vp, C.POINTER(i64)]
+        L.cmsbwt_parse_collection.restype = i64
+        L.cmsbwt_build_sa.argtypes = [vp, vp, C.c_uint32, vp]
+        L.cmsbwt_index_upload.argtypes = [vp, vp, C.c_uint32, vp]
+        L.cmsbwt_index_download.argtypes = [vp, vp, vp, vp, vp]
+        L.cmsbwt_ms_run.argtypes = [vp, vp, u64]
+        L.cmsbwt_ms_run_device.argtypes = [vp, vp, u64]
+        L.cmsbwt_set_ms_dump.argtypes = [vp, C.c_int]
+        L.cmsbwt_ms_download.argtypes = [vp, vp, vp, vp, vp]
+        L.cmsbwt_heads_sort.argtypes = [vp]
+        L.cmsbwt_heads_download.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.cmsbwt_emit.argtypes = [vp, C.c_int, C.POINTER(u64)]
+        L.cmsbwt_result_device.argtypes = [vp]
+        L.cmsbwt_result_device.restype = vp
+        L.cmsbwt_result_download.argtypes = [vp, vp, u64]
+        L.cmsbwt_run.argtypes = [vp, vp, u64, C.c_int, vp, u64, C.POINTER(u64)]
+        L.cmsbwt_set_param.argtypes = [vp, C.c_char_p, i64]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+# ---- host loaders (reference semantics; pure host code inside the library) -----------------
+def read_reference(file_bytes):
+    src = np.frombuffer(file_bytes, dtype=np.uint8)
+    out = np.empty(len(src) + 1, np.uint8)
+    m = lib().cmsbwt_read_reference(_p(src), len(src), _p(out))
+    if m < 0:
+        raise CmsBwtError(m, "read_reference")
+    return out[:m].copy()
+
+
+def augment(ref):
+    ref = np.ascontiguousarray(ref, dtype=np.uint8)
+    out = np.empty(len(ref) + 128, np.uint8)
+    m = lib().cmsbwt_augment(_p(ref), len(ref), _p(out))
+    if m < 0:
+        raise CmsBwtError(m, "reference holds a reserved byte (0,1,2 or >127)")
+    return out[:m].copy()
+
+
+def parse_collection(file_bytes, prefix=UINT64_MAX):
+    src = np.frombuffer(file_bytes, dtype=np.uint8)
+    out = np.empty(len(src) + 2, np.uint8)
+    nd = C.c_int64(0)
+    N = lib().cmsbwt_parse_collection(_p(src), len(src), C.c_uint64(prefix), _p(out), C.byref(nd))
+    if N < 0:
+        raise CmsBwtError(N, "parse_collection")
+    return out[:N].copy(), nd.value
+
+
+class Context:
+    """One GPU context (one per device)."""
+
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        rc = lib().cmsbwt_ctx_create(device, C.byref(self.h))
+        if rc != 0:
+            self.h = None
+            raise CmsBwtError(rc, "no usable CUDA device %d (this package has no CPU fallback)" % device)
+        self.n = 0
+        self.N = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().cmsbwt_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise CmsBwtError(rc, lib().cmsbwt_last_error(self.h).decode())
+
+    def set_param(self, name, value):
+        self._ck(lib().cmsbwt_set_param(self.h, name.encode(), int(value)))
+
+    def stats(self):
+        s = Stats()
+        self._ck(lib().cmsbwt_get_stats(self.h, C.byref(s)))
+        return s.asdict()
+
+    def build_sa(self, x):
+        x = np.ascontiguousarray(x, dtype=np.uint8)
+        sa = np.empty(len(x), np.int32)
+        self._ck(lib().cmsbwt_build_sa(self.h, _p(x), len(x), _p(sa)))
+        return sa
+
+    def index_upload(self, x, sa=None):
+        x = np.ascontiguousarray(x, dtype=np.uint8)
+        if sa is not None:
+            sa = np.ascontiguousarray(sa, dtype=np.int32)
+            assert len(sa) == len(x)
+        self._ck(lib().cmsbwt_index_upload(self.h, _p(x), len(x), _p(sa)))
+        self.n = len(x)
+
+    def index_download(self):
+        n = self.n
+        sa = np.empty(n, np.int32); isa = np.empty(n, np.uint32)
+        pp = np.empty(n, np.uint32); rb = np.empty(n, np.uint8)
+        self._ck(lib().cmsbwt_index_download(self.h, _p(sa), _p(isa), _p(pp), _p(rb)))
+        return dict(sa=sa, isa=isa, plcp_prime=pp, ref_bwt=rb)
+
+    def set_ms_dump(self, on=True):
+        self._ck(lib().cmsbwt_set_ms_dump(self.h, 1 if on else 0))
+
+    def ms_run(self, text):
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        self.N = len(text)
+        self._ck(lib().cmsbwt_ms_run(self.h, _p(text), len(text)))
+
+    def ms_run_device(self, dptr, N):
+        self.N = int(N)
+        self._ck(lib().cmsbwt_ms_run_device(self.h, C.c_void_p(int(dptr)), int(N)))
+
+    def ms_download(self):
+        N = self.N
+        pos = np.empty(N, np.uint32); ln = np.empty(N, np.uint32)
+        sm = np.empty(N, np.uint8); hd = np.empty(N, np.uint8)
+        self._ck(lib().cmsbwt_ms_download(self.h, _p(pos), _p(ln), _p(sm), _p(hd)))
+        return pos, ln, sm, hd
+
+    def heads_sort(self):
+        self._ck(lib().cmsbwt_heads_sort(self.h))
+
+    def heads_download(self, within=False, offset=False):
+        H = self.stats()["n_heads"]
+        g = np.empty(H, np.uint64); pos = np.empty(H, np.uint32); ln = np.empty(H, np.uint32)
+        w = np.empty(H, np.uint64) if within else None
+        o = np.empty(H, np.uint64) if offset else None
+        self._ck(lib().cmsbwt_heads_download(self.h, _p(g), _p(pos), _p(ln), _p(w), _p(o)))
+        return dict(gstart=g, pos=pos, len=ln, within=w, offset=o)
+
+    def emit(self, mode=MODE_PLAIN):
+        ob = C.c_uint64(0)
+        self._ck(lib().cmsbwt_emit(self.h, mode, C.byref(ob)))
+        self.out_bytes = ob.value
+        return ob.value
+
+    def result_device(self):
+        return lib().cmsbwt_result_device(self.h)
+
+    def result_download(self, out=None):
+        if out is None:
+            out = np.empty(self.out_bytes, np.uint8)
+        self._ck(lib().cmsbwt_result_download(self.h, _p(out), out.nbytes))
+        return out[:self.out_bytes]
+
+    def run(self, text, mode=MODE_PLAIN, out=None):
+        """ms_run + heads_sort + emit + download on host buffers (the drop-in call)."""
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        self.N = len(text)
+        if out is None:
+            out = np.empty(len(text) if mode == MODE_PLAIN else 9 * len(text), np.uint8)
+        ob = C.c_uint64(0)
+        self._ck(lib().cmsbwt_run(self.h, _p(text), len(text), mode, _p(out), out.nbytes, C.byref(ob)))
+        self.out_bytes = ob.value
+        return out[:ob.value]
+
+
+class Args:
+    """The reference's Args (utils.h:8-14)."""
+
+    def __init__(self, filename="", outname="", prefixLength=UINT64_MAX, buffer=2, format=0):
+        self.filename, self.outname = filename, outname or filename
+        self.prefixLength, self.buffer, self.format = prefixLength, buffer, format
+
+
+def compute_bwt(args, ref_file, coll_file, device=0, sa=None):
+    """Mirror of computeBWT (CMS-BWT-functions.cpp:1788-1797): reads the two files, builds the
+    index, runs the path on the GPU and writes <outname>.bwt or <outname>.rl_bwt.  Returns stats."""
+    with open(ref_file, "rb") as f:
+        ref = read_reference(f.read())
+    x = augment(ref)
+    with open(coll_file, "rb") as f:
+        text, ndocs = parse_collection(f.read(), args.prefixLength)
+    ctx = Context(device)
+    try:
+        ctx.index_upload(x, sa)
+        out = ctx.run(text, MODE_RLE if args.format else MODE_PLAIN)
+        with open(args.outname + (".rl_bwt" if args.format else ".bwt"), "wb") as f:
+            f.write(out.tobytes())
+        return ctx.stats()
+    finally:
+        ctx.close()

@@ -1,0 +1,375 @@
+// C ABI (include/cmsbwt_b200.h) over the stage implementations.
+#include "common.cuh"
+#include <string.h>
+#include <chrono>
+
+static int fail(cmsbwt_ctx *c, int code, const std::string &msg) {
+  if (c) c->err = msg;
+  return code;
+}
+#define GUARD_BEGIN try {
+#define GUARD_END(c)                                                                         \
+  }                                                                                          \
+  catch (const CudaErr &e) {                                                                 \
+    cudaGetLastError();                                                                      \
+    return fail(c, CMSBWT_E_CUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e));     \
+  }                                                                                          \
+  catch (const CmsErr &e) { return fail(c, e.code, e.msg); }                                 \
+  catch (const std::exception &e) { return fail(c, CMSBWT_E_NOMEM, e.what()); }
+
+struct Timer {
+  cudaEvent_t a, b;
+  cudaStream_t st;
+  Timer(cudaStream_t s) : st(s) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, s); }
+  double stop() {
+    cudaEventRecord(b, st);
+    cudaEventSynchronize(b);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    return ms;
+  }
+  ~Timer() { cudaEventDestroy(a); cudaEventDestroy(b); }
+};
+
+extern "C" {
+
+int cmsbwt_ctx_create(int dev, cmsbwt_ctx **out) {
+  if (!out) return CMSBWT_E_ARG;
+  *out = nullptr;
+  int cnt = 0;
+  if (cudaGetDeviceCount(&cnt) != cudaSuccess || dev < 0 || dev >= cnt) return CMSBWT_E_CUDA;
+  cmsbwt_ctx *c = new cmsbwt_ctx();
+  c->dev = dev;
+  GUARD_BEGIN
+  CK(cudaSetDevice(dev));
+  CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
+  cudaMemPool_t pool;
+  CK(cudaDeviceGetDefaultMemPool(&pool, dev));
+  uint64_t thr = UINT64_MAX;               // keep freed blocks cached in the pool
+  CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+  }
+  catch (const CudaErr &e) { delete c; return CMSBWT_E_CUDA; }
+  *out = c;
+  return CMSBWT_OK;
+}
+
+void cmsbwt_ctx_destroy(cmsbwt_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->dev);
+  cudaStream_t st = c->st;
+  cudaStreamSynchronize(st);
+  delete c;                                 // DBufs free stream-ordered
+  cudaStreamSynchronize(st);
+  cudaStreamDestroy(st);
+}
+
+const char *cmsbwt_last_error(const cmsbwt_ctx *c) { return c ? c->err.c_str() : "null context"; }
+
+int cmsbwt_get_stats(const cmsbwt_ctx *c, cmsbwt_stats *out) {
+  if (!c || !out) return CMSBWT_E_ARG;
+  *out = c->stats;
+  out->kernel_launches = c->launches;
+  return CMSBWT_OK;
+}
+
+int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
+  if (!c || !name) return CMSBWT_E_ARG;
+  if (!strcmp(name, "chunk_len")) { if (v < 64) return CMSBWT_E_ARG; c->chunk_len = v; }
+  else if (!strcmp(name, "pool_div")) { if (v < 1) return CMSBWT_E_ARG; c->pool_div = v; }
+  else if (!strcmp(name, "kmer_k")) { if (v < 0 || v > 13) return CMSBWT_E_ARG; c->kmer_k = v; }
+  else return CMSBWT_E_ARG;
+  return CMSBWT_OK;
+}
+
+// ---- host loaders with the reference's semantics ------------------------------------------
+// reference :208-213 (one trailing \n, \r or \0 dropped, then one '$') and :231-237
+int64_t cmsbwt_augment(const uint8_t *ref, int64_t len, uint8_t *out) {
+  if (!ref || !out || len < 0) return CMSBWT_E_ARG;
+  if (len > 0) { uint8_t b = ref[len - 1]; if (b == '\n' || b == '\r' || b == 0) len--; }
+  if (len > 0 && ref[len - 1] == '$') len--;
+  bool seen[256] = {false};
+  for (int64_t i = 0; i < len; i++) seen[ref[i]] = true;
+  if (seen[0] || seen[1] || seen[2]) return CMSBWT_E_SYMBOL;   // reserved (CMS-BWT.h:28)
+  for (int v = 128; v < 256; v++) if (seen[v]) return CMSBWT_E_SYMBOL;
+  if (out != ref) memmove(out, ref, (size_t)len);
+  int64_t n = len;
+  for (int v = 3; v <= 127; v++) if (!seen[v]) out[n++] = (uint8_t)v;
+  out[n++] = 1;
+  out[n++] = 0;
+  return n;
+}
+
+// reference :171-199: '>' first => FASTA, all records concatenated; lines are taken while the
+// stream is good(), so a last line without '\n' is lost; otherwise the raw bytes.
+int64_t cmsbwt_read_reference(const uint8_t *file, int64_t size, uint8_t *out) {
+  if (!file || !out || size < 0) return CMSBWT_E_ARG;
+  if (size == 0 || file[0] != '>') { memcpy(out, file, (size_t)size); return size; }
+  int64_t w = 0, a = 0;
+  for (;;) {
+    const uint8_t *e = (const uint8_t *)memchr(file + a, '\n', (size_t)(size - a));
+    if (!e) break;
+    int64_t L = (e - file) - a;
+    if (L > 0 && file[a] != '>') { memcpy(out + w, file + a, (size_t)L); w += L; }
+    a += L + 1;
+    if (a >= size) break;
+  }
+  return w;
+}
+
+// reference :1138-1140 + :1257-1275 (small path :344-346,:464-482): header or blank line closes
+// the current document; -p: sn = min(file size, prefix); the line that reaches sn-1 symbols is
+// cut by (read - sn) + 1 symbols and ends the input; a non-empty remainder is a last document.
+int64_t cmsbwt_parse_collection(const uint8_t *file, int64_t size, uint64_t prefix,
+                                uint8_t *out, int64_t *ndocs) {
+  if (!file || !out || size < 0) return CMSBWT_E_ARG;
+  const uint64_t sn = (uint64_t)size < prefix ? (uint64_t)size : prefix;
+  uint64_t got = 0;
+  int64_t w = 0, a = 0, docs = 0, open_from = 0;
+  while (a < size) {
+    const uint8_t *e = (const uint8_t *)memchr(file + a, '\n', (size_t)(size - a));
+    if (!e) break;
+    const int64_t L = (e - file) - a;
+    if (L == 0 || file[a] == '>') {
+      out[w++] = 2; got++; docs++; open_from = w;
+    } else {
+      got += (uint64_t)L;
+      uint64_t keep = (uint64_t)L;
+      bool last = false;
+      if (got >= sn - 1) {
+        uint64_t cut = (got - sn) + 1;          // wraps like the reference's size_t arithmetic
+        keep = (uint64_t)L - cut;
+        if (keep > (uint64_t)L) keep = (uint64_t)L;
+        last = true;
+      }
+      memcpy(out + w, file + a, (size_t)keep);
+      w += (int64_t)keep;
+      if (last) break;
+    }
+    a += L + 1;
+  }
+  if (w > open_from) { out[w++] = 2; docs++; }
+  if (ndocs) *ndocs = docs;
+  return w;
+}
+
+// ---- index ------------------------------------------------------------------------------------
+static void upload_x(cmsbwt_ctx *c, const uint8_t *x, uint32_t n) {
+  c->d_x.alloc((size_t)n + CMS_PAD, c->st);
+  CK(cudaMemsetAsync(c->d_x.p, 0xFF, (size_t)n + CMS_PAD, c->st));
+  CK(cudaMemcpyAsync(c->d_x.p, x, n, cudaMemcpyHostToDevice, c->st));
+  c->ix.n = n;
+}
+
+int cmsbwt_build_sa(cmsbwt_ctx *c, const uint8_t *x, uint32_t n, int32_t *sa_out) {
+  if (!c || !x || n < 2 || n >= 0x7FFFFF00u) return fail(c, CMSBWT_E_ARG, "bad reference");
+  if (x[n - 1] != 0) return fail(c, CMSBWT_E_ARG, "reference is not augmented (x[n-1] != 0)");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  upload_x(c, x, n);
+  c->d_sa.alloc((size_t)n * 4, c->st);
+  Timer t(c->st);
+  sa_build_device(c, c->d_x.as<u8>(), n, c->d_sa.as<i32>());
+  c->stats.sa_build_ms = t.stop();
+  if (sa_out) CK(cudaMemcpyAsync(sa_out, c->d_sa.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
+  CK(cudaStreamSynchronize(c->st));
+  c->have_sa = true;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_index_upload(cmsbwt_ctx *c, const uint8_t *x, uint32_t n, const int32_t *sa) {
+  if (!c || !x || n < 2 || n >= 0x7FFFFF00u) return fail(c, CMSBWT_E_ARG, "bad reference");
+  if (x[n - 1] != 0) return fail(c, CMSBWT_E_ARG, "reference is not augmented (x[n-1] != 0)");
+  c->have_index = false;
+  if (!sa) { int rc = cmsbwt_build_sa(c, x, n, nullptr); if (rc) return rc; }
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  if (sa) {
+    upload_x(c, x, n);
+    c->d_sa.alloc((size_t)n * 4, c->st);
+    CK(cudaMemcpyAsync(c->d_sa.p, sa, (size_t)n * 4, cudaMemcpyHostToDevice, c->st));
+    c->stats.sa_build_ms = 0;
+  }
+  Timer t(c->st);
+  index_build(c);
+  c->stats.index_build_ms = t.stop();
+  c->have_index = true;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+__global__ void k_plcp_prime(const u32 *G, u32 n, u32 *out) {
+  u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = G[i] - i;
+}
+
+int cmsbwt_index_download(cmsbwt_ctx *c, int32_t *sa, uint32_t *isa, uint32_t *pp, uint8_t *rb) {
+  if (!c || !c->have_index) return fail(c, CMSBWT_E_ARG, "no index");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  const u32 n = c->ix.n;
+  if (sa) CK(cudaMemcpyAsync(sa, c->d_sa.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
+  if (isa) CK(cudaMemcpyAsync(isa, c->d_isa.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
+  if (rb) CK(cudaMemcpyAsync(rb, c->d_rbwt.p, (size_t)n, cudaMemcpyDeviceToHost, c->st));
+  if (pp) {
+    DBuf t; t.alloc((size_t)n * 4, c->st);
+    k_plcp_prime<<<(n + 255) / 256, 256, 0, c->st>>>(c->ix.G, n, t.as<u32>());
+    CK(cudaMemcpyAsync(pp, t.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+  }
+  CK(cudaStreamSynchronize(c->st));
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+// ---- stages -------------------------------------------------------------------------------------
+static int ms_common(cmsbwt_ctx *c) {
+  GUARD_BEGIN
+  u8 last = 0;
+  CK(cudaMemcpyAsync(&last, c->text + (c->N - 1), 1, cudaMemcpyDeviceToHost, c->st));
+  CK(cudaStreamSynchronize(c->st));
+  if (last != 2) throw CmsErr{CMSBWT_E_ARG, "text must end with the 0x02 document separator"};
+  c->have_ms = c->have_sort = false;
+  c->launches = 0;
+  Timer t(c->st);
+  ms_stage(c);
+  c->stats.ms_ms = t.stop();
+  c->have_ms = true;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_ms_run(cmsbwt_ctx *c, const uint8_t *text, uint64_t N) {
+  if (!c || !c->have_index) return fail(c, CMSBWT_E_ARG, "index_upload first");
+  if (!text || N == 0) return fail(c, CMSBWT_E_ARG, "empty text");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  Timer t(c->st);
+  c->d_text.alloc(N + CMS_PAD, c->st);
+  CK(cudaMemsetAsync(c->d_text.as<u8>() + N, 2, CMS_PAD, c->st));
+  CK(cudaMemcpyAsync(c->d_text.p, text, N, cudaMemcpyHostToDevice, c->st));
+  c->stats.h2d_ms = t.stop();
+  c->text = c->d_text.as<u8>();
+  c->N = N;
+  GUARD_END(c)
+  return ms_common(c);
+}
+
+int cmsbwt_ms_run_device(cmsbwt_ctx *c, const void *d_text, uint64_t N) {
+  if (!c || !c->have_index) return fail(c, CMSBWT_E_ARG, "index_upload first");
+  if (!d_text || N == 0 || ((uintptr_t)d_text & 15)) return fail(c, CMSBWT_E_ARG, "bad device text");
+  cudaSetDevice(c->dev);
+  c->d_text.release();
+  c->text = (const u8 *)d_text;
+  c->N = N;
+  c->stats.h2d_ms = 0;
+  return ms_common(c);
+}
+
+int cmsbwt_set_ms_dump(cmsbwt_ctx *c, int enable) {
+  if (!c) return CMSBWT_E_ARG;
+  c->dump = enable != 0;
+  return CMSBWT_OK;
+}
+
+int cmsbwt_ms_download(cmsbwt_ctx *c, uint32_t *pos, uint32_t *len, uint8_t *sm, uint8_t *hd) {
+  if (!c || !c->have_ms || !c->dump_pos.p) return fail(c, CMSBWT_E_ARG, "no MS dump");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  const u64 N = c->N;
+  if (pos) CK(cudaMemcpyAsync(pos, c->dump_pos.p, N * 4, cudaMemcpyDeviceToHost, c->st));
+  if (len) CK(cudaMemcpyAsync(len, c->dump_len.p, N * 4, cudaMemcpyDeviceToHost, c->st));
+  if (sm) CK(cudaMemcpyAsync(sm, c->dump_sm.p, N, cudaMemcpyDeviceToHost, c->st));
+  if (hd) CK(cudaMemcpyAsync(hd, c->dump_head.p, N, cudaMemcpyDeviceToHost, c->st));
+  CK(cudaStreamSynchronize(c->st));
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_heads_sort(cmsbwt_ctx *c) {
+  if (!c || !c->have_ms) return fail(c, CMSBWT_E_ARG, "ms_run first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  Timer t(c->st);
+  sort_stage(c);
+  c->stats.sort_ms = t.stop();
+  c->have_sort = true;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+__global__ void k_widen(const u32 *a, u64 n, u64 *b) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) b[i] = a[i];
+}
+
+int cmsbwt_heads_download(cmsbwt_ctx *c, uint64_t *g, uint32_t *pos, uint32_t *len, uint64_t *within,
+                          uint64_t *off) {
+  if (!c || !c->have_ms) return fail(c, CMSBWT_E_ARG, "ms_run first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  const u64 H = c->H;
+  if (g) CK(cudaMemcpyAsync(g, c->h_gstart.p, H * 8, cudaMemcpyDeviceToHost, c->st));
+  if (pos) CK(cudaMemcpyAsync(pos, c->h_pos.p, H * 4, cudaMemcpyDeviceToHost, c->st));
+  if (len) CK(cudaMemcpyAsync(len, c->h_len.p, H * 4, cudaMemcpyDeviceToHost, c->st));
+  if (within) {
+    if (!c->have_sort) throw CmsErr{CMSBWT_E_ARG, "heads_sort first"};
+    DBuf t; t.alloc(H * 8, c->st);
+    k_widen<<<(u32)((H + 255) / 256), 256, 0, c->st>>>(c->h_within.as<u32>(), H, t.as<u64>());
+    CK(cudaMemcpyAsync(within, t.p, H * 8, cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+  }
+  if (off) {
+    if (!c->h_off.p) throw CmsErr{CMSBWT_E_ARG, "emit first"};
+    CK(cudaMemcpyAsync(off, c->h_off.p, H * 8, cudaMemcpyDeviceToHost, c->st));
+  }
+  CK(cudaStreamSynchronize(c->st));
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_emit(cmsbwt_ctx *c, int mode, uint64_t *out_bytes) {
+  if (!c || !c->have_sort) return fail(c, CMSBWT_E_ARG, "heads_sort first");
+  if (mode != CMSBWT_MODE_PLAIN && mode != CMSBWT_MODE_RLE) return fail(c, CMSBWT_E_ARG, "bad mode");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  Timer t(c->st);
+  emit_stage(c, mode);
+  c->stats.emit_ms = t.stop();
+  c->have_sort = false;            // coverage deltas were consumed
+  if (out_bytes) *out_bytes = c->out_bytes;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+const void *cmsbwt_result_device(const cmsbwt_ctx *c) {
+  if (!c) return nullptr;
+  return c->out_mode == CMSBWT_MODE_RLE ? c->d_rle.p : c->d_out.p;
+}
+
+int cmsbwt_result_download(cmsbwt_ctx *c, void *host_out, uint64_t cap) {
+  if (!c || !host_out || !c->d_out.p) return fail(c, CMSBWT_E_ARG, "emit first");
+  if (cap < c->out_bytes) return fail(c, CMSBWT_E_ARG, "output buffer too small");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
+  Timer t(c->st);
+  CK(cudaMemcpyAsync(host_out, cmsbwt_result_device(c), c->out_bytes, cudaMemcpyDeviceToHost, c->st));
+  c->stats.d2h_ms = t.stop();
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_run(cmsbwt_ctx *c, const uint8_t *text, uint64_t N, int mode, void *host_out, uint64_t cap,
+               uint64_t *out_bytes) {
+  int rc = cmsbwt_ms_run(c, text, N);
+  if (rc) return rc;
+  rc = cmsbwt_heads_sort(c);
+  if (rc) return rc;
+  uint64_t ob = 0;
+  rc = cmsbwt_emit(c, mode, &ob);
+  if (rc) return rc;
+  if (out_bytes) *out_bytes = ob;
+  return cmsbwt_result_download(c, host_out, cap);
+}
+
+}  // extern "C"

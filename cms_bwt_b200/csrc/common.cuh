@@ -1,0 +1,123 @@
+// Shared declarations of the cmsbwt_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/cmsbwt_b200.h"
+
+typedef uint8_t u8;
+typedef uint16_t u16;
+typedef uint32_t u32;
+typedef uint64_t u64;
+typedef int32_t i32;
+typedef int64_t i64;
+
+#define CMS_PAD 64          // readable bytes past the end of x / text
+#define CMS_TILE_W 64       // reference positions per counting tile (one 64-bit mask)
+#define CMS_CAP 32          // per-lane LCE budget (bytes) before a probe is handed to the warp
+
+struct CudaErr { cudaError_t e; const char *what; };
+
+#define CK(call)                                                                      \
+  do {                                                                                \
+    cudaError_t _e = (call);                                                          \
+    if (_e != cudaSuccess) throw CudaErr{_e, #call};                                  \
+  } while (0)
+
+struct CmsErr { int code; std::string msg; };
+
+// Device buffer owned by a context; freed stream-ordered.
+struct DBuf {
+  void *p = nullptr;
+  size_t bytes = 0;
+  cudaStream_t st = 0;
+  void alloc(size_t b, cudaStream_t s) {
+    release();
+    st = s;
+    bytes = b;
+    if (b == 0) b = 16;
+    CK(cudaMallocAsync(&p, b, s));
+  }
+  void release() {
+    if (p) cudaFreeAsync(p, st);
+    p = nullptr;
+    bytes = 0;
+  }
+  template <class T> T *as() const { return (T *)p; }
+  ~DBuf() { release(); }
+  DBuf() {}
+  DBuf(const DBuf &) = delete;
+  DBuf &operator=(const DBuf &) = delete;
+};
+
+struct Index {             // device-resident reference index
+  u32 n = 0;
+  int k = 0;               // k-mer table order
+  const u8 *x = nullptr;   // augmented reference, CMS_PAD bytes of 0xFF after it
+  const i32 *sa = nullptr;
+  const u32 *isa = nullptr;
+  const u32 *G = nullptr;  // G[q] = q + PLCP'[q]
+  const u8 *rbwt = nullptr;
+  const u32 *ktab = nullptr;   // 4^k + 1 entries: #suffixes < k-mer m
+};
+
+struct cmsbwt_ctx {
+  int dev = 0;
+  cudaStream_t st = 0;
+  std::string err;
+  cmsbwt_stats stats{};
+  u64 launches = 0;
+  // index
+  Index ix;
+  DBuf d_x, d_sa, d_isa, d_G, d_rbwt, d_ktab;
+  bool have_sa = false, have_index = false;
+  // text
+  const u8 *text = nullptr;
+  u64 N = 0;
+  DBuf d_text;
+  // stage 1 products (text-order heads)
+  u64 H = 0;
+  DBuf h_gstart, h_pos, h_len, h_cs;     // u64, u32, u32, u16 (ch | sm << 8)
+  bool dump = false;
+  DBuf dump_pos, dump_len, dump_sm, dump_head;
+  // stage 2 products
+  DBuf h_toNext, h_within, h_off, d_cov;  // u32, u32, u64, i32[n+1]
+  bool have_ms = false, have_sort = false;
+  // stage 3
+  DBuf d_out, d_rle;
+  u64 out_bytes = 0;
+  int out_mode = 0;
+  // params
+  i64 chunk_len = 8192;
+  i64 pool_div = 6;          // initial head-pool capacity = N / pool_div records
+  i64 kmer_k = 0;            // 0 = auto
+};
+
+#define LAUNCH(ctx) ((ctx)->launches++)
+
+// stage entry points (each throws CudaErr / CmsErr)
+void sa_build_device(cmsbwt_ctx *c, const u8 *d_x, u32 n, i32 *d_sa);
+void index_build(cmsbwt_ctx *c);
+void ms_stage(cmsbwt_ctx *c);
+void sort_stage(cmsbwt_ctx *c);
+void emit_stage(cmsbwt_ctx *c, int mode);
+
+// ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+// unaligned little-endian 8-byte load; the buffer base must be 8-byte aligned and padded.
+__device__ __forceinline__ u64 ld8u(const u8 *p) {
+  uintptr_t a = (uintptr_t)p;
+  unsigned sh = (unsigned)(a & 7) * 8;
+  const u64 *q = (const u64 *)(a & ~(uintptr_t)7);
+  u64 lo = __ldg(q);
+  if (sh == 0) return lo;
+  u64 hi = __ldg(q + 1);
+  return (lo >> sh) | (hi << (64 - sh));
+}
+__device__ __forceinline__ u32 cls_of(u32 pos, u32 len, u32 sm) {
+  u32 E = pos + len;
+  return sm ? E : 0xFFFFFFFFu - E;
+}
+#endif

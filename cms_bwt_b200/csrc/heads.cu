@@ -1,0 +1,308 @@
+// Stage 2: head linking, tail ranking, head keys and the count of non-head suffixes that precede
+// every head inside its bucket.  Replaces CMS-BWT-functions.cpp:1359-1603 (head linking, phrase
+// sort + keyed insertion, naming, libsais_int, next-rank substitution, prefix sums,
+// counterSmallerThanHead).  Formulation (checked on the CPU by
+// tests/model_pipeline.py):
+//   tail(i)   = text suffix at g_end = gstart + len (shared by all heads with that match end)
+//   label(t)  = (ISA[reference position of the suffix at g_end], cls of the phrase containing it)
+//   tailrank  = rank of the label sequence along next-tail pointers (prefix doubling)
+//   kappa(i)  = (cls_i, tailrank[tail(i)]),  cls = smaller ? E : ~E,  E = pos + len
+//   within(h) = #{phrases p : pos_p <= pos_h <= pos_p + toNext_p, kappa_p < kappa_h}
+#include "common.cuh"
+#include <cub/cub.cuh>
+#include <utility>
+
+// ---- linking (toNext :1373, coverage deltas :368-390, tail flags) -------------------------
+__global__ void k_link(const u64 *g, const u32 *pos, const u32 *len, u64 H, u32 *toNext,
+                       i32 *diff, u32 *tflag, u32 *sflag) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H) return;
+  u32 l = len[i];
+  u64 gi = g[i];
+  u32 tn = l == 0 ? 0 : (u32)(g[i + 1] - gi - 1);     // a sentinel always follows a real head
+  toNext[i] = tn;
+  u32 p = pos[i];
+  atomicAdd(diff + p, 1);
+  atomicAdd(diff + p + tn + 1, -1);
+  tflag[i] = (i == 0) || (gi + l != g[i - 1] + len[i - 1]);
+  sflag[i] = l == 0;
+}
+__global__ void k_tail_first(const u32 *tflag, const u32 *tail_incl, u64 H, u32 *tail_first) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H) return;
+  if (tflag[i]) tail_first[tail_incl[i] - 1] = (u32)i;
+}
+// label + next pointer of every tail
+__global__ void k_tail_label(const u64 *g, const u32 *pos, const u32 *len, const u16 *cs,
+                             const u32 *tail_incl, const u32 *sent_excl, const u32 *tail_first,
+                             const u32 *isa, u64 H, u32 Tn, u64 *label, u32 *next, u32 *tid) {
+  u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= Tn) return;
+  u32 f = tail_first[t];
+  u64 e = g[f] + len[f];
+  // j = last head with gstart <= e (gallop from f, then bisect)
+  u64 lo = f, step = 1;
+  while (lo + step < H && g[lo + step] <= e) { lo += step; step <<= 1; }
+  u64 hi = min(H, lo + step);          // g[hi] > e or hi == H
+  while (hi - lo > 1) {
+    u64 mid = (lo + hi) >> 1;
+    if (g[mid] <= e) lo = mid; else hi = mid;
+  }
+  u32 j = (u32)lo;
+  tid[t] = t;
+  if (len[j] == 0) {                   // the suffix at g_end is a document terminator
+    label[t] = (u64)sent_excl[j];
+    next[t] = t;
+  } else {
+    u32 pe = pos[j] + (u32)(e - g[j]);
+    u32 c = cls_of(pos[j], len[j], cs[j] >> 8);
+    label[t] = ((u64)isa[pe] << 32) | c;
+    next[t] = tail_incl[j] - 1;
+  }
+}
+// dense ranks from sorted keys
+__global__ void k_key_flags(const u64 *key, u32 n, u32 *flag) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) flag[j] = j > 0 && key[j] != key[j - 1];
+}
+__global__ void k_rank_scatter(const u32 *ids, const u32 *dense, u32 n, u32 *rank) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) rank[ids[j]] = dense[j];
+}
+__global__ void k_double(const u32 *rank, const u32 *next, u32 n, u64 *key, u32 *tid, u32 *next2) {
+  u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  u32 nx = next[t];
+  key[t] = ((u64)rank[t] << 32) | rank[nx];
+  tid[t] = t;
+  next2[t] = next[nx];
+}
+
+// ---- head keys and tile items ---------------------------------------------------------------
+__global__ void k_kappa_count(const u32 *pos, const u32 *len, const u16 *cs, const u32 *toNext,
+                              const u32 *tail_incl, const u32 *trank, u64 H, u64 *kappa,
+                              u32 *nitems) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H) return;
+  u32 p = pos[i];
+  kappa[i] = ((u64)cls_of(p, len[i], cs[i] >> 8) << 32) | trank[tail_incl[i] - 1];
+  nitems[i] = (p + toNext[i]) / CMS_TILE_W - p / CMS_TILE_W + 1;
+}
+// item = (tile, kappa) with payload (head id or ~0, lo, hi); one warp expands 32 heads
+__global__ void k_items(const u32 *pos, const u32 *toNext, const u64 *kappa, const u32 *nitems,
+                        const u64 *ioff, u64 H, u32 *it_tr, u64 *it_key, u64 *it_pay) {
+  const int lane = threadIdx.x & 31;
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  bool in = i < H;
+  u32 p = in ? pos[i] : 0, tn = in ? toNext[i] : 0, ni = in ? nitems[i] : 0;
+  u64 kp = in ? kappa[i] : 0, off = in ? ioff[i] : 0;
+  u32 t0 = p / CMS_TILE_W;
+  if (in && ni <= 4) {
+    for (u32 k = 0; k < ni; k++) {
+      u32 t = t0 + k, a = t * CMS_TILE_W;
+      u32 lo = max(p, a) - a, hi = min(p + tn, a + CMS_TILE_W - 1) - a;
+      it_tr[off + k] = (u32)kp;
+      it_key[off + k] = ((u64)t << 32) | (kp >> 32);
+      it_pay[off + k] = ((u64)(k == 0 ? (u32)i : 0xFFFFFFFFu) << 32) | (lo << 8) | hi;
+    }
+  }
+  unsigned big = __ballot_sync(0xffffffffu, in && ni > 4);
+  while (big) {
+    int src = __ffs(big) - 1;
+    big &= big - 1;
+    u32 bp = __shfl_sync(0xffffffffu, p, src), btn = __shfl_sync(0xffffffffu, tn, src);
+    u32 bni = __shfl_sync(0xffffffffu, ni, src), bt0 = __shfl_sync(0xffffffffu, t0, src);
+    u64 bkp = __shfl_sync(0xffffffffu, kp, src), boff = __shfl_sync(0xffffffffu, off, src);
+    u64 bi = i - lane + src;
+    for (u32 k = lane; k < bni; k += 32) {
+      u32 t = bt0 + k, a = t * CMS_TILE_W;
+      u32 lo = max(bp, a) - a, hi = min(bp + btn, a + CMS_TILE_W - 1) - a;
+      it_tr[boff + k] = (u32)bkp;
+      it_key[boff + k] = ((u64)t << 32) | (bkp >> 32);
+      it_pay[boff + k] = ((u64)(k == 0 ? (u32)bi : 0xFFFFFFFFu) << 32) | (lo << 8) | hi;
+    }
+  }
+}
+__global__ void k_iota(u32 *a, u64 n) {
+  u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) a[j] = (u32)j;
+}
+__global__ void k_gather_keys(const u32 *idx, const u64 *key, u64 n, u64 *out) {
+  u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) out[j] = key[idx[j]];
+}
+__global__ void k_tile_bounds(const u64 *skey, u64 n, u32 *tbeg, u32 *tend) {
+  u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  u32 t = (u32)(skey[j] >> 32);
+  if (j == 0 || (u32)(skey[j - 1] >> 32) != t) tbeg[t] = (u32)j;
+  if (j + 1 == n || (u32)(skey[j + 1] >> 32) != t) tend[t] = (u32)j + 1;
+}
+// one warp per tile: walk the tile's items in kappa order, 32 at a time; for every head item
+// count the earlier items whose interval holds the head's position.
+__global__ void k_tile_count(const u32 *sidx, const u64 *it_pay, const u32 *pos, const u32 *tbeg,
+                             const u32 *tend, u32 ntiles, u32 *within) {
+  const int lane = threadIdx.x & 31;
+  u32 t = (u32)(((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  if (t >= ntiles) return;
+  u32 b = tbeg[t], e = tend[t];
+  if (b >= e) return;
+  u32 run0 = 0, run1 = 0;           // items so far covering tile offsets lane / lane + 32
+  for (u32 j0 = b; j0 < e; j0 += 32) {
+    u32 j = j0 + lane;
+    u32 lo = 1, hi = 0, hid = 0xFFFFFFFFu, q = 0;
+    if (j < e) {
+      u64 pay = it_pay[sidx[j]];
+      hid = (u32)(pay >> 32); lo = (u32)(pay >> 8) & 0xFF; hi = (u32)pay & 0xFF;
+      if (hid != 0xFFFFFFFFu) q = pos[hid] - t * CMS_TILE_W;
+    }
+    // the select must happen on the reading lane, so fetch both counters and pick here
+    u32 r0 = __shfl_sync(0xffffffffu, run0, q & 31), r1 = __shfl_sync(0xffffffffu, run1, q & 31);
+    u32 base = q < 32 ? r0 : r1;
+    u32 cnt = 0, a0 = 0, a1 = 0;
+    for (int jj = 0; jj < 32; jj++) {
+      u32 l2 = __shfl_sync(0xffffffffu, lo, jj), h2 = __shfl_sync(0xffffffffu, hi, jj);
+      cnt += (jj < lane) & (l2 <= q) & (q <= h2);
+      a0 += (l2 <= (u32)lane) & ((u32)lane <= h2);
+      a1 += (l2 <= (u32)lane + 32) & ((u32)lane + 32 <= h2);
+    }
+    if (hid != 0xFFFFFFFFu) within[hid] = base + cnt;
+    run0 += a0; run1 += a1;
+  }
+}
+
+struct Tmp {                      // growable CUB scratch
+  DBuf b;
+  void need(size_t bytes, cudaStream_t st) { if (bytes > b.bytes) b.alloc(bytes, st); }
+};
+
+void sort_stage(cmsbwt_ctx *c) {
+  cudaStream_t st = c->st;
+  const u64 H = c->H;
+  const u32 n = c->ix.n;
+  const int B = 256;
+  const u32 gH = (u32)((H + B - 1) / B);
+  const u64 *g = c->h_gstart.as<u64>();
+  const u32 *pos = c->h_pos.as<u32>(), *len = c->h_len.as<u32>();
+  const u16 *cs = c->h_cs.as<u16>();
+  Tmp tmp;
+  size_t tb;
+  // ---- link ----
+  c->h_toNext.alloc(H * 4, st);
+  c->d_cov.alloc(((size_t)n + 1) * 4, st);
+  CK(cudaMemsetAsync(c->d_cov.p, 0, ((size_t)n + 1) * 4, st));
+  DBuf tflag, sflag, tincl, sexcl;
+  tflag.alloc(H * 4, st); sflag.alloc(H * 4, st); tincl.alloc(H * 4, st); sexcl.alloc(H * 4, st);
+  k_link<<<gH, B, 0, st>>>(g, pos, len, H, c->h_toNext.as<u32>(), c->d_cov.as<i32>(),
+                           tflag.as<u32>(), sflag.as<u32>());
+  LAUNCH(c);
+  tb = 0; cub::DeviceScan::InclusiveSum(nullptr, tb, tflag.as<u32>(), tincl.as<u32>(), (int)H, st);
+  tmp.need(tb, st);
+  CK(cub::DeviceScan::InclusiveSum(tmp.b.p, tb, tflag.as<u32>(), tincl.as<u32>(), (int)H, st));
+  tb = 0; cub::DeviceScan::ExclusiveSum(nullptr, tb, sflag.as<u32>(), sexcl.as<u32>(), (int)H, st);
+  tmp.need(tb, st);
+  CK(cub::DeviceScan::ExclusiveSum(tmp.b.p, tb, sflag.as<u32>(), sexcl.as<u32>(), (int)H, st));
+  c->launches += 2;
+  u32 Tn = 0, lastS = 0, lastF = 0;
+  CK(cudaMemcpyAsync(&Tn, tincl.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&lastS, sexcl.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&lastF, sflag.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  c->stats.n_docs = (u64)lastS + lastF;
+  c->stats.n_tails = Tn;
+  // ---- tails ----
+  const u32 gT = (Tn + B - 1) / B;
+  DBuf tfirst, label, label2, next, next2, tid, tid2, trank, fl, dense;
+  tfirst.alloc((size_t)Tn * 4, st); label.alloc((size_t)Tn * 8, st); label2.alloc((size_t)Tn * 8, st);
+  next.alloc((size_t)Tn * 4, st); next2.alloc((size_t)Tn * 4, st); tid.alloc((size_t)Tn * 4, st);
+  tid2.alloc((size_t)Tn * 4, st); trank.alloc((size_t)Tn * 4, st); fl.alloc((size_t)Tn * 4, st);
+  dense.alloc((size_t)Tn * 4, st);
+  k_tail_first<<<gH, B, 0, st>>>(tflag.as<u32>(), tincl.as<u32>(), H, tfirst.as<u32>());
+  k_tail_label<<<gT, B, 0, st>>>(g, pos, len, cs, tincl.as<u32>(), sexcl.as<u32>(), tfirst.as<u32>(),
+                                 c->ix.isa, H, Tn, label.as<u64>(), next.as<u32>(), tid.as<u32>());
+  c->launches += 2;
+  u32 rounds = 0;
+  while (true) {
+    tb = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, label.as<u64>(), label2.as<u64>(), tid.as<u32>(),
+                                    tid2.as<u32>(), (int)Tn, 0, 64, st);
+    tmp.need(tb, st);
+    CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, label.as<u64>(), label2.as<u64>(), tid.as<u32>(),
+                                       tid2.as<u32>(), (int)Tn, 0, 64, st));
+    k_key_flags<<<gT, B, 0, st>>>(label2.as<u64>(), Tn, fl.as<u32>());
+    tb = 0; cub::DeviceScan::InclusiveSum(nullptr, tb, fl.as<u32>(), dense.as<u32>(), (int)Tn, st);
+    tmp.need(tb, st);
+    CK(cub::DeviceScan::InclusiveSum(tmp.b.p, tb, fl.as<u32>(), dense.as<u32>(), (int)Tn, st));
+    k_rank_scatter<<<gT, B, 0, st>>>(tid2.as<u32>(), dense.as<u32>(), Tn, trank.as<u32>());
+    c->launches += 6;
+    u32 last = 0;
+    CK(cudaMemcpyAsync(&last, dense.as<u32>() + (Tn - 1), 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (last + 1 == Tn) break;
+    if (++rounds > 64) throw CmsErr{CMSBWT_E_INTERNAL, "tail ranking did not converge"};
+    k_double<<<gT, B, 0, st>>>(trank.as<u32>(), next.as<u32>(), Tn, label.as<u64>(), tid.as<u32>(),
+                               next2.as<u32>());
+    LAUNCH(c);
+    std::swap(next.p, next2.p);
+  }
+  c->stats.rank_rounds = rounds;
+  // ---- kappa + items ----
+  DBuf kappa, nitems, ioff;
+  kappa.alloc(H * 8, st); nitems.alloc((H + 1) * 4, st); ioff.alloc((H + 1) * 8, st);
+  CK(cudaMemsetAsync(nitems.p, 0, (H + 1) * 4, st));
+  k_kappa_count<<<gH, B, 0, st>>>(pos, len, cs, c->h_toNext.as<u32>(), tincl.as<u32>(),
+                                  trank.as<u32>(), H, kappa.as<u64>(), nitems.as<u32>());
+  tb = 0; cub::DeviceScan::ExclusiveSum(nullptr, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st);
+  tmp.need(tb, st);
+  CK(cub::DeviceScan::ExclusiveSum(tmp.b.p, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st));
+  c->launches += 3;
+  u64 I = 0;
+  CK(cudaMemcpyAsync(&I, ioff.as<u64>() + H, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (I >= 0x7FFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^31 tile items on one device"};
+  c->stats.n_items = I;
+  // free what is no longer needed before the big item arrays
+  tfirst.release(); label.release(); label2.release(); next.release(); next2.release();
+  tid.release(); tid2.release(); fl.release(); dense.release(); tflag.release(); sflag.release();
+  DBuf it_tr, it_tr2, it_key, it_key2, it_pay, idx, idx2;
+  it_tr.alloc(I * 4, st); it_tr2.alloc(I * 4, st); it_key.alloc(I * 8, st); it_key2.alloc(I * 8, st);
+  it_pay.alloc(I * 8, st); idx.alloc(I * 4, st); idx2.alloc(I * 4, st);
+  k_items<<<gH, B, 0, st>>>(pos, c->h_toNext.as<u32>(), kappa.as<u64>(), nitems.as<u32>(),
+                            ioff.as<u64>(), H, it_tr.as<u32>(), it_key.as<u64>(), it_pay.as<u64>());
+  LAUNCH(c);
+  // stable LSD: by tailrank (low word of kappa), then by (tile, cls)
+  {
+    const u32 gI = (u32)((I + B - 1) / B);
+    k_iota<<<gI, B, 0, st>>>(idx2.as<u32>(), I);
+    int tbits = 1; while ((1ull << tbits) < (u64)Tn) tbits++;
+    tb = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, it_tr.as<u32>(), it_tr2.as<u32>(), idx2.as<u32>(),
+                                    idx.as<u32>(), (int)I, 0, tbits, st);
+    tmp.need(tb, st);
+    CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_tr.as<u32>(), it_tr2.as<u32>(),
+                                       idx2.as<u32>(), idx.as<u32>(), (int)I, 0, tbits, st));
+    k_gather_keys<<<gI, B, 0, st>>>(idx.as<u32>(), it_key.as<u64>(), I, it_key2.as<u64>());
+    u32 ntiles = n / CMS_TILE_W + 1;
+    int kb = 33; while ((1ull << (kb - 32)) < (u64)ntiles) kb++;
+    tb = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
+                                    idx2.as<u32>(), (int)I, 0, kb, st);
+    tmp.need(tb, st);
+    CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
+                                       idx2.as<u32>(), (int)I, 0, kb, st));
+    c->launches += 12;
+    DBuf tbeg, tend;
+    tbeg.alloc((size_t)ntiles * 4, st); tend.alloc((size_t)ntiles * 4, st);
+    CK(cudaMemsetAsync(tbeg.p, 0, (size_t)ntiles * 4, st));
+    CK(cudaMemsetAsync(tend.p, 0, (size_t)ntiles * 4, st));
+    k_tile_bounds<<<gI, B, 0, st>>>(it_key.as<u64>(), I, tbeg.as<u32>(), tend.as<u32>());
+    c->h_within.alloc(H * 4, st);
+    u64 threads = (u64)ntiles * 32;
+    k_tile_count<<<(u32)((threads + B - 1) / B), B, 0, st>>>(idx2.as<u32>(), it_pay.as<u64>(), pos,
+                                                           tbeg.as<u32>(), tend.as<u32>(), ntiles,
+                                                           c->h_within.as<u32>());
+    c->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+  }
+}

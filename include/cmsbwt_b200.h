@@ -1,0 +1,139 @@
+/*
+ * cmsbwt_b200 -- C ABI of the B200-native CMS-BWT hot path.
+ *
+ * The reference (fmasillo/CMS-BWT) exposes no FFI; its hot path sits behind one C++ call,
+ *     void computeBWT(Args arg, std::string& refFile, std::string& collFile)      CMS-BWT.h:69
+ * which runs initialize_reference (CMS-BWT-functions.cpp:151-310) and then
+ * process_collection_{small,large}_reference (:312-1091 / :1093-1785) on file-scope globals.
+ * This header is what a binding of that path would call instead: the three stages (matching
+ * statistics, head sort, emit) plus the index upload that precedes them, with plain pointers
+ * and sizes.  INTEGRATION.md shows the reference-side stub.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative CMSBWT_E_* code; nothing throws, nothing
+ *     calls exit() (the reference exit()s on errors, main.cpp:91-115, :156-160,:648-652);
+ *   - `x` is the AUGMENTED reference (reference :208-213 trim + :231-237 augmentation: every byte
+ *     3..127 that does not occur, then 0x01, 0x00); n = its length (the reference's _n), n < 2^31;
+ *   - `text` is the parsed collection: every document followed by the separator 0x02
+ *     (reference :1138-1213: documents are closed by header / blank lines; _sx += 0x02);
+ *     bytes must be in [3,127] or 0x02; N = its length (the reference's _sn worth of symbols);
+ *   - host pointers unless the name says _device; device buffers passed in must be 16-byte
+ *     aligned and have at least 64 readable bytes after their last element;
+ *   - one context per GPU; calls on one context are serialised by the caller (the reference is
+ *     single threaded); contexts on different GPUs may be driven from different host threads.
+ */
+#ifndef CMSBWT_B200_H
+#define CMSBWT_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cmsbwt_ctx cmsbwt_ctx;
+
+enum {
+  CMSBWT_OK = 0,
+  CMSBWT_E_CUDA = -1,        /* a CUDA call failed; see cmsbwt_last_error() */
+  CMSBWT_E_ARG = -2,         /* bad argument / call order */
+  CMSBWT_E_LIMIT = -3,       /* input exceeds an index-width limit of this build */
+  CMSBWT_E_SYMBOL = -4,      /* text or reference holds a byte outside the allowed set */
+  CMSBWT_E_INTERNAL = -5,    /* self-check failed (coverage total != N etc.) */
+  CMSBWT_E_NOMEM = -6
+};
+
+enum { CMSBWT_MODE_PLAIN = 0, CMSBWT_MODE_RLE = 1 };
+
+/* Stage timings (CUDA events on the context's stream), milliseconds, and counters.
+ * Mirrors what the reference prints to <out>.log (e.g. :248-252 "Computed SA in", :618-622
+ * "Time to compute matching statistics", :907-917). */
+typedef struct {
+  double sa_build_ms;       /* GPU suffix array (only when cmsbwt_index_upload got sa == NULL) */
+  double index_build_ms;    /* ISA, PLCP', G, reference BWT, k-mer table         (:263-297) */
+  double ms_ms;             /* stage 1: matching statistics + head compaction    (:1138-1213) */
+  double sort_ms;           /* stage 2: linking, tail ranking, head keys, counting (:1359-1603) */
+  double emit_ms;           /* stage 3: coverage->offsets, fill, head scatter, RLE (:1618-1777) */
+  double h2d_ms, d2h_ms;
+  uint64_t n_heads;         /* the reference's headNumber (incl. one sentinel per document) */
+  uint64_t n_docs;          /* the reference's D-1 */
+  uint64_t n_tails;         /* distinct match-end text positions */
+  uint64_t n_items;         /* (phrase, tile) incidences used by the counting step */
+  uint64_t n_runs;          /* records written in RLE mode */
+  uint32_t rank_rounds;     /* doubling rounds of the tail ranking */
+  uint32_t kmer_k;
+  uint64_t kernel_launches; /* launches issued by ms_run + heads_sort + emit of the last job */
+} cmsbwt_stats;
+
+/* replaces: process start-up of the reference (no equivalent; it has no device). */
+int cmsbwt_ctx_create(int device_ordinal, cmsbwt_ctx **out);
+void cmsbwt_ctx_destroy(cmsbwt_ctx *ctx);
+const char *cmsbwt_last_error(const cmsbwt_ctx *ctx);
+int cmsbwt_get_stats(const cmsbwt_ctx *ctx, cmsbwt_stats *out);
+
+/* Host-side loaders with the reference's exact semantics (helpers for bindings and tests).
+ * cmsbwt_augment: :208-213 + :231-237.  `out` must hold len + 127 bytes; returns n (or <0). */
+int64_t cmsbwt_augment(const uint8_t *ref, int64_t len, uint8_t *out);
+/* cmsbwt_read_reference: :171-199 (FASTA records concatenated / raw bytes). out: size bytes. */
+int64_t cmsbwt_read_reference(const uint8_t *file, int64_t size, uint8_t *out);
+/* cmsbwt_parse_collection: :1138-1140,:1257-1275 incl. the -p rule.  out_text: size+2 bytes.
+ * Returns N; *ndocs = number of documents. */
+int64_t cmsbwt_parse_collection(const uint8_t *file, int64_t size, uint64_t prefix,
+                                uint8_t *out_text, int64_t *ndocs);
+
+/* replaces: libsais(x, sa, n, 0, NULL) at :247 when the caller has no host SA builder.
+ * GPU prefix doubling; sa_out (host, n entries) may be NULL to keep it on the device only. */
+int cmsbwt_build_sa(cmsbwt_ctx *ctx, const uint8_t *x, uint32_t n, int32_t *sa_out);
+
+/* replaces: initialize_reference :246-297 after the SA: constructISA (:3-9, :263),
+ * libsais_plcp/lcp (:270-271), PLCP' (:272-274), reference BWT (:294-297); the rmq_tree
+ * (:284) is superseded by a k-mer interval table + exact search.
+ * sa == NULL: the SA is built on the GPU (cmsbwt_build_sa). */
+int cmsbwt_index_upload(cmsbwt_ctx *ctx, const uint8_t *x, uint32_t n, const int32_t *sa);
+/* copies back index arrays for parity tests (any pointer may be NULL).
+ * isa[n], plcp_prime[n] (= G[i]-i), ref_bwt[n], sa[n] */
+int cmsbwt_index_download(cmsbwt_ctx *ctx, int32_t *sa, uint32_t *isa, uint32_t *plcp_prime,
+                          uint8_t *ref_bwt);
+
+/* replaces: stage 1, the per-document MS driver :1138-1213 (small path :344-419) with
+ * computeMSFactorAt :45-88, binarySearchLB/RB :94-149, the PLCP' skip loop :1176-1185 and the
+ * head records of match.h:5-16.  Host text is copied to the device first. */
+int cmsbwt_ms_run(cmsbwt_ctx *ctx, const uint8_t *text, uint64_t N);
+/* same, text already resident in device memory (not copied, must stay valid until emit). */
+int cmsbwt_ms_run_device(cmsbwt_ctx *ctx, const void *d_text, uint64_t N);
+/* parity hook: per-position matching statistics of the last ms_run, which
+ * must have been preceded by cmsbwt_set_ms_dump(ctx, 1).  Arrays of N entries (may be NULL). */
+int cmsbwt_set_ms_dump(cmsbwt_ctx *ctx, int enable);
+int cmsbwt_ms_download(cmsbwt_ctx *ctx, uint32_t *pos, uint32_t *len, uint8_t *smaller,
+                       uint8_t *is_head);
+
+/* replaces: stage 2, :1359-1603 (head linking, phrase sort / keyed insertion, naming,
+ * libsais_int :1456, next-rank substitution, prefix sums, counterSmallerThanHead). */
+int cmsbwt_heads_sort(cmsbwt_ctx *ctx);
+/* intermediate arrays for parity tests (text-order heads; any pointer may be NULL):
+ * gstart[H], pos[H], len[H], within[H] (suffixes of the same bucket that precede the head),
+ * offset[H] (final position in the BWT). */
+int cmsbwt_heads_download(cmsbwt_ctx *ctx, uint64_t *gstart, uint32_t *pos, uint32_t *len,
+                          uint64_t *within, uint64_t *offset);
+
+/* replaces: stage 3, bucket inversion :1618-1628 and the writers :1631-1694 (plain) /
+ * :1695-1777 (RLE: 9-byte records, LE uint64 run + uint8 symbol, maximal runs -- i.e. the
+ * writer with its remainder flush after the sub-bucket loop).
+ * Leaves the result on the device; *out_bytes = N (plain) or 9*R (RLE). */
+int cmsbwt_emit(cmsbwt_ctx *ctx, int mode, uint64_t *out_bytes);
+/* device pointer of the last emit's result (valid until the next ms_run / destroy). */
+const void *cmsbwt_result_device(const cmsbwt_ctx *ctx);
+/* copy the last emit's result to host memory (cap >= out_bytes). */
+int cmsbwt_result_download(cmsbwt_ctx *ctx, void *host_out, uint64_t cap);
+
+/* Whole path on host buffers: ms_run + heads_sort + emit + result_download.  This is the call
+ * that stands where computeBWT's process_collection_* call stands (:1792-1796). */
+int cmsbwt_run(cmsbwt_ctx *ctx, const uint8_t *text, uint64_t N, int mode, void *host_out,
+               uint64_t cap, uint64_t *out_bytes);
+
+/* tuning knobs (0 = default): chunk length of the MS kernel, tile width is fixed at 64. */
+int cmsbwt_set_param(cmsbwt_ctx *ctx, const char *name, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,157 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against the
+oracle (oracle/cms_oracle.c) on seeded inputs and against the committed golden fixtures made
+from the unmodified reference binary.  Integer/byte work: the bar is bit-exact."""
+import glob
+import os
+import numpy as np
+import pytest
+
+import cms_bwt_b200 as P
+import oracle_lib as O
+import fuzz_cases
+import gen_synth
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = P.Context(0)
+    yield c
+    c.close()
+
+
+def _inputs(ref_file, coll_file, prefix=P.UINT64_MAX):
+    x = P.augment(P.read_reference(ref_file))
+    text, nd = P.parse_collection(coll_file, prefix)
+    return x, text
+
+
+def _check_case(ctx, x, text, want_bwt=None, desc="", chunk=None, check_ms=True):
+    o = O.Oracle(x)
+    if chunk:
+        ctx.set_param("chunk_len", chunk)
+    ctx.index_upload(x)                       # SA built on the GPU
+    ix = ctx.index_download()
+    assert np.array_equal(ix["sa"], o.sa), "SA " + desc
+    assert np.array_equal(ix["isa"], o.isa), "ISA " + desc
+    assert np.array_equal(ix["plcp_prime"].astype(np.int64), o.plcp_prime.astype(np.int64)), "PLCP' " + desc
+    assert np.array_equal(ix["ref_bwt"], o.ref_bwt), "refBWT " + desc
+    ctx.set_ms_dump(check_ms)
+    ctx.ms_run(text)
+    if check_ms:
+        pos, ln, sm, hd = ctx.ms_download()
+        opos, oln, osm, ohd = o.ms(text)
+        assert np.array_equal(ln, oln), "MS len " + desc
+        assert np.array_equal(pos, opos), "MS pos " + desc
+        assert np.array_equal(sm, osm), "MS smaller " + desc
+        assert np.array_equal(hd, ohd), "MS heads " + desc
+    ctx.heads_sort()
+    ctx.emit(P.MODE_PLAIN)
+    got = ctx.result_download().copy()
+    want = o.bwt(text) if want_bwt is None else want_bwt
+    if not np.array_equal(got, want):
+        bad = np.flatnonzero(got != want) if len(got) == len(want) else []
+        raise AssertionError("BWT %s: %d mismatches, first %s" % (desc, len(bad), bad[:8]))
+    # RLE mode
+    ctx.ms_run(text)
+    ctx.heads_sort()
+    ctx.emit(P.MODE_RLE)
+    rl = ctx.result_download().copy()
+    assert np.array_equal(rl, O.rle(want)), "RLBWT " + desc
+    ctx.set_param("chunk_len", 8192)
+    return ctx.stats()
+
+
+def test_golden_fixtures(ctx):
+    files = sorted(glob.glob(os.path.join(GOLDEN, "*.npz")))
+    assert files
+    for f in files:
+        z = np.load(f)
+        x, text = _inputs(z["ref_file"].tobytes(), z["coll_file"].tobytes(), int(z["prefix"]))
+        _check_case(ctx, x, text, z["bwt"], os.path.basename(f))
+        # also with tiny chunks (exercises chunk borders inside phrases and documents)
+        _check_case(ctx, x, text, z["bwt"], os.path.basename(f) + " chunk=64", chunk=64)
+
+
+@pytest.mark.parametrize("block", range(4))
+def test_fuzz_vs_oracle(ctx, block):
+    for seed in range(block * 50, block * 50 + 50):
+        c = fuzz_cases.make_case(seed)
+        x, text = _inputs(c["ref_file"], c["coll_file"])
+        if len(text) == 0:
+            continue
+        _check_case(ctx, x, text, None, c["desc"], chunk=[64, 100, 8192][seed % 3])
+
+
+def test_config1_scaled_vs_oracle(ctx):
+    ref, copies = gen_synth.make_collection(200000, 6, 0.001, 7)
+    x = P.augment(ref)
+    text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)      # leading empty document
+    st = _check_case(ctx, x, text, None, "200k x6")
+    assert st["n_docs"] == 7
+
+
+def test_sv_and_dense_divergence(ctx):
+    ref, copies = gen_synth.make_collection(100000, 5, 0.01, 5, svs=4)
+    x = P.augment(ref)
+    text = O.docs_to_text(copies)
+    _check_case(ctx, x, text, None, "100k x5 1% + SVs")
+
+
+def test_many_short_documents(ctx):
+    ref, copies = gen_synth.make_collection(3000, 2000, 0.002, 9)
+    x = P.augment(ref)
+    text = O.docs_to_text(copies)
+    _check_case(ctx, x, text, None, "3k x2000", check_ms=True)
+
+
+def test_duplicate_documents_and_identity(ctx):
+    rng = np.random.default_rng(1)
+    ref = gen_synth.ACGT[rng.integers(0, 4, 5000)]
+    x = P.augment(ref)
+    docs = [ref.copy() for _ in range(40)] + [ref[100:900].copy() for _ in range(10)]
+    text = O.docs_to_text(docs)
+    st = _check_case(ctx, x, text, None, "40 exact copies")
+    assert st["rank_rounds"] >= 0
+
+
+def test_host_sa_path_matches_gpu_sa(ctx):
+    """index_upload with a host SA (the reference's libsais route) gives the same output."""
+    ref, copies = gen_synth.make_collection(50000, 4, 0.002, 3)
+    x = P.augment(ref)
+    text = O.docs_to_text(copies)
+    o = O.Oracle(x)
+    ctx.index_upload(x, o.sa)
+    got = ctx.run(text, P.MODE_PLAIN).copy()
+    assert np.array_equal(got, o.bwt(text))
+
+
+def test_bad_symbol_is_reported(ctx):
+    x = P.augment(np.frombuffer(b"ACGTACGTAGCTAGCTAGGATC", dtype=np.uint8))
+    ctx.index_upload(x)
+    text = np.frombuffer(b"ACGT\x90CGT\x02", dtype=np.uint8)
+    with pytest.raises(P.CmsBwtError) as e:
+        ctx.run(text)
+    assert e.value.code == -4
+
+
+def test_round_trip_properties_medium(ctx):
+    """Size-independent properties on an input too large for the oracle's O(N) python checks:
+    symbol histogram of the BWT equals that of the text; RLE decodes to the plain BWT; output
+    is identical for different chunk lengths."""
+    ref, copies = gen_synth.make_collection(1000000, 10, 0.001, 42)
+    x = P.augment(ref)
+    text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    ctx.index_upload(x)
+    a = ctx.run(text, P.MODE_PLAIN).copy()
+    assert np.array_equal(np.bincount(a, minlength=256), np.bincount(text, minlength=256))
+    ctx.set_param("chunk_len", 1000)
+    b = ctx.run(text, P.MODE_PLAIN).copy()
+    ctx.set_param("chunk_len", 8192)
+    assert np.array_equal(a, b)
+    rl = ctx.run(text, P.MODE_RLE).copy()
+    assert np.array_equal(O.rle_decode(rl), a)
+    want = O.Oracle(x, ctx.index_download()["sa"]).bwt(text)
+    assert np.array_equal(a, want)

@@ -1,0 +1,61 @@
+"""CPU-only checks of the product's host side: the C-ABI library loads, exports every symbol
+include/cmsbwt_b200.h declares, and its host loaders (reference reader, augmentation, collection
+parser with -p) agree with the oracle on the fuzz families and the golden fixtures.  No compute
+call is made (there is no GPU here and no CPU fallback)."""
+import glob
+import os
+import re
+import numpy as np
+import pytest
+
+import cms_bwt_b200 as P
+import oracle_lib as O
+import fuzz_cases
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "cmsbwt_b200.h")).read()
+    declared = set(re.findall(r"\b(cmsbwt_[a-z_0-9]+)\s*\(", hdr))
+    declared.discard("cmsbwt_ctx")
+    L = P.lib()
+    for name in sorted(declared):
+        assert hasattr(L, name), name
+    assert declared == set(P.EXPORTS)
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(P.CmsBwtError):
+        P.Context(0)
+
+
+def test_host_loaders_match_oracle_fuzz():
+    for seed in range(300):
+        c = fuzz_cases.make_case(seed)
+        r1, r2 = P.read_reference(c["ref_file"]), O.read_reference(c["ref_file"])
+        assert np.array_equal(r1, r2), c["desc"]
+        assert np.array_equal(P.augment(r1), O.augment(r2)), c["desc"]
+        t1, nd = P.parse_collection(c["coll_file"])
+        t2, ds = O.parse_collection(c["coll_file"])
+        assert np.array_equal(t1, t2), c["desc"]
+        assert nd == len(ds) - 1
+
+
+def test_host_parser_prefix_matches_oracle():
+    for f in sorted(glob.glob(os.path.join(GOLDEN, "*.npz"))):
+        z = np.load(f)
+        coll = z["coll_file"].tobytes()
+        for pfx in [int(z["prefix"]), 1, 2, 7, 100, 2001, 2002, 2003, len(coll) - 1, len(coll)]:
+            t1, _ = P.parse_collection(coll, pfx)
+            t2, _ = O.parse_collection(coll, pfx)
+            assert np.array_equal(t1, t2), (f, pfx)
+
+
+def test_augment_rejects_reserved_bytes():
+    with pytest.raises(P.CmsBwtError):
+        P.augment(np.frombuffer(b"AC\x02GT", dtype=np.uint8))
