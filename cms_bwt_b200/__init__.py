@@ -30,7 +30,7 @@ EXPORTS = [
 class Stats(C.Structure):
     _fields_ = [("sa_build_ms", C.c_double), ("index_build_ms", C.c_double), ("ms_ms", C.c_double),
                 ("sort_ms", C.c_double), ("emit_ms", C.c_double), ("h2d_ms", C.c_double),
-                ("d2h_ms", C.c_double), ("n_heads", C.c_uint64), ("n_docs", C.c_uint64),
+                ("d2h_ms", C.c_double), ("ms_kernel_ms", C.c_double), ("n_heads", C.c_uint64), ("n_docs", C.c_uint64),
                 ("n_tails", C.c_uint64), ("n_items", C.c_uint64), ("n_runs", C.c_uint64),
                 ("rank_rounds", C.c_uint32), ("kmer_k", C.c_uint32),
                 ("kernel_launches", C.c_uint64)]

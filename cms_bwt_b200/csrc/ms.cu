@@ -349,7 +349,11 @@ void ms_stage(cmsbwt_ctx *c) {
     P.dsm = c->dump_sm.as<u8>(); P.dhead = c->dump_head.as<u8>();
     u64 want_blocks = (nchunks + 3) / 4;
     u32 grid = (u32)min(want_blocks, (u64)sms * 12);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, st);
     k_ms<<<grid, 128, 0, st>>>(P);
+    cudaEventRecord(e1, st);
     LAUNCH(c);
     CK(cudaGetLastError());
     // chunk_off = exclusive scan over nchunks+1 entries (ccnt has nchunks; the extra reads 0)
@@ -361,6 +365,8 @@ void ms_stage(cmsbwt_ctx *c) {
     CK(cudaMemcpyAsync(&lastoff, coff.as<u64>() + (nchunks - 1), 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(&lastcnt, ccnt.as<u32>() + (nchunks - 1), 4, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    { float ms = 0; cudaEventElapsedTime(&ms, e0, e1); c->stats.ms_kernel_ms = ms; }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
     if (hf[1]) throw CmsErr{CMSBWT_E_SYMBOL, "text holds a byte that does not occur in the augmented reference"};
     const u64 H = lastoff + lastcnt;
     if (hf[0]) {                 // pool exhausted: counts are exact, rerun with the exact size

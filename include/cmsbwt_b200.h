@@ -54,6 +54,7 @@ typedef struct {
   double sort_ms;           /* stage 2: linking, tail ranking, head keys, counting (:1359-1603) */
   double emit_ms;           /* stage 3: coverage->offsets, fill, head scatter, RLE (:1618-1777) */
   double h2d_ms, d2h_ms;
+  double ms_kernel_ms;      /* the matching-statistics kernel alone (k_ms), last attempt */
   uint64_t n_heads;         /* the reference's headNumber (incl. one sentinel per document) */
   uint64_t n_docs;          /* the reference's D-1 */
   uint64_t n_tails;         /* distinct match-end text positions */

@@ -1,0 +1,74 @@
+"""Device-side synthetic collections (same mutation model as tools/gen_synth.py / SURVEY.md 8(d)),
+built with torch on the GPU so that the 5.9 Gbp workload is ready in seconds.  Bench tooling only.
+
+reference = i.i.d. uniform ACGT; every copy independently: per position u~U(0,1):
+u < d/3 substitute by another base, d/3 <= u < 2d/3 delete, 2d/3 <= u < d keep + insert one base.
+The text is laid out as the reference's parser would produce it from a FASTA collection
+(one leading empty document, then every copy followed by the 0x02 separator).
+"""
+import torch
+
+ACGT = (65, 67, 71, 84)
+
+
+def make_reference(n, gen, dev):
+    lut = torch.tensor(ACGT, dtype=torch.uint8, device=dev)
+    return lut[torch.randint(0, 4, (n,), generator=gen, device=dev)]
+
+
+def mutate(ref, codes, div, gen, dev):
+    n = ref.numel()
+    lut = torch.tensor(ACGT, dtype=torch.uint8, device=dev)
+    r = torch.rand(n, generator=gen, device=dev)
+    snp = r < div / 3
+    dele = (r >= div / 3) & (r < 2 * div / 3)
+    ins = (r >= 2 * div / 3) & (r < div)
+    s = ref.clone()
+    k = int(snp.sum())
+    if k:
+        s[snp] = lut[(codes[snp] + torch.randint(1, 4, (k,), generator=gen, device=dev)) % 4]
+    reps = torch.ones(n, dtype=torch.int64, device=dev)
+    reps[dele] = 0
+    reps[ins] = 2
+    t = torch.repeat_interleave(s, reps)
+    ip = (torch.cumsum(reps, 0) - 1)[ins]
+    if ip.numel():
+        t[ip] = lut[torch.randint(0, 4, (ip.numel(),), generator=gen, device=dev)]
+    return t
+
+
+def make_text(ref_bp, copies, div, seed, dev, pad=64, leading_empty=True, first_copy=0, ncopies=None):
+    """-> (ref uint8[ref_bp] on dev, text uint8[N + pad] on dev, N, ndocs).  Copies
+    first_copy .. first_copy+ncopies-1 of the `copies`-copy collection (every copy has its own
+    generator stream, so a shard of the collection is reproducible on any rank)."""
+    g0 = torch.Generator(device=dev)
+    g0.manual_seed(seed)
+    ref = make_reference(ref_bp, g0, dev)
+    codes = torch.zeros(ref_bp, dtype=torch.int64, device=dev)
+    codes[ref == 67] = 1
+    codes[ref == 71] = 2
+    codes[ref == 84] = 3
+    if ncopies is None:
+        ncopies = copies - first_copy
+    cap = int(ncopies * (ref_bp * (1 + div) + 64) + 64 + pad)
+    text = torch.empty(cap, dtype=torch.uint8, device=dev)
+    w = 0
+    ndocs = 0
+    if leading_empty and first_copy == 0:
+        text[0] = 2
+        w = 1
+        ndocs = 1
+    for k in range(first_copy, first_copy + ncopies):
+        g = torch.Generator(device=dev)
+        g.manual_seed(seed * 1000003 + k + 1)
+        t = mutate(ref, codes, div, g, dev)
+        L = t.numel()
+        if w + L + 1 + pad > cap:
+            raise RuntimeError("text buffer too small")
+        text[w:w + L] = t
+        text[w + L] = 2
+        w += L + 1
+        ndocs += 1
+        del t
+    text[w:w + pad] = 2
+    return ref, text, w, ndocs
