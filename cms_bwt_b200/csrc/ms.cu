@@ -324,7 +324,7 @@ void ms_stage(cmsbwt_ctx *c) {
     c->dump_sm.alloc(N, st); c->dump_head.alloc(N, st);
   }
   size_t tb = 0;
-  cub::DeviceScan::ExclusiveSum(nullptr, tb, ccnt.as<u32>(), coff.as<u64>(), (int)(nchunks + 1), st);
+  EXSUM64(nullptr, tb, ccnt.as<u32>(), coff.as<u64>(), (int)(nchunks + 1), st);
   tmp.alloc(tb, st);
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->dev);
@@ -358,7 +358,7 @@ void ms_stage(cmsbwt_ctx *c) {
     CK(cudaGetLastError());
     // chunk_off = exclusive scan over nchunks+1 entries (ccnt has nchunks; the extra reads 0)
     size_t t = tb;
-    CK(cub::DeviceScan::ExclusiveSum(tmp.p, t, ccnt.as<u32>(), coff.as<u64>(), (int)nchunks, st));
+    CK(EXSUM64(tmp.p, t, ccnt.as<u32>(), coff.as<u64>(), (int)nchunks, st));
     LAUNCH(c);
     u32 hf[2]; u64 lastoff = 0; u32 lastcnt = 0;
     CK(cudaMemcpyAsync(hf, flags.p, 8, cudaMemcpyDeviceToHost, st));
