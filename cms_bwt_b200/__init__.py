@@ -33,7 +33,9 @@ class Stats(C.Structure):
                 ("d2h_ms", C.c_double), ("ms_kernel_ms", C.c_double), ("n_heads", C.c_uint64), ("n_docs", C.c_uint64),
                 ("n_tails", C.c_uint64), ("n_items", C.c_uint64), ("n_runs", C.c_uint64),
                 ("rank_rounds", C.c_uint32), ("kmer_k", C.c_uint32),
-                ("kernel_launches", C.c_uint64)]
+                ("kernel_launches", C.c_uint64), ("pack_ms", C.c_double),
+                ("fast_path", C.c_uint32), ("light_tiles", C.c_uint32), ("pair_tests", C.c_uint64),
+                ("rank_tied", C.c_uint64)]
 
     def asdict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

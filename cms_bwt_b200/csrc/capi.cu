@@ -81,6 +81,9 @@ int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
   if (!strcmp(name, "chunk_len")) { if (v < 64) return CMSBWT_E_ARG; c->chunk_len = v; }
   else if (!strcmp(name, "pool_div")) { if (v < 1) return CMSBWT_E_ARG; c->pool_div = v; }
   else if (!strcmp(name, "kmer_k")) { if (v < 0 || v > 13) return CMSBWT_E_ARG; c->kmer_k = v; }
+  else if (!strcmp(name, "skip_min")) { if (v < 2) return CMSBWT_E_ARG; c->skip_min = v; }
+  else if (!strcmp(name, "fast")) { c->fast = v != 0; }
+  else if (!strcmp(name, "tile_budget")) { if (v < 0) return CMSBWT_E_ARG; c->tile_budget = v; }
   else return CMSBWT_E_ARG;
   return CMSBWT_OK;
 }
@@ -157,7 +160,20 @@ int64_t cmsbwt_parse_collection(const uint8_t *file, int64_t size, uint64_t pref
 }
 
 // ---- index ------------------------------------------------------------------------------------
+// fast-path eligibility: x = (A|C|G|T)+ followed by the augmentation only, and the first
+// augmentation symbol sorts before 'A' (true for every pure-ACGT reference: it is 0x03)
+static void classify_x(cmsbwt_ctx *c, const uint8_t *x, uint32_t n) {
+  auto acgt = [](uint8_t b) { return b == 'A' || b == 'C' || b == 'G' || b == 'T'; };
+  uint32_t m = 0;
+  while (m < n && acgt(x[m])) m++;
+  bool pure = m > 0 && m < n && x[m] < 'A';
+  for (uint32_t j = m; pure && j < n; j++) if (acgt(x[j])) pure = false;
+  c->pure = pure;
+  c->n_acgt = pure ? m : 0;
+}
+
 static void upload_x(cmsbwt_ctx *c, const uint8_t *x, uint32_t n) {
+  classify_x(c, x, n);
   c->d_x.alloc((size_t)n + CMS_PAD, c->st);
   CK(cudaMemsetAsync(c->d_x.p, 0xFF, (size_t)n + CMS_PAD, c->st));
   CK(cudaMemcpyAsync(c->d_x.p, x, n, cudaMemcpyHostToDevice, c->st));

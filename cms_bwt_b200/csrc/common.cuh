@@ -112,6 +112,12 @@ struct cmsbwt_ctx {
   Index ix;
   DBuf d_x, d_sa, d_isa, d_G, d_rbwt, d_ktab;
   bool have_sa = false, have_index = false;
+  // fast path (pure-ACGT reference): packed reference, {key, sa} per rank
+  bool pure = false;         // x = ACGT* + augmentation, x[n_acgt] < 'A'
+  u32 n_acgt = 0;
+  DBuf d_xp, d_sak;
+  DBuf d_tp, d_seps;         // packed text, sorted separator positions (+ sentinel)
+  u64 sep_hint = 0, head_hint = 0;
   // text
   const u8 *text = nullptr;
   u64 N = 0;
@@ -124,6 +130,10 @@ struct cmsbwt_ctx {
   // stage 2 products
   DBuf h_toNext, h_within, h_off, d_cov;  // u32, u32, u64, i32[n+1]
   bool have_ms = false, have_sort = false;
+  // stage 2, brute-force tile path (tiles.cu)
+  bool light = false;
+  DBuf t_hoff, t_roff, t_he, t_re, h_sexcl;
+  u32 tile_maxent = 0;
   // stage 3
   DBuf d_out, d_rle;
   u64 out_bytes = 0;
@@ -132,6 +142,9 @@ struct cmsbwt_ctx {
   i64 chunk_len = 8192;
   i64 pool_div = 6;          // initial head-pool capacity = N / pool_div records
   i64 kmer_k = 0;            // 0 = auto
+  i64 skip_min = 20;         // fast path: try the G skip for matches at least this long
+  i64 fast = 1;              // 0 = always use the general 8-bit kernel
+  i64 tile_budget = 1ll << 36; // stage 2: brute-force tile counting up to this many pair tests per job
 };
 
 #define LAUNCH(ctx) ((ctx)->launches++)
@@ -140,7 +153,12 @@ struct cmsbwt_ctx {
 void sa_build_device(cmsbwt_ctx *c, const u8 *d_x, u32 n, i32 *d_sa);
 void index_build(cmsbwt_ctx *c);
 void ms_stage(cmsbwt_ctx *c);
+bool ms_stage_fast(cmsbwt_ctx *c);
+void pack_2bit(cmsbwt_ctx *c, const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps, u64 sepcap,
+               unsigned long long *nsep, u32 *flags);
 void sort_stage(cmsbwt_ctx *c);
+void tail_rank(cmsbwt_ctx *c, const u64 *label, u32 *nexth, u32 Tn, u32 *trank);
+bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl);
 void emit_stage(cmsbwt_ctx *c, int mode);
 
 // ---------------------------------------------------------------------------------------------

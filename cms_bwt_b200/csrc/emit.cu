@@ -11,7 +11,8 @@ __global__ void k_cnt_sa(const i32 *cov, const i32 *sa, u32 n, u32 *cnt) {
 
 #define FILL_THREADS 256
 #define FILL_VEC_PER_THREAD 4
-#define FILL_BYTES (FILL_THREADS * FILL_VEC_PER_THREAD * 16)
+#define FILL_VECS (FILL_THREADS * FILL_VEC_PER_THREAD)
+#define FILL_BYTES (FILL_VECS * 16)
 #define FILL_SMEM_RUNS 2048
 
 // largest r in [lo, hi) with base[r] <= o   (base is non-decreasing, base[lo] <= o)
@@ -23,41 +24,89 @@ __device__ __forceinline__ u32 run_of(const u64 *base, u32 lo, u32 hi, u64 o) {
   return lo;
 }
 
-// Run-length expansion: every thread writes 16-byte vectors of the output.
-__global__ void __launch_bounds__(FILL_THREADS) k_fill(const u64 *base, const u8 *rbwt, u32 n, u64 N,
-                                                       u8 *out) {
-  __shared__ u64 sb[FILL_SMEM_RUNS + 1];
-  __shared__ u32 s_r0, s_r1;
+// merge-path style partition: the run that holds the first byte of every output block
+__global__ void k_fill_part(const u64 *base, u32 n, u64 N, u64 nblocks, u32 *bstart) {
+  u64 b = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > nblocks) return;
+  u64 o = b * FILL_BYTES;
+  bstart[b] = o < N ? run_of(base, 0, n, o) : n - 1;
+}
+
+// Run-length expansion (:1640-1688 without the head symbols): cov[SA[r]] copies of refBWT[r].
+// A block owns FILL_BYTES of output; the run covering every 16-byte vector comes from a max-scan
+// over "last run starting in this vector" marks, vectors inside one run are splatted.
+__global__ void __launch_bounds__(FILL_THREADS) k_fill(const u64 *base, const u8 *rbwt, const u32 *bstart,
+                                                       u32 n, u64 N, u8 *out) {
+  __shared__ u64 sb[FILL_SMEM_RUNS + 2];
+  __shared__ u8 ssym[FILL_SMEM_RUNS + 2];
+  __shared__ u32 s_m[FILL_VECS];
+  typedef cub::BlockScan<u32, FILL_THREADS> BS;
+  __shared__ typename BS::TempStorage ts;
+  const u32 tid = threadIdx.x;
   const u64 o0 = (u64)blockIdx.x * FILL_BYTES;
   const u64 o1 = min(N, o0 + FILL_BYTES);
-  if (threadIdx.x == 0) {
-    s_r0 = run_of(base, 0, n + 1, o0);
-    s_r1 = run_of(base, 0, n + 1, o1 - 1);
-  }
-  __syncthreads();
-  const u32 r0 = s_r0, r1 = s_r1;
+  const u32 r0 = bstart[blockIdx.x], r1 = bstart[blockIdx.x + 1];
   const u32 nr = r1 - r0 + 1;                 // runs r0..r1 intersect this block
   const bool use_s = nr <= FILL_SMEM_RUNS;
-  if (use_s)
-    for (u32 k = threadIdx.x; k <= nr; k += FILL_THREADS) sb[k] = base[r0 + k];
-  __syncthreads();
-  const u64 *bb = use_s ? sb : base + r0;
+  if (use_s) {
+    for (u32 k = tid; k <= nr; k += FILL_THREADS) { sb[k] = base[r0 + k]; ssym[k] = k < nr ? rbwt[r0 + k] : 0; }
+    if (tid == 0) sb[nr + 1] = ~0ull;          // the last block runs one entry past base[n] = N
+    for (u32 v = tid; v < FILL_VECS; v += FILL_THREADS) s_m[v] = 0;
+    __syncthreads();
+    for (u32 k = 1 + tid; k < nr; k += FILL_THREADS) {
+      u64 s = sb[k];
+      if (s >= o0 && s < o1) atomicMax(&s_m[(u32)(s - o0) >> 4], k);
+    }
+    __syncthreads();
+    u32 it[FILL_VEC_PER_THREAD];
+#pragma unroll
+    for (int v = 0; v < FILL_VEC_PER_THREAD; v++) it[v] = s_m[tid * FILL_VEC_PER_THREAD + v];
+    BS(ts).InclusiveScan(it, it, cub::Max());
+    __syncthreads();
+#pragma unroll
+    for (int v = 0; v < FILL_VEC_PER_THREAD; v++) s_m[tid * FILL_VEC_PER_THREAD + v] = it[v];
+    __syncthreads();
+  }
+#pragma unroll
   for (int v = 0; v < FILL_VEC_PER_THREAD; v++) {
-    u64 o = o0 + ((u64)v * FILL_THREADS + threadIdx.x) * 16;
+    const u32 vi = (u32)v * FILL_THREADS + tid;
+    const u64 o = o0 + (u64)vi * 16;
     if (o >= o1) break;
-    u32 k = run_of(bb, 0, nr, o);             // bb[k] <= o < bb[k+1]
-    u64 nextb = bb[k + 1];
-    u32 c = rbwt[r0 + k];
-    if (nextb >= o + 16 && o + 16 <= N) {
-      u32 w = c * 0x01010101u;
-      *(uint4 *)(out + o) = make_uint4(w, w, w, w);
+    u32 k;
+    u64 lo, hi;
+    if (use_s) {
+      k = vi ? s_m[vi - 1] : 0;
+      while (sb[k + 1] <= o) k++;              // runs that start exactly here, empty runs
+      lo = hi = (u64)ssym[k] * 0x0101010101010101ull;
+      u64 nb = sb[k + 1];
+      while (nb < o + 16) {                    // a run starts inside this vector: overwrite its bytes
+        k++;
+        const u32 d = (u32)(nb - o);
+        const u64 sp = (u64)ssym[k] * 0x0101010101010101ull;
+        const u64 mlo = d < 8 ? ~0ull << (8 * d) : 0ull;
+        const u64 mhi = d < 8 ? ~0ull : ~0ull << (8 * (d - 8));
+        lo = (lo & ~mlo) | (sp & mlo);
+        hi = (hi & ~mhi) | (sp & mhi);
+        nb = sb[k + 1];
+      }
     } else {
-      u64 lim = min(N, o + 16);
-      for (u64 b = o; b < lim; b++) {
-        while (bb[k + 1] <= b) k++;
-        out[b] = rbwt[r0 + k];
+      const u64 *bb = base + r0;
+      k = run_of(bb, 0, nr, o);
+      lo = hi = (u64)rbwt[r0 + k] * 0x0101010101010101ull;
+      u64 nb = bb[k + 1];
+      while (nb < o + 16) {
+        k++;
+        const u32 d = (u32)(nb - o);
+        const u64 sp = (u64)rbwt[r0 + k] * 0x0101010101010101ull;
+        const u64 mlo = d < 8 ? ~0ull << (8 * d) : 0ull;
+        const u64 mhi = d < 8 ? ~0ull : ~0ull << (8 * (d - 8));
+        lo = (lo & ~mlo) | (sp & mlo);
+        hi = (hi & ~mhi) | (sp & mhi);
+        nb = bb[k + 1];
       }
     }
+    // out has CMS_PAD bytes of slack, so the last vector may be written whole
+    *(uint4 *)(out + o) = make_uint4((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
   }
 }
 
@@ -124,27 +173,36 @@ __global__ void k_rle_records(const u8 *out, const u64 *starts, u64 R, u64 N, u8
   d[8] = out[s];
 }
 
+void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out);
+
 void emit_stage(cmsbwt_ctx *c, int mode) {
   cudaStream_t st = c->st;
   const u32 n = c->ix.n;
   const u64 N = c->N, H = c->H;
   const int B = 256;
-  DBuf cnt, base, tmp;
+  DBuf cnt, base, tmp, bstart;
   cnt.alloc(((size_t)n + 1) * 4, st);
   base.alloc(((size_t)n + 2) * 8, st);
   size_t tb = 0, tb2 = 0;
-  // coverage = inclusive scan of the deltas (in place)
   cub::DeviceScan::InclusiveSum(nullptr, tb, c->d_cov.as<i32>(), c->d_cov.as<i32>(), (int)n, st);
   EXSUM64(nullptr, tb2, cnt.as<u32>(), base.as<u64>(), (int)(n + 1), st);
   if (tb2 > tb) tb = tb2;
   tmp.alloc(tb, st);
   size_t t = tb;
-  CK(cub::DeviceScan::InclusiveSum(tmp.p, t, c->d_cov.as<i32>(), c->d_cov.as<i32>(), (int)n, st));
-  CK(cudaMemsetAsync(cnt.p, 0, ((size_t)n + 1) * 4, st));
+  if (!c->light) {     // sort-based path: coverage = inclusive scan of the deltas (in place)
+    CK(cub::DeviceScan::InclusiveSum(tmp.p, t, c->d_cov.as<i32>(), c->d_cov.as<i32>(), (int)n, st));
+    LAUNCH(c);
+  }
+  CK(cudaMemsetAsync(cnt.as<u32>() + n, 0, 4, st));
   k_cnt_sa<<<(n + B - 1) / B, B, 0, st>>>(c->d_cov.as<i32>(), c->ix.sa, n, cnt.as<u32>());
   t = tb;
   CK(EXSUM64(tmp.p, t, cnt.as<u32>(), base.as<u64>(), (int)(n + 1), st));
-  c->launches += 3;
+  CK(cudaMemsetAsync(base.as<u64>() + (n + 1), 0xFF, 8, st));     // sentinel past base[n] = N
+  c->launches += 2;
+  const u64 nblocks = (N + FILL_BYTES - 1) / FILL_BYTES;
+  bstart.alloc((nblocks + 1) * 4, st);
+  k_fill_part<<<(u32)((nblocks + 1 + B - 1) / B), B, 0, st>>>(base.as<u64>(), n, N, nblocks, bstart.as<u32>());
+  LAUNCH(c);
   u64 total = 0;
   CK(cudaMemcpyAsync(&total, base.as<u64>() + n, 8, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
@@ -155,14 +213,18 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
     throw CmsErr{CMSBWT_E_INTERNAL, buf};
   }
   c->d_out.alloc(N + CMS_PAD, st);
-  c->h_off.alloc(H * 8, st);
   u8 *out = c->d_out.as<u8>();
-  k_fill<<<(u32)((N + FILL_BYTES - 1) / FILL_BYTES), FILL_THREADS, 0, st>>>(base.as<u64>(), c->ix.rbwt,
-                                                                          n, N, out);
-  k_scatter_heads<<<(u32)((H + B - 1) / B), B, 0, st>>>(c->h_pos.as<u32>(), c->h_cs.as<u16>(),
-                                                       c->h_within.as<u32>(), c->ix.isa,
-                                                       base.as<u64>(), H, out, c->h_off.as<u64>());
-  c->launches += 2;
+  k_fill<<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), c->ix.rbwt, bstart.as<u32>(), n, N, out);
+  LAUNCH(c);
+  if (c->light) {
+    tiles_place_heads(c, base.as<u64>(), out);
+  } else {
+    c->h_off.alloc(H * 8, st);
+    k_scatter_heads<<<(u32)((H + B - 1) / B), B, 0, st>>>(c->h_pos.as<u32>(), c->h_cs.as<u16>(),
+                                                         c->h_within.as<u32>(), c->ix.isa,
+                                                         base.as<u64>(), H, out, c->h_off.as<u64>());
+    LAUNCH(c);
+  }
   CK(cudaGetLastError());
   c->out_mode = mode;
   c->out_bytes = N;

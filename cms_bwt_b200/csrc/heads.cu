@@ -21,11 +21,21 @@ __global__ void k_link(const u64 *g, const u32 *pos, const u32 *len, u64 H, u32 
   u64 gi = g[i];
   u32 tn = l == 0 ? 0 : (u32)(g[i + 1] - gi - 1);     // a sentinel always follows a real head
   toNext[i] = tn;
-  u32 p = pos[i];
-  atomicAdd(diff + p, 1);
-  atomicAdd(diff + p + tn + 1, -1);
+  if (diff) {                     // sort-based path only: coverage deltas by global atomics
+    u32 p = pos[i];
+    atomicAdd(diff + p, 1);
+    atomicAdd(diff + p + tn + 1, -1);
+  }
   tflag[i] = (i == 0) || (gi + l != g[i - 1] + len[i - 1]);
   sflag[i] = l == 0;
+}
+// coverage deltas of the sort-based path (:368-390): +1 at pos, -1 past the phrase
+__global__ void k_cov_diff(const u32 *pos, const u32 *toNext, u64 H, i32 *diff) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H) return;
+  u32 p = pos[i];
+  atomicAdd(diff + p, 1);
+  atomicAdd(diff + p + toNext[i] + 1, -1);
 }
 __global__ void k_tail_first(const u32 *tflag, const u32 *tail_incl, u64 H, u32 *tail_first) {
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -189,12 +199,13 @@ void sort_stage(cmsbwt_ctx *c) {
   size_t tb;
   // ---- link ----
   c->h_toNext.alloc(H * 4, st);
-  c->d_cov.alloc(((size_t)n + 1) * 4, st);
-  CK(cudaMemsetAsync(c->d_cov.p, 0, ((size_t)n + 1) * 4, st));
+  c->light = false;
+  c->stats.light_tiles = 0;
+  c->stats.pair_tests = 0;
   DBuf tflag, sflag, tincl, sexcl;
   tflag.alloc(H * 4, st); sflag.alloc(H * 4, st); tincl.alloc(H * 4, st); sexcl.alloc(H * 4, st);
-  k_link<<<gH, B, 0, st>>>(g, pos, len, H, c->h_toNext.as<u32>(), c->d_cov.as<i32>(),
-                           tflag.as<u32>(), sflag.as<u32>());
+  k_link<<<gH, B, 0, st>>>(g, pos, len, H, c->h_toNext.as<u32>(), nullptr, tflag.as<u32>(),
+                           sflag.as<u32>());
   LAUNCH(c);
   tb = 0; cub::DeviceScan::InclusiveSum(nullptr, tb, tflag.as<u32>(), tincl.as<u32>(), (int)H, st);
   tmp.need(tb, st);
@@ -213,39 +224,15 @@ void sort_stage(cmsbwt_ctx *c) {
   // ---- tails ----
   const u32 gT = (Tn + B - 1) / B;
   DBuf tfirst, label, label2, next, next2, tid, tid2, trank, fl, dense;
-  tfirst.alloc((size_t)Tn * 4, st); label.alloc((size_t)Tn * 8, st); label2.alloc((size_t)Tn * 8, st);
-  next.alloc((size_t)Tn * 4, st); next2.alloc((size_t)Tn * 4, st); tid.alloc((size_t)Tn * 4, st);
-  tid2.alloc((size_t)Tn * 4, st); trank.alloc((size_t)Tn * 4, st); fl.alloc((size_t)Tn * 4, st);
-  dense.alloc((size_t)Tn * 4, st);
+  tfirst.alloc((size_t)Tn * 4, st); label.alloc((size_t)Tn * 8, st);
+  next.alloc((size_t)Tn * 4, st); tid.alloc((size_t)Tn * 4, st);
+  trank.alloc((size_t)Tn * 4, st);
   k_tail_first<<<gH, B, 0, st>>>(tflag.as<u32>(), tincl.as<u32>(), H, tfirst.as<u32>());
   k_tail_label<<<gT, B, 0, st>>>(g, pos, len, cs, tincl.as<u32>(), sexcl.as<u32>(), tfirst.as<u32>(),
                                  c->ix.isa, H, Tn, label.as<u64>(), next.as<u32>(), tid.as<u32>());
   c->launches += 2;
-  u32 rounds = 0;
-  while (true) {
-    tb = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, tb, label.as<u64>(), label2.as<u64>(), tid.as<u32>(),
-                                    tid2.as<u32>(), (int)Tn, 0, 64, st);
-    tmp.need(tb, st);
-    CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, label.as<u64>(), label2.as<u64>(), tid.as<u32>(),
-                                       tid2.as<u32>(), (int)Tn, 0, 64, st));
-    k_key_flags<<<gT, B, 0, st>>>(label2.as<u64>(), Tn, fl.as<u32>());
-    tb = 0; cub::DeviceScan::InclusiveSum(nullptr, tb, fl.as<u32>(), dense.as<u32>(), (int)Tn, st);
-    tmp.need(tb, st);
-    CK(cub::DeviceScan::InclusiveSum(tmp.b.p, tb, fl.as<u32>(), dense.as<u32>(), (int)Tn, st));
-    k_rank_scatter<<<gT, B, 0, st>>>(tid2.as<u32>(), dense.as<u32>(), Tn, trank.as<u32>());
-    c->launches += 6;
-    u32 last = 0;
-    CK(cudaMemcpyAsync(&last, dense.as<u32>() + (Tn - 1), 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    if (last + 1 == Tn) break;
-    if (++rounds > 64) throw CmsErr{CMSBWT_E_INTERNAL, "tail ranking did not converge"};
-    k_double<<<gT, B, 0, st>>>(trank.as<u32>(), next.as<u32>(), Tn, label.as<u64>(), tid.as<u32>(),
-                               next2.as<u32>());
-    LAUNCH(c);
-    std::swap(next.p, next2.p);
-  }
-  c->stats.rank_rounds = rounds;
+  label2.release(); tid2.release(); next2.release(); fl.release(); dense.release(); tid.release();
+  tail_rank(c, label.as<u64>(), next.as<u32>(), Tn, trank.as<u32>());
   // ---- kappa + items ----
   DBuf kappa, nitems, ioff;
   kappa.alloc(H * 8, st); nitems.alloc((H + 1) * 4, st); ioff.alloc((H + 1) * 8, st);
@@ -259,9 +246,23 @@ void sort_stage(cmsbwt_ctx *c) {
   u64 I = 0;
   CK(cudaMemcpyAsync(&I, ioff.as<u64>() + H, 8, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  if (I >= 0x7FFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^31 tile items on one device"};
   c->stats.n_items = I;
   // free what is no longer needed before the big item arrays
+  tfirst.release(); label.release(); label2.release(); next.release(); next2.release();
+  tid.release(); tid2.release(); fl.release(); dense.release(); tflag.release(); sflag.release();
+  // ---- brute-force tile path (tiles.cu) unless the collection is too deep for it ----
+  if (c->tile_budget > 0 && tiles_build(c, kappa.as<u64>(), sexcl)) {
+    c->stats.light_tiles = 1;
+    CK(cudaStreamSynchronize(st));
+    return;
+  }
+  // ---- sort-based sweep ----
+  if (I >= 0x7FFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^31 tile items on one device"};
+  c->stats.n_items = I;
+  c->d_cov.alloc(((size_t)n + 1) * 4, st);
+  CK(cudaMemsetAsync(c->d_cov.p, 0, ((size_t)n + 1) * 4, st));
+  k_cov_diff<<<gH, B, 0, st>>>(pos, c->h_toNext.as<u32>(), H, c->d_cov.as<i32>());
+  LAUNCH(c);
   tfirst.release(); label.release(); label2.release(); next.release(); next2.release();
   tid.release(); tid2.release(); fl.release(); dense.release(); tflag.release(); sflag.release();
   DBuf it_tr, it_tr2, it_key, it_key2, it_pay, idx, idx2;

@@ -1,6 +1,7 @@
 // Reference index on the device: suffix array (prefix doubling), ISA, PLCP' -> G, reference BWT,
 // k-mer interval table.  Replaces initialize_reference (CMS-BWT-functions.cpp:246-297).
 #include "common.cuh"
+#include "ms_fast.cuh"
 #include <cub/cub.cuh>
 
 // ------------------------------------------------------------------------------------------
@@ -134,26 +135,22 @@ __global__ void k_G(const i32 *sa, const u32 *isa, const u32 *plcp, u32 n, u32 *
 // ------------------------------------------------------------------------------------------
 // k-mer table: ktab[m] = number of suffixes smaller than the ACGT k-mer m (m in [0,4^k]).
 // f(r) = number of k-mers <= suffix r (non-decreasing in r); ktab[m] = r for f(r-1) <= m < f(r).
-__device__ __forceinline__ u32 kmers_le_suffix(const u8 *x, u32 s, int k) {
-  u32 m = 0;
-  for (int j = 0; j < k; j++) {
-    u8 c = x[s + j];                 // padding (0xFF) past the end is never reached: x[n-1] = 0
-    int d = c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : -1;
-    if (d < 0) {
-      int dl = (c > 'A') + (c > 'C') + (c > 'G') + (c > 'T');
-      return (m * 4 + dl) << (2 * (k - 1 - j));
-    }
-    m = m * 4 + d;
-  }
-  return m + 1;
-}
+// (kmers_le_suffix lives in ms_fast.cuh as msf_kmers_le_suffix, shared with the CPU harness)
 __global__ void k_ktab_mark(const u8 *x, const i32 *sa, u32 n, int k, u32 *ktab) {
   u32 r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= n) return;
-  u32 f = kmers_le_suffix(x, (u32)sa[r], k);
-  u32 fp = r > 0 ? kmers_le_suffix(x, (u32)sa[r - 1], k) : 0;
+  u32 f = msf_kmers_le_suffix(x, (u32)sa[r], k);
+  u32 fp = r > 0 ? msf_kmers_le_suffix(x, (u32)sa[r - 1], k) : 0;
   if (f > fp) ktab[fp] = r;
   if (r == n - 1) { u32 K = 1u << (2 * k); if (f <= K) ktab[f] = n; }
+}
+
+// fast path: per SA rank the 16 bases after the k-mer (big-endian) and the suffix itself
+__global__ void k_sak(const i32 *sa, const u64 *xp, u32 n, u32 n_acgt, int k, u64 *sak) {
+  u32 r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  u32 s = (u32)sa[r];
+  sak[r] = (u64)msf_make_key(xp, s, n_acgt, k) | ((u64)s << 32);
 }
 
 static int pick_k(u32 n, i64 forced) {
@@ -201,5 +198,19 @@ void index_build(cmsbwt_ctx *c) {
   c->ix.rbwt = c->d_rbwt.as<u8>();
   c->ix.ktab = c->d_ktab.as<u32>();
   c->stats.kmer_k = (u32)k;
+  if (c->pure) {
+    const u64 nwords = ((u64)n + 31) / 32 + MSF_PAD_WORDS;
+    c->d_xp.alloc(nwords * 8, st);
+    c->d_sak.alloc((size_t)n * 8, st);
+    DBuf fl;
+    fl.alloc(8, st);
+    CK(cudaMemsetAsync(fl.p, 0, 8, st));
+    pack_2bit(c, x, c->n_acgt, c->d_xp.as<u64>(), nwords, nullptr, 0, nullptr, fl.as<u32>());
+    k_sak<<<g, B, 0, st>>>(sa, c->d_xp.as<u64>(), n, c->n_acgt, k, c->d_sak.as<u64>());
+    CK(cudaGetLastError());
+  } else {
+    c->d_xp.release();
+    c->d_sak.release();
+  }
   CK(cudaStreamSynchronize(st));
 }

@@ -1,0 +1,259 @@
+// Stage 1, fast path (pure-ACGT reference and text): 2-bit packing, the lane-per-window matching
+// statistics kernel (state machine in ms_fast.cuh) and the compaction of its head records into the
+// text-order arrays the rest of the pipeline reads.  Replaces CMS-BWT-functions.cpp:1138-1213
+// (small path :344-419) for such inputs; anything else goes through k_ms (ms.cu).
+#include "common.cuh"
+#include "ms_fast.cuh"
+#include <cub/cub.cuh>
+
+// ---- 8-bit -> 2-bit ---------------------------------------------------------------------------
+// One thread packs 32 symbols into one word.  Symbols at positions >= len pack as 0.  Separators
+// (0x02) are appended to `seps` (unsorted); any other byte outside A,C,G,T raises flags[0].
+__device__ __forceinline__ u32 pack4(u32 w, bool &clean) {
+  // 2-bit codes of four symbols (A,C,G,T -> 0,1,2,3), one per byte, and back through a PRMT table:
+  // the round trip equals the input exactly when all four bytes are A, C, G or T
+  u32 c = ((w >> 1) & 0x03030303u) ^ ((w >> 2) & 0x01010101u);
+  u32 t = c | (c >> 4);                         // byte 0: c0 | c1 << 4, byte 2: c2 | c3 << 4
+  u32 sel = __byte_perm(t, 0, 0x4420);          // selector nibbles c0, c1, c2, c3
+  clean = __byte_perm(0x54474341u, 0, sel) == w;
+  u32 p = c | (c >> 6);                         // byte 0: c0 | c1 << 2, byte 2: c2 | c3 << 2
+  return (p & 0xFu) | ((p >> 12) & 0xF0u);
+}
+
+__global__ void __launch_bounds__(256) k_pack(const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps,
+                                              u64 sepcap, unsigned long long *nsep, u32 *flags) {
+  for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < nwords; j += (u64)gridDim.x * blockDim.x) {
+    const u64 p0 = j * 32;
+    u64 word = 0;
+    if (p0 < len) {
+      const uint4 *q = (const uint4 *)(src + p0);
+      uint4 a = __ldg(q), b = __ldg(q + 1);
+      u32 v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+      bool bad = false;
+#pragma unroll
+      for (int t = 0; t < 8; t++) {
+        u32 w = v[t];
+        bool clean;
+        u32 c8 = pack4(w, clean);
+        if (!clean || p0 + 4 * t + 4 > len) {     // rare: separator, foreign symbol, end of the text
+          const u64 pb = p0 + 4 * t;
+          c8 = 0;
+#pragma unroll
+          for (int bb = 0; bb < 4; bb++) {
+            u32 ch = (w >> (8 * bb)) & 0xFF;
+            if (pb + bb >= len) continue;
+            if (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') c8 |= msf_code_of(ch) << (2 * bb);
+            else if (ch == 2 && seps) {
+              unsigned long long k = atomicAdd(nsep, 1ull);
+              if (k < sepcap) seps[k] = pb + bb;
+            } else bad = true;
+          }
+        }
+        word |= (u64)c8 << (8 * t);
+      }
+      if (bad) flags[0] = 1;
+    }
+    dst[j] = word;
+  }
+}
+
+void pack_2bit(cmsbwt_ctx *c, const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps, u64 sepcap,
+               unsigned long long *nsep, u32 *flags) {
+  u64 blocks = (nwords + 255) / 256;
+  if (blocks > 148 * 64) blocks = 148 * 64;
+  k_pack<<<(u32)blocks, 256, 0, c->st>>>(src, len, dst, nwords, seps, sepcap, nsep, flags);
+  LAUNCH(c);
+  CK(cudaGetLastError());
+}
+
+// index of the first separator >= window start
+__global__ void k_wsep(const u64 *seps, u64 nseps, u32 WL, u64 nwin, u32 *wsep) {
+  u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nwin) return;
+  u64 key = w * WL, lo = 0, hi = nseps;
+  while (lo < hi) {
+    u64 mid = (lo + hi) >> 1;
+    if (seps[mid] < key) lo = mid + 1; else hi = mid;
+  }
+  wsep[w] = (u32)lo;
+}
+
+// ---- the kernel ---------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_ms_fast(MsfParams P) {
+  MsfLane L;
+  L.i = L.w0 = L.w1 = L.sepnext = 0;
+  L.sepidx = L.w = 0;
+  L.prevpos = MSF_INVALID; L.prevterm = 0; L.first = 0;
+  L.curb = MSF_NOB; L.fill = 0; L.cnt = 0; L.limit = 0;
+  L.tkey = L.lo = L.hi = L.rb = L.prevkey = L.prevsa = L.haveprev = 0;
+  L.pos = L.len = L.sm = L.maxl = 0;
+  L.glo = L.ghi = L.E = L.gsteps = 0;
+  L.state = MSF_S_FETCH;
+  while (L.state != MSF_S_DONE) msf_step(P, L);
+}
+
+// ---- compaction -------------------------------------------------------------------------------
+__global__ void k_msf_fix(const u32 *wcnt, const u32 *wfirstpos, const u32 *wlastpos, u64 nwin, u32 WL,
+                          u32 *wadj, u8 *dhead) {
+  u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nwin) return;
+  u32 drop = msf_window_drop(wfirstpos, wlastpos, w);
+  wadj[w] = wcnt[w] - drop;
+  if (drop && dhead) dhead[w * WL] = 0;
+}
+
+// 8 threads per window walk its batch list and write the text-order arrays
+__global__ void __launch_bounds__(256) k_msf_gather(const uint4 *pool, const u32 *batch_next,
+                                                    const u32 *wfirst, const u32 *wcnt, const u32 *wadj,
+                                                    const u64 *woff, u64 nwin, u32 WL, u64 *g, u32 *pos,
+                                                    u32 *len, u16 *cs) {
+  u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  u64 w = gid >> 3;
+  u32 l = (u32)gid & 7;
+  if (w >= nwin) return;
+  u32 cnt = wcnt[w];
+  if (cnt == 0) return;
+  u32 drop = cnt - wadj[w];
+  u64 off = woff[w];
+  u32 b = wfirst[w];
+  for (u32 j0 = 0; j0 < cnt; j0 += 8) {
+    if (j0 && (j0 % MSF_RB) == 0) b = batch_next[b];
+    u32 j = j0 + l;
+    if (j < cnt && !(j == 0 && drop)) {
+      uint4 r = pool[(u64)b * MSF_RB + (j % MSF_RB)];
+      u64 o = off + j - drop;
+      g[o] = w * WL + r.x; pos[o] = r.y; len[o] = r.z; cs[o] = (u16)(r.w & 0x1FF);
+    }
+  }
+}
+
+// Returns false (nothing changed) when the text is not pure ACGT + separators.
+bool ms_stage_fast(cmsbwt_ctx *c) {
+  cudaStream_t st = c->st;
+  const u64 N = c->N;
+  const u32 WL = (u32)c->chunk_len;
+  const u64 nwin = (N + WL - 1) / WL;
+  if (nwin >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "too many windows"};
+  // ---- pack the text, collect separators ----
+  const u64 nwords = (N + 31) / 32 + MSF_PAD_WORDS;
+  c->d_tp.alloc(nwords * 8, st);
+  DBuf flags, nsep, tmp;
+  flags.alloc(8, st); nsep.alloc(8, st);
+  u64 sepcap = c->sep_hint ? c->sep_hint + 16 : (N / 1024 + (1u << 16));
+  unsigned long long hsep = 0;
+  u32 hf[2] = {0, 0};
+  cudaEvent_t e0, e1, e2;
+  cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
+  cudaEventRecord(e0, st);
+  for (int attempt = 0; attempt < 2; attempt++) {
+    c->d_seps.alloc((sepcap + 1) * 8, st);
+    CK(cudaMemsetAsync(flags.p, 0, 8, st));
+    CK(cudaMemsetAsync(nsep.p, 0, 8, st));
+    pack_2bit(c, c->text, N, c->d_tp.as<u64>(), nwords, c->d_seps.as<u64>(), sepcap,
+              nsep.as<unsigned long long>(), flags.as<u32>());
+    CK(cudaMemcpyAsync(&hsep, nsep.p, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hf, flags.p, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (hf[0]) { cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); return false; }
+    if (hsep <= sepcap) break;
+    if (attempt == 1) throw CmsErr{CMSBWT_E_INTERNAL, "separator list overflow on exact-size rerun"};
+    sepcap = hsep;
+  }
+  c->sep_hint = hsep;
+  const u64 nseps = hsep;
+  if (nseps >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 documents"};
+  {                                   // sort the separator positions, add the sentinel
+    DBuf sorted;
+    sorted.alloc((nseps + 1) * 8, st);
+    int bits = 1; while (bits < 64 && (1ull << bits) < N) bits++;
+    size_t tb = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_seps.as<u64>(), sorted.as<u64>(), (int)nseps, 0, bits, st);
+    tmp.alloc(tb, st);
+    CK(cub::DeviceRadixSort::SortKeys(tmp.p, tb, c->d_seps.as<u64>(), sorted.as<u64>(), (int)nseps, 0, bits, st));
+    CK(cudaMemsetAsync(sorted.as<u64>() + nseps, 0xFF, 8, st));
+    std::swap(c->d_seps.p, sorted.p);
+    std::swap(c->d_seps.bytes, sorted.bytes);
+    c->launches += 2;
+  }
+  DBuf wsep, wfirst, wcnt, wfp, wlp, wadj, woff, counter, nbused;
+  wsep.alloc(nwin * 4, st); wfirst.alloc(nwin * 4, st); wcnt.alloc(nwin * 4, st);
+  wfp.alloc(nwin * 4, st); wlp.alloc(nwin * 4, st); wadj.alloc((nwin + 1) * 4, st);
+  woff.alloc((nwin + 1) * 8, st); counter.alloc(8, st); nbused.alloc(4, st);
+  k_wsep<<<(u32)((nwin + 255) / 256), 256, 0, st>>>(c->d_seps.as<u64>(), nseps, WL, nwin, wsep.as<u32>());
+  LAUNCH(c);
+  cudaEventRecord(e1, st);
+  if (c->dump) {
+    c->dump_pos.alloc(N * 4, st); c->dump_len.alloc(N * 4, st);
+    c->dump_sm.alloc(N, st); c->dump_head.alloc(N, st);
+  }
+  size_t tb = 0;
+  EXSUM64(nullptr, tb, wadj.as<u32>(), woff.as<u64>(), (int)(nwin + 1), st);
+  tmp.alloc(tb, st);
+  int sms = 148, occ = 4;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->dev);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ms_fast, 128, 0);
+  if (occ < 1) occ = 1;
+  // pool: batches of MSF_RB records; every window wastes at most one partly filled batch
+  u64 rec_est = c->head_hint ? c->head_hint + c->head_hint / 8 : N / 16;
+  u64 nb = rec_est / MSF_RB + nwin + 1024;
+  for (int attempt = 0; attempt < 2; attempt++) {
+    if (nb >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "head pool too large"};
+    DBuf pool, bnext;
+    pool.alloc(nb * MSF_RB * 16, st); bnext.alloc(nb * 4, st);
+    CK(cudaMemsetAsync(flags.p, 0, 8, st));
+    CK(cudaMemsetAsync(counter.p, 0, 8, st));
+    CK(cudaMemsetAsync(nbused.p, 0, 4, st));
+    MsfParams P;
+    P.xp = c->d_xp.as<u64>(); P.x8 = c->ix.x; P.sak = c->d_sak.as<u64>(); P.ktab = c->ix.ktab; P.G = c->ix.G;
+    P.n = c->ix.n; P.n_acgt = c->n_acgt; P.k = c->ix.k;
+    P.tp = c->d_tp.as<u64>(); P.N = N; P.seps = c->d_seps.as<u64>(); P.nseps = nseps; P.wsep = wsep.as<u32>();
+    P.WL = WL; P.nwin = nwin; P.skip_min = (u32)c->skip_min;
+    P.pool = pool.as<u32>(); P.batch_next = bnext.as<u32>(); P.nb_cap = (u32)nb; P.nb_used = nbused.as<u32>();
+    P.wfirst = wfirst.as<u32>(); P.wcnt = wcnt.as<u32>(); P.wfirstpos = wfp.as<u32>(); P.wlastpos = wlp.as<u32>();
+    P.flags = flags.as<u32>(); P.win_counter = counter.as<unsigned long long>();
+    P.dpos = c->dump ? c->dump_pos.as<u32>() : nullptr; P.dlen = c->dump_len.as<u32>();
+    P.dsm = c->dump_sm.as<u8>(); P.dhead = c->dump_head.as<u8>();
+    u64 want = (nwin + 127) / 128;
+    u32 grid = (u32)min(want, (u64)sms * occ);
+    cudaEventRecord(e1, st);
+    k_ms_fast<<<grid, 128, 0, st>>>(P);
+    cudaEventRecord(e2, st);
+    LAUNCH(c);
+    CK(cudaGetLastError());
+    k_msf_fix<<<(u32)((nwin + 255) / 256), 256, 0, st>>>(wcnt.as<u32>(), wfp.as<u32>(), wlp.as<u32>(), nwin, WL,
+                                                        wadj.as<u32>(), c->dump ? c->dump_head.as<u8>() : nullptr);
+    size_t t = tb;
+    CK(EXSUM64(tmp.p, t, wadj.as<u32>(), woff.as<u64>(), (int)nwin, st));
+    c->launches += 2;
+    u64 lastoff = 0; u32 lastcnt = 0;
+    CK(cudaMemcpyAsync(hf, flags.p, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&lastoff, woff.as<u64>() + (nwin - 1), 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&lastcnt, wadj.as<u32>() + (nwin - 1), 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    { float ms = 0; cudaEventElapsedTime(&ms, e1, e2); c->stats.ms_kernel_ms = ms;
+      cudaEventElapsedTime(&ms, e0, e1); c->stats.pack_ms = ms; }
+    const u64 H = lastoff + lastcnt;
+    if (hf[0]) {                    // pool exhausted: counts are exact, rerun with the exact size
+      if (attempt == 1) throw CmsErr{CMSBWT_E_INTERNAL, "head pool overflow on exact-size rerun"};
+      nb = (H + nwin) / MSF_RB + 2 * nwin + 1024;
+      continue;
+    }
+    if (H >= 0x7FFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^31 heads on one device"};
+    c->H = H;
+    c->head_hint = H;
+    c->h_gstart.alloc((H + 1) * 8, st); c->h_pos.alloc((H + 1) * 4, st);
+    c->h_len.alloc((H + 1) * 4, st); c->h_cs.alloc((H + 1) * 2, st);
+    u64 threads = nwin * 8;
+    k_msf_gather<<<(u32)((threads + 255) / 256), 256, 0, st>>>(
+        pool.as<uint4>(), bnext.as<u32>(), wfirst.as<u32>(), wcnt.as<u32>(), wadj.as<u32>(), woff.as<u64>(),
+        nwin, WL, c->h_gstart.as<u64>(), c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>());
+    LAUNCH(c);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+    break;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+  c->stats.n_heads = c->H;
+  c->stats.fast_path = 1;
+  return true;
+}

@@ -1,0 +1,497 @@
+// Fast matching-statistics path for pure-ACGT inputs: one *lane* per text window.
+//
+// Replaces the reference's per-document MS driver (CMS-BWT-functions.cpp:1138-1213; small path
+// :344-419) with computeMSFactorAt :45-88, binarySearchLB/RB :94-149 and the PLCP' skip loop
+// :1176-1185.  MS is a pure function of the suffix, so every window of the
+// text is walked independently by one lane running a flat state machine (one memory round trip
+// per step, so 32 lanes of a warp stay busy even though they are in different phases):
+//
+//   S_POS    read 32 packed bases at i, look the k-mer up in ktab            -> bucket [L,R)
+//   S_BIN    (large buckets only) bisect the bucket on the 16-base keys
+//   S_SCAN   scan the bucket: entries are {key = the 16 bases after the k-mer, sa}; predecessor and
+//            successor and their LCE (< k+16) come from the keys alone
+//   S_EQ     a key equals the text's: make sure it is the only one
+//   S_EXT    extend the single candidate 128 bases per step on the packed streams
+//   S_GSCAN  after a long match: first q in (pos, E) with G[q] >= E (:1176-1185 as a search)
+//   S_GBIN   same, by bisection when the hard zone is long
+//   generic_search()  exact binary search on packed data for everything rare (separator within
+//            k+16 bases, empty bucket, repeated key, suffixes that touch the augmentation)
+//
+// The neighbour rule is the one of :53-76 as restated in ms.cu: the successor wins ties
+// (smaller = 1).  This header is plain C++ when compiled without nvcc so that the same code is
+// run lane by lane on the CPU by tests/harness (test infrastructure; the product only ever runs
+// it inside k_ms_fast).
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define MSF_HD __host__ __device__ __forceinline__
+#define MSF_HDN static __host__ __device__ __forceinline__
+#else
+#define MSF_HD inline
+#define MSF_HDN static inline
+#endif
+
+typedef uint8_t msf_u8;
+typedef uint32_t msf_u32;
+typedef uint64_t msf_u64;
+
+#if defined(__CUDA_ARCH__)
+#define MSF_LD64(p) ((msf_u64)__ldg((const unsigned long long *)(p)))
+#define MSF_LD32(p) ((msf_u32)__ldg((const unsigned int *)(p)))
+#define MSF_LD8(p) ((msf_u8)__ldg((const unsigned char *)(p)))
+#define MSF_ATOMIC_INC32(p) atomicAdd((unsigned int *)(p), 1u)
+#define MSF_ATOMIC_INC64(p) atomicAdd((unsigned long long *)(p), 1ull)
+#define MSF_BREV64(x) ((msf_u64)__brevll((unsigned long long)(x)))
+#define MSF_BREV32(x) ((msf_u32)__brev((unsigned int)(x)))
+#define MSF_CLZ32(x) ((msf_u32)__clz((int)(x)))
+#define MSF_CTZ64(x) ((msf_u32)(__ffsll((long long)(x)) - 1))
+#else
+#define MSF_LD64(p) (*(const msf_u64 *)(p))
+#define MSF_LD32(p) (*(const msf_u32 *)(p))
+#define MSF_LD8(p) (*(const msf_u8 *)(p))
+#define MSF_ATOMIC_INC32(p) __sync_fetch_and_add((msf_u32 *)(p), 1u)
+#define MSF_ATOMIC_INC64(p) __sync_fetch_and_add((unsigned long long *)(p), 1ull)
+static inline msf_u64 msf_brev64_host(msf_u64 v) {
+  v = ((v >> 1) & 0x5555555555555555ull) | ((v & 0x5555555555555555ull) << 1);
+  v = ((v >> 2) & 0x3333333333333333ull) | ((v & 0x3333333333333333ull) << 2);
+  v = ((v >> 4) & 0x0F0F0F0F0F0F0F0Full) | ((v & 0x0F0F0F0F0F0F0F0Full) << 4);
+  return __builtin_bswap64(v);
+}
+#define MSF_BREV64(x) msf_brev64_host(x)
+#define MSF_BREV32(x) ((msf_u32)(msf_brev64_host((msf_u64)(x)) >> 32))
+#define MSF_CLZ32(x) ((msf_u32)__builtin_clz((unsigned)(x)))
+#define MSF_CTZ64(x) ((msf_u32)__builtin_ctzll((unsigned long long)(x)))
+#endif
+
+#define MSF_RB 32                   // head records per pool batch (32 x 16 B; one atomic per batch)
+#define MSF_NOB 0xFFFFFFFFu
+#define MSF_BADB 0xFFFFFFFEu
+#define MSF_INVALID 0xFFFFFFFFu
+#define MSF_PAD_WORDS 4             // zero words readable past the last packed word
+
+enum { MSF_S_FETCH = 0, MSF_S_POS, MSF_S_BIN, MSF_S_SCAN, MSF_S_EQ, MSF_S_EXT, MSF_S_GSCAN,
+       MSF_S_GBIN, MSF_S_DONE };
+
+// ---- 2-bit helpers -----------------------------------------------------------------------------
+// Packed layout: base j lives in word j >> 5, bits [2 (j & 31), 2 (j & 31) + 2); A,C,G,T = 0,1,2,3.
+MSF_HD msf_u32 msf_code_of(msf_u32 c) { return ((c >> 1) & 3u) ^ ((c >> 2) & 1u); }   // A C G T only
+MSF_HD msf_u8 msf_sym_of(msf_u32 b) { return (msf_u8)(b == 0 ? 'A' : b == 1 ? 'C' : b == 2 ? 'G' : 'T'); }
+// 32 bases starting at base j (little-endian: base j in the low bits)
+MSF_HD msf_u64 msf_get64(const msf_u64 *p, msf_u64 j) {
+  const msf_u64 *q = p + (j >> 5);
+  msf_u32 sh = (msf_u32)(j & 31) * 2;
+  msf_u64 lo = MSF_LD64(q);
+  if (sh == 0) return lo;
+  msf_u64 hi = MSF_LD64(q + 1);
+  return (lo >> sh) | (hi << (64 - sh));
+}
+MSF_HD msf_u32 msf_base(const msf_u64 *p, msf_u64 j) {
+  return (msf_u32)(MSF_LD64(p + (j >> 5)) >> ((j & 31) * 2)) & 3u;
+}
+// little-endian packed bases -> big-endian (first base in the top bits): integer order = lexicographic
+MSF_HD msf_u64 msf_be64(msf_u64 w) {
+  msf_u64 r = MSF_BREV64(w);
+  return ((r & 0x5555555555555555ull) << 1) | ((r >> 1) & 0x5555555555555555ull);
+}
+// LCE of text bases [i, ...) and reference bases [s, ...), at most maxl
+MSF_HD msf_u32 msf_lce(const msf_u64 *tp, msf_u64 i, const msf_u64 *xp, msf_u64 s, msf_u32 maxl) {
+  msf_u32 m = 0;
+  while (m < maxl) {
+    msf_u64 d = msf_get64(tp, i + m) ^ msf_get64(xp, s + m);
+    if (d) {
+      m += MSF_CTZ64(d) >> 1;
+      break;
+    }
+    m += 32;
+  }
+  return m < maxl ? m : maxl;
+}
+
+// ---- index construction helpers (shared by index.cu and the CPU harness) ----------------------
+// key of the suffix s: the 16 bases after its first k, big-endian, bases past n_acgt as zeros;
+// suffixes with fewer than k pure bases get the largest key (they sort after every member of the
+// k-mer bucket they fall into).
+MSF_HD msf_u32 msf_make_key(const msf_u64 *xp, msf_u32 s, msf_u32 n_acgt, int k) {
+  if ((msf_u64)s + (msf_u32)k > n_acgt) return 0xFFFFFFFFu;
+  msf_u32 valid = n_acgt - (s + (msf_u32)k);
+  msf_u64 be = msf_be64(msf_get64(xp, (msf_u64)s + (msf_u32)k));
+  msf_u32 key = (msf_u32)(be >> 32);
+  if (valid < 16) key = valid == 0 ? 0u : (key & (0xFFFFFFFFu << (2 * (16 - valid))));
+  return key;
+}
+
+struct MsfParams {
+  // reference index
+  const msf_u64 *xp;      // packed pure prefix of x (n_acgt bases), zero padded
+  const msf_u8 *x8;       // augmented reference bytes
+  const msf_u64 *sak;     // per SA rank: key (low 32 bits) | sa (high 32 bits)
+  const msf_u32 *ktab;    // 4^k + 1 entries: number of suffixes smaller than k-mer m
+  const msf_u32 *G;       // G[q] = q + PLCP'[q]
+  msf_u32 n, n_acgt;
+  int k;
+  // text
+  const msf_u64 *tp;      // packed text (separators hold arbitrary codes)
+  msf_u64 N;
+  const msf_u64 *seps;    // sorted separator positions, seps[nseps] = ~0
+  msf_u64 nseps;
+  const msf_u32 *wsep;    // per window: index of the first separator >= window start
+  msf_u32 WL;             // window length
+  msf_u64 nwin;
+  msf_u32 skip_min;       // try the G skip when len >= skip_min
+  // output
+  msf_u32 *pool;          // records of 4 x u32: rel, pos, len, cs (ch | sm << 8 | tentative << 9)
+  msf_u32 *batch_next;
+  msf_u32 nb_cap;
+  msf_u32 *nb_used;
+  msf_u32 *wfirst, *wcnt, *wfirstpos, *wlastpos;
+  msf_u32 *flags;         // [0] pool overflow
+  unsigned long long *win_counter;
+  msf_u32 *dpos, *dlen;   // optional per-position dump (parity hook)
+  msf_u8 *dsm, *dhead;
+};
+
+struct MsfLane {
+  msf_u64 i, w0, w1, sepnext;
+  msf_u32 sepidx, w;
+  msf_u32 state, prevpos, prevterm, first;
+  msf_u32 curb, fill, cnt;
+  msf_u32 limit;
+  msf_u32 tkey, lo, hi, rb, prevkey, prevsa, haveprev;
+  msf_u32 pos, len, sm, maxl;
+  msf_u32 glo, ghi, E, gsteps;
+};
+
+MSF_HD void msf_store_rec(const MsfParams &P, msf_u64 slot, msf_u32 a, msf_u32 b, msf_u32 c, msf_u32 d) {
+#if defined(__CUDA_ARCH__)
+  ((uint4 *)P.pool)[slot] = make_uint4(a, b, c, d);
+#else
+  msf_u32 *r = P.pool + 4 * slot;
+  r[0] = a; r[1] = b; r[2] = c; r[3] = d;
+#endif
+}
+
+MSF_HD void msf_emit(const MsfParams &P, MsfLane &L, msf_u32 rel, msf_u32 pos, msf_u32 len, msf_u32 cs) {
+  if (L.curb == MSF_NOB || L.fill == MSF_RB) {
+    msf_u32 nb = MSF_ATOMIC_INC32(P.nb_used);
+    if (nb >= P.nb_cap) {
+      P.flags[0] = 1;
+      nb = MSF_BADB;
+    } else if (L.curb == MSF_NOB) {
+      P.wfirst[L.w] = nb;
+    } else if (L.curb != MSF_BADB) {
+      P.batch_next[L.curb] = nb;
+    }
+    L.curb = nb;
+    L.fill = 0;
+  }
+  if (L.curb != MSF_BADB) msf_store_rec(P, (msf_u64)L.curb * MSF_RB + L.fill, rel, pos, len, cs);
+  L.fill++;
+  L.cnt++;
+}
+
+// order of the reference suffix s against the text suffix at i (limit symbols up to its separator):
+// m = LCE, returns true when the reference suffix is the smaller one.  Same semantics as probe()
+// in ms.cu on the 8-bit data: past n_acgt the reference holds no A/C/G/T, and the separator 0x02
+// is smaller than every reference symbol but x[n-2] = 1 and x[n-1] = 0.
+MSF_HD bool msf_compare(const MsfParams &P, msf_u64 i, msf_u32 limit, msf_u32 s, msf_u32 &m, msf_u32 &xb,
+                        msf_u32 &tb) {
+  msf_u32 room = s < P.n_acgt ? P.n_acgt - s : 0u;
+  msf_u32 maxl = limit < room ? limit : room;
+  m = msf_lce(P.tp, i, P.xp, s, maxl);
+  xb = MSF_LD8(P.x8 + s + m);
+  tb = m == limit ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, i + m));
+  return xb < tb;
+}
+
+// exact search on packed data (rare cases); same result as lane_search()/warp_search() in ms.cu
+MSF_HDN void msf_generic_search(const MsfParams &P, msf_u64 i, msf_u32 limit, msf_u32 &pos, msf_u32 &len,
+                                msf_u32 &sm) {
+  msf_u32 lo = 0, hi = P.n;
+  if (limit >= (msf_u32)P.k) {
+    msf_u64 be = msf_be64(msf_get64(P.tp, i));
+    msf_u32 code = (msf_u32)(be >> (64 - 2 * P.k));
+    lo = MSF_LD32(P.ktab + code);
+    hi = MSF_LD32(P.ktab + code + 1);
+  }
+  msf_u32 m, xb, tb;
+  while (lo < hi) {
+    msf_u32 mid = lo + ((hi - lo) >> 1);
+    msf_u32 s = (msf_u32)(MSF_LD64(P.sak + mid) >> 32);
+    if (msf_compare(P, i, limit, s, m, xb, tb)) lo = mid + 1; else hi = mid;
+  }
+  long long lp = -1, ls = -1;
+  msf_u32 ppos = 0, spos = 0;
+  if (lo > 0) {
+    ppos = (msf_u32)(MSF_LD64(P.sak + lo - 1) >> 32);
+    msf_compare(P, i, limit, ppos, m, xb, tb);
+    lp = m;
+  }
+  if (lo < P.n) {
+    spos = (msf_u32)(MSF_LD64(P.sak + lo) >> 32);
+    msf_compare(P, i, limit, spos, m, xb, tb);
+    ls = m;
+  }
+  if (ls >= lp) { pos = spos; len = (msf_u32)ls; sm = 1; }
+  else { pos = ppos; len = (msf_u32)lp; sm = 0; }
+}
+
+// ---- the state machine ------------------------------------------------------------------------
+MSF_HD void msf_dump(const MsfParams &P, msf_u64 p, msf_u32 pos, msf_u32 len, msf_u32 sm, msf_u32 head) {
+  if (P.dpos) {
+    P.dpos[p] = pos; P.dlen[p] = len; P.dsm[p] = (msf_u8)sm; P.dhead[p] = (msf_u8)head;
+  }
+}
+
+// what the common tail of a step has to do
+#define MSF_ACT_NONE 0u
+#define MSF_ACT_FIN 1u        // (L.pos, L.len, L.sm) is the MS of position L.i
+#define MSF_ACT_GENERIC 2u    // run the exact search first, then FIN
+#define MSF_ACT_TERM 4u       // position L.i is a document terminator
+
+// MS of position L.i is (L.pos, L.len, L.sm): head test (:1154), record, then skip or step.
+// term: L.i holds a separator -> sentinel head (:1198-1212).
+MSF_HD void msf_fin(const MsfParams &P, MsfLane &L, bool term) {
+  const bool tent = !term && L.first && !L.prevterm;   // window starts inside a document
+  const bool head = term || L.prevterm || L.pos != L.prevpos + 1;
+  if (L.first) P.wfirstpos[L.w] = (term || L.prevterm) ? MSF_INVALID : L.pos;
+  if (head || tent) {
+    msf_u32 ch = L.prevterm ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i - 1));
+    msf_emit(P, L, (msf_u32)(L.i - L.w0), L.pos, L.len, ch | (L.sm << 8) | (tent ? 1u << 9 : 0u));
+  }
+  msf_dump(P, L.i, L.pos, L.len, L.sm, head || tent);
+  L.first = 0;
+  L.prevterm = term ? 1u : 0u;
+  if (term) {
+    L.sepidx++;
+    L.sepnext = MSF_LD64(P.seps + L.sepidx);
+    L.i++;
+    L.state = MSF_S_POS;
+  } else if (L.len >= P.skip_min && L.len > 1) {
+    L.E = L.pos + L.len;
+    L.glo = L.pos + 1;
+    L.ghi = L.E;
+    L.gsteps = 0;
+    L.state = MSF_S_GSCAN;
+  } else {
+    L.prevpos = L.pos;
+    L.i++;
+    L.state = MSF_S_POS;
+  }
+}
+
+// the non-head run after a head ends at q = first position in (pos, E) with G[q] >= E (or E)
+MSF_HD void msf_skip_to(const MsfParams &P, MsfLane &L, msf_u32 q) {
+  msf_u32 skip = q - L.pos - 1;
+  if (P.dpos)
+    for (msf_u32 k2 = 1; k2 <= skip; k2++) msf_dump(P, L.i + k2, L.pos + k2, L.len - k2, L.sm, 0);
+  L.i += 1 + (msf_u64)skip;
+  L.prevpos = L.pos + skip;
+  L.state = MSF_S_POS;
+}
+
+// single candidate s whose key equals the text's: extend it (or leave it to the exact search)
+MSF_HD msf_u32 msf_start_ext(const MsfParams &P, MsfLane &L, msf_u32 s) {
+  const msf_u32 KL = (msf_u32)P.k + 16;
+  if ((msf_u64)s + KL > P.n_acgt) return MSF_ACT_GENERIC;
+  L.pos = s;
+  L.len = KL;
+  msf_u32 room = P.n_acgt - s;
+  L.maxl = L.limit < room ? L.limit : room;
+  L.state = MSF_S_EXT;
+  return MSF_ACT_NONE;
+}
+
+// predecessor (prevkey/prevsa, if any) and successor (skey/ssa, if found) are known by key only
+MSF_HD msf_u32 msf_decide(const MsfParams &P, MsfLane &L, bool found, msf_u32 skey, msf_u32 ssa) {
+  const msf_u32 KL = (msf_u32)P.k + 16;
+  if ((found && (msf_u64)ssa + KL > P.n_acgt) || (L.haveprev && (msf_u64)L.prevsa + KL > P.n_acgt))
+    return MSF_ACT_GENERIC;
+  msf_u32 lp = 0, ls = 0;
+  if (L.haveprev) lp = (msf_u32)P.k + (MSF_CLZ32(L.prevkey ^ L.tkey) >> 1);
+  if (found) ls = (msf_u32)P.k + (MSF_CLZ32(skey ^ L.tkey) >> 1);
+  if (found && (!L.haveprev || ls >= lp)) { L.pos = ssa; L.len = ls; L.sm = 1; }
+  else { L.pos = L.prevsa; L.len = lp; L.sm = 0; }
+  return MSF_ACT_FIN;
+}
+
+MSF_HD void msf_step(const MsfParams &P, MsfLane &L) {
+  msf_u32 act = MSF_ACT_NONE;
+  switch (L.state) {
+    case MSF_S_FETCH: {
+      msf_u64 w = MSF_ATOMIC_INC64(P.win_counter);
+      if (w >= P.nwin) { L.state = MSF_S_DONE; break; }
+      L.w = (msf_u32)w;
+      L.w0 = w * P.WL;
+      L.w1 = L.w0 + P.WL < P.N ? L.w0 + P.WL : P.N;
+      L.i = L.w0;
+      L.sepidx = MSF_LD32(P.wsep + w);
+      L.sepnext = MSF_LD64(P.seps + L.sepidx);
+      L.prevterm = (L.w0 == 0) || (L.sepidx > 0 && MSF_LD64(P.seps + L.sepidx - 1) == L.w0 - 1);
+      L.prevpos = MSF_INVALID;
+      L.first = 1;
+      L.curb = MSF_NOB;
+      L.fill = 0;
+      L.cnt = 0;
+      L.state = MSF_S_POS;
+      break;
+    }
+    case MSF_S_POS: {
+      if (L.i >= L.w1) {                                  // close the window
+        P.wcnt[L.w] = L.cnt;
+        P.wlastpos[L.w] = L.prevterm ? MSF_INVALID : L.prevpos - (msf_u32)(L.i - L.w1);
+        L.state = MSF_S_FETCH;
+        break;
+      }
+      if (L.i == L.sepnext) {                             // document terminator (:1198-1212)
+        L.pos = P.n - 1; L.len = 0; L.sm = 0;
+        act = MSF_ACT_TERM;
+        break;
+      }
+      const msf_u32 KL = (msf_u32)P.k + 16;
+      msf_u64 dist = L.sepnext - L.i;
+      L.limit = dist > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (msf_u32)dist;
+      if (L.limit < KL) { act = MSF_ACT_GENERIC; break; }
+      msf_u64 be = msf_be64(msf_get64(P.tp, L.i));
+      msf_u32 code = (msf_u32)(be >> (64 - 2 * P.k));
+      L.tkey = (msf_u32)((be << (2 * P.k)) >> 32);
+      msf_u32 lb = MSF_LD32(P.ktab + code), rb = MSF_LD32(P.ktab + code + 1);
+      if (lb == rb) { act = MSF_ACT_GENERIC; break; }
+      L.lo = lb; L.hi = rb; L.rb = rb; L.haveprev = 0;
+      if (rb - lb > 16) { L.state = MSF_S_BIN; break; }
+      L.state = MSF_S_SCAN;
+    }                                                     // small bucket: scan it in the same step
+    // fall through
+    case MSF_S_SCAN: {
+      msf_u64 e[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) e[j] = L.lo + j < L.hi ? MSF_LD64(P.sak + L.lo + j) : ~0ull;
+      // first entry (of these four) whose key is >= the text's; smaller ones become the predecessor
+      int f = 4;
+#pragma unroll
+      for (int j = 3; j >= 0; j--)
+        if (L.lo + j < L.hi && (msf_u32)e[j] >= L.tkey) f = j;
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (j < f && L.lo + j < L.hi) { L.prevkey = (msf_u32)e[j]; L.prevsa = (msf_u32)(e[j] >> 32); L.haveprev = 1; }
+      if (f < 4) {
+        msf_u64 ef = f == 0 ? e[0] : f == 1 ? e[1] : f == 2 ? e[2] : e[3];
+        msf_u64 en = f == 0 ? e[1] : f == 1 ? e[2] : e[3];             // entry after it (if loaded)
+        msf_u32 key = (msf_u32)ef, s = (msf_u32)(ef >> 32), idx = L.lo + f;
+        if (key != L.tkey) act = msf_decide(P, L, true, key, s);
+        else if (idx + 1 >= L.rb) act = msf_start_ext(P, L, s);          // last of the bucket: unique
+        else if (f < 3 && idx + 1 < L.hi) act = (msf_u32)en == L.tkey ? MSF_ACT_GENERIC : msf_start_ext(P, L, s);
+        else { L.pos = s; L.lo = idx; L.state = MSF_S_EQ; }
+      } else {
+        L.lo += 4;
+        if (L.lo >= L.hi) act = msf_decide(P, L, false, 0, 0);           // every key is smaller
+      }
+      break;
+    }
+    case MSF_S_EQ: {                                      // is the entry after the equal one equal too?
+      msf_u64 e = MSF_LD64(P.sak + L.lo + 1);
+      act = (msf_u32)e == L.tkey ? MSF_ACT_GENERIC : msf_start_ext(P, L, L.pos);
+      break;
+    }
+    case MSF_S_BIN: {                                     // keys < tkey left of lo, >= tkey from hi on
+      msf_u32 mid = L.lo + ((L.hi - L.lo) >> 1);
+      msf_u64 e = MSF_LD64(P.sak + mid);
+      if ((msf_u32)e < L.tkey) { L.lo = mid + 1; L.prevkey = (msf_u32)e; L.prevsa = (msf_u32)(e >> 32); L.haveprev = 1; }
+      else L.hi = mid;
+      if (L.hi - L.lo <= 3) {
+        L.hi = L.hi + 1 < L.rb ? L.hi + 1 : L.rb;
+        L.state = MSF_S_SCAN;
+      }
+      break;
+    }
+    case MSF_S_EXT: {
+      bool fin = false;
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        msf_u32 rem = L.maxl - L.len;
+        if (fin || rem == 0) { fin = true; continue; }
+        msf_u64 d = msf_get64(P.tp, L.i + L.len) ^ msf_get64(P.xp, (msf_u64)L.pos + L.len);
+        msf_u32 take = rem < 32 ? rem : 32;
+        msf_u32 m = d ? (MSF_CTZ64(d) >> 1) : 32;
+        if (m >= take) { L.len += take; if (take == rem) fin = true; }
+        else { L.len += m; fin = true; }
+      }
+      if (fin) {
+        msf_u32 xb = MSF_LD8(P.x8 + L.pos + L.len);
+        msf_u32 tb = L.len == L.limit ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i + L.len));
+        L.sm = xb > tb ? 1u : 0u;
+        act = MSF_ACT_FIN;
+      }
+      break;
+    }
+    case MSF_S_GSCAN: {                                   // G[q] >= E for all q in [ghi, E)
+      if (L.ghi <= L.glo) { msf_skip_to(P, L, L.glo < L.E ? L.glo : L.E); break; }
+      // 16 entries below ghi, in aligned groups of four
+      msf_u32 top = L.ghi - 1;
+      msf_u32 blk = top >> 2;
+      msf_u32 q = L.ghi;                                  // smallest index known to satisfy
+      bool stop = false;
+#pragma unroll
+      for (int b = 0; b < 4; b++) {
+        if (stop || blk < (msf_u32)b) continue;
+        msf_u32 base = (blk - b) << 2;
+        if (base + 3 < L.glo) { stop = true; continue; }
+        msf_u32 g[4];
+#if defined(__CUDA_ARCH__)
+        uint4 v = __ldg((const uint4 *)(P.G + base));
+        g[0] = v.x; g[1] = v.y; g[2] = v.z; g[3] = v.w;
+#else
+        for (int t = 0; t < 4; t++) g[t] = base + t < P.n ? P.G[base + t] : 0xFFFFFFFFu;
+#endif
+#pragma unroll
+        for (int t = 3; t >= 0; t--) {
+          msf_u32 idx = base + t;
+          if (stop || idx >= q || idx < L.glo) continue;
+          if (g[t] >= L.E) q = idx; else stop = true;
+        }
+      }
+      if (stop || q <= L.glo) { msf_skip_to(P, L, q); break; }
+      L.ghi = q;
+      if (++L.gsteps >= 2) L.state = MSF_S_GBIN;
+      break;
+    }
+    case MSF_S_GBIN: {                                    // bisection on [glo, ghi)
+      if (L.glo >= L.ghi) { msf_skip_to(P, L, L.glo); break; }
+      msf_u32 mid = L.glo + ((L.ghi - L.glo) >> 1);
+      if (MSF_LD32(P.G + mid) >= L.E) L.ghi = mid; else L.glo = mid + 1;
+      break;
+    }
+    default: break;
+  }
+  // ---- common tail: one copy of the exact search and of the head test / record ----
+  if (act & MSF_ACT_GENERIC) msf_generic_search(P, L.i, L.limit, L.pos, L.len, L.sm);
+  if (act) msf_fin(P, L, (act & MSF_ACT_TERM) != 0);
+}
+
+// ---- window fix-up (head test across window borders) ------------------------------------------
+// The first position of a window that starts inside a document is recorded tentatively; it is a
+// head iff its pos differs from the previous position's pos + 1 (:1154), which the previous
+// window reports in wlastpos.  Returns 1 when the tentative record has to be dropped.
+MSF_HD msf_u32 msf_window_drop(const msf_u32 *wfirstpos, const msf_u32 *wlastpos, msf_u64 w) {
+  if (w == 0) return 0;
+  msf_u32 fp = wfirstpos[w];
+  if (fp == MSF_INVALID) return 0;                 // window starts at a document start / terminator
+  msf_u32 lp = wlastpos[w - 1];
+  return (lp != MSF_INVALID && fp == lp + 1) ? 1u : 0u;
+}
+
+// number of k-mers <= the suffix s of the 8-bit augmented reference (non-decreasing in SA order);
+// ktab[m] = first rank r with m < f(r)   (index.cu: k_ktab_mark + max-scan)
+MSF_HD msf_u32 msf_kmers_le_suffix(const msf_u8 *x, msf_u32 s, int k) {
+  msf_u32 m = 0;
+  for (int j = 0; j < k; j++) {
+    msf_u8 c = x[s + j];                // x[n-1] = 0 stops the walk before the padding
+    int d = c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : -1;
+    if (d < 0) {
+      int dl = (c > 'A') + (c > 'C') + (c > 'G') + (c > 'T');
+      return (m * 4 + dl) << (2 * (k - 1 - j));
+    }
+    m = m * 4 + d;
+  }
+  return m + 1;
+}

@@ -1,0 +1,275 @@
+// Stage 2/3, brute-force tile path: how many suffixes of its bucket precede every head
+// (counterSmallerThanHead, CMS-BWT-functions.cpp:1517-1603 / small path :709-902), the bucket sizes
+// (:368-390 as interval coverage) and the placement of the head symbols (:1640-1688).
+//
+// The reference walks every non-head of every phrase and does an ordered-map lower_bound per
+// incidence.  Here the reference positions are cut into tiles of CMS_LT_W positions; every head is
+// filed under the tile of its pos, every long phrase (toNext > 0) under each tile its non-head
+// run [pos+1, pos+toNext] intersects.  One CTA per tile then
+//   pass A (k_tile_cov):    bucket sizes cov[p] = heads at p + ranges covering p, coalesced
+//   pass B (k_tile_place):  within(h) = #{heads at pos_h with smaller kappa} + #{ranges covering
+//                           pos_h with smaller kappa}; the head symbol goes to
+//                           out[base[ISA[pos_h]] + within(h)].
+// No sort is involved; the pair tests are O(heads x depth) and run out of shared memory.  When a
+// collection is so deep that this would cost more than `tile_budget` pair tests, or a tile does not
+// fit shared memory, tiles_build returns false and the sort-based sweep of heads.cu is used.
+#include "common.cuh"
+#include <cub/cub.cuh>
+
+#define LT_SHIFT 8
+#define LT_W (1u << LT_SHIFT)
+#define LT_THREADS 256
+#define LT_MAX_ENTRIES 12288          // heads + ranges of one tile that fit shared memory (16 B each)
+
+struct __align__(16) TileEnt { u32 a, b; u64 kappa; };   // head: a = id, b = q | ch << 8; range: a = lo | hi << 16
+
+// ---- histogram of entries per tile ---------------------------------------------------------------
+__global__ void k_tile_hist(const u32 *pos, const u32 *len, const u32 *toNext, u64 H, u32 *hcnt, u32 *rcnt) {
+  const int lane = threadIdx.x & 31;
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  bool in = i < H && len[i] != 0;                  // sentinels (len 0) are placed by document index
+  u32 p = in ? pos[i] : 0, tn = in ? toNext[i] : 0;
+  if (in) atomicAdd(hcnt + (p >> LT_SHIFT), 1u);
+  u32 ta = (p + 1) >> LT_SHIFT, tb = (p + tn) >> LT_SHIFT;
+  u32 nt = (in && tn) ? tb - ta + 1 : 0;
+  if (nt && nt <= 8)
+    for (u32 t = ta; t <= tb; t++) atomicAdd(rcnt + t, 1u);
+  unsigned big = __ballot_sync(0xffffffffu, nt > 8);
+  while (big) {
+    int src = __ffs(big) - 1;
+    big &= big - 1;
+    u32 a = __shfl_sync(0xffffffffu, ta, src), m = __shfl_sync(0xffffffffu, nt, src);
+    for (u32 k = lane; k < m; k += 32) atomicAdd(rcnt + a + k, 1u);
+  }
+}
+
+__device__ __forceinline__ void put_range(TileEnt *re, const u32 *roff, u32 *rcur, u32 t, u32 p, u32 tn,
+                                          u64 kap) {
+  u32 a = t << LT_SHIFT;
+  u32 lo = max(p + 1, a) - a, hi = min(p + tn, a + LT_W - 1) - a;
+  u32 slot = roff[t] + atomicAdd(rcur + t, 1u);
+  TileEnt e; e.a = lo | (hi << 16); e.b = 0; e.kappa = kap;
+  re[slot] = e;
+}
+
+__global__ void k_tile_scatter(const u32 *pos, const u32 *len, const u16 *cs, const u32 *toNext,
+                               const u64 *kappa, u64 H, const u32 *hoff, const u32 *roff, u32 *hcur,
+                               u32 *rcur, TileEnt *he, TileEnt *re) {
+  const int lane = threadIdx.x & 31;
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  bool in = i < H && len[i] != 0;
+  u32 p = in ? pos[i] : 0, tn = in ? toNext[i] : 0;
+  u64 kap = in ? kappa[i] : 0;
+  if (in) {
+    u32 t = p >> LT_SHIFT;
+    u32 slot = hoff[t] + atomicAdd(hcur + t, 1u);
+    TileEnt e; e.a = (u32)i; e.b = (p & (LT_W - 1)) | ((u32)(cs[i] & 0xFF) << 8); e.kappa = kap;
+    he[slot] = e;
+  }
+  u32 ta = (p + 1) >> LT_SHIFT, tb = (p + tn) >> LT_SHIFT;
+  u32 nt = (in && tn) ? tb - ta + 1 : 0;
+  if (nt && nt <= 8)
+    for (u32 t = ta; t <= tb; t++) put_range(re, roff, rcur, t, p, tn, kap);
+  unsigned big = __ballot_sync(0xffffffffu, nt > 8);
+  while (big) {
+    int src = __ffs(big) - 1;
+    big &= big - 1;
+    u32 a = __shfl_sync(0xffffffffu, ta, src), m = __shfl_sync(0xffffffffu, nt, src);
+    u32 bp = __shfl_sync(0xffffffffu, p, src), btn = __shfl_sync(0xffffffffu, tn, src);
+    u64 bk = __shfl_sync(0xffffffffu, kap, src);
+    for (u32 k = lane; k < m; k += 32) put_range(re, roff, rcur, a + k, bp, btn, bk);
+  }
+}
+
+// ---- pass A: bucket sizes + cost of pass B -------------------------------------------------------
+__global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, const TileEnt *re, const u32 *hoff,
+                                                         const u32 *roff, u32 n, u32 ndocs, u32 *cov,
+                                                         unsigned long long *work, u32 *maxent) {
+  __shared__ u32 s_h[LT_W];
+  __shared__ int s_d[LT_W + 1];
+  typedef cub::BlockScan<int, LT_THREADS> BS;
+  typedef cub::BlockReduce<unsigned long long, LT_THREADS> BR;
+  __shared__ typename BS::TempStorage ts;
+  __shared__ typename BR::TempStorage tr;
+  const u32 t = blockIdx.x, tid = threadIdx.x;
+  const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
+  s_h[tid] = 0; s_d[tid] = 0;
+  if (tid == 0) s_d[LT_W] = 0;
+  __syncthreads();
+  for (u32 j = h0 + tid; j < h1; j += LT_THREADS) atomicAdd(&s_h[he[j].b & (LT_W - 1)], 1u);
+  for (u32 j = r0 + tid; j < r1; j += LT_THREADS) {
+    u32 lh = re[j].a;
+    atomicAdd(&s_d[lh & 0xFFFF], 1);
+    atomicAdd(&s_d[(lh >> 16) + 1], -1);
+  }
+  __syncthreads();
+  int d = s_d[tid], incl;
+  BS(ts).InclusiveSum(d, incl);
+  const u32 hq = s_h[tid];
+  const u32 p = (t << LT_SHIFT) + tid;
+  if (p < n) cov[p] = (u32)incl + hq + (p == n - 1 ? ndocs : 0u);
+  // pair tests of pass B for this tile: every head against every range and its position mates
+  unsigned long long w = (unsigned long long)hq * (hq + (r1 - r0));
+  unsigned long long tot = BR(tr).Sum(w);
+  if (tid == 0) {
+    if (tot) atomicAdd(work, tot);
+    atomicMax(maxent, (h1 - h0) + (r1 - r0));
+  }
+}
+
+// ---- pass B: within + head symbols --------------------------------------------------------------
+__global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, const TileEnt *re, const u32 *hoff,
+                                                           const u32 *roff, const u32 *isa, const u64 *base,
+                                                           u32 n, u8 *out, u32 *within_out, u64 *off_out) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W];
+  __shared__ u64 s_base[LT_W];
+  typedef cub::BlockScan<u32, LT_THREADS> BS;
+  __shared__ typename BS::TempStorage ts;
+  const u32 t = blockIdx.x, tid = threadIdx.x;
+  const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
+  const u32 hc = h1 - h0, rc = r1 - r0;
+  if (hc == 0) return;
+  TileEnt *s_he = (TileEnt *)smem;
+  TileEnt *s_re = s_he + hc;
+  s_cnt[tid] = 0; s_cur[tid] = 0;
+  {
+    u32 p = (t << LT_SHIFT) + tid;
+    s_base[tid] = p < n ? base[isa[p]] : 0;
+  }
+  __syncthreads();
+  for (u32 j = tid; j < rc; j += LT_THREADS) s_re[j] = re[r0 + j];
+  for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[he[h0 + j].b & (LT_W - 1)], 1u);
+  __syncthreads();
+  u32 ex;
+  BS(ts).ExclusiveSum(s_cnt[tid], ex);
+  s_off[tid] = ex;
+  if (tid == LT_THREADS - 1) s_off[LT_W] = ex + s_cnt[tid];
+  __syncthreads();
+  for (u32 j = tid; j < hc; j += LT_THREADS) {          // heads grouped by position
+    TileEnt e = he[h0 + j];
+    u32 q = e.b & (LT_W - 1);
+    s_he[s_off[q] + atomicAdd(&s_cur[q], 1u)] = e;
+  }
+  __syncthreads();
+  for (u32 j = tid; j < hc; j += LT_THREADS) {
+    const TileEnt e = s_he[j];
+    const u32 q = e.b & (LT_W - 1);
+    const u64 kap = e.kappa;
+    u32 w = 0;
+    for (u32 jj = s_off[q]; jj < s_off[q + 1]; jj++) w += s_he[jj].kappa < kap;
+    for (u32 r = 0; r < rc; r++) {
+      const TileEnt g = s_re[r];
+      w += ((g.a & 0xFFFF) <= q) & (q <= (g.a >> 16)) & (g.kappa < kap);
+    }
+    const u64 off = s_base[q] + w;
+    out[off] = (u8)(e.b >> 8);
+    if (within_out) { within_out[e.a] = w; off_out[e.a] = off; }
+  }
+}
+
+// terminators: bucket of x[n-1..] (SA rank 0) holds one suffix per document, in document order
+__global__ void k_place_sentinels(const u32 *len, const u16 *cs, const u32 *sexcl, u64 H, u8 *out,
+                                  u32 *within_out, u64 *off_out) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H || len[i] != 0) return;
+  u32 d = sexcl[i];
+  out[d] = (u8)(cs[i] & 0xFF);
+  if (within_out) { within_out[i] = d; off_out[i] = d; }
+}
+
+// Builds the tile entries and cov[]; false = too heavy for the brute-force path (nothing kept).
+bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
+  cudaStream_t st = c->st;
+  const u64 H = c->H;
+  const u32 n = c->ix.n;
+  const int B = 256;
+  const u32 gH = (u32)((H + B - 1) / B);
+  const u32 ntiles = (n >> LT_SHIFT) + 1;
+  c->light = false;
+  DBuf hcnt, rcnt, tmp, acc;
+  hcnt.alloc(((size_t)ntiles + 1) * 4, st); rcnt.alloc(((size_t)ntiles + 1) * 4, st);
+  c->t_hoff.alloc(((size_t)ntiles + 1) * 4, st); c->t_roff.alloc(((size_t)ntiles + 1) * 4, st);
+  acc.alloc(16, st);
+  CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
+  CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
+  CK(cudaMemsetAsync(acc.p, 0, 16, st));
+  k_tile_hist<<<gH, B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_toNext.as<u32>(), H,
+                                hcnt.as<u32>(), rcnt.as<u32>());
+  size_t tb = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tb, hcnt.as<u32>(), c->t_hoff.as<u32>(), (int)(ntiles + 1), st);
+  tmp.alloc(tb, st);
+  size_t t1 = tb;
+  CK(cub::DeviceScan::ExclusiveSum(tmp.p, t1, hcnt.as<u32>(), c->t_hoff.as<u32>(), (int)(ntiles + 1), st));
+  t1 = tb;
+  // the range total can exceed 2^32 only for collections far deeper than one device holds
+  DBuf rtot; rtot.alloc(8, st);
+  {
+    size_t tr = 0;
+    cub::DeviceReduce::Sum(nullptr, tr, rcnt.as<u32>(), rtot.as<unsigned long long>(), (int)ntiles, st);
+    DBuf tmp2; tmp2.alloc(tr, st);
+    CK(cub::DeviceReduce::Sum(tmp2.p, tr, rcnt.as<u32>(), rtot.as<unsigned long long>(), (int)ntiles, st));
+    CK(cudaStreamSynchronize(st));
+  }
+  unsigned long long R = 0;
+  CK(cudaMemcpyAsync(&R, rtot.p, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  c->launches += 4;
+  if (R >= 0xFFFFFFF0ull) return false;
+  CK(cub::DeviceScan::ExclusiveSum(tmp.p, t1, rcnt.as<u32>(), c->t_roff.as<u32>(), (int)(ntiles + 1), st));
+  u32 HE = 0;
+  CK(cudaMemcpyAsync(&HE, c->t_hoff.as<u32>() + ntiles, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  c->t_he.alloc(((size_t)HE + 1) * sizeof(TileEnt), st);
+  c->t_re.alloc(((size_t)R + 1) * sizeof(TileEnt), st);
+  CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));      // reused as cursors
+  CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
+  k_tile_scatter<<<gH, B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
+                                   c->h_toNext.as<u32>(), kappa, H, c->t_hoff.as<u32>(), c->t_roff.as<u32>(),
+                                   hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>());
+  c->d_cov.alloc(((size_t)n + 1) * 4, st);
+  k_tile_cov<<<ntiles, LT_THREADS, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+                                            c->t_roff.as<u32>(), n, (u32)c->stats.n_docs, c->d_cov.as<u32>(),
+                                            acc.as<unsigned long long>(), acc.as<u32>() + 2);
+  c->launches += 3;
+  CK(cudaGetLastError());
+  unsigned long long hacc[2] = {0, 0};
+  CK(cudaMemcpyAsync(hacc, acc.p, 16, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const u64 work = hacc[0];
+  const u32 maxent = (u32)hacc[1];
+  c->stats.n_items = (u64)HE + R;
+  c->stats.pair_tests = work;
+  if (work > (u64)c->tile_budget || maxent > LT_MAX_ENTRIES) {
+    c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release(); c->d_cov.release();
+    return false;
+  }
+  c->tile_maxent = maxent;
+  c->h_sexcl.release();
+  std::swap(c->h_sexcl.p, sexcl.p);
+  std::swap(c->h_sexcl.bytes, sexcl.bytes);
+  c->light = true;
+  return true;
+}
+
+// pass B + terminators, after the output has been filled with the reference symbols
+void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out) {
+  cudaStream_t st = c->st;
+  const u64 H = c->H;
+  const u32 n = c->ix.n;
+  const u32 ntiles = (n >> LT_SHIFT) + 1;
+  u32 *wo = nullptr; u64 *oo = nullptr;
+  if (c->dump) {
+    c->h_within.alloc(H * 4, st); c->h_off.alloc(H * 8, st);
+    wo = c->h_within.as<u32>(); oo = c->h_off.as<u64>();
+  }
+  size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt);
+  if (sm > 40 * 1024)
+    CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_tile_place<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+                                               c->t_roff.as<u32>(), c->ix.isa, base, n, out, wo, oo);
+  k_place_sentinels<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
+                                                           c->h_sexcl.as<u32>(), H, out, wo, oo);
+  c->launches += 2;
+  CK(cudaGetLastError());
+}

@@ -63,6 +63,11 @@ typedef struct {
   uint32_t rank_rounds;     /* doubling rounds of the tail ranking */
   uint32_t kmer_k;
   uint64_t kernel_launches; /* launches issued by ms_run + heads_sort + emit of the last job */
+  double pack_ms;           /* fast path: 2-bit packing of the text + separator list (inside ms_ms) */
+  uint32_t fast_path;       /* 1 = the last ms_run used the 2-bit lane-per-window kernel */
+  uint32_t light_tiles;     /* 1 = the last heads_sort counted every tile by brute force */
+  uint64_t pair_tests;      /* head x (range | position mate) tests of that brute-force pass */
+  uint64_t rank_tied;       /* tails whose reference ISA rank is shared (refined after the radix sort) */
 } cmsbwt_stats;
 
 /* replaces: process start-up of the reference (no equivalent; it has no device). */

@@ -1,0 +1,117 @@
+// TEST INFRASTRUCTURE ONLY: runs the lane state machine of cms_bwt_b200/csrc/ms_fast.cuh on the CPU,
+// lane by lane, so that its logic can be checked against the oracle without a GPU.  The product
+// never loads this; k_ms_fast (ms_fast.cu) is the only shipped user of that header.
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <vector>
+#include "../../cms_bwt_b200/csrc/ms_fast.cuh"
+
+typedef uint8_t u8;
+typedef uint32_t u32;
+typedef uint64_t u64;
+
+static void pack(const u8 *s, u64 len, std::vector<u64> &out) {
+  out.assign((len + 31) / 32 + MSF_PAD_WORDS, 0);
+  for (u64 j = 0; j < len; j++) {
+    u8 c = s[j];
+    if (c == 'A' || c == 'C' || c == 'G' || c == 'T') out[j >> 5] |= (u64)msf_code_of(c) << ((j & 31) * 2);
+  }
+}
+
+extern "C" {
+// step counts per state of the last runs (used to model the kernel's cost per mutation)
+unsigned long long g_steps[16];
+void msf_host_steps(unsigned long long *out) { for (int i = 0; i < 16; i++) { out[i] = g_steps[i]; g_steps[i] = 0; } }
+
+// returns the number of heads (text order) or -1 when the input is not eligible for the fast path
+// (reference or text not pure ACGT), -2 on pool overflow.
+// outputs: per-position dump arrays (N entries) and the compacted head list (capacity N).
+long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plcp_prime, const u8 *text,
+                       u64 N, u32 WL, int k, u32 skip_min, u32 nlanes, u32 *dpos, u32 *dlen, u8 *dsm,
+                       u8 *dhead, u64 *hg, u32 *hpos, u32 *hlen, uint16_t *hcs) {
+  // ---- eligibility (capi.cu: index purity) ----
+  u32 n_acgt = 0;
+  while (n_acgt < n && (x[n_acgt] == 'A' || x[n_acgt] == 'C' || x[n_acgt] == 'G' || x[n_acgt] == 'T')) n_acgt++;
+  for (u32 j = n_acgt; j < n; j++)
+    if (x[j] == 'A' || x[j] == 'C' || x[j] == 'G' || x[j] == 'T') return -1;
+  if (n_acgt == 0 || x[n_acgt] >= 'A') return -1;
+  for (u64 j = 0; j < N; j++) {
+    u8 c = text[j];
+    if (!(c == 2 || c == 'A' || c == 'C' || c == 'G' || c == 'T')) return -1;
+  }
+  // ---- index ----
+  std::vector<u64> xp, tp;
+  pack(x, n_acgt, xp);
+  xp.resize((n + 31) / 32 + MSF_PAD_WORDS, 0);
+  std::vector<u8> x8(x, x + n);
+  x8.resize(n + 64, 0xFF);
+  const u64 K = 1ull << (2 * k);
+  std::vector<u32> ktab(K + 2, 0);
+  {
+    u32 fp = 0;
+    for (u32 r = 0; r < n; r++) {
+      u32 f = msf_kmers_le_suffix(x8.data(), (u32)sa[r], k);
+      if (f > fp) ktab[fp] = r;
+      if (r == n - 1 && f <= K) ktab[f] = n;
+      fp = f;
+    }
+    u32 mx = 0;
+    for (u64 m = 0; m <= K; m++) { mx = std::max(mx, ktab[m]); ktab[m] = mx; }
+  }
+  std::vector<u64> sak(n);
+  for (u32 r = 0; r < n; r++)
+    sak[r] = (u64)msf_make_key(xp.data(), (u32)sa[r], n_acgt, k) | ((u64)(u32)sa[r] << 32);
+  std::vector<u32> G(n + 8);
+  for (u32 i = 0; i < n; i++) G[i] = i + (u32)plcp_prime[i];
+  // ---- text ----
+  pack(text, N, tp);
+  std::vector<u64> seps;
+  for (u64 j = 0; j < N; j++) if (text[j] == 2) seps.push_back(j);
+  const u64 nseps = seps.size();
+  seps.push_back(~0ull);
+  const u64 nwin = (N + WL - 1) / WL;
+  std::vector<u32> wsep(nwin);
+  for (u64 w = 0; w < nwin; w++)
+    wsep[w] = (u32)(std::lower_bound(seps.begin(), seps.begin() + nseps, w * WL) - seps.begin());
+  // ---- run ----
+  const u64 nb_cap = N / MSF_RB + 2 * nwin + 16;
+  std::vector<u32> pool(nb_cap * MSF_RB * 4), bnext(nb_cap), wfirst(nwin), wcnt(nwin, 0), wfp(nwin), wlp(nwin);
+  u32 nb_used = 0, flags[2] = {0, 0};
+  unsigned long long counter = 0;
+  MsfParams P;
+  P.xp = xp.data(); P.x8 = x8.data(); P.sak = sak.data(); P.ktab = ktab.data(); P.G = G.data();
+  P.n = n; P.n_acgt = n_acgt; P.k = k;
+  P.tp = tp.data(); P.N = N; P.seps = seps.data(); P.nseps = nseps; P.wsep = wsep.data();
+  P.WL = WL; P.nwin = nwin; P.skip_min = skip_min;
+  P.pool = pool.data(); P.batch_next = bnext.data(); P.nb_cap = (u32)nb_cap; P.nb_used = &nb_used;
+  P.wfirst = wfirst.data(); P.wcnt = wcnt.data(); P.wfirstpos = wfp.data(); P.wlastpos = wlp.data();
+  P.flags = flags; P.win_counter = &counter;
+  P.dpos = dpos; P.dlen = dlen; P.dsm = dsm; P.dhead = dhead;
+  std::vector<MsfLane> lanes(nlanes);
+  for (auto &L : lanes) { memset(&L, 0, sizeof L); L.state = MSF_S_FETCH; }
+  bool any = true;
+  while (any) {                       // round-robin: lanes interleave like threads of a warp
+    any = false;
+    for (auto &L : lanes)
+      if (L.state != MSF_S_DONE) { g_steps[L.state]++; msf_step(P, L); any = true; }
+  }
+  if (flags[0]) return -2;
+  // ---- compaction (ms_fast.cu: k_msf_fix + scan + k_msf_gather) ----
+  u64 H = 0;
+  for (u64 w = 0; w < nwin; w++) {
+    u32 drop = msf_window_drop(wfp.data(), wlp.data(), w);
+    if (dhead && drop) dhead[w * WL] = 0;
+    u32 b = wcnt[w] ? wfirst[w] : 0;
+    for (u32 j = 0; j < wcnt[w]; j++) {
+      if (j && j % MSF_RB == 0) b = bnext[b];
+      const u32 *r = &pool[((u64)b * MSF_RB + j % MSF_RB) * 4];
+      if (j == 0 && drop) continue;
+      hg[H] = w * WL + r[0]; hpos[H] = r[1]; hlen[H] = r[2]; hcs[H] = (uint16_t)(r[3] & 0x1FF);
+      H++;
+    }
+  }
+  return (long long)H;
+}
+
+}  // extern "C"

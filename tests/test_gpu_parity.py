@@ -28,8 +28,19 @@ def _inputs(ref_file, coll_file, prefix=P.UINT64_MAX):
     return x, text
 
 
-def _check_case(ctx, x, text, want_bwt=None, desc="", chunk=None, check_ms=True):
+MODES = {                       # which kernels run (DESIGN.md sections 3-5)
+    "fast+tiles": dict(fast=1, tile_budget=1 << 36),     # 2-bit lane kernel + brute-force tiles
+    "general+sweep": dict(fast=0, tile_budget=0),        # 8-bit warp kernel + sort-based sweep
+    "fast+sweep": dict(fast=1, tile_budget=0),
+}
+
+
+def _check_case(ctx, x, text, want_bwt=None, desc="", chunk=None, check_ms=True, mode="fast+tiles",
+                expect_fast=None):
     o = O.Oracle(x)
+    for k, v in MODES[mode].items():
+        ctx.set_param(k, v)
+    desc = "%s [%s]" % (desc, mode)
     if chunk:
         ctx.set_param("chunk_len", chunk)
     ctx.index_upload(x)                       # SA built on the GPU
@@ -47,7 +58,11 @@ def _check_case(ctx, x, text, want_bwt=None, desc="", chunk=None, check_ms=True)
         assert np.array_equal(pos, opos), "MS pos " + desc
         assert np.array_equal(sm, osm), "MS smaller " + desc
         assert np.array_equal(hd, ohd), "MS heads " + desc
+    if expect_fast is not None:
+        assert ctx.stats()["fast_path"] == int(expect_fast), "fast path selection " + desc
     ctx.heads_sort()
+    if mode.endswith("sweep"):
+        assert ctx.stats()["light_tiles"] == 0
     ctx.emit(P.MODE_PLAIN)
     got = ctx.result_download().copy()
     want = o.bwt(text) if want_bwt is None else want_bwt
@@ -61,7 +76,10 @@ def _check_case(ctx, x, text, want_bwt=None, desc="", chunk=None, check_ms=True)
     rl = ctx.result_download().copy()
     assert np.array_equal(rl, O.rle(want)), "RLBWT " + desc
     ctx.set_param("chunk_len", 8192)
-    return ctx.stats()
+    st = ctx.stats()
+    for k, v in MODES["fast+tiles"].items():
+        ctx.set_param(k, v)
+    return st
 
 
 def test_golden_fixtures(ctx):
@@ -70,9 +88,10 @@ def test_golden_fixtures(ctx):
     for f in files:
         z = np.load(f)
         x, text = _inputs(z["ref_file"].tobytes(), z["coll_file"].tobytes(), int(z["prefix"]))
-        _check_case(ctx, x, text, z["bwt"], os.path.basename(f))
-        # also with tiny chunks (exercises chunk borders inside phrases and documents)
-        _check_case(ctx, x, text, z["bwt"], os.path.basename(f) + " chunk=64", chunk=64)
+        for mode in MODES:
+            _check_case(ctx, x, text, z["bwt"], os.path.basename(f), mode=mode)
+            # also with tiny chunks (exercises chunk borders inside phrases and documents)
+            _check_case(ctx, x, text, z["bwt"], os.path.basename(f) + " chunk=64", chunk=64, mode=mode)
 
 
 @pytest.mark.parametrize("block", range(4))
@@ -82,29 +101,40 @@ def test_fuzz_vs_oracle(ctx, block):
         x, text = _inputs(c["ref_file"], c["coll_file"])
         if len(text) == 0:
             continue
-        _check_case(ctx, x, text, None, c["desc"], chunk=[64, 100, 8192][seed % 3])
+        for mode in ("fast+tiles", "general+sweep"):
+            _check_case(ctx, x, text, None, c["desc"], chunk=[64, 100, 8192][seed % 3], mode=mode)
 
 
 def test_config1_scaled_vs_oracle(ctx):
     ref, copies = gen_synth.make_collection(200000, 6, 0.001, 7)
     x = P.augment(ref)
     text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)      # leading empty document
-    st = _check_case(ctx, x, text, None, "200k x6")
-    assert st["n_docs"] == 7
+    st = _check_case(ctx, x, text, None, "200k x6", expect_fast=True)
+    assert st["n_docs"] == 7 and st["light_tiles"] == 1
+    _check_case(ctx, x, text, None, "200k x6", mode="general+sweep", expect_fast=False)
 
 
 def test_sv_and_dense_divergence(ctx):
     ref, copies = gen_synth.make_collection(100000, 5, 0.01, 5, svs=4)
     x = P.augment(ref)
     text = O.docs_to_text(copies)
-    _check_case(ctx, x, text, None, "100k x5 1% + SVs")
+    for mode in MODES:
+        _check_case(ctx, x, text, None, "100k x5 1% + SVs", mode=mode)
 
 
 def test_many_short_documents(ctx):
     ref, copies = gen_synth.make_collection(3000, 2000, 0.002, 9)
     x = P.augment(ref)
     text = O.docs_to_text(copies)
-    _check_case(ctx, x, text, None, "3k x2000", check_ms=True)
+    for mode in MODES:
+        _check_case(ctx, x, text, None, "3k x2000", check_ms=True, mode=mode)
+    # deep enough that a small pair-test budget sends stage 2 to the sort-based sweep
+    ctx.set_param("tile_budget", 1000)
+    ctx.index_upload(x)
+    got = ctx.run(text, P.MODE_PLAIN).copy()
+    assert ctx.stats()["light_tiles"] == 0
+    ctx.set_param("tile_budget", 1 << 36)
+    assert np.array_equal(got, O.Oracle(x).bwt(text))
 
 
 def test_duplicate_documents_and_identity(ctx):
@@ -113,7 +143,8 @@ def test_duplicate_documents_and_identity(ctx):
     x = P.augment(ref)
     docs = [ref.copy() for _ in range(40)] + [ref[100:900].copy() for _ in range(10)]
     text = O.docs_to_text(docs)
-    st = _check_case(ctx, x, text, None, "40 exact copies")
+    for mode in MODES:
+        st = _check_case(ctx, x, text, None, "40 exact copies", mode=mode)
     assert st["rank_rounds"] >= 0
 
 

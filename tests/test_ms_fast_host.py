@@ -1,0 +1,128 @@
+"""CPU check of the lane state machine of the fast matching-statistics kernel.
+
+cms_bwt_b200/csrc/ms_fast.cuh is plain C++ when compiled without nvcc; tests/harness/msf_host.cpp
+runs it lane by lane (round-robin, like the threads of a warp) and this test compares every
+position's (pos, len, smaller, head) and the compacted head list with the oracle
+(oracle/cms_oracle.c) on the golden fixtures, the fuzz cases and synthetic collections, for several
+window lengths (so window borders fall inside phrases, hard zones and documents).
+The product never runs this host build: it is test infrastructure for "host logic".
+"""
+import ctypes as C
+import glob
+import os
+import subprocess
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import fuzz_cases
+import gen_synth
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+SRC = os.path.join(HERE, "harness", "msf_host.cpp")
+HDR = os.path.join(ROOT, "cms_bwt_b200", "csrc", "ms_fast.cuh")
+WORK = os.path.join(HERE, "_work")
+SO = os.path.join(WORK, "libmsf_host.so")
+
+
+@pytest.fixture(scope="module")
+def harness():
+    os.makedirs(WORK, exist_ok=True)
+    if (not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(SRC), os.path.getmtime(HDR))):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-x", "c++", SRC, "-o", SO])
+    L = C.CDLL(SO)
+    L.msf_host_run.restype = C.c_longlong
+    L.msf_host_run.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
+                               C.c_uint32, C.c_int, C.c_uint32, C.c_uint32] + [C.c_void_p] * 8
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def pick_k(n):
+    k = 1
+    while k < 12 and (1 << (2 * (k + 1))) <= n:
+        k += 1
+    return k
+
+
+def run_case(L, x, text, WL, k=None, skip_min=20, nlanes=7, desc=""):
+    o = O.Oracle(x)
+    sa = o.sa
+    pp = o.plcp_prime.astype(np.int32)
+    N = len(text)
+    k = k or pick_k(len(x))
+    dpos = np.zeros(N, np.uint32); dlen = np.zeros(N, np.uint32)
+    dsm = np.zeros(N, np.uint8); dhd = np.zeros(N, np.uint8)
+    hg = np.zeros(N, np.uint64); hpos = np.zeros(N, np.uint32); hlen = np.zeros(N, np.uint32)
+    hcs = np.zeros(N, np.uint16)
+    xc = np.ascontiguousarray(x); tc = np.ascontiguousarray(text)
+    H = L.msf_host_run(_p(xc), len(xc), _p(sa), _p(pp), _p(tc), N, WL, k, skip_min, nlanes,
+                       _p(dpos), _p(dlen), _p(dsm), _p(dhd), _p(hg), _p(hpos), _p(hlen), _p(hcs))
+    if H == -1:
+        return None
+    assert H >= 0, "pool overflow " + desc
+    opos, olen, osm, ohd = o.ms(text)
+    tag = "%s WL=%d k=%d" % (desc, WL, k)
+    assert np.array_equal(dlen, olen), "MS len " + tag + " first bad %s" % np.flatnonzero(dlen != olen)[:5]
+    assert np.array_equal(dpos, opos), "MS pos " + tag + " first bad %s" % np.flatnonzero(dpos != opos)[:5]
+    assert np.array_equal(dsm, osm), "MS smaller " + tag
+    assert np.array_equal(dhd, ohd), "MS heads " + tag + " first bad %s" % np.flatnonzero(dhd != ohd)[:5]
+    idx = np.flatnonzero(ohd)
+    assert H == len(idx), "head count " + tag
+    assert np.array_equal(hg[:H], idx.astype(np.uint64)), "head positions " + tag
+    assert np.array_equal(hpos[:H], opos[idx]) and np.array_equal(hlen[:H], olen[idx]), "head records " + tag
+    prev = np.where((idx == 0) | (text[np.maximum(idx, 1) - 1] == 2), 2, text[np.maximum(idx, 1) - 1])
+    assert np.array_equal(hcs[:H] & 0xFF, prev.astype(np.uint16)), "head symbols " + tag
+    assert np.array_equal(hcs[:H] >> 8, osm[idx].astype(np.uint16)), "head smaller flags " + tag
+    return H
+
+
+def test_golden_and_fuzz(harness):
+    ran = 0
+    for f in sorted(glob.glob(os.path.join(HERE, "golden", "*.npz"))):
+        z = np.load(f)
+        x = O.augment(O.read_reference(z["ref_file"].tobytes()))
+        text, _ = O.parse_collection(z["coll_file"].tobytes(), int(z["prefix"]))
+        for WL in (64, 100, 4096):
+            if run_case(harness, x, text, WL, desc=os.path.basename(f)) is not None:
+                ran += 1
+    for seed in range(200):
+        c = fuzz_cases.make_case(seed)
+        x = O.augment(O.read_reference(c["ref_file"]))
+        text, _ = O.parse_collection(c["coll_file"])
+        if len(text) == 0:
+            continue
+        if run_case(harness, x, text, [64, 100, 4096][seed % 3], desc=c["desc"]) is not None:
+            ran += 1
+    assert ran >= 20, "too few pure-ACGT cases exercised the fast path (%d)" % ran
+
+
+@pytest.mark.parametrize("WL", [37, 256, 4096])
+def test_synthetic(harness, WL):
+    ref, copies = gen_synth.make_collection(60000, 6, 0.002, 3)
+    x = O.augment(ref)
+    text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    assert run_case(harness, x, text, WL, desc="60k x6") is not None
+    ref, copies = gen_synth.make_collection(20000, 5, 0.01, 5, svs=4)
+    assert run_case(harness, O.augment(ref), O.docs_to_text(copies), WL, desc="20k x5 sv") is not None
+
+
+def test_small_k_and_repeats(harness):
+    rng = np.random.default_rng(2)
+    unit = gen_synth.ACGT[rng.integers(0, 4, 23)]
+    ref = np.concatenate([np.tile(unit, 40), gen_synth.ACGT[rng.integers(0, 4, 500)], np.tile(unit, 25)])
+    docs = [ref[100:1200].copy(), ref[5:900].copy(), np.tile(unit, 60), ref.copy()]
+    docs[1][300] = ord("A") if docs[1][300] != ord("A") else ord("C")
+    x = O.augment(ref)
+    text = O.docs_to_text(docs)
+    for k in (2, 5, 8):
+        for WL in (50, 1000):
+            assert run_case(harness, x, text, WL, k=k, skip_min=2, desc="tandem") is not None
+    # many short documents (separators closer than k + 16)
+    ref, copies = gen_synth.make_collection(3000, 300, 0.003, 9)
+    short = [c[a:a + ln] for c in copies for a, ln in ((5, 11), (40, 30), (100, 3))]
+    assert run_case(harness, O.augment(ref), O.docs_to_text(short), 64, desc="short docs") is not None
