@@ -157,7 +157,8 @@ bool ms_stage_fast(cmsbwt_ctx *c);
 void pack_2bit(cmsbwt_ctx *c, const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps, u64 sepcap,
                unsigned long long *nsep, u32 *flags);
 void sort_stage(cmsbwt_ctx *c);
-void tail_rank(cmsbwt_ctx *c, const u64 *label, u32 *nexth, u32 Tn, u32 *trank);
+void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_bits, u32 *nexth, u32 Tn,
+               u32 *trank);
 bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl);
 void emit_stage(cmsbwt_ctx *c, int mode);
 

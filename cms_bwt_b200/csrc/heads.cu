@@ -45,7 +45,8 @@ __global__ void k_tail_first(const u32 *tflag, const u32 *tail_incl, u64 H, u32 
 // label + next pointer of every tail
 __global__ void k_tail_label(const u64 *g, const u32 *pos, const u32 *len, const u16 *cs,
                              const u32 *tail_incl, const u32 *sent_excl, const u32 *tail_first,
-                             const u32 *isa, u64 H, u32 Tn, u64 *label, u32 *next, u32 *tid) {
+                             const u32 *isa, u64 H, u32 Tn, int qb, u64 *label, u32 *next, u32 *tid,
+                             u32 *key32) {
   u32 t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= Tn) return;
   u32 f = tail_first[t];
@@ -60,14 +61,23 @@ __global__ void k_tail_label(const u64 *g, const u32 *pos, const u32 *len, const
   }
   u32 j = (u32)lo;
   tid[t] = t;
+  // key32 = ISA rank, then qb bits of the cls order (weakly order preserving; tailrank.cu)
+  const u32 Q = 1u << qb, half = Q >> 1;
   if (len[j] == 0) {                   // the suffix at g_end is a document terminator
-    label[t] = (u64)sent_excl[j];
+    u32 d = sent_excl[j];
+    label[t] = (u64)d;
     next[t] = t;
+    key32[t] = d < Q - 1 ? d : Q - 1;
   } else {
     u32 pe = pos[j] + (u32)(e - g[j]);
-    u32 c = cls_of(pos[j], len[j], cs[j] >> 8);
-    label[t] = ((u64)isa[pe] << 32) | c;
+    u32 sm = cs[j] >> 8;
+    u32 c = cls_of(pos[j], len[j], sm);
+    u32 r = isa[pe];
+    label[t] = ((u64)r << 32) | c;
     next[t] = tail_incl[j] - 1;
+    u32 rest = (pos[j] + len[j] - pe) >> 5;            // bases left in the phrase, in bins of 32
+    u32 f = half ? (rest < half - 1 ? rest : half - 1) : 0;
+    key32[t] = (r << qb) | (sm ? f : Q - 1 - f);
   }
 }
 // dense ranks from sorted keys
@@ -228,11 +238,16 @@ void sort_stage(cmsbwt_ctx *c) {
   next.alloc((size_t)Tn * 4, st); tid.alloc((size_t)Tn * 4, st);
   trank.alloc((size_t)Tn * 4, st);
   k_tail_first<<<gH, B, 0, st>>>(tflag.as<u32>(), tincl.as<u32>(), H, tfirst.as<u32>());
+  int isa_bits = 1;
+  while (isa_bits < 32 && (1ull << isa_bits) < (u64)n) isa_bits++;
+  const int qb = 32 - isa_bits < 6 ? 32 - isa_bits : 6;
+  DBuf key32;
+  key32.alloc((size_t)Tn * 4, st);
   k_tail_label<<<gT, B, 0, st>>>(g, pos, len, cs, tincl.as<u32>(), sexcl.as<u32>(), tfirst.as<u32>(),
-                                 c->ix.isa, H, Tn, label.as<u64>(), next.as<u32>(), tid.as<u32>());
+                                 c->ix.isa, H, Tn, qb, label.as<u64>(), next.as<u32>(), tid.as<u32>(),
+                                 key32.as<u32>());
   c->launches += 2;
-  label2.release(); tid2.release(); next2.release(); fl.release(); dense.release(); tid.release();
-  tail_rank(c, label.as<u64>(), next.as<u32>(), Tn, trank.as<u32>());
+  tail_rank(c, label.as<u64>(), key32, tid, isa_bits + qb, next.as<u32>(), Tn, trank.as<u32>());
   // ---- kappa + items ----
   DBuf kappa, nitems, ioff;
   kappa.alloc(H * 8, st); nitems.alloc((H + 1) * 4, st); ioff.alloc((H + 1) * 8, st);

@@ -81,15 +81,14 @@ __global__ void k_wsep(const u64 *seps, u64 nseps, u32 WL, u64 nwin, u32 *wsep) 
 // ---- the kernel ---------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_ms_fast(MsfParams P) {
   MsfLane L;
-  L.i = L.w0 = L.w1 = L.sepnext = 0;
+  L.i = L.w1 = L.sepnext = 0;
   L.sepidx = L.w = 0;
   L.prevpos = MSF_INVALID; L.prevterm = 0; L.first = 0;
   L.curb = MSF_NOB; L.fill = 0; L.cnt = 0; L.limit = 0;
   L.tkey = L.lo = L.hi = L.rb = L.prevkey = L.prevsa = L.haveprev = 0;
-  L.pos = L.len = L.sm = L.maxl = 0;
-  L.glo = L.ghi = L.E = L.gsteps = 0;
+  L.pos = L.len = L.sm = 0;
   L.state = MSF_S_FETCH;
-  while (L.state != MSF_S_DONE) msf_step(P, L);
+  while (!__all_sync(0xffffffffu, L.state == MSF_S_DONE)) msf_warp_iter(P, L);
 }
 
 // ---- compaction -------------------------------------------------------------------------------

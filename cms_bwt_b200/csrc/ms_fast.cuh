@@ -3,24 +3,25 @@
 // Replaces the reference's per-document MS driver (CMS-BWT-functions.cpp:1138-1213; small path
 // :344-419) with computeMSFactorAt :45-88, binarySearchLB/RB :94-149 and the PLCP' skip loop
 // :1176-1185.  MS is a pure function of the suffix, so every window of the
-// text is walked independently by one lane running a flat state machine (one memory round trip
-// per step, so 32 lanes of a warp stay busy even though they are in different phases):
+// text is walked independently by one lane.  A warp iteration has four phases:
 //
-//   S_POS    read 32 packed bases at i, look the k-mer up in ktab            -> bucket [L,R)
-//   S_BIN    (large buckets only) bisect the bucket on the 16-base keys
-//   S_SCAN   scan the bucket: entries are {key = the 16 bases after the k-mer, sa}; predecessor and
-//            successor and their LCE (< k+16) come from the keys alone
-//   S_EQ     a key equals the text's: make sure it is the only one
-//   S_EXT    extend the single candidate 128 bases per step on the packed streams
-//   S_GSCAN  after a long match: first q in (pos, E) with G[q] >= E (:1176-1185 as a search)
-//   S_GBIN   same, by bisection when the hard zone is long
-//   generic_search()  exact binary search on packed data for everything rare (separator within
-//            k+16 bases, empty bucket, repeated key, suffixes that touch the augmentation)
+//   A  search (lane-local):  S_POS reads 32 packed bases at i, looks the k-mer up in ktab and scans
+//      the bucket [L,R) of {key = the 16 bases after the k-mer, sa} entries (S_SCAN; S_BIN first
+//      when the bucket is large, S_EQ when an equal key sits at the edge of the scanned group).
+//      Predecessor, successor and their LCE (< k+16) come from the keys alone.
+//   B  extension (warp-cooperative): a lane whose key matched hands its single candidate to the
+//      warp, which compares 1024 packed bases per round (32 lanes x 32 bases, coalesced).
+//   C  head test + record (lane-local, one copy of the code); msf_generic_search(), an exact
+//      binary search on the packed data, serves everything rare (separator within k+16 bases,
+//      empty bucket, repeated key, suffixes that touch the augmentation).
+//   D  skip (warp-cooperative): after a long match, the first q in (pos, E) with G[q] >= E
+//      (:1176-1185 as a search) from one coalesced read of the 32 entries below E.
 //
 // The neighbour rule is the one of :53-76 as restated in ms.cu: the successor wins ties
-// (smaller = 1).  This header is plain C++ when compiled without nvcc so that the same code is
-// run lane by lane on the CPU by tests/harness (test infrastructure; the product only ever runs
-// it inside k_ms_fast).
+// (smaller = 1).  This header is plain C++ when compiled without nvcc so that the same lane code
+// is run on the CPU by tests/harness (test infrastructure; the product only ever runs it inside
+// k_ms_fast); the cooperative phases have a device form (shuffles) and a host form (loops over
+// the lanes of an emulated warp) built from the same per-lane probes.
 #pragma once
 #include <stdint.h>
 
@@ -70,8 +71,7 @@ static inline msf_u64 msf_brev64_host(msf_u64 v) {
 #define MSF_INVALID 0xFFFFFFFFu
 #define MSF_PAD_WORDS 4             // zero words readable past the last packed word
 
-enum { MSF_S_FETCH = 0, MSF_S_POS, MSF_S_BIN, MSF_S_SCAN, MSF_S_EQ, MSF_S_EXT, MSF_S_GSCAN,
-       MSF_S_GBIN, MSF_S_DONE };
+enum { MSF_S_FETCH = 0, MSF_S_POS, MSF_S_BIN, MSF_S_SCAN, MSF_S_EQ, MSF_S_DONE };
 
 // ---- 2-bit helpers -----------------------------------------------------------------------------
 // Packed layout: base j lives in word j >> 5, bits [2 (j & 31), 2 (j & 31) + 2); A,C,G,T = 0,1,2,3.
@@ -152,14 +152,13 @@ struct MsfParams {
 };
 
 struct MsfLane {
-  msf_u64 i, w0, w1, sepnext;
+  msf_u64 i, w1, sepnext;
   msf_u32 sepidx, w;
   msf_u32 state, prevpos, prevterm, first;
   msf_u32 curb, fill, cnt;
   msf_u32 limit;
   msf_u32 tkey, lo, hi, rb, prevkey, prevsa, haveprev;
-  msf_u32 pos, len, sm, maxl;
-  msf_u32 glo, ghi, E, gsteps;
+  msf_u32 pos, len, sm;
 };
 
 MSF_HD void msf_store_rec(const MsfParams &P, msf_u64 slot, msf_u32 a, msf_u32 b, msf_u32 c, msf_u32 d) {
@@ -243,41 +242,38 @@ MSF_HD void msf_dump(const MsfParams &P, msf_u64 p, msf_u32 pos, msf_u32 len, ms
   }
 }
 
-// what the common tail of a step has to do
+// what the later phases of an iteration have to do for this lane
 #define MSF_ACT_NONE 0u
 #define MSF_ACT_FIN 1u        // (L.pos, L.len, L.sm) is the MS of position L.i
 #define MSF_ACT_GENERIC 2u    // run the exact search first, then FIN
 #define MSF_ACT_TERM 4u       // position L.i is a document terminator
+#define MSF_ACT_EXT 8u        // extend the candidate L.pos from L.len matched bases (phase B)
+#define MSF_ACT_SKIP 16u      // long match recorded: find the end of its non-head run (phase D)
 
-// MS of position L.i is (L.pos, L.len, L.sm): head test (:1154), record, then skip or step.
-// term: L.i holds a separator -> sentinel head (:1198-1212).
-MSF_HD void msf_fin(const MsfParams &P, MsfLane &L, bool term) {
+// phase C: head test (:1154), record, step.  term: L.i holds a separator (:1198-1212).
+// Returns MSF_ACT_SKIP when the non-head run after this head has to be looked up.
+MSF_HD msf_u32 msf_fin(const MsfParams &P, MsfLane &L, bool term) {
   const bool tent = !term && L.first && !L.prevterm;   // window starts inside a document
   const bool head = term || L.prevterm || L.pos != L.prevpos + 1;
   if (L.first) P.wfirstpos[L.w] = (term || L.prevterm) ? MSF_INVALID : L.pos;
   if (head || tent) {
     msf_u32 ch = L.prevterm ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i - 1));
-    msf_emit(P, L, (msf_u32)(L.i - L.w0), L.pos, L.len, ch | (L.sm << 8) | (tent ? 1u << 9 : 0u));
+    msf_emit(P, L, (msf_u32)(L.i - (msf_u64)L.w * P.WL), L.pos, L.len, ch | (L.sm << 8) | (tent ? 1u << 9 : 0u));
   }
   msf_dump(P, L.i, L.pos, L.len, L.sm, head || tent);
   L.first = 0;
   L.prevterm = term ? 1u : 0u;
+  L.state = MSF_S_POS;
   if (term) {
     L.sepidx++;
     L.sepnext = MSF_LD64(P.seps + L.sepidx);
     L.i++;
-    L.state = MSF_S_POS;
-  } else if (L.len >= P.skip_min && L.len > 1) {
-    L.E = L.pos + L.len;
-    L.glo = L.pos + 1;
-    L.ghi = L.E;
-    L.gsteps = 0;
-    L.state = MSF_S_GSCAN;
-  } else {
-    L.prevpos = L.pos;
-    L.i++;
-    L.state = MSF_S_POS;
+    return MSF_ACT_NONE;
   }
+  if (L.len >= P.skip_min && L.len > 1) return MSF_ACT_SKIP;
+  L.prevpos = L.pos;
+  L.i++;
+  return MSF_ACT_NONE;
 }
 
 // the non-head run after a head ends at q = first position in (pos, E) with G[q] >= E (or E)
@@ -287,19 +283,31 @@ MSF_HD void msf_skip_to(const MsfParams &P, MsfLane &L, msf_u32 q) {
     for (msf_u32 k2 = 1; k2 <= skip; k2++) msf_dump(P, L.i + k2, L.pos + k2, L.len - k2, L.sm, 0);
   L.i += 1 + (msf_u64)skip;
   L.prevpos = L.pos + skip;
-  L.state = MSF_S_POS;
 }
 
-// single candidate s whose key equals the text's: extend it (or leave it to the exact search)
+// single candidate s whose key equals the text's: hand it to the warp (or to the exact search)
 MSF_HD msf_u32 msf_start_ext(const MsfParams &P, MsfLane &L, msf_u32 s) {
   const msf_u32 KL = (msf_u32)P.k + 16;
   if ((msf_u64)s + KL > P.n_acgt) return MSF_ACT_GENERIC;
   L.pos = s;
   L.len = KL;
-  msf_u32 room = P.n_acgt - s;
-  L.maxl = L.limit < room ? L.limit : room;
-  L.state = MSF_S_EXT;
-  return MSF_ACT_NONE;
+  return MSF_ACT_EXT;
+}
+MSF_HD msf_u32 msf_ext_max(const MsfParams &P, msf_u32 limit, msf_u32 pos) {
+  msf_u32 room = P.n_acgt - pos;
+  return limit < room ? limit : room;
+}
+// phase B probe: first mismatch among the 32 bases at offset off of the two streams (32 = none)
+MSF_HD msf_u32 msf_ext_probe(const MsfParams &P, msf_u64 i, msf_u32 pos, msf_u32 off) {
+  msf_u64 d = msf_get64(P.tp, i + off) ^ msf_get64(P.xp, (msf_u64)pos + off);
+  return d ? (MSF_CTZ64(d) >> 1) : 32u;
+}
+// phase B result for the owner lane: the match is `len` long; smaller = x[pos+len] > next text symbol
+MSF_HD void msf_ext_done(const MsfParams &P, MsfLane &L, msf_u32 len) {
+  L.len = len;
+  msf_u32 xb = MSF_LD8(P.x8 + L.pos + len);
+  msf_u32 tb = len == L.limit ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i + len));
+  L.sm = xb > tb ? 1u : 0u;
 }
 
 // predecessor (prevkey/prevsa, if any) and successor (skey/ssa, if found) are known by key only
@@ -315,27 +323,27 @@ MSF_HD msf_u32 msf_decide(const MsfParams &P, MsfLane &L, bool found, msf_u32 sk
   return MSF_ACT_FIN;
 }
 
-MSF_HD void msf_step(const MsfParams &P, MsfLane &L) {
+// phase A: one search step of this lane
+MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
   msf_u32 act = MSF_ACT_NONE;
   switch (L.state) {
     case MSF_S_FETCH: {
       msf_u64 w = MSF_ATOMIC_INC64(P.win_counter);
       if (w >= P.nwin) { L.state = MSF_S_DONE; break; }
       L.w = (msf_u32)w;
-      L.w0 = w * P.WL;
-      L.w1 = L.w0 + P.WL < P.N ? L.w0 + P.WL : P.N;
-      L.i = L.w0;
+      L.i = w * P.WL;
+      L.w1 = L.i + P.WL < P.N ? L.i + P.WL : P.N;
       L.sepidx = MSF_LD32(P.wsep + w);
       L.sepnext = MSF_LD64(P.seps + L.sepidx);
-      L.prevterm = (L.w0 == 0) || (L.sepidx > 0 && MSF_LD64(P.seps + L.sepidx - 1) == L.w0 - 1);
+      L.prevterm = (L.i == 0) || (L.sepidx > 0 && MSF_LD64(P.seps + L.sepidx - 1) == L.i - 1);
       L.prevpos = MSF_INVALID;
       L.first = 1;
       L.curb = MSF_NOB;
       L.fill = 0;
       L.cnt = 0;
       L.state = MSF_S_POS;
-      break;
     }
+    // fall through
     case MSF_S_POS: {
       if (L.i >= L.w1) {                                  // close the window
         P.wcnt[L.w] = L.cnt;
@@ -404,69 +412,143 @@ MSF_HD void msf_step(const MsfParams &P, MsfLane &L) {
       }
       break;
     }
-    case MSF_S_EXT: {
-      bool fin = false;
-#pragma unroll
-      for (int r = 0; r < 4; r++) {
-        msf_u32 rem = L.maxl - L.len;
-        if (fin || rem == 0) { fin = true; continue; }
-        msf_u64 d = msf_get64(P.tp, L.i + L.len) ^ msf_get64(P.xp, (msf_u64)L.pos + L.len);
-        msf_u32 take = rem < 32 ? rem : 32;
-        msf_u32 m = d ? (MSF_CTZ64(d) >> 1) : 32;
-        if (m >= take) { L.len += take; if (take == rem) fin = true; }
-        else { L.len += m; fin = true; }
-      }
-      if (fin) {
-        msf_u32 xb = MSF_LD8(P.x8 + L.pos + L.len);
-        msf_u32 tb = L.len == L.limit ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i + L.len));
-        L.sm = xb > tb ? 1u : 0u;
-        act = MSF_ACT_FIN;
-      }
-      break;
-    }
-    case MSF_S_GSCAN: {                                   // G[q] >= E for all q in [ghi, E)
-      if (L.ghi <= L.glo) { msf_skip_to(P, L, L.glo < L.E ? L.glo : L.E); break; }
-      // 16 entries below ghi, in aligned groups of four
-      msf_u32 top = L.ghi - 1;
-      msf_u32 blk = top >> 2;
-      msf_u32 q = L.ghi;                                  // smallest index known to satisfy
-      bool stop = false;
-#pragma unroll
-      for (int b = 0; b < 4; b++) {
-        if (stop || blk < (msf_u32)b) continue;
-        msf_u32 base = (blk - b) << 2;
-        if (base + 3 < L.glo) { stop = true; continue; }
-        msf_u32 g[4];
-#if defined(__CUDA_ARCH__)
-        uint4 v = __ldg((const uint4 *)(P.G + base));
-        g[0] = v.x; g[1] = v.y; g[2] = v.z; g[3] = v.w;
-#else
-        for (int t = 0; t < 4; t++) g[t] = base + t < P.n ? P.G[base + t] : 0xFFFFFFFFu;
-#endif
-#pragma unroll
-        for (int t = 3; t >= 0; t--) {
-          msf_u32 idx = base + t;
-          if (stop || idx >= q || idx < L.glo) continue;
-          if (g[t] >= L.E) q = idx; else stop = true;
-        }
-      }
-      if (stop || q <= L.glo) { msf_skip_to(P, L, q); break; }
-      L.ghi = q;
-      if (++L.gsteps >= 2) L.state = MSF_S_GBIN;
-      break;
-    }
-    case MSF_S_GBIN: {                                    // bisection on [glo, ghi)
-      if (L.glo >= L.ghi) { msf_skip_to(P, L, L.glo); break; }
-      msf_u32 mid = L.glo + ((L.ghi - L.glo) >> 1);
-      if (MSF_LD32(P.G + mid) >= L.E) L.ghi = mid; else L.glo = mid + 1;
-      break;
-    }
     default: break;
   }
-  // ---- common tail: one copy of the exact search and of the head test / record ----
-  if (act & MSF_ACT_GENERIC) msf_generic_search(P, L.i, L.limit, L.pos, L.len, L.sm);
-  if (act) msf_fin(P, L, (act & MSF_ACT_TERM) != 0);
+  return act;
 }
+
+// phase D probe for one lane of the group looking at the 32 entries [E - 32 (w + 1), E - 32 w):
+// returns 1 when entry idx is inside (pos, E) and fails G[idx] >= E, 2 when inside and it holds
+MSF_HD msf_u32 msf_skip_probe(const MsfParams &P, msf_u32 pos, msf_u32 E, msf_u32 idx) {
+  if (idx <= pos || idx >= E) return 0;
+  return MSF_LD32(P.G + idx) >= E ? 2u : 1u;
+}
+// after MSF_SKIP_ROUNDS windows of 32 without a failing entry: bisection on (pos, hi)
+#define MSF_SKIP_ROUNDS 4
+MSF_HD msf_u32 msf_skip_bisect(const MsfParams &P, msf_u32 pos, msf_u32 E, msf_u32 hi) {
+  msf_u32 lo = pos + 1;                                   // G[q] >= E for all q in [hi, E)
+  while (lo < hi) {
+    msf_u32 mid = lo + ((hi - lo) >> 1);
+    if (MSF_LD32(P.G + mid) >= E) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+
+#if defined(__CUDACC__)
+// ---- one warp iteration (device) ----------------------------------------------------------------
+__device__ __forceinline__ void msf_warp_iter(const MsfParams &P, MsfLane &L) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  msf_u32 act = msf_search_step(P, L);
+  // phase B: cooperative extension, one candidate at a time
+  unsigned em = __ballot_sync(FULL, act == MSF_ACT_EXT);
+  while (em) {
+    const int src = __ffs(em) - 1;
+    em &= em - 1;
+    const msf_u64 bi = __shfl_sync(FULL, L.i, src);
+    const msf_u32 bpos = __shfl_sync(FULL, L.pos, src);
+    msf_u32 blen = __shfl_sync(FULL, L.len, src);
+    const msf_u32 bmax = __shfl_sync(FULL, msf_ext_max(P, L.limit, L.pos), src);
+    msf_u32 res;
+    while (true) {
+      const msf_u32 off = blen + 32u * lane;
+      msf_u32 cand = 0xFFFFFFFFu;
+      if (off < bmax) {
+        msf_u32 m = msf_ext_probe(P, bi, bpos, off);
+        if (m < 32) cand = off + m;
+      }
+      res = __reduce_min_sync(FULL, cand);
+      if (res != 0xFFFFFFFFu || blen + 1024u >= bmax) break;
+      blen += 1024u;
+    }
+    if (lane == src) { msf_ext_done(P, L, res < bmax ? res : bmax); act = MSF_ACT_FIN; }
+  }
+  // phase C
+  if (act & MSF_ACT_GENERIC) msf_generic_search(P, L.i, L.limit, L.pos, L.len, L.sm);
+  if (act) act = msf_fin(P, L, (act & MSF_ACT_TERM) != 0);
+  // phase D: cooperative skip
+  unsigned sk = __ballot_sync(FULL, act == MSF_ACT_SKIP);
+  while (sk) {
+    const int src = __ffs(sk) - 1;
+    sk &= sk - 1;
+    const msf_u32 bpos = __shfl_sync(FULL, L.pos, src);
+    const msf_u32 E = bpos + __shfl_sync(FULL, L.len, src);
+    msf_u32 q = E, round = 0;
+    bool found = false;
+    while (true) {
+      const msf_u32 top = E - 32u * round;                // entries [top - 32, top); top > pos + 1
+      const msf_u32 idx = top - 32u + lane;               // wraps below zero when top < 32: probe rejects it
+      const msf_u32 r = msf_skip_probe(P, bpos, E, idx);
+      const unsigned fail = __ballot_sync(FULL, r == 1u), hold = __ballot_sync(FULL, r == 2u);
+      if (fail) {                                         // q = just above the highest failing entry
+        q = top - 32u + (31 - __clz((int)fail)) + 1;
+        found = true;
+        break;
+      }
+      if (hold) q = top - 32u + (__ffs(hold) - 1);
+      if (top <= bpos + 33u) { found = true; break; }     // the window reached pos + 1
+      if (++round >= MSF_SKIP_ROUNDS) break;
+    }
+    if (lane == src) {
+      if (!found) q = msf_skip_bisect(P, bpos, E, q);
+      msf_skip_to(P, L, q);
+    }
+  }
+}
+#else
+// ---- one warp iteration (host emulation for tests/harness: same phases, loops instead of shuffles)
+inline void msf_warp_iter_host(const MsfParams &P, MsfLane *W, int nl) {
+  msf_u32 act[32];
+  for (int l = 0; l < nl; l++) act[l] = msf_search_step(P, W[l]);
+  for (int l = 0; l < nl; l++) {                          // phase B
+    if (act[l] != MSF_ACT_EXT) continue;
+    MsfLane &L = W[l];
+    msf_u32 blen = L.len, res;
+    const msf_u32 bmax = msf_ext_max(P, L.limit, L.pos);
+    while (true) {
+      res = 0xFFFFFFFFu;
+      for (msf_u32 lane = 0; lane < 32; lane++) {
+        const msf_u32 off = blen + 32u * lane;
+        if (off < bmax) {
+          msf_u32 m = msf_ext_probe(P, L.i, L.pos, off);
+          if (m < 32 && off + m < res) res = off + m;
+        }
+      }
+      if (res != 0xFFFFFFFFu || blen + 1024u >= bmax) break;
+      blen += 1024u;
+    }
+    msf_ext_done(P, L, res < bmax ? res : bmax);
+    act[l] = MSF_ACT_FIN;
+  }
+  for (int l = 0; l < nl; l++) {                          // phase C
+    MsfLane &L = W[l];
+    if (act[l] & MSF_ACT_GENERIC) msf_generic_search(P, L.i, L.limit, L.pos, L.len, L.sm);
+    if (act[l]) act[l] = msf_fin(P, L, (act[l] & MSF_ACT_TERM) != 0);
+  }
+  for (int l = 0; l < nl; l++) {                          // phase D
+    if (act[l] != MSF_ACT_SKIP) continue;
+    MsfLane &L = W[l];
+    const msf_u32 bpos = L.pos, E = L.pos + L.len;
+    msf_u32 q = E, round = 0;
+    bool found = false;
+    while (true) {
+      const msf_u32 top = E - 32u * round;
+      msf_u32 fail = 0, hold = 0;
+      for (msf_u32 lane = 0; lane < 32; lane++) {
+        msf_u32 r = msf_skip_probe(P, bpos, E, top - 32u + lane);
+        if (r == 1u) fail |= 1u << lane;
+        if (r == 2u) hold |= 1u << lane;
+      }
+      if (fail) { q = top - 32u + (31 - (msf_u32)__builtin_clz(fail)) + 1; found = true; break; }
+      if (hold) q = top - 32u + (msf_u32)__builtin_ctz(hold);
+      if (top <= bpos + 33u) { found = true; break; }
+      if (++round >= MSF_SKIP_ROUNDS) break;
+    }
+    if (!found) q = msf_skip_bisect(P, bpos, E, q);
+    msf_skip_to(P, L, q);
+  }
+}
+#endif
 
 // ---- window fix-up (head test across window borders) ------------------------------------------
 // The first position of a window that starts inside a document is recorded tentatively; it is a

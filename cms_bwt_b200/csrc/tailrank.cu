@@ -6,9 +6,11 @@
 // next(t) = the tail of that phrase; tails compare as the sequences label(t), label(next t), ...
 // (heads.cu).  Segmented LSD radix sort keyed on the reference ISA rank, then refinement of the
 // tied groups only (Larsson-Sadakane style prefix doubling on the subset):
-//   1. one radix sort of all tails on the ISA rank alone (32-bit keys);  rank = first sorted
-//      index of the tail's group, so ranks of already-unique tails never change again;
-//   2. the tails whose ISA rank is shared are sorted by (rank, cls);
+//   1. one radix sort of all tails on a 32-bit key = ISA rank, then as many bits of the cls order
+//      as fit (a weakly order-preserving quantisation of the phrase's remaining length; it
+//      separates most tails that merely land on the same reference position);  rank = first
+//      sorted index of the tail's group, so ranks of already-unique tails never change again;
+//   2. the tails whose key is shared are sorted by (rank, cls);
 //   3. the tails still tied are sorted by (rank, rank[next^(2^h) t]) for h = 0, 1, ... until no
 //      group of two is left -- only they are touched, so a collection with a handful of shared
 //      variants costs a handful of small sorts instead of log(chain) full ones.
@@ -96,18 +98,18 @@ static u32 select_tied(Scratch &tmp, const u32 *ids, const u8 *tie, u32 n, u32 *
   return m;
 }
 
-// label[Tn], nexth[Tn] (overwritten) -> trank[Tn]: distinct, order-preserving ranks
-void tail_rank(cmsbwt_ctx *c, const u64 *label, u32 *nexth, u32 Tn, u32 *trank) {
+// label[Tn], key32[Tn] (ISA rank + quantised cls order, consumed), id[Tn] = iota (consumed),
+// nexth[Tn] (overwritten) -> trank[Tn]: distinct, order-preserving ranks
+void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_bits, u32 *nexth, u32 Tn,
+               u32 *trank) {
   cudaStream_t st = c->st;
   const int B = 256;
   const u32 gT = (Tn + B - 1) / B;
   Scratch tmp;
-  DBuf key32, key32s, id, ids, gs, tie, cnt;
-  key32.alloc((size_t)Tn * 4, st); key32s.alloc((size_t)Tn * 4, st); id.alloc((size_t)Tn * 4, st);
+  DBuf key32s, ids, gs, tie, cnt;
+  key32s.alloc((size_t)Tn * 4, st);
   ids.alloc((size_t)Tn * 4, st); gs.alloc((size_t)Tn * 4, st); tie.alloc((size_t)Tn, st); cnt.alloc(4, st);
-  int bits = 1;
-  while (bits < 32 && (1ull << bits) < (u64)c->ix.n) bits++;
-  k_tr_split<<<gT, B, 0, st>>>(label, Tn, key32.as<u32>(), id.as<u32>());
+  const int bits = key_bits > 32 ? 32 : key_bits;
   size_t tb = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, tb, key32.as<u32>(), key32s.as<u32>(), id.as<u32>(), ids.as<u32>(),
                                   (int)Tn, 0, bits, st);

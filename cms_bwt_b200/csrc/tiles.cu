@@ -113,39 +113,71 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, cons
   unsigned long long tot = BR(tr).Sum(w);
   if (tid == 0) {
     if (tot) atomicAdd(work, tot);
-    atomicMax(maxent, (h1 - h0) + (r1 - r0));
+    u32 rcp = 1;
+    while (rcp < r1 - r0) rcp <<= 1;                    // pass B pads the ranges to a power of two
+    atomicMax(maxent, (h1 - h0) + rcp);
   }
 }
 
 // ---- pass B: within + head symbols --------------------------------------------------------------
+// The tile's ranges are sorted by kappa in shared memory (bitonic); a head then bisects for the
+// number of ranges with a smaller kappa and only tests the shorter side for coverage (the other
+// side follows from the per-position range coverage), so a short head costs ~a dozen tests.
 __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, const TileEnt *re, const u32 *hoff,
                                                            const u32 *roff, const u32 *isa, const u64 *base,
                                                            u32 n, u8 *out, u32 *within_out, u64 *off_out) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W];
+  __shared__ int s_d[LT_W + 1];
+  __shared__ u32 s_rcov[LT_W];
   __shared__ u64 s_base[LT_W];
   typedef cub::BlockScan<u32, LT_THREADS> BS;
-  __shared__ typename BS::TempStorage ts;
+  typedef cub::BlockScan<int, LT_THREADS> BSI;
+  __shared__ union { typename BS::TempStorage a; typename BSI::TempStorage b; } ts;
   const u32 t = blockIdx.x, tid = threadIdx.x;
   const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
   const u32 hc = h1 - h0, rc = r1 - r0;
   if (hc == 0) return;
-  TileEnt *s_he = (TileEnt *)smem;
-  TileEnt *s_re = s_he + hc;
-  s_cnt[tid] = 0; s_cur[tid] = 0;
+  u32 rcp = 1;
+  while (rcp < rc) rcp <<= 1;
+  TileEnt *s_re = (TileEnt *)smem;              // rcp entries, sorted by kappa
+  TileEnt *s_he = s_re + rcp;                   // hc entries, grouped by position
+  s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0;
+  if (tid == 0) s_d[LT_W] = 0;
   {
     u32 p = (t << LT_SHIFT) + tid;
     s_base[tid] = p < n ? base[isa[p]] : 0;
   }
   __syncthreads();
-  for (u32 j = tid; j < rc; j += LT_THREADS) s_re[j] = re[r0 + j];
+  for (u32 j = tid; j < rcp; j += LT_THREADS) {
+    TileEnt e;
+    if (j < rc) {
+      e = re[r0 + j];
+      atomicAdd(&s_d[e.a & 0xFFFF], 1);
+      atomicAdd(&s_d[(e.a >> 16) + 1], -1);
+    } else { e.a = 1; e.b = 0; e.kappa = ~0ull; }        // padding: covers nothing, sorts last
+    s_re[j] = e;
+  }
   for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[he[h0 + j].b & (LT_W - 1)], 1u);
   __syncthreads();
+  for (u32 k = 2; k <= rcp; k <<= 1)                     // bitonic sort of the ranges by kappa
+    for (u32 j = k >> 1; j > 0; j >>= 1) {
+      for (u32 x = tid; x < (rcp >> 1); x += LT_THREADS) {
+        const u32 i = ((x & ~(j - 1)) << 1) | (x & (j - 1));
+        const bool up = (i & k) == 0;
+        TileEnt a = s_re[i], b = s_re[i + j];
+        if ((a.kappa > b.kappa) == up) { s_re[i] = b; s_re[i + j] = a; }
+      }
+      __syncthreads();
+    }
   u32 ex;
-  BS(ts).ExclusiveSum(s_cnt[tid], ex);
+  BS(ts.a).ExclusiveSum(s_cnt[tid], ex);
   s_off[tid] = ex;
   if (tid == LT_THREADS - 1) s_off[LT_W] = ex + s_cnt[tid];
   __syncthreads();
+  int incl;
+  BSI(ts.b).InclusiveSum(s_d[tid], incl);
+  s_rcov[tid] = (u32)incl;
   for (u32 j = tid; j < hc; j += LT_THREADS) {          // heads grouped by position
     TileEnt e = he[h0 + j];
     u32 q = e.b & (LT_W - 1);
@@ -158,9 +190,23 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
     const u64 kap = e.kappa;
     u32 w = 0;
     for (u32 jj = s_off[q]; jj < s_off[q + 1]; jj++) w += s_he[jj].kappa < kap;
-    for (u32 r = 0; r < rc; r++) {
-      const TileEnt g = s_re[r];
-      w += ((g.a & 0xFFFF) <= q) & (q <= (g.a >> 16)) & (g.kappa < kap);
+    u32 lo = 0, hi = rc;                                 // ranges [0, lo) have a smaller kappa
+    while (lo < hi) {
+      u32 mid = (lo + hi) >> 1;
+      if (s_re[mid].kappa < kap) lo = mid + 1; else hi = mid;
+    }
+    if (lo <= rc - lo) {
+      for (u32 r = 0; r < lo; r++) {
+        const u32 lh = s_re[r].a;
+        w += ((lh & 0xFFFF) <= q) & (q <= (lh >> 16));
+      }
+    } else {
+      u32 above = 0;
+      for (u32 r = lo; r < rc; r++) {
+        const u32 lh = s_re[r].a;
+        above += ((lh & 0xFFFF) <= q) & (q <= (lh >> 16));
+      }
+      w += s_rcov[q] - above;
     }
     const u64 off = s_base[q] + w;
     out[off] = (u8)(e.b >> 8);

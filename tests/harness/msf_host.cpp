@@ -88,13 +88,16 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   P.wfirst = wfirst.data(); P.wcnt = wcnt.data(); P.wfirstpos = wfp.data(); P.wlastpos = wlp.data();
   P.flags = flags; P.win_counter = &counter;
   P.dpos = dpos; P.dlen = dlen; P.dsm = dsm; P.dhead = dhead;
+  if (nlanes < 1) nlanes = 1;
+  if (nlanes > 32) nlanes = 32;
   std::vector<MsfLane> lanes(nlanes);
   for (auto &L : lanes) { memset(&L, 0, sizeof L); L.state = MSF_S_FETCH; }
   bool any = true;
-  while (any) {                       // round-robin: lanes interleave like threads of a warp
+  while (any) {                       // one emulated warp of nlanes lanes
     any = false;
     for (auto &L : lanes)
-      if (L.state != MSF_S_DONE) { g_steps[L.state]++; msf_step(P, L); any = true; }
+      if (L.state != MSF_S_DONE) { g_steps[L.state]++; any = true; }
+    if (any) { g_steps[15]++; msf_warp_iter_host(P, lanes.data(), (int)nlanes); }
   }
   if (flags[0]) return -2;
   // ---- compaction (ms_fast.cu: k_msf_fix + scan + k_msf_gather) ----
