@@ -205,7 +205,7 @@ def main():
     sampler.start()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stage = {"ms_ms": 0.0, "sort_ms": 0.0, "emit_ms": 0.0, "ms_kernel_ms": 0.0}
+    stage = {"ms_ms": 0.0, "sort_ms": 0.0, "emit_ms": 0.0, "ms_kernel_ms": 0.0, "pack_ms": 0.0}
     launches = 0
     t0 = time.time()
     e0.record()
@@ -228,14 +228,23 @@ def main():
     H = s["n_heads"]
     n = len(x)
 
-    # ---- roofline of the dominant kernel (k_ms): algorithmic bytes = text read once + head
-    # records written once (18 B each), DESIGN.md section 5.
+    # ---- roofline of the dominant kernel (the matching-statistics kernel): algorithmic bytes =
+    # every collection symbol read once (1 B as parsed) + one 16-byte head record
+    # written per head, DESIGN.md section 6.  `traffic` is the DRAM read+write of one launch from
+    # the committed ncu --set full capture (profiles/), same workload.
     peak, peak_kind = measured_peak()
     kms = stage["ms_kernel_ms"] / args.steps
-    alg_bytes = N + 18 * H
+    alg_bytes = N + 16 * H
     achieved = alg_bytes / 1e9 / (kms / 1e3)
-    roofline = {"bound": "hbm", "kernel": "k_ms", "achieved": achieved, "peak": peak,
-                "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    kname = "k_ms_fast" if s.get("fast_path") else "k_ms"
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(args.workload, {}).get(kname)
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
+                "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "alg_bytes_per_launch": alg_bytes, "kernel_ms": kms,
                 "path_alg_bytes": nsym + N + 30 * n + 48 * H,
                 "path_frac": (nsym + N + 30 * n + 48 * H) / 1e9 / (dev_ms / 1e3) / peak}

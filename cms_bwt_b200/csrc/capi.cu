@@ -83,6 +83,21 @@ int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
   else if (!strcmp(name, "kmer_k")) { if (v < 0 || v > 13) return CMSBWT_E_ARG; c->kmer_k = v; }
   else if (!strcmp(name, "skip_min")) { if (v < 2) return CMSBWT_E_ARG; c->skip_min = v; }
   else if (!strcmp(name, "fast")) { c->fast = v != 0; }
+  else if (!strcmp(name, "ms_occ")) { c->ms_occ = v; }
+  else if (!strcmp(name, "l2_pin")) {
+    // experiment switch (measured slower on B200: the set-aside shrinks L2 for every other kernel)
+    c->l2_pin = v != 0;
+    if (c->l2_pin && !c->l2_persist_max) {
+      int pm = 0, wm = 0;
+      cudaDeviceGetAttribute(&pm, cudaDevAttrMaxPersistingL2CacheSize, c->dev);
+      cudaDeviceGetAttribute(&wm, cudaDevAttrMaxAccessPolicyWindowSize, c->dev);
+      if (pm > 0 && cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)pm) == cudaSuccess) {
+        c->l2_persist_max = pm;
+        c->l2_window_max = wm;
+      }
+      cudaGetLastError();
+    }
+  }
   else if (!strcmp(name, "tile_budget")) { if (v < 0) return CMSBWT_E_ARG; c->tile_budget = v; }
   else return CMSBWT_E_ARG;
   return CMSBWT_OK;

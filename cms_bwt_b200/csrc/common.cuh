@@ -115,7 +115,11 @@ struct cmsbwt_ctx {
   // fast path (pure-ACGT reference): packed reference, {key, sa} per rank
   bool pure = false;         // x = ACGT* + augmentation, x[n_acgt] < 'A'
   u32 n_acgt = 0;
-  DBuf d_xp, d_sak;
+  DBuf d_sak;
+  u64 *xp = nullptr;         // packed reference, inside d_ktab's allocation
+  size_t hot_bytes = 0;      // k-mer table + packed reference (L2 persistence window)
+  i64 l2_pin = 0;
+  i64 l2_persist_max = 0, l2_window_max = 0;   // device limits (bytes), read at ctx_create
   DBuf d_tp, d_seps;         // packed text, sorted separator positions (+ sentinel)
   u64 sep_hint = 0, head_hint = 0;
   // text
@@ -144,6 +148,7 @@ struct cmsbwt_ctx {
   i64 kmer_k = 0;            // 0 = auto
   i64 skip_min = 20;         // fast path: try the G skip for matches at least this long
   i64 fast = 1;              // 0 = always use the general 8-bit kernel
+  i64 ms_occ = 10;           // fast path: resident CTAs per SM the MS kernel is compiled for (8, 10, 12)
   i64 tile_budget = 1ll << 36; // stage 2: brute-force tile counting up to this many pair tests per job
 };
 

@@ -179,7 +179,13 @@ void index_build(cmsbwt_ctx *c) {
   k_G<<<g, B, 0, st>>>(sa, c->d_isa.as<u32>(), plcp.as<u32>(), n, c->d_G.as<u32>());
   int k = pick_k(n, c->kmer_k);
   size_t K = (size_t)1 << (2 * k);
-  c->d_ktab.alloc((K + 2) * 4, st);
+  // k-mer table and (fast path) the packed reference share one allocation: together they are the
+  // hot, L2-sized part of the index, pinned in L2 while the MS kernel runs (ms_fast.cu)
+  const size_t ktab_bytes = (((K + 2) * 4) + 255) & ~(size_t)255;
+  const u64 xp_words = c->pure ? ((u64)n + 31) / 32 + MSF_PAD_WORDS : 0;
+  c->d_ktab.alloc(ktab_bytes + xp_words * 8, st);
+  c->xp = c->pure ? (u64 *)((u8 *)c->d_ktab.p + ktab_bytes) : nullptr;
+  c->hot_bytes = ktab_bytes + xp_words * 8;
   CK(cudaMemsetAsync(c->d_ktab.p, 0, (K + 2) * 4, st));
   k_ktab_mark<<<g, B, 0, st>>>(x, sa, n, k, c->d_ktab.as<u32>());
   size_t tb = 0;
@@ -199,17 +205,15 @@ void index_build(cmsbwt_ctx *c) {
   c->ix.ktab = c->d_ktab.as<u32>();
   c->stats.kmer_k = (u32)k;
   if (c->pure) {
-    const u64 nwords = ((u64)n + 31) / 32 + MSF_PAD_WORDS;
-    c->d_xp.alloc(nwords * 8, st);
+    const u64 nwords = xp_words;
     c->d_sak.alloc((size_t)n * 8, st);
     DBuf fl;
     fl.alloc(8, st);
     CK(cudaMemsetAsync(fl.p, 0, 8, st));
-    pack_2bit(c, x, c->n_acgt, c->d_xp.as<u64>(), nwords, nullptr, 0, nullptr, fl.as<u32>());
-    k_sak<<<g, B, 0, st>>>(sa, c->d_xp.as<u64>(), n, c->n_acgt, k, c->d_sak.as<u64>());
+    pack_2bit(c, x, c->n_acgt, c->xp, nwords, nullptr, 0, nullptr, fl.as<u32>());
+    k_sak<<<g, B, 0, st>>>(sa, c->xp, n, c->n_acgt, k, c->d_sak.as<u64>());
     CK(cudaGetLastError());
   } else {
-    c->d_xp.release();
     c->d_sak.release();
   }
   CK(cudaStreamSynchronize(st));

@@ -5,6 +5,7 @@
 #include "common.cuh"
 #include "ms_fast.cuh"
 #include <cub/cub.cuh>
+#include <string.h>
 
 // ---- 8-bit -> 2-bit ---------------------------------------------------------------------------
 // One thread packs 32 symbols into one word.  Symbols at positions >= len pack as 0.  Separators
@@ -79,14 +80,15 @@ __global__ void k_wsep(const u64 *seps, u64 nseps, u32 WL, u64 nwin, u32 *wsep) 
 }
 
 // ---- the kernel ---------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_ms_fast(MsfParams P) {
+template <int OCC>
+__global__ void __launch_bounds__(128, OCC) k_ms_fast(MsfParams P) {
   MsfLane L;
   L.i = L.w1 = L.sepnext = 0;
   L.sepidx = L.w = 0;
   L.prevpos = MSF_INVALID; L.prevterm = 0; L.first = 0;
   L.curb = MSF_NOB; L.fill = 0; L.cnt = 0; L.limit = 0;
   L.tkey = L.lo = L.hi = L.rb = L.prevkey = L.prevsa = L.haveprev = 0;
-  L.pos = L.len = L.sm = 0;
+  L.pos = L.len = L.sm = 0; L.chb = 4;
   L.state = MSF_S_FETCH;
   while (!__all_sync(0xffffffffu, L.state == MSF_S_DONE)) msf_warp_iter(P, L);
 }
@@ -190,7 +192,8 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   tmp.alloc(tb, st);
   int sms = 148, occ = 4;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->dev);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_ms_fast, 128, 0);
+  void (*kern)(MsfParams) = c->ms_occ >= 12 ? k_ms_fast<12> : c->ms_occ >= 10 ? k_ms_fast<10> : k_ms_fast<8>;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 128, 0);
   if (occ < 1) occ = 1;
   // pool: batches of MSF_RB records; every window wastes at most one partly filled batch
   u64 rec_est = c->head_hint ? c->head_hint + c->head_hint / 8 : N / 16;
@@ -203,7 +206,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     CK(cudaMemsetAsync(counter.p, 0, 8, st));
     CK(cudaMemsetAsync(nbused.p, 0, 4, st));
     MsfParams P;
-    P.xp = c->d_xp.as<u64>(); P.x8 = c->ix.x; P.sak = c->d_sak.as<u64>(); P.ktab = c->ix.ktab; P.G = c->ix.G;
+    P.xp = c->xp; P.x8 = c->ix.x; P.sak = c->d_sak.as<u64>(); P.ktab = c->ix.ktab; P.G = c->ix.G;
     P.n = c->ix.n; P.n_acgt = c->n_acgt; P.k = c->ix.k;
     P.tp = c->d_tp.as<u64>(); P.N = N; P.seps = c->d_seps.as<u64>(); P.nseps = nseps; P.wsep = wsep.as<u32>();
     P.WL = WL; P.nwin = nwin; P.skip_min = (u32)c->skip_min;
@@ -215,7 +218,24 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     u64 want = (nwin + 127) / 128;
     u32 grid = (u32)min(want, (u64)sms * occ);
     cudaEventRecord(e1, st);
-    k_ms_fast<<<grid, 128, 0, st>>>(P);
+    // pin the k-mer table + packed reference in L2 for this kernel: every search starts there,
+    // while the {key, sa} array, G and the text stream through
+    cudaStreamAttrValue apw;
+    memset(&apw, 0, sizeof apw);
+    if (c->l2_pin && c->l2_persist_max) {
+      apw.accessPolicyWindow.base_ptr = c->d_ktab.p;
+      apw.accessPolicyWindow.num_bytes = c->hot_bytes < (size_t)c->l2_window_max ? c->hot_bytes : (size_t)c->l2_window_max;
+      double r = (double)c->l2_persist_max / (double)apw.accessPolicyWindow.num_bytes;
+      apw.accessPolicyWindow.hitRatio = r > 1.0 ? 1.0f : (float)r;
+      apw.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+      apw.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+      cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &apw);
+    }
+    kern<<<grid, 128, 0, st>>>(P);
+    if (c->l2_pin && c->l2_persist_max) {
+      apw.accessPolicyWindow.num_bytes = 0;
+      cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &apw);
+    }
     cudaEventRecord(e2, st);
     LAUNCH(c);
     CK(cudaGetLastError());

@@ -159,6 +159,7 @@ struct MsfLane {
   msf_u32 limit;
   msf_u32 tkey, lo, hi, rb, prevkey, prevsa, haveprev;
   msf_u32 pos, len, sm;
+  msf_u32 chb;            // code of the base before position i (4 = not loaded yet)
 };
 
 MSF_HD void msf_store_rec(const MsfParams &P, msf_u64 slot, msf_u32 a, msf_u32 b, msf_u32 c, msf_u32 d) {
@@ -257,7 +258,7 @@ MSF_HD msf_u32 msf_fin(const MsfParams &P, MsfLane &L, bool term) {
   const bool head = term || L.prevterm || L.pos != L.prevpos + 1;
   if (L.first) P.wfirstpos[L.w] = (term || L.prevterm) ? MSF_INVALID : L.pos;
   if (head || tent) {
-    msf_u32 ch = L.prevterm ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i - 1));
+    msf_u32 ch = L.prevterm ? 2u : (msf_u32)msf_sym_of(L.chb < 4 ? L.chb : msf_base(P.tp, L.i - 1));
     msf_emit(P, L, (msf_u32)(L.i - (msf_u64)L.w * P.WL), L.pos, L.len, ch | (L.sm << 8) | (tent ? 1u << 9 : 0u));
   }
   msf_dump(P, L.i, L.pos, L.len, L.sm, head || tent);
@@ -297,16 +298,26 @@ MSF_HD msf_u32 msf_ext_max(const MsfParams &P, msf_u32 limit, msf_u32 pos) {
   msf_u32 room = P.n_acgt - pos;
   return limit < room ? limit : room;
 }
-// phase B probe: first mismatch among the 32 bases at offset off of the two streams (32 = none)
+// phase B probe: the 32 bases at offset off of the two streams.  Returns 0xFFFFFFFF when they are
+// equal, else (offset of the first mismatch << 1) | (reference base > text base), so that a
+// min-reduction over the lanes yields the match length and the smaller flag at once.
 MSF_HD msf_u32 msf_ext_probe(const MsfParams &P, msf_u64 i, msf_u32 pos, msf_u32 off) {
-  msf_u64 d = msf_get64(P.tp, i + off) ^ msf_get64(P.xp, (msf_u64)pos + off);
-  return d ? (MSF_CTZ64(d) >> 1) : 32u;
+  const msf_u64 tw = msf_get64(P.tp, i + off), xw = msf_get64(P.xp, (msf_u64)pos + off);
+  const msf_u64 d = tw ^ xw;
+  if (!d) return 0xFFFFFFFFu;
+  const msf_u32 m = MSF_CTZ64(d) >> 1;
+  const msf_u32 tc = (msf_u32)(tw >> (2 * m)) & 3u, xc = (msf_u32)(xw >> (2 * m)) & 3u;
+  return ((off + m) << 1) | (xc > tc ? 1u : 0u);
 }
-// phase B result for the owner lane: the match is `len` long; smaller = x[pos+len] > next text symbol
-MSF_HD void msf_ext_done(const MsfParams &P, MsfLane &L, msf_u32 len) {
-  L.len = len;
-  msf_u32 xb = MSF_LD8(P.x8 + L.pos + len);
-  msf_u32 tb = len == L.limit ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i + len));
+// phase B result for the owner lane.  res = min over the probes (0xFFFFFFFF: no mismatch seen),
+// bmax = min(limit, room in the pure reference).  A mismatch before bmax decides everything;
+// otherwise the match ends at a separator or at the augmentation and the bytes decide
+// (smaller = x[pos+len] > next text symbol, :53-58).
+MSF_HD void msf_ext_done(const MsfParams &P, MsfLane &L, msf_u32 res, msf_u32 bmax) {
+  if (res != 0xFFFFFFFFu && (res >> 1) < bmax) { L.len = res >> 1; L.sm = res & 1u; return; }
+  L.len = bmax;
+  msf_u32 xb = MSF_LD8(P.x8 + L.pos + bmax);
+  msf_u32 tb = bmax == L.limit ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i + bmax));
   L.sm = xb > tb ? 1u : 0u;
 }
 
@@ -351,6 +362,7 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
         L.state = MSF_S_FETCH;
         break;
       }
+      L.chb = 4;
       if (L.i == L.sepnext) {                             // document terminator (:1198-1212)
         L.pos = P.n - 1; L.len = 0; L.sm = 0;
         act = MSF_ACT_TERM;
@@ -360,7 +372,10 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
       msf_u64 dist = L.sepnext - L.i;
       L.limit = dist > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (msf_u32)dist;
       if (L.limit < KL) { act = MSF_ACT_GENERIC; break; }
-      msf_u64 be = msf_be64(msf_get64(P.tp, L.i));
+      // one read serves the k-mer, the key and the symbol before i (the head record needs it)
+      msf_u64 tw = msf_get64(P.tp, L.i ? L.i - 1 : 0);
+      if (L.i) { L.chb = (msf_u32)tw & 3u; tw >>= 2; }
+      msf_u64 be = msf_be64(tw);
       msf_u32 code = (msf_u32)(be >> (64 - 2 * P.k));
       L.tkey = (msf_u32)((be << (2 * P.k)) >> 32);
       msf_u32 lb = MSF_LD32(P.ktab + code), rb = MSF_LD32(P.ktab + code + 1);
@@ -453,15 +468,12 @@ __device__ __forceinline__ void msf_warp_iter(const MsfParams &P, MsfLane &L) {
     while (true) {
       const msf_u32 off = blen + 32u * lane;
       msf_u32 cand = 0xFFFFFFFFu;
-      if (off < bmax) {
-        msf_u32 m = msf_ext_probe(P, bi, bpos, off);
-        if (m < 32) cand = off + m;
-      }
+      if (off < bmax) cand = msf_ext_probe(P, bi, bpos, off);
       res = __reduce_min_sync(FULL, cand);
       if (res != 0xFFFFFFFFu || blen + 1024u >= bmax) break;
       blen += 1024u;
     }
-    if (lane == src) { msf_ext_done(P, L, res < bmax ? res : bmax); act = MSF_ACT_FIN; }
+    if (lane == src) { msf_ext_done(P, L, res, bmax); act = MSF_ACT_FIN; }
   }
   // phase C
   if (act & MSF_ACT_GENERIC) msf_generic_search(P, L.i, L.limit, L.pos, L.len, L.sm);
@@ -510,14 +522,14 @@ inline void msf_warp_iter_host(const MsfParams &P, MsfLane *W, int nl) {
       for (msf_u32 lane = 0; lane < 32; lane++) {
         const msf_u32 off = blen + 32u * lane;
         if (off < bmax) {
-          msf_u32 m = msf_ext_probe(P, L.i, L.pos, off);
-          if (m < 32 && off + m < res) res = off + m;
+          msf_u32 cand = msf_ext_probe(P, L.i, L.pos, off);
+          if (cand < res) res = cand;
         }
       }
       if (res != 0xFFFFFFFFu || blen + 1024u >= bmax) break;
       blen += 1024u;
     }
-    msf_ext_done(P, L, res < bmax ? res : bmax);
+    msf_ext_done(P, L, res, bmax);
     act[l] = MSF_ACT_FIN;
   }
   for (int l = 0; l < nl; l++) {                          // phase C

@@ -113,72 +113,100 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, cons
   unsigned long long tot = BR(tr).Sum(w);
   if (tid == 0) {
     if (tot) atomicAdd(work, tot);
-    u32 rcp = 1;
-    while (rcp < r1 - r0) rcp <<= 1;                    // pass B pads the ranges to a power of two
-    atomicMax(maxent, (h1 - h0) + rcp);
+    atomicMax(maxent, (h1 - h0) + (r1 - r0));
   }
 }
 
 // ---- pass B: within + head symbols --------------------------------------------------------------
-// The tile's ranges are sorted by kappa in shared memory (bitonic); a head then bisects for the
-// number of ranges with a smaller kappa and only tests the shorter side for coverage (the other
-// side follows from the per-position range coverage), so a short head costs ~a dozen tests.
+// A head needs the number of ranges that cover its position with a smaller kappa.  The tile's
+// ranges are split into LT_NB kappa buckets by LT_NB-1 pivots sampled from the ranges themselves;
+// C[b][q] = ranges of buckets < b covering position q comes from per-bucket difference arrays
+// (two shared-memory atomics per range, one scan per bucket row, one prefix over the buckets), so
+// a head only tests the ranges of its own bucket one by one (about rc / LT_NB of them).
+#define LT_NB 16
 __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, const TileEnt *re, const u32 *hoff,
                                                            const u32 *roff, const u32 *isa, const u64 *base,
                                                            u32 n, u8 *out, u32 *within_out, u64 *off_out) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W];
-  __shared__ int s_d[LT_W + 1];
-  __shared__ u32 s_rcov[LT_W];
   __shared__ u64 s_base[LT_W];
+  __shared__ u64 s_praw[LT_NB], s_piv[LT_NB];
+  __shared__ u32 s_bcnt[LT_NB + 1], s_boff[LT_NB + 2], s_bcur[LT_NB + 1];
+  __shared__ int s_C[LT_NB + 1][LT_W + 1];
   typedef cub::BlockScan<u32, LT_THREADS> BS;
-  typedef cub::BlockScan<int, LT_THREADS> BSI;
-  __shared__ union { typename BS::TempStorage a; typename BSI::TempStorage b; } ts;
-  const u32 t = blockIdx.x, tid = threadIdx.x;
+  __shared__ typename BS::TempStorage ts;
+  const u32 t = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
   const u32 hc = h1 - h0, rc = r1 - r0;
   if (hc == 0) return;
-  u32 rcp = 1;
-  while (rcp < rc) rcp <<= 1;
-  TileEnt *s_re = (TileEnt *)smem;              // rcp entries, sorted by kappa
-  TileEnt *s_he = s_re + rcp;                   // hc entries, grouped by position
-  s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0;
-  if (tid == 0) s_d[LT_W] = 0;
+  TileEnt *s_he = (TileEnt *)smem;              // hc heads, grouped by position
+  u64 *s_rk = (u64 *)(s_he + hc);               // rc range kappas, grouped by bucket
+  u32 *s_rl = (u32 *)(s_rk + rc);               // their lo | hi << 16
+  const u32 npiv = rc < LT_NB - 1 ? rc : LT_NB - 1;
+  s_cnt[tid] = 0; s_cur[tid] = 0;
+  for (u32 k = tid; k < (LT_NB + 1) * (LT_W + 1); k += LT_THREADS) (&s_C[0][0])[k] = 0;
+  if (tid <= LT_NB) { s_bcnt[tid] = 0; s_bcur[tid] = 0; }
+  if (tid < npiv) s_praw[tid] = re[r0 + (u32)(((u64)(tid + 1) * rc) / (npiv + 1))].kappa;
   {
     u32 p = (t << LT_SHIFT) + tid;
     s_base[tid] = p < n ? base[isa[p]] : 0;
   }
   __syncthreads();
-  for (u32 j = tid; j < rcp; j += LT_THREADS) {
-    TileEnt e;
-    if (j < rc) {
-      e = re[r0 + j];
-      atomicAdd(&s_d[e.a & 0xFFFF], 1);
-      atomicAdd(&s_d[(e.a >> 16) + 1], -1);
-    } else { e.a = 1; e.b = 0; e.kappa = ~0ull; }        // padding: covers nothing, sorts last
-    s_re[j] = e;
+  if (tid < npiv) {                             // sort the pivots (distinct kappas) by rank counting
+    const u64 mine = s_praw[tid];
+    u32 rk = 0;
+    for (u32 k = 0; k < npiv; k++) rk += s_praw[k] < mine;
+    s_piv[rk] = mine;
+  }
+  __syncthreads();
+  // pass 1 over the ranges: bucket sizes and per-bucket coverage deltas; head counts per position
+  for (u32 j = tid; j < rc; j += LT_THREADS) {
+    const TileEnt e = re[r0 + j];
+    u32 bk = 0;
+    for (u32 k = 0; k < npiv; k++) bk += s_piv[k] <= e.kappa;
+    atomicAdd(&s_bcnt[bk], 1u);
+    atomicAdd(&s_C[bk][e.a & 0xFFFF], 1);
+    atomicAdd(&s_C[bk][(e.a >> 16) + 1], -1);
   }
   for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[he[h0 + j].b & (LT_W - 1)], 1u);
   __syncthreads();
-  for (u32 k = 2; k <= rcp; k <<= 1)                     // bitonic sort of the ranges by kappa
-    for (u32 j = k >> 1; j > 0; j >>= 1) {
-      for (u32 x = tid; x < (rcp >> 1); x += LT_THREADS) {
-        const u32 i = ((x & ~(j - 1)) << 1) | (x & (j - 1));
-        const bool up = (i & k) == 0;
-        TileEnt a = s_re[i], b = s_re[i + j];
-        if ((a.kappa > b.kappa) == up) { s_re[i] = b; s_re[i + j] = a; }
-      }
-      __syncthreads();
-    }
   u32 ex;
-  BS(ts.a).ExclusiveSum(s_cnt[tid], ex);
+  BS(ts).ExclusiveSum(s_cnt[tid], ex);
   s_off[tid] = ex;
   if (tid == LT_THREADS - 1) s_off[LT_W] = ex + s_cnt[tid];
+  if (tid == 0) {
+    u32 run = 0;
+    for (u32 k = 0; k <= LT_NB; k++) { s_boff[k] = run; run += s_bcnt[k]; }
+    s_boff[LT_NB + 1] = run;
+  }
+  // coverage per bucket: inclusive scan of every delta row (one warp per row, 8 entries per lane)
+  for (u32 row = warp; row <= LT_NB; row += LT_THREADS / 32) {
+    int v[8], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { sum += s_C[row][lane * 8 + k]; v[k] = sum; }
+    int incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { int o = __shfl_up_sync(0xffffffffu, incl, d); if ((int)lane >= d) incl += o; }
+    const int pre = incl - sum;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s_C[row][lane * 8 + k] = v[k] + pre;
+  }
   __syncthreads();
-  int incl;
-  BSI(ts.b).InclusiveSum(s_d[tid], incl);
-  s_rcov[tid] = (u32)incl;
-  for (u32 j = tid; j < hc; j += LT_THREADS) {          // heads grouped by position
+  {                                             // exclusive prefix over the buckets, per position
+    int run = 0;
+#pragma unroll
+    for (int bk = 0; bk <= LT_NB; bk++) { int c = s_C[bk][tid]; s_C[bk][tid] = run; run += c; }
+  }
+  // pass 2: ranges grouped by bucket, heads grouped by position
+  for (u32 j = tid; j < rc; j += LT_THREADS) {
+    const TileEnt e = re[r0 + j];
+    u32 bk = 0;
+    for (u32 k = 0; k < npiv; k++) bk += s_piv[k] <= e.kappa;
+    const u32 slot = s_boff[bk] + atomicAdd(&s_bcur[bk], 1u);
+    s_rk[slot] = e.kappa;
+    s_rl[slot] = e.a;
+  }
+  for (u32 j = tid; j < hc; j += LT_THREADS) {
     TileEnt e = he[h0 + j];
     u32 q = e.b & (LT_W - 1);
     s_he[s_off[q] + atomicAdd(&s_cur[q], 1u)] = e;
@@ -190,23 +218,12 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
     const u64 kap = e.kappa;
     u32 w = 0;
     for (u32 jj = s_off[q]; jj < s_off[q + 1]; jj++) w += s_he[jj].kappa < kap;
-    u32 lo = 0, hi = rc;                                 // ranges [0, lo) have a smaller kappa
-    while (lo < hi) {
-      u32 mid = (lo + hi) >> 1;
-      if (s_re[mid].kappa < kap) lo = mid + 1; else hi = mid;
-    }
-    if (lo <= rc - lo) {
-      for (u32 r = 0; r < lo; r++) {
-        const u32 lh = s_re[r].a;
-        w += ((lh & 0xFFFF) <= q) & (q <= (lh >> 16));
-      }
-    } else {
-      u32 above = 0;
-      for (u32 r = lo; r < rc; r++) {
-        const u32 lh = s_re[r].a;
-        above += ((lh & 0xFFFF) <= q) & (q <= (lh >> 16));
-      }
-      w += s_rcov[q] - above;
+    u32 bk = 0;
+    for (u32 k = 0; k < npiv; k++) bk += s_piv[k] <= kap;
+    w += (u32)s_C[bk][q];
+    for (u32 r = s_boff[bk]; r < s_boff[bk + 1]; r++) {
+      const u32 lh = s_rl[r];
+      w += (s_rk[r] < kap) & ((lh & 0xFFFF) <= q) & (q <= (lh >> 16));
     }
     const u64 off = s_base[q] + w;
     out[off] = (u8)(e.b >> 8);
@@ -309,7 +326,7 @@ void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out) {
     c->h_within.alloc(H * 4, st); c->h_off.alloc(H * 8, st);
     wo = c->h_within.as<u32>(); oo = c->h_off.as<u64>();
   }
-  size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt);
+  size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;     // heads 16 B, ranges 12 B each
   if (sm > 40 * 1024)
     CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_place<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
