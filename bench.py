@@ -56,7 +56,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -98,7 +98,11 @@ def reference_arm(args, rank):
     import numpy as np
     import gen_synth
     exe = os.path.join(ROOT, "oracle", "_ref", "cmsbwt")
-    sample = dict(ref_bp=2_000_000, copies=8, div=WORKLOADS[args.workload]["div"], seed=13)
+    # bounded sample: about 1 s of index build + 0.4 s per 5 Mbp copy on one core; the whole
+    # --steps/--warmup run is kept under ~150 s
+    runs = max(1, args.steps + args.warmup)
+    ncopies = int(max(2, min(40, (150.0 / runs - 1.0) / 0.42)))
+    sample = dict(ref_bp=5_000_000, copies=ncopies, div=WORKLOADS[args.workload]["div"], seed=13)
     if not os.path.exists(exe):
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/cmsbwt not built"}))
         return
@@ -136,7 +140,7 @@ def cpu_baseline(div):
     if not os.path.exists(exe):
         return None
     wd = tempfile.mkdtemp(prefix="cmsref")
-    ref_bp, copies_n = 2_000_000, 8
+    ref_bp, copies_n = 5_000_000, 30
     ref, copies = gen_synth.make_collection(ref_bp, copies_n, div, 13)
     gen_synth.write_files(os.path.join(wd, "s"), ref, copies)
     nsym = int(sum(len(c) for c in copies))
@@ -152,7 +156,7 @@ def cpu_baseline(div):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
@@ -199,10 +203,10 @@ def main():
         ctx.heads_sort()
         ctx.emit(P.MODE_PLAIN)
 
-    for _ in range(args.warmup):
-        step()
     sampler = ClockSampler(local)
-    sampler.start()
+    sampler.start()                            # nvidia-smi needs ~0.1 s to come up: start it before
+    for _ in range(args.warmup):               # the warm-up (same load as the timed steps)
+        step()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage = {"ms_ms": 0.0, "sort_ms": 0.0, "emit_ms": 0.0, "ms_kernel_ms": 0.0, "pack_ms": 0.0}
