@@ -209,6 +209,9 @@ def main():
         step()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    profiling = os.environ.get("CMSBWT_PROFILE") == "1"      # ncu --profile-from-start off
+    if profiling:
+        torch.cuda.profiler.start()
     stage = {"ms_ms": 0.0, "sort_ms": 0.0, "emit_ms": 0.0, "ms_kernel_ms": 0.0, "pack_ms": 0.0}
     launches = 0
     t0 = time.time()
@@ -222,6 +225,8 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     wall = time.time() - t0
+    if profiling:
+        torch.cuda.profiler.stop()
     clocks = sampler.stop()
     s = ctx.stats()
     # device time of the timed region = sum of the library's CUDA-event stage times (its own
