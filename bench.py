@@ -153,6 +153,142 @@ def cpu_baseline(div):
                       % (ref_bp, copies_n, div, nsym / 1e6, dt)}
 
 
+def run_multi(args, rank, world, local, dev, dist):
+    """N > 1: one process per GPU, the collection's documents sharded by rank (strong scaling: the
+    workload is the same 100-copy collection at every N), cms_bwt_b200.multi over NCCL."""
+    import numpy as np
+    import torch
+    import cms_bwt_b200 as P
+    from cms_bwt_b200 import multi
+    import gen_device
+    w = WORKLOADS[args.workload]
+    # contiguous ranges of copies per rank (all copies have nearly the same length)
+    plan = multi.shard_documents([w["ref_bp"]] * w["copies"], world)
+    a, b = plan[rank]
+    if b <= a:
+        raise SystemExit("bench.py: more ranks than documents")
+    ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev,
+                                               first_copy=a, ncopies=b - a)
+    torch.cuda.synchronize()
+    x = P.augment(ref.cpu().numpy())
+    ctx = P.Context(local)
+    ctx.index_upload(x)                       # replicated index, built on every GPU, timed separately
+    st0 = ctx.stats()
+    state = {}
+
+    def step():
+        sp, out = multi.run_sharded(ctx, dev, text.data_ptr(), N, ndocs, rank, world)
+        state["sp"], state["out"] = sp, out
+
+    def allmax(v):
+        t = torch.tensor([float(v)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(v):
+        t = torch.tensor([float(v)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage = {"ms_ms": 0.0, "sort_ms": 0.0, "emit_ms": 0.0, "ms_kernel_ms": 0.0, "pack_ms": 0.0}
+    launches = 0
+    t0 = time.time()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+        s = ctx.stats()
+        for k in stage:
+            stage[k] += s[k]
+        launches += s["kernel_launches"]
+    e1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    wall = time.time() - t0
+    dev_ms_local = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_per_step = allmax(max(wall * 1e3, dev_ms_local)) / args.steps
+    sp = state["sp"]
+    nsym = sp.N_total - sp.ndocs_total
+    s = ctx.stats()
+    H_total = allsum(s["n_heads"])
+    launches_total = allsum(launches)
+    comm_bytes = allsum(sp.comm_bytes)
+    lib_ms = (stage["ms_ms"] + stage["sort_ms"] + stage["emit_ms"]) / args.steps
+    lib_ms_max = allmax(lib_ms)
+
+    # e2e: every rank copies its documents H2D and its slice of the BWT D2H inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        host_text = torch.empty(N + 64, dtype=torch.uint8, pin_memory=True)
+        host_text.copy_(text[:N + 64])
+        dtext = torch.empty(N + 64, dtype=torch.uint8, device=dev)
+        host_out = torch.empty(sp.out_len + 64, dtype=torch.uint8, pin_memory=True)
+
+        def e2e_step():
+            dtext.copy_(host_text, non_blocking=True)
+            torch.cuda.synchronize()
+            sp2, out = multi.run_sharded(ctx, dev, dtext.data_ptr(), N, ndocs, rank, world)
+            host_out[:out.numel()].copy_(out, non_blocking=True)
+            torch.cuda.synchronize()
+        e2e_step()
+        reps = max(1, min(args.steps, 3))
+        dist.barrier()
+        t1 = time.time()
+        for _ in range(reps):
+            e2e_step()
+        dist.barrier()
+        dt = allmax(time.time() - t1) / reps
+        e2e = {"value": nsym / 1e9 / dt, "unit": "Gbp/s", "h2d_bytes_per_step": int(sp.N_total),
+               "d2h_bytes_per_step": int(sp.N_total), "ms_per_step": dt * 1e3}
+    if rank == 0:
+        peak, peak_kind = measured_peak()
+        kms = stage["ms_kernel_ms"] / args.steps
+        alg_bytes = N + 16 * s["n_heads"]
+        achieved = alg_bytes / 1e9 / (kms / 1e3)
+        n = len(x)
+        path_bytes = nsym + sp.N_total + 30 * n * world + 48 * H_total
+        line = {
+            "metric": METRIC, "value": nsym / 1e9 / (ms_per_step / 1e3), "unit": "Gbp/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "%s: %d bp random ACGT reference + %d mutated copies at %g (SNP/ins/del), "
+                                   "plain BWT, documents sharded over %d GPUs" %
+                                   (args.workload, w["ref_bp"], w["copies"], w["div"], world),
+                       "N_symbols": int(nsym), "documents": int(sp.ndocs_total), "n_ref_augmented": int(n),
+                       "heads": int(H_total), "cache": "inputs (%.1f GB per GPU) larger than L2" % (N / 1e9),
+                       "parallelism": "documents sharded (stage 1), tails by key range, tiles by reference-"
+                                      "position range, output by byte range; index replicated",
+                       "device_ms_per_step_rank0": dev_ms_local / args.steps,
+                       "kernel_stage_ms_max": lib_ms_max,
+                       "stage_ms_rank0": {k: v / args.steps for k, v in stage.items()},
+                       "exchange_bytes_per_step": comm_bytes, "collectives_per_step": sp.collectives,
+                       "rank_rounds": sp.rank_rounds,
+                       "index_ms": {"sa_build_gpu": st0["sa_build_ms"], "index_build": st0["index_build_ms"]}},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_total),
+            "roofline": {"bound": "hbm", "kernel": "k_ms_fast" if s.get("fast_path") else "k_ms",
+                         "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "alg_bytes_per_launch": alg_bytes,
+                         "kernel_ms": kms, "note": "rank 0's launch on its shard",
+                         "path_alg_bytes": path_bytes,
+                         "path_frac": path_bytes / 1e9 / (ms_per_step / 1e3) / (peak * world)},
+            "cpu_baseline": None,
+        }
+        print(json.dumps(line))
+    dist.barrier()
+    ctx.close()
+    dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -185,8 +321,7 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
     if world > 1:
-        import bench_multi
-        bench_multi.run(args, rank, world, local, dist)
+        run_multi(args, rank, world, local, dev, dist)
         return
 
     w = WORKLOADS[args.workload]

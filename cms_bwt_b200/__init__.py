@@ -24,6 +24,9 @@ EXPORTS = [
     "cmsbwt_set_ms_dump", "cmsbwt_ms_download", "cmsbwt_heads_sort", "cmsbwt_heads_download",
     "cmsbwt_emit", "cmsbwt_result_device", "cmsbwt_result_download", "cmsbwt_run",
     "cmsbwt_set_param",
+    "cmsbwt_shard_tails", "cmsbwt_shard_buffer", "cmsbwt_shard_lower_bound", "cmsbwt_shard_rank_owner",
+    "cmsbwt_shard_rank_apply", "cmsbwt_shard_tie_keys", "cmsbwt_shard_tie_refine",
+    "cmsbwt_shard_tiles_local", "cmsbwt_shard_tiles_merge", "cmsbwt_shard_emit", "cmsbwt_shard_apply",
 ]
 
 

@@ -3,13 +3,8 @@
 #include <string.h>
 #include <chrono>
 
-// one cache per device (contexts of one process on one GPU share it; calls are serialised)
-static DevCache g_cache[16];
-DevCache &dev_cache() {
-  int d = 0;
-  cudaGetDevice(&d);
-  return g_cache[d & 15];
-}
+static thread_local DevCache *tl_cache = nullptr;
+DevCache *&current_cache() { return tl_cache; }
 
 static int fail(cmsbwt_ctx *c, int code, const std::string &msg) {
   if (c) c->err = msg;
@@ -60,11 +55,12 @@ int cmsbwt_ctx_create(int dev, cmsbwt_ctx **out) {
 void cmsbwt_ctx_destroy(cmsbwt_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->dev);
+  tl_cache = &c->cache;
   cudaStream_t st = c->st;
   cudaStreamSynchronize(st);
-  delete c;                                 // DBufs go back to the device cache
+  delete c;                                 // DBufs go back to the context's cache, which frees them
+  tl_cache = nullptr;
   cudaStreamDestroy(st);
-  dev_cache().trim();
 }
 
 const char *cmsbwt_last_error(const cmsbwt_ctx *c) { return c ? c->err.c_str() : "null context"; }
@@ -199,7 +195,7 @@ int cmsbwt_build_sa(cmsbwt_ctx *c, const uint8_t *x, uint32_t n, int32_t *sa_out
   if (!c || !x || n < 2 || n >= 0x7FFFFF00u) return fail(c, CMSBWT_E_ARG, "bad reference");
   if (x[n - 1] != 0) return fail(c, CMSBWT_E_ARG, "reference is not augmented (x[n-1] != 0)");
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   upload_x(c, x, n);
   c->d_sa.alloc((size_t)n * 4, c->st);
   Timer t(c->st);
@@ -218,7 +214,7 @@ int cmsbwt_index_upload(cmsbwt_ctx *c, const uint8_t *x, uint32_t n, const int32
   c->have_index = false;
   if (!sa) { int rc = cmsbwt_build_sa(c, x, n, nullptr); if (rc) return rc; }
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   if (sa) {
     upload_x(c, x, n);
     c->d_sa.alloc((size_t)n * 4, c->st);
@@ -241,7 +237,7 @@ __global__ void k_plcp_prime(const u32 *G, u32 n, u32 *out) {
 int cmsbwt_index_download(cmsbwt_ctx *c, int32_t *sa, uint32_t *isa, uint32_t *pp, uint8_t *rb) {
   if (!c || !c->have_index) return fail(c, CMSBWT_E_ARG, "no index");
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   const u32 n = c->ix.n;
   if (sa) CK(cudaMemcpyAsync(sa, c->d_sa.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
   if (isa) CK(cudaMemcpyAsync(isa, c->d_isa.p, (size_t)n * 4, cudaMemcpyDeviceToHost, c->st));
@@ -278,7 +274,7 @@ int cmsbwt_ms_run(cmsbwt_ctx *c, const uint8_t *text, uint64_t N) {
   if (!c || !c->have_index) return fail(c, CMSBWT_E_ARG, "index_upload first");
   if (!text || N == 0) return fail(c, CMSBWT_E_ARG, "empty text");
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   Timer t(c->st);
   c->d_text.alloc(N + CMS_PAD, c->st);
   CK(cudaMemsetAsync(c->d_text.as<u8>() + N, 2, CMS_PAD, c->st));
@@ -294,6 +290,7 @@ int cmsbwt_ms_run_device(cmsbwt_ctx *c, const void *d_text, uint64_t N) {
   if (!c || !c->have_index) return fail(c, CMSBWT_E_ARG, "index_upload first");
   if (!d_text || N == 0 || ((uintptr_t)d_text & 15)) return fail(c, CMSBWT_E_ARG, "bad device text");
   cudaSetDevice(c->dev);
+  tl_cache = &c->cache;
   c->d_text.release();
   c->text = (const u8 *)d_text;
   c->N = N;
@@ -310,7 +307,7 @@ int cmsbwt_set_ms_dump(cmsbwt_ctx *c, int enable) {
 int cmsbwt_ms_download(cmsbwt_ctx *c, uint32_t *pos, uint32_t *len, uint8_t *sm, uint8_t *hd) {
   if (!c || !c->have_ms || !c->dump_pos.p) return fail(c, CMSBWT_E_ARG, "no MS dump");
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   const u64 N = c->N;
   if (pos) CK(cudaMemcpyAsync(pos, c->dump_pos.p, N * 4, cudaMemcpyDeviceToHost, c->st));
   if (len) CK(cudaMemcpyAsync(len, c->dump_len.p, N * 4, cudaMemcpyDeviceToHost, c->st));
@@ -324,7 +321,7 @@ int cmsbwt_ms_download(cmsbwt_ctx *c, uint32_t *pos, uint32_t *len, uint8_t *sm,
 int cmsbwt_heads_sort(cmsbwt_ctx *c) {
   if (!c || !c->have_ms) return fail(c, CMSBWT_E_ARG, "ms_run first");
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   Timer t(c->st);
   sort_stage(c);
   c->stats.sort_ms = t.stop();
@@ -342,7 +339,7 @@ int cmsbwt_heads_download(cmsbwt_ctx *c, uint64_t *g, uint32_t *pos, uint32_t *l
                           uint64_t *off) {
   if (!c || !c->have_ms) return fail(c, CMSBWT_E_ARG, "ms_run first");
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   const u64 H = c->H;
   if (g) CK(cudaMemcpyAsync(g, c->h_gstart.p, H * 8, cudaMemcpyDeviceToHost, c->st));
   if (pos) CK(cudaMemcpyAsync(pos, c->h_pos.p, H * 4, cudaMemcpyDeviceToHost, c->st));
@@ -367,7 +364,7 @@ int cmsbwt_emit(cmsbwt_ctx *c, int mode, uint64_t *out_bytes) {
   if (!c || !c->have_sort) return fail(c, CMSBWT_E_ARG, "heads_sort first");
   if (mode != CMSBWT_MODE_PLAIN && mode != CMSBWT_MODE_RLE) return fail(c, CMSBWT_E_ARG, "bad mode");
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   Timer t(c->st);
   emit_stage(c, mode);
   c->stats.emit_ms = t.stop();
@@ -386,7 +383,7 @@ int cmsbwt_result_download(cmsbwt_ctx *c, void *host_out, uint64_t cap) {
   if (!c || !host_out || !c->d_out.p) return fail(c, CMSBWT_E_ARG, "emit first");
   if (cap < c->out_bytes) return fail(c, CMSBWT_E_ARG, "output buffer too small");
   GUARD_BEGIN
-  CK(cudaSetDevice(c->dev));
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   Timer t(c->st);
   CK(cudaMemcpyAsync(host_out, cmsbwt_result_device(c), c->out_bytes, cudaMemcpyDeviceToHost, c->st));
   c->stats.d2h_ms = t.stop();
@@ -405,6 +402,177 @@ int cmsbwt_run(cmsbwt_ctx *c, const uint8_t *text, uint64_t N, int mode, void *h
   if (rc) return rc;
   if (out_bytes) *out_bytes = ob;
   return cmsbwt_result_download(c, host_out, cap);
+}
+
+
+// ---- multi-GPU shard API ------------------------------------------------------------------------
+__global__ void k_lb32(const u32 *a, u64 n, const u64 *v, u32 cnt, u64 *out) {
+  u32 k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= cnt) return;
+  u64 lo = 0, hi = n, key = v[k];
+  while (lo < hi) { u64 mid = (lo + hi) >> 1; if ((u64)a[mid] < key) lo = mid + 1; else hi = mid; }
+  out[k] = lo;
+}
+__global__ void k_lb64(const u64 *a, u64 n, const u64 *v, u32 cnt, u64 *out) {
+  u32 k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= cnt) return;
+  u64 lo = 0, hi = n, key = v[k];
+  while (lo < hi) { u64 mid = (lo + hi) >> 1; if (a[mid] < key) lo = mid + 1; else hi = mid; }
+  out[k] = lo;
+}
+
+int cmsbwt_shard_tails(cmsbwt_ctx *c, uint64_t doc_base, uint32_t *n_tails) {
+  if (!c || !c->have_ms) return fail(c, CMSBWT_E_ARG, "ms_run first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  Timer t(c->st);
+  sort_prepare(c, doc_base);
+  shard_tails_sort(c);
+  c->stats.sort_ms = t.stop();
+  if (n_tails) *n_tails = c->s_Tn;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_buffer(cmsbwt_ctx *c, const char *name, const void **dptr, uint64_t *count) {
+  if (!c || !name || !dptr || !count) return CMSBWT_E_ARG;
+  const void *p = nullptr;
+  u64 n = 0;
+  if (!strcmp(name, "tail_keys")) { p = c->sh_ks.p; n = c->s_Tn; }                 // u32, sorted
+  else if (!strcmp(name, "tail_cls")) { p = c->sh_cs.p; n = c->s_Tn; }            // u32, same order
+  else if (!strcmp(name, "tie_keys")) { p = c->sh_tiekeys.p; n = c->sh_m; }       // u64
+  else if (!strcmp(name, "tile_heads")) { p = c->t_he.p; n = c->sh_he; }          // 16-byte entries
+  else if (!strcmp(name, "tile_ranges")) { p = c->t_re.p; n = c->sh_re; }         // 16-byte entries
+  else if (!strcmp(name, "tile_hoff")) { p = c->t_hoff.p; n = (u64)c->sh_tp * c->sh_world + 1; }   // u32
+  else if (!strcmp(name, "tile_roff")) { p = c->t_roff.p; n = (u64)c->sh_tp * c->sh_world + 1; }   // u32
+  else if (!strcmp(name, "cov_slice")) { p = c->sh_cov.p; n = (u64)c->sh_tp * 256; }               // u32
+  else if (!strcmp(name, "placements")) { p = c->sh_plc.p; n = c->sh_nplc; }      // u64, sorted
+  else if (!strcmp(name, "result")) { p = c->d_out.p; n = c->out_bytes; }         // u8
+  else return fail(c, CMSBWT_E_ARG, "unknown shard buffer");
+  *dptr = p;
+  *count = n;
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_lower_bound(cmsbwt_ctx *c, const char *name, const uint64_t *values, uint32_t count,
+                             uint64_t *out_idx) {
+  if (!c || !name || !values || !out_idx) return CMSBWT_E_ARG;
+  const void *p = nullptr;
+  uint64_t n = 0;
+  int rc = cmsbwt_shard_buffer(c, name, &p, &n);
+  if (rc) return rc;
+  const bool is32 = !strcmp(name, "tail_keys"), is64 = !strcmp(name, "placements");
+  if (!is32 && !is64) return fail(c, CMSBWT_E_ARG, "lower_bound: not a sorted buffer");
+  if (count == 0) return CMSBWT_OK;
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  DBuf v, o;
+  v.alloc((size_t)count * 8, c->st); o.alloc((size_t)count * 8, c->st);
+  CK(cudaMemcpyAsync(v.p, values, (size_t)count * 8, cudaMemcpyHostToDevice, c->st));
+  if (is32) k_lb32<<<(count + 63) / 64, 64, 0, c->st>>>((const u32 *)p, n, v.as<u64>(), count, o.as<u64>());
+  else k_lb64<<<(count + 63) / 64, 64, 0, c->st>>>((const u64 *)p, n, v.as<u64>(), count, o.as<u64>());
+  LAUNCH(c);
+  CK(cudaMemcpyAsync(out_idx, o.p, (size_t)count * 8, cudaMemcpyDeviceToHost, c->st));
+  CK(cudaStreamSynchronize(c->st));
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_rank_owner(cmsbwt_ctx *c, const void *d_keys, const void *d_cls, uint32_t M, uint32_t rank_base,
+                            void *d_rank_out, void *d_tie_out) {
+  if (!c || (M && (!d_keys || !d_cls || !d_rank_out || !d_tie_out))) return fail(c, CMSBWT_E_ARG, "rank_owner");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  shard_rank_owner(c, (const u32 *)d_keys, (const u32 *)d_cls, M, rank_base, (u32 *)d_rank_out, (u8 *)d_tie_out);
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_rank_apply(cmsbwt_ctx *c, const void *d_rank_sorted, const void *d_tie_sorted, uint32_t *m_tied) {
+  if (!c || !c->sh_perm.p) return fail(c, CMSBWT_E_ARG, "shard_tails first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  u32 m = shard_rank_apply(c, (const u32 *)d_rank_sorted, (const u8 *)d_tie_sorted);
+  if (m_tied) *m_tied = m;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_tie_keys(cmsbwt_ctx *c, uint32_t *m) {
+  if (!c || !c->sh_sub.p) return fail(c, CMSBWT_E_ARG, "shard_rank_apply first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  shard_tie_keys(c);
+  if (m) *m = c->sh_m;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_tie_refine(cmsbwt_ctx *c, const void *d_allkeys, uint32_t m_total, uint32_t my_off,
+                            uint32_t *m_tied) {
+  if (!c || !c->sh_sub.p) return fail(c, CMSBWT_E_ARG, "shard_rank_apply first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  u32 m = shard_tie_refine(c, (const u64 *)d_allkeys, m_total, my_off);
+  if (m_tied) *m_tied = m;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_tiles_local(cmsbwt_ctx *c, uint32_t world, uint32_t *tiles_per_rank) {
+  if (!c || !c->s_trank.p || world == 0) return fail(c, CMSBWT_E_ARG, "shard ranking first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  Timer t(c->st);
+  sort_kappa(c);
+  shard_tiles_local(c, world);
+  c->stats.sort_ms += t.stop();
+  if (tiles_per_rank) *tiles_per_rank = c->sh_tp;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_tiles_merge(cmsbwt_ctx *c, uint32_t world, uint32_t rank, const void *d_he, const void *d_re,
+                             const void *d_hoffs, const void *d_roffs, const uint64_t *he_slab,
+                             const uint64_t *re_slab, uint64_t ndocs_total, uint32_t *max_entries) {
+  if (!c || world != c->sh_world || rank >= world || !d_hoffs || !d_roffs || !he_slab || !re_slab)
+    return fail(c, CMSBWT_E_ARG, "tiles_merge");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  Timer t(c->st);
+  u32 me = shard_tiles_merge(c, world, rank, d_he, d_re, (const u32 *)d_hoffs, (const u32 *)d_roffs, he_slab,
+                             re_slab, ndocs_total);
+  c->stats.sort_ms += t.stop();
+  if (max_entries) *max_entries = me;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_emit(cmsbwt_ctx *c, const void *d_cov_full, uint64_t N_total, uint32_t world, uint32_t rank,
+                      uint64_t doc_base, uint64_t *out_begin, uint64_t *out_len, uint64_t *chunk_bytes) {
+  if (!c || !d_cov_full || world != c->sh_world || rank != c->sh_rank) return fail(c, CMSBWT_E_ARG, "shard_emit");
+  if (c->tile_maxent > 12288) return fail(c, CMSBWT_E_LIMIT, "a tile holds more entries than shared memory");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  Timer t(c->st);
+  shard_emit(c, (const u32 *)d_cov_full, N_total, world, rank, doc_base);
+  c->stats.emit_ms = t.stop();
+  if (out_begin) *out_begin = c->sh_obeg;
+  if (out_len) *out_len = c->sh_olen;
+  if (chunk_bytes) *chunk_bytes = c->sh_chunk;
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_apply(cmsbwt_ctx *c, const void *d_plc, uint64_t count) {
+  if (!c || !c->sh_base.p || (count && !d_plc)) return fail(c, CMSBWT_E_ARG, "shard_emit first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  Timer t(c->st);
+  shard_apply(c, (const u64 *)d_plc, count);
+  c->stats.emit_ms += t.stop();
+  GUARD_END(c)
+  return CMSBWT_OK;
 }
 
 }  // extern "C"

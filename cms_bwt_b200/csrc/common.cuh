@@ -29,9 +29,11 @@ struct CudaErr { cudaError_t e; const char *what; };
 
 struct CmsErr { int code; std::string msg; };
 
-// Caching device allocator: blocks are recycled by size class inside one process, so a repeated
-// job of the same shape performs no cudaMalloc / cudaFree at all.  All work of a context runs on
-// one stream, so handing a released block to a later kernel is ordered correctly.
+// Caching device allocator, one per context: blocks are recycled by size class, so a repeated job
+// of the same shape performs no cudaMalloc / cudaFree at all.  All work of a context runs on one
+// stream, so handing a released block to a later kernel is ordered correctly; every API entry
+// makes its context's cache the calling thread's current one (contexts may be driven from
+// different host threads).
 struct DevCache {
   std::vector<std::pair<size_t, void *>> free_blocks;
   size_t held = 0;
@@ -64,26 +66,31 @@ struct DevCache {
   }
   void put(void *p, size_t b) { free_blocks.push_back({round(b), p}); }
   void trim() {
+    if (free_blocks.empty()) return;
     cudaDeviceSynchronize();
     for (auto &fb : free_blocks) { cudaFree(fb.second); held -= fb.first; }
     free_blocks.clear();
   }
+  ~DevCache() { trim(); }
 };
-DevCache &dev_cache();
+DevCache *&current_cache();        // thread-local
 
 struct DBuf {
   void *p = nullptr;
   size_t bytes = 0;
+  DevCache *owner = nullptr;
   void alloc(size_t b, cudaStream_t) {
     release();
     bytes = b;
-    p = dev_cache().get(b ? b : 16);
+    owner = current_cache();
+    p = owner->get(b ? b : 16);
   }
   void release() {
-    if (p) dev_cache().put(p, bytes ? bytes : 16);
+    if (p) owner->put(p, bytes ? bytes : 16);
     p = nullptr;
     bytes = 0;
   }
+  void swap(DBuf &o) { std::swap(p, o.p); std::swap(bytes, o.bytes); std::swap(owner, o.owner); }
   template <class T> T *as() const { return (T *)p; }
   ~DBuf() { release(); }
   DBuf() {}
@@ -103,6 +110,7 @@ struct Index {             // device-resident reference index
 };
 
 struct cmsbwt_ctx {
+  DevCache cache;            // first member: destroyed after every DBuf below has been returned to it
   int dev = 0;
   cudaStream_t st = 0;
   std::string err;
@@ -138,6 +146,16 @@ struct cmsbwt_ctx {
   bool light = false;
   DBuf t_hoff, t_roff, t_he, t_re, h_sexcl;
   u32 tile_maxent = 0;
+  // stage 2 working set (kept in the context so that the multi-GPU shard calls can interleave
+  // collectives between the phases)
+  DBuf s_tincl, s_sexcl, s_label, s_next, s_tid, s_key32, s_trank, s_kappa, s_nitems;
+  u32 s_Tn = 0;
+  int s_key_bits = 32;
+  // shard state (shard.cu / tailrank.cu): locally sorted tail keys, tied subset, merged tiles
+  DBuf sh_ks, sh_cs, sh_perm, sh_sub, sh_tiekeys, sh_cov, sh_plc, sh_base;
+  u32 sh_m = 0, sh_round = 0;
+  u32 sh_world = 1, sh_rank = 0, sh_tp = 0;      // tiles per rank
+  u64 sh_he = 0, sh_re = 0, sh_nplc = 0, sh_obeg = 0, sh_olen = 0, sh_chunk = 0, sh_Ntotal = 0;
   // stage 3
   DBuf d_out, d_rle;
   u64 out_bytes = 0;
@@ -162,9 +180,26 @@ bool ms_stage_fast(cmsbwt_ctx *c);
 void pack_2bit(cmsbwt_ctx *c, const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps, u64 sepcap,
                unsigned long long *nsep, u32 *flags);
 void sort_stage(cmsbwt_ctx *c);
+void sort_prepare(cmsbwt_ctx *c, u64 doc_base);
+void sort_kappa(cmsbwt_ctx *c);
 void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_bits, u32 *nexth, u32 Tn,
                u32 *trank);
+void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32, DBuf &id, int key_bits,
+                  u32 *nexth, u32 Tn, u32 *trank, u32 rank_base, bool cls_only, u8 *tie_by_id);
 bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl);
+// multi-GPU shard steps (tailrank.cu, tiles.cu, emit.cu); the collectives between them are the
+// host layer's (cms_bwt_b200/multi.py)
+void shard_tails_sort(cmsbwt_ctx *c);
+void shard_rank_owner(cmsbwt_ctx *c, const u32 *keys, const u32 *cls, u32 M, u32 rank_base, u32 *rank_out,
+                      u8 *tie_out);
+u32 shard_rank_apply(cmsbwt_ctx *c, const u32 *rk_sorted, const u8 *tie_sorted);
+void shard_tie_keys(cmsbwt_ctx *c);
+u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off);
+void shard_tiles_local(cmsbwt_ctx *c, u32 world);
+u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const void *re, const u32 *hoffs,
+                      const u32 *roffs, const u64 *he_slab, const u64 *re_slab, u64 ndocs_total);
+void shard_emit(cmsbwt_ctx *c, const u32 *cov_full, u64 N_total, u32 world, u32 rank, u64 doc_base);
+void shard_apply(cmsbwt_ctx *c, const u64 *plc, u64 cnt);
 void emit_stage(cmsbwt_ctx *c, int mode);
 
 // ---------------------------------------------------------------------------------------------

@@ -25,10 +25,11 @@ __device__ __forceinline__ u32 run_of(const u64 *base, u32 lo, u32 hi, u64 o) {
 }
 
 // merge-path style partition: the run that holds the first byte of every output block
-__global__ void k_fill_part(const u64 *base, u32 n, u64 N, u64 nblocks, u32 *bstart) {
+// (blk0: first output block of this device; bstart is indexed from it)
+__global__ void k_fill_part(const u64 *base, u32 n, u64 N, u64 nblocks, u64 blk0, u32 *bstart) {
   u64 b = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   if (b > nblocks) return;
-  u64 o = b * FILL_BYTES;
+  u64 o = (b + blk0) * FILL_BYTES;
   bstart[b] = o < N ? run_of(base, 0, n, o) : n - 1;
 }
 
@@ -36,15 +37,16 @@ __global__ void k_fill_part(const u64 *base, u32 n, u64 N, u64 nblocks, u32 *bst
 // A block owns FILL_BYTES of output; the run covering every 16-byte vector comes from a max-scan
 // over "last run starting in this vector" marks, vectors inside one run are splatted.
 __global__ void __launch_bounds__(FILL_THREADS) k_fill(const u64 *base, const u8 *rbwt, const u32 *bstart,
-                                                       u32 n, u64 N, u8 *out) {
+                                                       u32 n, u64 N, u64 blk0, u8 *out) {
   __shared__ u64 sb[FILL_SMEM_RUNS + 2];
   __shared__ u8 ssym[FILL_SMEM_RUNS + 2];
   __shared__ u32 s_m[FILL_VECS];
   typedef cub::BlockScan<u32, FILL_THREADS> BS;
   __shared__ typename BS::TempStorage ts;
   const u32 tid = threadIdx.x;
-  const u64 o0 = (u64)blockIdx.x * FILL_BYTES;
+  const u64 o0 = ((u64)blockIdx.x + blk0) * FILL_BYTES;
   const u64 o1 = min(N, o0 + FILL_BYTES);
+  out -= blk0 * FILL_BYTES;                   // out points at this device's first byte
   const u32 r0 = bstart[blockIdx.x], r1 = bstart[blockIdx.x + 1];
   const u32 nr = r1 - r0 + 1;                 // runs r0..r1 intersect this block
   const bool use_s = nr <= FILL_SMEM_RUNS;
@@ -201,7 +203,7 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   c->launches += 2;
   const u64 nblocks = (N + FILL_BYTES - 1) / FILL_BYTES;
   bstart.alloc((nblocks + 1) * 4, st);
-  k_fill_part<<<(u32)((nblocks + 1 + B - 1) / B), B, 0, st>>>(base.as<u64>(), n, N, nblocks, bstart.as<u32>());
+  k_fill_part<<<(u32)((nblocks + 1 + B - 1) / B), B, 0, st>>>(base.as<u64>(), n, N, nblocks, 0, bstart.as<u32>());
   LAUNCH(c);
   u64 total = 0;
   CK(cudaMemcpyAsync(&total, base.as<u64>() + n, 8, cudaMemcpyDeviceToHost, st));
@@ -214,7 +216,7 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   }
   c->d_out.alloc(N + CMS_PAD, st);
   u8 *out = c->d_out.as<u8>();
-  k_fill<<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), c->ix.rbwt, bstart.as<u32>(), n, N, out);
+  k_fill<<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), c->ix.rbwt, bstart.as<u32>(), n, N, 0, out);
   LAUNCH(c);
   if (c->light) {
     tiles_place_heads(c, base.as<u64>(), out);
@@ -252,4 +254,81 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
     c->stats.n_runs = R;
   }
   CK(cudaStreamSynchronize(st));
+}
+
+// ================================================================================================
+// Multi-GPU emit: every device gets the all-gathered bucket sizes, computes the
+// (replicated, n-sized) offsets, expands the reference symbols of ITS contiguous output range and
+// produces the head placements of ITS tile range sorted by output offset (exchanged by the host
+// layer, then stored with shard_apply).
+void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base);
+
+void shard_emit(cmsbwt_ctx *c, const u32 *cov_full, u64 N_total, u32 world, u32 rank, u64 doc_base) {
+  cudaStream_t st = c->st;
+  const u32 n = c->ix.n;
+  const int B = 256;
+  DBuf cnt, tmp, bstart;
+  cnt.alloc(((size_t)n + 1) * 4, st);
+  c->sh_base.alloc(((size_t)n + 2) * 8, st);
+  u64 *base = c->sh_base.as<u64>();
+  size_t tb = 0;
+  EXSUM64(nullptr, tb, cnt.as<u32>(), base, (int)(n + 1), st);
+  tmp.alloc(tb, st);
+  CK(cudaMemsetAsync(cnt.as<u32>() + n, 0, 4, st));
+  k_cnt_sa<<<(n + B - 1) / B, B, 0, st>>>((const i32 *)cov_full, c->ix.sa, n, cnt.as<u32>());
+  CK(EXSUM64(tmp.p, tb, cnt.as<u32>(), base, (int)(n + 1), st));
+  CK(cudaMemsetAsync(base + (n + 1), 0xFF, 8, st));
+  c->launches += 2;
+  u64 total = 0;
+  CK(cudaMemcpyAsync(&total, base + n, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (total != N_total) {
+    char buf[128];
+    snprintf(buf, sizeof buf, "coverage total %llu != N %llu", (unsigned long long)total,
+             (unsigned long long)N_total);
+    throw CmsErr{CMSBWT_E_INTERNAL, buf};
+  }
+  c->sh_Ntotal = N_total;
+  const u64 nblocks = (N_total + FILL_BYTES - 1) / FILL_BYTES;
+  const u64 bp = (nblocks + world - 1) / world;
+  const u64 b0 = min(nblocks, (u64)rank * bp), b1 = min(nblocks, b0 + bp);
+  c->sh_chunk = bp * FILL_BYTES;
+  c->sh_obeg = b0 * FILL_BYTES;
+  c->sh_olen = min(N_total, b1 * FILL_BYTES) - min(N_total, c->sh_obeg);
+  const u64 nb = b1 - b0;
+  c->d_out.alloc(c->sh_olen + CMS_PAD, st);
+  if (nb) {
+    bstart.alloc((nb + 1) * 4, st);
+    k_fill_part<<<(u32)((nb + 1 + B - 1) / B), B, 0, st>>>(base, n, N_total, nb, b0, bstart.as<u32>());
+    k_fill<<<(u32)nb, FILL_THREADS, 0, st>>>(base, c->ix.rbwt, bstart.as<u32>(), n, N_total, b0, c->d_out.as<u8>());
+    c->launches += 2;
+  }
+  CK(cudaGetLastError());
+  shard_place(c, base, doc_base);
+  c->out_mode = CMSBWT_MODE_PLAIN;
+  c->out_bytes = c->sh_olen;
+}
+
+__global__ void k_sh_apply(const u64 *plc, u64 cnt, u64 obeg, u64 olen, u8 *out, u32 *bad) {
+  u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= cnt) return;
+  u64 p = plc[j], off = (p >> 8) - obeg;
+  if (off < olen) out[off] = (u8)(p & 0xFF); else *bad = 1;
+}
+
+void shard_apply(cmsbwt_ctx *c, const u64 *plc, u64 cnt) {
+  cudaStream_t st = c->st;
+  DBuf bad;
+  bad.alloc(4, st);
+  CK(cudaMemsetAsync(bad.p, 0, 4, st));
+  if (cnt) {
+    k_sh_apply<<<(u32)((cnt + 255) / 256), 256, 0, st>>>(plc, cnt, c->sh_obeg, c->sh_olen, c->d_out.as<u8>(),
+                                                        bad.as<u32>());
+    LAUNCH(c);
+  }
+  u32 hb = 0;
+  CK(cudaMemcpyAsync(&hb, bad.p, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (hb) throw CmsErr{CMSBWT_E_INTERNAL, "a head placement fell outside this device's output range"};
+  c->sh_base.release(); c->sh_plc.release(); c->t_he.release(); c->t_re.release();
 }

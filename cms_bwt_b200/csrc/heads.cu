@@ -45,8 +45,8 @@ __global__ void k_tail_first(const u32 *tflag, const u32 *tail_incl, u64 H, u32 
 // label + next pointer of every tail
 __global__ void k_tail_label(const u64 *g, const u32 *pos, const u32 *len, const u16 *cs,
                              const u32 *tail_incl, const u32 *sent_excl, const u32 *tail_first,
-                             const u32 *isa, u64 H, u32 Tn, int qb, u64 *label, u32 *next, u32 *tid,
-                             u32 *key32) {
+                             const u32 *isa, u64 H, u32 Tn, int qb, u32 doc_base, u64 *label, u32 *next,
+                             u32 *tid, u32 *key32) {
   u32 t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= Tn) return;
   u32 f = tail_first[t];
@@ -64,7 +64,7 @@ __global__ void k_tail_label(const u64 *g, const u32 *pos, const u32 *len, const
   // key32 = ISA rank, then qb bits of the cls order (weakly order preserving; tailrank.cu)
   const u32 Q = 1u << qb, half = Q >> 1;
   if (len[j] == 0) {                   // the suffix at g_end is a document terminator
-    u32 d = sent_excl[j];
+    u32 d = doc_base + sent_excl[j];
     label[t] = (u64)d;
     next[t] = t;
     key32[t] = d < Q - 1 ? d : Q - 1;
@@ -196,7 +196,9 @@ struct Tmp {                      // growable CUB scratch
   void need(size_t bytes, cudaStream_t st) { if (bytes > b.bytes) b.alloc(bytes, st); }
 };
 
-void sort_stage(cmsbwt_ctx *c) {
+// link + tail labels (everything here is local to a shard of whole documents: phrases, tails and
+// next-tail pointers never leave a document).  doc_base = documents on lower shards.
+void sort_prepare(cmsbwt_ctx *c, u64 doc_base) {
   cudaStream_t st = c->st;
   const u64 H = c->H;
   const u32 n = c->ix.n;
@@ -207,79 +209,102 @@ void sort_stage(cmsbwt_ctx *c) {
   const u16 *cs = c->h_cs.as<u16>();
   Tmp tmp;
   size_t tb;
-  // ---- link ----
   c->h_toNext.alloc(H * 4, st);
   c->light = false;
   c->stats.light_tiles = 0;
   c->stats.pair_tests = 0;
-  DBuf tflag, sflag, tincl, sexcl;
-  tflag.alloc(H * 4, st); sflag.alloc(H * 4, st); tincl.alloc(H * 4, st); sexcl.alloc(H * 4, st);
+  DBuf tflag, sflag, tfirst;
+  tflag.alloc(H * 4, st); sflag.alloc(H * 4, st); c->s_tincl.alloc(H * 4, st); c->s_sexcl.alloc(H * 4, st);
   k_link<<<gH, B, 0, st>>>(g, pos, len, H, c->h_toNext.as<u32>(), nullptr, tflag.as<u32>(),
                            sflag.as<u32>());
   LAUNCH(c);
-  tb = 0; cub::DeviceScan::InclusiveSum(nullptr, tb, tflag.as<u32>(), tincl.as<u32>(), (int)H, st);
+  tb = 0; cub::DeviceScan::InclusiveSum(nullptr, tb, tflag.as<u32>(), c->s_tincl.as<u32>(), (int)H, st);
   tmp.need(tb, st);
-  CK(cub::DeviceScan::InclusiveSum(tmp.b.p, tb, tflag.as<u32>(), tincl.as<u32>(), (int)H, st));
-  tb = 0; cub::DeviceScan::ExclusiveSum(nullptr, tb, sflag.as<u32>(), sexcl.as<u32>(), (int)H, st);
+  CK(cub::DeviceScan::InclusiveSum(tmp.b.p, tb, tflag.as<u32>(), c->s_tincl.as<u32>(), (int)H, st));
+  tb = 0; cub::DeviceScan::ExclusiveSum(nullptr, tb, sflag.as<u32>(), c->s_sexcl.as<u32>(), (int)H, st);
   tmp.need(tb, st);
-  CK(cub::DeviceScan::ExclusiveSum(tmp.b.p, tb, sflag.as<u32>(), sexcl.as<u32>(), (int)H, st));
+  CK(cub::DeviceScan::ExclusiveSum(tmp.b.p, tb, sflag.as<u32>(), c->s_sexcl.as<u32>(), (int)H, st));
   c->launches += 2;
   u32 Tn = 0, lastS = 0, lastF = 0;
-  CK(cudaMemcpyAsync(&Tn, tincl.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(&lastS, sexcl.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&Tn, c->s_tincl.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&lastS, c->s_sexcl.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(&lastF, sflag.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   c->stats.n_docs = (u64)lastS + lastF;
   c->stats.n_tails = Tn;
-  // ---- tails ----
+  c->s_Tn = Tn;
   const u32 gT = (Tn + B - 1) / B;
-  DBuf tfirst, label, label2, next, next2, tid, tid2, trank, fl, dense;
-  tfirst.alloc((size_t)Tn * 4, st); label.alloc((size_t)Tn * 8, st);
-  next.alloc((size_t)Tn * 4, st); tid.alloc((size_t)Tn * 4, st);
-  trank.alloc((size_t)Tn * 4, st);
-  k_tail_first<<<gH, B, 0, st>>>(tflag.as<u32>(), tincl.as<u32>(), H, tfirst.as<u32>());
+  tfirst.alloc((size_t)Tn * 4, st); c->s_label.alloc((size_t)Tn * 8, st);
+  c->s_next.alloc((size_t)Tn * 4, st); c->s_tid.alloc((size_t)Tn * 4, st);
+  c->s_trank.alloc((size_t)Tn * 4, st);
+  k_tail_first<<<gH, B, 0, st>>>(tflag.as<u32>(), c->s_tincl.as<u32>(), H, tfirst.as<u32>());
   int isa_bits = 1;
   while (isa_bits < 32 && (1ull << isa_bits) < (u64)n) isa_bits++;
   const int qb = 32 - isa_bits < 6 ? 32 - isa_bits : 6;
-  DBuf key32;
-  key32.alloc((size_t)Tn * 4, st);
-  k_tail_label<<<gT, B, 0, st>>>(g, pos, len, cs, tincl.as<u32>(), sexcl.as<u32>(), tfirst.as<u32>(),
-                                 c->ix.isa, H, Tn, qb, label.as<u64>(), next.as<u32>(), tid.as<u32>(),
-                                 key32.as<u32>());
+  c->s_key_bits = isa_bits + qb;
+  c->s_key32.alloc((size_t)Tn * 4, st);
+  k_tail_label<<<gT, B, 0, st>>>(g, pos, len, cs, c->s_tincl.as<u32>(), c->s_sexcl.as<u32>(), tfirst.as<u32>(),
+                                 c->ix.isa, H, Tn, qb, (u32)doc_base, c->s_label.as<u64>(), c->s_next.as<u32>(),
+                                 c->s_tid.as<u32>(), c->s_key32.as<u32>());
   c->launches += 2;
-  tail_rank(c, label.as<u64>(), key32, tid, isa_bits + qb, next.as<u32>(), Tn, trank.as<u32>());
-  // ---- kappa + items ----
-  DBuf kappa, nitems, ioff;
-  kappa.alloc(H * 8, st); nitems.alloc((H + 1) * 4, st); ioff.alloc((H + 1) * 8, st);
-  CK(cudaMemsetAsync(nitems.p, 0, (H + 1) * 4, st));
-  k_kappa_count<<<gH, B, 0, st>>>(pos, len, cs, c->h_toNext.as<u32>(), tincl.as<u32>(),
-                                  trank.as<u32>(), H, kappa.as<u64>(), nitems.as<u32>());
-  tb = 0; EXSUM64(nullptr, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st);
-  tmp.need(tb, st);
-  CK(EXSUM64(tmp.b.p, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st));
-  c->launches += 3;
-  u64 I = 0;
-  CK(cudaMemcpyAsync(&I, ioff.as<u64>() + H, 8, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  c->stats.n_items = I;
-  // free what is no longer needed before the big item arrays
-  tfirst.release(); label.release(); label2.release(); next.release(); next2.release();
-  tid.release(); tid2.release(); fl.release(); dense.release(); tflag.release(); sflag.release();
+  CK(cudaGetLastError());
+}
+
+// kappa per head from the tail ranks (local)
+void sort_kappa(cmsbwt_ctx *c) {
+  cudaStream_t st = c->st;
+  const u64 H = c->H;
+  const int B = 256;
+  const u32 gH = (u32)((H + B - 1) / B);
+  c->s_kappa.alloc(H * 8, st); c->s_nitems.alloc((H + 1) * 4, st);
+  CK(cudaMemsetAsync(c->s_nitems.p, 0, (H + 1) * 4, st));
+  k_kappa_count<<<gH, B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_toNext.as<u32>(),
+                                  c->s_tincl.as<u32>(), c->s_trank.as<u32>(), H, c->s_kappa.as<u64>(),
+                                  c->s_nitems.as<u32>());
+  LAUNCH(c);
+  c->s_label.release(); c->s_next.release(); c->s_tid.release(); c->s_key32.release();
+  CK(cudaGetLastError());
+}
+
+void sort_stage(cmsbwt_ctx *c) {
+  cudaStream_t st = c->st;
+  const u64 H = c->H;
+  const u32 n = c->ix.n;
+  const int B = 256;
+  const u32 gH = (u32)((H + B - 1) / B);
+  const u32 *pos = c->h_pos.as<u32>();
+  Tmp tmp;
+  size_t tb;
+  sort_prepare(c, 0);
+  const u32 Tn = c->s_Tn;
+  tail_rank(c, c->s_label.as<u64>(), c->s_key32, c->s_tid, c->s_key_bits, c->s_next.as<u32>(), Tn,
+            c->s_trank.as<u32>());
+  sort_kappa(c);
+  DBuf &kappa = c->s_kappa, &nitems = c->s_nitems, &sexcl = c->s_sexcl;
   // ---- brute-force tile path (tiles.cu) unless the collection is too deep for it ----
   if (c->tile_budget > 0 && tiles_build(c, kappa.as<u64>(), sexcl)) {
     c->stats.light_tiles = 1;
+    c->s_kappa.release(); c->s_nitems.release(); c->s_tincl.release(); c->s_trank.release();
     CK(cudaStreamSynchronize(st));
     return;
   }
   // ---- sort-based sweep ----
+  DBuf ioff;
+  ioff.alloc((H + 1) * 8, st);
+  tb = 0; EXSUM64(nullptr, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st);
+  tmp.need(tb, st);
+  CK(EXSUM64(tmp.b.p, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st));
+  c->launches += 2;
+  u64 I = 0;
+  CK(cudaMemcpyAsync(&I, ioff.as<u64>() + H, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
   if (I >= 0x7FFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^31 tile items on one device"};
   c->stats.n_items = I;
   c->d_cov.alloc(((size_t)n + 1) * 4, st);
   CK(cudaMemsetAsync(c->d_cov.p, 0, ((size_t)n + 1) * 4, st));
   k_cov_diff<<<gH, B, 0, st>>>(pos, c->h_toNext.as<u32>(), H, c->d_cov.as<i32>());
   LAUNCH(c);
-  tfirst.release(); label.release(); label2.release(); next.release(); next2.release();
-  tid.release(); tid2.release(); fl.release(); dense.release(); tflag.release(); sflag.release();
+  c->s_tincl.release(); c->s_trank.release();
   DBuf it_tr, it_tr2, it_key, it_key2, it_pay, idx, idx2;
   it_tr.alloc(I * 4, st); it_tr2.alloc(I * 4, st); it_key.alloc(I * 8, st); it_key2.alloc(I * 8, st);
   it_pay.alloc(I * 8, st); idx.alloc(I * 4, st); idx2.alloc(I * 4, st);
@@ -321,4 +346,5 @@ void sort_stage(cmsbwt_ctx *c) {
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(st));
   }
+  c->s_kappa.release(); c->s_nitems.release(); c->s_sexcl.release();
 }

@@ -172,8 +172,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     tmp.alloc(tb, st);
     CK(cub::DeviceRadixSort::SortKeys(tmp.p, tb, c->d_seps.as<u64>(), sorted.as<u64>(), (int)nseps, 0, bits, st));
     CK(cudaMemsetAsync(sorted.as<u64>() + nseps, 0xFF, 8, st));
-    std::swap(c->d_seps.p, sorted.p);
-    std::swap(c->d_seps.bytes, sorted.bytes);
+    c->d_seps.swap(sorted);
     c->launches += 2;
   }
   DBuf wsep, wfirst, wcnt, wfp, wlp, wadj, woff, counter, nbused;

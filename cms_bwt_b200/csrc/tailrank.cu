@@ -35,18 +35,23 @@ __global__ void k_tr_gs32(const u32 *key, u32 n, u32 *gs) {
   gs[j] = (j == 0 || key[j] != key[j - 1]) ? j : 0;
 }
 // rank[id] = group start; tie flag = group has more than one member
-__global__ void k_tr_rank0(const u32 *key, const u32 *id, const u32 *gs, u32 n, u32 *rank, u8 *tie) {
+__global__ void k_tr_rank0(const u32 *key, const u32 *id, const u32 *gs, u32 n, u32 base, u32 *rank, u8 *tie) {
   u32 j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  rank[id[j]] = gs[j];
+  rank[id[j]] = base + gs[j];
   tie[j] = (gs[j] != j) || (j + 1 < n && key[j + 1] == key[j]);
 }
 // subset keys: (current rank, secondary) with secondary = cls (round 0) or rank of the far tail
-__global__ void k_tr_key_cls(const u32 *sub, u32 m, const u32 *rank, const u64 *label, u64 *key) {
+__global__ void k_tr_key_cls(const u32 *sub, u32 m, const u32 *rank, const u64 *label, const u32 *cls32,
+                             u64 *key) {
   u32 j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= m) return;
   u32 t = sub[j];
-  key[j] = ((u64)rank[t] << 32) | (u32)label[t];
+  key[j] = ((u64)rank[t] << 32) | (cls32 ? cls32[t] : (u32)label[t]);
+}
+__global__ void k_tr_mark(const u32 *sub, u32 m, u8 *flag) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < m) flag[sub[j]] = 1;
 }
 __global__ void k_tr_key_next(const u32 *sub, u32 m, const u32 *rank, const u32 *nexth, u64 *key) {
   u32 j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -102,6 +107,14 @@ static u32 select_tied(Scratch &tmp, const u32 *ids, const u8 *tie, u32 n, u32 *
 // nexth[Tn] (overwritten) -> trank[Tn]: distinct, order-preserving ranks
 void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_bits, u32 *nexth, u32 Tn,
                u32 *trank) {
+  tail_rank_ex(c, label, nullptr, key32, id, key_bits, nexth, Tn, trank, 0, false, nullptr);
+}
+
+// General form.  cls32 != NULL: the cls words come from there instead of the labels.  rank_base is
+// added to every rank.  cls_only: stop after the (rank, cls) round (the owner side of the multi-GPU
+// ranking); tie_by_id[t] (zeroed here) is then set for the tails that are still tied.
+void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32, DBuf &id, int key_bits,
+                  u32 *nexth, u32 Tn, u32 *trank, u32 rank_base, bool cls_only, u8 *tie_by_id) {
   cudaStream_t st = c->st;
   const int B = 256;
   const u32 gT = (Tn + B - 1) / B;
@@ -111,6 +124,7 @@ void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_b
   ids.alloc((size_t)Tn * 4, st); gs.alloc((size_t)Tn * 4, st); tie.alloc((size_t)Tn, st); cnt.alloc(4, st);
   const int bits = key_bits > 32 ? 32 : key_bits;
   size_t tb = 0;
+  if (tie_by_id) CK(cudaMemsetAsync(tie_by_id, 0, Tn, st));
   cub::DeviceRadixSort::SortPairs(nullptr, tb, key32.as<u32>(), key32s.as<u32>(), id.as<u32>(), ids.as<u32>(),
                                   (int)Tn, 0, bits, st);
   tmp.need(tb, st);
@@ -118,7 +132,7 @@ void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_b
                                      ids.as<u32>(), (int)Tn, 0, bits, st));
   k_tr_gs32<<<gT, B, 0, st>>>(key32s.as<u32>(), Tn, gs.as<u32>());
   max_scan(tmp, gs.as<u32>(), Tn, st);
-  k_tr_rank0<<<gT, B, 0, st>>>(key32s.as<u32>(), ids.as<u32>(), gs.as<u32>(), Tn, trank, tie.as<u8>());
+  k_tr_rank0<<<gT, B, 0, st>>>(key32s.as<u32>(), ids.as<u32>(), gs.as<u32>(), Tn, rank_base, trank, tie.as<u8>());
   c->launches += 8;
   // subset of tied tails (reuses id as the compacted list)
   u32 m = select_tied(tmp, ids.as<u32>(), tie.as<u8>(), Tn, id.as<u32>(), cnt, st);
@@ -135,7 +149,7 @@ void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_b
     bool first = true;
     while (m) {
       const u32 gM = (m + B - 1) / B;
-      if (first) k_tr_key_cls<<<gM, B, 0, st>>>(sub, m, trank, label, key.as<u64>());
+      if (first) k_tr_key_cls<<<gM, B, 0, st>>>(sub, m, trank, label, cls32, key.as<u64>());
       else k_tr_key_next<<<gM, B, 0, st>>>(sub, m, trank, nexth, key.as<u64>());
       tb = 0;
       cub::DeviceRadixSort::SortPairs(nullptr, tb, key.as<u64>(), keys.as<u64>(), sub, subs, (int)m, 0,
@@ -149,6 +163,10 @@ void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_b
       k_tr_refine<<<gM, B, 0, st>>>(keys.as<u64>(), subs, grp.as<u32>(), sg.as<u32>(), m, trank, tie.as<u8>());
       c->launches += 12;
       u32 m2 = select_tied(tmp, subs, tie.as<u8>(), m, sub, cnt, st);
+      if (cls_only) {
+        if (tie_by_id && m2) { k_tr_mark<<<(m2 + B - 1) / B, B, 0, st>>>(sub, m2, tie_by_id); LAUNCH(c); }
+        break;
+      }
       if (m2 && !first) {             // next round looks twice as far
         const u32 g2 = (m2 + B - 1) / B;
         k_tr_jump<<<g2, B, 0, st>>>(sub, m2, nexth, jt.as<u32>());
@@ -163,4 +181,152 @@ void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_b
   }
   c->stats.rank_rounds = rounds;
   CK(cudaGetLastError());
+}
+
+// ================================================================================================
+// Multi-GPU ranking (SURVEY.md 8e "global head order").  Tails are range-partitioned by their
+// 32-bit key; the owner of a key range ranks what it receives (radix sort + the (rank, cls) round)
+// and sends ranks and tie flags back; the tails that are still tied are refined by every rank on the
+// all-gathered (rank, rank[next^(2^h)]) keys of the tied subset -- the same rounds as above, with
+// the collectives (driven by the host layer, cms_bwt_b200/multi.py) between the calls.
+__global__ void k_sh_gather_cls(const u32 *perm, const u64 *label, u32 n, u32 *cs) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) cs[j] = (u32)label[perm[j]];
+}
+__global__ void k_sh_iota(u32 *a, u32 n) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) a[j] = j;
+}
+__global__ void k_sh_unperm(const u32 *perm, const u32 *rk, u32 n, u32 *trank) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) trank[perm[j]] = rk[j];
+}
+__global__ void k_sh_refine_scatter(const u64 *key, const u32 *id, const u32 *grp, const u32 *sg, u32 m,
+                                    u32 *nr, u8 *nt) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m) return;
+  u32 o = id[j];
+  nr[o] = (u32)(key[j] >> 32) + (sg[j] - grp[j]);
+  nt[o] = (sg[j] != j) || (j + 1 < m && key[j + 1] == key[j]);
+}
+__global__ void k_sh_apply_own(const u32 *sub, u32 m, const u32 *nr, u32 *trank) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < m) trank[sub[j]] = nr[j];
+}
+
+// local sort of the shard's tails by key: sh_ks (sorted keys), sh_perm, sh_cs (cls in that order)
+void shard_tails_sort(cmsbwt_ctx *c) {
+  cudaStream_t st = c->st;
+  const u32 Tn = c->s_Tn;
+  const int B = 256;
+  const u32 gT = (Tn + B - 1) / B;
+  Scratch tmp;
+  c->sh_ks.alloc((size_t)Tn * 4 + 16, st); c->sh_perm.alloc((size_t)Tn * 4 + 16, st);
+  c->sh_cs.alloc((size_t)Tn * 4 + 16, st);
+  const int bits = c->s_key_bits > 32 ? 32 : c->s_key_bits;
+  size_t tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, c->s_key32.as<u32>(), c->sh_ks.as<u32>(), c->s_tid.as<u32>(),
+                                  c->sh_perm.as<u32>(), (int)Tn, 0, bits, st);
+  tmp.need(tb, st);
+  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, c->s_key32.as<u32>(), c->sh_ks.as<u32>(), c->s_tid.as<u32>(),
+                                     c->sh_perm.as<u32>(), (int)Tn, 0, bits, st));
+  k_sh_gather_cls<<<gT, B, 0, st>>>(c->sh_perm.as<u32>(), c->s_label.as<u64>(), Tn, c->sh_cs.as<u32>());
+  c->launches += 6;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+}
+
+// owner side: M received (key, cls) pairs -> rank_out[M] (rank_base + order), tie_out[M]
+void shard_rank_owner(cmsbwt_ctx *c, const u32 *keys, const u32 *cls, u32 M, u32 rank_base, u32 *rank_out,
+                      u8 *tie_out) {
+  cudaStream_t st = c->st;
+  if (M == 0) return;
+  DBuf key32, id;
+  key32.alloc((size_t)M * 4, st); id.alloc((size_t)M * 4, st);
+  CK(cudaMemcpyAsync(key32.p, keys, (size_t)M * 4, cudaMemcpyDeviceToDevice, st));
+  k_sh_iota<<<(M + 255) / 256, 256, 0, st>>>(id.as<u32>(), M);
+  LAUNCH(c);
+  tail_rank_ex(c, nullptr, cls, key32, id, c->s_key_bits, nullptr, M, rank_out, rank_base, true, tie_out);
+  CK(cudaStreamSynchronize(st));
+}
+
+// origin side: ranks and tie flags came back in sh_ks order -> trank, tied subset; returns its size
+u32 shard_rank_apply(cmsbwt_ctx *c, const u32 *rk_sorted, const u8 *tie_sorted) {
+  cudaStream_t st = c->st;
+  const u32 Tn = c->s_Tn;
+  Scratch tmp;
+  DBuf cnt;
+  cnt.alloc(4, st);
+  k_sh_unperm<<<(Tn + 255) / 256, 256, 0, st>>>(c->sh_perm.as<u32>(), rk_sorted, Tn, c->s_trank.as<u32>());
+  LAUNCH(c);
+  c->sh_sub.alloc((size_t)Tn * 4 + 16, st);
+  c->sh_m = select_tied(tmp, c->sh_perm.as<u32>(), tie_sorted, Tn, c->sh_sub.as<u32>(), cnt, st);
+  c->launches += 2;
+  c->sh_round = 0;
+  c->stats.rank_tied = c->sh_m;
+  c->sh_ks.release(); c->sh_cs.release(); c->sh_perm.release();
+  return c->sh_m;
+}
+
+// keys (rank, rank[next^(2^h)]) of the local tied subset -> sh_tiekeys
+void shard_tie_keys(cmsbwt_ctx *c) {
+  cudaStream_t st = c->st;
+  const u32 m = c->sh_m;
+  c->sh_tiekeys.alloc((size_t)m * 8 + 16, st);
+  if (m) {
+    k_tr_key_next<<<(m + 255) / 256, 256, 0, st>>>(c->sh_sub.as<u32>(), m, c->s_trank.as<u32>(), c->s_next.as<u32>(),
+                                                   c->sh_tiekeys.as<u64>());
+    LAUNCH(c);
+  }
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+}
+
+// every rank refines the all-gathered keys; this shard's entries are [my_off, my_off + sh_m)
+u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off) {
+  cudaStream_t st = c->st;
+  const int B = 256;
+  const u32 m = c->sh_m;
+  if (m_total == 0) return 0;
+  Scratch tmp;
+  DBuf keys, ids0, ids, grp, sg, nr, nt, cnt, sub2, jt;
+  keys.alloc((size_t)m_total * 8, st); ids0.alloc((size_t)m_total * 4, st); ids.alloc((size_t)m_total * 4, st);
+  grp.alloc((size_t)m_total * 4, st); sg.alloc((size_t)m_total * 4, st); nr.alloc((size_t)m_total * 4, st);
+  nt.alloc((size_t)m_total, st); cnt.alloc(4, st);
+  const u32 gM = (m_total + B - 1) / B;
+  k_sh_iota<<<gM, B, 0, st>>>(ids0.as<u32>(), m_total);
+  size_t tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, allkeys, keys.as<u64>(), ids0.as<u32>(), ids.as<u32>(), (int)m_total,
+                                  0, 64, st);
+  tmp.need(tb, st);
+  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, allkeys, keys.as<u64>(), ids0.as<u32>(), ids.as<u32>(),
+                                     (int)m_total, 0, 64, st));
+  k_tr_gs64<<<gM, B, 0, st>>>(keys.as<u64>(), m_total, grp.as<u32>(), sg.as<u32>());
+  max_scan(tmp, grp.as<u32>(), m_total, st);
+  max_scan(tmp, sg.as<u32>(), m_total, st);
+  k_sh_refine_scatter<<<gM, B, 0, st>>>(keys.as<u64>(), ids.as<u32>(), grp.as<u32>(), sg.as<u32>(), m_total,
+                                        nr.as<u32>(), nt.as<u8>());
+  c->launches += 14;
+  u32 m2 = 0;
+  if (m) {
+    k_sh_apply_own<<<(m + B - 1) / B, B, 0, st>>>(c->sh_sub.as<u32>(), m, nr.as<u32>() + my_off, c->s_trank.as<u32>());
+    sub2.alloc((size_t)m * 4 + 16, st);
+    m2 = select_tied(tmp, c->sh_sub.as<u32>(), nt.as<u8>() + my_off, m, sub2.as<u32>(), cnt, st);
+    c->launches += 3;
+    if (m2) {                           // the next round looks twice as far
+      jt.alloc((size_t)m2 * 4, st);
+      const u32 g2 = (m2 + B - 1) / B;
+      k_tr_jump<<<g2, B, 0, st>>>(sub2.as<u32>(), m2, c->s_next.as<u32>(), jt.as<u32>());
+      k_tr_jump_store<<<g2, B, 0, st>>>(sub2.as<u32>(), m2, jt.as<u32>(), c->s_next.as<u32>());
+      c->launches += 2;
+    }
+    c->sh_sub.swap(sub2);
+  }
+  c->sh_m = m2;
+  c->sh_round++;
+  c->stats.rank_rounds = c->sh_round;
+  if (c->sh_round > 64) throw CmsErr{CMSBWT_E_INTERNAL, "tail ranking did not converge"};
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+  return m2;
 }

@@ -83,7 +83,7 @@ __global__ void k_tile_scatter(const u32 *pos, const u32 *len, const u16 *cs, co
 
 // ---- pass A: bucket sizes + cost of pass B -------------------------------------------------------
 __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, const TileEnt *re, const u32 *hoff,
-                                                         const u32 *roff, u32 n, u32 ndocs, u32 *cov,
+                                                         const u32 *roff, u32 n, u32 ndocs, u32 t0, u32 *cov,
                                                          unsigned long long *work, u32 *maxent) {
   __shared__ u32 s_h[LT_W];
   __shared__ int s_d[LT_W + 1];
@@ -91,6 +91,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, cons
   typedef cub::BlockReduce<unsigned long long, LT_THREADS> BR;
   __shared__ typename BS::TempStorage ts;
   __shared__ typename BR::TempStorage tr;
+  // t0 = first tile of this device (multi-GPU: the entry arrays and cov are local to its tile range)
   const u32 t = blockIdx.x, tid = threadIdx.x;
   const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
   s_h[tid] = 0; s_d[tid] = 0;
@@ -106,8 +107,8 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, cons
   int d = s_d[tid], incl;
   BS(ts).InclusiveSum(d, incl);
   const u32 hq = s_h[tid];
-  const u32 p = (t << LT_SHIFT) + tid;
-  if (p < n) cov[p] = (u32)incl + hq + (p == n - 1 ? ndocs : 0u);
+  const u32 p = ((t + t0) << LT_SHIFT) + tid;
+  if (p < n) cov[(t << LT_SHIFT) + tid] = (u32)incl + hq + (p == n - 1 ? ndocs : 0u);
   // pair tests of pass B for this tile: every head against every range and its position mates
   unsigned long long w = (unsigned long long)hq * (hq + (r1 - r0));
   unsigned long long tot = BR(tr).Sum(w);
@@ -126,7 +127,8 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, cons
 #define LT_NB 16
 __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, const TileEnt *re, const u32 *hoff,
                                                            const u32 *roff, const u32 *isa, const u64 *base,
-                                                           u32 n, u8 *out, u32 *within_out, u64 *off_out) {
+                                                           u32 n, u32 t0, u8 *out, u64 *plc, u32 *within_out,
+                                                           u64 *off_out) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W];
   __shared__ u64 s_base[LT_W];
@@ -148,7 +150,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   if (tid <= LT_NB) { s_bcnt[tid] = 0; s_bcur[tid] = 0; }
   if (tid < npiv) s_praw[tid] = re[r0 + (u32)(((u64)(tid + 1) * rc) / (npiv + 1))].kappa;
   {
-    u32 p = (t << LT_SHIFT) + tid;
+    u32 p = ((t + t0) << LT_SHIFT) + tid;
     s_base[tid] = p < n ? base[isa[p]] : 0;
   }
   __syncthreads();
@@ -226,7 +228,8 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
       w += (s_rk[r] < kap) & ((lh & 0xFFFF) <= q) & (q <= (lh >> 16));
     }
     const u64 off = s_base[q] + w;
-    out[off] = (u8)(e.b >> 8);
+    if (plc) plc[h0 + j] = (off << 8) | ((e.b >> 8) & 0xFF);   // multi-GPU: the byte belongs to another device
+    else out[off] = (u8)(e.b >> 8);
     if (within_out) { within_out[e.a] = w; off_out[e.a] = off; }
   }
 }
@@ -242,21 +245,18 @@ __global__ void k_place_sentinels(const u32 *len, const u16 *cs, const u32 *sexc
 }
 
 // Builds the tile entries and cov[]; false = too heavy for the brute-force path (nothing kept).
-bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
+static bool tiles_finish(cmsbwt_ctx *c, DBuf &acc, u32 HE, u64 R, DBuf &sexcl);
+// histogram + scan + scatter of this device's heads over ntiles tiles -> t_he, t_re, t_hoff, t_roff
+static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_out, u64 *R_out) {
   cudaStream_t st = c->st;
   const u64 H = c->H;
-  const u32 n = c->ix.n;
   const int B = 256;
   const u32 gH = (u32)((H + B - 1) / B);
-  const u32 ntiles = (n >> LT_SHIFT) + 1;
-  c->light = false;
-  DBuf hcnt, rcnt, tmp, acc;
+  DBuf hcnt, rcnt, tmp;
   hcnt.alloc(((size_t)ntiles + 1) * 4, st); rcnt.alloc(((size_t)ntiles + 1) * 4, st);
   c->t_hoff.alloc(((size_t)ntiles + 1) * 4, st); c->t_roff.alloc(((size_t)ntiles + 1) * 4, st);
-  acc.alloc(16, st);
   CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
   CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
-  CK(cudaMemsetAsync(acc.p, 0, 16, st));
   k_tile_hist<<<gH, B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_toNext.as<u32>(), H,
                                 hcnt.as<u32>(), rcnt.as<u32>());
   size_t tb = 0;
@@ -272,7 +272,6 @@ bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
     cub::DeviceReduce::Sum(nullptr, tr, rcnt.as<u32>(), rtot.as<unsigned long long>(), (int)ntiles, st);
     DBuf tmp2; tmp2.alloc(tr, st);
     CK(cub::DeviceReduce::Sum(tmp2.p, tr, rcnt.as<u32>(), rtot.as<unsigned long long>(), (int)ntiles, st));
-    CK(cudaStreamSynchronize(st));
   }
   unsigned long long R = 0;
   CK(cudaMemcpyAsync(&R, rtot.p, 8, cudaMemcpyDeviceToHost, st));
@@ -290,12 +289,35 @@ bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
   k_tile_scatter<<<gH, B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                    c->h_toNext.as<u32>(), kappa, H, c->t_hoff.as<u32>(), c->t_roff.as<u32>(),
                                    hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>());
+  c->launches += 2;
+  CK(cudaGetLastError());
+  *HE_out = HE;
+  *R_out = R;
+  return true;
+}
+
+bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
+  cudaStream_t st = c->st;
+  const u32 n = c->ix.n;
+  const u32 ntiles = (n >> LT_SHIFT) + 1;
+  c->light = false;
+  DBuf acc;
+  acc.alloc(16, st);
+  CK(cudaMemsetAsync(acc.p, 0, 16, st));
+  u32 HE = 0;
+  u64 R = 0;
+  if (!tiles_scatter(c, kappa, ntiles, &HE, &R)) return false;
   c->d_cov.alloc(((size_t)n + 1) * 4, st);
   k_tile_cov<<<ntiles, LT_THREADS, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                            c->t_roff.as<u32>(), n, (u32)c->stats.n_docs, c->d_cov.as<u32>(),
+                                            c->t_roff.as<u32>(), n, (u32)c->stats.n_docs, 0, c->d_cov.as<u32>(),
                                             acc.as<unsigned long long>(), acc.as<u32>() + 2);
-  c->launches += 3;
+  LAUNCH(c);
   CK(cudaGetLastError());
+  return tiles_finish(c, acc, HE, R, sexcl);
+}
+
+static bool tiles_finish(cmsbwt_ctx *c, DBuf &acc, u32 HE, u64 R, DBuf &sexcl) {
+  cudaStream_t st = c->st;
   unsigned long long hacc[2] = {0, 0};
   CK(cudaMemcpyAsync(hacc, acc.p, 16, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
@@ -309,8 +331,7 @@ bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
   }
   c->tile_maxent = maxent;
   c->h_sexcl.release();
-  std::swap(c->h_sexcl.p, sexcl.p);
-  std::swap(c->h_sexcl.bytes, sexcl.bytes);
+  c->h_sexcl.swap(sexcl);
   c->light = true;
   return true;
 }
@@ -330,9 +351,154 @@ void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out) {
   if (sm > 40 * 1024)
     CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_place<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                               c->t_roff.as<u32>(), c->ix.isa, base, n, out, wo, oo);
+                                               c->t_roff.as<u32>(), c->ix.isa, base, n, 0, out, nullptr, wo, oo);
   k_place_sentinels<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                                            c->h_sexcl.as<u32>(), H, out, wo, oo);
   c->launches += 2;
   CK(cudaGetLastError());
+}
+
+// ================================================================================================
+// Multi-GPU (SURVEY.md 8e "non-head counting in position-partitioned space"): the reference
+// positions are cut into `world` ranges of tp tiles; every device files ITS heads under the global
+// tile space, the entry arrays (already grouped by tile, so every destination's slab is one
+// contiguous range) are exchanged all-to-all, and the owner merges the slabs tile by tile.
+void shard_tiles_local(cmsbwt_ctx *c, u32 world) {
+  const u32 n = c->ix.n;
+  const u32 ntiles = (n >> LT_SHIFT) + 1;
+  const u32 tp = (ntiles + world - 1) / world;
+  c->sh_world = world;
+  c->sh_tp = tp;
+  u32 HE = 0;
+  u64 R = 0;
+  if (!tiles_scatter(c, c->s_kappa.as<u64>(), tp * world, &HE, &R))
+    throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 tile ranges on one device"};
+  c->sh_he = HE;
+  c->sh_re = R;
+  c->s_kappa.release(); c->s_nitems.release(); c->s_tincl.release(); c->s_trank.release();
+  CK(cudaStreamSynchronize(c->st));
+}
+
+// per-tile entry counts summed over the W source slabs (offs: W rows of tp + 1 raw offsets)
+__global__ void k_sh_tile_counts(const u32 *hoffs, const u32 *roffs, u32 W, u32 tp, u32 *hc, u32 *rc) {
+  u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t > tp) return;
+  u32 a = 0, b = 0;
+  if (t < tp)
+    for (u32 s = 0; s < W; s++) {
+      a += hoffs[(size_t)s * (tp + 1) + t + 1] - hoffs[(size_t)s * (tp + 1) + t];
+      b += roffs[(size_t)s * (tp + 1) + t + 1] - roffs[(size_t)s * (tp + 1) + t];
+    }
+  hc[t] = a; rc[t] = b;
+}
+// one warp per tile copies the tile's segment of every slab behind one another
+__global__ void k_sh_tile_merge(const TileEnt *src, const u32 *offs, const u64 *slab, u32 W, u32 tp, const u32 *moff,
+                                TileEnt *dst) {
+  const u32 t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (t >= tp) return;
+  u32 d = moff[t];
+  for (u32 s = 0; s < W; s++) {
+    const u32 *o = offs + (size_t)s * (tp + 1);
+    const u32 a = o[t] - o[0], cnt = o[t + 1] - o[t];
+    const TileEnt *p = src + slab[s] + a;
+    for (u32 k = lane; k < cnt; k += 32) dst[d + k] = p[k];
+    d += cnt;
+  }
+}
+
+// he/re: the received slabs (slab s starts at he_slab[s] / re_slab[s] entries); hoffs/roffs: the
+// senders' offset slices for this device's tile range.  Leaves the merged entries in t_he/t_re
+// (tile-local offsets t_hoff/t_roff) and the bucket sizes of the range in sh_cov (tp * 256 entries).
+u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const void *re, const u32 *hoffs,
+                      const u32 *roffs, const u64 *he_slab, const u64 *re_slab, u64 ndocs_total) {
+  cudaStream_t st = c->st;
+  const u32 n = c->ix.n;
+  const u32 tp = c->sh_tp;
+  const int B = 256;
+  c->sh_rank = rank;
+  DBuf hc, rc, slab, tmp, acc, mh, mr;
+  hc.alloc(((size_t)tp + 1) * 4, st); rc.alloc(((size_t)tp + 1) * 4, st);
+  mh.alloc(((size_t)tp + 1) * 4, st); mr.alloc(((size_t)tp + 1) * 4, st);
+  slab.alloc((size_t)world * 16, st); acc.alloc(16, st);
+  CK(cudaMemsetAsync(acc.p, 0, 16, st));
+  CK(cudaMemcpyAsync(slab.p, he_slab, (size_t)world * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(slab.as<u64>() + world, re_slab, (size_t)world * 8, cudaMemcpyHostToDevice, st));
+  k_sh_tile_counts<<<(tp + 1 + B - 1) / B, B, 0, st>>>(hoffs, roffs, world, tp, hc.as<u32>(), rc.as<u32>());
+  size_t tb = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, tb, hc.as<u32>(), mh.as<u32>(), (int)(tp + 1), st);
+  tmp.alloc(tb, st);
+  size_t t1 = tb;
+  CK(cub::DeviceScan::ExclusiveSum(tmp.p, t1, hc.as<u32>(), mh.as<u32>(), (int)(tp + 1), st));
+  t1 = tb;
+  CK(cub::DeviceScan::ExclusiveSum(tmp.p, t1, rc.as<u32>(), mr.as<u32>(), (int)(tp + 1), st));
+  u32 HE = 0, R = 0;
+  CK(cudaMemcpyAsync(&HE, mh.as<u32>() + tp, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&R, mr.as<u32>() + tp, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  DBuf mhe, mre;
+  mhe.alloc(((size_t)HE + 1) * sizeof(TileEnt), st); mre.alloc(((size_t)R + 1) * sizeof(TileEnt), st);
+  const u32 gW = (u32)(((u64)tp * 32 + B - 1) / B);
+  k_sh_tile_merge<<<gW, B, 0, st>>>((const TileEnt *)he, hoffs, slab.as<u64>(), world, tp, mh.as<u32>(),
+                                    mhe.as<TileEnt>());
+  k_sh_tile_merge<<<gW, B, 0, st>>>((const TileEnt *)re, roffs, slab.as<u64>() + world, world, tp, mr.as<u32>(),
+                                    mre.as<TileEnt>());
+  c->t_he.swap(mhe);
+  c->t_re.swap(mre);
+  c->t_hoff.swap(mh);
+  c->t_roff.swap(mr);
+  c->sh_he = HE;
+  c->sh_re = R;
+  c->sh_cov.alloc((size_t)tp * LT_W * 4, st);
+  CK(cudaMemsetAsync(c->sh_cov.p, 0, (size_t)tp * LT_W * 4, st));
+  k_tile_cov<<<tp, LT_THREADS, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+                                        c->t_roff.as<u32>(), n, (u32)ndocs_total, rank * tp, c->sh_cov.as<u32>(),
+                                        acc.as<unsigned long long>(), acc.as<u32>() + 2);
+  c->launches += 7;
+  CK(cudaGetLastError());
+  unsigned long long hacc[2] = {0, 0};
+  CK(cudaMemcpyAsync(hacc, acc.p, 16, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  c->stats.n_items = (u64)HE + R;
+  c->stats.pair_tests = hacc[0];
+  c->tile_maxent = (u32)hacc[1];
+  return c->tile_maxent;
+}
+
+__global__ void k_sh_sentinel_plc(const u32 *len, const u16 *cs, const u32 *sexcl, u64 H, u64 doc_base, u64 *plc) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H || len[i] != 0) return;
+  u32 d = sexcl[i];
+  plc[d] = ((doc_base + d) << 8) | (u64)(cs[i] & 0xFF);
+}
+
+// pass B for this device's tile range: (offset << 8 | symbol) per head entry, then this shard's
+// document terminators (offset = global document index); sorted by offset into sh_plc.
+void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
+  cudaStream_t st = c->st;
+  const u32 n = c->ix.n;
+  const u32 tp = c->sh_tp;
+  const u64 H = c->H;
+  const u64 nd = c->stats.n_docs;
+  const u64 P = c->sh_he + nd;
+  DBuf raw, tmp;
+  raw.alloc((P + 1) * 8, st);
+  c->sh_plc.alloc((P + 1) * 8, st);
+  size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;
+  if (sm > 40 * 1024)
+    CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_tile_place<<<tp, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+                                           c->t_roff.as<u32>(), c->ix.isa, base, n, c->sh_rank * tp, nullptr,
+                                           raw.as<u64>(), nullptr, nullptr);
+  k_sh_sentinel_plc<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
+                                                           c->s_sexcl.as<u32>(), H, doc_base, raw.as<u64>() + c->sh_he);
+  int bits = 9;
+  while (bits < 64 && (1ull << (bits - 8)) < c->sh_Ntotal) bits++;
+  size_t tb = 0;
+  cub::DeviceRadixSort::SortKeys(nullptr, tb, raw.as<u64>(), c->sh_plc.as<u64>(), (int)P, 0, bits, st);
+  tmp.alloc(tb, st);
+  CK(cub::DeviceRadixSort::SortKeys(tmp.p, tb, raw.as<u64>(), c->sh_plc.as<u64>(), (int)P, 0, bits, st));
+  c->launches += 8;
+  c->sh_nplc = P;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
 }

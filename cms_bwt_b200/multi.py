@@ -1,0 +1,394 @@
+"""Multi-GPU host layer of the CMS-BWT path: one process per GPU, documents sharded
+whole, three exchange phases between the device steps of include/cmsbwt_b200.h ("shard API").
+
+The reference is single threaded and has no counterpart of this file; what it mirrors is the order
+of the reference's stages (CMS-BWT-functions.cpp:1138-1213 MS per document, :1359-1603 head order,
+:1618-1777 emit) with the collectives where data has to change owner:
+
+    stage 1   matching statistics of this rank's documents            (no communication)
+    stage 2a  tails -> owners by 32-bit key range      all-to-all     (sampled splitters)
+              ranks + tie flags back                   all-to-all
+              refinement of the still tied tails       all-gather per round (small)
+    stage 2b  tile entries -> owners by reference-position range      all-to-all
+              bucket sizes of every position range     all-gather
+    stage 3   head placements -> owners by output byte range          all-to-all
+
+`ShardedPath` is written against an `ops` object (the device steps) and `torch.distributed` (the
+collectives) only, so the same orchestration runs on NCCL with `CudaShardOps` (the product) and,
+in tests/, on gloo with a numpy model of the device steps (test infrastructure, CPU).
+"""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import lib, CmsBwtError, MODE_PLAIN
+
+SAMPLES_PER_RANK = 1024
+TILE_MAX_ENTRIES = 12288          # tiles.cu LT_MAX_ENTRIES
+
+
+def shard_documents(doc_lengths, world):
+    """Contiguous ranges of whole documents with balanced symbol counts (incl. terminators).
+    doc_lengths: symbols per document without its terminator.  -> list of (first, last+1)."""
+    total = sum(l + 1 for l in doc_lengths)
+    bounds, acc, d = [0], 0, 0
+    for r in range(1, world):
+        target = total * r // world
+        while d < len(doc_lengths) and acc + (doc_lengths[d] + 1) // 2 < target:
+            acc += doc_lengths[d] + 1
+            d += 1
+        bounds.append(d)
+    bounds.append(len(doc_lengths))
+    return [(bounds[r], bounds[r + 1]) for r in range(world)]
+
+
+def merge_rle_borders(parts):
+    """Concatenates per-rank lists of (run, symbol) records, merging a run that straddles a border
+    (the -r writer emits maximal runs, CMS-BWT-functions.cpp:1695-1777 / BASELINE.md section 2)."""
+    out = []
+    for recs in parts:
+        for run, sym in recs:
+            if out and out[-1][1] == sym:
+                out[-1] = (out[-1][0] + run, sym)
+            else:
+                out.append((run, sym))
+    return out
+
+
+class DistComm:
+    """The two collectives the path needs, on torch.distributed (NCCL on GPUs, gloo in the CPU tests)."""
+
+    def __init__(self, group=None):
+        self.group = group
+
+    def all_gather(self, out, inp):
+        dist.all_gather_into_tensor(out, inp, group=self.group)
+
+    def all_to_all(self, out, inp, out_splits, in_splits):
+        dist.all_to_all_single(out, inp, out_splits, in_splits, group=self.group)
+
+
+class ThreadComm:
+    """Same collectives between `world` threads of ONE process (one context per thread, all on the
+    same device): used to run the multi-rank path on a single-GPU box."""
+
+    class Shared:
+        def __init__(self, world):
+            import threading
+            self.world = world
+            self.barrier = threading.Barrier(world)
+            self.slots = [None] * world
+
+    def __init__(self, shared, rank):
+        self.sh, self.rank = shared, rank
+
+    def _exchange(self, item):
+        self.sh.slots[self.rank] = item
+        self.sh.barrier.wait()
+        items = list(self.sh.slots)
+        self.sh.barrier.wait()
+        return items
+
+    def all_gather(self, out, inp):
+        items = self._exchange(inp)
+        n = inp.numel()
+        for r, t in enumerate(items):
+            out[r * n:(r + 1) * n].copy_(t)
+        if out.is_cuda:
+            torch.cuda.synchronize(out.device)
+        self.sh.barrier.wait()                   # nobody may free its input before all have copied
+
+    def all_to_all(self, out, inp, out_splits, in_splits):
+        items = self._exchange((inp, list(in_splits)))
+        o = 0
+        for r, (t, splits) in enumerate(items):
+            a = sum(splits[:self.rank])
+            out[o:o + out_splits[r]].copy_(t[a:a + splits[self.rank]])
+            o += out_splits[r]
+        if out.is_cuda:
+            torch.cuda.synchronize(out.device)
+        self.sh.barrier.wait()
+
+
+class ShardedPath:
+    """Stages 2-3 across ranks.  `ops` has already run stage 1 on this rank's documents."""
+
+    def __init__(self, ops, rank, world, group=None, comm=None):
+        self.ops, self.rank, self.world = ops, rank, world
+        self.comm = comm if comm is not None else DistComm(group)
+        self.comm_bytes = 0
+        self.collectives = 0
+
+    # ---- collectives ---------------------------------------------------------------------------
+    def _sync(self):
+        self.ops.sync()
+
+    def _allgather_ints(self, vals):
+        t = self.ops.from_list(vals, torch.int64)
+        out = self.ops.empty(len(vals) * self.world, torch.int64)
+        self.comm.all_gather(out, t)
+        self._sync()
+        self.collectives += 1
+        return out.cpu().view(self.world, len(vals)).tolist()
+
+    def _a2a_counts(self, send_counts):
+        t = self.ops.from_list(send_counts, torch.int64)
+        out = self.ops.empty(self.world, torch.int64)
+        self.comm.all_to_all(out, t, [1] * self.world, [1] * self.world)
+        self._sync()
+        self.collectives += 1
+        return out.cpu().tolist()
+
+    def _a2a(self, send, send_counts, recv_counts, width=1):
+        """all-to-all-v of a flat tensor; counts are in entries of `width` elements."""
+        out = self.ops.empty(sum(recv_counts) * width, send.dtype)
+        self.comm.all_to_all(out, send, [c * width for c in recv_counts], [c * width for c in send_counts])
+        self._sync()
+        self.collectives += 1
+        self.comm_bytes += (send.numel() + out.numel()) * send.element_size()
+        return out
+
+    def _allgather_v(self, t, counts):
+        """all-gather of tensors of different lengths (padded to the longest)."""
+        mx = max(counts)
+        if mx == 0:
+            return self.ops.empty(0, t.dtype)
+        pad = self.ops.empty(mx, t.dtype)
+        pad[:t.numel()] = t
+        out = self.ops.empty(mx * self.world, t.dtype)
+        self.comm.all_gather(out, pad)
+        self._sync()
+        self.collectives += 1
+        self.comm_bytes += out.numel() * out.element_size()
+        return torch.cat([out[r * mx:r * mx + counts[r]] for r in range(self.world)])
+
+    # ---- the path ------------------------------------------------------------------------------
+    def run(self, N_local, ndocs_local):
+        ops, W, R = self.ops, self.world, self.rank
+        g = self._allgather_ints([N_local, ndocs_local])
+        N_total = sum(x[0] for x in g)
+        ndocs_total = sum(x[1] for x in g)
+        doc_base = sum(x[1] for x in g[:R])
+        self.N_total, self.ndocs_total, self.doc_base = N_total, ndocs_total, doc_base
+
+        # -- stage 2a: global order of the tails
+        Tn = ops.tails(doc_base)
+        ks, cs = ops.tail_keys(), ops.tail_cls()
+        splitters = self._splitters(ks, Tn)
+        b = [0] + ops.lower_bound("tail_keys", splitters) + [Tn]
+        send = [b[d + 1] - b[d] for d in range(W)]
+        recv = self._a2a_counts(send)
+        rk = self._a2a(ks, send, recv)
+        rc = self._a2a(cs, send, recv)
+        M = sum(recv)
+        Ms = self._allgather_ints([M])
+        rank_base = sum(x[0] for x in Ms[:R])
+        if sum(x[0] for x in Ms) >= 2 ** 32:
+            raise CmsBwtError(-3, "more than 2^32 tails in the collection")
+        r_out, t_out = ops.rank_owner(rk, rc, M, rank_base)
+        rs = self._a2a(r_out, recv, send)
+        ts = self._a2a(t_out, recv, send)
+        m = ops.rank_apply(rs, ts)
+        self.rank_rounds = 0
+        while True:
+            ms = [x[0] for x in self._allgather_ints([m])]
+            if sum(ms) == 0:
+                break
+            keys = ops.tie_keys()
+            allk = self._allgather_v(keys, ms)
+            m = ops.tie_refine(allk, sum(ms), sum(ms[:R]))
+            self.rank_rounds += 1
+
+        # -- stage 2b: tile entries to the owners of the reference-position ranges
+        tp = ops.tiles_local(W)
+        hoff, roff = ops.buffer("tile_hoff"), ops.buffer("tile_roff")
+        edge = torch.arange(0, W * tp + 1, tp, device=hoff.device)
+        hb = [int(v) & 0xFFFFFFFF for v in hoff[edge].cpu().tolist()]
+        rb = [int(v) & 0xFFFFFFFF for v in roff[edge].cpu().tolist()]
+        hsend = [hb[d + 1] - hb[d] for d in range(W)]
+        rsend = [rb[d + 1] - rb[d] for d in range(W)]
+        hrecv = self._a2a_counts(hsend)
+        rrecv = self._a2a_counts(rsend)
+        he = self._a2a(ops.buffer("tile_heads"), hsend, hrecv, width=2)
+        re = self._a2a(ops.buffer("tile_ranges"), rsend, rrecv, width=2)
+        rows = (torch.arange(W, device=hoff.device)[:, None] * tp +
+                torch.arange(tp + 1, device=hoff.device)[None, :]).reshape(-1)
+        eq = [tp + 1] * W
+        hoffs = self._a2a(hoff[rows].contiguous(), eq, eq)
+        roffs = self._a2a(roff[rows].contiguous(), eq, eq)
+        he_slab = [sum(hrecv[:s]) for s in range(W)]
+        re_slab = [sum(rrecv[:s]) for s in range(W)]
+        maxent = ops.tiles_merge(W, R, he, re, hoffs, roffs, he_slab, re_slab, ndocs_total)
+        gmax = max(x[0] for x in self._allgather_ints([maxent]))
+        if gmax > TILE_MAX_ENTRIES:
+            raise CmsBwtError(-3, "a tile holds %d entries (limit %d): collection too deep for the "
+                                  "multi-GPU tile path" % (gmax, TILE_MAX_ENTRIES))
+        cov = ops.buffer("cov_slice")
+        cov_full = ops.empty(cov.numel() * W, cov.dtype)
+        self.comm.all_gather(cov_full, cov)
+        self._sync()
+        self.collectives += 1
+        self.comm_bytes += cov_full.numel() * 4
+
+        # -- stage 3: own output range + placements to the owners of the output ranges
+        obeg, olen, chunk = ops.emit(cov_full, N_total, W, R, doc_base)
+        plc = ops.buffer("placements")
+        P = plc.numel()
+        pb = [0] + ops.lower_bound("placements", [(d * chunk) << 8 for d in range(1, W)]) + [P]
+        psend = [pb[d + 1] - pb[d] for d in range(W)]
+        precv = self._a2a_counts(psend)
+        got = self._a2a(plc, psend, precv)
+        ops.apply(got, sum(precv))
+        self.out_begin, self.out_len = obeg, olen
+        return ops.buffer("result")
+
+    def _splitters(self, ks, Tn):
+        """W-1 key values from SAMPLES_PER_RANK evenly spaced local samples per rank; equal keys
+        always land on one owner because the slabs are cut at lower bounds of key VALUES."""
+        W = self.world
+        S = SAMPLES_PER_RANK
+        if Tn > 0:
+            idx = torch.linspace(0, Tn - 1, S, device=ks.device).to(torch.int64)
+            smp = ks[idx].to(torch.int64) & 0xFFFFFFFF
+        else:
+            smp = torch.full((S,), 0xFFFFFFFF, dtype=torch.int64, device=ks.device)
+        allsmp = self.ops.empty(S * W, torch.int64)
+        self.comm.all_gather(allsmp, smp.contiguous())
+        self._sync()
+        self.collectives += 1
+        srt = torch.sort(allsmp).values.cpu().tolist()
+        return [srt[(d * S * W) // W] for d in range(1, W)]
+
+
+# ---- the CUDA device steps ------------------------------------------------------------------------
+class _DevArray:
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = dict(shape=(n,), typestr=typestr, data=(ptr, False), version=2)
+
+
+_TYPES = {  # shard buffer -> (elements per entry, typestr, torch dtype)
+    "tail_keys": (1, "<i4", torch.int32), "tail_cls": (1, "<i4", torch.int32), "tie_keys": (1, "<i8", torch.int64),
+    "tile_heads": (2, "<i8", torch.int64), "tile_ranges": (2, "<i8", torch.int64),
+    "tile_hoff": (1, "<i4", torch.int32), "tile_roff": (1, "<i4", torch.int32),
+    "cov_slice": (1, "<i4", torch.int32), "placements": (1, "<i8", torch.int64), "result": (1, "|u1", torch.uint8),
+}
+
+
+class CudaShardOps:
+    """Device steps of the shard API on one GPU (ctypes over libcmsbwt_b200.so)."""
+
+    def __init__(self, ctx, device):
+        self.ctx, self.h, self.device = ctx, ctx.h, torch.device(device)
+        L = lib()
+        vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
+        L.cmsbwt_shard_tails.argtypes = [vp, u64, C.POINTER(u32)]
+        L.cmsbwt_shard_buffer.argtypes = [vp, C.c_char_p, C.POINTER(vp), C.POINTER(u64)]
+        L.cmsbwt_shard_lower_bound.argtypes = [vp, C.c_char_p, C.POINTER(u64), u32, C.POINTER(u64)]
+        L.cmsbwt_shard_rank_owner.argtypes = [vp, vp, vp, u32, u32, vp, vp]
+        L.cmsbwt_shard_rank_apply.argtypes = [vp, vp, vp, C.POINTER(u32)]
+        L.cmsbwt_shard_tie_keys.argtypes = [vp, C.POINTER(u32)]
+        L.cmsbwt_shard_tie_refine.argtypes = [vp, vp, u32, u32, C.POINTER(u32)]
+        L.cmsbwt_shard_tiles_local.argtypes = [vp, u32, C.POINTER(u32)]
+        L.cmsbwt_shard_tiles_merge.argtypes = [vp, u32, u32, vp, vp, vp, vp, C.POINTER(u64), C.POINTER(u64), u64,
+                                               C.POINTER(u32)]
+        L.cmsbwt_shard_emit.argtypes = [vp, vp, u64, u32, u32, u64, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+        L.cmsbwt_shard_apply.argtypes = [vp, vp, u64]
+        self.L = L
+
+    def _ck(self, rc):
+        self.ctx._ck(rc)
+
+    def sync(self):
+        torch.cuda.current_stream(self.device).synchronize()
+
+    def empty(self, n, dtype):
+        return torch.empty(max(int(n), 0), dtype=dtype, device=self.device)
+
+    def from_list(self, vals, dtype):
+        return torch.tensor(vals, dtype=dtype, device=self.device)
+
+    @staticmethod
+    def _ptr(t):
+        return C.c_void_p(t.data_ptr() if t.numel() else 0)
+
+    def buffer(self, name):
+        p, n = C.c_void_p(), C.c_uint64()
+        self._ck(self.L.cmsbwt_shard_buffer(self.h, name.encode(), C.byref(p), C.byref(n)))
+        per, ts, dt = _TYPES[name]
+        if n.value == 0 or not p.value:
+            return torch.empty(0, dtype=dt, device=self.device)
+        return torch.as_tensor(_DevArray(p.value, n.value * per, ts), device=self.device)
+
+    def tails(self, doc_base):
+        n = C.c_uint32()
+        self._ck(self.L.cmsbwt_shard_tails(self.h, doc_base, C.byref(n)))
+        return n.value
+
+    def tail_keys(self):
+        return self.buffer("tail_keys")
+
+    def tail_cls(self):
+        return self.buffer("tail_cls")
+
+    def lower_bound(self, name, values):
+        k = len(values)
+        if k == 0:
+            return []
+        v = (C.c_uint64 * k)(*values)
+        o = (C.c_uint64 * k)()
+        self._ck(self.L.cmsbwt_shard_lower_bound(self.h, name.encode(), v, k, o))
+        return list(o)
+
+    def rank_owner(self, keys, cls, M, rank_base):
+        r = self.empty(M, torch.int32)
+        t = self.empty(M, torch.uint8)
+        self._ck(self.L.cmsbwt_shard_rank_owner(self.h, self._ptr(keys), self._ptr(cls), M, rank_base,
+                                                self._ptr(r), self._ptr(t)))
+        return r, t
+
+    def rank_apply(self, rs, ts):
+        m = C.c_uint32()
+        self._ck(self.L.cmsbwt_shard_rank_apply(self.h, self._ptr(rs), self._ptr(ts), C.byref(m)))
+        return m.value
+
+    def tie_keys(self):
+        m = C.c_uint32()
+        self._ck(self.L.cmsbwt_shard_tie_keys(self.h, C.byref(m)))
+        return self.buffer("tie_keys")
+
+    def tie_refine(self, allkeys, m_total, my_off):
+        m = C.c_uint32()
+        self._ck(self.L.cmsbwt_shard_tie_refine(self.h, self._ptr(allkeys), m_total, my_off, C.byref(m)))
+        return m.value
+
+    def tiles_local(self, world):
+        tp = C.c_uint32()
+        self._ck(self.L.cmsbwt_shard_tiles_local(self.h, world, C.byref(tp)))
+        return tp.value
+
+    def tiles_merge(self, world, rank, he, re, hoffs, roffs, he_slab, re_slab, ndocs_total):
+        me = C.c_uint32()
+        hs = (C.c_uint64 * world)(*he_slab)
+        rs = (C.c_uint64 * world)(*re_slab)
+        self._ck(self.L.cmsbwt_shard_tiles_merge(self.h, world, rank, self._ptr(he), self._ptr(re), self._ptr(hoffs),
+                                                 self._ptr(roffs), hs, rs, ndocs_total, C.byref(me)))
+        return me.value
+
+    def emit(self, cov_full, N_total, world, rank, doc_base):
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._ck(self.L.cmsbwt_shard_emit(self.h, self._ptr(cov_full), N_total, world, rank, doc_base,
+                                          C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def apply(self, plc, count):
+        self._ck(self.L.cmsbwt_shard_apply(self.h, self._ptr(plc), count))
+
+
+def run_sharded(ctx, device, d_text_ptr, N_local, ndocs_local, rank, world, group=None, comm=None):
+    """Whole path for this rank's documents (text resident in HBM): stage 1 on the shard, then the
+    exchange phases.  -> (ShardedPath, result tensor = this rank's contiguous slice of the BWT)."""
+    ctx.ms_run_device(d_text_ptr, N_local)
+    sp = ShardedPath(CudaShardOps(ctx, device), rank, world, group, comm)
+    out = sp.run(N_local, ndocs_local)
+    return sp, out

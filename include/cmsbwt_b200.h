@@ -136,6 +136,53 @@ int cmsbwt_result_download(cmsbwt_ctx *ctx, void *host_out, uint64_t cap);
 int cmsbwt_run(cmsbwt_ctx *ctx, const uint8_t *text, uint64_t N, int mode, void *host_out,
                uint64_t cap, uint64_t *out_bytes);
 
+/* ---- multi-GPU shard API (no reference counterpart: the reference is one thread) ----
+ * One context per GPU, one process per GPU.  Documents are sharded whole (the MS state is reset per
+ * document, reference :349-355 / :1143-1149), so cmsbwt_ms_run[_device] is called on the shard's
+ * text as is.  Stages 2-3 then alternate these device steps with collectives that the host layer
+ * owns (cms_bwt_b200/multi.py: torch.distributed over NCCL; the library itself links no NCCL):
+ *
+ *   shard_tails            link + tail labels (:1359-1385) + local sort by the 32-bit tail key
+ *   [all-to-all of keys/cls by key range]
+ *   shard_rank_owner       rank what was received (replaces naming + libsais_int :1432-1472 for the range)
+ *   [all-to-all back]      shard_rank_apply
+ *   loop: shard_tie_keys   [all-gather]  shard_tie_refine     (next-rank substitution :1480-1494)
+ *   shard_tiles_local      kappa + tile entries of this shard's heads over the global tile space
+ *   [all-to-all of entries by reference-position range]
+ *   shard_tiles_merge      merged tiles of this device's position range + bucket sizes (:368-390)
+ *   [all-gather of bucket sizes]
+ *   shard_emit             offsets (:1618-1628), reference symbols of this device's output range
+ *                          (:1640-1688), head placements of its position range
+ *   [all-to-all of placements by output range]   shard_apply
+ *
+ * All pointers named d_* are device pointers on the context's GPU (16-byte aligned).  Every call
+ * synchronises the context's stream before it returns. */
+int cmsbwt_shard_tails(cmsbwt_ctx *ctx, uint64_t doc_base, uint32_t *n_tails);
+/* named device arrays of the current shard state: "tail_keys" u32 (sorted), "tail_cls" u32,
+ * "tie_keys" u64, "tile_heads"/"tile_ranges" 16-byte entries grouped by tile, "tile_hoff"/
+ * "tile_roff" u32[world * tiles_per_rank + 1], "cov_slice" u32[tiles_per_rank * 256],
+ * "placements" u64 (offset << 8 | symbol, sorted), "result" u8 */
+int cmsbwt_shard_buffer(cmsbwt_ctx *ctx, const char *name, const void **dptr, uint64_t *count);
+/* first index whose element is >= values[k], for the sorted buffers "tail_keys" and "placements" */
+int cmsbwt_shard_lower_bound(cmsbwt_ctx *ctx, const char *name, const uint64_t *values, uint32_t count,
+                             uint64_t *out_idx);
+int cmsbwt_shard_rank_owner(cmsbwt_ctx *ctx, const void *d_keys, const void *d_cls, uint32_t M,
+                            uint32_t rank_base, void *d_rank_out, void *d_tie_out);
+int cmsbwt_shard_rank_apply(cmsbwt_ctx *ctx, const void *d_rank_sorted, const void *d_tie_sorted,
+                            uint32_t *m_tied);
+int cmsbwt_shard_tie_keys(cmsbwt_ctx *ctx, uint32_t *m);
+int cmsbwt_shard_tie_refine(cmsbwt_ctx *ctx, const void *d_allkeys, uint32_t m_total, uint32_t my_off,
+                            uint32_t *m_tied);
+int cmsbwt_shard_tiles_local(cmsbwt_ctx *ctx, uint32_t world, uint32_t *tiles_per_rank);
+int cmsbwt_shard_tiles_merge(cmsbwt_ctx *ctx, uint32_t world, uint32_t rank, const void *d_he,
+                             const void *d_re, const void *d_hoffs, const void *d_roffs,
+                             const uint64_t *he_slab, const uint64_t *re_slab, uint64_t ndocs_total,
+                             uint32_t *max_entries);
+int cmsbwt_shard_emit(cmsbwt_ctx *ctx, const void *d_cov_full, uint64_t N_total, uint32_t world,
+                      uint32_t rank, uint64_t doc_base, uint64_t *out_begin, uint64_t *out_len,
+                      uint64_t *chunk_bytes);
+int cmsbwt_shard_apply(cmsbwt_ctx *ctx, const void *d_plc, uint64_t count);
+
 /* tuning knobs (0 = default): chunk length of the MS kernel, tile width is fixed at 64. */
 int cmsbwt_set_param(cmsbwt_ctx *ctx, const char *name, int64_t value);
 

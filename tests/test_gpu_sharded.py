@@ -1,0 +1,183 @@
+"""GPU parity tests of the multi-GPU path (cms_bwt_b200.multi + the shard API of the C ABI).
+
+On a single-GPU box the ranks are threads of this process, one context each on cuda:0, exchanging
+through multi.ThreadComm -- every CUDA shard step and the whole orchestration run exactly as under
+NCCL; only the transport differs.  With >= 2 GPUs the same cases also run as one process per GPU over
+NCCL (torchrun-style environment, tests/shard_worker_gpu.py).  Bit-exact against the oracle."""
+import glob
+import os
+import socket
+import subprocess
+import sys
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+import cms_bwt_b200 as P
+from cms_bwt_b200 import multi
+import oracle_lib as O
+import fuzz_cases
+import gen_synth
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = os.path.join(HERE, "golden")
+
+
+def split_text(text, world):
+    ends = np.flatnonzero(text == 2)
+    starts = np.concatenate([[0], ends[:-1] + 1])
+    plan = multi.shard_documents((ends - starts).tolist(), world)
+    out = []
+    for a, b in plan:
+        lo = int(starts[a]) if a < len(ends) else len(text)
+        hi = int(ends[b - 1]) + 1 if b > a else lo
+        out.append((text[lo:hi], b - a))
+    return out
+
+
+def run_threads(x, text, world, params=None):
+    dev = torch.device("cuda:0")
+    shards = split_text(text, world)
+    shared = multi.ThreadComm.Shared(world)
+    res, err = [None] * world, [None] * world
+
+    def work(r):
+        ctx = None
+        try:
+            torch.cuda.set_device(0)
+            ctx = P.Context(0)
+            for k, v in (params or {}).items():
+                ctx.set_param(k, v)
+            ctx.index_upload(x)
+            shard, nd = shards[r]
+            pad = np.full(64, 2, np.uint8)
+            t = torch.from_numpy(np.concatenate([shard, pad])).to(dev)
+            if len(shard) == 0:
+                raise RuntimeError("empty shard")
+            sp, out = multi.run_sharded(ctx, dev, t.data_ptr(), len(shard), nd, r, world,
+                                        comm=multi.ThreadComm(shared, r))
+            res[r] = (sp.out_begin, out.cpu().numpy().copy(), sp.rank_rounds, ctx.stats())
+        except BaseException as e:          # noqa: BLE001  (a dead rank must not leave the others waiting)
+            err[r] = e
+            shared.barrier.abort()
+        finally:
+            if ctx is not None:
+                ctx.close()
+
+    th = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for e in err:
+        if e is not None and not isinstance(e, threading.BrokenBarrierError):
+            raise e
+    for e in err:
+        if e is not None:
+            raise e
+    off = 0
+    for b, o, _, _ in res:
+        assert b == off or len(o) == 0
+        off += len(o)
+    return np.concatenate([o for _, o, _, _ in res]), res
+
+
+def _check(x, text, world, desc, params=None):
+    want = O.Oracle(x).bwt(text)
+    got, res = run_threads(x, text, world, params)
+    if not np.array_equal(got, want):
+        bad = np.flatnonzero(got != want) if len(got) == len(want) else []
+        raise AssertionError("sharded BWT %s world=%d: len %d/%d, %d mismatches, first %s"
+                             % (desc, world, len(got), len(want), len(bad), bad[:8]))
+    return res
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 4])
+def test_sharded_synthetic(world):
+    ref, copies = gen_synth.make_collection(30000, 9, 0.004, 21)
+    x = P.augment(ref)
+    text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    res = _check(x, text, world, "synthetic 30k x 9")
+    assert all(r[3]["fast_path"] == 1 for r in res)
+
+
+def test_sharded_golden_fixtures():
+    n = 0
+    for f in sorted(glob.glob(os.path.join(GOLDEN, "*.npz"))):
+        z = np.load(f)
+        x = P.augment(P.read_reference(z["ref_file"].tobytes()))
+        text, nd = P.parse_collection(z["coll_file"].tobytes(), int(z["prefix"]))
+        if nd < 2:
+            continue
+        got, _ = run_threads(x, text, 2)
+        assert np.array_equal(got, z["bwt"]), f
+        n += 1
+    assert n >= 5
+
+
+def test_sharded_fuzz_general_alphabets():
+    done = 0
+    for seed in range(40):
+        c = fuzz_cases.make_case(seed)
+        x = P.augment(P.read_reference(c["ref_file"]))
+        text, nd = P.parse_collection(c["coll_file"])
+        if nd < 3 or len(text) < 40:
+            continue
+        shards = split_text(text, 2)
+        if any(len(s) == 0 for s, _ in shards):
+            continue
+        _check(x, text, 2, c["desc"])
+        done += 1
+    assert done >= 10
+
+
+def test_sharded_duplicates_need_refinement_rounds():
+    rng = np.random.default_rng(8)
+    ref = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 20000)]
+    mut = ref.copy()
+    for q in rng.integers(100, 19900, 40):
+        mut[q] = ord("A") if mut[q] != ord("A") else ord("C")
+    docs = [mut.copy(), ref.copy(), mut.copy(), mut[5000:].copy(), ref[:7000].copy(), mut.copy(), mut.copy()]
+    x = P.augment(ref)
+    text = O.docs_to_text(docs)
+    res = _check(x, text, 3, "duplicates")
+    assert max(r[2] for r in res) >= 1
+
+
+def test_sharded_many_short_documents():
+    rng = np.random.default_rng(4)
+    ref = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 3000)]
+    docs = []
+    for k in range(1500):
+        a = int(rng.integers(0, 2900))
+        d = ref[a:a + int(rng.integers(1, 100))].copy()
+        if rng.random() < 0.3 and len(d) > 2:
+            d[len(d) // 2] = ord("A") if d[len(d) // 2] != ord("A") else ord("G")
+        docs.append(d)
+    x = P.augment(ref)
+    _check(x, O.docs_to_text(docs), 4, "1500 short documents")
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_sharded_nccl_two_gpus(workdir):
+    ref, copies = gen_synth.make_collection(200000, 8, 0.002, 3)
+    x = P.augment(ref)
+    text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    case = os.path.join(workdir, "nccl_case.npz")
+    np.savez(case, x=x, text=text)
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, os.path.join(HERE, "shard_worker_gpu.py"), case,
+                                       os.path.join(workdir, "nccl_out")], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT))
+    logs = [p.communicate(timeout=600)[0].decode() for p in procs]
+    for p, lg in zip(procs, logs):
+        assert p.returncode == 0, lg[-3000:]
+    parts = [np.load(os.path.join(workdir, "nccl_out.%d.npz" % r))["out"] for r in range(2)]
+    assert np.array_equal(np.concatenate(parts), O.Oracle(x).bwt(text))
