@@ -174,11 +174,13 @@ def run_multi(args, rank, world, local, dev, dist):
     ctx = P.Context(local)
     ctx.index_upload(x)                       # replicated index, built on every GPU, timed separately
     st0 = ctx.stats()
-    state = {}
+    state = {"phase": {}}
 
     def step():
         sp, out = multi.run_sharded(ctx, dev, text.data_ptr(), N, ndocs, rank, world)
         state["sp"], state["out"] = sp, out
+        for k, v in sp.phase_ms.items():
+            state["phase"][k] = state["phase"].get(k, 0.0) + v
 
     def allmax(v):
         t = torch.tensor([float(v)], dtype=torch.float64, device=dev)
@@ -198,6 +200,7 @@ def run_multi(args, rank, world, local, dev, dist):
     torch.cuda.synchronize()
     dist.barrier()
     torch.cuda.synchronize()
+    state["phase"] = {}
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage = {"ms_ms": 0.0, "sort_ms": 0.0, "emit_ms": 0.0, "ms_kernel_ms": 0.0, "pack_ms": 0.0}
     launches = 0
@@ -271,6 +274,7 @@ def run_multi(args, rank, world, local, dev, dist):
                        "device_ms_per_step_rank0": dev_ms_local / args.steps,
                        "kernel_stage_ms_max": lib_ms_max,
                        "stage_ms_rank0": {k: v / args.steps for k, v in stage.items()},
+                       "phase_ms_rank0": {k: round(v / args.steps, 3) for k, v in state["phase"].items()},
                        "exchange_bytes_per_step": comm_bytes, "collectives_per_step": sp.collectives,
                        "rank_rounds": sp.rank_rounds,
                        "index_ms": {"sa_build_gpu": st0["sa_build_ms"], "index_build": st0["index_build_ms"]}},
@@ -330,6 +334,9 @@ def main():
     nsym = N - ndocs
     x = P.augment(ref.cpu().numpy())
     ctx = P.Context(local)
+    for kv in os.environ.get("CMSBWT_PARAMS", "").split():          # tuning experiments only
+        k, v = kv.split("=")
+        ctx.set_param(k, int(v))
     ctx.index_upload(x)                       # SA + index built on the GPU, timed separately
     st0 = ctx.stats()
 

@@ -94,6 +94,14 @@ int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
       cudaGetLastError();
     }
   }
+  else if (!strcmp(name, "scatter_mb")) { if (v < 0) return CMSBWT_E_ARG; c->scatter_mb = v; }
+  else if (!strcmp(name, "l2_fetch")) {
+    // device-wide L2 fetch granularity hint (32, 64 or 128 bytes): the path is dominated by random
+    // 4..16-byte gathers, which a 64/128-byte fetch turns into 2-4x the DRAM traffic
+    if (v != 32 && v != 64 && v != 128) return CMSBWT_E_ARG;
+    cudaSetDevice(c->dev);
+    if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v) != cudaSuccess) { cudaGetLastError(); return CMSBWT_E_CUDA; }
+  }
   else if (!strcmp(name, "tile_budget")) { if (v < 0) return CMSBWT_E_ARG; c->tile_budget = v; }
   else return CMSBWT_E_ARG;
   return CMSBWT_OK;

@@ -167,6 +167,7 @@ struct cmsbwt_ctx {
   i64 skip_min = 20;         // fast path: try the G skip for matches at least this long
   i64 fast = 1;              // 0 = always use the general 8-bit kernel
   i64 ms_occ = 10;           // fast path: resident CTAs per SM the MS kernel is compiled for (8, 10, 12)
+  i64 scatter_mb = 48;       // random 4-byte scatters run in passes over target regions of this many MB (L2)
   i64 tile_budget = 1ll << 36; // stage 2: brute-force tile counting up to this many pair tests per job
 };
 

@@ -35,11 +35,16 @@ __global__ void k_tr_gs32(const u32 *key, u32 n, u32 *gs) {
   gs[j] = (j == 0 || key[j] != key[j - 1]) ? j : 0;
 }
 // rank[id] = group start; tie flag = group has more than one member
-__global__ void k_tr_rank0(const u32 *key, const u32 *id, const u32 *gs, u32 n, u32 base, u32 *rank, u8 *tie) {
+// The scatter rank[id[j]] is a random 4-byte write per tail; done over the whole array it costs a
+// DRAM read-modify-write of a 64-byte granule each.  It is therefore run in passes over id ranges
+// [lo, hi) small enough for the written region to stay in L2 (the inputs are streamed past it).
+__global__ void k_tr_rank0(const u32 *key, const u32 *id, const u32 *gs, u32 n, u32 base, u32 *rank, u8 *tie,
+                           u32 lo, u32 hi, int first) {
   u32 j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  rank[id[j]] = base + gs[j];
-  tie[j] = (gs[j] != j) || (j + 1 < n && key[j + 1] == key[j]);
+  const u32 t = __ldcs(id + j), g = __ldcs(gs + j);
+  if (t >= lo && t < hi) rank[t] = base + g;
+  if (first) tie[j] = (g != j) || (j + 1 < n && __ldcs(key + j + 1) == __ldcs(key + j));
 }
 // subset keys: (current rank, secondary) with secondary = cls (round 0) or rank of the far tail
 __global__ void k_tr_key_cls(const u32 *sub, u32 m, const u32 *rank, const u64 *label, const u32 *cls32,
@@ -132,7 +137,17 @@ void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32
                                      ids.as<u32>(), (int)Tn, 0, bits, st));
   k_tr_gs32<<<gT, B, 0, st>>>(key32s.as<u32>(), Tn, gs.as<u32>());
   max_scan(tmp, gs.as<u32>(), Tn, st);
-  k_tr_rank0<<<gT, B, 0, st>>>(key32s.as<u32>(), ids.as<u32>(), gs.as<u32>(), Tn, rank_base, trank, tie.as<u8>());
+  {
+    const u64 region = (u64)(c->scatter_mb > 0 ? c->scatter_mb : 1 << 20) * (1u << 20) / 4;   // entries per pass
+    int first = 1;
+    for (u64 lo = 0; lo < Tn; lo += region) {
+      const u64 hi = lo + region < Tn ? lo + region : Tn;
+      k_tr_rank0<<<gT, B, 0, st>>>(key32s.as<u32>(), ids.as<u32>(), gs.as<u32>(), Tn, rank_base, trank, tie.as<u8>(),
+                                   (u32)lo, (u32)hi, first);
+      first = 0;
+      LAUNCH(c);
+    }
+  }
   c->launches += 8;
   // subset of tied tails (reuses id as the compacted list)
   u32 m = select_tied(tmp, ids.as<u32>(), tie.as<u8>(), Tn, id.as<u32>(), cnt, st);

@@ -52,32 +52,49 @@ __device__ __forceinline__ void put_range(TileEnt *re, const u32 *roff, u32 *rcu
   re[slot] = e;
 }
 
-__global__ void k_tile_scatter(const u32 *pos, const u32 *len, const u16 *cs, const u32 *toNext,
-                               const u64 *kappa, u64 H, const u32 *hoff, const u32 *roff, u32 *hcur,
-                               u32 *rcur, TileEnt *he, TileEnt *re) {
+// TS_ILP heads per thread: the slot atomics of all of them are in flight together (the kernel is
+// bound by the latency of atomic -> dependent store, not by bandwidth)
+#define TS_ILP 4
+__global__ void __launch_bounds__(256) k_tile_scatter(const u32 *pos, const u32 *len, const u16 *cs,
+                                                      const u32 *toNext, const u64 *kappa, u64 H, const u32 *hoff,
+                                                      const u32 *roff, u32 *hcur, u32 *rcur, TileEnt *he,
+                                                      TileEnt *re) {
   const int lane = threadIdx.x & 31;
-  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  bool in = i < H && len[i] != 0;
-  u32 p = in ? pos[i] : 0, tn = in ? toNext[i] : 0;
-  u64 kap = in ? kappa[i] : 0;
-  if (in) {
-    u32 t = p >> LT_SHIFT;
-    u32 slot = hoff[t] + atomicAdd(hcur + t, 1u);
-    TileEnt e; e.a = (u32)i; e.b = (p & (LT_W - 1)) | ((u32)(cs[i] & 0xFF) << 8); e.kappa = kap;
-    he[slot] = e;
+  const u64 i0 = (u64)blockIdx.x * (blockDim.x * TS_ILP) + threadIdx.x;
+  u32 p[TS_ILP], tn[TS_ILP], c8[TS_ILP], slot[TS_ILP];
+  u64 kap[TS_ILP];
+  bool in[TS_ILP];
+#pragma unroll
+  for (int k = 0; k < TS_ILP; k++) {
+    const u64 i = i0 + (u64)k * blockDim.x;
+    in[k] = i < H && len[i] != 0;
+    p[k] = in[k] ? pos[i] : 0; tn[k] = in[k] ? toNext[i] : 0;
+    kap[k] = in[k] ? kappa[i] : 0; c8[k] = in[k] ? (u32)(cs[i] & 0xFF) : 0;
   }
-  u32 ta = (p + 1) >> LT_SHIFT, tb = (p + tn) >> LT_SHIFT;
-  u32 nt = (in && tn) ? tb - ta + 1 : 0;
-  if (nt && nt <= 8)
-    for (u32 t = ta; t <= tb; t++) put_range(re, roff, rcur, t, p, tn, kap);
-  unsigned big = __ballot_sync(0xffffffffu, nt > 8);
-  while (big) {
-    int src = __ffs(big) - 1;
-    big &= big - 1;
-    u32 a = __shfl_sync(0xffffffffu, ta, src), m = __shfl_sync(0xffffffffu, nt, src);
-    u32 bp = __shfl_sync(0xffffffffu, p, src), btn = __shfl_sync(0xffffffffu, tn, src);
-    u64 bk = __shfl_sync(0xffffffffu, kap, src);
-    for (u32 k = lane; k < m; k += 32) put_range(re, roff, rcur, a + k, bp, btn, bk);
+#pragma unroll
+  for (int k = 0; k < TS_ILP; k++)
+    if (in[k]) { const u32 t = p[k] >> LT_SHIFT; slot[k] = hoff[t] + atomicAdd(hcur + t, 1u); }
+#pragma unroll
+  for (int k = 0; k < TS_ILP; k++)
+    if (in[k]) {
+      TileEnt e; e.a = (u32)(i0 + (u64)k * blockDim.x); e.b = (p[k] & (LT_W - 1)) | (c8[k] << 8); e.kappa = kap[k];
+      he[slot[k]] = e;
+    }
+#pragma unroll
+  for (int k = 0; k < TS_ILP; k++) {
+    const u32 ta = (p[k] + 1) >> LT_SHIFT, tb = (p[k] + tn[k]) >> LT_SHIFT;
+    const u32 nt = (in[k] && tn[k]) ? tb - ta + 1 : 0;
+    if (nt && nt <= 8)
+      for (u32 t = ta; t <= tb; t++) put_range(re, roff, rcur, t, p[k], tn[k], kap[k]);
+    unsigned big = __ballot_sync(0xffffffffu, nt > 8);
+    while (big) {
+      int src = __ffs(big) - 1;
+      big &= big - 1;
+      u32 a = __shfl_sync(0xffffffffu, ta, src), m = __shfl_sync(0xffffffffu, nt, src);
+      u32 bp = __shfl_sync(0xffffffffu, p[k], src), btn = __shfl_sync(0xffffffffu, tn[k], src);
+      u64 bk = __shfl_sync(0xffffffffu, kap[k], src);
+      for (u32 kk = lane; kk < m; kk += 32) put_range(re, roff, rcur, a + kk, bp, btn, bk);
+    }
   }
 }
 
@@ -144,15 +161,23 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   TileEnt *s_he = (TileEnt *)smem;              // hc heads, grouped by position
   u64 *s_rk = (u64 *)(s_he + hc);               // rc range kappas, grouped by bucket
   u32 *s_rl = (u32 *)(s_rk + rc);               // their lo | hi << 16
-  const u32 npiv = rc < LT_NB - 1 ? rc : LT_NB - 1;
+  // number of kappa buckets by depth: a shallow tile is cheaper by plain pair tests than by the
+  // fixed cost of LT_NB difference rows
+  const u32 NB = rc <= 48 ? 1u : rc <= 160 ? 4u : rc <= 512 ? 8u : (u32)LT_NB;
+  const u32 npiv = NB - 1;                      // rc >= npiv by construction
   s_cnt[tid] = 0; s_cur[tid] = 0;
-  for (u32 k = tid; k < (LT_NB + 1) * (LT_W + 1); k += LT_THREADS) (&s_C[0][0])[k] = 0;
+  for (u32 k = tid; k < NB * (LT_W + 1); k += LT_THREADS) (&s_C[0][0])[k] = 0;
   if (tid <= LT_NB) { s_bcnt[tid] = 0; s_bcur[tid] = 0; }
   if (tid < npiv) s_praw[tid] = re[r0 + (u32)(((u64)(tid + 1) * rc) / (npiv + 1))].kappa;
   {
     u32 p = ((t + t0) << LT_SHIFT) + tid;
     s_base[tid] = p < n ? base[isa[p]] : 0;
   }
+  // the first range / head of every thread stays in registers between the two passes
+  TileEnt re0, he0;
+  re0.a = re0.b = 0; re0.kappa = 0; he0 = re0;
+  if (tid < rc) re0 = re[r0 + tid];
+  if (tid < hc) he0 = he[h0 + tid];
   __syncthreads();
   if (tid < npiv) {                             // sort the pivots (distinct kappas) by rank counting
     const u64 mine = s_praw[tid];
@@ -163,14 +188,16 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   __syncthreads();
   // pass 1 over the ranges: bucket sizes and per-bucket coverage deltas; head counts per position
   for (u32 j = tid; j < rc; j += LT_THREADS) {
-    const TileEnt e = re[r0 + j];
+    const TileEnt e = j == tid ? re0 : re[r0 + j];
     u32 bk = 0;
     for (u32 k = 0; k < npiv; k++) bk += s_piv[k] <= e.kappa;
     atomicAdd(&s_bcnt[bk], 1u);
-    atomicAdd(&s_C[bk][e.a & 0xFFFF], 1);
-    atomicAdd(&s_C[bk][(e.a >> 16) + 1], -1);
+    if (NB > 1) {
+      atomicAdd(&s_C[bk][e.a & 0xFFFF], 1);
+      atomicAdd(&s_C[bk][(e.a >> 16) + 1], -1);
+    }
   }
-  for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[he[h0 + j].b & (LT_W - 1)], 1u);
+  for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[(j == tid ? he0 : he[h0 + j]).b & (LT_W - 1)], 1u);
   __syncthreads();
   u32 ex;
   BS(ts).ExclusiveSum(s_cnt[tid], ex);
@@ -178,30 +205,33 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   if (tid == LT_THREADS - 1) s_off[LT_W] = ex + s_cnt[tid];
   if (tid == 0) {
     u32 run = 0;
-    for (u32 k = 0; k <= LT_NB; k++) { s_boff[k] = run; run += s_bcnt[k]; }
-    s_boff[LT_NB + 1] = run;
+    for (u32 k = 0; k < NB; k++) { s_boff[k] = run; run += s_bcnt[k]; }
+    s_boff[NB] = run;
   }
-  // coverage per bucket: inclusive scan of every delta row (one warp per row, 8 entries per lane)
-  for (u32 row = warp; row <= LT_NB; row += LT_THREADS / 32) {
-    int v[8], sum = 0;
+  if (NB > 1) {
+    // coverage per bucket: inclusive scan of every delta row (one warp per row, 8 entries per lane)
+    for (u32 row = warp; row < NB; row += LT_THREADS / 32) {
+      int v[8], sum = 0;
 #pragma unroll
-    for (int k = 0; k < 8; k++) { sum += s_C[row][lane * 8 + k]; v[k] = sum; }
-    int incl = sum;
+      for (int k = 0; k < 8; k++) { sum += s_C[row][lane * 8 + k]; v[k] = sum; }
+      int incl = sum;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) { int o = __shfl_up_sync(0xffffffffu, incl, d); if ((int)lane >= d) incl += o; }
-    const int pre = incl - sum;
+      for (int d = 1; d < 32; d <<= 1) { int o = __shfl_up_sync(0xffffffffu, incl, d); if ((int)lane >= d) incl += o; }
+      const int pre = incl - sum;
 #pragma unroll
-    for (int k = 0; k < 8; k++) s_C[row][lane * 8 + k] = v[k] + pre;
-  }
-  __syncthreads();
-  {                                             // exclusive prefix over the buckets, per position
-    int run = 0;
-#pragma unroll
-    for (int bk = 0; bk <= LT_NB; bk++) { int c = s_C[bk][tid]; s_C[bk][tid] = run; run += c; }
+      for (int k = 0; k < 8; k++) s_C[row][lane * 8 + k] = v[k] + pre;
+    }
+    __syncthreads();
+    {                                           // exclusive prefix over the buckets, per position
+      int run = 0;
+      for (u32 bk = 0; bk < NB; bk++) { int c = s_C[bk][tid]; s_C[bk][tid] = run; run += c; }
+    }
+  } else {
+    __syncthreads();
   }
   // pass 2: ranges grouped by bucket, heads grouped by position
   for (u32 j = tid; j < rc; j += LT_THREADS) {
-    const TileEnt e = re[r0 + j];
+    const TileEnt e = j == tid ? re0 : re[r0 + j];
     u32 bk = 0;
     for (u32 k = 0; k < npiv; k++) bk += s_piv[k] <= e.kappa;
     const u32 slot = s_boff[bk] + atomicAdd(&s_bcur[bk], 1u);
@@ -209,7 +239,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
     s_rl[slot] = e.a;
   }
   for (u32 j = tid; j < hc; j += LT_THREADS) {
-    TileEnt e = he[h0 + j];
+    TileEnt e = j == tid ? he0 : he[h0 + j];
     u32 q = e.b & (LT_W - 1);
     s_he[s_off[q] + atomicAdd(&s_cur[q], 1u)] = e;
   }
@@ -222,7 +252,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
     for (u32 jj = s_off[q]; jj < s_off[q + 1]; jj++) w += s_he[jj].kappa < kap;
     u32 bk = 0;
     for (u32 k = 0; k < npiv; k++) bk += s_piv[k] <= kap;
-    w += (u32)s_C[bk][q];
+    if (NB > 1) w += (u32)s_C[bk][q];
     for (u32 r = s_boff[bk]; r < s_boff[bk + 1]; r++) {
       const u32 lh = s_rl[r];
       w += (s_rk[r] < kap) & ((lh & 0xFFFF) <= q) & (q <= (lh >> 16));
@@ -286,7 +316,7 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   c->t_re.alloc(((size_t)R + 1) * sizeof(TileEnt), st);
   CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));      // reused as cursors
   CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
-  k_tile_scatter<<<gH, B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
+  k_tile_scatter<<<(u32)((H + B * TS_ILP - 1) / (B * TS_ILP)), B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                    c->h_toNext.as<u32>(), kappa, H, c->t_hoff.as<u32>(), c->t_roff.as<u32>(),
                                    hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>());
   c->launches += 2;

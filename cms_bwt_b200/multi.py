@@ -119,6 +119,16 @@ class ShardedPath:
         self.comm = comm if comm is not None else DistComm(group)
         self.comm_bytes = 0
         self.collectives = 0
+        self.phase_ms = {}
+        self._t = None
+
+    def _mark(self, name):
+        """wall time of the phase that just ended (every device step and collective is synchronous)"""
+        import time
+        now = time.perf_counter()
+        if self._t is not None and name:
+            self.phase_ms[name] = self.phase_ms.get(name, 0.0) + (now - self._t) * 1e3
+        self._t = now
 
     # ---- collectives ---------------------------------------------------------------------------
     def _sync(self):
@@ -166,6 +176,7 @@ class ShardedPath:
     # ---- the path ------------------------------------------------------------------------------
     def run(self, N_local, ndocs_local):
         ops, W, R = self.ops, self.world, self.rank
+        self._mark(None)
         g = self._allgather_ints([N_local, ndocs_local])
         N_total = sum(x[0] for x in g)
         ndocs_total = sum(x[1] for x in g)
@@ -173,7 +184,9 @@ class ShardedPath:
         self.N_total, self.ndocs_total, self.doc_base = N_total, ndocs_total, doc_base
 
         # -- stage 2a: global order of the tails
+        self._mark("x_sizes")
         Tn = ops.tails(doc_base)
+        self._mark("d_tails")
         ks, cs = ops.tail_keys(), ops.tail_cls()
         splitters = self._splitters(ks, Tn)
         b = [0] + ops.lower_bound("tail_keys", splitters) + [Tn]
@@ -186,9 +199,12 @@ class ShardedPath:
         rank_base = sum(x[0] for x in Ms[:R])
         if sum(x[0] for x in Ms) >= 2 ** 32:
             raise CmsBwtError(-3, "more than 2^32 tails in the collection")
+        self._mark("x_tails")
         r_out, t_out = ops.rank_owner(rk, rc, M, rank_base)
+        self._mark("d_rank_owner")
         rs = self._a2a(r_out, recv, send)
         ts = self._a2a(t_out, recv, send)
+        self._mark("x_ranks")
         m = ops.rank_apply(rs, ts)
         self.rank_rounds = 0
         while True:
@@ -201,7 +217,9 @@ class ShardedPath:
             self.rank_rounds += 1
 
         # -- stage 2b: tile entries to the owners of the reference-position ranges
+        self._mark("d_x_refine")
         tp = ops.tiles_local(W)
+        self._mark("d_tiles_local")
         hoff, roff = ops.buffer("tile_hoff"), ops.buffer("tile_roff")
         edge = torch.arange(0, W * tp + 1, tp, device=hoff.device)
         hb = [int(v) & 0xFFFFFFFF for v in hoff[edge].cpu().tolist()]
@@ -219,7 +237,9 @@ class ShardedPath:
         roffs = self._a2a(roff[rows].contiguous(), eq, eq)
         he_slab = [sum(hrecv[:s]) for s in range(W)]
         re_slab = [sum(rrecv[:s]) for s in range(W)]
+        self._mark("x_tiles")
         maxent = ops.tiles_merge(W, R, he, re, hoffs, roffs, he_slab, re_slab, ndocs_total)
+        self._mark("d_tiles_merge")
         gmax = max(x[0] for x in self._allgather_ints([maxent]))
         if gmax > TILE_MAX_ENTRIES:
             raise CmsBwtError(-3, "a tile holds %d entries (limit %d): collection too deep for the "
@@ -232,14 +252,18 @@ class ShardedPath:
         self.comm_bytes += cov_full.numel() * 4
 
         # -- stage 3: own output range + placements to the owners of the output ranges
+        self._mark("x_cov")
         obeg, olen, chunk = ops.emit(cov_full, N_total, W, R, doc_base)
+        self._mark("d_emit")
         plc = ops.buffer("placements")
         P = plc.numel()
         pb = [0] + ops.lower_bound("placements", [(d * chunk) << 8 for d in range(1, W)]) + [P]
         psend = [pb[d + 1] - pb[d] for d in range(W)]
         precv = self._a2a_counts(psend)
         got = self._a2a(plc, psend, precv)
+        self._mark("x_placements")
         ops.apply(got, sum(precv))
+        self._mark("d_apply")
         self.out_begin, self.out_len = obeg, olen
         return ops.buffer("result")
 

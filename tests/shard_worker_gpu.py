@@ -8,7 +8,7 @@ import torch
 import torch.distributed as dist
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-for p in (HERE, os.path.dirname(HERE)):
+for p in (HERE, os.path.dirname(HERE), os.path.join(os.path.dirname(HERE), "tools")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
