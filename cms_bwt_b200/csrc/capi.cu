@@ -94,6 +94,7 @@ int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
       cudaGetLastError();
     }
   }
+  else if (!strcmp(name, "slots")) { c->use_slots = v != 0; }          // takes effect at the next index_upload
   else if (!strcmp(name, "scatter_mb")) { if (v < 0) return CMSBWT_E_ARG; c->scatter_mb = v; }
   else if (!strcmp(name, "l2_fetch")) {
     // device-wide L2 fetch granularity hint (32, 64 or 128 bytes): the path is dominated by random
@@ -559,7 +560,7 @@ int cmsbwt_shard_tiles_merge(cmsbwt_ctx *c, uint32_t world, uint32_t rank, const
 int cmsbwt_shard_emit(cmsbwt_ctx *c, const void *d_cov_full, uint64_t N_total, uint32_t world, uint32_t rank,
                       uint64_t doc_base, uint64_t *out_begin, uint64_t *out_len, uint64_t *chunk_bytes) {
   if (!c || !d_cov_full || world != c->sh_world || rank != c->sh_rank) return fail(c, CMSBWT_E_ARG, "shard_emit");
-  if (c->tile_maxent > 12288) return fail(c, CMSBWT_E_LIMIT, "a tile holds more entries than shared memory");
+  if (c->tile_maxent > 11000) return fail(c, CMSBWT_E_LIMIT, "a tile holds more entries than shared memory");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   Timer t(c->st);

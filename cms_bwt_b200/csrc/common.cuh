@@ -123,7 +123,7 @@ struct cmsbwt_ctx {
   // fast path (pure-ACGT reference): packed reference, {key, sa} per rank
   bool pure = false;         // x = ACGT* + augmentation, x[n_acgt] < 'A'
   u32 n_acgt = 0;
-  DBuf d_sak;
+  DBuf d_sak, d_slots;       // {key, sa} per rank; k-mer slot table (64 B per k-mer)
   u64 *xp = nullptr;         // packed reference, inside d_ktab's allocation
   size_t hot_bytes = 0;      // k-mer table + packed reference (L2 persistence window)
   i64 l2_pin = 0;
@@ -166,8 +166,9 @@ struct cmsbwt_ctx {
   i64 kmer_k = 0;            // 0 = auto
   i64 skip_min = 20;         // fast path: try the G skip for matches at least this long
   i64 fast = 1;              // 0 = always use the general 8-bit kernel
-  i64 ms_occ = 10;           // fast path: resident CTAs per SM the MS kernel is compiled for (8, 10, 12)
-  i64 scatter_mb = 48;       // random 4-byte scatters run in passes over target regions of this many MB (L2)
+  i64 ms_occ = 8;            // fast path: resident CTAs per SM the MS kernel is compiled for (8, 10, 12)
+  i64 use_slots = 1;         // fast path: k-mer slot table (one 64-byte read per search) on / off
+  i64 scatter_mb = 64;       // random 4-byte scatters run in passes over target regions of this many MB (L2)
   i64 tile_budget = 1ll << 36; // stage 2: brute-force tile counting up to this many pair tests per job
 };
 

@@ -191,8 +191,8 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   tmp.alloc(tb, st);
   int sms = 148, occ = 4;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->dev);
-  void (*kern)(MsfParams) = c->ms_occ >= 12 ? k_ms_fast<12> : c->ms_occ >= 10 ? k_ms_fast<10> : k_ms_fast<8>;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 128, 0);
+  void (*kern)(MsfParams) = c->ms_occ >= 12 ? k_ms_fast<12> : c->ms_occ >= 10 ? k_ms_fast<10> : c->ms_occ >= 8 ? k_ms_fast<8> : k_ms_fast<6>;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 128, MSF_STG * 128 * sizeof(uint4));
   if (occ < 1) occ = 1;
   // pool: batches of MSF_RB records; every window wastes at most one partly filled batch
   u64 rec_est = c->head_hint ? c->head_hint + c->head_hint / 8 : N / 16;
@@ -205,6 +205,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     CK(cudaMemsetAsync(counter.p, 0, 8, st));
     CK(cudaMemsetAsync(nbused.p, 0, 4, st));
     MsfParams P;
+    P.slots = c->d_slots.as<u64>();
     P.xp = c->xp; P.x8 = c->ix.x; P.sak = c->d_sak.as<u64>(); P.ktab = c->ix.ktab; P.G = c->ix.G;
     P.n = c->ix.n; P.n_acgt = c->n_acgt; P.k = c->ix.k;
     P.tp = c->d_tp.as<u64>(); P.N = N; P.seps = c->d_seps.as<u64>(); P.nseps = nseps; P.wsep = wsep.as<u32>();
@@ -230,7 +231,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
       apw.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
       cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &apw);
     }
-    kern<<<grid, 128, 0, st>>>(P);
+    kern<<<grid, 128, MSF_STG * 128 * sizeof(uint4), st>>>(P);
     if (c->l2_pin && c->l2_persist_max) {
       apw.accessPolicyWindow.num_bytes = 0;
       cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &apw);

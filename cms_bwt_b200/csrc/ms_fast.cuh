@@ -66,6 +66,8 @@ static inline msf_u64 msf_brev64_host(msf_u64 v) {
 #endif
 
 #define MSF_RB 32                   // head records per pool batch (32 x 16 B; one atomic per batch)
+#define MSF_STG 4                   // head records staged per lane before one 64-byte store to the pool
+struct msf_rec4 { msf_u32 x, y, z, w; };
 #define MSF_NOB 0xFFFFFFFFu
 #define MSF_BADB 0xFFFFFFFEu
 #define MSF_INVALID 0xFFFFFFFFu
@@ -121,8 +123,21 @@ MSF_HD msf_u32 msf_make_key(const msf_u64 *xp, msf_u32 s, msf_u32 n_acgt, int k)
   return key;
 }
 
+// ---- k-mer slot table -----------------------------------------------------------------------------
+// slots[code * 8 .. code * 8 + 8): the {key, sa} entries of the k-mer's bucket (sorted, as in sak),
+// padded with MSF_SLOT_EMPTY; a bucket of more than 8 suffixes keeps its first 7 and ends with
+// MSF_SLOT_OVF (the lane then takes the ktab + sak path).  One aligned 64-byte read -- one DRAM
+// granule -- replaces the dependent ktab -> sak round trips of the common case.
+#define MSF_SLOT_EMPTY 0xFFFFFFFFFFFFFFFFull
+#define MSF_SLOT_OVF 0xFFFFFFFEFFFFFFFFull
+MSF_HD msf_u64 msf_slot_entry(const msf_u64 *sak, msf_u32 lb, msf_u32 cnt, int j) {
+  if (cnt > 8 && j == 7) return MSF_SLOT_OVF;
+  return (msf_u32)j < cnt ? sak[lb + j] : MSF_SLOT_EMPTY;
+}
+
 struct MsfParams {
   // reference index
+  const msf_u64 *slots;   // k-mer slot table (NULL: every search goes through ktab + sak)
   const msf_u64 *xp;      // packed pure prefix of x (n_acgt bases), zero padded
   const msf_u8 *x8;       // augmented reference bytes
   const msf_u64 *sak;     // per SA rank: key (low 32 bits) | sa (high 32 bits)
@@ -160,7 +175,21 @@ struct MsfLane {
   msf_u32 tkey, lo, hi, rb, prevkey, prevsa, haveprev;
   msf_u32 pos, len, sm;
   msf_u32 chb;            // code of the base before position i (4 = not loaded yet)
+#if !defined(__CUDA_ARCH__)
+  msf_rec4 hstage[MSF_STG];
+#endif
 };
+
+// Head records are staged four at a time (64 bytes = one DRAM granule) before they go to the pool:
+// a lane emits a record every ~20 us, long after L2 has dropped the sector of its previous one, so
+// single 16-byte stores each cost a DRAM read-modify-write.  Device: shared memory, one column
+// per thread; host harness: inside the lane.
+#if defined(__CUDA_ARCH__)
+extern __shared__ uint4 msf_stage_smem[];
+#define MSF_STAGE(L, j) msf_stage_smem[(j) * blockDim.x + threadIdx.x]
+#else
+#define MSF_STAGE(L, j) (L).hstage[j]
+#endif
 
 MSF_HD void msf_store_rec(const MsfParams &P, msf_u64 slot, msf_u32 a, msf_u32 b, msf_u32 c, msf_u32 d) {
 #if defined(__CUDA_ARCH__)
@@ -169,6 +198,19 @@ MSF_HD void msf_store_rec(const MsfParams &P, msf_u64 slot, msf_u32 a, msf_u32 b
   msf_u32 *r = P.pool + 4 * slot;
   r[0] = a; r[1] = b; r[2] = c; r[3] = d;
 #endif
+}
+
+// writes the last cnt staged records of the current batch (they end at record L.fill)
+MSF_HD void msf_flush(const MsfParams &P, MsfLane &L, msf_u32 cnt) {
+  if (L.curb == MSF_BADB || L.curb == MSF_NOB) return;
+  const msf_u64 base = (msf_u64)L.curb * MSF_RB + (L.fill - cnt);
+  for (msf_u32 j = 0; j < cnt; j++) {
+#if defined(__CUDA_ARCH__)
+    ((uint4 *)P.pool)[base + j] = MSF_STAGE(L, j);
+#else
+    msf_store_rec(P, base + j, MSF_STAGE(L, j).x, MSF_STAGE(L, j).y, MSF_STAGE(L, j).z, MSF_STAGE(L, j).w);
+#endif
+  }
 }
 
 MSF_HD void msf_emit(const MsfParams &P, MsfLane &L, msf_u32 rel, msf_u32 pos, msf_u32 len, msf_u32 cs) {
@@ -185,8 +227,16 @@ MSF_HD void msf_emit(const MsfParams &P, MsfLane &L, msf_u32 rel, msf_u32 pos, m
     L.curb = nb;
     L.fill = 0;
   }
-  if (L.curb != MSF_BADB) msf_store_rec(P, (msf_u64)L.curb * MSF_RB + L.fill, rel, pos, len, cs);
+  {
+    const msf_u32 k = L.fill & (MSF_STG - 1);
+#if defined(__CUDA_ARCH__)
+    MSF_STAGE(L, k) = make_uint4(rel, pos, len, cs);
+#else
+    MSF_STAGE(L, k).x = rel; MSF_STAGE(L, k).y = pos; MSF_STAGE(L, k).z = len; MSF_STAGE(L, k).w = cs;
+#endif
+  }
   L.fill++;
+  if ((L.fill & (MSF_STG - 1)) == 0) msf_flush(P, L, MSF_STG);
   L.cnt++;
 }
 
@@ -321,6 +371,16 @@ MSF_HD void msf_ext_done(const MsfParams &P, MsfLane &L, msf_u32 res, msf_u32 bm
   L.sm = xb > tb ? 1u : 0u;
 }
 
+MSF_HD void msf_load_slot(const msf_u64 *sp, msf_u64 *e) {
+#if defined(__CUDA_ARCH__)
+  const ulonglong2 *q = (const ulonglong2 *)sp;
+  const ulonglong2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+  e[0] = a.x; e[1] = a.y; e[2] = b.x; e[3] = b.y; e[4] = c.x; e[5] = c.y; e[6] = d.x; e[7] = d.y;
+#else
+  for (int j = 0; j < 8; j++) e[j] = sp[j];
+#endif
+}
+
 // predecessor (prevkey/prevsa, if any) and successor (skey/ssa, if found) are known by key only
 MSF_HD msf_u32 msf_decide(const MsfParams &P, MsfLane &L, bool found, msf_u32 skey, msf_u32 ssa) {
   const msf_u32 KL = (msf_u32)P.k + 16;
@@ -357,6 +417,7 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
     // fall through
     case MSF_S_POS: {
       if (L.i >= L.w1) {                                  // close the window
+        if (L.fill & (MSF_STG - 1)) msf_flush(P, L, L.fill & (MSF_STG - 1));
         P.wcnt[L.w] = L.cnt;
         P.wlastpos[L.w] = L.prevterm ? MSF_INVALID : L.prevpos - (msf_u32)(L.i - L.w1);
         L.state = MSF_S_FETCH;
@@ -378,6 +439,33 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
       msf_u64 be = msf_be64(tw);
       msf_u32 code = (msf_u32)(be >> (64 - 2 * P.k));
       L.tkey = (msf_u32)((be << (2 * P.k)) >> 32);
+      if (P.slots) {
+        msf_u64 e[8];
+        msf_load_slot(P.slots + (msf_u64)code * 8, e);
+        if (e[0] == MSF_SLOT_EMPTY) { act = MSF_ACT_GENERIC; break; }        // the k-mer does not occur
+        if (e[7] != MSF_SLOT_OVF) {
+          // pred = last entry with a smaller key, succ = first entry with a key >= the text's, nxt =
+          // the entry after succ (empty entries hold the largest key and sort last).  Written as
+          // running selections over constant indices so that the slot stays in registers.
+          msf_u64 pred = 0, succ = MSF_SLOT_EMPTY, nxt = MSF_SLOT_EMPTY;
+#pragma unroll
+          for (int j = 0; j < 8; j++)
+            if ((msf_u32)e[j] < L.tkey) pred = e[j];
+#pragma unroll
+          for (int j = 7; j >= 0; j--)
+            if (!((msf_u32)e[j] < L.tkey)) { nxt = succ; succ = e[j]; }
+          L.haveprev = (msf_u32)e[0] < L.tkey;
+          L.prevkey = (msf_u32)pred; L.prevsa = (msf_u32)(pred >> 32);
+          if (succ == MSF_SLOT_EMPTY) act = msf_decide(P, L, false, 0, 0);   // every key is smaller
+          else {
+            const msf_u32 key = (msf_u32)succ, s = (msf_u32)(succ >> 32);
+            if (key != L.tkey) act = msf_decide(P, L, true, key, s);
+            else if (nxt != MSF_SLOT_EMPTY && (msf_u32)nxt == L.tkey) act = MSF_ACT_GENERIC;   // repeated key
+            else act = msf_start_ext(P, L, s);
+          }
+          break;
+        }
+      }
       msf_u32 lb = MSF_LD32(P.ktab + code), rb = MSF_LD32(P.ktab + code + 1);
       if (lb == rb) { act = MSF_ACT_GENERIC; break; }
       L.lo = lb; L.hi = rb; L.rb = rb; L.haveprev = 0;

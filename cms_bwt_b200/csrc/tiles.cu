@@ -19,7 +19,7 @@
 #define LT_SHIFT 8
 #define LT_W (1u << LT_SHIFT)
 #define LT_THREADS 256
-#define LT_MAX_ENTRIES 12288          // heads + ranges of one tile that fit shared memory (16 B each)
+#define LT_MAX_ENTRIES 11000          // heads + ranges of one tile that fit shared memory (16 B each)
 
 struct __align__(16) TileEnt { u32 a, b; u64 kappa; };   // head: a = id, b = q | ch << 8; range: a = lo | hi << 16
 
@@ -377,7 +377,7 @@ void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out) {
     c->h_within.alloc(H * 4, st); c->h_off.alloc(H * 8, st);
     wo = c->h_within.as<u32>(); oo = c->h_off.as<u64>();
   }
-  size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;     // heads 16 B, ranges 12 B each
+  size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;
   if (sm > 40 * 1024)
     CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_place<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),

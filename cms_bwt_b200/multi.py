@@ -25,7 +25,7 @@ import torch.distributed as dist
 from . import lib, CmsBwtError, MODE_PLAIN
 
 SAMPLES_PER_RANK = 1024
-TILE_MAX_ENTRIES = 12288          # tiles.cu LT_MAX_ENTRIES
+TILE_MAX_ENTRIES = 11000          # tiles.cu LT_MAX_ENTRIES
 
 
 def shard_documents(doc_lengths, world):

@@ -28,7 +28,7 @@ void msf_host_steps(unsigned long long *out) { for (int i = 0; i < 16; i++) { ou
 // (reference or text not pure ACGT), -2 on pool overflow.
 // outputs: per-position dump arrays (N entries) and the compacted head list (capacity N).
 long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plcp_prime, const u8 *text,
-                       u64 N, u32 WL, int k, u32 skip_min, u32 nlanes, u32 *dpos, u32 *dlen, u8 *dsm,
+                       u64 N, u32 WL, int k, u32 skip_min, u32 nlanes, int use_slots, u32 *dpos, u32 *dlen, u8 *dsm,
                        u8 *dhead, u64 *hg, u32 *hpos, u32 *hlen, uint16_t *hcs) {
   // ---- eligibility (capi.cu: index purity) ----
   u32 n_acgt = 0;
@@ -62,6 +62,10 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   std::vector<u64> sak(n);
   for (u32 r = 0; r < n; r++)
     sak[r] = (u64)msf_make_key(xp.data(), (u32)sa[r], n_acgt, k) | ((u64)(u32)sa[r] << 32);
+  std::vector<u64> slots(K * 8);
+  for (u64 code = 0; code < K; code++)
+    for (int j = 0; j < 8; j++)
+      slots[code * 8 + j] = msf_slot_entry(sak.data(), ktab[code], ktab[code + 1] - ktab[code], j);
   std::vector<u32> G(n + 8);
   for (u32 i = 0; i < n; i++) G[i] = i + (u32)plcp_prime[i];
   // ---- text ----
@@ -80,6 +84,7 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   u32 nb_used = 0, flags[2] = {0, 0};
   unsigned long long counter = 0;
   MsfParams P;
+  P.slots = use_slots ? slots.data() : nullptr;
   P.xp = xp.data(); P.x8 = x8.data(); P.sak = sak.data(); P.ktab = ktab.data(); P.G = G.data();
   P.n = n; P.n_acgt = n_acgt; P.k = k;
   P.tp = tp.data(); P.N = N; P.seps = seps.data(); P.nseps = nseps; P.wsep = wsep.data();

@@ -34,7 +34,7 @@ def harness():
     L = C.CDLL(SO)
     L.msf_host_run.restype = C.c_longlong
     L.msf_host_run.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
-                               C.c_uint32, C.c_int, C.c_uint32, C.c_uint32] + [C.c_void_p] * 8
+                               C.c_uint32, C.c_int, C.c_uint32, C.c_uint32, C.c_int] + [C.c_void_p] * 8
     return L
 
 
@@ -49,7 +49,10 @@ def pick_k(n):
     return k
 
 
-def run_case(L, x, text, WL, k=None, skip_min=20, nlanes=7, desc=""):
+def run_case(L, x, text, WL, k=None, skip_min=20, nlanes=7, desc="", slots=None):
+    if slots is None:                      # both search paths: k-mer slot table, and ktab + sak only
+        r = run_case(L, x, text, WL, k, skip_min, nlanes, desc + " [slots]", slots=1)
+        return r if r is None else run_case(L, x, text, WL, k, skip_min, nlanes, desc + " [ktab]", slots=0)
     o = O.Oracle(x)
     sa = o.sa
     pp = o.plcp_prime.astype(np.int32)
@@ -60,7 +63,7 @@ def run_case(L, x, text, WL, k=None, skip_min=20, nlanes=7, desc=""):
     hg = np.zeros(N, np.uint64); hpos = np.zeros(N, np.uint32); hlen = np.zeros(N, np.uint32)
     hcs = np.zeros(N, np.uint16)
     xc = np.ascontiguousarray(x); tc = np.ascontiguousarray(text)
-    H = L.msf_host_run(_p(xc), len(xc), _p(sa), _p(pp), _p(tc), N, WL, k, skip_min, nlanes,
+    H = L.msf_host_run(_p(xc), len(xc), _p(sa), _p(pp), _p(tc), N, WL, k, skip_min, nlanes, slots,
                        _p(dpos), _p(dlen), _p(dsm), _p(dhd), _p(hg), _p(hpos), _p(hlen), _p(hcs))
     if H == -1:
         return None
