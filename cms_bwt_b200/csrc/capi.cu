@@ -455,7 +455,7 @@ int cmsbwt_shard_buffer(cmsbwt_ctx *c, const char *name, const void **dptr, uint
   else if (!strcmp(name, "tile_hoff")) { p = c->t_hoff.p; n = (u64)c->sh_tp * c->sh_world + 1; }   // u32
   else if (!strcmp(name, "tile_roff")) { p = c->t_roff.p; n = (u64)c->sh_tp * c->sh_world + 1; }   // u32
   else if (!strcmp(name, "cov_slice")) { p = c->sh_cov.p; n = (u64)c->sh_tp * 256; }               // u32
-  else if (!strcmp(name, "placements")) { p = c->sh_plc.p; n = c->sh_nplc; }      // u64, sorted
+  else if (!strcmp(name, "placements")) { p = c->sh_plc.p; n = c->sh_nplc; }      // u64, grouped by destination
   else if (!strcmp(name, "result")) { p = c->d_out.p; n = c->out_bytes; }         // u8
   else return fail(c, CMSBWT_E_ARG, "unknown shard buffer");
   *dptr = p;
@@ -470,7 +470,7 @@ int cmsbwt_shard_lower_bound(cmsbwt_ctx *c, const char *name, const uint64_t *va
   uint64_t n = 0;
   int rc = cmsbwt_shard_buffer(c, name, &p, &n);
   if (rc) return rc;
-  const bool is32 = !strcmp(name, "tail_keys"), is64 = !strcmp(name, "placements");
+  const bool is32 = !strcmp(name, "tail_keys"), is64 = false;
   if (!is32 && !is64) return fail(c, CMSBWT_E_ARG, "lower_bound: not a sorted buffer");
   if (count == 0) return CMSBWT_OK;
   GUARD_BEGIN
@@ -558,8 +558,9 @@ int cmsbwt_shard_tiles_merge(cmsbwt_ctx *c, uint32_t world, uint32_t rank, const
 }
 
 int cmsbwt_shard_emit(cmsbwt_ctx *c, const void *d_cov_full, uint64_t N_total, uint32_t world, uint32_t rank,
-                      uint64_t doc_base, uint64_t *out_begin, uint64_t *out_len, uint64_t *chunk_bytes) {
-  if (!c || !d_cov_full || world != c->sh_world || rank != c->sh_rank) return fail(c, CMSBWT_E_ARG, "shard_emit");
+                      uint64_t doc_base, uint64_t *out_begin, uint64_t *out_len, uint64_t *plc_counts) {
+  if (!c || !d_cov_full || world != c->sh_world || rank != c->sh_rank || world > 64)
+    return fail(c, CMSBWT_E_ARG, "shard_emit");
   if (c->tile_maxent > 11000) return fail(c, CMSBWT_E_LIMIT, "a tile holds more entries than shared memory");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
@@ -568,7 +569,7 @@ int cmsbwt_shard_emit(cmsbwt_ctx *c, const void *d_cov_full, uint64_t N_total, u
   c->stats.emit_ms = t.stop();
   if (out_begin) *out_begin = c->sh_obeg;
   if (out_len) *out_len = c->sh_olen;
-  if (chunk_bytes) *chunk_bytes = c->sh_chunk;
+  if (plc_counts) for (u32 d = 0; d < world; d++) plc_counts[d] = c->sh_plc_cnt[d];
   GUARD_END(c)
   return CMSBWT_OK;
 }

@@ -154,6 +154,7 @@ struct cmsbwt_ctx {
   // shard state (shard.cu / tailrank.cu): locally sorted tail keys, tied subset, merged tiles
   DBuf sh_ks, sh_cs, sh_perm, sh_sub, sh_tiekeys, sh_cov, sh_plc, sh_base;
   u32 sh_m = 0, sh_round = 0;
+  std::vector<u64> sh_plc_cnt;                   // placements per destination rank
   u32 sh_world = 1, sh_rank = 0, sh_tp = 0;      // tiles per rank
   u64 sh_he = 0, sh_re = 0, sh_nplc = 0, sh_obeg = 0, sh_olen = 0, sh_chunk = 0, sh_Ntotal = 0;
   // stage 3

@@ -501,8 +501,43 @@ __global__ void k_sh_sentinel_plc(const u32 *len, const u16 *cs, const u32 *sexc
   plc[d] = ((doc_base + d) << 8) | (u64)(cs[i] & 0xFF);
 }
 
+// per-destination counts / scatter of placements (destination = offset / chunk), block-aggregated
+#define PLC_MAXW 64
+__global__ void __launch_bounds__(256) k_sh_plc_hist(const u64 *plc, u64 P, u64 chunk, u32 W,
+                                                     unsigned long long *cnt) {
+  __shared__ u32 s_c[PLC_MAXW];
+  if (threadIdx.x < PLC_MAXW) s_c[threadIdx.x] = 0;
+  __syncthreads();
+  for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < P; j += (u64)gridDim.x * blockDim.x)
+    atomicAdd(&s_c[(u32)((plc[j] >> 8) / chunk)], 1u);
+  __syncthreads();
+  if (threadIdx.x < W && s_c[threadIdx.x]) atomicAdd(cnt + threadIdx.x, (unsigned long long)s_c[threadIdx.x]);
+}
+__global__ void __launch_bounds__(256) k_sh_plc_scatter(const u64 *plc, u64 P, u64 chunk, u32 W,
+                                                        unsigned long long *cur, u64 *out) {
+  __shared__ u32 s_c[PLC_MAXW];
+  __shared__ unsigned long long s_b[PLC_MAXW];
+  // every block handles one contiguous slice: counts, one reservation per destination, scatter
+  const u64 per = (P + gridDim.x - 1) / gridDim.x;
+  const u64 a = (u64)blockIdx.x * per, b = min(P, a + per);
+  if (threadIdx.x < PLC_MAXW) s_c[threadIdx.x] = 0;
+  __syncthreads();
+  for (u64 j = a + threadIdx.x; j < b; j += blockDim.x) atomicAdd(&s_c[(u32)((plc[j] >> 8) / chunk)], 1u);
+  __syncthreads();
+  if (threadIdx.x < W) {
+    s_b[threadIdx.x] = s_c[threadIdx.x] ? atomicAdd(cur + threadIdx.x, (unsigned long long)s_c[threadIdx.x]) : 0ull;
+    s_c[threadIdx.x] = 0;
+  }
+  __syncthreads();
+  for (u64 j = a + threadIdx.x; j < b; j += blockDim.x) {
+    const u64 v = plc[j];
+    const u32 d = (u32)((v >> 8) / chunk);
+    out[s_b[d] + atomicAdd(&s_c[d], 1u)] = v;
+  }
+}
+
 // pass B for this device's tile range: (offset << 8 | symbol) per head entry, then this shard's
-// document terminators (offset = global document index); sorted by offset into sh_plc.
+// document terminators (offset = global document index); grouped by destination in sh_plc.
 void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
   cudaStream_t st = c->st;
   const u32 n = c->ix.n;
@@ -521,13 +556,24 @@ void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
                                            raw.as<u64>(), nullptr, nullptr);
   k_sh_sentinel_plc<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                                            c->s_sexcl.as<u32>(), H, doc_base, raw.as<u64>() + c->sh_he);
-  int bits = 9;
-  while (bits < 64 && (1ull << (bits - 8)) < c->sh_Ntotal) bits++;
-  size_t tb = 0;
-  cub::DeviceRadixSort::SortKeys(nullptr, tb, raw.as<u64>(), c->sh_plc.as<u64>(), (int)P, 0, bits, st);
-  tmp.alloc(tb, st);
-  CK(cub::DeviceRadixSort::SortKeys(tmp.p, tb, raw.as<u64>(), c->sh_plc.as<u64>(), (int)P, 0, bits, st));
-  c->launches += 8;
+  // group the placements by destination (= owner of the output byte range): histogram, offsets,
+  // scatter -- two passes instead of a sort, the order inside a destination does not matter
+  const u32 W = c->sh_world;
+  DBuf cnt, cur;
+  cnt.alloc((size_t)W * 8, st); cur.alloc((size_t)W * 8, st);
+  CK(cudaMemsetAsync(cnt.p, 0, (size_t)W * 8, st));
+  const u32 gP = (u32)min((u64)148 * 16, (P + 255) / 256);
+  if (P) k_sh_plc_hist<<<gP, 256, 0, st>>>(raw.as<u64>(), P, c->sh_chunk, W, cnt.as<unsigned long long>());
+  std::vector<unsigned long long> hc(W), ho(W);
+  CK(cudaMemcpyAsync(hc.data(), cnt.p, (size_t)W * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  c->sh_plc_cnt.assign(W, 0);
+  unsigned long long run = 0;
+  for (u32 d = 0; d < W; d++) { ho[d] = run; run += hc[d]; c->sh_plc_cnt[d] = hc[d]; }
+  CK(cudaMemcpyAsync(cur.p, ho.data(), (size_t)W * 8, cudaMemcpyHostToDevice, st));
+  if (P) k_sh_plc_scatter<<<gP, 256, 0, st>>>(raw.as<u64>(), P, c->sh_chunk, W, cur.as<unsigned long long>(),
+                                               c->sh_plc.as<u64>());
+  c->launches += 4;
   c->sh_nplc = P;
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(st));

@@ -174,10 +174,12 @@ class ShardedPath:
         return torch.cat([out[r * mx:r * mx + counts[r]] for r in range(self.world)])
 
     # ---- the path ------------------------------------------------------------------------------
-    def run(self, N_local, ndocs_local):
+    def run(self, N_local, ndocs_local, plan=None):
+        """plan: [(N, ndocs)] of every rank when the caller already knows the shard plan (saves the
+        first collective)."""
         ops, W, R = self.ops, self.world, self.rank
         self._mark(None)
-        g = self._allgather_ints([N_local, ndocs_local])
+        g = [list(x) for x in plan] if plan is not None else self._allgather_ints([N_local, ndocs_local])
         N_total = sum(x[0] for x in g)
         ndocs_total = sum(x[1] for x in g)
         doc_base = sum(x[1] for x in g[:R])
@@ -191,11 +193,12 @@ class ShardedPath:
         splitters = self._splitters(ks, Tn)
         b = [0] + ops.lower_bound("tail_keys", splitters) + [Tn]
         send = [b[d + 1] - b[d] for d in range(W)]
-        recv = self._a2a_counts(send)
+        cm = self._allgather_ints(send)             # the whole count matrix: cm[src][dst]
+        recv = [cm[s_][R] for s_ in range(W)]
         rk = self._a2a(ks, send, recv)
         rc = self._a2a(cs, send, recv)
         M = sum(recv)
-        Ms = self._allgather_ints([M])
+        Ms = [[sum(cm[s_][d] for s_ in range(W))] for d in range(W)]
         rank_base = sum(x[0] for x in Ms[:R])
         if sum(x[0] for x in Ms) >= 2 ** 32:
             raise CmsBwtError(-3, "more than 2^32 tails in the collection")
@@ -226,15 +229,18 @@ class ShardedPath:
         rb = [int(v) & 0xFFFFFFFF for v in roff[edge].cpu().tolist()]
         hsend = [hb[d + 1] - hb[d] for d in range(W)]
         rsend = [rb[d + 1] - rb[d] for d in range(W)]
-        hrecv = self._a2a_counts(hsend)
-        rrecv = self._a2a_counts(rsend)
+        cm = self._allgather_ints(hsend + rsend)
+        hrecv = [cm[s_][R] for s_ in range(W)]
+        rrecv = [cm[s_][W + R] for s_ in range(W)]
         he = self._a2a(ops.buffer("tile_heads"), hsend, hrecv, width=2)
         re = self._a2a(ops.buffer("tile_ranges"), rsend, rrecv, width=2)
         rows = (torch.arange(W, device=hoff.device)[:, None] * tp +
                 torch.arange(tp + 1, device=hoff.device)[None, :]).reshape(-1)
-        eq = [tp + 1] * W
-        hoffs = self._a2a(hoff[rows].contiguous(), eq, eq)
-        roffs = self._a2a(roff[rows].contiguous(), eq, eq)
+        eq = [2 * (tp + 1)] * W                     # per destination: its hoff slice, then its roff slice
+        both = torch.stack([hoff[rows].view(W, tp + 1), roff[rows].view(W, tp + 1)], dim=1).reshape(-1)
+        got2 = self._a2a(both.contiguous(), eq, eq).view(W, 2, tp + 1)
+        hoffs = got2[:, 0, :].contiguous().view(-1)
+        roffs = got2[:, 1, :].contiguous().view(-1)
         he_slab = [sum(hrecv[:s]) for s in range(W)]
         re_slab = [sum(rrecv[:s]) for s in range(W)]
         self._mark("x_tiles")
@@ -253,12 +259,9 @@ class ShardedPath:
 
         # -- stage 3: own output range + placements to the owners of the output ranges
         self._mark("x_cov")
-        obeg, olen, chunk = ops.emit(cov_full, N_total, W, R, doc_base)
+        obeg, olen, psend = ops.emit(cov_full, N_total, W, R, doc_base)
         self._mark("d_emit")
         plc = ops.buffer("placements")
-        P = plc.numel()
-        pb = [0] + ops.lower_bound("placements", [(d * chunk) << 8 for d in range(1, W)]) + [P]
-        psend = [pb[d + 1] - pb[d] for d in range(W)]
         precv = self._a2a_counts(psend)
         got = self._a2a(plc, psend, precv)
         self._mark("x_placements")
@@ -400,19 +403,20 @@ class CudaShardOps:
         return me.value
 
     def emit(self, cov_full, N_total, world, rank, doc_base):
-        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        a, b = C.c_uint64(), C.c_uint64()
+        cnt = (C.c_uint64 * world)()
         self._ck(self.L.cmsbwt_shard_emit(self.h, self._ptr(cov_full), N_total, world, rank, doc_base,
-                                          C.byref(a), C.byref(b), C.byref(c)))
-        return a.value, b.value, c.value
+                                          C.byref(a), C.byref(b), cnt))
+        return a.value, b.value, list(cnt)
 
     def apply(self, plc, count):
         self._ck(self.L.cmsbwt_shard_apply(self.h, self._ptr(plc), count))
 
 
-def run_sharded(ctx, device, d_text_ptr, N_local, ndocs_local, rank, world, group=None, comm=None):
+def run_sharded(ctx, device, d_text_ptr, N_local, ndocs_local, rank, world, group=None, comm=None, plan=None):
     """Whole path for this rank's documents (text resident in HBM): stage 1 on the shard, then the
     exchange phases.  -> (ShardedPath, result tensor = this rank's contiguous slice of the BWT)."""
     ctx.ms_run_device(d_text_ptr, N_local)
     sp = ShardedPath(CudaShardOps(ctx, device), rank, world, group, comm)
-    out = sp.run(N_local, ndocs_local)
+    out = sp.run(N_local, ndocs_local, plan)
     return sp, out

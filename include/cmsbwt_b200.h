@@ -161,9 +161,9 @@ int cmsbwt_shard_tails(cmsbwt_ctx *ctx, uint64_t doc_base, uint32_t *n_tails);
 /* named device arrays of the current shard state: "tail_keys" u32 (sorted), "tail_cls" u32,
  * "tie_keys" u64, "tile_heads"/"tile_ranges" 16-byte entries grouped by tile, "tile_hoff"/
  * "tile_roff" u32[world * tiles_per_rank + 1], "cov_slice" u32[tiles_per_rank * 256],
- * "placements" u64 (offset << 8 | symbol, sorted), "result" u8 */
+ * "placements" u64 (offset << 8 | symbol, grouped by destination rank), "result" u8 */
 int cmsbwt_shard_buffer(cmsbwt_ctx *ctx, const char *name, const void **dptr, uint64_t *count);
-/* first index whose element is >= values[k], for the sorted buffers "tail_keys" and "placements" */
+/* first index whose element is >= values[k], for the sorted buffer "tail_keys" */
 int cmsbwt_shard_lower_bound(cmsbwt_ctx *ctx, const char *name, const uint64_t *values, uint32_t count,
                              uint64_t *out_idx);
 int cmsbwt_shard_rank_owner(cmsbwt_ctx *ctx, const void *d_keys, const void *d_cls, uint32_t M,
@@ -180,7 +180,7 @@ int cmsbwt_shard_tiles_merge(cmsbwt_ctx *ctx, uint32_t world, uint32_t rank, con
                              uint32_t *max_entries);
 int cmsbwt_shard_emit(cmsbwt_ctx *ctx, const void *d_cov_full, uint64_t N_total, uint32_t world,
                       uint32_t rank, uint64_t doc_base, uint64_t *out_begin, uint64_t *out_len,
-                      uint64_t *chunk_bytes);
+                      uint64_t *plc_counts /* [world]: placements per destination rank */);
 int cmsbwt_shard_apply(cmsbwt_ctx *ctx, const void *d_plc, uint64_t count);
 
 /* tuning knobs (0 = default): chunk length of the MS kernel, tile width is fixed at 64. */

@@ -251,8 +251,10 @@ class NumpyShardOps:
         h = self.h
         for i in np.flatnonzero(h["len"] == 0):
             plc.append(((doc_base + int(self.sexcl[i])) << 8) | int(h["ch"][i]))
-        self.buf["placements"] = _i64(np.sort(np.array(plc, np.uint64)))
-        return obeg, olen, chunk
+        plc = np.sort(np.array(plc, np.uint64))
+        self.buf["placements"] = _i64(plc)
+        dest = (plc >> np.uint64(8)).astype(np.int64) // max(chunk, 1)
+        return obeg, olen, np.bincount(dest, minlength=world)[:world].astype(np.int64).tolist()
 
     # ---- emit.cu: shard_apply
     def apply(self, plc, count):

@@ -162,16 +162,18 @@ def test_sharded_many_short_documents():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_sharded_nccl_two_gpus(workdir):
-    ref, copies = gen_synth.make_collection(200000, 8, 0.002, 3)
+def test_sharded_nccl_all_gpus(workdir):
+    """one process per visible GPU over NCCL (2, 4 or 8 ranks)"""
+    world = min(8, torch.cuda.device_count())
+    ref, copies = gen_synth.make_collection(200000, 19, 0.002, 3)
     x = P.augment(ref)
     text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
     case = os.path.join(workdir, "nccl_case.npz")
     np.savez(case, x=x, text=text)
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     procs = []
-    for r in range(2):
-        env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1",
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
                    MASTER_PORT=str(port))
         procs.append(subprocess.Popen([sys.executable, os.path.join(HERE, "shard_worker_gpu.py"), case,
                                        os.path.join(workdir, "nccl_out")], env=env, stdout=subprocess.PIPE,
@@ -179,5 +181,5 @@ def test_sharded_nccl_two_gpus(workdir):
     logs = [p.communicate(timeout=600)[0].decode() for p in procs]
     for p, lg in zip(procs, logs):
         assert p.returncode == 0, lg[-3000:]
-    parts = [np.load(os.path.join(workdir, "nccl_out.%d.npz" % r))["out"] for r in range(2)]
+    parts = [np.load(os.path.join(workdir, "nccl_out.%d.npz" % r))["out"] for r in range(world)]
     assert np.array_equal(np.concatenate(parts), O.Oracle(x).bwt(text))
