@@ -597,9 +597,16 @@ __device__ __forceinline__ void msf_warp_iter(const MsfParams &P, MsfLane &L) {
 }
 #else
 // ---- one warp iteration (host emulation for tests/harness: same phases, loops instead of shuffles)
+// how often each action came out of a search step (harness statistics: [1] FIN, [2] GENERIC, [3] TERM,
+// [4] EXT, [5] SKIP)
+static unsigned long long msf_host_acts[8];
 inline void msf_warp_iter_host(const MsfParams &P, MsfLane *W, int nl) {
   msf_u32 act[32];
-  for (int l = 0; l < nl; l++) act[l] = msf_search_step(P, W[l]);
+  for (int l = 0; l < nl; l++) {
+    act[l] = msf_search_step(P, W[l]);
+    msf_host_acts[act[l] == MSF_ACT_FIN ? 1 : (act[l] & MSF_ACT_GENERIC) ? 2 : (act[l] & MSF_ACT_TERM) ? 3 :
+                  act[l] == MSF_ACT_EXT ? 4 : 0]++;
+  }
   for (int l = 0; l < nl; l++) {                          // phase B
     if (act[l] != MSF_ACT_EXT) continue;
     MsfLane &L = W[l];
@@ -627,6 +634,7 @@ inline void msf_warp_iter_host(const MsfParams &P, MsfLane *W, int nl) {
   }
   for (int l = 0; l < nl; l++) {                          // phase D
     if (act[l] != MSF_ACT_SKIP) continue;
+    msf_host_acts[5]++;
     MsfLane &L = W[l];
     const msf_u32 bpos = L.pos, E = L.pos + L.len;
     msf_u32 q = E, round = 0;

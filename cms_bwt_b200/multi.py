@@ -25,6 +25,9 @@ import torch.distributed as dist
 from . import lib, CmsBwtError, MODE_PLAIN
 
 SAMPLES_PER_RANK = 1024
+PACK_FROM_WORLD = int(__import__("os").environ.get("CMSBWT_PACK_FROM_WORLD", 4))   # pack paired exchanges into one collective
+# from this many ranks on (measured: the packing passes cost more than a collective at 2 ranks)
+TIE_CAPACITY = int(__import__("os").environ.get("CMSBWT_TIE_CAPACITY", 1 << 17))             # tied tails per rank that ride along with the count of a refinement round
 TILE_MAX_ENTRIES = 11000          # tiles.cu LT_MAX_ENTRIES
 
 
@@ -195,8 +198,15 @@ class ShardedPath:
         send = [b[d + 1] - b[d] for d in range(W)]
         cm = self._allgather_ints(send)             # the whole count matrix: cm[src][dst]
         recv = [cm[s_][R] for s_ in range(W)]
-        rk = self._a2a(ks, send, recv)
-        rc = self._a2a(cs, send, recv)
+        pack = W >= PACK_FROM_WORLD
+        if pack:    # key and cls travel as one 64-bit word per tail (one collective instead of two)
+            kc = ((ks.to(torch.int64) & 0xFFFFFFFF) << 32) | (cs.to(torch.int64) & 0xFFFFFFFF)
+            got = self._a2a(kc, send, recv)
+            rk = (got >> 32).to(torch.int32)
+            rc = got.to(torch.int32)
+        else:
+            rk = self._a2a(ks, send, recv)
+            rc = self._a2a(cs, send, recv)
         M = sum(recv)
         Ms = [[sum(cm[s_][d] for s_ in range(W))] for d in range(W)]
         rank_base = sum(x[0] for x in Ms[:R])
@@ -205,18 +215,39 @@ class ShardedPath:
         self._mark("x_tails")
         r_out, t_out = ops.rank_owner(rk, rc, M, rank_base)
         self._mark("d_rank_owner")
-        rs = self._a2a(r_out, recv, send)
-        ts = self._a2a(t_out, recv, send)
+        if pack:
+            back = self._a2a((r_out.to(torch.int64) & 0xFFFFFFFF) | (t_out.to(torch.int64) << 32), recv, send)
+            rs = back.to(torch.int32)
+            ts = (back >> 32).to(torch.uint8)
+        else:
+            rs = self._a2a(r_out, recv, send)
+            ts = self._a2a(t_out, recv, send)
         self._mark("x_ranks")
         m = ops.rank_apply(rs, ts)
         self.rank_rounds = 0
+        # refinement rounds: every rank sends [m, keys...] padded to a common capacity, so a round
+        # is ONE all-gather as long as every tied subset fits (they only shrink from round to round)
+        cap = TIE_CAPACITY
         while True:
-            ms = [x[0] for x in self._allgather_ints([m])]
+            keys = ops.tie_keys() if m else self.ops.empty(0, torch.int64)
+            buf = self.ops.empty(cap + 1, torch.int64)
+            buf[0] = m
+            if 0 < m <= cap:
+                buf[1:m + 1] = keys
+            allb = self.ops.empty((cap + 1) * W, torch.int64)
+            self.comm.all_gather(allb, buf)
+            self._sync()
+            self.collectives += 1
+            allb = allb.view(W, cap + 1)
+            ms = [int(v) for v in allb[:, 0].cpu().tolist()]
             if sum(ms) == 0:
                 break
-            keys = ops.tie_keys()
-            allk = self._allgather_v(keys, ms)
-            m = ops.tie_refine(allk, sum(ms), sum(ms[:R]))
+            if max(ms) <= cap:
+                allk = torch.cat([allb[r, 1:ms[r] + 1] for r in range(W)])
+            else:
+                allk = self._allgather_v(keys, ms)
+            m = ops.tie_refine(allk.contiguous(), sum(ms), sum(ms[:R]))
+            cap = max(16, min(cap, max(ms)))
             self.rank_rounds += 1
 
         # -- stage 2b: tile entries to the owners of the reference-position ranges
@@ -368,6 +399,7 @@ class CudaShardOps:
         return list(o)
 
     def rank_owner(self, keys, cls, M, rank_base):
+        self.sync()      # inputs may come from torch ops on torch's stream; the library has its own
         r = self.empty(M, torch.int32)
         t = self.empty(M, torch.uint8)
         self._ck(self.L.cmsbwt_shard_rank_owner(self.h, self._ptr(keys), self._ptr(cls), M, rank_base,
@@ -375,6 +407,7 @@ class CudaShardOps:
         return r, t
 
     def rank_apply(self, rs, ts):
+        self.sync()      # inputs may come from torch ops on torch's stream; the library has its own
         m = C.c_uint32()
         self._ck(self.L.cmsbwt_shard_rank_apply(self.h, self._ptr(rs), self._ptr(ts), C.byref(m)))
         return m.value
@@ -385,6 +418,7 @@ class CudaShardOps:
         return self.buffer("tie_keys")
 
     def tie_refine(self, allkeys, m_total, my_off):
+        self.sync()      # inputs may come from torch ops on torch's stream; the library has its own
         m = C.c_uint32()
         self._ck(self.L.cmsbwt_shard_tie_refine(self.h, self._ptr(allkeys), m_total, my_off, C.byref(m)))
         return m.value
@@ -395,6 +429,7 @@ class CudaShardOps:
         return tp.value
 
     def tiles_merge(self, world, rank, he, re, hoffs, roffs, he_slab, re_slab, ndocs_total):
+        self.sync()      # inputs may come from torch ops on torch's stream; the library has its own
         me = C.c_uint32()
         hs = (C.c_uint64 * world)(*he_slab)
         rs = (C.c_uint64 * world)(*re_slab)
@@ -403,6 +438,7 @@ class CudaShardOps:
         return me.value
 
     def emit(self, cov_full, N_total, world, rank, doc_base):
+        self.sync()      # inputs may come from torch ops on torch's stream; the library has its own
         a, b = C.c_uint64(), C.c_uint64()
         cnt = (C.c_uint64 * world)()
         self._ck(self.L.cmsbwt_shard_emit(self.h, self._ptr(cov_full), N_total, world, rank, doc_base,
@@ -410,6 +446,7 @@ class CudaShardOps:
         return a.value, b.value, list(cnt)
 
     def apply(self, plc, count):
+        self.sync()      # inputs may come from torch ops on torch's stream; the library has its own
         self._ck(self.L.cmsbwt_shard_apply(self.h, self._ptr(plc), count))
 
 

@@ -22,7 +22,10 @@ static void pack(const u8 *s, u64 len, std::vector<u64> &out) {
 extern "C" {
 // step counts per state of the last runs (used to model the kernel's cost per mutation)
 unsigned long long g_steps[16];
-void msf_host_steps(unsigned long long *out) { for (int i = 0; i < 16; i++) { out[i] = g_steps[i]; g_steps[i] = 0; } }
+void msf_host_steps(unsigned long long *out) {
+  for (int i = 0; i < 16; i++) { out[i] = g_steps[i]; g_steps[i] = 0; }
+  for (int i = 1; i < 6; i++) { out[8 + i] = msf_host_acts[i]; msf_host_acts[i] = 0; }
+}
 
 // returns the number of heads (text order) or -1 when the input is not eligible for the fast path
 // (reference or text not pure ACGT), -2 on pool overflow.
