@@ -162,6 +162,18 @@ def run_multi(args, rank, world, local, dev, dist):
     from cms_bwt_b200 import multi
     import gen_device
     w = WORKLOADS[args.workload]
+    # pinned host buffers should live on the NUMA node of this rank's GPU: run this process on the
+    # CPUs NVML reports as local to the device (first touch then places the pages there)
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass
     # contiguous ranges of copies per rank (all copies have nearly the same length)
     plan = multi.shard_documents([w["ref_bp"]] * w["copies"], world)
     a, b = plan[rank]

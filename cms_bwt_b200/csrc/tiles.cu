@@ -169,10 +169,10 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   for (u32 k = tid; k < NB * (LT_W + 1); k += LT_THREADS) (&s_C[0][0])[k] = 0;
   if (tid <= LT_NB) { s_bcnt[tid] = 0; s_bcur[tid] = 0; }
   if (tid < npiv) s_praw[tid] = re[r0 + (u32)(((u64)(tid + 1) * rc) / (npiv + 1))].kappa;
-  {
-    u32 p = ((t + t0) << LT_SHIFT) + tid;
-    s_base[tid] = p < n ? base[isa[p]] : 0;
-  }
+  // the rank of position p is needed only if p has heads, but that is known a sync later: fetch
+  // isa[p] now (coalesced) and do the random gather base[rank] once the head counts are in
+  const u32 p_own = ((t + t0) << LT_SHIFT) + tid;
+  const u32 rank_own = p_own < n ? isa[p_own] : 0;
   // the first range / head of every thread stays in registers between the two passes
   TileEnt re0, he0;
   re0.a = re0.b = 0; re0.kappa = 0; he0 = re0;
@@ -199,6 +199,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   }
   for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[(j == tid ? he0 : he[h0 + j]).b & (LT_W - 1)], 1u);
   __syncthreads();
+  s_base[tid] = s_cnt[tid] ? base[rank_own] : 0;      // 1/3 of the positions have no head: no gather
   u32 ex;
   BS(ts).ExclusiveSum(s_cnt[tid], ex);
   s_off[tid] = ex;
