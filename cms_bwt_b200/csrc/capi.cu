@@ -95,6 +95,9 @@ int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
     }
   }
   else if (!strcmp(name, "slots")) { c->use_slots = v != 0; }          // takes effect at the next index_upload
+  else if (!strcmp(name, "nb_t1")) { c->nb_t[0] = v; }
+  else if (!strcmp(name, "nb_t4")) { c->nb_t[1] = v; }
+  else if (!strcmp(name, "nb_t8")) { c->nb_t[2] = v; }
   else if (!strcmp(name, "scatter_mb")) { if (v < 0) return CMSBWT_E_ARG; c->scatter_mb = v; }
   else if (!strcmp(name, "l2_fetch")) {
     // device-wide L2 fetch granularity hint (32, 64 or 128 bytes): the path is dominated by random

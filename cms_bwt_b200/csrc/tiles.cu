@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, cons
 __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, const TileEnt *re, const u32 *hoff,
                                                            const u32 *roff, const u32 *isa, const u64 *base,
                                                            u32 n, u32 t0, u8 *out, u64 *plc, u32 *within_out,
-                                                           u64 *off_out) {
+                                                           u64 *off_out, int3 nb_t) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W];
   __shared__ u64 s_base[LT_W];
@@ -163,7 +163,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   u32 *s_rl = (u32 *)(s_rk + rc);               // their lo | hi << 16
   // number of kappa buckets by depth: a shallow tile is cheaper by plain pair tests than by the
   // fixed cost of LT_NB difference rows
-  const u32 NB = rc <= 48 ? 1u : rc <= 160 ? 4u : rc <= 512 ? 8u : (u32)LT_NB;
+  const u32 NB = rc <= (u32)nb_t.x ? 1u : rc <= (u32)nb_t.y ? 4u : rc <= (u32)nb_t.z ? 8u : (u32)LT_NB;
   const u32 npiv = NB - 1;                      // rc >= npiv by construction
   s_cnt[tid] = 0; s_cur[tid] = 0;
   for (u32 k = tid; k < NB * (LT_W + 1); k += LT_THREADS) (&s_C[0][0])[k] = 0;
@@ -382,7 +382,8 @@ void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out) {
   if (sm > 40 * 1024)
     CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_place<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                               c->t_roff.as<u32>(), c->ix.isa, base, n, 0, out, nullptr, wo, oo);
+                                               c->t_roff.as<u32>(), c->ix.isa, base, n, 0, out, nullptr, wo, oo,
+                                               make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]));
   k_place_sentinels<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                                            c->h_sexcl.as<u32>(), H, out, wo, oo);
   c->launches += 2;
@@ -554,7 +555,8 @@ void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
     CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_place<<<tp, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                            c->t_roff.as<u32>(), c->ix.isa, base, n, c->sh_rank * tp, nullptr,
-                                           raw.as<u64>(), nullptr, nullptr);
+                                           raw.as<u64>(), nullptr, nullptr,
+                                           make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]));
   k_sh_sentinel_plc<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                                            c->s_sexcl.as<u32>(), H, doc_base, raw.as<u64>() + c->sh_he);
   // group the placements by destination (= owner of the output byte range): histogram, offsets,
