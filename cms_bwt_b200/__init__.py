@@ -27,6 +27,7 @@ EXPORTS = [
     "cmsbwt_shard_tails", "cmsbwt_shard_buffer", "cmsbwt_shard_lower_bound", "cmsbwt_shard_rank_owner",
     "cmsbwt_shard_rank_apply", "cmsbwt_shard_tie_keys", "cmsbwt_shard_tie_refine",
     "cmsbwt_shard_tiles_local", "cmsbwt_shard_tiles_merge", "cmsbwt_shard_emit", "cmsbwt_shard_apply",
+    "cmsbwt_shard_rle",
 ]
 
 

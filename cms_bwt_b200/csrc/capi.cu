@@ -459,7 +459,8 @@ int cmsbwt_shard_buffer(cmsbwt_ctx *c, const char *name, const void **dptr, uint
   else if (!strcmp(name, "tile_roff")) { p = c->t_roff.p; n = (u64)c->sh_tp * c->sh_world + 1; }   // u32
   else if (!strcmp(name, "cov_slice")) { p = c->sh_cov.p; n = (u64)c->sh_tp * 256; }               // u32
   else if (!strcmp(name, "placements")) { p = c->sh_plc.p; n = c->sh_nplc; }      // u64, grouped by destination
-  else if (!strcmp(name, "result")) { p = c->d_out.p; n = c->out_bytes; }         // u8
+  else if (!strcmp(name, "result")) { p = c->d_out.p; n = c->sh_olen; }           // u8
+  else if (!strcmp(name, "rle")) { p = c->d_rle.p; n = c->stats.n_runs * 9; }     // u8, 9-byte records
   else return fail(c, CMSBWT_E_ARG, "unknown shard buffer");
   *dptr = p;
   *count = n;
@@ -573,6 +574,18 @@ int cmsbwt_shard_emit(cmsbwt_ctx *c, const void *d_cov_full, uint64_t N_total, u
   if (out_begin) *out_begin = c->sh_obeg;
   if (out_len) *out_len = c->sh_olen;
   if (plc_counts) for (u32 d = 0; d < world; d++) plc_counts[d] = c->sh_plc_cnt[d];
+  GUARD_END(c)
+  return CMSBWT_OK;
+}
+
+int cmsbwt_shard_rle(cmsbwt_ctx *c, uint64_t *n_records) {
+  if (!c || !c->d_out.p) return fail(c, CMSBWT_E_ARG, "shard_apply first");
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  Timer t(c->st);
+  rle_encode(c, c->d_out.as<u8>(), c->sh_olen);
+  c->stats.emit_ms += t.stop();
+  if (n_records) *n_records = c->stats.n_runs;
   GUARD_END(c)
   return CMSBWT_OK;
 }

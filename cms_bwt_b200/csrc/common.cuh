@@ -204,6 +204,7 @@ u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const 
                       const u32 *roffs, const u64 *he_slab, const u64 *re_slab, u64 ndocs_total);
 void shard_emit(cmsbwt_ctx *c, const u32 *cov_full, u64 N_total, u32 world, u32 rank, u64 doc_base);
 void shard_apply(cmsbwt_ctx *c, const u64 *plc, u64 cnt);
+void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N);
 void emit_stage(cmsbwt_ctx *c, int mode);
 
 // ---------------------------------------------------------------------------------------------

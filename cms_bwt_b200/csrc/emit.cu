@@ -177,6 +177,34 @@ __global__ void k_rle_records(const u8 *out, const u64 *starts, u64 R, u64 N, u8
 
 void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out);
 
+// maximal-run records (9 bytes: LE u64 run, u8 symbol) of out[0, N) -> d_rle (:1695-1777)
+void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N) {
+  cudaStream_t st = c->st;
+  const int B = 256;
+  u64 nb = (N + RLE_BLOCK - 1) / RLE_BLOCK;
+  DBuf bcnt, boff, starts;
+  bcnt.alloc((nb + 1) * 4, st); boff.alloc((nb + 1) * 8, st);
+  CK(cudaMemsetAsync(bcnt.p, 0, (nb + 1) * 4, st));
+  if (nb) k_rle_count<<<(u32)nb, RLE_THREADS, 0, st>>>(out, N, bcnt.as<u32>());
+  size_t tb3 = 0;
+  EXSUM64(nullptr, tb3, bcnt.as<u32>(), boff.as<u64>(), (int)(nb + 1), st);
+  DBuf tmp3; tmp3.alloc(tb3, st);
+  CK(EXSUM64(tmp3.p, tb3, bcnt.as<u32>(), boff.as<u64>(), (int)(nb + 1), st));
+  u64 R = 0;
+  CK(cudaMemcpyAsync(&R, boff.as<u64>() + nb, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  starts.alloc((R + 1) * 8, st);
+  c->d_rle.alloc(R * 9 + CMS_PAD, st);
+  if (nb) k_rle_starts<<<(u32)nb, RLE_THREADS, 0, st>>>(out, N, boff.as<u64>(), starts.as<u64>());
+  if (R) k_rle_records<<<(u32)((R + B - 1) / B), B, 0, st>>>(out, starts.as<u64>(), R, N, c->d_rle.as<u8>());
+  c->launches += 4;
+  CK(cudaGetLastError());
+  c->out_mode = CMSBWT_MODE_RLE;
+  c->out_bytes = R * 9;
+  c->stats.n_runs = R;
+  CK(cudaStreamSynchronize(st));
+}
+
 void emit_stage(cmsbwt_ctx *c, int mode) {
   cudaStream_t st = c->st;
   const u32 n = c->ix.n;
@@ -231,28 +259,7 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   c->out_mode = mode;
   c->out_bytes = N;
   c->stats.n_runs = 0;
-  if (mode == CMSBWT_MODE_RLE) {
-    u64 nb = (N + RLE_BLOCK - 1) / RLE_BLOCK;
-    DBuf bcnt, boff, starts;
-    bcnt.alloc((nb + 1) * 4, st); boff.alloc((nb + 1) * 8, st);
-    CK(cudaMemsetAsync(bcnt.p, 0, (nb + 1) * 4, st));
-    k_rle_count<<<(u32)nb, RLE_THREADS, 0, st>>>(out, N, bcnt.as<u32>());
-    size_t tb3 = 0;
-    EXSUM64(nullptr, tb3, bcnt.as<u32>(), boff.as<u64>(), (int)(nb + 1), st);
-    DBuf tmp3; tmp3.alloc(tb3, st);
-    CK(EXSUM64(tmp3.p, tb3, bcnt.as<u32>(), boff.as<u64>(), (int)(nb + 1), st));
-    u64 R = 0;
-    CK(cudaMemcpyAsync(&R, boff.as<u64>() + nb, 8, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    starts.alloc((R + 1) * 8, st);
-    c->d_rle.alloc(R * 9 + CMS_PAD, st);
-    k_rle_starts<<<(u32)nb, RLE_THREADS, 0, st>>>(out, N, boff.as<u64>(), starts.as<u64>());
-    k_rle_records<<<(u32)((R + B - 1) / B), B, 0, st>>>(out, starts.as<u64>(), R, N, c->d_rle.as<u8>());
-    c->launches += 4;
-    CK(cudaGetLastError());
-    c->out_bytes = R * 9;
-    c->stats.n_runs = R;
-  }
+  if (mode == CMSBWT_MODE_RLE) rle_encode(c, out, N);
   CK(cudaStreamSynchronize(st));
 }
 

@@ -59,6 +59,25 @@ def merge_rle_borders(parts):
     return out
 
 
+def plan_rle_borders(info):
+    """info[r] = (records, first_run, first_sym, last_run, last_sym) of rank r's slice.  A run that
+    straddles borders belongs to the leftmost rank it touches.  -> per rank (drop_first, add_to_last):
+    whether its first record is absorbed by a rank to the left, and what its own last record gains."""
+    W = len(info)
+    drop, add = [False] * W, [0] * W
+    owner, sym = None, None
+    for r, (R, frun, fsym, lrun, lsym) in enumerate(info):
+        if R == 0:
+            continue
+        if owner is not None and fsym == sym:
+            drop[r] = True
+            add[owner] += frun
+            if R == 1:
+                continue                    # the whole slice went into the open run; it stays open
+        owner, sym = r, lsym
+    return drop, add
+
+
 class DistComm:
     """The two collectives the path needs, on torch.distributed (NCCL on GPUs, gloo in the CPU tests)."""
 
@@ -301,6 +320,30 @@ class ShardedPath:
         self.out_begin, self.out_len = obeg, olen
         return ops.buffer("result")
 
+    def rle(self):
+        """-r: this rank's 9-byte records with the runs that straddle rank borders merged.
+        -> (uint8 tensor of records, index of its first record in the global record list)"""
+        ops, W, R = self.ops, self.world, self.rank
+        nrec = ops.rle()
+        rec = ops.buffer("rle")
+        if nrec:
+            edge = torch.cat([rec[:9], rec[-9:]]).cpu().numpy()
+            mine = [nrec, int.from_bytes(edge[0:8].tobytes(), "little"), int(edge[8]),
+                    int.from_bytes(edge[9:17].tobytes(), "little"), int(edge[17])]
+        else:
+            mine = [0, 0, 0, 0, 0]
+        info = self._allgather_ints(mine)
+        drop, add = plan_rle_borders(info)
+        out = rec.clone()
+        if drop[R]:
+            out = out[9:]
+        if add[R]:
+            n = out.numel()
+            run = int.from_bytes(out[n - 9:n - 1].cpu().numpy().tobytes(), "little") + add[R]
+            out[n - 9:n - 1] = torch.tensor(list(run.to_bytes(8, "little")), dtype=torch.uint8, device=out.device)
+        counts = [info[r][0] - (1 if drop[r] else 0) for r in range(W)]
+        return out, sum(counts[:R])
+
     def _splitters(self, ks, Tn):
         """W-1 key values from SAMPLES_PER_RANK evenly spaced local samples per rank; equal keys
         always land on one owner because the slabs are cut at lower bounds of key VALUES."""
@@ -329,7 +372,7 @@ _TYPES = {  # shard buffer -> (elements per entry, typestr, torch dtype)
     "tail_keys": (1, "<i4", torch.int32), "tail_cls": (1, "<i4", torch.int32), "tie_keys": (1, "<i8", torch.int64),
     "tile_heads": (2, "<i8", torch.int64), "tile_ranges": (2, "<i8", torch.int64),
     "tile_hoff": (1, "<i4", torch.int32), "tile_roff": (1, "<i4", torch.int32),
-    "cov_slice": (1, "<i4", torch.int32), "placements": (1, "<i8", torch.int64), "result": (1, "|u1", torch.uint8),
+    "cov_slice": (1, "<i4", torch.int32), "placements": (1, "<i8", torch.int64), "result": (1, "|u1", torch.uint8), "rle": (1, "|u1", torch.uint8),
 }
 
 
@@ -352,6 +395,7 @@ class CudaShardOps:
                                                C.POINTER(u32)]
         L.cmsbwt_shard_emit.argtypes = [vp, vp, u64, u32, u32, u64, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
         L.cmsbwt_shard_apply.argtypes = [vp, vp, u64]
+        L.cmsbwt_shard_rle.argtypes = [vp, C.POINTER(u64)]
         self.L = L
 
     def _ck(self, rc):
@@ -444,6 +488,11 @@ class CudaShardOps:
         self._ck(self.L.cmsbwt_shard_emit(self.h, self._ptr(cov_full), N_total, world, rank, doc_base,
                                           C.byref(a), C.byref(b), cnt))
         return a.value, b.value, list(cnt)
+
+    def rle(self):
+        n = C.c_uint64()
+        self._ck(self.L.cmsbwt_shard_rle(self.h, C.byref(n)))
+        return n.value
 
     def apply(self, plc, count):
         self.sync()      # inputs may come from torch ops on torch's stream; the library has its own

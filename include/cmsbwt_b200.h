@@ -161,7 +161,8 @@ int cmsbwt_shard_tails(cmsbwt_ctx *ctx, uint64_t doc_base, uint32_t *n_tails);
 /* named device arrays of the current shard state: "tail_keys" u32 (sorted), "tail_cls" u32,
  * "tie_keys" u64, "tile_heads"/"tile_ranges" 16-byte entries grouped by tile, "tile_hoff"/
  * "tile_roff" u32[world * tiles_per_rank + 1], "cov_slice" u32[tiles_per_rank * 256],
- * "placements" u64 (offset << 8 | symbol, grouped by destination rank), "result" u8 */
+ * "placements" u64 (offset << 8 | symbol, grouped by destination rank), "result" u8,
+ * "rle" u8 (9-byte records) */
 int cmsbwt_shard_buffer(cmsbwt_ctx *ctx, const char *name, const void **dptr, uint64_t *count);
 /* first index whose element is >= values[k], for the sorted buffer "tail_keys" */
 int cmsbwt_shard_lower_bound(cmsbwt_ctx *ctx, const char *name, const uint64_t *values, uint32_t count,
@@ -182,6 +183,9 @@ int cmsbwt_shard_emit(cmsbwt_ctx *ctx, const void *d_cov_full, uint64_t N_total,
                       uint32_t rank, uint64_t doc_base, uint64_t *out_begin, uint64_t *out_len,
                       uint64_t *plc_counts /* [world]: placements per destination rank */);
 int cmsbwt_shard_apply(cmsbwt_ctx *ctx, const void *d_plc, uint64_t count);
+/* -r for a shard: maximal-run records (:1695-1777) of this device's slice of the BWT -> buffer "rle";
+ * a run that straddles a device border is merged by the host layer (multi.rle_sharded). */
+int cmsbwt_shard_rle(cmsbwt_ctx *ctx, uint64_t *n_records);
 
 /* tuning knobs (0 = default): chunk length of the MS kernel, tile width is fixed at 64. */
 int cmsbwt_set_param(cmsbwt_ctx *ctx, const char *name, int64_t value);

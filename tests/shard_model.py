@@ -263,3 +263,10 @@ class NumpyShardOps:
         assert ((off >= 0) & (off < self.olen)).all()
         self.out[off] = (p & np.uint64(0xFF)).astype(np.uint8)
         self.buf["result"] = torch.from_numpy(self.out)
+
+    # ---- emit.cu: rle_encode on the local slice
+    def rle(self):
+        import oracle_lib as O
+        rec = O.rle(self.out) if len(self.out) else np.zeros(0, np.uint8)
+        self.buf["rle"] = torch.from_numpy(np.ascontiguousarray(rec))
+        return len(rec) // 9

@@ -33,8 +33,9 @@ def main():
     ops = NumpyShardOps(orc, shard)
     sp = multi.ShardedPath(ops, rank, world)
     out = sp.run(len(shard), b - a)
+    rl, rl_first = sp.rle()
     np.savez(outp + ".%d.npz" % rank, out=out.numpy(), begin=sp.out_begin, rounds=sp.rank_rounds,
-             collectives=sp.collectives)
+             collectives=sp.collectives, rle=rl.numpy(), rle_first=rl_first)
     dist.barrier()
     dist.destroy_process_group()
 

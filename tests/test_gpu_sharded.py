@@ -59,7 +59,9 @@ def run_threads(x, text, world, params=None):
                 raise RuntimeError("empty shard")
             sp, out = multi.run_sharded(ctx, dev, t.data_ptr(), len(shard), nd, r, world,
                                         comm=multi.ThreadComm(shared, r))
-            res[r] = (sp.out_begin, out.cpu().numpy().copy(), sp.rank_rounds, ctx.stats())
+            plain = out.cpu().numpy().copy()
+            rl, rl_first = sp.rle()
+            res[r] = (sp.out_begin, plain, sp.rank_rounds, ctx.stats(), rl.cpu().numpy().copy(), rl_first)
         except BaseException as e:          # noqa: BLE001  (a dead rank must not leave the others waiting)
             err[r] = e
             shared.barrier.abort()
@@ -79,10 +81,10 @@ def run_threads(x, text, world, params=None):
         if e is not None:
             raise e
     off = 0
-    for b, o, _, _ in res:
-        assert b == off or len(o) == 0
-        off += len(o)
-    return np.concatenate([o for _, o, _, _ in res]), res
+    for r_ in res:
+        assert r_[0] == off or len(r_[1]) == 0
+        off += len(r_[1])
+    return np.concatenate([r_[1] for r_ in res]), res
 
 
 def _check(x, text, world, desc, params=None):
@@ -92,6 +94,12 @@ def _check(x, text, world, desc, params=None):
         bad = np.flatnonzero(got != want) if len(got) == len(want) else []
         raise AssertionError("sharded BWT %s world=%d: len %d/%d, %d mismatches, first %s"
                              % (desc, world, len(got), len(want), len(bad), bad[:8]))
+    # -r across ranks: concatenated records = maximal-run RLE of the whole BWT
+    assert np.array_equal(np.concatenate([r_[4] for r_ in res]), O.rle(want)), "sharded RLE " + desc
+    cnt = 0
+    for r_ in res:
+        assert r_[5] == cnt
+        cnt += len(r_[4]) // 9
     return res
 
 

@@ -47,7 +47,15 @@ def _run_world(x, text, workdir, name, world=2):
     for z in parts:
         assert int(z["begin"]) == off or len(z["out"]) == 0
         off += len(z["out"])
-    return np.concatenate([z["out"] for z in parts]), parts
+    got = np.concatenate([z["out"] for z in parts])
+    # -r across ranks: the concatenated records are the maximal-run RLE of the whole BWT
+    recs = np.concatenate([z["rle"] for z in parts])
+    assert np.array_equal(recs, O.rle(got)), "sharded RLE records"
+    cnt = 0
+    for z in parts:
+        assert int(z["rle_first"]) == cnt
+        cnt += len(z["rle"]) // 9
+    return got, parts
 
 
 def test_shard_documents_plan():
@@ -57,6 +65,17 @@ def test_shard_documents_plan():
     assert plan[0][0] == 0 and plan[-1][1] == 7 and all(a <= b for a, b in plan)
     assert all(plan[i][1] == plan[i + 1][0] for i in range(7))
     assert multi.shard_documents([], 2) == [(0, 0), (0, 0)]
+
+
+def test_plan_rle_borders():
+    A, C_, G = 65, 67, 71
+    # rank 1's single run and rank 2's first run continue rank 0's last run; rank 3 is empty
+    info = [(3, 5, A, 2, C_), (1, 4, C_, 4, C_), (2, 1, C_, 7, G), (0, 0, 0, 0, 0), (2, 3, G, 1, A)]
+    drop, add = multi.plan_rle_borders(info)
+    assert drop == [False, True, True, False, True]
+    assert add == [5, 0, 3, 0, 0]
+    drop, add = multi.plan_rle_borders([(2, 1, A, 1, C_), (2, 1, A, 1, C_)])
+    assert drop == [False, False] and add == [0, 0]
 
 
 def test_merge_rle_borders():
