@@ -506,3 +506,64 @@ def run_sharded(ctx, device, d_text_ptr, N_local, ndocs_local, rank, world, grou
     sp = ShardedPath(CudaShardOps(ctx, device), rank, world, group, comm)
     out = sp.run(N_local, ndocs_local, plan)
     return sp, out
+
+
+# ---- the command line across GPUs -----------------------------------------------------------------
+def main(argv=None):
+    """`cms_bwt` over all ranks of a torchrun launch: same options and files as the reference's
+    main.cpp:37-132 (-p/-b/-r/-o, two-line list file), every rank writes its slice of <out>.bwt /
+    <out>.rl_bwt at its offset.  usage: torchrun --nproc-per-node N tools/cms_bwt_multi.py [opts] list"""
+    import argparse
+    import os
+    import time
+    import numpy as np
+    from . import Context, read_reference, augment, parse_collection, UINT64_MAX
+    ap = argparse.ArgumentParser(prog="cms_bwt_multi")
+    ap.add_argument("-p", type=int, default=UINT64_MAX)
+    ap.add_argument("-b", type=float, default=2.0)            # accepted and ignored (INTEGRATION.md)
+    ap.add_argument("-r", action="store_true")
+    ap.add_argument("-o", default=None)
+    ap.add_argument("listfile")
+    a = ap.parse_args(argv)
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    t0 = time.time()
+    with open(a.listfile) as f:
+        lines = f.read().split("\n")
+    ref_path, coll_path = lines[0], lines[1].rstrip()
+    outname = a.o or a.listfile
+    with open(ref_path, "rb") as f:
+        x = augment(read_reference(f.read()))
+    with open(coll_path, "rb") as f:
+        text, ndocs = parse_collection(f.read(), a.p)
+    ends = np.flatnonzero(text == 2)
+    starts = np.concatenate([[0], ends[:-1] + 1])
+    plan = shard_documents((ends - starts).tolist(), world)
+    d0, d1 = plan[rank]
+    lo = int(starts[d0]) if d0 < len(ends) else len(text)
+    hi = int(ends[d1 - 1]) + 1 if d1 > d0 else lo
+    if hi == lo:
+        raise SystemExit("cms_bwt_multi: more ranks than documents")
+    shard = torch.from_numpy(np.concatenate([text[lo:hi], np.full(64, 2, np.uint8)])).to(dev)
+    ctx = Context(local)
+    ctx.index_upload(x)
+    sp, out = run_sharded(ctx, dev, shard.data_ptr(), hi - lo, d1 - d0, rank, world)
+    if a.r:
+        rec, first = sp.rle()
+        data, offset, path = rec.cpu().numpy(), 9 * first, outname + ".rl_bwt"
+    else:
+        data, offset, path = out.cpu().numpy(), sp.out_begin, outname + ".bwt"
+    if rank == 0:
+        open(path, "wb").close()
+    dist.barrier()
+    fd = os.open(path, os.O_WRONLY)
+    os.pwrite(fd, data.tobytes(), offset)
+    os.close(fd)
+    dist.barrier()
+    if rank == 0:
+        print("==== Time elapsed: %d ms" % int((time.time() - t0) * 1e3))
+    ctx.close()
+    dist.destroy_process_group()

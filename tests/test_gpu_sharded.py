@@ -191,3 +191,31 @@ def test_sharded_nccl_all_gpus(workdir):
         assert p.returncode == 0, lg[-3000:]
     parts = [np.load(os.path.join(workdir, "nccl_out.%d.npz" % r))["out"] for r in range(world)]
     assert np.array_equal(np.concatenate(parts), O.Oracle(x).bwt(text))
+
+
+@pytest.mark.parametrize("rle_mode", [False, True])
+def test_cli_multi_matches_golden(workdir, rle_mode):
+    """tools/cms_bwt_multi.py (the cms_bwt command line over a torchrun launch) on every visible GPU
+    (one rank on a single-GPU box) against a golden .bwt of the reference binary"""
+    z = np.load(os.path.join(GOLDEN, "synth_20k_x8.npz"))
+    d = os.path.join(workdir, "cli_multi_%d" % rle_mode)
+    os.makedirs(d, exist_ok=True)
+    with open(os.path.join(d, "ref.fa"), "wb") as f:
+        f.write(z["ref_file"].tobytes())
+    with open(os.path.join(d, "coll.fa"), "wb") as f:
+        f.write(z["coll_file"].tobytes())
+    with open(os.path.join(d, "list.txt"), "w") as f:
+        f.write(os.path.join(d, "ref.fa") + "\n" + os.path.join(d, "coll.fa") + "\n")
+    world = max(1, min(4, torch.cuda.device_count()))
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(os.path.dirname(HERE), "tools", "cms_bwt_multi.py"), "-o", os.path.join(d, "out")]
+    if rle_mode:
+        cmd.append("-r")
+    cmd.append(os.path.join(d, "list.txt"))
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=600)
+    assert r.returncode == 0, r.stdout.decode()[-3000:]
+    got = np.fromfile(os.path.join(d, "out.rl_bwt" if rle_mode else "out.bwt"), dtype=np.uint8)
+    want = O.rle(z["bwt"]) if rle_mode else z["bwt"]
+    assert np.array_equal(got, want)
