@@ -29,6 +29,11 @@ WORKLOADS = {
     "config3": dict(ref_bp=59_000_000, copies=100, div=0.001, seed=13),
     "config2": dict(ref_bp=5_000_000, copies=100, div=0.001, seed=11),
     "config1": dict(ref_bp=1_000_000, copies=10, div=0.001, seed=42),
+    # config 5 shape (248 Mbp reference, 1 % + 20 block SVs per copy): 4 copies fit the single-GPU
+    # bench; the full 64 copies are for --gpus 8
+    "config5_4": dict(ref_bp=248_000_000, copies=4, div=0.01, seed=17, svs=20),
+    "config5_16": dict(ref_bp=248_000_000, copies=16, div=0.01, seed=17, svs=20),
+    "config5": dict(ref_bp=248_000_000, copies=64, div=0.01, seed=17, svs=20),
 }
 METRIC = "collection Gbp/s to BWT (MS+head sort+emit)"
 
@@ -180,7 +185,7 @@ def run_multi(args, rank, world, local, dev, dist):
     if b <= a:
         raise SystemExit("bench.py: more ranks than documents")
     ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev,
-                                               first_copy=a, ncopies=b - a)
+                                               first_copy=a, ncopies=b - a, svs=w.get("svs", 0))
     torch.cuda.synchronize()
     x = P.augment(ref.cpu().numpy())
     ctx = P.Context(local)
@@ -281,9 +286,10 @@ def run_multi(args, rank, world, local, dev, dist):
             "metric": METRIC, "value": nsym / 1e9 / (ms_per_step / 1e3), "unit": "Gbp/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "%s: %d bp random ACGT reference + %d mutated copies at %g (SNP/ins/del), "
+            "config": {"workload": "%s: %d bp random ACGT reference + %d mutated copies at %g (SNP/ins/del)%s, "
                                    "plain BWT, documents sharded over %d GPUs" %
-                                   (args.workload, w["ref_bp"], w["copies"], w["div"], world),
+                                   (args.workload, w["ref_bp"], w["copies"], w["div"],
+                                    " + %d block SVs per copy" % w["svs"] if w.get("svs") else "", world),
                        "N_symbols": int(nsym), "documents": int(sp.ndocs_total), "n_ref_augmented": int(n),
                        "heads": int(H_total), "cache": "inputs (%.1f GB per GPU) larger than L2" % (N / 1e9),
                        "parallelism": "documents sharded (stage 1), tails by key range, tiles by reference-"
@@ -346,7 +352,8 @@ def main():
         return
 
     w = WORKLOADS[args.workload]
-    ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev)
+    ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev,
+                                               svs=w.get("svs", 0))
     torch.cuda.synchronize()
     nsym = N - ndocs
     x = P.augment(ref.cpu().numpy())
@@ -441,7 +448,8 @@ def main():
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": "%s: %d bp random ACGT reference + %d mutated copies at %g "
-                               "(SNP/ins/del), plain BWT" % (args.workload, w["ref_bp"], w["copies"], w["div"]),
+                               "(SNP/ins/del)%s, plain BWT" % (args.workload, w["ref_bp"], w["copies"], w["div"],
+                                                               " + %d block SVs per copy" % w["svs"] if w.get("svs") else ""),
                    "N_symbols": int(nsym), "documents": int(ndocs), "n_ref_augmented": int(n),
                    "heads": int(H), "cache": "inputs (%.1f GB) larger than L2" % (N / 1e9),
                    "device_ms_per_step": dev_ms,

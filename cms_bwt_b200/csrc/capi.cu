@@ -74,9 +74,9 @@ int cmsbwt_get_stats(const cmsbwt_ctx *c, cmsbwt_stats *out) {
 
 int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
   if (!c || !name) return CMSBWT_E_ARG;
-  if (!strcmp(name, "chunk_len")) { if (v < 64) return CMSBWT_E_ARG; c->chunk_len = v; }
+  if (!strcmp(name, "chunk_len")) { if (v != 0 && v < 64) return CMSBWT_E_ARG; c->chunk_len = v; }   // 0 = auto
   else if (!strcmp(name, "pool_div")) { if (v < 1) return CMSBWT_E_ARG; c->pool_div = v; }
-  else if (!strcmp(name, "kmer_k")) { if (v < 0 || v > 13) return CMSBWT_E_ARG; c->kmer_k = v; }
+  else if (!strcmp(name, "kmer_k")) { if (v < 0 || v > 14) return CMSBWT_E_ARG; c->kmer_k = v; }
   else if (!strcmp(name, "skip_min")) { if (v < 2) return CMSBWT_E_ARG; c->skip_min = v; }
   else if (!strcmp(name, "fast")) { c->fast = v != 0; }
   else if (!strcmp(name, "ms_occ")) { c->ms_occ = v; }

@@ -162,7 +162,7 @@ struct cmsbwt_ctx {
   u64 out_bytes = 0;
   int out_mode = 0;
   // params
-  i64 chunk_len = 8192;
+  i64 chunk_len = 0;         // text window per lane; 0 = by text length (ms_fast.cu), 8192 in k_ms
   i64 pool_div = 6;          // initial head-pool capacity = N / pool_div records
   i64 kmer_k = 0;            // 0 = auto
   i64 skip_min = 20;         // fast path: try the G skip for matches at least this long

@@ -316,7 +316,7 @@ void ms_stage(cmsbwt_ctx *c) {
   c->stats.pack_ms = 0;
   if (c->fast && c->pure && c->chunk_len <= 0x7FFFFFFF && ms_stage_fast(c)) return;
   const u64 N = c->N;
-  const u32 CH = (u32)c->chunk_len;
+  const u32 CH = c->chunk_len ? (u32)c->chunk_len : 8192u;
   const u64 nchunks = (N + CH - 1) / CH;
   if (nchunks >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "too many chunks"};
   DBuf cfirst, ccnt, coff, flags, counter, nbused, tmp;

@@ -132,7 +132,19 @@ __global__ void __launch_bounds__(256) k_msf_gather(const uint4 *pool, const u32
 bool ms_stage_fast(cmsbwt_ctx *c) {
   cudaStream_t st = c->st;
   const u64 N = c->N;
-  const u32 WL = (u32)c->chunk_len;
+  int sms = 148, occ = 4;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->dev);
+  void (*kern)(MsfParams) = c->ms_occ >= 12 ? k_ms_fast<12> : c->ms_occ >= 10 ? k_ms_fast<10> : c->ms_occ >= 8 ? k_ms_fast<8> : k_ms_fast<6>;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 128, MSF_STG * 128 * sizeof(uint4));
+  if (occ < 1) occ = 1;
+  // window length: a lane walks its window serially, so the kernel ends with its slowest window; at
+  // least 4 windows per resident lane keep that tail short (measured: 8192 is best at 5.9 Gbp,
+  // 1024-2048 at <= 1 Gbp or when whole windows are novel sequence), 0 = pick by the text length
+  u32 WL = (u32)c->chunk_len;
+  if (c->chunk_len == 0) {
+    u64 per = N / ((u64)sms * occ * 128 * 4);
+    WL = per >= 8192 ? 8192u : per <= 1024 ? 1024u : (u32)(per & ~63ull);
+  }
   const u64 nwin = (N + WL - 1) / WL;
   if (nwin >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "too many windows"};
   // ---- pack the text, collect separators ----
@@ -189,11 +201,6 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   size_t tb = 0;
   EXSUM64(nullptr, tb, wadj.as<u32>(), woff.as<u64>(), (int)(nwin + 1), st);
   tmp.alloc(tb, st);
-  int sms = 148, occ = 4;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->dev);
-  void (*kern)(MsfParams) = c->ms_occ >= 12 ? k_ms_fast<12> : c->ms_occ >= 10 ? k_ms_fast<10> : c->ms_occ >= 8 ? k_ms_fast<8> : k_ms_fast<6>;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 128, MSF_STG * 128 * sizeof(uint4));
-  if (occ < 1) occ = 1;
   // pool: batches of MSF_RB records; every window wastes at most one partly filled batch
   u64 rec_est = c->head_hint ? c->head_hint + c->head_hint / 8 : N / 16;
   u64 nb = rec_est / MSF_RB + nwin + 1024;

@@ -350,7 +350,7 @@ class ShardedPath:
         W = self.world
         S = SAMPLES_PER_RANK
         if Tn > 0:
-            idx = torch.linspace(0, Tn - 1, S, device=ks.device).to(torch.int64)
+            idx = (torch.arange(S, dtype=torch.int64, device=ks.device) * (Tn - 1)) // (S - 1)   # exact: Tn can exceed 2^24
             smp = ks[idx].to(torch.int64) & 0xFFFFFFFF
         else:
             smp = torch.full((S,), 0xFFFFFFFF, dtype=torch.int64, device=ks.device)

@@ -30,7 +30,7 @@ def _run_single(ctx, text, N, mode=P.MODE_PLAIN, **params):
     nbytes = ctx.emit(mode)
     out = _dev_u8(ctx.result_device(), nbytes, text.device).clone()
     st = ctx.stats()
-    ctx.set_param("fast", 1); ctx.set_param("tile_budget", 1 << 36); ctx.set_param("chunk_len", 8192)
+    ctx.set_param("fast", 1); ctx.set_param("tile_budget", 1 << 36); ctx.set_param("chunk_len", 0)
     return out, st
 
 
@@ -40,7 +40,7 @@ def _rle_decode_dev(rec):
     return torch.repeat_interleave(rec[:, 8].contiguous(), runs)
 
 
-def _run_two_ranks(x, dev, ref_bp, copies, div, seed):
+def _run_two_ranks(x, dev, ref_bp, copies, div, seed, svs=0):
     world = 2
     plan = multi.shard_documents([ref_bp] * copies, world)
     shared = multi.ThreadComm.Shared(world)
@@ -51,7 +51,7 @@ def _run_two_ranks(x, dev, ref_bp, copies, div, seed):
         try:
             torch.cuda.set_device(dev)
             a, b = plan[r]
-            _, text, N, nd = gen_device.make_text(ref_bp, copies, div, seed, dev, first_copy=a, ncopies=b - a)
+            _, text, N, nd = gen_device.make_text(ref_bp, copies, div, seed, dev, first_copy=a, ncopies=b - a, svs=svs)
             ctx = P.Context(dev.index)
             ctx.index_upload(x)
             sp, out = multi.run_sharded(ctx, dev, text.data_ptr(), N, nd, r, world, comm=multi.ThreadComm(shared, r))
@@ -154,4 +154,42 @@ def test_config3_full_size_paths_agree():
         ctx.close()
     del text
     d = _run_two_ranks(x, dev, ref_bp, copies, div, seed)
+    assert torch.equal(a, d), "two-rank path differs from the single-GPU path"
+
+
+def test_config5_scaled_chr1_reference_one_percent_with_svs():
+    """config 5 at 1/16 of the collection: the full 248 Mbp reference (n > 2^27: 28-bit SA ranks, the
+    widest keys of the tail sort) + 4 haplotypes at 1 % divergence with 20 block SVs each (deletion,
+    tandem duplication, reversal, translocation of 1-50 kbp): ~10 % of the positions are heads.
+    Lane kernel + tiles == warp kernel + sweep == two-rank path; histogram; RLE round trip."""
+    dev = torch.device("cuda:0")
+    if torch.cuda.get_device_properties(0).total_memory < 100 * 2 ** 30:
+        pytest.skip("needs a 180 GB device")
+    ref_bp, copies, div, seed, svs = 248_000_000, 4, 0.01, 17, 20
+    ref, text, N, nd = gen_device.make_text(ref_bp, copies, div, seed, dev, svs=svs)
+    x = P.augment(ref.cpu().numpy())
+    del ref
+    ctx = P.Context(0)
+    try:
+        ctx.index_upload(x)
+        a, st = _run_single(ctx, text, N)
+        assert st["fast_path"] == 1 and a.numel() == N
+        assert st["n_heads"] > 0.05 * N
+        hist_t = torch.zeros(256, dtype=torch.int64, device=dev)
+        hist_a = torch.zeros(256, dtype=torch.int64, device=dev)
+        for o in range(0, N, 1 << 29):
+            hist_t += torch.bincount(text[o:min(N, o + (1 << 29))].to(torch.int32), minlength=256)
+            hist_a += torch.bincount(a[o:min(N, o + (1 << 29))].to(torch.int32), minlength=256)
+        assert torch.equal(hist_t, hist_a)
+        c, st = _run_single(ctx, text, N, fast=0, tile_budget=0)
+        assert st["fast_path"] == 0 and st["light_tiles"] == 0
+        assert torch.equal(a, c), "general kernel + sweep differ from the lane kernel + tiles"
+        del c
+        rl, st = _run_single(ctx, text, N, mode=P.MODE_RLE)
+        assert torch.equal(_rle_decode_dev(rl), a), "RLE records do not decode to the plain BWT"
+        del rl
+    finally:
+        ctx.close()
+    del text
+    d = _run_two_ranks(x, dev, ref_bp, copies, div, seed, svs=svs)
     assert torch.equal(a, d), "two-rank path differs from the single-GPU path"

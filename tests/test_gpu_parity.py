@@ -75,7 +75,7 @@ def _check_case(ctx, x, text, want_bwt=None, desc="", chunk=None, check_ms=True,
     ctx.emit(P.MODE_RLE)
     rl = ctx.result_download().copy()
     assert np.array_equal(rl, O.rle(want)), "RLBWT " + desc
-    ctx.set_param("chunk_len", 8192)
+    ctx.set_param("chunk_len", 0)
     st = ctx.stats()
     for k, v in MODES["fast+tiles"].items():
         ctx.set_param(k, v)
@@ -180,7 +180,7 @@ def test_round_trip_properties_medium(ctx):
     assert np.array_equal(np.bincount(a, minlength=256), np.bincount(text, minlength=256))
     ctx.set_param("chunk_len", 1000)
     b = ctx.run(text, P.MODE_PLAIN).copy()
-    ctx.set_param("chunk_len", 8192)
+    ctx.set_param("chunk_len", 0)
     assert np.array_equal(a, b)
     rl = ctx.run(text, P.MODE_RLE).copy()
     assert np.array_equal(O.rle_decode(rl), a)

@@ -37,7 +37,39 @@ def mutate(ref, codes, div, gen, dev):
     return t
 
 
-def make_text(ref_bp, copies, div, seed, dev, pad=64, leading_empty=True, first_copy=0, ncopies=None):
+def apply_svs(s, gen, count, lo=1000, hi=50000):
+    """count block events on a device string, the model of tools/gen_synth.apply_svs: length uniform
+    in [lo, hi]; 30 % deletion, 30 % tandem duplication, 20 % reversal, 20 % translocation."""
+    for _ in range(count):
+        n = s.numel()
+        u = torch.rand(3, generator=gen, device=s.device).cpu().tolist()
+        L = lo + int(u[0] * (hi + 1 - lo))
+        if L >= n // 2:
+            L = max(1, n // 4)
+        a = int(u[1] * (n - L))
+        blk = s[a:a + L]
+        if u[2] < 0.3:
+            s = torch.cat([s[:a], s[a + L:]])
+        elif u[2] < 0.6:
+            s = torch.cat([s[:a + L], blk, s[a + L:]])
+        elif u[2] < 0.8:
+            s = torch.cat([s[:a], blk.flip(0), s[a + L:]])
+        else:
+            rest = torch.cat([s[:a], s[a + L:]])
+            b = int(torch.rand(1, generator=gen, device=s.device).item() * (rest.numel() + 1))
+            s = torch.cat([rest[:b], blk, rest[b:]])
+    return s
+
+
+def _codes(s):
+    codes = torch.zeros(s.numel(), dtype=torch.int64, device=s.device)
+    codes[s == 67] = 1
+    codes[s == 71] = 2
+    codes[s == 84] = 3
+    return codes
+
+
+def make_text(ref_bp, copies, div, seed, dev, pad=64, leading_empty=True, first_copy=0, ncopies=None, svs=0):
     """-> (ref uint8[ref_bp] on dev, text uint8[N + pad] on dev, N, ndocs).  Copies
     first_copy .. first_copy+ncopies-1 of the `copies`-copy collection (every copy has its own
     generator stream, so a shard of the collection is reproducible on any rank)."""
@@ -50,7 +82,7 @@ def make_text(ref_bp, copies, div, seed, dev, pad=64, leading_empty=True, first_
     codes[ref == 84] = 3
     if ncopies is None:
         ncopies = copies - first_copy
-    cap = int(ncopies * (ref_bp * (1 + div) + 64) + 64 + pad)
+    cap = int(ncopies * (ref_bp * (1 + div) + 64 + svs * 50000) + 64 + pad)
     text = torch.empty(cap, dtype=torch.uint8, device=dev)
     w = 0
     ndocs = 0
@@ -61,7 +93,12 @@ def make_text(ref_bp, copies, div, seed, dev, pad=64, leading_empty=True, first_
     for k in range(first_copy, first_copy + ncopies):
         g = torch.Generator(device=dev)
         g.manual_seed(seed * 1000003 + k + 1)
-        t = mutate(ref, codes, div, g, dev)
+        if svs:
+            base = apply_svs(ref, g, svs)
+            t = mutate(base, _codes(base), div, g, dev)
+            del base
+        else:
+            t = mutate(ref, codes, div, g, dev)
         L = t.numel()
         if w + L + 1 + pad > cap:
             raise RuntimeError("text buffer too small")
