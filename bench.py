@@ -31,6 +31,7 @@ WORKLOADS = {
     "config1": dict(ref_bp=1_000_000, copies=10, div=0.001, seed=42),
     # config 5 shape (248 Mbp reference, 1 % + 20 block SVs per copy): 4 copies fit the single-GPU
     # bench; the full 64 copies are for --gpus 8
+    "config4_10": dict(ref_bp=30_000, copies=30_000, div=0.001, seed=9),     # config 4 at 1/10
     "config5_4": dict(ref_bp=248_000_000, copies=4, div=0.01, seed=17, svs=20),
     "config5_16": dict(ref_bp=248_000_000, copies=16, div=0.01, seed=17, svs=20),
     "config5": dict(ref_bp=248_000_000, copies=64, div=0.01, seed=17, svs=20),

@@ -565,7 +565,6 @@ int cmsbwt_shard_emit(cmsbwt_ctx *c, const void *d_cov_full, uint64_t N_total, u
                       uint64_t doc_base, uint64_t *out_begin, uint64_t *out_len, uint64_t *plc_counts) {
   if (!c || !d_cov_full || world != c->sh_world || rank != c->sh_rank || world > 64)
     return fail(c, CMSBWT_E_ARG, "shard_emit");
-  if (c->tile_maxent > 11000) return fail(c, CMSBWT_E_LIMIT, "a tile holds more entries than shared memory");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
   Timer t(c->st);

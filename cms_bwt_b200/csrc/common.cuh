@@ -186,6 +186,8 @@ void pack_2bit(cmsbwt_ctx *c, const u8 *src, u64 len, u64 *dst, u64 nwords, u64 
 void sort_stage(cmsbwt_ctx *c);
 void sort_prepare(cmsbwt_ctx *c, u64 doc_base);
 void sort_kappa(cmsbwt_ctx *c);
+void sweep_count(cmsbwt_ctx *c, u64 I, DBuf &it_tr, DBuf &it_key, DBuf &it_pay, const u32 *pos, u32 ntiles,
+                 int tbits, u32 *within);
 void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_bits, u32 *nexth, u32 Tn,
                u32 *trank);
 void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32, DBuf &id, int key_bits,

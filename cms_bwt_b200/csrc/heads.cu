@@ -196,6 +196,51 @@ struct Tmp {                      // growable CUB scratch
   void need(size_t bytes, cudaStream_t st) { if (bytes > b.bytes) b.alloc(bytes, st); }
 };
 
+// Sort-based counting over I items (tailrank it_tr, key = tile << 32 | cls, payload = head id or ~0,
+// lo, hi inside the 64-position tile): stable LSD by tailrank, then by (tile, cls); one warp per tile
+// walks its items in kappa order.  pos[head id] = position in the same tile numbering.  Items of
+// tile `ntiles` (one past the last) are padding and are never visited.  Used by the single-GPU
+// fallback below and by the owners of deep tile ranges on the multi-GPU path (tiles.cu).
+void sweep_count(cmsbwt_ctx *c, u64 I, DBuf &it_tr, DBuf &it_key, DBuf &it_pay, const u32 *pos, u32 ntiles,
+                 int tbits, u32 *within) {
+  cudaStream_t st = c->st;
+  const int B = 256;
+  if (I == 0) return;
+  if (I >= 0x7FFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^31 tile items on one device"};
+  Tmp tmp;
+  size_t tb;
+  DBuf it_tr2, it_key2, idx, idx2;
+  it_tr2.alloc(I * 4, st); it_key2.alloc(I * 8, st); idx.alloc(I * 4, st); idx2.alloc(I * 4, st);
+  const u32 gI = (u32)((I + B - 1) / B);
+  k_iota<<<gI, B, 0, st>>>(idx2.as<u32>(), I);
+  tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, it_tr.as<u32>(), it_tr2.as<u32>(), idx2.as<u32>(),
+                                  idx.as<u32>(), (int)I, 0, tbits, st);
+  tmp.need(tb, st);
+  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_tr.as<u32>(), it_tr2.as<u32>(),
+                                     idx2.as<u32>(), idx.as<u32>(), (int)I, 0, tbits, st));
+  k_gather_keys<<<gI, B, 0, st>>>(idx.as<u32>(), it_key.as<u64>(), I, it_key2.as<u64>());
+  int kb = 33; while ((1ull << (kb - 32)) < (u64)ntiles + 1) kb++;
+  tb = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
+                                  idx2.as<u32>(), (int)I, 0, kb, st);
+  tmp.need(tb, st);
+  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
+                                     idx2.as<u32>(), (int)I, 0, kb, st));
+  c->launches += 12;
+  DBuf tbeg, tend;
+  tbeg.alloc(((size_t)ntiles + 1) * 4, st); tend.alloc(((size_t)ntiles + 1) * 4, st);
+  CK(cudaMemsetAsync(tbeg.p, 0, ((size_t)ntiles + 1) * 4, st));
+  CK(cudaMemsetAsync(tend.p, 0, ((size_t)ntiles + 1) * 4, st));
+  k_tile_bounds<<<gI, B, 0, st>>>(it_key.as<u64>(), I, tbeg.as<u32>(), tend.as<u32>());
+  u64 threads = (u64)ntiles * 32;
+  k_tile_count<<<(u32)((threads + B - 1) / B), B, 0, st>>>(idx2.as<u32>(), it_pay.as<u64>(), pos,
+                                                         tbeg.as<u32>(), tend.as<u32>(), ntiles, within);
+  c->launches += 2;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+}
+
 // link + tail labels (everything here is local to a shard of whole documents: phrases, tails and
 // next-tail pointers never leave a document).  doc_base = documents on lower shards.
 void sort_prepare(cmsbwt_ctx *c, u64 doc_base) {
@@ -305,46 +350,15 @@ void sort_stage(cmsbwt_ctx *c) {
   k_cov_diff<<<gH, B, 0, st>>>(pos, c->h_toNext.as<u32>(), H, c->d_cov.as<i32>());
   LAUNCH(c);
   c->s_tincl.release(); c->s_trank.release();
-  DBuf it_tr, it_tr2, it_key, it_key2, it_pay, idx, idx2;
-  it_tr.alloc(I * 4, st); it_tr2.alloc(I * 4, st); it_key.alloc(I * 8, st); it_key2.alloc(I * 8, st);
-  it_pay.alloc(I * 8, st); idx.alloc(I * 4, st); idx2.alloc(I * 4, st);
+  DBuf it_tr, it_key, it_pay;
+  it_tr.alloc(I * 4, st); it_key.alloc(I * 8, st); it_pay.alloc(I * 8, st);
   k_items<<<gH, B, 0, st>>>(pos, c->h_toNext.as<u32>(), kappa.as<u64>(), nitems.as<u32>(),
                             ioff.as<u64>(), H, it_tr.as<u32>(), it_key.as<u64>(), it_pay.as<u64>());
   LAUNCH(c);
-  // stable LSD: by tailrank (low word of kappa), then by (tile, cls)
   {
-    const u32 gI = (u32)((I + B - 1) / B);
-    k_iota<<<gI, B, 0, st>>>(idx2.as<u32>(), I);
     int tbits = 1; while ((1ull << tbits) < (u64)Tn) tbits++;
-    tb = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, tb, it_tr.as<u32>(), it_tr2.as<u32>(), idx2.as<u32>(),
-                                    idx.as<u32>(), (int)I, 0, tbits, st);
-    tmp.need(tb, st);
-    CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_tr.as<u32>(), it_tr2.as<u32>(),
-                                       idx2.as<u32>(), idx.as<u32>(), (int)I, 0, tbits, st));
-    k_gather_keys<<<gI, B, 0, st>>>(idx.as<u32>(), it_key.as<u64>(), I, it_key2.as<u64>());
-    u32 ntiles = n / CMS_TILE_W + 1;
-    int kb = 33; while ((1ull << (kb - 32)) < (u64)ntiles) kb++;
-    tb = 0;
-    cub::DeviceRadixSort::SortPairs(nullptr, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
-                                    idx2.as<u32>(), (int)I, 0, kb, st);
-    tmp.need(tb, st);
-    CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
-                                       idx2.as<u32>(), (int)I, 0, kb, st));
-    c->launches += 12;
-    DBuf tbeg, tend;
-    tbeg.alloc((size_t)ntiles * 4, st); tend.alloc((size_t)ntiles * 4, st);
-    CK(cudaMemsetAsync(tbeg.p, 0, (size_t)ntiles * 4, st));
-    CK(cudaMemsetAsync(tend.p, 0, (size_t)ntiles * 4, st));
-    k_tile_bounds<<<gI, B, 0, st>>>(it_key.as<u64>(), I, tbeg.as<u32>(), tend.as<u32>());
     c->h_within.alloc(H * 4, st);
-    u64 threads = (u64)ntiles * 32;
-    k_tile_count<<<(u32)((threads + B - 1) / B), B, 0, st>>>(idx2.as<u32>(), it_pay.as<u64>(), pos,
-                                                           tbeg.as<u32>(), tend.as<u32>(), ntiles,
-                                                           c->h_within.as<u32>());
-    c->launches += 2;
-    CK(cudaGetLastError());
-    CK(cudaStreamSynchronize(st));
+    sweep_count(c, I, it_tr, it_key, it_pay, pos, n / CMS_TILE_W + 1, tbits, c->h_within.as<u32>());
   }
   c->s_kappa.release(); c->s_nitems.release(); c->s_sexcl.release();
 }

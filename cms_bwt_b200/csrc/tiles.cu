@@ -538,6 +538,64 @@ __global__ void __launch_bounds__(256) k_sh_plc_scatter(const u64 *plc, u64 P, u
   }
 }
 
+// ---- deep tile ranges (more entries per tile than shared memory holds, e.g. a short reference
+// under very many documents): the owner counts with the sort-based sweep of heads.cu instead of
+// k_tile_place.  Items live in 64-position sub-tiles (CMS_TILE_W) numbered inside the device's range.
+#define SUBT (LT_W / CMS_TILE_W)
+__global__ void __launch_bounds__(256) k_sh_deep_items(const TileEnt *he, const TileEnt *re, const u32 *hoff,
+                                                       const u32 *roff, u32 HE, u32 pad_tile, u32 *it_tr,
+                                                       u64 *it_key, u64 *it_pay, u32 *epos) {
+  const u32 t = blockIdx.x;
+  const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
+  for (u32 j = h0 + threadIdx.x; j < h1; j += blockDim.x) {
+    const TileEnt e = he[j];
+    const u32 q = e.b & (LT_W - 1), q6 = q & (CMS_TILE_W - 1);
+    it_tr[j] = (u32)e.kappa;
+    it_key[j] = ((u64)(t * SUBT + q / CMS_TILE_W) << 32) | (e.kappa >> 32);
+    it_pay[j] = ((u64)j << 32) | (q6 << 8) | q6;
+    epos[j] = t * LT_W + q;
+  }
+  for (u32 j = r0 + threadIdx.x; j < r1; j += blockDim.x) {
+    const TileEnt e = re[j];
+    const u32 lo = e.a & 0xFFFF, hi = e.a >> 16;
+    for (u32 s = 0; s < SUBT; s++) {
+      const u32 a = s * CMS_TILE_W, b = a + CMS_TILE_W - 1;
+      const u64 o = (u64)HE + (u64)j * SUBT + s;
+      const bool in = lo <= b && hi >= a;
+      it_tr[o] = (u32)e.kappa;
+      it_key[o] = ((u64)(in ? t * SUBT + s : pad_tile) << 32) | (e.kappa >> 32);
+      it_pay[o] = (0xFFFFFFFFull << 32) | ((in ? max(lo, a) - a : 1u) << 8) | (in ? min(hi, b) - a : 0u);
+    }
+  }
+}
+__global__ void __launch_bounds__(256) k_sh_deep_plc(const TileEnt *he, const u32 *hoff, const u32 *within,
+                                                     const u32 *isa, const u64 *base, u32 n, u32 t0, u64 *plc) {
+  const u32 t = blockIdx.x;
+  for (u32 j = hoff[t] + threadIdx.x; j < hoff[t + 1]; j += blockDim.x) {
+    const TileEnt e = he[j];
+    const u32 p = ((t + t0) << LT_SHIFT) + (e.b & (LT_W - 1));
+    const u64 off = (p < n ? base[isa[p]] : 0) + within[j];
+    plc[j] = (off << 8) | ((e.b >> 8) & 0xFF);
+  }
+}
+static void shard_place_deep(cmsbwt_ctx *c, const u64 *base, u64 *plc) {
+  cudaStream_t st = c->st;
+  const u32 tp = c->sh_tp, HE = c->sh_he;
+  const u64 I = (u64)HE + (u64)c->sh_re * SUBT;
+  DBuf it_tr, it_key, it_pay, epos, within;
+  it_tr.alloc((I + 1) * 4, st); it_key.alloc((I + 1) * 8, st); it_pay.alloc((I + 1) * 8, st);
+  epos.alloc(((size_t)HE + 1) * 4, st); within.alloc(((size_t)HE + 1) * 4, st);
+  k_sh_deep_items<<<tp, 256, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+                                      c->t_roff.as<u32>(), HE, tp * SUBT, it_tr.as<u32>(), it_key.as<u64>(),
+                                      it_pay.as<u64>(), epos.as<u32>());
+  LAUNCH(c);
+  sweep_count(c, I, it_tr, it_key, it_pay, epos.as<u32>(), tp * SUBT, 32, within.as<u32>());
+  k_sh_deep_plc<<<tp, 256, 0, st>>>(c->t_he.as<TileEnt>(), c->t_hoff.as<u32>(), within.as<u32>(), c->ix.isa, base,
+                                    c->ix.n, c->sh_rank * tp, plc);
+  LAUNCH(c);
+  CK(cudaGetLastError());
+}
+
 // pass B for this device's tile range: (offset << 8 | symbol) per head entry, then this shard's
 // document terminators (offset = global document index); grouped by destination in sh_plc.
 void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
@@ -550,13 +608,18 @@ void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
   DBuf raw, tmp;
   raw.alloc((P + 1) * 8, st);
   c->sh_plc.alloc((P + 1) * 8, st);
-  size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;
-  if (sm > 40 * 1024)
-    CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  k_tile_place<<<tp, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                           c->t_roff.as<u32>(), c->ix.isa, base, n, c->sh_rank * tp, nullptr,
-                                           raw.as<u64>(), nullptr, nullptr,
-                                           make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]));
+  c->stats.light_tiles = c->tile_maxent <= LT_MAX_ENTRIES && c->tile_budget > 0;
+  if (!c->stats.light_tiles) {
+    shard_place_deep(c, base, raw.as<u64>());
+  } else {
+    size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;
+    if (sm > 40 * 1024)
+      CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_tile_place<<<tp, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+                                             c->t_roff.as<u32>(), c->ix.isa, base, n, c->sh_rank * tp, nullptr,
+                                             raw.as<u64>(), nullptr, nullptr,
+                                             make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]));
+  }
   k_sh_sentinel_plc<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                                            c->s_sexcl.as<u32>(), H, doc_base, raw.as<u64>() + c->sh_he);
   // group the placements by destination (= owner of the output byte range): histogram, offsets,

@@ -28,7 +28,6 @@ SAMPLES_PER_RANK = 1024
 PACK_FROM_WORLD = int(__import__("os").environ.get("CMSBWT_PACK_FROM_WORLD", 4))   # pack paired exchanges into one collective
 # from this many ranks on (measured: the packing passes cost more than a collective at 2 ranks)
 TIE_CAPACITY = int(__import__("os").environ.get("CMSBWT_TIE_CAPACITY", 1 << 17))             # tied tails per rank that ride along with the count of a refinement round
-TILE_MAX_ENTRIES = 11000          # tiles.cu LT_MAX_ENTRIES
 
 
 def shard_documents(doc_lengths, world):
@@ -294,12 +293,10 @@ class ShardedPath:
         he_slab = [sum(hrecv[:s]) for s in range(W)]
         re_slab = [sum(rrecv[:s]) for s in range(W)]
         self._mark("x_tiles")
-        maxent = ops.tiles_merge(W, R, he, re, hoffs, roffs, he_slab, re_slab, ndocs_total)
+        # a tile range deeper than shared memory holds (very many documents over a short reference)
+        # is counted by its owner with the sort-based sweep instead of the tile kernel (tiles.cu)
+        self.tile_max_entries = ops.tiles_merge(W, R, he, re, hoffs, roffs, he_slab, re_slab, ndocs_total)
         self._mark("d_tiles_merge")
-        gmax = max(x[0] for x in self._allgather_ints([maxent]))
-        if gmax > TILE_MAX_ENTRIES:
-            raise CmsBwtError(-3, "a tile holds %d entries (limit %d): collection too deep for the "
-                                  "multi-GPU tile path" % (gmax, TILE_MAX_ENTRIES))
         cov = ops.buffer("cov_slice")
         cov_full = ops.empty(cov.numel() * W, cov.dtype)
         self.comm.all_gather(cov_full, cov)

@@ -122,8 +122,13 @@ def test_config4_scaled_many_short_documents():
         assert torch.equal(a, c)
         rl, st3 = _run_single(ctx, text, N, mode=P.MODE_RLE)
         assert torch.equal(_rle_decode_dev(rl), a)
+        del c, rl
     finally:
         ctx.close()
+    del text
+    # two ranks: every tile of the 118 holds ~10^5 entries, so the owners count with the sweep
+    d = _run_two_ranks(x, dev, 30_000, 30_000, 0.001, 9)
+    assert torch.equal(a, d), "two-rank path differs from the single-GPU path"
 
 
 def test_config3_full_size_paths_agree():

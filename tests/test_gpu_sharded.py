@@ -112,6 +112,27 @@ def test_sharded_synthetic(world):
     assert all(r[3]["fast_path"] == 1 for r in res)
 
 
+@pytest.mark.parametrize("world", [1, 2, 3])
+def test_sharded_deep_tile_ranges(world):
+    """owners count with the sort-based sweep (forced here; taken by itself when a tile holds more
+    entries than shared memory, e.g. config 4's 300,000 documents over 30 kbp)"""
+    ref, copies = gen_synth.make_collection(30000, 9, 0.004, 21)
+    x = P.augment(ref)
+    text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    res = _check(x, text, world, "synthetic 30k x 9, deep", params={"tile_budget": 0})
+    assert all(r[3]["light_tiles"] == 0 for r in res)
+    done = 0
+    for seed in range(40, 80):
+        c = fuzz_cases.make_case(seed)
+        x = P.augment(P.read_reference(c["ref_file"]))
+        text, nd = P.parse_collection(c["coll_file"])
+        if nd < world + 1 or len(text) < 40 or any(len(s_) == 0 for s_, _ in split_text(text, world)):
+            continue
+        _check(x, text, world, "fuzz %d deep" % seed, params={"tile_budget": 0})
+        done += 1
+    assert done >= 10
+
+
 def test_sharded_golden_fixtures():
     n = 0
     for f in sorted(glob.glob(os.path.join(GOLDEN, "*.npz"))):
