@@ -94,6 +94,7 @@ int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
       cudaGetLastError();
     }
   }
+  else if (!strcmp(name, "ms_variant")) { c->ms_variant = v; }
   else if (!strcmp(name, "slots")) { c->use_slots = v != 0; }          // takes effect at the next index_upload
   else if (!strcmp(name, "nb_t1")) { c->nb_t[0] = v; }
   else if (!strcmp(name, "nb_t4")) { c->nb_t[1] = v; }

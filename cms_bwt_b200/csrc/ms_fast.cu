@@ -135,7 +135,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   int sms = 148, occ = 4;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->dev);
   void (*kern)(MsfParams) = c->ms_occ >= 12 ? k_ms_fast<12> : c->ms_occ >= 10 ? k_ms_fast<10> : c->ms_occ >= 8 ? k_ms_fast<8> : k_ms_fast<6>;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 128, MSF_STG * 128 * sizeof(uint4));
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 128, MSF_SMEM_BYTES(128));
   if (occ < 1) occ = 1;
   // window length: a lane walks its window serially, so the kernel ends with its slowest window; at
   // least 4 windows per resident lane keep that tail short (measured: 8192 is best at 5.9 Gbp,
@@ -216,7 +216,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     P.xp = c->xp; P.x8 = c->ix.x; P.sak = c->d_sak.as<u64>(); P.ktab = c->ix.ktab; P.G = c->ix.G;
     P.n = c->ix.n; P.n_acgt = c->n_acgt; P.k = c->ix.k;
     P.tp = c->d_tp.as<u64>(); P.N = N; P.seps = c->d_seps.as<u64>(); P.nseps = nseps; P.wsep = wsep.as<u32>();
-    P.WL = WL; P.nwin = nwin; P.skip_min = (u32)c->skip_min;
+    P.WL = WL; P.nwin = nwin; P.skip_min = (u32)c->skip_min; P.variant = (u32)c->ms_variant;
     P.pool = pool.as<u32>(); P.batch_next = bnext.as<u32>(); P.nb_cap = (u32)nb; P.nb_used = nbused.as<u32>();
     P.wfirst = wfirst.as<u32>(); P.wcnt = wcnt.as<u32>(); P.wfirstpos = wfp.as<u32>(); P.wlastpos = wlp.as<u32>();
     P.flags = flags.as<u32>(); P.win_counter = counter.as<unsigned long long>();
@@ -238,7 +238,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
       apw.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
       cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &apw);
     }
-    kern<<<grid, 128, MSF_STG * 128 * sizeof(uint4), st>>>(P);
+    kern<<<grid, 128, MSF_SMEM_BYTES(128), st>>>(P);
     if (c->l2_pin && c->l2_persist_max) {
       apw.accessPolicyWindow.num_bytes = 0;
       cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &apw);

@@ -154,6 +154,8 @@ struct MsfParams {
   msf_u32 WL;             // window length
   msf_u64 nwin;
   msf_u32 skip_min;       // try the G skip when len >= skip_min
+  msf_u32 variant;        // bit 1: per-lane text word cache in shared memory; bit 3: L2 prefetch of the G
+                          // line(s) a skip will probe, issued when the extension ends (both on by default)
   // output
   msf_u32 *pool;          // records of 4 x u32: rel, pos, len, cs (ch | sm << 8 | tentative << 9)
   msf_u32 *batch_next;
@@ -177,6 +179,8 @@ struct MsfLane {
   msf_u32 chb;            // code of the base before position i (4 = not loaded yet)
 #if !defined(__CUDA_ARCH__)
   msf_rec4 hstage[MSF_STG];
+  msf_u64 htc0, htc1;
+  msf_u32 htcw;
 #endif
 };
 
@@ -187,9 +191,33 @@ struct MsfLane {
 #if defined(__CUDA_ARCH__)
 extern __shared__ uint4 msf_stage_smem[];
 #define MSF_STAGE(L, j) msf_stage_smem[(j) * blockDim.x + threadIdx.x]
+// per-lane text cache behind the stage area: two consecutive packed words and the index of the first
+#define MSF_TC0(L) (((msf_u64 *)(msf_stage_smem + MSF_STG * blockDim.x))[threadIdx.x])
+#define MSF_TC1(L) (((msf_u64 *)(msf_stage_smem + MSF_STG * blockDim.x))[blockDim.x + threadIdx.x])
+#define MSF_TCW(L) (((msf_u32 *)(msf_stage_smem + MSF_STG * blockDim.x))[4 * blockDim.x + threadIdx.x])
 #else
 #define MSF_STAGE(L, j) (L).hstage[j]
+#define MSF_TC0(L) (L).htc0
+#define MSF_TC1(L) (L).htc1
+#define MSF_TCW(L) (L).htcw
 #endif
+#define MSF_SMEM_BYTES(threads) ((size_t)(threads) * (MSF_STG * 16 + 8 + 8 + 4))
+
+// 32 text bases starting at base j through the lane's two-word cache: consecutive search positions
+// (the cluster of short heads before a mutation) share their words, and the lane's line has long
+// left L1 by the time it comes back (1024 lanes per SM each stream slots through it)
+MSF_HD msf_u64 msf_text64_cached(const MsfParams &P, MsfLane &L, msf_u64 j) {
+  const msf_u64 wi = j >> 5;
+  const msf_u32 sh = (msf_u32)(j & 31) * 2, w32 = (msf_u32)wi;
+  msf_u64 c0, c1;
+  if (MSF_TCW(L) == w32) { c0 = MSF_TC0(L); c1 = MSF_TC1(L); }
+  else {
+    if (MSF_TCW(L) + 1u == w32 && w32 != 0) c0 = MSF_TC1(L); else c0 = MSF_LD64(P.tp + wi);
+    c1 = MSF_LD64(P.tp + wi + 1);
+    MSF_TC0(L) = c0; MSF_TC1(L) = c1; MSF_TCW(L) = w32;
+  }
+  return sh ? (c0 >> sh) | (c1 << (64 - sh)) : c0;
+}
 
 MSF_HD void msf_store_rec(const MsfParams &P, msf_u64 slot, msf_u32 a, msf_u32 b, msf_u32 c, msf_u32 d) {
 #if defined(__CUDA_ARCH__)
@@ -409,6 +437,7 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
       L.prevterm = (L.i == 0) || (L.sepidx > 0 && MSF_LD64(P.seps + L.sepidx - 1) == L.i - 1);
       L.prevpos = MSF_INVALID;
       L.first = 1;
+      MSF_TCW(L) = 0xFFFFFFFFu;
       L.curb = MSF_NOB;
       L.fill = 0;
       L.cnt = 0;
@@ -434,7 +463,7 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
       L.limit = dist > 0xFFFFFFF0ull ? 0xFFFFFFF0u : (msf_u32)dist;
       if (L.limit < KL) { act = MSF_ACT_GENERIC; break; }
       // one read serves the k-mer, the key and the symbol before i (the head record needs it)
-      msf_u64 tw = msf_get64(P.tp, L.i ? L.i - 1 : 0);
+      msf_u64 tw = (P.variant & 2u) ? msf_text64_cached(P, L, L.i ? L.i - 1 : 0) : msf_get64(P.tp, L.i ? L.i - 1 : 0);
       if (L.i) { L.chb = (msf_u32)tw & 3u; tw >>= 2; }
       msf_u64 be = msf_be64(tw);
       msf_u32 code = (msf_u32)(be >> (64 - 2 * P.k));
@@ -561,7 +590,16 @@ __device__ __forceinline__ void msf_warp_iter(const MsfParams &P, MsfLane &L) {
       if (res != 0xFFFFFFFFu || blen + 1024u >= bmax) break;
       blen += 1024u;
     }
-    if (lane == src) { msf_ext_done(P, L, res, bmax); act = MSF_ACT_FIN; }
+    if (lane == src) {
+      msf_ext_done(P, L, res, bmax);
+      act = MSF_ACT_FIN;
+      // phase D will probe G[E - 32, E): have the line(s) on their way while phase C runs
+      if ((P.variant & 8u) && L.len >= P.skip_min && L.len >= 32u) {
+        const msf_u32 *gp = P.G + L.pos + L.len;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(gp - 32));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(gp - 1));
+      }
+    }
   }
   // phase C
   if (act & MSF_ACT_GENERIC) msf_generic_search(P, L.i, L.limit, L.pos, L.len, L.sm);

@@ -91,7 +91,7 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   P.xp = xp.data(); P.x8 = x8.data(); P.sak = sak.data(); P.ktab = ktab.data(); P.G = G.data();
   P.n = n; P.n_acgt = n_acgt; P.k = k;
   P.tp = tp.data(); P.N = N; P.seps = seps.data(); P.nseps = nseps; P.wsep = wsep.data();
-  P.WL = WL; P.nwin = nwin; P.skip_min = skip_min;
+  P.WL = WL; P.nwin = nwin; P.skip_min = skip_min; P.variant = 2;
   P.pool = pool.data(); P.batch_next = bnext.data(); P.nb_cap = (u32)nb_cap; P.nb_used = &nb_used;
   P.wfirst = wfirst.data(); P.wcnt = wcnt.data(); P.wfirstpos = wfp.data(); P.wlastpos = wlp.data();
   P.flags = flags; P.win_counter = &counter;
