@@ -187,7 +187,11 @@ int cmsbwt_shard_apply(cmsbwt_ctx *ctx, const void *d_plc, uint64_t count);
  * a run that straddles a device border is merged by the host layer (multi.rle_sharded). */
 int cmsbwt_shard_rle(cmsbwt_ctx *ctx, uint64_t *n_records);
 
-/* tuning knobs (0 = default): chunk length of the MS kernel, tile width is fixed at 64. */
+/* tuning knobs: "chunk_len" (text window of an MS lane; 0 = by text length, 1024..8192), "kmer_k"
+ * (order of the k-mer table, 0 = largest k <= 14 with 4^k <= n; takes effect at the next
+ * index_upload), "fast" (0: 8-bit warp kernel for every input), "tile_budget" (0: sort-based sweep
+ * instead of the tile kernels), "slots", "skip_min", "ms_occ", "scatter_mb", "nb_t1/4/8",
+ * "ms_variant" (measurement switches).  Results never depend on them. */
 int cmsbwt_set_param(cmsbwt_ctx *ctx, const char *name, int64_t value);
 
 #ifdef __cplusplus
