@@ -31,7 +31,8 @@ WORKLOADS = {
     "config1": dict(ref_bp=1_000_000, copies=10, div=0.001, seed=42),
     # config 5 shape (248 Mbp reference, 1 % + 20 block SVs per copy): 4 copies fit the single-GPU
     # bench; the full 64 copies are for --gpus 8
-    "config4_10": dict(ref_bp=30_000, copies=30_000, div=0.001, seed=9),     # config 4 at 1/10
+    "config4_10": dict(ref_bp=30_000, copies=30_000, div=0.001, seed=9, many=True),     # config 4 at 1/10
+    "config4": dict(ref_bp=30_000, copies=300_000, div=0.001, seed=9, many=True),
     "config5_4": dict(ref_bp=248_000_000, copies=4, div=0.01, seed=17, svs=20),
     "config5_16": dict(ref_bp=248_000_000, copies=16, div=0.01, seed=17, svs=20),
     "config5": dict(ref_bp=248_000_000, copies=64, div=0.01, seed=17, svs=20),
@@ -185,8 +186,13 @@ def run_multi(args, rank, world, local, dev, dist):
     a, b = plan[rank]
     if b <= a:
         raise SystemExit("bench.py: more ranks than documents")
-    ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev,
-                                               first_copy=a, ncopies=b - a, svs=w.get("svs", 0))
+    if w.get("many"):       # shards on batch borders of the generator
+        a, b = (a // 2000) * 2000, (w["copies"] if rank == world - 1 else (b // 2000) * 2000)
+        ref, text, N, ndocs = gen_device.make_text_many(w["ref_bp"], w["copies"], w["div"], w["seed"], dev,
+                                                        first_copy=a, ncopies=b - a)
+    else:
+        ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev,
+                                                   first_copy=a, ncopies=b - a, svs=w.get("svs", 0))
     torch.cuda.synchronize()
     x = P.augment(ref.cpu().numpy())
     ctx = P.Context(local)
@@ -353,8 +359,11 @@ def main():
         return
 
     w = WORKLOADS[args.workload]
-    ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev,
-                                               svs=w.get("svs", 0))
+    if w.get("many"):
+        ref, text, N, ndocs = gen_device.make_text_many(w["ref_bp"], w["copies"], w["div"], w["seed"], dev)
+    else:
+        ref, text, N, ndocs = gen_device.make_text(w["ref_bp"], w["copies"], w["div"], w["seed"], dev,
+                                                   svs=w.get("svs", 0))
     torch.cuda.synchronize()
     nsym = N - ndocs
     x = P.augment(ref.cpu().numpy())

@@ -159,35 +159,55 @@ __global__ void k_tile_bounds(const u64 *skey, u64 n, u32 *tbeg, u32 *tend) {
   if (j + 1 == n || (u32)(skey[j + 1] >> 32) != t) tend[t] = (u32)j + 1;
 }
 // one warp per tile: walk the tile's items in kappa order, 32 at a time; for every head item
-// count the earlier items whose interval holds the head's position.
-__global__ void k_tile_count(const u32 *sidx, const u64 *it_pay, const u32 *pos, const u32 *tbeg,
-                             const u32 *tend, u32 ntiles, u32 *within) {
+// count the earlier items whose interval holds the head's position.  A tile is walked by ONE warp, so
+// nothing else hides the three dependent reads of an item (sorted index -> payload -> position):
+// they are issued TC_K blocks of 32 at a time, one group ahead of their use.
+#define TC_K 8
+#define TC_NONE 0xFFFFFFFF00000100ull       // no head, empty interval (lo 1 > hi 0)
+__device__ __forceinline__ void tc_load(const u32 *__restrict__ sidx, const u64 *__restrict__ it_pay,
+                                        const u32 *__restrict__ pos, u32 j0, u32 e, int lane, u64 *P, u32 *Q) {
+  u32 s[TC_K];
+#pragma unroll
+  for (int k = 0; k < TC_K; k++) { const u32 j = j0 + 32u * k + lane; s[k] = j < e ? sidx[j] : 0xFFFFFFFFu; }
+#pragma unroll
+  for (int k = 0; k < TC_K; k++) P[k] = s[k] != 0xFFFFFFFFu ? it_pay[s[k]] : TC_NONE;
+#pragma unroll
+  for (int k = 0; k < TC_K; k++) { const u32 hid = (u32)(P[k] >> 32); Q[k] = hid != 0xFFFFFFFFu ? pos[hid] : 0u; }
+}
+__global__ void k_tile_count(const u32 *__restrict__ sidx, const u64 *__restrict__ it_pay,
+                             const u32 *__restrict__ pos, const u32 *tbeg, const u32 *tend, u32 ntiles,
+                             u32 *__restrict__ within) {
   const int lane = threadIdx.x & 31;
   u32 t = (u32)(((u64)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   if (t >= ntiles) return;
   u32 b = tbeg[t], e = tend[t];
   if (b >= e) return;
   u32 run0 = 0, run1 = 0;           // items so far covering tile offsets lane / lane + 32
-  for (u32 j0 = b; j0 < e; j0 += 32) {
-    u32 j = j0 + lane;
-    u32 lo = 1, hi = 0, hid = 0xFFFFFFFFu, q = 0;
-    if (j < e) {
-      u64 pay = it_pay[sidx[j]];
-      hid = (u32)(pay >> 32); lo = (u32)(pay >> 8) & 0xFF; hi = (u32)pay & 0xFF;
-      if (hid != 0xFFFFFFFFu) q = pos[hid] - t * CMS_TILE_W;
+  u64 pay[TC_K], npay[TC_K];
+  u32 ps[TC_K], nps[TC_K];
+  tc_load(sidx, it_pay, pos, b, e, lane, npay, nps);
+  for (u32 g0 = b; g0 < e; g0 += 32u * TC_K) {
+#pragma unroll
+    for (int k = 0; k < TC_K; k++) { pay[k] = npay[k]; ps[k] = nps[k]; }
+    if (g0 + 32u * TC_K < e) tc_load(sidx, it_pay, pos, g0 + 32u * TC_K, e, lane, npay, nps);
+#pragma unroll
+    for (int k = 0; k < TC_K; k++) {
+      if (g0 + 32u * k >= e) break;                       // uniform over the warp
+      const u32 hid = (u32)(pay[k] >> 32), lo = (u32)(pay[k] >> 8) & 0xFF, hi = (u32)pay[k] & 0xFF;
+      const u32 q = hid != 0xFFFFFFFFu ? ps[k] - t * CMS_TILE_W : 0u;
+      // the select must happen on the reading lane, so fetch both counters and pick here
+      u32 r0 = __shfl_sync(0xffffffffu, run0, q & 31), r1 = __shfl_sync(0xffffffffu, run1, q & 31);
+      u32 base = q < 32 ? r0 : r1;
+      u32 cnt = 0, a0 = 0, a1 = 0;
+      for (int jj = 0; jj < 32; jj++) {
+        u32 l2 = __shfl_sync(0xffffffffu, lo, jj), h2 = __shfl_sync(0xffffffffu, hi, jj);
+        cnt += (jj < lane) & (l2 <= q) & (q <= h2);
+        a0 += (l2 <= (u32)lane) & ((u32)lane <= h2);
+        a1 += (l2 <= (u32)lane + 32) & ((u32)lane + 32 <= h2);
+      }
+      if (hid != 0xFFFFFFFFu) within[hid] = base + cnt;
+      run0 += a0; run1 += a1;
     }
-    // the select must happen on the reading lane, so fetch both counters and pick here
-    u32 r0 = __shfl_sync(0xffffffffu, run0, q & 31), r1 = __shfl_sync(0xffffffffu, run1, q & 31);
-    u32 base = q < 32 ? r0 : r1;
-    u32 cnt = 0, a0 = 0, a1 = 0;
-    for (int jj = 0; jj < 32; jj++) {
-      u32 l2 = __shfl_sync(0xffffffffu, lo, jj), h2 = __shfl_sync(0xffffffffu, hi, jj);
-      cnt += (jj < lane) & (l2 <= q) & (q <= h2);
-      a0 += (l2 <= (u32)lane) & ((u32)lane <= h2);
-      a1 += (l2 <= (u32)lane + 32) & ((u32)lane + 32 <= h2);
-    }
-    if (hid != 0xFFFFFFFFu) within[hid] = base + cnt;
-    run0 += a0; run1 += a1;
   }
 }
 

@@ -278,10 +278,20 @@ __global__ void k_place_sentinels(const u32 *len, const u16 *cs, const u32 *sexc
 // Builds the tile entries and cov[]; false = too heavy for the brute-force path (nothing kept).
 static bool tiles_finish(cmsbwt_ctx *c, DBuf &acc, u32 HE, u64 R, DBuf &sexcl);
 // histogram + scan + scatter of this device's heads over ntiles tiles -> t_he, t_re, t_hoff, t_roff
-static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_out, u64 *R_out) {
+__global__ void k_tile_deepest(const u32 *hcnt, const u32 *rcnt, u32 ntiles, u32 *mx) {
+  u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+  u32 v = t < ntiles ? hcnt[t] + rcnt[t] : 0;
+  v = __reduce_max_sync(0xffffffffu, v);
+  if ((threadIdx.x & 31) == 0 && v) atomicMax(mx, v);
+}
+// depth_limit > 0: give up (false) as soon as a tile is known to hold more entries than that --
+// before the histogram when even the average does, else right after it, before the scatter
+static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_out, u64 *R_out,
+                          u32 depth_limit = 0) {
   cudaStream_t st = c->st;
   const u64 H = c->H;
   const int B = 256;
+  if (depth_limit && H > (u64)ntiles * depth_limit) return false;
   const u32 gH = (u32)((H + B - 1) / B);
   DBuf hcnt, rcnt, tmp;
   hcnt.alloc(((size_t)ntiles + 1) * 4, st); rcnt.alloc(((size_t)ntiles + 1) * 4, st);
@@ -305,10 +315,16 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
     CK(cub::DeviceReduce::Sum(tmp2.p, tr, rcnt.as<u32>(), rtot.as<unsigned long long>(), (int)ntiles, st));
   }
   unsigned long long R = 0;
+  u32 deepest = 0;
+  DBuf mx; mx.alloc(4, st);
+  CK(cudaMemsetAsync(mx.p, 0, 4, st));
+  k_tile_deepest<<<(ntiles + B - 1) / B, B, 0, st>>>(hcnt.as<u32>(), rcnt.as<u32>(), ntiles, mx.as<u32>());
   CK(cudaMemcpyAsync(&R, rtot.p, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&deepest, mx.p, 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  c->launches += 4;
+  c->launches += 5;
   if (R >= 0xFFFFFFF0ull) return false;
+  if (depth_limit && deepest > depth_limit) return false;
   CK(cub::DeviceScan::ExclusiveSum(tmp.p, t1, rcnt.as<u32>(), c->t_roff.as<u32>(), (int)(ntiles + 1), st));
   u32 HE = 0;
   CK(cudaMemcpyAsync(&HE, c->t_hoff.as<u32>() + ntiles, 4, cudaMemcpyDeviceToHost, st));
@@ -337,7 +353,7 @@ bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
   CK(cudaMemsetAsync(acc.p, 0, 16, st));
   u32 HE = 0;
   u64 R = 0;
-  if (!tiles_scatter(c, kappa, ntiles, &HE, &R)) return false;
+  if (!tiles_scatter(c, kappa, ntiles, &HE, &R, LT_MAX_ENTRIES)) return false;
   c->d_cov.alloc(((size_t)n + 1) * 4, st);
   k_tile_cov<<<ntiles, LT_THREADS, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                             c->t_roff.as<u32>(), n, (u32)c->stats.n_docs, 0, c->d_cov.as<u32>(),

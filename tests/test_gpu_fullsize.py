@@ -40,7 +40,7 @@ def _rle_decode_dev(rec):
     return torch.repeat_interleave(rec[:, 8].contiguous(), runs)
 
 
-def _run_two_ranks(x, dev, ref_bp, copies, div, seed, svs=0):
+def _run_two_ranks(x, dev, ref_bp, copies, div, seed, svs=0, many=False):
     world = 2
     plan = multi.shard_documents([ref_bp] * copies, world)
     shared = multi.ThreadComm.Shared(world)
@@ -51,7 +51,10 @@ def _run_two_ranks(x, dev, ref_bp, copies, div, seed, svs=0):
         try:
             torch.cuda.set_device(dev)
             a, b = plan[r]
-            _, text, N, nd = gen_device.make_text(ref_bp, copies, div, seed, dev, first_copy=a, ncopies=b - a, svs=svs)
+            if many:
+                _, text, N, nd = gen_device.make_text_many(ref_bp, copies, div, seed, dev, first_copy=a, ncopies=b - a)
+            else:
+                _, text, N, nd = gen_device.make_text(ref_bp, copies, div, seed, dev, first_copy=a, ncopies=b - a, svs=svs)
             ctx = P.Context(dev.index)
             ctx.index_upload(x)
             sp, out = multi.run_sharded(ctx, dev, text.data_ptr(), N, nd, r, world, comm=multi.ThreadComm(shared, r))
@@ -197,4 +200,42 @@ def test_config5_scaled_chr1_reference_one_percent_with_svs():
         ctx.close()
     del text
     d = _run_two_ranks(x, dev, ref_bp, copies, div, seed, svs=svs)
+    assert torch.equal(a, d), "two-rank path differs from the single-GPU path"
+
+
+def test_config4_full_size_300k_documents():
+    """config 4 at full size: 30 kbp reference + 300,000 copies at 0.1 % (9.0 Gbp, 300,001 documents,
+    N > 2^33).  Lane kernel + sweep == warp kernel + sweep == two-rank path (owners count their deep
+    tile ranges with the sweep); histogram; the first 300,001 symbols are the terminators' rows."""
+    dev = torch.device("cuda:0")
+    if torch.cuda.get_device_properties(0).total_memory < 100 * 2 ** 30:
+        pytest.skip("needs a 180 GB device")
+    ref_bp, copies, div, seed = 30_000, 300_000, 0.001, 9
+    ref, text, N, nd = gen_device.make_text_many(ref_bp, copies, div, seed, dev)
+    assert nd == copies + 1 and N > 2 ** 33
+    x = P.augment(ref.cpu().numpy())
+    ctx = P.Context(0)
+    try:
+        ctx.index_upload(x)
+        a, st = _run_single(ctx, text, N)
+        assert st["n_docs"] == nd and st["fast_path"] == 1 and st["light_tiles"] == 0 and a.numel() == N
+        hist_t = torch.zeros(256, dtype=torch.int64, device=dev)
+        hist_a = torch.zeros(256, dtype=torch.int64, device=dev)
+        for o in range(0, N, 1 << 29):
+            hist_t += torch.bincount(text[o:min(N, o + (1 << 29))].to(torch.int32), minlength=256)
+            hist_a += torch.bincount(a[o:min(N, o + (1 << 29))].to(torch.int32), minlength=256)
+        assert torch.equal(hist_t, hist_a)
+        # rows of the nd terminators come first, in document order: the symbol before each terminator
+        ends = torch.nonzero(text[:N] == 2).view(-1)
+        assert ends.numel() == nd
+        last = torch.where(ends > 0, text[(ends - 1).clamp(min=0)], torch.full_like(text[ends], 2))
+        assert torch.equal(a[:nd], last)
+        c, st2 = _run_single(ctx, text, N, fast=0, tile_budget=0)
+        assert st2["fast_path"] == 0
+        assert torch.equal(a, c), "general kernel differs from the lane kernel"
+        del c
+    finally:
+        ctx.close()
+    del text
+    d = _run_two_ranks(x, dev, ref_bp, copies, div, seed, many=True)
     assert torch.equal(a, d), "two-rank path differs from the single-GPU path"

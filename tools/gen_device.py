@@ -16,10 +16,13 @@ def make_reference(n, gen, dev):
     return lut[torch.randint(0, 4, (n,), generator=gen, device=dev)]
 
 
-def mutate(ref, codes, div, gen, dev):
+def mutate(ref, codes, div, gen, dev, keep=None):
+    """keep: positions that are copied unchanged (separators of a batch of copies)"""
     n = ref.numel()
     lut = torch.tensor(ACGT, dtype=torch.uint8, device=dev)
     r = torch.rand(n, generator=gen, device=dev)
+    if keep is not None:
+        r[keep] = 1.0
     snp = r < div / 3
     dele = (r >= div / 3) & (r < 2 * div / 3)
     ins = (r >= 2 * div / 3) & (r < div)
@@ -107,5 +110,43 @@ def make_text(ref_bp, copies, div, seed, dev, pad=64, leading_empty=True, first_
         w += L + 1
         ndocs += 1
         del t
+    text[w:w + pad] = 2
+    return ref, text, w, ndocs
+
+
+def make_text_many(ref_bp, copies, div, seed, dev, pad=64, first_copy=0, ncopies=None, batch=2000):
+    """Same layout as make_text for collections of very many short copies (config 4: 300,000 copies of
+    a 30 kbp reference): copies are mutated `batch` at a time as one string whose separators are
+    kept.  first_copy must be a multiple of `batch` (every batch has its own generator stream)."""
+    assert first_copy % batch == 0
+    g0 = torch.Generator(device=dev)
+    g0.manual_seed(seed)
+    ref = make_reference(ref_bp, g0, dev)
+    if ncopies is None:
+        ncopies = copies - first_copy
+    unit = torch.cat([ref, torch.full((1,), 2, dtype=torch.uint8, device=dev)])
+    ucodes = _codes(unit)
+    cap = int(ncopies * (ref_bp * (1 + div) + 2) + 4096 * 64 + 64 + pad)
+    text = torch.empty(cap, dtype=torch.uint8, device=dev)
+    w = 0
+    ndocs = 0
+    if first_copy == 0:
+        text[0] = 2
+        w = 1
+        ndocs = 1
+    for b0 in range(first_copy, first_copy + ncopies, batch):
+        k = min(batch, first_copy + ncopies - b0)
+        g = torch.Generator(device=dev)
+        g.manual_seed(seed * 1000003 + b0 // batch + 1)
+        base = unit.repeat(k)
+        keep = torch.arange(ref_bp, base.numel(), ref_bp + 1, device=dev)
+        t = mutate(base, ucodes.repeat(k), div, g, dev, keep=keep)
+        L = t.numel()
+        if w + L + pad > cap:
+            raise RuntimeError("text buffer too small")
+        text[w:w + L] = t
+        w += L
+        ndocs += k
+        del t, base
     text[w:w + pad] = 2
     return ref, text, w, ndocs
