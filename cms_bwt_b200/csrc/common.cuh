@@ -188,7 +188,9 @@ void sort_stage(cmsbwt_ctx *c);
 void sort_prepare(cmsbwt_ctx *c, u64 doc_base);
 void sort_kappa(cmsbwt_ctx *c);
 void sweep_count(cmsbwt_ctx *c, u64 I, DBuf &it_tr, DBuf &it_key, DBuf &it_pay, const u32 *pos, u32 ntiles,
-                 int tbits, u32 *within);
+                 int tbits, int cshift, u32 *within);
+// bits that hold cls = smaller ? E : ~E order-preservingly (E = pos + len <= n): the low bits(n) + 1
+static inline int sweep_cls_bits(u32 n) { int b = 1; while (b < 32 && (1ull << b) <= (u64)n) b++; return b + 1 > 32 ? 32 : b + 1; }
 void tail_rank(cmsbwt_ctx *c, const u64 *label, DBuf &key32, DBuf &id, int key_bits, u32 *nexth, u32 Tn,
                u32 *trank);
 void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32, DBuf &id, int key_bits,

@@ -110,7 +110,8 @@ __global__ void k_kappa_count(const u32 *pos, const u32 *len, const u16 *cs, con
 }
 // item = (tile, kappa) with payload (head id or ~0, lo, hi); one warp expands 32 heads
 __global__ void k_items(const u32 *pos, const u32 *toNext, const u64 *kappa, const u32 *nitems,
-                        const u64 *ioff, u64 H, u32 *it_tr, u64 *it_key, u64 *it_pay) {
+                        const u64 *ioff, u64 H, int cshift, u32 *it_tr, u64 *it_key, u64 *it_pay) {
+  const u64 cmask = (1ull << cshift) - 1;
   const int lane = threadIdx.x & 31;
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   bool in = i < H;
@@ -122,7 +123,7 @@ __global__ void k_items(const u32 *pos, const u32 *toNext, const u64 *kappa, con
       u32 t = t0 + k, a = t * CMS_TILE_W;
       u32 lo = max(p, a) - a, hi = min(p + tn, a + CMS_TILE_W - 1) - a;
       it_tr[off + k] = (u32)kp;
-      it_key[off + k] = ((u64)t << 32) | (kp >> 32);
+      it_key[off + k] = ((u64)t << cshift) | ((kp >> 32) & cmask);
       it_pay[off + k] = ((u64)(k == 0 ? (u32)i : 0xFFFFFFFFu) << 32) | (lo << 8) | hi;
     }
   }
@@ -138,7 +139,7 @@ __global__ void k_items(const u32 *pos, const u32 *toNext, const u64 *kappa, con
       u32 t = bt0 + k, a = t * CMS_TILE_W;
       u32 lo = max(bp, a) - a, hi = min(bp + btn, a + CMS_TILE_W - 1) - a;
       it_tr[boff + k] = (u32)bkp;
-      it_key[boff + k] = ((u64)t << 32) | (bkp >> 32);
+      it_key[boff + k] = ((u64)t << cshift) | ((bkp >> 32) & cmask);
       it_pay[boff + k] = ((u64)(k == 0 ? (u32)bi : 0xFFFFFFFFu) << 32) | (lo << 8) | hi;
     }
   }
@@ -151,12 +152,12 @@ __global__ void k_gather_keys(const u32 *idx, const u64 *key, u64 n, u64 *out) {
   u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   if (j < n) out[j] = key[idx[j]];
 }
-__global__ void k_tile_bounds(const u64 *skey, u64 n, u32 *tbeg, u32 *tend) {
+__global__ void k_tile_bounds(const u64 *skey, u64 n, int cshift, u32 *tbeg, u32 *tend) {
   u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  u32 t = (u32)(skey[j] >> 32);
-  if (j == 0 || (u32)(skey[j - 1] >> 32) != t) tbeg[t] = (u32)j;
-  if (j + 1 == n || (u32)(skey[j + 1] >> 32) != t) tend[t] = (u32)j + 1;
+  u32 t = (u32)(skey[j] >> cshift);
+  if (j == 0 || (u32)(skey[j - 1] >> cshift) != t) tbeg[t] = (u32)j;
+  if (j + 1 == n || (u32)(skey[j + 1] >> cshift) != t) tend[t] = (u32)j + 1;
 }
 // one warp per tile: walk the tile's items in kappa order, 32 at a time; for every head item
 // count the earlier items whose interval holds the head's position.  A tile is walked by ONE warp, so
@@ -216,13 +217,13 @@ struct Tmp {                      // growable CUB scratch
   void need(size_t bytes, cudaStream_t st) { if (bytes > b.bytes) b.alloc(bytes, st); }
 };
 
-// Sort-based counting over I items (tailrank it_tr, key = tile << 32 | cls, payload = head id or ~0,
+// Sort-based counting over I items (tailrank it_tr, key = tile << cshift | cls, payload = head id or ~0,
 // lo, hi inside the 64-position tile): stable LSD by tailrank, then by (tile, cls); one warp per tile
 // walks its items in kappa order.  pos[head id] = position in the same tile numbering.  Items of
 // tile `ntiles` (one past the last) are padding and are never visited.  Used by the single-GPU
 // fallback below and by the owners of deep tile ranges on the multi-GPU path (tiles.cu).
 void sweep_count(cmsbwt_ctx *c, u64 I, DBuf &it_tr, DBuf &it_key, DBuf &it_pay, const u32 *pos, u32 ntiles,
-                 int tbits, u32 *within) {
+                 int tbits, int cshift, u32 *within) {
   cudaStream_t st = c->st;
   const int B = 256;
   if (I == 0) return;
@@ -240,7 +241,7 @@ void sweep_count(cmsbwt_ctx *c, u64 I, DBuf &it_tr, DBuf &it_key, DBuf &it_pay, 
   CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_tr.as<u32>(), it_tr2.as<u32>(),
                                      idx2.as<u32>(), idx.as<u32>(), (int)I, 0, tbits, st));
   k_gather_keys<<<gI, B, 0, st>>>(idx.as<u32>(), it_key.as<u64>(), I, it_key2.as<u64>());
-  int kb = 33; while ((1ull << (kb - 32)) < (u64)ntiles + 1) kb++;
+  int kb = cshift + 1; while ((1ull << (kb - cshift)) < (u64)ntiles + 1) kb++;
   tb = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
                                   idx2.as<u32>(), (int)I, 0, kb, st);
@@ -252,7 +253,7 @@ void sweep_count(cmsbwt_ctx *c, u64 I, DBuf &it_tr, DBuf &it_key, DBuf &it_pay, 
   tbeg.alloc(((size_t)ntiles + 1) * 4, st); tend.alloc(((size_t)ntiles + 1) * 4, st);
   CK(cudaMemsetAsync(tbeg.p, 0, ((size_t)ntiles + 1) * 4, st));
   CK(cudaMemsetAsync(tend.p, 0, ((size_t)ntiles + 1) * 4, st));
-  k_tile_bounds<<<gI, B, 0, st>>>(it_key.as<u64>(), I, tbeg.as<u32>(), tend.as<u32>());
+  k_tile_bounds<<<gI, B, 0, st>>>(it_key.as<u64>(), I, cshift, tbeg.as<u32>(), tend.as<u32>());
   u64 threads = (u64)ntiles * 32;
   k_tile_count<<<(u32)((threads + B - 1) / B), B, 0, st>>>(idx2.as<u32>(), it_pay.as<u64>(), pos,
                                                          tbeg.as<u32>(), tend.as<u32>(), ntiles, within);
@@ -372,13 +373,14 @@ void sort_stage(cmsbwt_ctx *c) {
   c->s_tincl.release(); c->s_trank.release();
   DBuf it_tr, it_key, it_pay;
   it_tr.alloc(I * 4, st); it_key.alloc(I * 8, st); it_pay.alloc(I * 8, st);
+  const int cshift = sweep_cls_bits(n);
   k_items<<<gH, B, 0, st>>>(pos, c->h_toNext.as<u32>(), kappa.as<u64>(), nitems.as<u32>(),
-                            ioff.as<u64>(), H, it_tr.as<u32>(), it_key.as<u64>(), it_pay.as<u64>());
+                            ioff.as<u64>(), H, cshift, it_tr.as<u32>(), it_key.as<u64>(), it_pay.as<u64>());
   LAUNCH(c);
   {
     int tbits = 1; while ((1ull << tbits) < (u64)Tn) tbits++;
     c->h_within.alloc(H * 4, st);
-    sweep_count(c, I, it_tr, it_key, it_pay, pos, n / CMS_TILE_W + 1, tbits, c->h_within.as<u32>());
+    sweep_count(c, I, it_tr, it_key, it_pay, pos, n / CMS_TILE_W + 1, tbits, cshift, c->h_within.as<u32>());
   }
   c->s_kappa.release(); c->s_nitems.release(); c->s_sexcl.release();
 }

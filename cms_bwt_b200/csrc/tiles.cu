@@ -559,15 +559,16 @@ __global__ void __launch_bounds__(256) k_sh_plc_scatter(const u64 *plc, u64 P, u
 // k_tile_place.  Items live in 64-position sub-tiles (CMS_TILE_W) numbered inside the device's range.
 #define SUBT (LT_W / CMS_TILE_W)
 __global__ void __launch_bounds__(256) k_sh_deep_items(const TileEnt *he, const TileEnt *re, const u32 *hoff,
-                                                       const u32 *roff, u32 HE, u32 pad_tile, u32 *it_tr,
-                                                       u64 *it_key, u64 *it_pay, u32 *epos) {
+                                                       const u32 *roff, u32 HE, u32 pad_tile, int cshift,
+                                                       u32 *it_tr, u64 *it_key, u64 *it_pay, u32 *epos) {
+  const u64 cmask = (1ull << cshift) - 1;
   const u32 t = blockIdx.x;
   const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
   for (u32 j = h0 + threadIdx.x; j < h1; j += blockDim.x) {
     const TileEnt e = he[j];
     const u32 q = e.b & (LT_W - 1), q6 = q & (CMS_TILE_W - 1);
     it_tr[j] = (u32)e.kappa;
-    it_key[j] = ((u64)(t * SUBT + q / CMS_TILE_W) << 32) | (e.kappa >> 32);
+    it_key[j] = ((u64)(t * SUBT + q / CMS_TILE_W) << cshift) | ((e.kappa >> 32) & cmask);
     it_pay[j] = ((u64)j << 32) | (q6 << 8) | q6;
     epos[j] = t * LT_W + q;
   }
@@ -579,7 +580,7 @@ __global__ void __launch_bounds__(256) k_sh_deep_items(const TileEnt *he, const 
       const u64 o = (u64)HE + (u64)j * SUBT + s;
       const bool in = lo <= b && hi >= a;
       it_tr[o] = (u32)e.kappa;
-      it_key[o] = ((u64)(in ? t * SUBT + s : pad_tile) << 32) | (e.kappa >> 32);
+      it_key[o] = ((u64)(in ? t * SUBT + s : pad_tile) << cshift) | ((e.kappa >> 32) & cmask);
       it_pay[o] = (0xFFFFFFFFull << 32) | ((in ? max(lo, a) - a : 1u) << 8) | (in ? min(hi, b) - a : 0u);
     }
   }
@@ -598,14 +599,15 @@ static void shard_place_deep(cmsbwt_ctx *c, const u64 *base, u64 *plc) {
   cudaStream_t st = c->st;
   const u32 tp = c->sh_tp, HE = c->sh_he;
   const u64 I = (u64)HE + (u64)c->sh_re * SUBT;
+  const int cshift = sweep_cls_bits(c->ix.n);
   DBuf it_tr, it_key, it_pay, epos, within;
   it_tr.alloc((I + 1) * 4, st); it_key.alloc((I + 1) * 8, st); it_pay.alloc((I + 1) * 8, st);
   epos.alloc(((size_t)HE + 1) * 4, st); within.alloc(((size_t)HE + 1) * 4, st);
   k_sh_deep_items<<<tp, 256, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                      c->t_roff.as<u32>(), HE, tp * SUBT, it_tr.as<u32>(), it_key.as<u64>(),
+                                      c->t_roff.as<u32>(), HE, tp * SUBT, cshift, it_tr.as<u32>(), it_key.as<u64>(),
                                       it_pay.as<u64>(), epos.as<u32>());
   LAUNCH(c);
-  sweep_count(c, I, it_tr, it_key, it_pay, epos.as<u32>(), tp * SUBT, 32, within.as<u32>());
+  sweep_count(c, I, it_tr, it_key, it_pay, epos.as<u32>(), tp * SUBT, 32, cshift, within.as<u32>());
   k_sh_deep_plc<<<tp, 256, 0, st>>>(c->t_he.as<TileEnt>(), c->t_hoff.as<u32>(), within.as<u32>(), c->ix.isa, base,
                                     c->ix.n, c->sh_rank * tp, plc);
   LAUNCH(c);
