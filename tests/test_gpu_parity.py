@@ -148,6 +148,38 @@ def test_duplicate_documents_and_identity(ctx):
     assert st["rank_rounds"] >= 0
 
 
+def _repetitive(kind, rng):
+    acgt = np.frombuffer(b"ACGT", np.uint8)
+    if kind == "units":          # 1000 noisy copies of one 500-bp unit: k-mers with hundreds of suffixes
+        unit = acgt[rng.integers(0, 4, 500)]
+        ref = np.concatenate([gen_synth.mutate(unit, 0.01, rng) for _ in range(1000)])
+        nc = 8
+    elif kind == "period7":      # tandem repeat of period 7 with 0.2 % noise
+        unit = acgt[rng.integers(0, 4, 7)]
+        ref = np.concatenate([gen_synth.mutate(unit, 0.002, rng) for _ in range(60000)])
+        nc = 6
+    else:                        # homopolymer: one k-mer, one slot, every suffix in it
+        ref = np.full(200000, 65, np.uint8)
+        nc = 5
+    copies = [gen_synth.mutate(ref, 0.005, rng) for _ in range(nc)]
+    return ref, copies
+
+
+@pytest.mark.parametrize("kind", ["units", "period7", "homopolymer"])
+def test_repetitive_references_medium(ctx, kind):
+    """0.2-0.5 Mbp references that are all repeats (overflowing k-mer slots, exact searches, long tie
+    chains in the tail ranking, skewed tiles), 1-4 Mbp of copies, against the oracle: MS per position,
+    BWT and RLBWT in all three kernel modes"""
+    ref, copies = _repetitive(kind, np.random.default_rng(5))
+    x = P.augment(ref)
+    text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    want = O.Oracle(x).bwt(text)
+    for mode in MODES:
+        st = _check_case(ctx, x, text, want, "repetitive " + kind, mode=mode)
+    # a homopolymer reference gets C, G and T in its augmentation, so it is not "pure": 8-bit kernel
+    assert st["fast_path"] == (0 if kind == "homopolymer" else 1)
+
+
 def test_host_sa_path_matches_gpu_sa(ctx):
     """index_upload with a host SA (the reference's libsais route) gives the same output."""
     ref, copies = gen_synth.make_collection(50000, 4, 0.002, 3)

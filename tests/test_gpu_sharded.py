@@ -133,6 +133,16 @@ def test_sharded_deep_tile_ranges(world):
     assert done >= 10
 
 
+@pytest.mark.parametrize("kind", ["units", "period7", "homopolymer"])
+def test_sharded_repetitive_references(kind):
+    """all-repeat references (long tie chains refined across ranks, skewed key ranges and tiles) on 3 ranks"""
+    from test_gpu_parity import _repetitive
+    ref, copies = _repetitive(kind, np.random.default_rng(6))
+    x = P.augment(ref)
+    text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    _check(x, text, 3, "repetitive " + kind)
+
+
 def test_sharded_golden_fixtures():
     n = 0
     for f in sorted(glob.glob(os.path.join(GOLDEN, "*.npz"))):
