@@ -98,6 +98,75 @@ __global__ void __launch_bounds__(256) k_tile_scatter(const u32 *pos, const u32 
   }
 }
 
+// ---- the same two kernels for FEW tiles (short reference): every global counter would take the
+// atomics of H / ntiles heads one after the other (measured: 11 + 12 ms for 58 M heads on 118 tiles),
+// so a block first counts its slice of heads in shared memory and touches every global counter once.
+#define TA_MAX_TILES 4096u
+#define TA_SLICE 2048u
+template <bool COUNT>
+__device__ __forceinline__ void ta_ranges(u32 p, u32 tn, u32 *s_r, const u32 *s_rb, const u32 *roff, TileEnt *re,
+                                          u64 kap) {
+  const u32 ta = (p + 1) >> LT_SHIFT, tb = (p + tn) >> LT_SHIFT;
+  for (u32 t = ta; t <= tb; t++) {
+    const u32 k = atomicAdd(&s_r[t], 1u);
+    if (!COUNT) {
+      const u32 a = t << LT_SHIFT;
+      TileEnt e; e.a = (max(p + 1, a) - a) | ((min(p + tn, a + LT_W - 1) - a) << 16); e.b = 0; e.kappa = kap;
+      re[roff[t] + s_rb[t] + k] = e;
+    }
+  }
+}
+__global__ void __launch_bounds__(256) k_tile_hist_few(const u32 *pos, const u32 *len, const u32 *toNext, u64 H,
+                                                       u32 ntiles, u32 *hcnt, u32 *rcnt) {
+  extern __shared__ u32 s_ta[];
+  u32 *s_h = s_ta, *s_r = s_ta + ntiles;
+  for (u32 k = threadIdx.x; k < 2 * ntiles; k += blockDim.x) s_ta[k] = 0;
+  __syncthreads();
+  const u64 i0 = (u64)blockIdx.x * TA_SLICE, i1 = min(H, i0 + TA_SLICE);
+  for (u64 i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+    if (len[i] == 0) continue;
+    const u32 p = pos[i], tn = toNext[i];
+    atomicAdd(&s_h[p >> LT_SHIFT], 1u);
+    if (tn) ta_ranges<true>(p, tn, s_r, nullptr, nullptr, nullptr, 0);
+  }
+  __syncthreads();
+  for (u32 k = threadIdx.x; k < ntiles; k += blockDim.x) {
+    if (s_h[k]) atomicAdd(hcnt + k, s_h[k]);
+    if (s_r[k]) atomicAdd(rcnt + k, s_r[k]);
+  }
+}
+__global__ void __launch_bounds__(256) k_tile_scatter_few(const u32 *pos, const u32 *len, const u16 *cs,
+                                                          const u32 *toNext, const u64 *kappa, u64 H, u32 ntiles,
+                                                          const u32 *hoff, const u32 *roff, u32 *hcur, u32 *rcur,
+                                                          TileEnt *he, TileEnt *re) {
+  extern __shared__ u32 s_ta[];
+  u32 *s_h = s_ta, *s_r = s_ta + ntiles, *s_hb = s_ta + 2 * ntiles, *s_rb = s_ta + 3 * ntiles;
+  for (u32 k = threadIdx.x; k < 2 * ntiles; k += blockDim.x) s_ta[k] = 0;
+  __syncthreads();
+  const u64 i0 = (u64)blockIdx.x * TA_SLICE, i1 = min(H, i0 + TA_SLICE);
+  for (u64 i = i0 + threadIdx.x; i < i1; i += blockDim.x) {          // pass 1: the slice's counts
+    if (len[i] == 0) continue;
+    const u32 p = pos[i], tn = toNext[i];
+    atomicAdd(&s_h[p >> LT_SHIFT], 1u);
+    if (tn) ta_ranges<true>(p, tn, s_r, nullptr, nullptr, nullptr, 0);
+  }
+  __syncthreads();
+  for (u32 k = threadIdx.x; k < ntiles; k += blockDim.x) {           // one reservation per tile
+    s_hb[k] = s_h[k] ? atomicAdd(hcur + k, s_h[k]) : 0u;
+    s_rb[k] = s_r[k] ? atomicAdd(rcur + k, s_r[k]) : 0u;
+    s_h[k] = 0; s_r[k] = 0;
+  }
+  __syncthreads();
+  for (u64 i = i0 + threadIdx.x; i < i1; i += blockDim.x) {          // pass 2: the entries
+    if (len[i] == 0) continue;
+    const u32 p = pos[i], tn = toNext[i], t = p >> LT_SHIFT;
+    const u64 kap = kappa[i];
+    TileEnt e; e.a = (u32)i; e.b = (p & (LT_W - 1)) | ((u32)(cs[i] & 0xFF) << 8); e.kappa = kap;
+    he[hoff[t] + s_hb[t] + atomicAdd(&s_h[t], 1u)] = e;
+    if (tn) ta_ranges<false>(p, tn, s_r, s_rb, roff, re, kap);
+  }
+}
+
 // ---- pass A: bucket sizes + cost of pass B -------------------------------------------------------
 __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, const TileEnt *re, const u32 *hoff,
                                                          const u32 *roff, u32 n, u32 ndocs, u32 t0, u32 *cov,
@@ -298,8 +367,14 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   c->t_hoff.alloc(((size_t)ntiles + 1) * 4, st); c->t_roff.alloc(((size_t)ntiles + 1) * 4, st);
   CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
   CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
-  k_tile_hist<<<gH, B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_toNext.as<u32>(), H,
-                                hcnt.as<u32>(), rcnt.as<u32>());
+  const bool few = ntiles <= TA_MAX_TILES;
+  const u32 gS = (u32)((H + TA_SLICE - 1) / TA_SLICE);
+  if (few)
+    k_tile_hist_few<<<gS, B, (size_t)ntiles * 8, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_toNext.as<u32>(), H,
+                                                       ntiles, hcnt.as<u32>(), rcnt.as<u32>());
+  else
+    k_tile_hist<<<gH, B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_toNext.as<u32>(), H,
+                                  hcnt.as<u32>(), rcnt.as<u32>());
   size_t tb = 0;
   cub::DeviceScan::ExclusiveSum(nullptr, tb, hcnt.as<u32>(), c->t_hoff.as<u32>(), (int)(ntiles + 1), st);
   tmp.alloc(tb, st);
@@ -333,6 +408,14 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   c->t_re.alloc(((size_t)R + 1) * sizeof(TileEnt), st);
   CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));      // reused as cursors
   CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
+  if (few) {
+    if ((size_t)ntiles * 16 > 40 * 1024)
+      CK(cudaFuncSetAttribute(k_tile_scatter_few, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ntiles * 16)));
+    k_tile_scatter_few<<<gS, B, (size_t)ntiles * 16, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
+                                                           c->h_toNext.as<u32>(), kappa, H, ntiles, c->t_hoff.as<u32>(),
+                                                           c->t_roff.as<u32>(), hcnt.as<u32>(), rcnt.as<u32>(),
+                                                           c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>());
+  } else
   k_tile_scatter<<<(u32)((H + B * TS_ILP - 1) / (B * TS_ILP)), B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                    c->h_toNext.as<u32>(), kappa, H, c->t_hoff.as<u32>(), c->t_roff.as<u32>(),
                                    hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>());
@@ -454,6 +537,18 @@ __global__ void k_sh_tile_merge(const TileEnt *src, const u32 *offs, const u64 *
   }
 }
 
+// the same for deep tiles: block (t, s, z) copies every gridDim.z-th 256-entry piece of source s's segment
+__global__ void __launch_bounds__(256) k_sh_tile_merge_deep(const TileEnt *src, const u32 *offs, const u64 *slab,
+                                                            u32 W, u32 tp, const u32 *moff, TileEnt *dst) {
+  const u32 t = blockIdx.x, s = blockIdx.y;
+  u32 d = moff[t];
+  for (u32 s2 = 0; s2 < s; s2++) { const u32 *o2 = offs + (size_t)s2 * (tp + 1); d += o2[t + 1] - o2[t]; }
+  const u32 *o = offs + (size_t)s * (tp + 1);
+  const u32 a = o[t] - o[0], cnt = o[t + 1] - o[t];
+  const TileEnt *p = src + slab[s] + a;
+  for (u32 k = blockIdx.z * 256 + threadIdx.x; k < cnt; k += gridDim.z * 256) dst[d + k] = p[k];
+}
+
 // he/re: the received slabs (slab s starts at he_slab[s] / re_slab[s] entries); hoffs/roffs: the
 // senders' offset slices for this device's tile range.  Leaves the merged entries in t_he/t_re
 // (tile-local offsets t_hoff/t_roff) and the bucket sizes of the range in sh_cov (tp * 256 entries).
@@ -486,10 +581,19 @@ u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const 
   DBuf mhe, mre;
   mhe.alloc(((size_t)HE + 1) * sizeof(TileEnt), st); mre.alloc(((size_t)R + 1) * sizeof(TileEnt), st);
   const u32 gW = (u32)(((u64)tp * 32 + B - 1) / B);
-  k_sh_tile_merge<<<gW, B, 0, st>>>((const TileEnt *)he, hoffs, slab.as<u64>(), world, tp, mh.as<u32>(),
-                                    mhe.as<TileEnt>());
-  k_sh_tile_merge<<<gW, B, 0, st>>>((const TileEnt *)re, roffs, slab.as<u64>() + world, world, tp, mr.as<u32>(),
-                                    mre.as<TileEnt>());
+  if (((u64)HE + R) / ((u64)tp * world) >= 2048 && tp <= 65535) {     // deep tiles: blocks per (tile, source)
+    const u64 per = ((u64)HE + R) / ((u64)tp * world);
+    const dim3 g(tp, world, (u32)(per / 4096 < 1 ? 1 : per / 4096 > 32 ? 32 : per / 4096));
+    k_sh_tile_merge_deep<<<g, 256, 0, st>>>((const TileEnt *)he, hoffs, slab.as<u64>(), world, tp, mh.as<u32>(),
+                                            mhe.as<TileEnt>());
+    k_sh_tile_merge_deep<<<g, 256, 0, st>>>((const TileEnt *)re, roffs, slab.as<u64>() + world, world, tp,
+                                            mr.as<u32>(), mre.as<TileEnt>());
+  } else {
+    k_sh_tile_merge<<<gW, B, 0, st>>>((const TileEnt *)he, hoffs, slab.as<u64>(), world, tp, mh.as<u32>(),
+                                      mhe.as<TileEnt>());
+    k_sh_tile_merge<<<gW, B, 0, st>>>((const TileEnt *)re, roffs, slab.as<u64>() + world, world, tp, mr.as<u32>(),
+                                      mre.as<TileEnt>());
+  }
   c->t_he.swap(mhe);
   c->t_re.swap(mre);
   c->t_hoff.swap(mh);
@@ -564,7 +668,8 @@ __global__ void __launch_bounds__(256) k_sh_deep_items(const TileEnt *he, const 
   const u64 cmask = (1ull << cshift) - 1;
   const u32 t = blockIdx.x;
   const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
-  for (u32 j = h0 + threadIdx.x; j < h1; j += blockDim.x) {
+  const u32 z0 = blockIdx.y * blockDim.x + threadIdx.x, zs = gridDim.y * blockDim.x;
+  for (u32 j = h0 + z0; j < h1; j += zs) {
     const TileEnt e = he[j];
     const u32 q = e.b & (LT_W - 1), q6 = q & (CMS_TILE_W - 1);
     it_tr[j] = (u32)e.kappa;
@@ -572,7 +677,7 @@ __global__ void __launch_bounds__(256) k_sh_deep_items(const TileEnt *he, const 
     it_pay[j] = ((u64)j << 32) | (q6 << 8) | q6;
     epos[j] = t * LT_W + q;
   }
-  for (u32 j = r0 + threadIdx.x; j < r1; j += blockDim.x) {
+  for (u32 j = r0 + z0; j < r1; j += zs) {
     const TileEnt e = re[j];
     const u32 lo = e.a & 0xFFFF, hi = e.a >> 16;
     for (u32 s = 0; s < SUBT; s++) {
@@ -588,7 +693,7 @@ __global__ void __launch_bounds__(256) k_sh_deep_items(const TileEnt *he, const 
 __global__ void __launch_bounds__(256) k_sh_deep_plc(const TileEnt *he, const u32 *hoff, const u32 *within,
                                                      const u32 *isa, const u64 *base, u32 n, u32 t0, u64 *plc) {
   const u32 t = blockIdx.x;
-  for (u32 j = hoff[t] + threadIdx.x; j < hoff[t + 1]; j += blockDim.x) {
+  for (u32 j = hoff[t] + blockIdx.y * blockDim.x + threadIdx.x; j < hoff[t + 1]; j += gridDim.y * blockDim.x) {
     const TileEnt e = he[j];
     const u32 p = ((t + t0) << LT_SHIFT) + (e.b & (LT_W - 1));
     const u64 off = (p < n ? base[isa[p]] : 0) + within[j];
@@ -603,12 +708,15 @@ static void shard_place_deep(cmsbwt_ctx *c, const u64 *base, u64 *plc) {
   DBuf it_tr, it_key, it_pay, epos, within;
   it_tr.alloc((I + 1) * 4, st); it_key.alloc((I + 1) * 8, st); it_pay.alloc((I + 1) * 8, st);
   epos.alloc(((size_t)HE + 1) * 4, st); within.alloc(((size_t)HE + 1) * 4, st);
-  k_sh_deep_items<<<tp, 256, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+  // blocks per tile: the tiles of a deep range are few and hold 10^4..10^6 entries each
+  u32 zy = (u32)((((u64)HE + c->sh_re) / tp) / 8192);
+  zy = zy < 1 ? 1 : zy > 64 ? 64 : zy;
+  k_sh_deep_items<<<dim3(tp, zy), 256, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                       c->t_roff.as<u32>(), HE, tp * SUBT, cshift, it_tr.as<u32>(), it_key.as<u64>(),
                                       it_pay.as<u64>(), epos.as<u32>());
   LAUNCH(c);
   sweep_count(c, I, it_tr, it_key, it_pay, epos.as<u32>(), tp * SUBT, 32, cshift, within.as<u32>());
-  k_sh_deep_plc<<<tp, 256, 0, st>>>(c->t_he.as<TileEnt>(), c->t_hoff.as<u32>(), within.as<u32>(), c->ix.isa, base,
+  k_sh_deep_plc<<<dim3(tp, zy), 256, 0, st>>>(c->t_he.as<TileEnt>(), c->t_hoff.as<u32>(), within.as<u32>(), c->ix.isa, base,
                                     c->ix.n, c->sh_rank * tp, plc);
   LAUNCH(c);
   CK(cudaGetLastError());
