@@ -28,6 +28,9 @@ EXPORTS = [
     "cmsbwt_shard_rank_apply", "cmsbwt_shard_tie_keys", "cmsbwt_shard_tie_refine",
     "cmsbwt_shard_tiles_local", "cmsbwt_shard_tiles_merge", "cmsbwt_shard_emit", "cmsbwt_shard_apply",
     "cmsbwt_shard_rle",
+    "cmsbwt_parse_collection_mt", "cmsbwt_parse_piece", "cmsbwt_line_start",
+    "cmsbwt_host_alloc", "cmsbwt_host_free", "cmsbwt_text_begin", "cmsbwt_text_append",
+    "cmsbwt_ms_run_staged", "cmsbwt_result_read", "cmsbwt_copy_fence", "cmsbwt_copy_wait",
 ]
 
 
@@ -90,6 +93,21 @@ def lib():
         L.cmsbwt_result_download.argtypes = [vp, vp, u64]
         L.cmsbwt_run.argtypes = [vp, vp, u64, C.c_int, vp, u64, C.POINTER(u64)]
         L.cmsbwt_set_param.argtypes = [vp, C.c_char_p, i64]
+        L.cmsbwt_parse_collection_mt.argtypes = [vp, i64, u64, vp, C.POINTER(i64), C.c_int]
+        L.cmsbwt_parse_collection_mt.restype = i64
+        L.cmsbwt_parse_piece.argtypes = [vp, i64, i64, vp, C.POINTER(i64), C.POINTER(C.c_int32)]
+        L.cmsbwt_parse_piece.restype = i64
+        L.cmsbwt_line_start.argtypes = [vp, i64, i64]
+        L.cmsbwt_line_start.restype = i64
+        L.cmsbwt_host_alloc.argtypes = [C.POINTER(vp), u64]
+        L.cmsbwt_host_free.argtypes = [vp]
+        L.cmsbwt_host_free.restype = None
+        L.cmsbwt_text_begin.argtypes = [vp, u64]
+        L.cmsbwt_text_append.argtypes = [vp, vp, u64]
+        L.cmsbwt_ms_run_staged.argtypes = [vp]
+        L.cmsbwt_result_read.argtypes = [vp, vp, u64, u64]
+        L.cmsbwt_copy_fence.argtypes = [vp, C.c_int]
+        L.cmsbwt_copy_wait.argtypes = [vp, C.c_int]
         _lib = L
     return _lib
 
@@ -125,6 +143,39 @@ def parse_collection(file_bytes, prefix=UINT64_MAX):
     if N < 0:
         raise CmsBwtError(N, "parse_collection")
     return out[:N].copy(), nd.value
+
+
+def parse_collection_mt(file_bytes, prefix=UINT64_MAX, threads=0):
+    """cmsbwt_parse_collection on several host threads (same bytes, same document count)."""
+    src = np.frombuffer(file_bytes, dtype=np.uint8)
+    out = np.empty(len(src) + 2, np.uint8)
+    nd = C.c_int64(0)
+    N = lib().cmsbwt_parse_collection_mt(_p(src), len(src), C.c_uint64(prefix), _p(out), C.byref(nd),
+                                         threads)
+    if N < 0:
+        raise CmsBwtError(N, "parse_collection_mt")
+    return out[:N].copy(), nd.value
+
+
+def parse_pieces(file_bytes, piece):
+    """The streamed-ingest form of the parse: pieces of about `piece` bytes cut at line starts,
+    each parsed by cmsbwt_parse_piece; yields the text bytes of every piece, the closing separator
+    last.  Concatenated they equal parse_collection(file_bytes)[0]."""
+    src = np.frombuffer(file_bytes, dtype=np.uint8)
+    L = lib()
+    size, a = len(src), 0
+    op = C.c_int32(0)
+    nd = C.c_int64(0)
+    while a < size:
+        b = L.cmsbwt_line_start(_p(src), size, min(size, a + max(1, piece)))
+        out = np.empty(max(1, b - a), np.uint8)
+        w = L.cmsbwt_parse_piece(_p(src), a, b, _p(out), C.byref(nd), C.byref(op))
+        if w < 0:
+            raise CmsBwtError(w, "parse_piece")
+        yield out[:w]
+        a = b
+    if op.value == 1:
+        yield np.array([2], np.uint8)
 
 
 class Context:
@@ -238,6 +289,57 @@ class Context:
         self._ck(lib().cmsbwt_run(self.h, _p(text), len(text), mode, _p(out), out.nbytes, C.byref(ob)))
         self.out_bytes = ob.value
         return out[:ob.value]
+
+
+    def run_streamed(self, pieces, capacity, mode=MODE_PLAIN, chunk=1 << 20):
+        """The path with streamed ingest / egress (what the cms_bwt command line does): `pieces`
+        (uint8 arrays) are appended to the device text through two pinned staging slots, the result
+        is read back `chunk` bytes at a time through two more."""
+        L = lib()
+        slots = []
+        try:
+            for _ in range(4):
+                hp = C.c_void_p()
+                self._ck(L.cmsbwt_host_alloc(C.byref(hp), chunk))
+                slots.append(hp)
+            self._ck(L.cmsbwt_text_begin(self.h, capacity))
+            k = 0
+            for pc in pieces:
+                pc = np.ascontiguousarray(pc, dtype=np.uint8)
+                for a in range(0, len(pc), chunk):
+                    s = k & 1
+                    k += 1
+                    self._ck(L.cmsbwt_copy_wait(self.h, s))
+                    m = min(chunk, len(pc) - a)
+                    C.memmove(slots[s], pc[a:a + m].ctypes.data, m)
+                    self._ck(L.cmsbwt_text_append(self.h, slots[s], m))
+                    self._ck(L.cmsbwt_copy_fence(self.h, s))
+            self._ck(L.cmsbwt_ms_run_staged(self.h))
+            self._ck(L.cmsbwt_heads_sort(self.h))
+            ob = C.c_uint64(0)
+            self._ck(L.cmsbwt_emit(self.h, mode, C.byref(ob)))
+            self.out_bytes = ob.value
+            out = np.empty(ob.value, np.uint8)
+            pend = [None, None]
+            for j, a in enumerate(range(0, ob.value, chunk)):
+                s = 2 + (j & 1)
+                if pend[j & 1] is not None:
+                    self._ck(L.cmsbwt_copy_wait(self.h, s))
+                    pa, pm = pend[j & 1]
+                    C.memmove(out[pa:pa + pm].ctypes.data, slots[s], pm)
+                m = min(chunk, ob.value - a)
+                self._ck(L.cmsbwt_result_read(self.h, slots[s], a, m))
+                self._ck(L.cmsbwt_copy_fence(self.h, s))
+                pend[j & 1] = (a, m)
+            for i in (0, 1):
+                if pend[i] is not None:
+                    self._ck(L.cmsbwt_copy_wait(self.h, 2 + i))
+                    pa, pm = pend[i]
+                    C.memmove(out[pa:pa + pm].ctypes.data, slots[2 + i], pm)
+            return out
+        finally:
+            for hp in slots:
+                L.cmsbwt_host_free(hp)
 
 
 class Args:

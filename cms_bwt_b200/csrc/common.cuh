@@ -134,6 +134,13 @@ struct cmsbwt_ctx {
   const u8 *text = nullptr;
   u64 N = 0;
   DBuf d_text;
+  // streamed ingest / egress (cmsbwt_text_*, cmsbwt_result_read): a second stream for the copies,
+  // one event per host staging slot
+  cudaStream_t st_copy = 0;
+  cudaEvent_t ev_slot[CMSBWT_COPY_SLOTS] = {};
+  cudaEvent_t ev_in0 = 0, ev_in1 = 0;
+  u64 staged = 0, staged_cap = 0;
+  bool staging = false;
   // stage 1 products (text-order heads)
   u64 H = 0;
   DBuf h_gstart, h_pos, h_len, h_cs;     // u64, u32, u32, u16 (ch | sm << 8)

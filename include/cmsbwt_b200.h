@@ -86,6 +86,24 @@ int64_t cmsbwt_read_reference(const uint8_t *file, int64_t size, uint8_t *out);
 int64_t cmsbwt_parse_collection(const uint8_t *file, int64_t size, uint64_t prefix,
                                 uint8_t *out_text, int64_t *ndocs);
 
+/* Parallel form of cmsbwt_parse_collection (same bytes, same *ndocs) on `threads` host threads
+ * (<= 0: one per hardware thread, at most 32).  A -p prefix shorter than the file is parsed by the
+ * sequential function (the cut depends on everything before it). */
+int64_t cmsbwt_parse_collection_mt(const uint8_t *file, int64_t size, uint64_t prefix,
+                                   uint8_t *out_text, int64_t *ndocs, int threads);
+/* One piece of the same parse, for streamed ingest: the complete lines of file[begin, end) --
+ * `begin` must be the start of a line; a last line without '\n' before `end` is not consumed
+ * (the reference's getline().good() loop drops it at the end of the file, :1138-1140).  Writes the
+ * text bytes to `out` (may be NULL to count only; needs at most end - begin bytes), adds the
+ * documents closed inside the piece to *ndocs and sets *open to 1 / 0 when the piece's last line
+ * was a sequence / a header or blank line (left untouched when the piece holds no complete line).
+ * The caller appends one 0x02 (and one document) after the last piece when *open is 1 (:1269-1275).
+ * No -p handling.  Returns the bytes written. */
+int64_t cmsbwt_parse_piece(const uint8_t *file, int64_t begin, int64_t end, uint8_t *out,
+                           int64_t *ndocs, int32_t *open);
+/* first line start at or after `pos` (= pos when file[pos-1] is '\n' or pos is 0; size if none) */
+int64_t cmsbwt_line_start(const uint8_t *file, int64_t size, int64_t pos);
+
 /* replaces: libsais(x, sa, n, 0, NULL) at :247 when the caller has no host SA builder.
  * GPU prefix doubling; sa_out (host, n entries) may be NULL to keep it on the device only. */
 int cmsbwt_build_sa(cmsbwt_ctx *ctx, const uint8_t *x, uint32_t n, int32_t *sa_out);
@@ -130,6 +148,26 @@ int cmsbwt_emit(cmsbwt_ctx *ctx, int mode, uint64_t *out_bytes);
 const void *cmsbwt_result_device(const cmsbwt_ctx *ctx);
 /* copy the last emit's result to host memory (cap >= out_bytes). */
 int cmsbwt_result_download(cmsbwt_ctx *ctx, void *host_out, uint64_t cap);
+
+/* Streamed ingest / egress (replaces the getline loop :1138-1140 / :1257-1275 in
+ * front of stage 1 and the 1 MiB write buffer of the writers :1640-1688 behind stage 3).  Copies
+ * run on a second stream of the context, so the host can parse the next piece (or write the
+ * previous range to the file) while a copy is in flight.  Host buffers handed to text_append /
+ * result_read should come from cmsbwt_host_alloc (pinned) and must not be reused before
+ * cmsbwt_copy_wait(slot) returned for a cmsbwt_copy_fence(slot) issued after the copy.
+ *   text_begin(capacity)  device text buffer for up to `capacity` bytes
+ *   text_append           async H2D of the next bytes of the text (in order)
+ *   ms_run_staged         stage 1 on what was appended (= cmsbwt_ms_run on the same bytes)
+ *   result_read           async D2H of result[offset, offset + bytes) after cmsbwt_emit */
+enum { CMSBWT_COPY_SLOTS = 8 };
+int cmsbwt_host_alloc(void **out, uint64_t bytes);
+void cmsbwt_host_free(void *p);
+int cmsbwt_text_begin(cmsbwt_ctx *ctx, uint64_t capacity);
+int cmsbwt_text_append(cmsbwt_ctx *ctx, const uint8_t *chunk, uint64_t bytes);
+int cmsbwt_ms_run_staged(cmsbwt_ctx *ctx);
+int cmsbwt_result_read(cmsbwt_ctx *ctx, void *host_out, uint64_t offset, uint64_t bytes);
+int cmsbwt_copy_fence(cmsbwt_ctx *ctx, int slot);
+int cmsbwt_copy_wait(cmsbwt_ctx *ctx, int slot);
 
 /* Whole path on host buffers: ms_run + heads_sort + emit + result_download.  This is the call
  * that stands where computeBWT's process_collection_* call stands (:1792-1796). */

@@ -59,3 +59,40 @@ def test_host_parser_prefix_matches_oracle():
 def test_augment_rejects_reserved_bytes():
     with pytest.raises(P.CmsBwtError):
         P.augment(np.frombuffer(b"AC\x02GT", dtype=np.uint8))
+
+
+def _odd_files():
+    """Collections around the line rules: unterminated last line, blank-line splits, no header,
+    CR LF, header last, only headers, empty lines first."""
+    return [b"", b"\n", b">a\n", b"ACGT", b"ACGT\n", b">a\nAC\nGT", b">a\nAC\n\nGT\n", b"AC\nGT\n>b\n",
+            b"\n\n>a\n>b\nA\n", b">a\r\nAC\r\nGT\r\n", b">a\nACGT\n>b\nAC\n>c", b"A\n" * 50,
+            b">x\n" + b"ACGTACGTAC\n" * 40 + b">y\n" + b"TTTT\n" * 33 + b"\n" + b"GG"]
+
+
+def test_parallel_parser_matches_sequential():
+    # streamed ingest (SURVEY 8f-1): same bytes and document count as the sequential parse
+    cases = [fuzz_cases.make_case(s)["coll_file"] for s in range(120)] + _odd_files()
+    rng = np.random.default_rng(3)
+    big = b"".join(b">s%d\n" % k + b"\n".join(bytes(rng.choice(list(b"ACGT"), int(rng.integers(0, 70))).astype(np.uint8))
+                                             for _ in range(int(rng.integers(0, 400)))) + b"\n"
+                   for k in range(60))
+    cases.append(big)
+    for coll in cases:
+        want, nd = P.parse_collection(coll)
+        for T in (1, 2, 3, 8, 0):
+            got, nd2 = P.parse_collection_mt(coll, threads=T)
+            assert np.array_equal(got, want) and nd2 == nd, (coll[:40], T)
+        for piece in (1, 7, 64, 1000, 1 << 20):
+            if len(coll) > 20000 and piece < 64:
+                continue
+            parts = list(P.parse_pieces(coll, piece))
+            got = np.concatenate(parts) if parts else np.empty(0, np.uint8)
+            assert np.array_equal(got, want), (coll[:40], piece)
+
+
+def test_parallel_parser_prefix_falls_back_to_sequential():
+    coll = b">a\n" + b"ACGTACGTAC\n" * 300 + b">b\n" + b"TTTTGGGG\n" * 200
+    for pfx in (1, 2, 100, 2001, len(coll) - 1, len(coll), len(coll) + 5, P.UINT64_MAX):
+        t1, n1 = P.parse_collection(coll, pfx)
+        t2, n2 = P.parse_collection_mt(coll, pfx, threads=4)
+        assert np.array_equal(t1, t2) and n1 == n2, pfx
