@@ -10,7 +10,15 @@
 // Where the reference calls computeBWT (CMS-BWT.h:69) this driver calls the C ABI of
 // include/cmsbwt_b200.h: cmsbwt_index_upload, then cmsbwt_run.  There is no CPU fallback: without
 // a CUDA device the program exits 1.  Extra, non-reference options are long options only
-// (--device N, --no-host-sa) so the reference's getopt string "p:b:o:rh" keeps its meaning.
+// (--device N, --no-host-sa, --no-stream, --threads T) so the reference's getopt string "p:b:o:rh"
+// keeps its meaning.
+//
+// Ingest and egress are streamed (--no-stream keeps the plain read / parse / copy /
+// write sequence): the collection file is mapped and parsed in pieces by several host threads into
+// pinned staging slots (cmsbwt_parse_piece), each piece goes to the device while the next one is
+// parsed (cmsbwt_text_append), the host suffix array (libsais, one thread) is built meanwhile on
+// its own thread, and the result comes back range by range into pinned slots that writer threads
+// pwrite() into the output file while the next range is copied (cmsbwt_result_read).
 //
 // Reference SA: north-star keeps it on the host with libsais.  libsais is a third-party library
 // that is not vendored in this repository; when a libsais shared object can be dlopen()ed
@@ -29,6 +37,11 @@
 #include <string>
 #include <vector>
 #include <unistd.h>
+#include <fcntl.h>
+#include <future>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <thread>
 #include "cmsbwt_b200.h"
 
 struct Args {                       // utils.h:8-14
@@ -38,6 +51,8 @@ struct Args {                       // utils.h:8-14
   unsigned long long prefixLength = UINT64_MAX;
   int device = 0;
   bool host_sa = true;
+  bool stream = true;               // streamed ingest / egress
+  int threads = 0;                  // host threads of the parser (0 = hardware threads, at most 16)
 };
 
 static void print_help(char **argv) {
@@ -51,7 +66,9 @@ static void print_help(char **argv) {
             << "\t-o \tbasename for the output files, def. <input filename>" << std::endl
             << "\t-h \tprints this help" << std::endl
             << "\t--device N \tCUDA device ordinal, def. 0" << std::endl
-            << "\t--no-host-sa \tbuild the reference suffix array on the GPU even if libsais is available" << std::endl;
+            << "\t--no-host-sa \tbuild the reference suffix array on the GPU even if libsais is available" << std::endl
+            << "\t--no-stream \tread, parse, copy and write one after the other (no overlap)" << std::endl
+            << "\t--threads T \thost threads of the collection parser, def. all (at most 16)" << std::endl;
   exit(-1);
 }
 
@@ -61,6 +78,8 @@ static void parse_args(int argc, char **argv, Args &arg) {
   puts("");
   static const option longopts[] = {{"device", required_argument, nullptr, 1000},
                                     {"no-host-sa", no_argument, nullptr, 1001},
+                                    {"no-stream", no_argument, nullptr, 1002},
+                                    {"threads", required_argument, nullptr, 1003},
                                     {nullptr, 0, nullptr, 0}};
   int c;
   while ((c = getopt_long(argc, argv, "p:b:o:rh", longopts, nullptr)) != -1) {
@@ -71,6 +90,8 @@ static void parse_args(int argc, char **argv, Args &arg) {
       case 'o': arg.outname = optarg; break;
       case 1000: arg.device = atoi(optarg); break;
       case 1001: arg.host_sa = false; break;
+      case 1002: arg.stream = false; break;
+      case 1003: arg.threads = atoi(optarg); break;
       case 'h': print_help(argv); break;
       default:
         std::cout << "Unknown option. Use -h for help." << std::endl;
@@ -126,6 +147,139 @@ static double ms_since(std::chrono::high_resolution_clock::time_point t) {
   return std::chrono::duration<double, std::milli>(std::chrono::high_resolution_clock::now() - t).count();
 }
 
+// ---- streamed ingest / egress ---------------------------------------------------
+struct Mapped {                     // read-only view of a file: mmap, or a heap copy where mapping fails
+  const uint8_t *p = nullptr;
+  int64_t size = 0;
+  bool mapped = false;
+  std::vector<uint8_t> heap;
+  bool open(const std::string &path) {
+    int fd = ::open(path.c_str(), O_RDONLY);
+    if (fd < 0) return false;
+    struct stat sb;
+    if (fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && sb.st_size > 0) {
+      void *m = mmap(nullptr, (size_t)sb.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (m != MAP_FAILED) {
+        madvise(m, (size_t)sb.st_size, MADV_SEQUENTIAL);
+        p = (const uint8_t *)m;
+        size = (int64_t)sb.st_size;
+        mapped = true;
+        ::close(fd);
+        return true;
+      }
+    }
+    ::close(fd);
+    if (!read_file(path, heap)) return false;
+    p = heap.data();
+    size = (int64_t)heap.size();
+    return true;
+  }
+  void close() {
+    if (mapped) munmap((void *)p, (size_t)size);
+    std::vector<uint8_t>().swap(heap);
+    p = nullptr; size = 0; mapped = false;
+  }
+};
+
+static int64_t env_mb(const char *name, int64_t def_mb) {
+  const char *e = getenv(name);
+  int64_t v = e ? atoll(e) : 0;          // CMSBWT_PIECE_KB / CMSBWT_OUT_KB: sizes for tests
+  return v > 0 ? v * 1024 : def_mb * 1024 * 1024;
+}
+
+// Parses file[0, size) piece by piece on T threads into two pinned slots and appends every piece to
+// the device text while the next one is parsed.  Returns N (0: no document) or a negative code.
+static int64_t ingest_streamed(cmsbwt_ctx *ctx, const uint8_t *file, int64_t size, int T, int64_t *ndocs) {
+  const int64_t piece = env_mb("CMSBWT_PIECE_KB", 256);
+  int rc = cmsbwt_text_begin(ctx, (uint64_t)size + 1);
+  if (rc) return rc;
+  void *slot[2] = {nullptr, nullptr};
+  int64_t cap = 0;
+  int64_t N = 0, docs = 0;
+  int32_t open = 0;
+  std::vector<int64_t> cut((size_t)T + 1), w((size_t)T), d((size_t)T);
+  std::vector<int32_t> op((size_t)T);
+  int k = 0;
+  for (int64_t a = 0; a < size && rc == 0; k++) {
+    const int64_t b = cmsbwt_line_start(file, size, a + piece < size ? a + piece : size);
+    const int s = k & 1;
+    if (b - a + 16 > cap) {                 // first piece, or a line longer than a piece
+      for (int q = 0; q < 2; q++) { if ((rc = cmsbwt_copy_wait(ctx, q))) break; cmsbwt_host_free(slot[q]); slot[q] = nullptr; }
+      cap = b - a + 16;
+      for (int q = 0; q < 2 && rc == 0; q++) rc = cmsbwt_host_alloc(&slot[q], (uint64_t)cap);
+      if (rc) break;
+    }
+    if ((rc = cmsbwt_copy_wait(ctx, s))) break;      // the copy that last used this slot is done
+    uint8_t *dst = (uint8_t *)slot[s];
+    for (int t = 0; t <= T; t++) cut[t] = t == T ? b : cmsbwt_line_start(file, b, a + (b - a) / T * t);
+    auto work = [&](int t) {
+      d[t] = 0; op[t] = -1;
+      w[t] = cmsbwt_parse_piece(file, cut[t], cut[t + 1], dst + (cut[t] - a), &d[t], &op[t]);
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back(work, t);
+    work(0);
+    for (auto &x : th) x.join();
+    for (int t = 0; t < T && rc == 0; t++) {
+      if (w[t] < 0) { rc = (int)w[t]; break; }
+      rc = cmsbwt_text_append(ctx, dst + (cut[t] - a), (uint64_t)w[t]);
+      N += w[t]; docs += d[t];
+      if (op[t] >= 0) open = op[t];
+    }
+    if (rc == 0) rc = cmsbwt_copy_fence(ctx, s);
+    a = b;
+  }
+  if (rc == 0 && open == 1) {               // a non-empty remainder is one more document (:1269-1275)
+    const int s = k & 1;
+    if (!slot[s]) rc = cmsbwt_host_alloc(&slot[s], 16);
+    if (rc == 0) rc = cmsbwt_copy_wait(ctx, s);
+    if (rc == 0) {
+      *(uint8_t *)slot[s] = 2;
+      rc = cmsbwt_text_append(ctx, (const uint8_t *)slot[s], 1);
+      N++; docs++;
+    }
+    if (rc == 0) rc = cmsbwt_copy_fence(ctx, s);
+  }
+  for (int q = 0; q < 2; q++) { cmsbwt_copy_wait(ctx, q); cmsbwt_host_free(slot[q]); }
+  if (ndocs) *ndocs = docs;
+  return rc ? rc : N;
+}
+
+static bool write_all(int fd, const uint8_t *p, uint64_t bytes, uint64_t off) {
+  while (bytes) {
+    ssize_t k = pwrite(fd, p, (size_t)bytes, (off_t)off);
+    if (k <= 0) return false;
+    p += k; off += (uint64_t)k; bytes -= (uint64_t)k;
+  }
+  return true;
+}
+
+// Reads the result back range by range into pinned slots; writer threads pwrite() a range while the
+// next one is copied.  Returns 0, a negative library code, or 1 for a write error.
+static int egress_streamed(cmsbwt_ctx *ctx, int fd, uint64_t out_bytes) {
+  enum { NS = 4 };
+  const uint64_t ch = (uint64_t)env_mb("CMSBWT_OUT_KB", 32);
+  void *slot[NS] = {};
+  std::future<bool> pend[NS];
+  int rc = 0;
+  bool ok = true;
+  for (int q = 0; q < NS && rc == 0 && (uint64_t)q * ch < out_bytes; q++) rc = cmsbwt_host_alloc(&slot[q], ch);
+  uint64_t j = 0;
+  for (uint64_t off = 0; off < out_bytes && rc == 0 && ok; off += ch, j++) {
+    const int s = (int)(j % NS);
+    if (pend[s].valid()) ok = pend[s].get() && ok;
+    const uint64_t m = out_bytes - off < ch ? out_bytes - off : ch;
+    if ((rc = cmsbwt_result_read(ctx, slot[s], off, m))) break;
+    if ((rc = cmsbwt_copy_fence(ctx, 2 + s))) break;
+    if ((rc = cmsbwt_copy_wait(ctx, 2 + s))) break;
+    const uint8_t *src = (const uint8_t *)slot[s];
+    pend[s] = std::async(std::launch::async, [=] { return write_all(fd, src, m, off); });
+  }
+  for (int q = 0; q < NS; q++) if (pend[q].valid()) ok = pend[q].get() && ok;
+  for (int q = 0; q < NS; q++) cmsbwt_host_free(slot[q]);
+  return rc ? rc : (ok ? 0 : 1);
+}
+
 int main(int argc, char **argv) {
   Args arg;
   parse_args(argc, argv, arg);
@@ -167,20 +321,16 @@ int main(int argc, char **argv) {
   std::vector<uint8_t>().swap(ref);
 
   // ---- collection: the reference's document list (:1138-1140,:1257-1275) ----
-  if (!read_file(collFileName, collfile)) {
+  Mapped coll;
+  if (!coll.open(collFileName)) {
     fprintf(stderr, "Error opening file %s\n", collFileName.c_str());
     exit(1);
   }
-  if (collfile.empty()) { fprintf(stderr, "Error: collection %s is empty\n", collFileName.c_str()); exit(1); }
-  std::vector<uint8_t> text(collfile.size() + 2);
-  int64_t ndocs = 0;
-  auto tp = std::chrono::high_resolution_clock::now();
-  int64_t N = cmsbwt_parse_collection(collfile.data(), (int64_t)collfile.size(), arg.prefixLength,
-                                      text.data(), &ndocs);
-  std::vector<uint8_t>().swap(collfile);
-  if (N <= 0) { fprintf(stderr, "Error: collection %s holds no document\n", collFileName.c_str()); exit(1); }
-  log << "Collection parsed in " << ms_since(tp) << " ms: " << N << " symbols, " << ndocs
-      << " documents" << std::endl;
+  if (coll.size == 0) { fprintf(stderr, "Error: collection %s is empty\n", collFileName.c_str()); exit(1); }
+  int T = arg.threads > 0 ? arg.threads : (int)std::thread::hardware_concurrency();
+  if (T < 1) T = 1;
+  if (T > 16 && arg.threads <= 0) T = 16;
+  const bool streamed = arg.stream && arg.prefixLength >= (unsigned long long)coll.size;
 
   // ---- device ----
   cmsbwt_ctx *ctx = nullptr;
@@ -195,14 +345,48 @@ int main(int argc, char **argv) {
     exit(1);
   };
 
-  // ---- SA (:247) + device index (:263-297) ----
+  // ---- SA (:247) on its own host thread while the collection is parsed and copied ----
   std::vector<int32_t> sa;
   libsais_fn sais = arg.host_sa ? find_libsais(argv[0]) : nullptr;
   auto ts = std::chrono::high_resolution_clock::now();
+  double sa_ms = 0;
+  int sa_rc = 0;
+  std::thread sa_thread;
+  auto build_sa = [&] {
+    sa_rc = sais(x.data(), sa.data(), (int32_t)n, 0, nullptr);
+    sa_ms = ms_since(ts);
+  };
   if (sais) {
     sa.resize((size_t)n);
-    if (sais(x.data(), sa.data(), (int32_t)n, 0, nullptr) != 0) { fprintf(stderr, "Error: libsais failed\n"); exit(1); }
-    log << "Computed SA in " << ms_since(ts) << " ms (libsais, host)" << std::endl;
+    if (arg.stream) sa_thread = std::thread(build_sa);
+    else build_sa();
+  }
+
+  // ---- collection -> device text ----
+  std::vector<uint8_t> text;
+  int64_t ndocs = 0, N = 0;
+  auto tp = std::chrono::high_resolution_clock::now();
+  if (streamed) {
+    N = ingest_streamed(ctx, coll.p, coll.size, T, &ndocs);
+    if (N < 0) { if (sa_thread.joinable()) sa_thread.join(); die("ingest"); }
+  } else {
+    text.resize((size_t)coll.size + 2);
+    N = cmsbwt_parse_collection_mt(coll.p, coll.size, arg.prefixLength, text.data(), &ndocs, arg.stream ? T : 1);
+  }
+  coll.close();
+  if (N <= 0) {
+    if (sa_thread.joinable()) sa_thread.join();
+    fprintf(stderr, "Error: collection %s holds no document\n", collFileName.c_str());
+    exit(1);
+  }
+  log << "Collection parsed" << (streamed ? " and copied to the device" : "") << " in " << ms_since(tp)
+      << " ms: " << N << " symbols, " << ndocs << " documents (" << (arg.stream ? T : 1) << " threads)" << std::endl;
+
+  // ---- device index (:263-297) ----
+  if (sa_thread.joinable()) sa_thread.join();
+  if (sais) {
+    if (sa_rc != 0) { fprintf(stderr, "Error: libsais failed\n"); exit(1); }
+    log << "Computed SA in " << sa_ms << " ms (libsais, host" << (arg.stream ? ", beside the ingest" : "") << ")" << std::endl;
   }
   auto ti = std::chrono::high_resolution_clock::now();
   if (cmsbwt_index_upload(ctx, x.data(), (uint32_t)n, sais ? sa.data() : nullptr) != CMSBWT_OK) die("index_upload");
@@ -219,13 +403,32 @@ int main(int argc, char **argv) {
   // ---- the path: MS -> head sort -> emit ----
   const int mode = arg.format ? CMSBWT_MODE_RLE : CMSBWT_MODE_PLAIN;
   auto tr = std::chrono::high_resolution_clock::now();
-  if (cmsbwt_ms_run(ctx, text.data(), (uint64_t)N) != CMSBWT_OK) die("ms_run");
+  if (streamed) { if (cmsbwt_ms_run_staged(ctx) != CMSBWT_OK) die("ms_run_staged"); }
+  else if (cmsbwt_ms_run(ctx, text.data(), (uint64_t)N) != CMSBWT_OK) die("ms_run");
   std::vector<uint8_t>().swap(text);
   if (cmsbwt_heads_sort(ctx) != CMSBWT_OK) die("heads_sort");
   uint64_t out_bytes = 0;
   if (cmsbwt_emit(ctx, mode, &out_bytes) != CMSBWT_OK) die("emit");
-  std::vector<uint8_t> out((size_t)out_bytes);
-  if (cmsbwt_result_download(ctx, out.data(), out_bytes) != CMSBWT_OK) die("result_download");
+  std::string outpath = arg.outname + (arg.format ? ".rl_bwt" : ".bwt");
+  auto tw = std::chrono::high_resolution_clock::now();
+  if (arg.stream) {
+    int fd = ::open(outpath.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) { fprintf(stderr, "Error writing %s\n", outpath.c_str()); exit(1); }
+    int rc = egress_streamed(ctx, fd, out_bytes);
+    if (::close(fd) != 0 && rc == 0) rc = 1;
+    if (rc < 0) die("result_read");
+    if (rc > 0) { fprintf(stderr, "Error writing %s\n", outpath.c_str()); exit(1); }
+  } else {
+    std::vector<uint8_t> out((size_t)out_bytes);
+    if (cmsbwt_result_download(ctx, out.data(), out_bytes) != CMSBWT_OK) die("result_download");
+    FILE *fo = fopen(outpath.c_str(), "wb");
+    if (!fo || (out_bytes && fwrite(out.data(), 1, (size_t)out_bytes, fo) != (size_t)out_bytes)) {
+      fprintf(stderr, "Error writing %s\n", outpath.c_str());
+      exit(1);
+    }
+    fclose(fo);
+  }
+  double write_ms = ms_since(tw);
   double path_ms = ms_since(tr);
   cmsbwt_stats st{};
   cmsbwt_get_stats(ctx, &st);
@@ -241,13 +444,7 @@ int main(int argc, char **argv) {
   log << "Path (MS + head sort + emit + copies) wall: " << path_ms << " ms, kernel launches: "
       << st.kernel_launches << std::endl;
 
-  std::string outpath = arg.outname + (arg.format ? ".rl_bwt" : ".bwt");
-  FILE *fo = fopen(outpath.c_str(), "wb");
-  if (!fo || (out_bytes && fwrite(out.data(), 1, (size_t)out_bytes, fo) != (size_t)out_bytes)) {
-    fprintf(stderr, "Error writing %s\n", outpath.c_str());
-    exit(1);
-  }
-  fclose(fo);
+  log << "Result copied back and written in " << write_ms << " ms" << (arg.stream ? " (streamed)" : "") << std::endl;
   cmsbwt_ctx_destroy(ctx);
 
   std::cout << "==== Time elapsed: "

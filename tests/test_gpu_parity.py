@@ -218,3 +218,57 @@ def test_round_trip_properties_medium(ctx):
     assert np.array_equal(O.rle_decode(rl), a)
     want = O.Oracle(x, ctx.index_download()["sa"]).bwt(text)
     assert np.array_equal(a, want)
+
+
+def test_streamed_api_matches_run(ctx):
+    """cmsbwt_text_begin/append/ms_run_staged + cmsbwt_result_read give the bytes of
+    cmsbwt_run, with pieces from cmsbwt_parse_piece and staging slots smaller than the text."""
+    for name in ("synth_20k_x8.npz", "fuzz_042.npz", "edge_headerless.npz", "synth_600_x200.npz"):
+        z = np.load(os.path.join(GOLDEN, name))
+        coll = z["coll_file"].tobytes()
+        ctx.index_upload(P.augment(P.read_reference(z["ref_file"].tobytes())))
+        for piece, chunk in ((1 << 20, 1 << 20), (4096, 1000), (37, 64)):
+            if piece < 64 and len(coll) > 30000:
+                continue
+            got = ctx.run_streamed(P.parse_pieces(coll, piece), len(coll) + 1, P.MODE_PLAIN, chunk)
+            assert np.array_equal(got, z["bwt"]), (name, piece, chunk)
+        got = ctx.run_streamed(P.parse_pieces(coll, 5000), len(coll) + 1, P.MODE_RLE, 999)
+        assert np.array_equal(got, O.rle(z["bwt"])), name
+
+
+@pytest.mark.parametrize("stream", [True, False])
+def test_cli_binary_matches_golden(workdir, stream):
+    """The cms_bwt command line (cms_bwt_b200/host/cms_bwt.cpp; process contract of main.cpp:14-132)
+    on the golden fixtures of the unmodified reference binary: .bwt, .rl_bwt (-r), -p, with the
+    streamed ingest/egress cut into many small pieces and with --no-stream."""
+    import subprocess
+    exe = os.path.join(os.path.dirname(GOLDEN), "..", "cms_bwt_b200", "cms_bwt")
+    env = dict(os.environ, CMSBWT_PIECE_KB="3", CMSBWT_OUT_KB="2")
+    for f in sorted(glob.glob(os.path.join(GOLDEN, "*.npz"))):
+        z = np.load(f)
+        base = os.path.basename(f)[:-4]
+        d = os.path.join(workdir, "cli_%s_%d" % (base, stream))
+        os.makedirs(d, exist_ok=True)
+        z["ref_file"].tofile(os.path.join(d, "ref.fa"))
+        z["coll_file"].tofile(os.path.join(d, "coll.fa"))
+        with open(os.path.join(d, "list.txt"), "w") as fh:
+            fh.write("%s\n%s  \n" % (os.path.join(d, "ref.fa"), os.path.join(d, "coll.fa")))
+        for rle in (False, True):
+            for host_sa in ((True, False) if not rle else (True,)):
+                cmd = [exe, "-o", os.path.join(d, "out")]
+                if int(z["prefix"]) != P.UINT64_MAX:
+                    cmd += ["-p", str(int(z["prefix"]))]
+                if rle:
+                    cmd.append("-r")
+                if not stream:
+                    cmd.append("--no-stream")
+                if not host_sa:
+                    cmd.append("--no-host-sa")
+                r = subprocess.run(cmd + [os.path.join(d, "list.txt")], env=env, stdout=subprocess.PIPE,
+                                   stderr=subprocess.STDOUT, timeout=300)
+                assert r.returncode == 0, (base, r.stdout.decode()[-600:])
+                assert b"==== Time elapsed:" in r.stdout
+                got = np.fromfile(os.path.join(d, "out.rl_bwt" if rle else "out.bwt"), np.uint8)
+                want = z["rl_bwt"] if rle else z["bwt"]
+                assert np.array_equal(got, want), (base, rle, stream, host_sa)
+                assert os.path.exists(os.path.join(d, "out.log"))

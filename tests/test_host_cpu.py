@@ -96,3 +96,34 @@ def test_parallel_parser_prefix_falls_back_to_sequential():
         t1, n1 = P.parse_collection(coll, pfx)
         t2, n2 = P.parse_collection_mt(coll, pfx, threads=4)
         assert np.array_equal(t1, t2) and n1 == n2, pfx
+
+
+def test_cli_exit_codes(tmp_path):
+    """Process contract of main.cpp: usage -> exit(-1) (:23, :55-59), unreadable or empty inputs ->
+    exit(1) (:91-115, CMS-BWT-functions.cpp:156-160); without a device the program fails, it does
+    not fall back to the CPU."""
+    import subprocess
+    import torch
+    exe = os.path.join(ROOT, "cms_bwt_b200", "cms_bwt")
+    assert os.path.exists(exe), "build first"
+    run = lambda *a: subprocess.run([exe, *a], cwd=tmp_path, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    (tmp_path / "r.fa").write_bytes(b">ref\nACGTACGTTTGACA\n")
+    (tmp_path / "c.fa").write_bytes(b">s1\nACGTACGATTGACA\n>s2\nACGTACGTTTGCA\n")
+    (tmp_path / "e.fa").write_bytes(b"")
+    (tmp_path / "ok.txt").write_text("r.fa\nc.fa\n")
+    (tmp_path / "noref.txt").write_text("nope.fa\nc.fa\n")
+    (tmp_path / "nocoll.txt").write_text("r.fa\nnope.fa\n")
+    (tmp_path / "empty.txt").write_text("r.fa\ne.fa\n")
+    (tmp_path / "short.txt").write_text("r.fa\n")
+    assert run().returncode == 255
+    assert run("-x", "ok.txt").returncode == 255
+    assert run("a", "b").returncode == 255
+    assert run("missing.txt").returncode == 1
+    for lst in ("noref.txt", "nocoll.txt", "empty.txt", "short.txt"):
+        r = run(lst)
+        assert r.returncode == 1 and r.stderr, lst
+    r = run("ok.txt")
+    assert b"==== Command line:" in r.stdout and b"==== Parameters:" in r.stdout and b"==== CMS-BWT" in r.stdout
+    if not torch.cuda.is_available():
+        assert r.returncode == 1 and b"no CPU fallback" in r.stderr
+        assert not (tmp_path / "ok.txt.bwt").exists()
