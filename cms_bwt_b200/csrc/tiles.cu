@@ -478,7 +478,10 @@ void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out) {
     wo = c->h_within.as<u32>(); oo = c->h_off.as<u64>();
   }
   size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;
-  if (sm > 40 * 1024)
+  // static (24 KB of bucket rows) + dynamic shared memory above 48 KB needs the opt-in; a fresh
+  // process that starts with a tile of 1.6-2.5 K entries failed here before (threshold was 40 KB
+  // of dynamic memory alone)
+  if (sm > 16 * 1024)
     CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_place<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                                c->t_roff.as<u32>(), c->ix.isa, base, n, 0, out, nullptr, wo, oo,
@@ -739,7 +742,7 @@ void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
     shard_place_deep(c, base, raw.as<u64>());
   } else {
     size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;
-    if (sm > 40 * 1024)
+    if (sm > 16 * 1024)
       CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
     k_tile_place<<<tp, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                              c->t_roff.as<u32>(), c->ix.isa, base, n, c->sh_rank * tp, nullptr,

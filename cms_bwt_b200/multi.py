@@ -514,7 +514,7 @@ def main(argv=None):
     import os
     import time
     import numpy as np
-    from . import Context, read_reference, augment, parse_collection, UINT64_MAX
+    from . import Context, read_reference, augment, parse_collection_mt, UINT64_MAX
     ap = argparse.ArgumentParser(prog="cms_bwt_multi")
     ap.add_argument("-p", type=int, default=UINT64_MAX)
     ap.add_argument("-b", type=float, default=2.0)            # accepted and ignored
@@ -535,7 +535,8 @@ def main(argv=None):
     with open(ref_path, "rb") as f:
         x = augment(read_reference(f.read()))
     with open(coll_path, "rb") as f:
-        text, ndocs = parse_collection(f.read(), a.p)
+        # every rank parses the whole file (it needs the document table): the host threads are shared
+        text, ndocs = parse_collection_mt(f.read(), a.p, max(1, min(16, (os.cpu_count() or 1) // world)))
     ends = np.flatnonzero(text == 2)
     starts = np.concatenate([[0], ends[:-1] + 1])
     plan = shard_documents((ends - starts).tolist(), world)
@@ -557,7 +558,7 @@ def main(argv=None):
         open(path, "wb").close()
     dist.barrier()
     fd = os.open(path, os.O_WRONLY)
-    os.pwrite(fd, data.tobytes(), offset)
+    os.pwrite(fd, memoryview(np.ascontiguousarray(data)), offset)
     os.close(fd)
     dist.barrier()
     if rank == 0:

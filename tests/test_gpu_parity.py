@@ -264,6 +264,7 @@ def test_cli_binary_matches_golden(workdir, stream):
                     cmd.append("--no-stream")
                 if not host_sa:
                     cmd.append("--no-host-sa")
+                env["CMSBWT_OUT_MMAP"] = "0" if rle else "1"      # pwrite / shared-mapping writers
                 r = subprocess.run(cmd + [os.path.join(d, "list.txt")], env=env, stdout=subprocess.PIPE,
                                    stderr=subprocess.STDOUT, timeout=300)
                 assert r.returncode == 0, (base, r.stdout.decode()[-600:])
