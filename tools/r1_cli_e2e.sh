@@ -5,8 +5,8 @@ set -u
 cd "${GRAFT_REPO_ROOT:-/root/repo}"
 O=gpurun_out
 mkdir -p $O
-[ "${SKIP_TESTS:-0}" = 1 ] || timeout 420 python -m pytest tests/test_gpu_parity.py -x -q -m gpu \
-  -k "streamed_api or cli_binary" > $O/r1_v6_tests.log 2>&1
+[ "${SKIP_TESTS:-0}" = 1 ] || timeout 420 python -m pytest tests/test_gpu_parity.py tests/test_gpu_sharded.py -x -q -m gpu \
+  -k "streamed_api or cli_binary or cli_multi" > $O/r1_v6_tests.log 2>&1
 echo "tests rc=$?" >> $O/r1_v6_tests.log
 tail -3 $O/r1_v6_tests.log
 python tools/gen_synth.py 5000000 100 0.001 11 /dev/shm/c2
