@@ -45,6 +45,62 @@ def shard_documents(doc_lengths, world):
     return [(bounds[r], bounds[r + 1]) for r in range(world)]
 
 
+def file_shard_cuts(buf, world):
+    """Byte ranges of the collection FILE, one per rank, for a sharded ingest: the split points
+    size*r/world are moved forward to the next header line (a '>' at a line start), so every range
+    but the first starts with a header and every range but the last ends with a newline.
+    buf: bytes / mmap.  -> world + 1 offsets (a range may come out empty: the caller falls back)."""
+    size = len(buf)
+    cuts = [0]
+    for r in range(1, world):
+        p = max(size * r // world, cuts[-1])
+        if p <= 0:
+            q = 0
+        else:
+            k = buf.find(b"\n>", p - 1)
+            q = k + 1 if k >= 0 else size
+        cuts.append(q)
+    cuts.append(size)
+    return cuts
+
+
+def file_shards_usable(buf, cuts):
+    """True when every rank's range holds at least one complete line (an unterminated last line is
+    dropped by the reference's getline loop, which would leave the last rank without text)."""
+    if not all(x < y for x, y in zip(cuts, cuts[1:])):
+        return False
+    if len(cuts) == 2:
+        return True
+    k = buf.find(b"\n", cuts[-2])          # the last range: its header line and one more complete line
+    return k >= 0 and buf.find(b"\n", k + 1) >= 0
+
+
+def file_shard_text(buf, cuts, rank, threads=1):
+    """The text of rank's byte range under the reference's document rules (:1138-1140, :1257-1275),
+    such that the concatenation over the ranks is exactly parse_collection(whole file): the 0x02 a
+    header line emits closes the document BEFORE it, so the header that starts a range hands its
+    separator to the previous rank.  -> (uint8 text, documents)."""
+    import numpy as np
+    from . import parse_collection_mt
+    world = len(cuts) - 1
+    a, b = cuts[rank], cuts[rank + 1]
+    sub = np.frombuffer(buf, np.uint8, b - a, a)
+    text, nd = parse_collection_mt(sub, threads=threads)
+    if rank > 0:                       # the first line is a header: its separator belongs to rank - 1
+        if len(text) == 0 or text[0] != 2:
+            raise ValueError("range %d does not start with a complete header line" % rank)
+        text, nd = text[1:], nd - 1
+    if rank < world - 1:
+        # an open document at the end was closed by the stand-alone parse (= the next header's 0x02);
+        # after a header or blank line the next header still emits one (an empty document)
+        j = buf.rfind(b"\n", a, b - 1)
+        ls = j + 1 if j >= 0 else a      # start of the range's last line (it ends at b - 1)
+        first = buf[ls] if ls < b - 1 else None
+        if first is None or first == ord(">"):
+            text, nd = np.concatenate([text, np.array([2], np.uint8)]), nd + 1
+    return text, nd
+
+
 def merge_rle_borders(parts):
     """Concatenates per-rank lists of (run, symbol) records, merging a run that straddles a border
     (the -r writer emits maximal runs, CMS-BWT-functions.cpp:1695-1777 / BASELINE.md section 2)."""
@@ -534,15 +590,27 @@ def main(argv=None):
     outname = a.o or a.listfile
     with open(ref_path, "rb") as f:
         x = augment(read_reference(f.read()))
+    threads = max(1, min(16, (os.cpu_count() or 1) // world))
+    import mmap
     with open(coll_path, "rb") as f:
-        # every rank parses the whole file (it needs the document table): the host threads are shared
-        text, ndocs = parse_collection_mt(f.read(), a.p, max(1, min(16, (os.cpu_count() or 1) // world)))
-    ends = np.flatnonzero(text == 2)
-    starts = np.concatenate([[0], ends[:-1] + 1])
-    plan = shard_documents((ends - starts).tolist(), world)
-    d0, d1 = plan[rank]
-    lo = int(starts[d0]) if d0 < len(ends) else len(text)
-    hi = int(ends[d1 - 1]) + 1 if d1 > d0 else lo
+        size = os.fstat(f.fileno()).st_size
+        buf = mmap.mmap(f.fileno(), 0, access=mmap.ACCESS_READ) if size else b""
+    cuts = file_shard_cuts(buf, world)
+    if world > 1 and a.p >= size and file_shards_usable(buf, cuts):
+        # sharded ingest: every rank parses only its byte range of the file (cut at header lines)
+        text_r, nd_r = file_shard_text(buf, cuts, rank, threads)
+        lo, hi, d0, d1 = 0, len(text_r), 0, nd_r
+        text = text_r
+    else:
+        # -p, one rank, or fewer header lines than ranks: whole file on every rank, documents
+        # balanced by length
+        text, ndocs = parse_collection_mt(buf, a.p, threads)
+        ends = np.flatnonzero(text == 2)
+        starts = np.concatenate([[0], ends[:-1] + 1])
+        plan = shard_documents((ends - starts).tolist(), world)
+        d0, d1 = plan[rank]
+        lo = int(starts[d0]) if d0 < len(ends) else len(text)
+        hi = int(ends[d1 - 1]) + 1 if d1 > d0 else lo
     if hi == lo:
         raise SystemExit("cms_bwt_multi: more ranks than documents")
     shard = torch.from_numpy(np.concatenate([text[lo:hi], np.full(64, 2, np.uint8)])).to(dev)

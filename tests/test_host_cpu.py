@@ -127,3 +127,37 @@ def test_cli_exit_codes(tmp_path):
     if not torch.cuda.is_available():
         assert r.returncode == 1 and b"no CPU fallback" in r.stderr
         assert not (tmp_path / "ok.txt.bwt").exists()
+
+
+def test_sharded_ingest_concatenates_to_the_whole_parse(tmp_path):
+    """Multi-GPU command line: every rank parses only its byte range of the collection file
+    (multi.file_shard_cuts / file_shard_text); the rank texts concatenated are the whole parse."""
+    import mmap
+    from cms_bwt_b200 import multi
+    cases = [fuzz_cases.make_case(s)["coll_file"] for s in range(150)] + _odd_files()
+    cases.append(b">a\nAC\n\n>b\n>c\nGT\nAA\n\n\n>d\nT\n>e\n" * 7 + b"ACG")
+    used = 0
+    for i, coll in enumerate(cases):
+        want, nd = P.parse_collection(coll)
+        path = tmp_path / ("c%d.fa" % i)
+        path.write_bytes(coll)
+        bufs = [coll]
+        if len(coll) and i % 3 == 0:
+            with open(path, "rb") as fh:
+                bufs.append(mmap.mmap(fh.fileno(), 0, access=mmap.ACCESS_READ))
+        for buf in bufs:
+            for world in (1, 2, 3, 5, 8):
+                cuts = multi.file_shard_cuts(buf, world)
+                assert cuts[0] == 0 and cuts[-1] == len(coll) and all(x <= y for x, y in zip(cuts, cuts[1:]))
+                if not multi.file_shards_usable(buf, cuts):
+                    continue               # main() falls back to the whole-file parse
+                parts = [multi.file_shard_text(buf, cuts, r, threads=1 + r % 2) for r in range(world)]
+                got = np.concatenate([t for t, _ in parts])
+                assert np.array_equal(got, want), (i, world)
+                assert sum(n for _, n in parts) == nd, (i, world)
+                for t, n in parts:
+                    if world > 1:
+                        assert len(t) > 0, (i, world)
+                    assert len(t) == 0 or (t[-1] == 2 and n == int((t == 2).sum())), (i, world)
+                used += world > 1
+    assert used > 100
