@@ -345,7 +345,7 @@ int main(int argc, char **argv) {
   };
 
   // ---- reference: read, trim, augment (:155-237) ----
-  std::vector<uint8_t> reffile, collfile;
+  std::vector<uint8_t> reffile;
   if (!read_file(refFileName, reffile)) {
     fprintf(stderr, "Error opening file %s\n", refFileName.c_str());
     bail(1);
