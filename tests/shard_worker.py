@@ -22,13 +22,21 @@ def main():
     dist.init_process_group("gloo", rank=rank, world_size=world)
     z = np.load(case)
     x, text = z["x"], z["text"]
-    ends = np.flatnonzero(text == 2)
-    starts = np.concatenate([[0], ends[:-1] + 1])
-    lens = (ends - starts).tolist()
-    a, b = multi.shard_documents(lens, world)[rank]
-    lo = int(starts[a]) if a < len(lens) else len(text)
-    hi = int(ends[b - 1]) + 1 if b > a else lo
-    shard = text[lo:hi]
+    if "coll_file" in z.files:
+        # the multi-GPU command line's sharded ingest: this rank parses only its byte range of the file
+        coll = z["coll_file"].tobytes()
+        cuts = multi.file_shard_cuts(coll, world)
+        assert multi.file_shards_usable(coll, cuts)
+        shard, ndocs = multi.file_shard_text(coll, cuts, rank)
+        a, b = 0, ndocs
+    else:
+        ends = np.flatnonzero(text == 2)
+        starts = np.concatenate([[0], ends[:-1] + 1])
+        lens = (ends - starts).tolist()
+        a, b = multi.shard_documents(lens, world)[rank]
+        lo = int(starts[a]) if a < len(lens) else len(text)
+        hi = int(ends[b - 1]) + 1 if b > a else lo
+        shard = text[lo:hi]
     orc = O.Oracle(x)
     ops = NumpyShardOps(orc, shard)
     sp = multi.ShardedPath(ops, rank, world)

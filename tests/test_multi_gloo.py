@@ -28,9 +28,12 @@ def _free_port():
     return p
 
 
-def _run_world(x, text, workdir, name, world=2):
+def _run_world(x, text, workdir, name, world=2, coll_file=None):
     case = os.path.join(workdir, name + ".npz")
-    np.savez(case, x=x, text=text)
+    if coll_file is None:
+        np.savez(case, x=x, text=text)
+    else:
+        np.savez(case, x=x, text=text, coll_file=np.frombuffer(coll_file, np.uint8))
     port = _free_port()
     procs = []
     for r in range(world):
@@ -122,3 +125,22 @@ def test_sharded_path_fuzz(workdir):
         assert np.array_equal(got, O.Oracle(x).bwt(text)), c["desc"]
         done += 1
     assert done >= 4
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_ingest_by_file_ranges(workdir, world):
+    """The multi-GPU command line's ingest (multi.file_shard_cuts / file_shard_text): every rank
+    parses its own byte range of the collection file; a range that holds only header and blank lines
+    gives a rank nothing but empty documents."""
+    ref, copies = gen_synth.make_collection(2500, 6, 0.01, 8)
+    x = O.augment(ref)
+    fa = b"".join(gen_synth.fasta_bytes("s%d" % k, c) for k, c in enumerate(copies))
+    # blank lines and a header run in the middle (empty documents), unterminated last line
+    mid = len(fa) // 2
+    cutpos = fa.index(b"\n>", mid) + 1
+    coll = fa[:cutpos] + b"\n>e1\n>e2\n\n" + fa[cutpos:] + b"ACGTAC"
+    text, docs = O.parse_collection(coll)
+    cuts = multi.file_shard_cuts(coll, world)
+    assert multi.file_shards_usable(coll, cuts)
+    got, parts = _run_world(x, text, workdir, "fileshard%d" % world, world, coll_file=coll)
+    assert np.array_equal(got, O.Oracle(x).bwt(text))
