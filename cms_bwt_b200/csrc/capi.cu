@@ -1,6 +1,7 @@
 // C ABI (include/cmsbwt_b200.h) over the stage implementations.
 #include "common.cuh"
 #include <string.h>
+#include <stdlib.h>
 #include <chrono>
 
 static thread_local DevCache *tl_cache = nullptr;
@@ -43,6 +44,7 @@ int cmsbwt_ctx_create(int dev, cmsbwt_ctx **out) {
   if (cudaGetDeviceCount(&cnt) != cudaSuccess || dev < 0 || dev >= cnt) return CMSBWT_E_CUDA;
   cmsbwt_ctx *c = new cmsbwt_ctx();
   c->dev = dev;
+  if (const char *e = getenv("CMSBWT_MS_VARIANT")) c->ms_variant = atoll(e);   // measurement switch (= set_param "ms_variant")
   GUARD_BEGIN
   CK(cudaSetDevice(dev));
   CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));

@@ -154,13 +154,12 @@ __global__ void k_sak(const i32 *sa, const u64 *xp, u32 n, u32 n_acgt, int k, u6
 }
 
 // k-mer slot table (ms_fast.cuh): one thread per k-mer writes its 64-byte slot
-__global__ void k_slots(const u64 *sak, const u32 *ktab, u64 K, ulonglong2 *slots) {
+__global__ void k_slots(const u64 *sak, const u32 *ktab, const u64 *xp, u32 n, u32 n_acgt, int k, u64 K,
+                        ulonglong2 *slots) {
   u64 code = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   if (code >= K) return;
-  const u32 lb = ktab[code], cnt = ktab[code + 1] - lb;
   u64 e[8];
-#pragma unroll
-  for (int j = 0; j < 8; j++) e[j] = msf_slot_entry(sak, lb, cnt, j);
+  msf_slot_fill(sak, ktab, xp, n, n_acgt, k, code, e);
 #pragma unroll
   for (int j = 0; j < 4; j++) slots[code * 4 + j] = make_ulonglong2(e[2 * j], e[2 * j + 1]);
 }
@@ -229,8 +228,8 @@ void index_build(cmsbwt_ctx *c) {
     k_sak<<<g, B, 0, st>>>(sa, c->xp, n, c->n_acgt, k, c->d_sak.as<u64>());
     if (c->use_slots) {
       c->d_slots.alloc(K * 64, st);
-      k_slots<<<(u32)((K + B - 1) / B), B, 0, st>>>(c->d_sak.as<u64>(), c->d_ktab.as<u32>(), (u64)K,
-                                                    (ulonglong2 *)c->d_slots.p);
+      k_slots<<<(u32)((K + B - 1) / B), B, 0, st>>>(c->d_sak.as<u64>(), c->d_ktab.as<u32>(), c->xp, n, c->n_acgt,
+                                                    k, (u64)K, (ulonglong2 *)c->d_slots.p);
     } else {
       c->d_slots.release();
     }

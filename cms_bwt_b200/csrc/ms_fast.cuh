@@ -135,6 +135,30 @@ MSF_HD msf_u64 msf_slot_entry(const msf_u64 *sak, msf_u32 lb, msf_u32 cnt, int j
   return (msf_u32)j < cnt ? sak[lb + j] : MSF_SLOT_EMPTY;
 }
 
+// A k-mer that does not occur has an unused slot.  Its neighbours in suffix order are the ranks
+// lb - 1 and lb (lb = ktab[code]); when both are pure suffixes of at least k bases the slot holds
+// their {k-mer code, sa} in entries 1 and 2 and MSF_SLOT_NB in entry 3: the LCE of the text with a
+// suffix of another bucket is the common prefix of the two k-mer codes, so the search of such a
+// position (the novel k-mers behind a mutation) ends with the slot read instead of the exact
+// bisection (variant bit 16).  Entry 0 stays MSF_SLOT_EMPTY.
+#define MSF_SLOT_NB 0xFFFFFFFDFFFFFFFFull
+MSF_HD void msf_slot_fill(const msf_u64 *sak, const msf_u32 *ktab, const msf_u64 *xp, msf_u32 n,
+                          msf_u32 n_acgt, int k, msf_u64 code, msf_u64 *e) {
+  const msf_u32 lb = ktab[code], cnt = ktab[code + 1] - lb;
+#pragma unroll
+  for (int j = 0; j < 8; j++) e[j] = msf_slot_entry(sak, lb, cnt, j);
+  if (cnt == 0 && lb > 0 && lb < n && xp) {
+    const msf_u32 ps = (msf_u32)(sak[lb - 1] >> 32), ss = (msf_u32)(sak[lb] >> 32);
+    if ((msf_u64)ps + (msf_u32)k <= n_acgt && (msf_u64)ss + (msf_u32)k <= n_acgt) {
+      const msf_u32 pc = (msf_u32)(msf_be64(msf_get64(xp, ps)) >> (64 - 2 * k));
+      const msf_u32 sc = (msf_u32)(msf_be64(msf_get64(xp, ss)) >> (64 - 2 * k));
+      e[1] = (msf_u64)pc | ((msf_u64)ps << 32);
+      e[2] = (msf_u64)sc | ((msf_u64)ss << 32);
+      e[3] = MSF_SLOT_NB;
+    }
+  }
+}
+
 struct MsfParams {
   // reference index
   const msf_u64 *slots;   // k-mer slot table (NULL: every search goes through ktab + sak)
@@ -471,7 +495,21 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
       if (P.slots) {
         msf_u64 e[8];
         msf_load_slot(P.slots + (msf_u64)code * 8, e);
-        if (e[0] == MSF_SLOT_EMPTY) { act = MSF_ACT_GENERIC; break; }        // the k-mer does not occur
+        if (e[0] == MSF_SLOT_EMPTY) {                                        // the k-mer does not occur
+          if ((P.variant & 16u) && e[3] == MSF_SLOT_NB) {
+            // neighbours from other buckets: LCE = common prefix of the k-mer codes (< k <= limit);
+            // the successor wins ties, as in msf_generic_search
+            const msf_u32 sh = 32u - 2u * (msf_u32)P.k;
+            const msf_u32 lp = (MSF_CLZ32(((msf_u32)e[1] ^ code) << sh)) >> 1;
+            const msf_u32 ls = (MSF_CLZ32(((msf_u32)e[2] ^ code) << sh)) >> 1;
+            if (ls >= lp) { L.pos = (msf_u32)(e[2] >> 32); L.len = ls; L.sm = 1; }
+            else { L.pos = (msf_u32)(e[1] >> 32); L.len = lp; L.sm = 0; }
+            act = MSF_ACT_FIN;
+            break;
+          }
+          act = MSF_ACT_GENERIC;
+          break;
+        }
         if (e[7] != MSF_SLOT_OVF) {
           // pred = last entry with a smaller key, succ = first entry with a key >= the text's, nxt =
           // the entry after succ (empty entries hold the largest key and sort last).  Written as

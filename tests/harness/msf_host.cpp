@@ -67,8 +67,7 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
     sak[r] = (u64)msf_make_key(xp.data(), (u32)sa[r], n_acgt, k) | ((u64)(u32)sa[r] << 32);
   std::vector<u64> slots(K * 8);
   for (u64 code = 0; code < K; code++)
-    for (int j = 0; j < 8; j++)
-      slots[code * 8 + j] = msf_slot_entry(sak.data(), ktab[code], ktab[code + 1] - ktab[code], j);
+    msf_slot_fill(sak.data(), ktab.data(), xp.data(), n, n_acgt, k, code, &slots[code * 8]);
   std::vector<u32> G(n + 8);
   for (u32 i = 0; i < n; i++) G[i] = i + (u32)plcp_prime[i];
   // ---- text ----
@@ -91,7 +90,7 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   P.xp = xp.data(); P.x8 = x8.data(); P.sak = sak.data(); P.ktab = ktab.data(); P.G = G.data();
   P.n = n; P.n_acgt = n_acgt; P.k = k;
   P.tp = tp.data(); P.N = N; P.seps = seps.data(); P.nseps = nseps; P.wsep = wsep.data();
-  P.WL = WL; P.nwin = nwin; P.skip_min = skip_min; P.variant = 2;
+  P.WL = WL; P.nwin = nwin; P.skip_min = skip_min; P.variant = use_slots == 2 ? 2u | 16u : 2u;   // use_slots 2: empty-bucket slots too
   P.pool = pool.data(); P.batch_next = bnext.data(); P.nb_cap = (u32)nb_cap; P.nb_used = &nb_used;
   P.wfirst = wfirst.data(); P.wcnt = wcnt.data(); P.wfirstpos = wfp.data(); P.wlastpos = wlp.data();
   P.flags = flags; P.win_counter = &counter;

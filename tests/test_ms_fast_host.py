@@ -52,6 +52,8 @@ def pick_k(n):
 def run_case(L, x, text, WL, k=None, skip_min=20, nlanes=7, desc="", slots=None):
     if slots is None:                      # both search paths: k-mer slot table, and ktab + sak only
         r = run_case(L, x, text, WL, k, skip_min, nlanes, desc + " [slots]", slots=1)
+        if r is not None:                  # + neighbours of empty buckets read from the slot
+            run_case(L, x, text, WL, k, skip_min, nlanes, desc + " [slots+nb]", slots=2)
         return r if r is None else run_case(L, x, text, WL, k, skip_min, nlanes, desc + " [ktab]", slots=0)
     o = O.Oracle(x)
     sa = o.sa
