@@ -175,7 +175,7 @@ struct cmsbwt_ctx {
   i64 skip_min = 20;         // fast path: try the G skip for matches at least this long
   i64 fast = 1;              // 0 = always use the general 8-bit kernel
   i64 ms_occ = 8;            // fast path: resident CTAs per SM the MS kernel is compiled for (8, 10, 12)
-  i64 ms_variant = 10;       // MsfParams::variant (text word cache + G prefetch of k_ms_fast)
+  i64 ms_variant = 26;       // MsfParams::variant: 2 text word cache, 8 G prefetch, 16 empty-bucket slots (k_ms_fast)
   i64 use_slots = 1;         // fast path: k-mer slot table (one 64-byte read per search) on / off
   i64 nb_t[3] = {48, 160, 512};   // tile placement: most ranges per tile for 1 / 4 / 8 kappa buckets
   i64 scatter_mb = 64;       // random 4-byte scatters run in passes over target regions of this many MB (L2)
