@@ -422,10 +422,12 @@ def main():
     alg_bytes = N + 16 * H
     achieved = alg_bytes / 1e9 / (kms / 1e3)
     kname = "k_ms_fast" if s.get("fast_path") else "k_ms"
-    traffic = None
+    traffic, traffic_capture = None, None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get(args.workload, {}).get(kname)
+            tj = json.load(f)
+        traffic = tj.get(args.workload, {}).get(kname)
+        traffic_capture = tj.get("_capture", {}).get(kname)
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
@@ -433,6 +435,8 @@ def main():
                 "alg_bytes_per_launch": alg_bytes, "kernel_ms": kms,
                 "path_alg_bytes": nsym + N + 30 * n + 48 * H,
                 "path_frac": (nsym + N + 30 * n + 48 * H) / 1e9 / (dev_ms / 1e3) / peak}
+    if traffic is not None and traffic_capture:
+        roofline["traffic_capture"] = traffic_capture
 
     # ---- e2e: host buffers through cmsbwt_run (H2D text + D2H BWT inside the timed region)
     e2e = None
