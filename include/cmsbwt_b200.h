@@ -229,7 +229,9 @@ int cmsbwt_shard_rle(cmsbwt_ctx *ctx, uint64_t *n_records);
  * (order of the k-mer table, 0 = largest k <= 14 with 4^k <= n; takes effect at the next
  * index_upload), "fast" (0: 8-bit warp kernel for every input), "tile_budget" (0: sort-based sweep
  * instead of the tile kernels), "slots", "skip_min", "ms_occ", "scatter_mb", "nb_t1/4/8",
- * "ms_variant" (measurement switches).  Results never depend on them. */
+ * "ms_variant" (measurement switches; ms_variant bits: 2 text word cache, 8 G
+ * prefetch, 16 empty k-mer buckets resolved from their slot; default 26).  Results never depend on
+ * them. */
 int cmsbwt_set_param(cmsbwt_ctx *ctx, const char *name, int64_t value);
 
 #ifdef __cplusplus
