@@ -98,12 +98,105 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_info():
+    model = "unknown"
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+    except Exception:
+        pass
+    try:
+        allowed = sorted(os.sched_getaffinity(0))
+    except Exception:
+        allowed = list(range(os.cpu_count() or 1))
+    return {"cpu_model": model, "cores_total": os.cpu_count(), "cores_allowed": len(allowed)}, allowed
+
+
+def _elapsed_ms(stdout):
+    for line in stdout.splitlines():
+        if line.startswith("==== Time elapsed:"):
+            return float(line.split(":")[1].split()[0])
+    return None
+
+
+def _log_ms(path, key):
+    try:
+        for line in open(path):
+            if line.startswith(key):
+                return float(line[len(key):].split()[0])
+    except Exception:
+        pass
+    return None
+
+
+def run_reference_cli(list_file, out_prefix, cpu=None):
+    """one run of the unmodified reference binary, pinned to one core; -> dict of its own timers"""
+    exe = os.path.join(ROOT, "oracle", "_ref", "cmsbwt")
+    cmd = [exe, "-o", out_prefix, list_file]
+    if cpu is not None:
+        cmd = ["taskset", "-c", str(cpu)] + cmd
+    t = time.time()
+    r = subprocess.run(cmd, check=True, stdout=subprocess.PIPE, text=True)
+    wall = (time.time() - t) * 1e3
+    el = _elapsed_ms(r.stdout) or wall
+    pre = _log_ms(out_prefix + ".log", "Preprocessing done in") or 0.0
+    return {"elapsed_ms": el, "wall_ms": wall, "preprocessing_ms": pre, "path_ms": el - pre}
+
+
+def same_work(div):
+    """CLI against CLI on the SAME files (BASELINE config 2 whole: 5 Mbp reference + 100 copies, plain
+    BWT): the unmodified reference binary once on one pinned host core, cms_bwt_b200/cms_bwt three
+    times (best).  Both numbers are the programs' own `==== Time elapsed` (main.cpp:126): file parsing,
+    index build, the path and the output file included.  -> (same_work dict, cpu_baseline dict)"""
+    import genpin
+    exe_ref = os.path.join(ROOT, "oracle", "_ref", "cmsbwt")
+    exe_b200 = os.path.join(ROOT, "cms_bwt_b200", "cms_bwt")
+    if not (os.path.exists(exe_ref) and os.path.exists(exe_b200)):
+        return None, None
+    info, allowed = host_info()
+    cpu = allowed[-1] if allowed else None
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    wd = tempfile.mkdtemp(prefix="cmssame", dir=base)
+    g = dict(ref_bp=5_000_000, copies=100, div=div, seed=11, svs=0)
+    pre = os.path.join(wd, "c2")
+    genpin.write_files(g["ref_bp"], g["copies"], g["div"], g["seed"], g["svs"], pre)
+    nsym = None
+    try:
+        ref = run_reference_cli(pre + ".txt", pre + ".ref_out", cpu)
+        N = os.path.getsize(pre + ".ref_out.bwt")
+        nsym = N - (g["copies"] + 1)
+        ours = []
+        for _ in range(3):
+            r = subprocess.run([exe_b200, "-o", pre + ".b200_out", pre + ".txt"], check=True, stdout=subprocess.PIPE,
+                               text=True)
+            ours.append({"elapsed_ms": _elapsed_ms(r.stdout),
+                         "context_ms": _log_ms(pre + ".b200_out.log", "Device context created in"),
+                         "path_ms": _log_ms(pre + ".b200_out.log", "Path (MS + head sort + emit + copies) wall:")})
+        same = subprocess.run(["cmp", "-s", pre + ".ref_out.bwt", pre + ".b200_out.bwt"]).returncode == 0
+        best = min(ours, key=lambda o: o["elapsed_ms"])
+        desc = "config2 whole: %d bp reference + %d copies at %g (%.1f Mbp), plain BWT, files in %s" % (
+            g["ref_bp"], g["copies"], g["div"], nsym / 1e6, base or "tmp")
+        sw = {"same_config": True, "workload": desc, "what": "program wall time, `==== Time elapsed` of both CLIs on the same files",
+              "reference_ms": ref["elapsed_ms"], "reference_path_ms": ref["path_ms"], "reference_runs": 1,
+              "b200_ms": best["elapsed_ms"], "b200_context_ms": best["context_ms"], "b200_path_ms": best["path_ms"],
+              "b200_runs": len(ours), "ratio": ref["elapsed_ms"] / best["elapsed_ms"], "identical_bytes": same,
+              "host": info, "reference_pinned_to_cpu": cpu}
+        cb = {"value": nsym / 1e9 / (ref["elapsed_ms"] / 1e3), "unit": "Gbp/s", "cores": 1, "kind": "reference",
+              "sample": desc + "; whole program incl. index build and file I/O, %.1f s; without its preprocessing: %.4f Gbp/s"
+                        % (ref["elapsed_ms"] / 1e3, nsym / 1e9 / (ref["path_ms"] / 1e3)),
+              "host": info, "pinned_to_cpu": cpu}
+        return sw, cb
+    finally:
+        import shutil
+        shutil.rmtree(wd, ignore_errors=True)
+
+
 def reference_arm(args, rank):
     """The reference's own CPU implementation on a bounded sample of the workload."""
     if rank != 0:
         return
-    import numpy as np
-    import gen_synth
     exe = os.path.join(ROOT, "oracle", "_ref", "cmsbwt")
     # bounded sample: about 1 s of index build + 0.4 s per 5 Mbp copy on one core; the whole
     # --steps/--warmup run is kept under ~150 s
@@ -113,51 +206,38 @@ def reference_arm(args, rank):
     if not os.path.exists(exe):
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/cmsbwt not built"}))
         return
-    wd = tempfile.mkdtemp(prefix="cmsref")
-    ref, copies = gen_synth.make_collection(sample["ref_bp"], sample["copies"], sample["div"],
-                                            sample["seed"])
-    gen_synth.write_files(os.path.join(wd, "s"), ref, copies)
-    nsym = int(sum(len(c) for c in copies))
-    times = []
+    import genpin
+    wd = tempfile.mkdtemp(prefix="cmsref", dir="/dev/shm" if os.access("/dev/shm", os.W_OK) else None)
+    genpin.write_files(sample["ref_bp"], sample["copies"], sample["div"], sample["seed"], 0, os.path.join(wd, "s"))
+    _, _, Ns, nds = genpin.make_text(sample["ref_bp"], sample["copies"], sample["div"], sample["seed"], 0)
+    nsym = int(Ns - nds)
+    info, allowed = host_info()
+    cpu = allowed[-1] if allowed else None
+    times, paths = [], []
     for it in range(args.warmup + args.steps):
-        t = time.time()
-        subprocess.run([exe, "-o", os.path.join(wd, "out"), os.path.join(wd, "s.txt")], check=True,
-                       stdout=subprocess.DEVNULL)
+        r = run_reference_cli(os.path.join(wd, "s.txt"), os.path.join(wd, "out"), cpu)
         if it >= args.warmup:
-            times.append(time.time() - t)
+            times.append(r["wall_ms"] / 1e3)
+            paths.append(r["path_ms"] / 1e3)
     dt = sum(times) / len(times)
-    val = nsym / 1e9 / dt
-    desc = "%d bp reference + %d copies at %g (%.1f Mbp), whole reference program incl. its index build and file I/O" % (
-        sample["ref_bp"], sample["copies"], sample["div"], nsym / 1e6)
+    dp = sum(paths) / len(paths)
+    # `value` = the path alone (the program's elapsed time minus its own "Preprocessing done in": the
+    # MS, head-sort and writer stages with the file parsing and writing they contain), the same scope
+    # as the B200 arm's `value`; `e2e` = the whole program (index build included)
+    val, val_e2e = nsym / 1e9 / dp, nsym / 1e9 / dt
+    desc = ("bounded sample of %s: %d bp reference + %d copies at %g (%.1f Mbp), unmodified reference binary on one "
+            "pinned core; value = without its preprocessing (index build), e2e = whole program" % (
+                args.workload, sample["ref_bp"], sample["copies"], sample["div"], nsym / 1e6))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "Gbp/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dp * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8",
-        "data": "synthetic", "config": {"workload": args.workload, "sample": desc},
+        "data": "synthetic", "config": {"workload": args.workload, "sample": desc, "host": info,
+                                        "pinned_to_cpu": cpu, "program_ms_per_step": dt * 1e3},
         "cpu_baseline": {"value": val, "unit": "Gbp/s", "cores": 1, "kind": "reference",
                          "sample": desc},
-        "e2e": {"value": val, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "e2e": {"value": val_e2e, "unit": "Gbp/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
-
-
-def cpu_baseline(div):
-    """Reference binary, 1 thread, bounded sample (about 10-20 s of CPU work)."""
-    import gen_synth
-    exe = os.path.join(ROOT, "oracle", "_ref", "cmsbwt")
-    if not os.path.exists(exe):
-        return None
-    wd = tempfile.mkdtemp(prefix="cmsref")
-    ref_bp, copies_n = 5_000_000, 30
-    ref, copies = gen_synth.make_collection(ref_bp, copies_n, div, 13)
-    gen_synth.write_files(os.path.join(wd, "s"), ref, copies)
-    nsym = int(sum(len(c) for c in copies))
-    t = time.time()
-    subprocess.run([exe, "-o", os.path.join(wd, "out"), os.path.join(wd, "s.txt")], check=True,
-                   stdout=subprocess.DEVNULL)
-    dt = time.time() - t
-    return {"value": nsym / 1e9 / dt, "unit": "Gbp/s", "cores": 1, "kind": "reference",
-            "sample": "%d bp reference + %d copies at %g (%.1f Mbp), end to end incl. index build and file I/O, %.1f s"
-                      % (ref_bp, copies_n, div, nsym / 1e6, dt)}
 
 
 def run_multi(args, rank, world, local, dev, dist):
@@ -389,6 +469,7 @@ def main():
     if profiling:
         torch.cuda.profiler.start()
     stage = {"ms_ms": 0.0, "sort_ms": 0.0, "emit_ms": 0.0, "ms_kernel_ms": 0.0, "pack_ms": 0.0}
+    groups = {g: 0.0 for g in P.Stats.GROUPS}
     launches = 0
     t0 = time.time()
     e0.record()
@@ -397,6 +478,8 @@ def main():
         s = ctx.stats()
         for k in stage:
             stage[k] += s[k]
+        for g in groups:
+            groups[g] += s["group_ms"][g]
         launches += s["kernel_launches"]
     e1.record()
     torch.cuda.synchronize()
@@ -413,29 +496,50 @@ def main():
     H = s["n_heads"]
     n = len(x)
 
-    # ---- roofline of the dominant kernel (the matching-statistics kernel): algorithmic bytes =
-    # every collection symbol read once (1 B as parsed) + one 16-byte head record
-    # written per head, DESIGN.md section 6.  `traffic` is the DRAM read+write of one launch from
-    # the committed ncu --set full capture (profiles/), same workload.
+    # ---- roofline: algorithmic bytes of the path = N_sym (every collection symbol read
+    # once) + N (every BWT byte written once) + 30 n (index arrays read once, bucket counts written and
+    # read) + 48 H (one 24-byte head record written once and read once), split by stage; time = the
+    # CUDA-event time of the stage's kernel groups on the library's stream (stats.group_ms, live in
+    # this run).  `roofline` describes the dominant stage (largest share of the step); `traffic` is
+    # the DRAM read+write of its kernels per launch from the committed ncu --set full capture of the
+    # same command (profiles/traffic.json, made by tools/ncu_traffic.py).
     peak, peak_kind = measured_peak()
-    kms = stage["ms_kernel_ms"] / args.steps
-    alg_bytes = N + 16 * H
-    achieved = alg_bytes / 1e9 / (kms / 1e3)
-    kname = "k_ms_fast" if s.get("fast_path") else "k_ms"
-    traffic, traffic_capture = None, None
+    grp = {k: v / args.steps for k, v in groups.items()}
+    stage_groups = {"stage1_ms": ("pack", "ms", "gather"), "stage2_head_order": ("rank", "tiles", "place"),
+                    "stage3_emit": ("offsets", "fill", "rle")}
+    stage_alg = {"stage1_ms": nsym, "stage2_head_order": 48 * H, "stage3_emit": N + 30 * n}
+    stage_kernels = {"stage1_ms": "k_pack + k_ms_fast + k_msf_gather" if s.get("fast_path") else "k_ms + k_compact",
+                     "stage2_head_order": "k_link, k_tail_label, tail radix sort + refinement, k_tile_hist/scatter/cov, k_tile_place",
+                     "stage3_emit": "k_cnt_sa, offsets scan, k_fill_part, k_fill"}
+    traffic_tab, traffic_capture = {}, None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             tj = json.load(f)
-        traffic = tj.get(args.workload, {}).get(kname)
-        traffic_capture = tj.get("_capture", {}).get(kname)
+        traffic_tab = tj.get(args.workload, {})
+        traffic_capture = tj.get("_capture")
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak,
-                "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "alg_bytes_per_launch": alg_bytes, "kernel_ms": kms,
-                "path_alg_bytes": nsym + N + 30 * n + 48 * H,
-                "path_frac": (nsym + N + 30 * n + 48 * H) / 1e9 / (dev_ms / 1e3) / peak}
-    if traffic is not None and traffic_capture:
+    stages = {}
+    for name, gs in stage_groups.items():
+        ms = sum(grp[g] for g in gs)
+        tr = [traffic_tab.get(g) for g in gs if traffic_tab.get(g) is not None]
+        stages[name] = {"alg_bytes": int(stage_alg[name]), "ms": ms, "GBps": stage_alg[name] / 1e9 / (ms / 1e3) if ms else None,
+                        "frac": stage_alg[name] / 1e9 / (ms / 1e3) / peak if ms else None,
+                        "groups_ms": {g: grp[g] for g in gs}, "traffic": int(sum(tr)) if tr else None}
+    dom = max(stages, key=lambda k: stages[k]["ms"])
+    path_alg = nsym + N + 30 * n + 48 * H
+    roofline = {"bound": "hbm", "kernel": "%s (%s)" % (dom, stage_kernels[dom]),
+                "achieved": stages[dom]["GBps"], "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
+                "frac": stages[dom]["frac"], "traffic": stages[dom]["traffic"],
+                "alg_bytes_per_launch": stages[dom]["alg_bytes"], "kernel_ms": stages[dom]["ms"],
+                "share_of_step": stages[dom]["ms"] / dev_ms,
+                "stages": stages, "path_alg_bytes": int(path_alg),
+                "path_frac": path_alg / 1e9 / (dev_ms / 1e3) / peak,
+                "path_frac_of_8TBps_nominal": path_alg / 1e9 / (dev_ms / 1e3) / 8000.0,
+                "ms_kernel": {"name": "k_ms_fast" if s.get("fast_path") else "k_ms", "ms": grp["ms"],
+                              "alg_bytes": int(N // 4 + 16 * H),
+                              "note": "its own inputs/outputs: the 2-bit text (N/4) + one 16-byte record per head"}}
+    if traffic_capture:
         roofline["traffic_capture"] = traffic_capture
 
     # ---- e2e: host buffers through cmsbwt_run (H2D text + D2H BWT inside the timed region)
@@ -456,7 +560,8 @@ def main():
                "d2h_bytes_per_step": int(N), "ms_per_step": dt * 1e3}
         # cheap self-check: same bytes as the device-resident run
         chk = torch.from_numpy(ho[:1 << 20]).to(dev)
-    cb = None if args.no_cpu_baseline else cpu_baseline(w["div"])
+    ctx.close()
+    sw, cb = (None, None) if args.no_cpu_baseline else same_work(w["div"])
     line = {
         "metric": METRIC, "value": value, "unit": "Gbp/s", "n_gpus": 1, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -470,10 +575,9 @@ def main():
                    "stage_ms": {k: v / args.steps for k, v in stage.items()},
                    "index_ms": {"sa_build_gpu": st0["sa_build_ms"], "index_build": st0["index_build_ms"]}},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-        "cpu_baseline": cb,
+        "cpu_baseline": cb, "same_work": sw,
     }
     print(json.dumps(line))
-    ctx.close()
 
 
 if __name__ == "__main__":

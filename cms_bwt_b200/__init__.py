@@ -21,6 +21,7 @@ EXPORTS = [
     "cmsbwt_ctx_create", "cmsbwt_ctx_destroy", "cmsbwt_last_error", "cmsbwt_get_stats",
     "cmsbwt_augment", "cmsbwt_read_reference", "cmsbwt_parse_collection", "cmsbwt_build_sa",
     "cmsbwt_index_upload", "cmsbwt_index_download", "cmsbwt_ms_run", "cmsbwt_ms_run_device",
+    "cmsbwt_ms_run_device_ordered",
     "cmsbwt_set_ms_dump", "cmsbwt_ms_download", "cmsbwt_heads_sort", "cmsbwt_heads_download",
     "cmsbwt_emit", "cmsbwt_result_device", "cmsbwt_result_download", "cmsbwt_run",
     "cmsbwt_set_param",
@@ -42,10 +43,14 @@ class Stats(C.Structure):
                 ("rank_rounds", C.c_uint32), ("kmer_k", C.c_uint32),
                 ("kernel_launches", C.c_uint64), ("pack_ms", C.c_double),
                 ("fast_path", C.c_uint32), ("light_tiles", C.c_uint32), ("pair_tests", C.c_uint64),
-                ("rank_tied", C.c_uint64)]
+                ("rank_tied", C.c_uint64), ("group_ms", C.c_double * 12)]
+
+    GROUPS = ("pack", "ms", "gather", "rank", "tiles", "offsets", "fill", "place", "rle")
 
     def asdict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_}
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "group_ms"}
+        d["group_ms"] = {n: self.group_ms[i] for i, n in enumerate(self.GROUPS)}
+        return d
 
 
 class CmsBwtError(RuntimeError):
@@ -83,6 +88,7 @@ def lib():
         L.cmsbwt_index_download.argtypes = [vp, vp, vp, vp, vp]
         L.cmsbwt_ms_run.argtypes = [vp, vp, u64]
         L.cmsbwt_ms_run_device.argtypes = [vp, vp, u64]
+        L.cmsbwt_ms_run_device_ordered.argtypes = [vp, vp, u64, vp]
         L.cmsbwt_set_ms_dump.argtypes = [vp, C.c_int]
         L.cmsbwt_ms_download.argtypes = [vp, vp, vp, vp, vp]
         L.cmsbwt_heads_sort.argtypes = [vp]
@@ -245,6 +251,12 @@ class Context:
     def ms_run_device(self, dptr, N):
         self.N = int(N)
         self._ck(lib().cmsbwt_ms_run_device(self.h, C.c_void_p(int(dptr)), int(N)))
+
+    def ms_run_device_ordered(self, dptr, N, producer_stream):
+        """producer_stream: raw cudaStream_t (int; 0 = legacy default stream) the text was written on"""
+        self.N = int(N)
+        self._ck(lib().cmsbwt_ms_run_device_ordered(self.h, C.c_void_p(int(dptr)), int(N),
+                                                    C.c_void_p(int(producer_stream))))
 
     def ms_download(self):
         N = self.N

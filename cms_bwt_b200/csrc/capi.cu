@@ -7,6 +7,37 @@
 static thread_local DevCache *tl_cache = nullptr;
 DevCache *&current_cache() { return tl_cache; }
 
+static cudaEvent_t ev_get(cmsbwt_ctx *c) {
+  if (!c->ev_pool.empty()) { cudaEvent_t e = c->ev_pool.back(); c->ev_pool.pop_back(); return e; }
+  cudaEvent_t e;
+  CK(cudaEventCreate(&e));
+  return e;
+}
+GroupSpan::GroupSpan(cmsbwt_ctx *c_, int id_) : c(c_), id(id_) {
+  cudaEvent_t a = ev_get(c), b = ev_get(c);
+  cudaEventRecord(a, c->st);
+  c->spans.push_back({id, {a, b}});
+}
+GroupSpan::~GroupSpan() {
+  for (size_t k = c->spans.size(); k-- > 0;)
+    if (c->spans[k].first == id) { cudaEventRecord(c->spans[k].second.second, c->st); break; }
+}
+void group_reset(cmsbwt_ctx *c) {
+  for (auto &sp : c->spans) { c->ev_pool.push_back(sp.second.first); c->ev_pool.push_back(sp.second.second); }
+  c->spans.clear();
+  for (double &g : c->stats.group_ms) g = 0;
+}
+// the stream must be synchronised
+void group_collect(cmsbwt_ctx *c) {
+  for (auto &sp : c->spans) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, sp.second.first, sp.second.second) == cudaSuccess) c->stats.group_ms[sp.first] += ms;
+    else cudaGetLastError();
+    c->ev_pool.push_back(sp.second.first); c->ev_pool.push_back(sp.second.second);
+  }
+  c->spans.clear();
+}
+
 static int fail(cmsbwt_ctx *c, int code, const std::string &msg) {
   if (c) c->err = msg;
   return code;
@@ -67,6 +98,9 @@ void cmsbwt_ctx_destroy(cmsbwt_ctx *c) {
     if (c->ev_in1) cudaEventDestroy(c->ev_in1);
     cudaStreamDestroy(c->st_copy);
   }
+  group_reset(c);
+  for (auto e : c->ev_pool) cudaEventDestroy(e);
+  c->ev_pool.clear();
   delete c;                                 // DBufs go back to the context's cache, which frees them
   tl_cache = nullptr;
   cudaStreamDestroy(st);
@@ -284,9 +318,11 @@ static int ms_common(cmsbwt_ctx *c) {
   if (last != 2) throw CmsErr{CMSBWT_E_ARG, "text must end with the 0x02 document separator"};
   c->have_ms = c->have_sort = false;
   c->launches = 0;
+  group_reset(c);
   Timer t(c->st);
   ms_stage(c);
   c->stats.ms_ms = t.stop();
+  group_collect(c);
   c->have_ms = true;
   GUARD_END(c)
   return CMSBWT_OK;
@@ -309,17 +345,46 @@ int cmsbwt_ms_run(cmsbwt_ctx *c, const uint8_t *text, uint64_t N) {
   return ms_common(c);
 }
 
-int cmsbwt_ms_run_device(cmsbwt_ctx *c, const void *d_text, uint64_t N) {
+// Stream ordering of caller-produced device buffers.  All work of a context runs on its own
+// non-blocking stream, which is NOT ordered against the caller's streams (not even the legacy default
+// stream).  Every entry point that takes a device pointer therefore orders itself after the producer:
+// the plain forms synchronise the whole device first (everything launched on this device before the
+// call, on any stream, has completed when the library starts to read); cmsbwt_ms_run_device_ordered
+// instead makes the library's stream wait for an event recorded on the producer's stream -- no host
+// synchronisation.
+static void order_after_device(cmsbwt_ctx *c) { CK(cudaDeviceSynchronize()); }
+
+static int ms_run_device_common(cmsbwt_ctx *c, const void *d_text, uint64_t N, bool ordered, void *producer) {
   if (!c || !c->have_index) return fail(c, CMSBWT_E_ARG, "index_upload first");
   if (!d_text || N == 0 || ((uintptr_t)d_text & 15)) return fail(c, CMSBWT_E_ARG, "bad device text");
-  cudaSetDevice(c->dev);
+  GUARD_BEGIN
+  CK(cudaSetDevice(c->dev));
   tl_cache = &c->cache;
+  if (ordered) {
+    cudaEvent_t ev;
+    CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    cudaError_t e = cudaEventRecord(ev, (cudaStream_t)producer);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(c->st, ev, 0);
+    cudaEventDestroy(ev);                      // released once the wait has been satisfied
+    if (e != cudaSuccess) throw CudaErr{e, "ordering against the producer stream"};
+  } else {
+    order_after_device(c);
+  }
   c->d_text.release();
   c->staging = false;
   c->text = (const u8 *)d_text;
   c->N = N;
   c->stats.h2d_ms = 0;
+  GUARD_END(c)
   return ms_common(c);
+}
+
+int cmsbwt_ms_run_device(cmsbwt_ctx *c, const void *d_text, uint64_t N) {
+  return ms_run_device_common(c, d_text, N, false, nullptr);
+}
+
+int cmsbwt_ms_run_device_ordered(cmsbwt_ctx *c, const void *d_text, uint64_t N, void *producer_stream) {
+  return ms_run_device_common(c, d_text, N, true, producer_stream);
 }
 
 int cmsbwt_set_ms_dump(cmsbwt_ctx *c, int enable) {
@@ -349,6 +414,7 @@ int cmsbwt_heads_sort(cmsbwt_ctx *c) {
   Timer t(c->st);
   sort_stage(c);
   c->stats.sort_ms = t.stop();
+  group_collect(c);
   c->have_sort = true;
   GUARD_END(c)
   return CMSBWT_OK;
@@ -392,6 +458,7 @@ int cmsbwt_emit(cmsbwt_ctx *c, int mode, uint64_t *out_bytes) {
   Timer t(c->st);
   emit_stage(c, mode);
   c->stats.emit_ms = t.stop();
+  group_collect(c);
   c->have_sort = false;            // coverage deltas were consumed
   if (out_bytes) *out_bytes = c->out_bytes;
   GUARD_END(c)
@@ -618,6 +685,7 @@ int cmsbwt_shard_rank_owner(cmsbwt_ctx *c, const void *d_keys, const void *d_cls
   if (!c || (M && (!d_keys || !d_cls || !d_rank_out || !d_tie_out))) return fail(c, CMSBWT_E_ARG, "rank_owner");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  order_after_device(c);
   shard_rank_owner(c, (const u32 *)d_keys, (const u32 *)d_cls, M, rank_base, (u32 *)d_rank_out, (u8 *)d_tie_out);
   GUARD_END(c)
   return CMSBWT_OK;
@@ -627,6 +695,7 @@ int cmsbwt_shard_rank_apply(cmsbwt_ctx *c, const void *d_rank_sorted, const void
   if (!c || !c->sh_perm.p) return fail(c, CMSBWT_E_ARG, "shard_tails first");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  order_after_device(c);
   u32 m = shard_rank_apply(c, (const u32 *)d_rank_sorted, (const u8 *)d_tie_sorted);
   if (m_tied) *m_tied = m;
   GUARD_END(c)
@@ -648,6 +717,7 @@ int cmsbwt_shard_tie_refine(cmsbwt_ctx *c, const void *d_allkeys, uint32_t m_tot
   if (!c || !c->sh_sub.p) return fail(c, CMSBWT_E_ARG, "shard_rank_apply first");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  order_after_device(c);
   u32 m = shard_tie_refine(c, (const u64 *)d_allkeys, m_total, my_off);
   if (m_tied) *m_tied = m;
   GUARD_END(c)
@@ -674,6 +744,7 @@ int cmsbwt_shard_tiles_merge(cmsbwt_ctx *c, uint32_t world, uint32_t rank, const
     return fail(c, CMSBWT_E_ARG, "tiles_merge");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  order_after_device(c);
   Timer t(c->st);
   u32 me = shard_tiles_merge(c, world, rank, d_he, d_re, (const u32 *)d_hoffs, (const u32 *)d_roffs, he_slab,
                              re_slab, ndocs_total);
@@ -689,6 +760,7 @@ int cmsbwt_shard_emit(cmsbwt_ctx *c, const void *d_cov_full, uint64_t N_total, u
     return fail(c, CMSBWT_E_ARG, "shard_emit");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  order_after_device(c);
   Timer t(c->st);
   shard_emit(c, (const u32 *)d_cov_full, N_total, world, rank, doc_base);
   c->stats.emit_ms = t.stop();
@@ -715,6 +787,7 @@ int cmsbwt_shard_apply(cmsbwt_ctx *c, const void *d_plc, uint64_t count) {
   if (!c || !c->sh_base.p || (count && !d_plc)) return fail(c, CMSBWT_E_ARG, "shard_emit first");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
+  order_after_device(c);
   Timer t(c->st);
   shard_apply(c, (const u64 *)d_plc, count);
   c->stats.emit_ms += t.stop();

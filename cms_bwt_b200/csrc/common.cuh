@@ -168,6 +168,9 @@ struct cmsbwt_ctx {
   DBuf d_out, d_rle;
   u64 out_bytes = 0;
   int out_mode = 0;
+  // kernel-group timers: pairs of events per span, collected after the stage
+  std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> spans;
+  std::vector<cudaEvent_t> ev_pool;
   // params
   i64 chunk_len = 0;         // text window per lane; 0 = by text length (ms_fast.cu), 8192 in k_ms
   i64 pool_div = 6;          // initial head-pool capacity = N / pool_div records
@@ -183,6 +186,17 @@ struct cmsbwt_ctx {
 };
 
 #define LAUNCH(ctx) ((ctx)->launches++)
+
+// Kernel-group timers (stats.group_ms): events on the context's stream around a group of launches;
+// read back by group_collect() once the stage has synchronised.  A group may be opened several
+// times per job (its spans add up).
+struct GroupSpan {
+  cmsbwt_ctx *c; int id;
+  GroupSpan(cmsbwt_ctx *c_, int id_);
+  ~GroupSpan();
+};
+void group_reset(cmsbwt_ctx *c);
+void group_collect(cmsbwt_ctx *c);
 
 // stage entry points (each throws CudaErr / CmsErr)
 void sa_build_device(cmsbwt_ctx *c, const u8 *d_x, u32 n, i32 *d_sa);

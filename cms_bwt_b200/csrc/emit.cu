@@ -213,6 +213,7 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   DBuf cnt, base, tmp, bstart;
   cnt.alloc(((size_t)n + 1) * 4, st);
   base.alloc(((size_t)n + 2) * 8, st);
+  GroupSpan *goff = new GroupSpan(c, CMSBWT_G_OFFSETS);
   size_t tb = 0, tb2 = 0;
   cub::DeviceScan::InclusiveSum(nullptr, tb, c->d_cov.as<i32>(), c->d_cov.as<i32>(), (int)n, st);
   EXSUM64(nullptr, tb2, cnt.as<u32>(), base.as<u64>(), (int)(n + 1), st);
@@ -233,6 +234,7 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   bstart.alloc((nblocks + 1) * 4, st);
   k_fill_part<<<(u32)((nblocks + 1 + B - 1) / B), B, 0, st>>>(base.as<u64>(), n, N, nblocks, 0, bstart.as<u32>());
   LAUNCH(c);
+  delete goff;
   u64 total = 0;
   CK(cudaMemcpyAsync(&total, base.as<u64>() + n, 8, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
@@ -244,8 +246,10 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   }
   c->d_out.alloc(N + CMS_PAD, st);
   u8 *out = c->d_out.as<u8>();
-  k_fill<<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), c->ix.rbwt, bstart.as<u32>(), n, N, 0, out);
+  { GroupSpan g(c, CMSBWT_G_FILL);
+  k_fill<<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), c->ix.rbwt, bstart.as<u32>(), n, N, 0, out); }
   LAUNCH(c);
+  GroupSpan *gplace = new GroupSpan(c, CMSBWT_G_PLACE);
   if (c->light) {
     tiles_place_heads(c, base.as<u64>(), out);
   } else {
@@ -255,11 +259,12 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
                                                          base.as<u64>(), H, out, c->h_off.as<u64>());
     LAUNCH(c);
   }
+  delete gplace;
   CK(cudaGetLastError());
   c->out_mode = mode;
   c->out_bytes = N;
   c->stats.n_runs = 0;
-  if (mode == CMSBWT_MODE_RLE) rle_encode(c, out, N);
+  if (mode == CMSBWT_MODE_RLE) { GroupSpan g(c, CMSBWT_G_RLE); rle_encode(c, out, N); }
   CK(cudaStreamSynchronize(st));
 }
 

@@ -420,20 +420,27 @@ void sort_stage(cmsbwt_ctx *c) {
   const u32 *pos = c->h_pos.as<u32>();
   Tmp tmp;
   size_t tb;
-  sort_prepare(c, 0);
-  const u32 Tn = c->s_Tn;
-  tail_rank(c, c->s_label.as<u64>(), c->s_key32, c->s_tid, c->s_key_bits, c->s_next.as<u32>(), Tn,
-            c->s_trank.as<u32>());
-  sort_kappa(c);
+  u32 Tn;
+  {
+    GroupSpan g(c, CMSBWT_G_RANK);
+    sort_prepare(c, 0);
+    Tn = c->s_Tn;
+    tail_rank(c, c->s_label.as<u64>(), c->s_key32, c->s_tid, c->s_key_bits, c->s_next.as<u32>(), Tn,
+              c->s_trank.as<u32>());
+    sort_kappa(c);
+  }
   DBuf &kappa = c->s_kappa, &nitems = c->s_nitems, &sexcl = c->s_sexcl;
   // ---- brute-force tile path (tiles.cu) unless the collection is too deep for it ----
-  if (c->tile_budget > 0 && tiles_build(c, kappa.as<u64>(), sexcl)) {
+  bool light;
+  { GroupSpan g(c, CMSBWT_G_TILES); light = c->tile_budget > 0 && tiles_build(c, kappa.as<u64>(), sexcl); }
+  if (light) {
     c->stats.light_tiles = 1;
     c->s_kappa.release(); c->s_nitems.release(); c->s_tincl.release(); c->s_trank.release();
     CK(cudaStreamSynchronize(st));
     return;
   }
   // ---- sort-based sweep ----
+  GroupSpan gsweep(c, CMSBWT_G_PLACE);
   DBuf ioff;
   ioff.alloc((H + 1) * 8, st);
   tb = 0; EXSUM64(nullptr, tb, nitems.as<u32>(), ioff.as<u64>(), (int)(H + 1), st);

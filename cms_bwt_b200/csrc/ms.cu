@@ -355,11 +355,13 @@ void ms_stage(cmsbwt_ctx *c) {
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, st);
-    k_ms<<<grid, 128, 0, st>>>(P);
+    { GroupSpan g(c, CMSBWT_G_MS);
+    k_ms<<<grid, 128, 0, st>>>(P); }
     cudaEventRecord(e1, st);
     LAUNCH(c);
     CK(cudaGetLastError());
     // chunk_off = exclusive scan over nchunks+1 entries (ccnt has nchunks; the extra reads 0)
+    GroupSpan ggather(c, CMSBWT_G_GATHER);
     size_t t = tb;
     CK(EXSUM64(tmp.p, t, ccnt.as<u32>(), coff.as<u64>(), (int)nchunks, st));
     LAUNCH(c);

@@ -227,6 +227,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   cudaEvent_t e0, e1, e2;
   cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
   cudaEventRecord(e0, st);
+  GroupSpan *gpack = new GroupSpan(c, CMSBWT_G_PACK);
   for (int attempt = 0; attempt < 2; attempt++) {
     c->d_seps.alloc((sepcap + 1) * 8, st);
     CK(cudaMemsetAsync(flags.p, 0, 8, st));
@@ -236,7 +237,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     CK(cudaMemcpyAsync(&hsep, nsep.p, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hf, flags.p, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    if (hf[0]) { cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); return false; }
+    if (hf[0]) { delete gpack; cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); return false; }
     if (hsep <= sepcap) break;
     if (attempt == 1) throw CmsErr{CMSBWT_E_INTERNAL, "separator list overflow on exact-size rerun"};
     sepcap = hsep;
@@ -262,6 +263,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   woff.alloc((nwin + 1) * 8, st); counter.alloc(8, st); nbused.alloc(4, st);
   k_wsep<<<(u32)((nwin + 255) / 256), 256, 0, st>>>(c->d_seps.as<u64>(), nseps, WL, nwin, wsep.as<u32>());
   LAUNCH(c);
+  delete gpack;
   cudaEventRecord(e1, st);
   if (c->dump) {
     c->dump_pos.alloc(N * 4, st); c->dump_len.alloc(N * 4, st);
@@ -307,7 +309,8 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
       apw.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
       cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &apw);
     }
-    kern<<<grid, 128, MSF_SMEM_BYTES(128), st>>>(P);
+    { GroupSpan g(c, CMSBWT_G_MS);
+    kern<<<grid, 128, MSF_SMEM_BYTES(128), st>>>(P); }
     if (c->l2_pin && c->l2_persist_max) {
       apw.accessPolicyWindow.num_bytes = 0;
       cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &apw);
@@ -315,6 +318,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     cudaEventRecord(e2, st);
     LAUNCH(c);
     CK(cudaGetLastError());
+    GroupSpan ggather(c, CMSBWT_G_GATHER);
     k_msf_fix<<<(u32)((nwin + 255) / 256), 256, 0, st>>>(wcnt.as<u32>(), wfp.as<u32>(), wlp.as<u32>(), nwin, WL,
                                                         wadj.as<u32>(), c->dump ? c->dump_head.as<u8>() : nullptr);
     size_t t = tb;

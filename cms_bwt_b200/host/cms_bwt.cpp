@@ -20,11 +20,13 @@
 // its own thread, and the result comes back range by range into pinned slots that writer threads
 // pwrite() into the output file while the next range is copied (cmsbwt_result_read).
 //
-// Reference SA: north-star keeps it on the host with libsais.  libsais is a third-party library
-// that is not vendored in this repository; when a libsais shared object can be dlopen()ed
-// (CMSBWT_LIBSAIS=<path>, or libsais.so on the loader path, or oracle/_ref/libsais.so next to the
-// package) the SA is built with it (timed separately, "Computed SA in"); otherwise the SA is built
-// on the GPU by cmsbwt_build_sa.
+// Reference SA: north-star keeps it on the host with libsais (the reference's call at
+// CMS-BWT-functions.cpp:247).  libsais is a third-party dependency of the product: third_party/Makefile
+// compiles it into third_party/_build/libsais.a and this program links it statically
+// (CMSBWT_HAVE_LIBSAIS); a build without the archive, or --no-host-sa, builds the SA on the GPU with
+// cmsbwt_build_sa.  CMSBWT_LIBSAIS=<path of a libsais shared object> overrides the linked copy.  The
+// route taken is printed ("Computed SA in ... (libsais ...)" / "(GPU prefix doubling)").  No path
+// outside the files named on the command line (and CMSBWT_LIBSAIS) is ever opened by this program.
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
@@ -128,20 +130,24 @@ static bool read_file(const std::string &path, std::vector<uint8_t> &out) {
 }
 
 typedef int32_t (*libsais_fn)(const uint8_t *, int32_t *, int32_t, int32_t, int32_t *);
-static libsais_fn find_libsais(const char *argv0) {
-  std::vector<std::string> cands;
-  if (const char *e = getenv("CMSBWT_LIBSAIS")) cands.push_back(e);
-  cands.push_back("libsais.so");
-  std::string self(argv0);
-  size_t sl = self.find_last_of('/');
-  std::string dir = sl == std::string::npos ? "." : self.substr(0, sl);
-  cands.push_back(dir + "/../oracle/_ref/libsais.so");
-  for (auto &p : cands) {
-    void *h = dlopen(p.c_str(), RTLD_NOW | RTLD_LOCAL);
-    if (!h) continue;
-    if (void *s = dlsym(h, "libsais")) return (libsais_fn)s;
+#ifdef CMSBWT_HAVE_LIBSAIS
+extern "C" int32_t libsais(const uint8_t *T, int32_t *SA, int32_t n, int32_t fs, int32_t *freq);
+#endif
+static libsais_fn find_libsais(const char **route) {
+  if (const char *e = getenv("CMSBWT_LIBSAIS")) {          // explicit override, never a default path
+    void *h = dlopen(e, RTLD_NOW | RTLD_LOCAL);
+    if (h)
+      if (void *s = dlsym(h, "libsais")) { *route = "libsais, CMSBWT_LIBSAIS"; return (libsais_fn)s; }
+    fprintf(stderr, "Error: CMSBWT_LIBSAIS=%s is not a libsais shared object\n", e);
+    exit(1);
   }
+#ifdef CMSBWT_HAVE_LIBSAIS
+  *route = "libsais, linked";
+  return &libsais;
+#else
+  *route = "GPU prefix doubling";
   return nullptr;
+#endif
 }
 
 static double ms_since(std::chrono::high_resolution_clock::time_point t) {
@@ -375,7 +381,8 @@ int main(int argc, char **argv) {
 
   // ---- SA (:247) on its own host thread while the context comes up and the collection is parsed ----
   std::vector<int32_t> sa;
-  libsais_fn sais = arg.host_sa ? find_libsais(argv[0]) : nullptr;
+  const char *sa_route = "GPU prefix doubling";
+  libsais_fn sais = arg.host_sa ? find_libsais(&sa_route) : nullptr;
   auto ts = std::chrono::high_resolution_clock::now();
   double sa_ms = 0;
   int sa_rc = 0;
@@ -433,7 +440,7 @@ int main(int argc, char **argv) {
   if (sa_thread.joinable()) sa_thread.join();
   if (sais) {
     if (sa_rc != 0) { fprintf(stderr, "Error: libsais failed\n"); exit(1); }
-    log << "Computed SA in " << sa_ms << " ms (libsais, host" << (arg.stream ? ", beside the context creation and the ingest" : "") << ")" << std::endl;
+    log << "Computed SA in " << sa_ms << " ms (" << sa_route << ", host" << (arg.stream ? ", beside the context creation and the ingest" : "") << ")" << std::endl;
   }
   auto ti = std::chrono::high_resolution_clock::now();
   if (cmsbwt_index_upload(ctx, x.data(), (uint32_t)n, sais ? sa.data() : nullptr) != CMSBWT_OK) die("index_upload");

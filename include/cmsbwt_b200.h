@@ -20,7 +20,15 @@
  *   - host pointers unless the name says _device; device buffers passed in must be 16-byte
  *     aligned and have at least 64 readable bytes after their last element;
  *   - one context per GPU; calls on one context are serialised by the caller (the reference is
- *     single threaded); contexts on different GPUs may be driven from different host threads.
+ *     single threaded); contexts on different GPUs may be driven from different host threads;
+ *   - STREAM ORDERING: a context runs its kernels on its own non-blocking stream, which is ordered
+ *     against no stream of the caller (not even the legacy default stream).  Every function that
+ *     takes a device pointer produced by the caller (cmsbwt_ms_run_device and the cmsbwt_shard_*
+ *     calls with d_* arguments) first synchronises the whole device, so all work launched on the
+ *     device before the call -- on any stream -- has completed before the library reads the buffer;
+ *     cmsbwt_ms_run_device_ordered replaces that host synchronisation by an event wait on the
+ *     producer's stream.  Every function returns with the context's stream synchronised, so results
+ *     (cmsbwt_result_device, cmsbwt_shard_buffer) may be read from any stream afterwards.
  */
 #ifndef CMSBWT_B200_H
 #define CMSBWT_B200_H
@@ -68,7 +76,23 @@ typedef struct {
   uint32_t light_tiles;     /* 1 = the last heads_sort counted every tile by brute force */
   uint64_t pair_tests;      /* head x (range | position mate) tests of that brute-force pass */
   uint64_t rank_tied;       /* tails whose reference ISA rank is shared (refined after the radix sort) */
+  /* CUDA-event time of the kernel groups of the last job (single-GPU path), milliseconds; the sum is
+   * ms_ms + sort_ms + emit_ms minus host gaps.  Indices: CMSBWT_G_* below. */
+  double group_ms[12];
 } cmsbwt_stats;
+
+enum {
+  CMSBWT_G_PACK = 0,      /* 8-bit -> 2-bit text + separator list (k_pack, sort of separators)          */
+  CMSBWT_G_MS = 1,        /* the matching-statistics kernel (k_ms_fast / k_ms)                           */
+  CMSBWT_G_GATHER = 2,    /* head records -> text-order arrays (k_msf_fix, scan, k_msf_gather)           */
+  CMSBWT_G_RANK = 3,      /* linking, tail labels, radix sort + tie refinement, kappa (:1359-1494)       */
+  CMSBWT_G_TILES = 4,     /* tile filing + bucket sizes: histogram, scan, scatter, k_tile_cov (:1387-1416) */
+  CMSBWT_G_OFFSETS = 5,   /* bucket inversion to SA order + offsets (k_cnt_sa, scan, k_fill_part; :1618-1628) */
+  CMSBWT_G_FILL = 6,      /* run expansion of the reference symbols (k_fill; :1640-1688)                 */
+  CMSBWT_G_PLACE = 7,     /* counterSmallerThanHead + head symbols (k_tile_place / sweep; :1517-1603)    */
+  CMSBWT_G_RLE = 8,       /* 9-byte run records (:1695-1777)                                             */
+  CMSBWT_G_COUNT = 9
+};
 
 /* replaces: process start-up of the reference (no equivalent; it has no device). */
 int cmsbwt_ctx_create(int device_ordinal, cmsbwt_ctx **out);
@@ -122,8 +146,12 @@ int cmsbwt_index_download(cmsbwt_ctx *ctx, int32_t *sa, uint32_t *isa, uint32_t 
  * computeMSFactorAt :45-88, binarySearchLB/RB :94-149, the PLCP' skip loop :1176-1185 and the
  * head records of match.h:5-16.  Host text is copied to the device first. */
 int cmsbwt_ms_run(cmsbwt_ctx *ctx, const uint8_t *text, uint64_t N);
-/* same, text already resident in device memory (not copied, must stay valid until emit). */
+/* same, text already resident in device memory (not copied, must stay valid until emit).  The
+ * whole device is synchronised before d_text is read (see STREAM ORDERING above). */
 int cmsbwt_ms_run_device(cmsbwt_ctx *ctx, const void *d_text, uint64_t N);
+/* same without the device-wide synchronisation: the library's stream waits for everything enqueued
+ * so far on `producer_stream` (a cudaStream_t passed as void*; NULL = the legacy default stream). */
+int cmsbwt_ms_run_device_ordered(cmsbwt_ctx *ctx, const void *d_text, uint64_t N, void *producer_stream);
 /* parity hook: per-position matching statistics of the last ms_run, which
  * must have been preceded by cmsbwt_set_ms_dump(ctx, 1).  Arrays of N entries (may be NULL). */
 int cmsbwt_set_ms_dump(cmsbwt_ctx *ctx, int enable);

@@ -7,6 +7,8 @@ import numpy as np
 import pytest
 
 import oracle_lib as O
+
+HERE = os.path.dirname(os.path.abspath(__file__))
 import fuzz_cases
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
@@ -133,3 +135,47 @@ def test_oracle_matches_golden():
                                              int(z["prefix"]))
         assert np.array_equal(got, z["bwt"]), f
         assert np.array_equal(O.rle(got), z["rl_bwt"]), f
+
+
+# ---- full-size pins (tests/golden/fullsize_pins.json, made by tests/golden/make_pins.py) -------------
+def test_genpin_text_is_the_parse_of_its_fasta(tmp_path):
+    """tools/genpin.c: the text it hands to the GPU tests equals the reference's document list of the
+    FASTA files it writes for the reference binary; shards of copies concatenate to the whole."""
+    import genpin
+    import cms_bwt_b200 as P
+    pre = str(tmp_path / "gp")
+    genpin.write_files(20000, 5, 0.002, 3, 2, pre)
+    ref, t, N, nd = genpin.make_text(20000, 5, 0.002, 3, 2)
+    text, nd2 = P.parse_collection(open(pre + ".coll.fa", "rb").read())
+    assert nd == nd2 == 6 and np.array_equal(t[:N], text)
+    assert np.array_equal(ref, P.read_reference(open(pre + ".ref.fa", "rb").read()))
+    _, t0, N0, d0 = genpin.make_text(20000, 5, 0.002, 3, 2, first=0, count=2)
+    _, t1, N1, d1 = genpin.make_text(20000, 5, 0.002, 3, 2, first=2, count=3)
+    assert np.array_equal(np.concatenate([t0[:N0], t1[:N1]]), t[:N]) and d0 + d1 == nd
+
+
+def test_pins_cover_every_baseline_config():
+    import json
+    pins = json.load(open(os.path.join(HERE, "golden", "fullsize_pins.json")))
+    for name in ("config1", "config2", "config3", "config4_100", "config4_10", "config5_400", "config5_16"):
+        assert name in pins, name
+        p = pins[name]
+        assert len(p["bwt_md5"]) == 32 and len(p["rle_md5"]) == 32 and p["runs"] > 0 and p["N"] > 0
+
+
+def test_oracle_restatement_matches_the_config1_pin():
+    """the C restatement (oracle/cms_oracle.c) on the genpin config-1 collection gives the bytes whose
+    md5 the unmodified reference binary produced (pin) -- ties the oracle to the full-size pins"""
+    import hashlib
+    import json
+    import genpin
+    pins = json.load(open(os.path.join(HERE, "golden", "fullsize_pins.json")))
+    p = pins["config1"]
+    g = p["gen"]
+    ref, t, N, nd = genpin.make_text(g["ref_bp"], g["copies"], g["div"], g["seed"], g["svs"])
+    assert N == p["N"]
+    x = O.augment(ref)
+    bwt = O.Oracle(x).bwt(t[:N].copy())
+    assert hashlib.md5(bwt.tobytes()).hexdigest() == p["bwt_md5"]
+    rl = O.rle(bwt)
+    assert len(rl) == 9 * p["runs"] and hashlib.md5(rl.tobytes()).hexdigest() == p["rle_md5"]
