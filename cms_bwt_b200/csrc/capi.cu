@@ -471,7 +471,7 @@ const void *cmsbwt_result_device(const cmsbwt_ctx *c) {
 }
 
 int cmsbwt_result_download(cmsbwt_ctx *c, void *host_out, uint64_t cap) {
-  if (!c || !host_out || !c->d_out.p) return fail(c, CMSBWT_E_ARG, "emit first");
+  if (!c || !host_out || !cmsbwt_result_device(c)) return fail(c, CMSBWT_E_ARG, "emit first");
   if (cap < c->out_bytes) return fail(c, CMSBWT_E_ARG, "output buffer too small");
   GUARD_BEGIN
   CK(cudaSetDevice(c->dev)); tl_cache = &c->cache;
@@ -594,7 +594,7 @@ int cmsbwt_ms_run_staged(cmsbwt_ctx *c) {
 }
 
 int cmsbwt_result_read(cmsbwt_ctx *c, void *host_out, uint64_t offset, uint64_t bytes) {
-  if (!c || !host_out || !c->d_out.p) return fail(c, CMSBWT_E_ARG, "emit first");
+  if (!c || !host_out || !cmsbwt_result_device(c)) return fail(c, CMSBWT_E_ARG, "emit first");
   if (offset > c->out_bytes || bytes > c->out_bytes - offset) return fail(c, CMSBWT_E_ARG, "range past the result");
   if (bytes == 0) return CMSBWT_OK;
   GUARD_BEGIN

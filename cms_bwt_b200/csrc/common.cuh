@@ -153,6 +153,10 @@ struct cmsbwt_ctx {
   bool light = false;
   DBuf t_hoff, t_roff, t_he, t_re, h_sexcl;
   u32 tile_maxent = 0;
+  // pull emit (single GPU, light path): per position {bucket size, first head slot}; heads grouped by
+  // position as (within << 8 | symbol); terminator symbols in document order
+  DBuf d_pcov, d_hw, d_termsym;
+  u64 n_hw = 0;
   // stage 2 working set (kept in the context so that the multi-GPU shard calls can interleave
   // collectives between the phases)
   DBuf s_tincl, s_sexcl, s_label, s_next, s_tid, s_key32, s_trank, s_kappa, s_nitems;
@@ -231,6 +235,7 @@ u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const 
 void shard_emit(cmsbwt_ctx *c, const u32 *cov_full, u64 N_total, u32 world, u32 rank, u64 doc_base);
 void shard_apply(cmsbwt_ctx *c, const u64 *plc, u64 cnt);
 void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N);
+void tiles_count_heads(cmsbwt_ctx *c);
 void emit_stage(cmsbwt_ctx *c, int mode);
 
 // ---------------------------------------------------------------------------------------------

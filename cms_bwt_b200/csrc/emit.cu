@@ -3,6 +3,7 @@
 // with the head symbols stored at offset base[ISA[pos]] + within.
 #include "common.cuh"
 #include <cub/cub.cuh>
+#include <stdlib.h>
 
 __global__ void k_cnt_sa(const i32 *cov, const i32 *sa, u32 n, u32 *cnt) {
   u32 r = blockIdx.x * blockDim.x + threadIdx.x;
@@ -175,7 +176,6 @@ __global__ void k_rle_records(const u8 *out, const u64 *starts, u64 R, u64 N, u8
   d[8] = out[s];
 }
 
-void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out);
 
 // maximal-run records (9 bytes: LE u64 run, u8 symbol) of out[0, N) -> d_rle (:1695-1777)
 void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N) {
@@ -205,7 +205,345 @@ void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N) {
   CK(cudaStreamSynchronize(st));
 }
 
+// ================================================================================================
+// Pull emit (single GPU, tile path).  The output is walked in "virtual rank" order: v < nd is the
+// terminator of document v (the bucket of SA rank 0 holds exactly one suffix per document, in document
+// order: the writers' "first D-1 head chars", :1640-1643), v >= nd is SA rank r = v - nd + 1.  Per
+// virtual rank: cnt[v] = bucket size (:1618-1628 bucket inversion as a gather), vsym[v] = reference
+// BWT symbol, hl[v] = (first slot << 32 | number) of the bucket's heads in hw[] (tiles.cu).  The fill
+// kernel expands the runs of its 16 KB output block in SHARED memory, pulls the head symbols of the
+// buckets it intersects into it and stores the finished block with one bulk copy (TMA,
+// cp.async.bulk.global.shared::cta) -- every output sector is written exactly once and nothing is
+// scattered into the cold output (round 1: one sector read-modify-write per head symbol).
+__global__ void k_vrank(const uint2 *__restrict__ pcov, const i32 *__restrict__ sa, const u8 *__restrict__ rbwt,
+                        const u8 *__restrict__ termsym, u32 nd, u32 nv, u32 *__restrict__ cnt,
+                        u64 *__restrict__ hl, u8 *__restrict__ vsym) {
+  const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nv) return;
+  if (v < nd) { cnt[v] = 1; hl[v] = 0; vsym[v] = termsym[v]; return; }
+  const u32 r = v - nd + 1;
+  const u32 p = (u32)sa[r];
+  const uint2 a = __ldg(pcov + p), b = __ldg(pcov + p + 1);
+  cnt[v] = a.x;
+  hl[v] = ((u64)a.y << 32) | (u64)(b.y - a.y);
+  vsym[v] = rbwt[r];
+}
+
+#define PULL_SERIAL 24          // heads of one bucket a single thread pulls; longer lists go to a warp
+#define PULL_QCAP 128
+
+__device__ __forceinline__ void bulk_store_block(u8 *gdst, const u8 *s_src, u32 bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               :: "l"(gdst), "r"((u32)__cvta_generic_to_shared(s_src)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");    // smem may be reused / the CTA may exit
+}
+
+template <int STORE>      // 1 = bulk copy (TMA), 0 = 16-byte stores from shared memory
+__global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restrict__ base, const u8 *__restrict__ vsym,
+                                                            const u64 *__restrict__ hl, const u64 *__restrict__ hw,
+                                                            const u32 *__restrict__ bstart, u64 N, u8 *out) {
+  __shared__ u64 sb[FILL_SMEM_RUNS + 2];
+  __shared__ u8 ssym[FILL_SMEM_RUNS + 2];
+  __shared__ u32 s_m[FILL_VECS];
+  __shared__ __align__(128) u8 s_out[FILL_BYTES];
+  __shared__ u32 s_q[PULL_QCAP], s_qn;
+  typedef cub::BlockScan<u32, FILL_THREADS> BS;
+  __shared__ typename BS::TempStorage ts;
+  const u32 tid = threadIdx.x;
+  const u64 o0 = (u64)blockIdx.x * FILL_BYTES;
+  const u64 o1 = min(N, o0 + FILL_BYTES);
+  const u32 r0 = bstart[blockIdx.x], r1 = bstart[blockIdx.x + 1];
+  const u32 nr = r1 - r0 + 1;                 // runs r0..r1 intersect this block
+  const bool use_s = nr <= FILL_SMEM_RUNS;
+  if (tid == 0) s_qn = 0;
+  if (use_s) {
+    for (u32 k = tid; k <= nr; k += FILL_THREADS) { sb[k] = base[r0 + k]; ssym[k] = k < nr ? vsym[r0 + k] : 0; }
+    if (tid == 0) sb[nr + 1] = ~0ull;          // the last block runs one entry past base[nv] = N
+    for (u32 v = tid; v < FILL_VECS; v += FILL_THREADS) s_m[v] = 0;
+    __syncthreads();
+    for (u32 k = 1 + tid; k < nr; k += FILL_THREADS) {
+      u64 s = sb[k];
+      if (s >= o0 && s < o1) atomicMax(&s_m[(u32)(s - o0) >> 4], k);
+    }
+    __syncthreads();
+    u32 it[FILL_VEC_PER_THREAD];
+#pragma unroll
+    for (int v = 0; v < FILL_VEC_PER_THREAD; v++) it[v] = s_m[tid * FILL_VEC_PER_THREAD + v];
+    BS(ts).InclusiveScan(it, it, cub::Max());
+    __syncthreads();
+#pragma unroll
+    for (int v = 0; v < FILL_VEC_PER_THREAD; v++) s_m[tid * FILL_VEC_PER_THREAD + v] = it[v];
+    __syncthreads();
+  }
+#pragma unroll
+  for (int v = 0; v < FILL_VEC_PER_THREAD; v++) {
+    const u32 vi = (u32)v * FILL_THREADS + tid;
+    const u64 o = o0 + (u64)vi * 16;
+    if (o >= o1) break;
+    u32 k;
+    u64 lo, hi;
+    if (use_s) {
+      k = vi ? s_m[vi - 1] : 0;
+      while (sb[k + 1] <= o) k++;              // runs that start exactly here, empty runs
+      lo = hi = (u64)ssym[k] * 0x0101010101010101ull;
+      u64 nb = sb[k + 1];
+      while (nb < o + 16) {                    // a run starts inside this vector: overwrite its bytes
+        k++;
+        const u32 d = (u32)(nb - o);
+        const u64 sp = (u64)ssym[k] * 0x0101010101010101ull;
+        const u64 mlo = d < 8 ? ~0ull << (8 * d) : 0ull;
+        const u64 mhi = d < 8 ? ~0ull : ~0ull << (8 * (d - 8));
+        lo = (lo & ~mlo) | (sp & mlo);
+        hi = (hi & ~mhi) | (sp & mhi);
+        nb = sb[k + 1];
+      }
+    } else {
+      const u64 *bb = base + r0;
+      k = run_of(bb, 0, nr, o);
+      lo = hi = (u64)vsym[r0 + k] * 0x0101010101010101ull;
+      u64 nb = bb[k + 1];
+      while (nb < o + 16) {
+        k++;
+        const u32 d = (u32)(nb - o);
+        const u64 sp = (u64)vsym[r0 + k] * 0x0101010101010101ull;
+        const u64 mlo = d < 8 ? ~0ull << (8 * d) : 0ull;
+        const u64 mhi = d < 8 ? ~0ull : ~0ull << (8 * (d - 8));
+        lo = (lo & ~mlo) | (sp & mlo);
+        hi = (hi & ~mhi) | (sp & mhi);
+        nb = bb[k + 1];
+      }
+    }
+    *(uint4 *)(s_out + vi * 16) = make_uint4((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
+  }
+  __syncthreads();
+  // ---- pull the head symbols of the buckets that intersect this block (:1653-1676 as a gather) ----
+  for (u32 k = tid; k < nr; k += FILL_THREADS) {
+    const u64 h = __ldg(hl + r0 + k);
+    const u32 nh = (u32)h;
+    if (!nh) continue;
+    if (nh > PULL_SERIAL) {
+      const u32 q = atomicAdd(&s_qn, 1u);
+      if (q < PULL_QCAP) { s_q[q] = k; continue; }
+    }
+    const u64 b0 = use_s ? sb[k] : base[r0 + k];
+    const u64 *e = hw + (h >> 32);
+    for (u32 j = 0; j < nh; j++) {
+      const u64 x = __ldg(e + j);
+      const u64 off = b0 + (x >> 8);
+      if (off >= o1) break;                    // ascending within
+      if (off >= o0) s_out[off - o0] = (u8)x;
+    }
+  }
+  __syncthreads();
+  {
+    const u32 qn = min(s_qn, (u32)PULL_QCAP), lane = tid & 31;
+    for (u32 q = tid >> 5; q < qn; q += FILL_THREADS / 32) {
+      const u32 k = s_q[q];
+      const u64 h = __ldg(hl + r0 + k);
+      const u32 nh = (u32)h;
+      const u64 b0 = use_s ? sb[k] : base[r0 + k];
+      const u64 *e = hw + (h >> 32);
+      for (u32 j = lane; j < nh; j += 32) {
+        const u64 x = __ldg(e + j);
+        const u64 off = b0 + (x >> 8);
+        if (off >= o0 && off < o1) s_out[off - o0] = (u8)x;
+      }
+    }
+  }
+  // generic-proxy writes to shared memory must be visible to the async proxy before the bulk copy:
+  // every writer fences, then the barrier, then one thread issues the copy
+  if (STORE == 1) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncthreads();
+  const u32 bytes = (u32)(((o1 - o0) + 15) & ~15ull);          // out has CMS_PAD bytes of slack
+  if (STORE == 1) {
+    if (tid == 0) bulk_store_block(out + o0, s_out, bytes);
+  } else {
+    for (u32 vi = tid; vi * 16 < bytes; vi += FILL_THREADS) *(uint4 *)(out + o0 + (u64)vi * 16) = *(const uint4 *)(s_out + vi * 16);
+  }
+}
+
+// text-order offsets for the parity hook (cmsbwt_heads_download): off = base[virtual rank of pos] + within
+__global__ void k_head_offsets(const u32 *pos, const u32 *len, const u32 *within, const u32 *isa, const u64 *base,
+                               u32 nd, u64 H, u64 *off) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H) return;
+  off[i] = len[i] == 0 ? (u64)within[i] : base[nd + isa[pos[i]] - 1] + within[i];
+}
+
+// ---- run-length records without the plain BWT (:1695-1777 with the remainder
+// flush after the sub-bucket loop): the symbol sequence of bucket v is vsym[v] everywhere except at
+// the heads' offsets, so its runs follow from O(1 + heads) segments; runs are merged across buckets
+// through the last symbol before each bucket (a scan), and a record's length is the distance to the
+// next run start.  Nothing here is O(N).
+#define RLE_NONE 0xFFu
+__global__ void k_rled_last(const u32 *cnt, const u8 *vsym, const u64 *hl, const u64 *hw, u32 nv, u8 *lastsym) {
+  const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nv) return;
+  const u32 c = cnt[v];
+  u8 s = RLE_NONE;
+  if (c) {
+    s = vsym[v];
+    const u64 h = hl[v];
+    const u32 nh = (u32)h;
+    if (nh) { const u64 x = hw[(h >> 32) + nh - 1]; if ((u32)(x >> 8) == c - 1) s = (u8)x; }
+  }
+  lastsym[v] = s;
+}
+struct LastValid {
+  __device__ __forceinline__ u8 operator()(const u8 &a, const u8 &b) const { return b != RLE_NONE ? b : a; }
+};
+// walks the segments of bucket v; F(offset in the bucket, symbol) is called at every run start
+template <class F>
+__device__ __forceinline__ void rled_walk(u32 c, u8 vs, u64 h, const u64 *hw, u8 prev, F f) {
+  if (!c) return;
+  const u32 nh = (u32)h;
+  const u64 *e = hw + (h >> 32);
+  u32 at = 0;
+  for (u32 j = 0; j < nh; j++) {
+    const u64 x = __ldg(e + j);
+    const u32 w = (u32)(x >> 8);
+    const u8 s = (u8)x;
+    if (w > at) { if (vs != prev) f(at, vs); prev = vs; }
+    if (s != prev) f(w, s);
+    prev = s;
+    at = w + 1;
+  }
+  if (at < c && vs != prev) f(at, vs);
+}
+__global__ void k_rled_count(const u32 *cnt, const u8 *vsym, const u64 *hl, const u64 *hw, const u8 *prevsym, u32 nv,
+                             u32 *nstart) {
+  const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nv) return;
+  u32 k = 0;
+  rled_walk(cnt[v], vsym[v], hl[v], hw, prevsym[v], [&](u32, u8) { k++; });
+  nstart[v] = k;
+}
+__global__ void k_rled_write(const u32 *cnt, const u8 *vsym, const u64 *hl, const u64 *hw, const u8 *prevsym,
+                             const u64 *base, const u64 *soff, u32 nv, u64 *starts, u8 *syms) {
+  const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nv) return;
+  u64 w = soff[v];
+  const u64 b0 = base[v];
+  rled_walk(cnt[v], vsym[v], hl[v], hw, prevsym[v], [&](u32 at, u8 s) { starts[w] = b0 + at; syms[w] = s; w++; });
+}
+__global__ void k_rled_records(const u64 *starts, const u8 *syms, u64 R, u64 N, u8 *rec) {
+  u64 k = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= R) return;
+  const u64 s = starts[k];
+  const u64 run = (k + 1 < R ? starts[k + 1] : N) - s;
+  u8 *d = rec + 9 * k;
+  for (int b = 0; b < 8; b++) d[b] = (u8)(run >> (8 * b));
+  d[8] = syms[k];
+}
+
+static int fill_store_variant() {     // measurement switch: CMSBWT_FILL_STORE=0 selects 16-byte stores instead of the bulk copy
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("CMSBWT_FILL_STORE"); v = e ? atoi(e) : 1; }
+  return v;
+}
+
+static void emit_pull(cmsbwt_ctx *c, int mode) {
+  cudaStream_t st = c->st;
+  const u32 n = c->ix.n;
+  const u64 N = c->N, H = c->H;
+  const int B = 256;
+  const u64 nd64 = c->stats.n_docs;
+  if (nd64 + n >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "documents + reference length exceed 2^32"};
+  const u32 nd = (u32)nd64, nv = nd + n - 1;
+  {
+    GroupSpan g(c, CMSBWT_G_PLACE);
+    tiles_count_heads(c);
+  }
+  DBuf cnt, base, hl, vsym, tmp, bstart;
+  cnt.alloc(((size_t)nv + 1) * 4, st);
+  base.alloc(((size_t)nv + 2) * 8, st);
+  hl.alloc(((size_t)nv + 1) * 8, st);
+  vsym.alloc((size_t)nv + 16, st);
+  GroupSpan *goff = new GroupSpan(c, CMSBWT_G_OFFSETS);
+  k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(c->d_pcov.as<uint2>(), c->ix.sa, c->ix.rbwt, c->d_termsym.as<u8>(), nd, nv,
+                                         cnt.as<u32>(), hl.as<u64>(), vsym.as<u8>());
+  CK(cudaMemsetAsync(cnt.as<u32>() + nv, 0, 4, st));
+  size_t tb = 0;
+  EXSUM64(nullptr, tb, cnt.as<u32>(), base.as<u64>(), (int)(nv + 1), st);
+  tmp.alloc(tb, st);
+  CK(EXSUM64(tmp.p, tb, cnt.as<u32>(), base.as<u64>(), (int)(nv + 1), st));
+  CK(cudaMemsetAsync(base.as<u64>() + (nv + 1), 0xFF, 8, st));     // sentinel past base[nv] = N
+  c->launches += 3;
+  const u64 nblocks = (N + FILL_BYTES - 1) / FILL_BYTES;
+  if (mode == CMSBWT_MODE_PLAIN) {
+    bstart.alloc((nblocks + 1) * 4, st);
+    k_fill_part<<<(u32)((nblocks + 1 + B - 1) / B), B, 0, st>>>(base.as<u64>(), nv, N, nblocks, 0, bstart.as<u32>());
+    LAUNCH(c);
+  }
+  delete goff;
+  u64 total = 0;
+  CK(cudaMemcpyAsync(&total, base.as<u64>() + nv, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (total != N) {
+    char buf[128];
+    snprintf(buf, sizeof buf, "coverage total %llu != N %llu", (unsigned long long)total, (unsigned long long)N);
+    throw CmsErr{CMSBWT_E_INTERNAL, buf};
+  }
+  if (c->dump) {
+    c->h_off.alloc(H * 8, st);
+    k_head_offsets<<<(u32)((H + B - 1) / B), B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_within.as<u32>(),
+                                                        c->ix.isa, base.as<u64>(), nd, H, c->h_off.as<u64>());
+    LAUNCH(c);
+  }
+  c->out_mode = mode;
+  c->stats.n_runs = 0;
+  if (mode == CMSBWT_MODE_PLAIN) {
+    GroupSpan g(c, CMSBWT_G_FILL);
+    c->d_out.alloc(N + CMS_PAD, st);
+    u8 *out = c->d_out.as<u8>();
+    if (fill_store_variant() == 1)
+      k_fill_pull<1><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(),
+                                                            bstart.as<u32>(), N, out);
+    else
+      k_fill_pull<0><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(),
+                                                            bstart.as<u32>(), N, out);
+    LAUNCH(c);
+    c->out_bytes = N;
+  } else {
+    GroupSpan g(c, CMSBWT_G_RLE);
+    DBuf lastsym, prevsym, nstart, soff, starts, syms;
+    lastsym.alloc((size_t)nv + 16, st); prevsym.alloc((size_t)nv + 16, st);
+    nstart.alloc(((size_t)nv + 1) * 4, st); soff.alloc(((size_t)nv + 2) * 8, st);
+    const u32 gV = (nv + B - 1) / B;
+    k_rled_last<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(), nv, lastsym.as<u8>());
+    size_t t1 = 0, t2 = 0;
+    cub::DeviceScan::ExclusiveScan(nullptr, t1, lastsym.as<u8>(), prevsym.as<u8>(), LastValid(), (u8)RLE_NONE, (int)nv, st);
+    EXSUM64(nullptr, t2, nstart.as<u32>(), soff.as<u64>(), (int)(nv + 1), st);
+    DBuf tmp2; tmp2.alloc(t1 > t2 ? t1 : t2, st);
+    size_t tt = t1;
+    CK(cub::DeviceScan::ExclusiveScan(tmp2.p, tt, lastsym.as<u8>(), prevsym.as<u8>(), LastValid(), (u8)RLE_NONE, (int)nv, st));
+    k_rled_count<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(), prevsym.as<u8>(), nv,
+                                   nstart.as<u32>());
+    CK(cudaMemsetAsync(nstart.as<u32>() + nv, 0, 4, st));
+    tt = t2;
+    CK(EXSUM64(tmp2.p, tt, nstart.as<u32>(), soff.as<u64>(), (int)(nv + 1), st));
+    u64 R = 0;
+    CK(cudaMemcpyAsync(&R, soff.as<u64>() + nv, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    starts.alloc((R + 1) * 8, st); syms.alloc(R + 16, st);
+    c->d_rle.alloc(R * 9 + CMS_PAD, st);
+    k_rled_write<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(), prevsym.as<u8>(),
+                                   base.as<u64>(), soff.as<u64>(), nv, starts.as<u64>(), syms.as<u8>());
+    if (R) k_rled_records<<<(u32)((R + B - 1) / B), B, 0, st>>>(starts.as<u64>(), syms.as<u8>(), R, N, c->d_rle.as<u8>());
+    c->launches += 7;
+    c->out_bytes = R * 9;
+    c->stats.n_runs = R;
+    c->d_out.release();
+  }
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));
+  c->d_hw.release(); c->d_pcov.release(); c->d_termsym.release();
+  c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release();
+}
+
 void emit_stage(cmsbwt_ctx *c, int mode) {
+  if (c->light) { emit_pull(c, mode); return; }
   cudaStream_t st = c->st;
   const u32 n = c->ix.n;
   const u64 N = c->N, H = c->H;
@@ -220,10 +558,9 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   if (tb2 > tb) tb = tb2;
   tmp.alloc(tb, st);
   size_t t = tb;
-  if (!c->light) {     // sort-based path: coverage = inclusive scan of the deltas (in place)
-    CK(cub::DeviceScan::InclusiveSum(tmp.p, t, c->d_cov.as<i32>(), c->d_cov.as<i32>(), (int)n, st));
-    LAUNCH(c);
-  }
+  // sort-based path: coverage = inclusive scan of the deltas (in place)
+  CK(cub::DeviceScan::InclusiveSum(tmp.p, t, c->d_cov.as<i32>(), c->d_cov.as<i32>(), (int)n, st));
+  LAUNCH(c);
   CK(cudaMemsetAsync(cnt.as<u32>() + n, 0, 4, st));
   k_cnt_sa<<<(n + B - 1) / B, B, 0, st>>>(c->d_cov.as<i32>(), c->ix.sa, n, cnt.as<u32>());
   t = tb;
@@ -249,17 +586,14 @@ void emit_stage(cmsbwt_ctx *c, int mode) {
   { GroupSpan g(c, CMSBWT_G_FILL);
   k_fill<<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), c->ix.rbwt, bstart.as<u32>(), n, N, 0, out); }
   LAUNCH(c);
-  GroupSpan *gplace = new GroupSpan(c, CMSBWT_G_PLACE);
-  if (c->light) {
-    tiles_place_heads(c, base.as<u64>(), out);
-  } else {
+  {
+    GroupSpan gplace(c, CMSBWT_G_PLACE);
     c->h_off.alloc(H * 8, st);
     k_scatter_heads<<<(u32)((H + B - 1) / B), B, 0, st>>>(c->h_pos.as<u32>(), c->h_cs.as<u16>(),
                                                          c->h_within.as<u32>(), c->ix.isa,
                                                          base.as<u64>(), H, out, c->h_off.as<u64>());
     LAUNCH(c);
   }
-  delete gplace;
   CK(cudaGetLastError());
   c->out_mode = mode;
   c->out_bytes = N;

@@ -168,14 +168,17 @@ __global__ void __launch_bounds__(256) k_tile_scatter_few(const u32 *pos, const 
 }
 
 // ---- pass A: bucket sizes + cost of pass B -------------------------------------------------------
+// pcov != NULL (single-GPU pull emit, emit.cu): pcov[p] = {bucket size without the terminators, index of
+// the position's first head in the position-grouped head array hw[] that k_tile_place fills}, for p <= n.
 __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, const TileEnt *re, const u32 *hoff,
                                                          const u32 *roff, u32 n, u32 ndocs, u32 t0, u32 *cov,
-                                                         unsigned long long *work, u32 *maxent) {
+                                                         uint2 *pcov, unsigned long long *work, u32 *maxent) {
   __shared__ u32 s_h[LT_W];
   __shared__ int s_d[LT_W + 1];
   typedef cub::BlockScan<int, LT_THREADS> BS;
   typedef cub::BlockReduce<unsigned long long, LT_THREADS> BR;
   __shared__ typename BS::TempStorage ts;
+  __shared__ typename BS::TempStorage ts2;
   __shared__ typename BR::TempStorage tr;
   // t0 = first tile of this device (multi-GPU: the entry arrays and cov are local to its tile range)
   const u32 t = blockIdx.x, tid = threadIdx.x;
@@ -194,7 +197,12 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, cons
   BS(ts).InclusiveSum(d, incl);
   const u32 hq = s_h[tid];
   const u32 p = ((t + t0) << LT_SHIFT) + tid;
-  if (p < n) cov[(t << LT_SHIFT) + tid] = (u32)incl + hq + (p == n - 1 ? ndocs : 0u);
+  if (cov && p < n) cov[(t << LT_SHIFT) + tid] = (u32)incl + hq + (p == n - 1 ? ndocs : 0u);
+  if (pcov) {
+    int hex;
+    BS(ts2).ExclusiveSum((int)hq, hex);
+    if (p <= n) pcov[p] = make_uint2((u32)incl + hq, h0 + (u32)hex);
+  }
   // pair tests of pass B for this tile: every head against every range and its position mates
   unsigned long long w = (unsigned long long)hq * (hq + (r1 - r0));
   unsigned long long tot = BR(tr).Sum(w);
@@ -214,7 +222,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_cov(const TileEnt *he, cons
 __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, const TileEnt *re, const u32 *hoff,
                                                            const u32 *roff, const u32 *isa, const u64 *base,
                                                            u32 n, u32 t0, u8 *out, u64 *plc, u32 *within_out,
-                                                           u64 *off_out, int3 nb_t) {
+                                                           u64 *off_out, int3 nb_t, u64 *hw) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W];
   __shared__ u64 s_base[LT_W];
@@ -241,7 +249,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   // the rank of position p is needed only if p has heads, but that is known a sync later: fetch
   // isa[p] now (coalesced) and do the random gather base[rank] once the head counts are in
   const u32 p_own = ((t + t0) << LT_SHIFT) + tid;
-  const u32 rank_own = p_own < n ? isa[p_own] : 0;
+  const u32 rank_own = (!hw && p_own < n) ? isa[p_own] : 0;
   // the first range / head of every thread stays in registers between the two passes
   TileEnt re0, he0;
   re0.a = re0.b = 0; re0.kappa = 0; he0 = re0;
@@ -268,7 +276,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   }
   for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[(j == tid ? he0 : he[h0 + j]).b & (LT_W - 1)], 1u);
   __syncthreads();
-  s_base[tid] = s_cnt[tid] ? base[rank_own] : 0;      // 1/3 of the positions have no head: no gather
+  s_base[tid] = (!hw && s_cnt[tid]) ? base[rank_own] : 0;      // 1/3 of the positions have no head: no gather
   u32 ex;
   BS(ts).ExclusiveSum(s_cnt[tid], ex);
   s_off[tid] = ex;
@@ -320,12 +328,18 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
     const u64 kap = e.kappa;
     u32 w = 0;
     for (u32 jj = s_off[q]; jj < s_off[q + 1]; jj++) w += s_he[jj].kappa < kap;
+    const u32 mates = w;                        // kappas of one position are distinct: a permutation
     u32 bk = 0;
     for (u32 k = 0; k < npiv; k++) bk += s_piv[k] <= kap;
     if (NB > 1) w += (u32)s_C[bk][q];
     for (u32 r = s_boff[bk]; r < s_boff[bk + 1]; r++) {
       const u32 lh = s_rl[r];
       w += (s_rk[r] < kap) & ((lh & 0xFFFF) <= q) & (q <= (lh >> 16));
+    }
+    if (hw) {       // pull emit: (within << 8 | symbol), grouped by position, ascending within
+      hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);
+      if (within_out) within_out[e.a] = w;
+      continue;
     }
     const u64 off = s_base[q] + w;
     if (plc) plc[h0 + j] = (off << 8) | ((e.b >> 8) & 0xFF);   // multi-GPU: the byte belongs to another device
@@ -437,10 +451,11 @@ bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
   u32 HE = 0;
   u64 R = 0;
   if (!tiles_scatter(c, kappa, ntiles, &HE, &R, LT_MAX_ENTRIES)) return false;
-  c->d_cov.alloc(((size_t)n + 1) * 4, st);
+  c->d_cov.release();
+  c->d_pcov.alloc(((size_t)ntiles * LT_W + 1) * 8, st);
   k_tile_cov<<<ntiles, LT_THREADS, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                            c->t_roff.as<u32>(), n, (u32)c->stats.n_docs, 0, c->d_cov.as<u32>(),
-                                            acc.as<unsigned long long>(), acc.as<u32>() + 2);
+                                            c->t_roff.as<u32>(), n, (u32)c->stats.n_docs, 0, nullptr,
+                                            c->d_pcov.as<uint2>(), acc.as<unsigned long long>(), acc.as<u32>() + 2);
   LAUNCH(c);
   CK(cudaGetLastError());
   return tiles_finish(c, acc, HE, R, sexcl);
@@ -456,27 +471,39 @@ static bool tiles_finish(cmsbwt_ctx *c, DBuf &acc, u32 HE, u64 R, DBuf &sexcl) {
   c->stats.n_items = (u64)HE + R;
   c->stats.pair_tests = work;
   if (work > (u64)c->tile_budget || maxent > LT_MAX_ENTRIES) {
-    c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release(); c->d_cov.release();
+    c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release(); c->d_pcov.release();
     return false;
   }
   c->tile_maxent = maxent;
+  c->n_hw = HE;
   c->h_sexcl.release();
   c->h_sexcl.swap(sexcl);
   c->light = true;
   return true;
 }
 
-// pass B + terminators, after the output has been filled with the reference symbols
-void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out) {
+// terminator symbols in document order (the bucket of SA rank 0, :1640-1643 "first D-1 head chars")
+__global__ void k_term_syms(const u32 *len, const u16 *cs, const u32 *sexcl, u64 H, u8 *termsym, u32 *within_out) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H || len[i] != 0) return;
+  u32 d = sexcl[i];
+  termsym[d] = (u8)(cs[i] & 0xFF);
+  if (within_out) within_out[i] = d;
+}
+
+// pass B for the pull emit (emit.cu): within(h) of every head -> hw[] = (within << 8 | symbol), grouped
+// by reference position in ascending within, and the terminators' symbols in document order.  Nothing
+// is gathered from base[] and nothing is scattered into the output here: the fill kernel, which owns
+// an output block in shared memory, pulls the heads of its buckets.
+void tiles_count_heads(cmsbwt_ctx *c) {
   cudaStream_t st = c->st;
   const u64 H = c->H;
   const u32 n = c->ix.n;
   const u32 ntiles = (n >> LT_SHIFT) + 1;
-  u32 *wo = nullptr; u64 *oo = nullptr;
-  if (c->dump) {
-    c->h_within.alloc(H * 4, st); c->h_off.alloc(H * 8, st);
-    wo = c->h_within.as<u32>(); oo = c->h_off.as<u64>();
-  }
+  u32 *wo = nullptr;
+  if (c->dump) { c->h_within.alloc(H * 4, st); wo = c->h_within.as<u32>(); }
+  c->d_hw.alloc(((size_t)c->n_hw + 1) * 8, st);
+  c->d_termsym.alloc((size_t)c->stats.n_docs + 16, st);
   size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;
   // static (24 KB of bucket rows) + dynamic shared memory above 48 KB needs the opt-in; a fresh
   // process that starts with a tile of 1.6-2.5 K entries failed here before (threshold was 40 KB
@@ -484,10 +511,11 @@ void tiles_place_heads(cmsbwt_ctx *c, const u64 *base, u8 *out) {
   if (sm > 16 * 1024)
     CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_place<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                               c->t_roff.as<u32>(), c->ix.isa, base, n, 0, out, nullptr, wo, oo,
-                                               make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]));
-  k_place_sentinels<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
-                                                           c->h_sexcl.as<u32>(), H, out, wo, oo);
+                                               c->t_roff.as<u32>(), c->ix.isa, nullptr, n, 0, nullptr, nullptr, wo,
+                                               nullptr, make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]),
+                                               c->d_hw.as<u64>());
+  k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
+                                                     c->d_termsym.as<u8>(), wo);
   c->launches += 2;
   CK(cudaGetLastError());
 }
@@ -607,7 +635,7 @@ u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const 
   CK(cudaMemsetAsync(c->sh_cov.p, 0, (size_t)tp * LT_W * 4, st));
   k_tile_cov<<<tp, LT_THREADS, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                         c->t_roff.as<u32>(), n, (u32)ndocs_total, rank * tp, c->sh_cov.as<u32>(),
-                                        acc.as<unsigned long long>(), acc.as<u32>() + 2);
+                                        nullptr, acc.as<unsigned long long>(), acc.as<u32>() + 2);
   c->launches += 7;
   CK(cudaGetLastError());
   unsigned long long hacc[2] = {0, 0};
@@ -747,7 +775,7 @@ void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
     k_tile_place<<<tp, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                              c->t_roff.as<u32>(), c->ix.isa, base, n, c->sh_rank * tp, nullptr,
                                              raw.as<u64>(), nullptr, nullptr,
-                                             make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]));
+                                             make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]), nullptr);
   }
   k_sh_sentinel_plc<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                                            c->s_sexcl.as<u32>(), H, doc_base, raw.as<u64>() + c->sh_he);
