@@ -15,6 +15,6 @@ timeout 300 python bench.py --steps 2 --no-e2e --no-cpu-baseline > $O/r2_c1_plai
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file $O/r2_c1_launches_config3.csv \
   env CMSBWT_PROFILE=1 python bench.py --steps 2 --no-e2e --no-cpu-baseline > $O/r2_c1_ncu_list.log 2>&1
 ncu --set full --clock-control none --import-source on --profile-from-start off \
-  -k 'regex:k_ms_fast|k_tile_place|k_tile_scatter|k_fill|k_pack|k_cnt_sa|k_tail_label|k_tr_rank0|k_msf_gather|k_tile_cov|k_tile_hist|k_kappa|k_link' \
+  -k 'regex:k_ms_fast|k_tile_place|k_tile_scatter|k_fill|k_pack|k_vrank|k_tail_label|k_tr_rank0|k_msf_gather|k_tile_cov|k_tile_hist|k_kappa|k_link' \
   -c 18 -o $O/r2_c1_kernels_full env CMSBWT_PROFILE=1 python bench.py --steps 1 --no-e2e --no-cpu-baseline > $O/r2_c1_ncu_full.log 2>&1
 echo "ncu rc=$?"; ls -la $O | tail -12
