@@ -285,9 +285,14 @@ def run_multi(args, rank, world, local, dev, dist):
     dist.all_gather_into_tensor(allp, pt)
     plan = allp.cpu().view(world, 2).tolist()
 
+    # the C++ host layer (cms_bwt_b200/csrc/sharded.cu): the library's own NCCL communicator and exchanges
+    multi.comm_init(ctx, rank, world, dev)
+    ndocs_total = int(sum(p_[1] for p_ in plan))
+
     def step():
-        sp, out = multi.run_sharded(ctx, dev, text.data_ptr(), N, ndocs, rank, world, plan=plan)
-        state["sp"], state["out"] = sp, out
+        sp = multi.run_sharded_native(ctx, dev, text.data_ptr(), N, ndocs, P.MODE_PLAIN)
+        sp.ndocs_total = ndocs_total
+        state["sp"], state["out"] = sp, sp.out
         for k, v in sp.phase_ms.items():
             state["phase"][k] = state["phase"].get(k, 0.0) + v
 
@@ -349,7 +354,7 @@ def run_multi(args, rank, world, local, dev, dist):
         def e2e_step():
             dtext.copy_(host_text, non_blocking=True)
             torch.cuda.synchronize()
-            sp2, out = multi.run_sharded(ctx, dev, dtext.data_ptr(), N, ndocs, rank, world, plan=plan)
+            out = multi.run_sharded_native(ctx, dev, dtext.data_ptr(), N, ndocs, P.MODE_PLAIN).out
             host_out[:out.numel()].copy_(out, non_blocking=True)
             torch.cuda.synchronize()
         e2e_step()
@@ -380,7 +385,8 @@ def run_multi(args, rank, world, local, dev, dist):
                        "N_symbols": int(nsym), "documents": int(sp.ndocs_total), "n_ref_augmented": int(n),
                        "heads": int(H_total), "cache": "inputs (%.1f GB per GPU) larger than L2" % (N / 1e9),
                        "parallelism": "documents sharded (stage 1), tails by key range, tiles by reference-"
-                                      "position range, output by byte range; index replicated",
+                                      "position range, output by byte range; index replicated; host layer = "
+                                      "cmsbwt_run_sharded (C++, NCCL grouped send/recv + all-gather on the library's stream)",
                        "device_ms_per_step_rank0": dev_ms_local / args.steps,
                        "kernel_stage_ms_max": lib_ms_max,
                        "stage_ms_rank0": {k: v / args.steps for k, v in stage.items()},

@@ -29,6 +29,8 @@ EXPORTS = [
     "cmsbwt_shard_rank_apply", "cmsbwt_shard_tie_keys", "cmsbwt_shard_tie_refine",
     "cmsbwt_shard_tiles_local", "cmsbwt_shard_tiles_merge", "cmsbwt_shard_emit", "cmsbwt_shard_apply",
     "cmsbwt_shard_rle",
+    "cmsbwt_nccl_unique_id", "cmsbwt_comm_init", "cmsbwt_comm_destroy", "cmsbwt_run_sharded",
+    "cmsbwt_sharded_after_ms", "cmsbwt_sharded_rle", "cmsbwt_sharded_stats",
     "cmsbwt_parse_collection_mt", "cmsbwt_parse_piece", "cmsbwt_line_start",
     "cmsbwt_host_alloc", "cmsbwt_host_free", "cmsbwt_text_begin", "cmsbwt_text_append",
     "cmsbwt_ms_run_staged", "cmsbwt_result_read", "cmsbwt_copy_fence", "cmsbwt_copy_wait",
@@ -114,6 +116,13 @@ def lib():
         L.cmsbwt_result_read.argtypes = [vp, vp, u64, u64]
         L.cmsbwt_copy_fence.argtypes = [vp, C.c_int]
         L.cmsbwt_copy_wait.argtypes = [vp, C.c_int]
+        L.cmsbwt_nccl_unique_id.argtypes = [vp]
+        L.cmsbwt_comm_init.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
+        L.cmsbwt_comm_destroy.argtypes = [vp]
+        L.cmsbwt_run_sharded.argtypes = [vp, vp, u64, u64, C.c_int, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+        L.cmsbwt_sharded_after_ms.argtypes = [vp, u64, C.c_int, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]
+        L.cmsbwt_sharded_rle.argtypes = [vp, C.POINTER(vp), C.POINTER(u64), C.POINTER(u64)]
+        L.cmsbwt_sharded_stats.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(C.c_double), C.c_uint32]
         _lib = L
     return _lib
 

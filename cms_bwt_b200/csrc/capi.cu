@@ -52,20 +52,6 @@ static int fail(cmsbwt_ctx *c, int code, const std::string &msg) {
   catch (const CmsErr &e) { return fail(c, e.code, e.msg); }                                 \
   catch (const std::exception &e) { return fail(c, CMSBWT_E_NOMEM, e.what()); }
 
-struct Timer {
-  cudaEvent_t a, b;
-  cudaStream_t st;
-  Timer(cudaStream_t s) : st(s) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, s); }
-  double stop() {
-    cudaEventRecord(b, st);
-    cudaEventSynchronize(b);
-    float ms = 0;
-    cudaEventElapsedTime(&ms, a, b);
-    return ms;
-  }
-  ~Timer() { cudaEventDestroy(a); cudaEventDestroy(b); }
-};
-
 extern "C" {
 
 int cmsbwt_ctx_create(int dev, cmsbwt_ctx **out) {
@@ -98,6 +84,7 @@ void cmsbwt_ctx_destroy(cmsbwt_ctx *c) {
     if (c->ev_in1) cudaEventDestroy(c->ev_in1);
     cudaStreamDestroy(c->st_copy);
   }
+  cmsbwt_comm_destroy(c);
   group_reset(c);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
   c->ev_pool.clear();
@@ -467,7 +454,8 @@ int cmsbwt_emit(cmsbwt_ctx *c, int mode, uint64_t *out_bytes) {
 
 const void *cmsbwt_result_device(const cmsbwt_ctx *c) {
   if (!c) return nullptr;
-  return c->out_mode == CMSBWT_MODE_RLE ? c->d_rle.p : c->d_out.p;
+  if (c->out_mode == CMSBWT_MODE_RLE) return c->d_rle.p ? (const void *)(c->d_rle.as<u8>() + c->rle_off) : nullptr;
+  return c->d_out.p;
 }
 
 int cmsbwt_result_download(cmsbwt_ctx *c, void *host_out, uint64_t cap) {

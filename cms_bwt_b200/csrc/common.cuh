@@ -168,9 +168,14 @@ struct cmsbwt_ctx {
   std::vector<u64> sh_plc_cnt;                   // placements per destination rank
   u32 sh_world = 1, sh_rank = 0, sh_tp = 0;      // tiles per rank
   u64 sh_he = 0, sh_re = 0, sh_nplc = 0, sh_obeg = 0, sh_olen = 0, sh_chunk = 0, sh_Ntotal = 0;
+  // multi-GPU host layer (sharded.cu): NCCL communicator of this rank, phase wall times, counters
+  void *comm = nullptr;
+  u32 comm_rank = 0, comm_world = 1;
+  double sh_phase_ms[16] = {};
+  u64 sh_collectives = 0, sh_comm_bytes = 0, sh_rle_first = 0, sh_rle_skip = 0;
   // stage 3
   DBuf d_out, d_rle;
-  u64 out_bytes = 0;
+  u64 out_bytes = 0, rle_off = 0;   // rle_off: bytes of d_rle that belong to the rank on the left (sharded -r)
   int out_mode = 0;
   // kernel-group timers: pairs of events per span, collected after the stage
   std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> spans;
@@ -190,6 +195,21 @@ struct cmsbwt_ctx {
 };
 
 #define LAUNCH(ctx) ((ctx)->launches++)
+
+struct Timer {
+  cudaEvent_t a, b;
+  cudaStream_t st;
+  Timer(cudaStream_t s) : st(s) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, s); }
+  double stop() {
+    cudaEventRecord(b, st);
+    cudaEventSynchronize(b);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, a, b);
+    return ms;
+  }
+  ~Timer() { cudaEventDestroy(a); cudaEventDestroy(b); }
+};
+
 
 // Kernel-group timers (stats.group_ms): events on the context's stream around a group of launches;
 // read back by group_collect() once the stage has synchronised.  A group may be opened several

@@ -201,6 +201,7 @@ void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N) {
   CK(cudaGetLastError());
   c->out_mode = CMSBWT_MODE_RLE;
   c->out_bytes = R * 9;
+  c->rle_off = 0;
   c->stats.n_runs = R;
   CK(cudaStreamSynchronize(st));
 }
@@ -243,7 +244,9 @@ template <int STORE>      // 1 = bulk copy (TMA), 0 = 16-byte stores from shared
 __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restrict__ base, const u8 *__restrict__ vsym,
                                                             const u64 *__restrict__ hl, const u64 *__restrict__ hw,
                                                             const u32 *__restrict__ bstart, u64 N, u8 *out) {
-  __shared__ u64 sb[FILL_SMEM_RUNS + 2];
+  // run starts RELATIVE to the block's first byte (a block is 16 KB: 32 bits do; starts before the block
+  // clamp to 0 -- only the first run can --, starts past it to 0xFFFFFFFE)
+  __shared__ u32 sb[FILL_SMEM_RUNS + 2];
   __shared__ u8 ssym[FILL_SMEM_RUNS + 2];
   __shared__ u32 s_m[FILL_VECS];
   __shared__ __align__(128) u8 s_out[FILL_BYTES];
@@ -253,18 +256,35 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
   const u32 tid = threadIdx.x;
   const u64 o0 = (u64)blockIdx.x * FILL_BYTES;
   const u64 o1 = min(N, o0 + FILL_BYTES);
+  const u32 olen = (u32)(o1 - o0);
   const u32 r0 = bstart[blockIdx.x], r1 = bstart[blockIdx.x + 1];
   const u32 nr = r1 - r0 + 1;                 // runs r0..r1 intersect this block
   const bool use_s = nr <= FILL_SMEM_RUNS;
+  // the head list of this thread's first run is requested before anything else: its two dependent
+  // reads (hl -> hw) are in flight while the block expands the runs
+  u64 h_pre = 0, e_pre0 = 0, e_pre1 = 0;
+  if (tid < nr) h_pre = __ldg(hl + r0 + tid);
+  const u64 base_r0 = __ldg(base + r0);
   if (tid == 0) s_qn = 0;
   if (use_s) {
-    for (u32 k = tid; k <= nr; k += FILL_THREADS) { sb[k] = base[r0 + k]; ssym[k] = k < nr ? vsym[r0 + k] : 0; }
-    if (tid == 0) sb[nr + 1] = ~0ull;          // the last block runs one entry past base[nv] = N
+    for (u32 k = tid; k <= nr; k += FILL_THREADS) {
+      const u64 bk = base[r0 + k];
+      sb[k] = bk <= o0 ? 0u : (bk - o0 >= 0xFFFFFFFEull ? 0xFFFFFFFEu : (u32)(bk - o0));
+      ssym[k] = k < nr ? vsym[r0 + k] : 0;
+    }
+    if (tid == 0) sb[nr + 1] = 0xFFFFFFFFu;    // the last block runs one entry past base[nv] = N
     for (u32 v = tid; v < FILL_VECS; v += FILL_THREADS) s_m[v] = 0;
+  }
+  if ((u32)h_pre) {
+    const u64 *e = hw + (h_pre >> 32);
+    e_pre0 = __ldg(e);
+    if ((u32)h_pre > 1) e_pre1 = __ldg(e + 1);
+  }
+  if (use_s) {
     __syncthreads();
     for (u32 k = 1 + tid; k < nr; k += FILL_THREADS) {
-      u64 s = sb[k];
-      if (s >= o0 && s < o1) atomicMax(&s_m[(u32)(s - o0) >> 4], k);
+      const u32 s = sb[k];
+      if (s < olen) atomicMax(&s_m[s >> 4], k);
     }
     __syncthreads();
     u32 it[FILL_VEC_PER_THREAD];
@@ -279,18 +299,18 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
 #pragma unroll
   for (int v = 0; v < FILL_VEC_PER_THREAD; v++) {
     const u32 vi = (u32)v * FILL_THREADS + tid;
-    const u64 o = o0 + (u64)vi * 16;
-    if (o >= o1) break;
+    const u32 orel = vi * 16;
+    if (orel >= olen) break;
     u32 k;
     u64 lo, hi;
     if (use_s) {
       k = vi ? s_m[vi - 1] : 0;
-      while (sb[k + 1] <= o) k++;              // runs that start exactly here, empty runs
+      while (sb[k + 1] <= orel) k++;           // runs that start exactly here, empty runs
       lo = hi = (u64)ssym[k] * 0x0101010101010101ull;
-      u64 nb = sb[k + 1];
-      while (nb < o + 16) {                    // a run starts inside this vector: overwrite its bytes
+      u32 nb = sb[k + 1];
+      while (nb < orel + 16) {                 // a run starts inside this vector: overwrite its bytes
         k++;
-        const u32 d = (u32)(nb - o);
+        const u32 d = nb - orel;
         const u64 sp = (u64)ssym[k] * 0x0101010101010101ull;
         const u64 mlo = d < 8 ? ~0ull << (8 * d) : 0ull;
         const u64 mhi = d < 8 ? ~0ull : ~0ull << (8 * (d - 8));
@@ -300,6 +320,7 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
       }
     } else {
       const u64 *bb = base + r0;
+      const u64 o = o0 + orel;
       k = run_of(bb, 0, nr, o);
       lo = hi = (u64)vsym[r0 + k] * 0x0101010101010101ull;
       u64 nb = bb[k + 1];
@@ -314,25 +335,27 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
         nb = bb[k + 1];
       }
     }
-    *(uint4 *)(s_out + vi * 16) = make_uint4((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
+    *(uint4 *)(s_out + orel) = make_uint4((u32)lo, (u32)(lo >> 32), (u32)hi, (u32)(hi >> 32));
   }
   __syncthreads();
   // ---- pull the head symbols of the buckets that intersect this block (:1653-1676 as a gather) ----
+  // offset of a head inside the block = (start of its run - o0) + within; only the first run can start
+  // before the block (signed arithmetic on its true start)
   for (u32 k = tid; k < nr; k += FILL_THREADS) {
-    const u64 h = __ldg(hl + r0 + k);
+    const u64 h = k == tid ? h_pre : __ldg(hl + r0 + k);
     const u32 nh = (u32)h;
     if (!nh) continue;
     if (nh > PULL_SERIAL) {
       const u32 q = atomicAdd(&s_qn, 1u);
       if (q < PULL_QCAP) { s_q[q] = k; continue; }
     }
-    const u64 b0 = use_s ? sb[k] : base[r0 + k];
+    const i64 b0 = k == 0 ? (i64)(base_r0 - o0) : (i64)(use_s ? (u64)sb[k] : base[r0 + k] - o0);
     const u64 *e = hw + (h >> 32);
     for (u32 j = 0; j < nh; j++) {
-      const u64 x = __ldg(e + j);
-      const u64 off = b0 + (x >> 8);
-      if (off >= o1) break;                    // ascending within
-      if (off >= o0) s_out[off - o0] = (u8)x;
+      const u64 x = (k == tid && j < 2) ? (j ? e_pre1 : e_pre0) : __ldg(e + j);
+      const i64 off = b0 + (i64)(x >> 8);
+      if (off >= (i64)olen) break;             // ascending within
+      if (off >= 0) s_out[off] = (u8)x;
     }
   }
   __syncthreads();
@@ -342,12 +365,12 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
       const u32 k = s_q[q];
       const u64 h = __ldg(hl + r0 + k);
       const u32 nh = (u32)h;
-      const u64 b0 = use_s ? sb[k] : base[r0 + k];
+      const i64 b0 = k == 0 ? (i64)(base_r0 - o0) : (i64)(use_s ? (u64)sb[k] : base[r0 + k] - o0);
       const u64 *e = hw + (h >> 32);
       for (u32 j = lane; j < nh; j += 32) {
         const u64 x = __ldg(e + j);
-        const u64 off = b0 + (x >> 8);
-        if (off >= o0 && off < o1) s_out[off - o0] = (u8)x;
+        const i64 off = b0 + (i64)(x >> 8);
+        if (off >= 0 && off < (i64)olen) s_out[off] = (u8)x;
       }
     }
   }
@@ -355,7 +378,7 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
   // every writer fences, then the barrier, then one thread issues the copy
   if (STORE == 1) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
-  const u32 bytes = (u32)(((o1 - o0) + 15) & ~15ull);          // out has CMS_PAD bytes of slack
+  const u32 bytes = (olen + 15) & ~15u;                        // out has CMS_PAD bytes of slack
   if (STORE == 1) {
     if (tid == 0) bulk_store_block(out + o0, s_out, bytes);
   } else {
@@ -533,6 +556,7 @@ static void emit_pull(cmsbwt_ctx *c, int mode) {
     if (R) k_rled_records<<<(u32)((R + B - 1) / B), B, 0, st>>>(starts.as<u64>(), syms.as<u8>(), R, N, c->d_rle.as<u8>());
     c->launches += 7;
     c->out_bytes = R * 9;
+    c->rle_off = 0;
     c->stats.n_runs = R;
     c->d_out.release();
   }

@@ -56,6 +56,7 @@ struct Args {                       // utils.h:8-14
   bool host_sa = true;
   bool stream = true;               // streamed ingest / egress
   int threads = 0;                  // host threads of the parser (0 = hardware threads, at most 16)
+  int gpus = 0;                     // > 0: the multi-GPU path on devices 0..gpus-1 (one host thread per GPU, NCCL)
 };
 
 static void print_help(char **argv) {
@@ -71,7 +72,8 @@ static void print_help(char **argv) {
             << "\t--device N \tCUDA device ordinal, def. 0" << std::endl
             << "\t--no-host-sa \tbuild the reference suffix array on the GPU even if libsais is available" << std::endl
             << "\t--no-stream \tread, parse, copy and write one after the other (no overlap)" << std::endl
-            << "\t--threads T \thost threads of the collection parser, def. all (at most 16)" << std::endl;
+            << "\t--threads T \thost threads of the collection parser, def. all (at most 16)" << std::endl
+            << "\t--gpus N \tshard the collection's documents over GPUs 0..N-1 (NCCL), def. one GPU" << std::endl;
   exit(-1);
 }
 
@@ -83,6 +85,7 @@ static void parse_args(int argc, char **argv, Args &arg) {
                                     {"no-host-sa", no_argument, nullptr, 1001},
                                     {"no-stream", no_argument, nullptr, 1002},
                                     {"threads", required_argument, nullptr, 1003},
+                                    {"gpus", required_argument, nullptr, 1004},
                                     {nullptr, 0, nullptr, 0}};
   int c;
   while ((c = getopt_long(argc, argv, "p:b:o:rh", longopts, nullptr)) != -1) {
@@ -95,6 +98,7 @@ static void parse_args(int argc, char **argv, Args &arg) {
       case 1001: arg.host_sa = false; break;
       case 1002: arg.stream = false; break;
       case 1003: arg.threads = atoi(optarg); break;
+      case 1004: arg.gpus = atoi(optarg); break;
       case 'h': print_help(argv); break;
       default:
         std::cout << "Unknown option. Use -h for help." << std::endl;
@@ -310,6 +314,91 @@ static int egress_streamed(cmsbwt_ctx *ctx, int fd, uint64_t out_bytes) {
   return rc ? rc : (ok ? 0 : 1);
 }
 
+// ---- multi-GPU: whole documents sharded over GPUs 0..W-1 by cumulative length, one host
+// thread per GPU driving its context; the exchanges are the library's (cmsbwt_sharded_after_ms over
+// NCCL).  Every rank writes its slice of <out>.bwt / <out>.rl_bwt at its own offset.
+static int run_multi_gpu(const Args &arg, const std::vector<uint8_t> &x, int64_t n, const int32_t *sa,
+                         const std::vector<uint8_t> &text, int64_t N, std::ofstream &log) {
+  const int W = arg.gpus;
+  // contiguous ranges of whole documents with balanced symbol counts
+  std::vector<int64_t> ends;
+  for (int64_t i = 0; i < N; i++) if (text[(size_t)i] == 2) ends.push_back(i);
+  const int64_t D = (int64_t)ends.size();
+  if (D < W) { fprintf(stderr, "Error: more GPUs (%d) than documents (%lld)\n", W, (long long)D); return 1; }
+  std::vector<int64_t> bound(W + 1, 0);
+  {
+    int64_t d = 0;
+    for (int r = 1; r < W; r++) {
+      const int64_t target = N * r / W;
+      while (d < D && (d == 0 ? 0 : ends[(size_t)d - 1] + 1) + (ends[(size_t)d] - (d == 0 ? -1 : ends[(size_t)d - 1])) / 2 < target) d++;
+      if (d <= bound[(size_t)r - 1]) d = bound[(size_t)r - 1] + 1;   // every rank gets at least one document
+      if (d > D - (W - r)) d = D - (W - r);
+      bound[r] = d;
+    }
+    bound[W] = D;
+  }
+  uint8_t id[128];
+  if (cmsbwt_nccl_unique_id(id) != CMSBWT_OK) { fprintf(stderr, "Error: NCCL is not available (libnccl.so.2 / CMSBWT_NCCL)\n"); return 1; }
+  const std::string outpath = arg.outname + (arg.format ? ".rl_bwt" : ".bwt");
+  int fd = ::open(outpath.c_str(), O_RDWR | O_CREAT | O_TRUNC, 0644);
+  if (fd < 0) { fprintf(stderr, "Error writing %s\n", outpath.c_str()); return 1; }
+  std::vector<int> rcs((size_t)W, 0);
+  std::vector<std::string> errs((size_t)W);
+  std::vector<cmsbwt_stats> sts((size_t)W);
+  std::vector<std::vector<double>> phases((size_t)W, std::vector<double>(16, 0.0));
+  std::vector<uint64_t> colls((size_t)W, 0), xbytes((size_t)W, 0);
+  const int mode = arg.format ? CMSBWT_MODE_RLE : CMSBWT_MODE_PLAIN;
+  auto work = [&](int r) {
+    cmsbwt_ctx *ctx = nullptr;
+    auto failed = [&](const char *what, int rc) {
+      errs[(size_t)r] = std::string(what) + ": " + (ctx ? cmsbwt_last_error(ctx) : "no context");
+      rcs[(size_t)r] = rc ? rc : 1;
+      // a rank that stops here would leave the others waiting inside a collective: end the process
+      fprintf(stderr, "Error in %s (GPU %d): %s\n", what, r, ctx ? cmsbwt_last_error(ctx) : "no usable CUDA device");
+      _exit(1);
+    };
+    int rc = cmsbwt_ctx_create(r, &ctx);
+    if (rc) failed("ctx_create", rc);
+    if ((rc = cmsbwt_index_upload(ctx, x.data(), (uint32_t)n, sa))) failed("index_upload", rc);
+    if ((rc = cmsbwt_comm_init(ctx, id, (uint32_t)r, (uint32_t)W))) failed("comm_init", rc);
+    const int64_t d0 = bound[(size_t)r], d1 = bound[(size_t)r + 1];
+    const int64_t lo = d0 == 0 ? 0 : ends[(size_t)d0 - 1] + 1, hi = ends[(size_t)d1 - 1] + 1;
+    if ((rc = cmsbwt_ms_run(ctx, text.data() + lo, (uint64_t)(hi - lo)))) failed("ms_run", rc);
+    uint64_t ob = 0, ol = 0, tot = 0;
+    if ((rc = cmsbwt_sharded_after_ms(ctx, (uint64_t)(d1 - d0), mode, &ob, &ol, &tot))) failed("sharded_after_ms", rc);
+    uint64_t bytes = ol, off = ob;
+    if (mode == CMSBWT_MODE_RLE) {
+      const void *rec = nullptr; uint64_t nrec = 0, first = 0;
+      if ((rc = cmsbwt_sharded_rle(ctx, &rec, &nrec, &first))) failed("sharded_rle", rc);
+      bytes = 9 * nrec; off = 9 * first;
+    }
+    std::vector<uint8_t> out((size_t)bytes + 16);
+    if (bytes && (rc = cmsbwt_result_download(ctx, out.data(), bytes))) failed("result_download", rc);
+    if (bytes && !write_all(fd, out.data(), bytes, off)) { fprintf(stderr, "Error writing %s\n", outpath.c_str()); _exit(1); }
+    cmsbwt_get_stats(ctx, &sts[(size_t)r]);
+    cmsbwt_sharded_stats(ctx, &colls[(size_t)r], &xbytes[(size_t)r], phases[(size_t)r].data(), 16);
+    cmsbwt_ctx_destroy(ctx);
+  };
+  std::vector<std::thread> th;
+  for (int r = 1; r < W; r++) th.emplace_back(work, r);
+  work(0);
+  for (auto &t : th) t.join();
+  if (::close(fd) != 0) { fprintf(stderr, "Error writing %s\n", outpath.c_str()); return 1; }
+  static const char *PH[] = {"sizes", "tails", "x_tails", "rank_owner", "x_ranks", "refine", "tiles_local", "x_tiles",
+                             "tiles_merge", "x_cov", "emit", "x_placements", "apply", "rle"};
+  uint64_t heads = 0;
+  for (int r = 0; r < W; r++) heads += sts[(size_t)r].n_heads;
+  log << "Multi-GPU path on " << W << " GPUs (documents sharded; NCCL): headNumber: " << heads << ", collectives per job: "
+      << colls[0] << ", exchanged bytes (rank 0): " << xbytes[0] << std::endl;
+  for (int r = 0; r < W; r++) {
+    log << "  GPU " << r << ": documents " << bound[(size_t)r] << ".." << bound[(size_t)r + 1] << ", MS " << sts[(size_t)r].ms_ms
+        << " ms, phases";
+    for (int k = 0; k < 14; k++) log << " " << PH[k] << "=" << phases[(size_t)r][(size_t)k];
+    log << std::endl;
+  }
+  return 0;
+}
+
 int main(int argc, char **argv) {
   Args arg;
   parse_args(argc, argv, arg);
@@ -343,6 +432,7 @@ int main(int argc, char **argv) {
     ctx_rc = cmsbwt_ctx_create(arg.device, &ctx);
     ctx_ms = ms_since(tc);
   };
+  if (arg.gpus > 0) arg.stream = false;     // the multi-GPU path parses the whole collection first
   if (arg.stream) ctx_thread = std::thread(make_ctx);
   auto bail = [&](int code) {          // no thread may be left running when exit() tears the process down
     if (ctx_thread.joinable()) ctx_thread.join();
@@ -393,6 +483,40 @@ int main(int argc, char **argv) {
   if (sais && arg.stream) {
     sa.resize((size_t)n);
     sa_thread = std::thread(build_sa);
+  }
+
+  if (arg.gpus > 0) {
+    // ---- multi-GPU: SA on the host (libsais) or on GPU 0, whole parse, then one thread per GPU ----
+    std::vector<int32_t> sa_m((size_t)n);
+    if (sais) {
+      ts = std::chrono::high_resolution_clock::now();
+      if (sais(x.data(), sa_m.data(), (int32_t)n, 0, nullptr) != 0) { fprintf(stderr, "Error: libsais failed\n"); exit(1); }
+      log << "Computed SA in " << ms_since(ts) << " ms (" << sa_route << ", host)" << std::endl;
+    } else {
+      cmsbwt_ctx *c0 = nullptr;
+      if (cmsbwt_ctx_create(0, &c0) != CMSBWT_OK || cmsbwt_build_sa(c0, x.data(), (uint32_t)n, sa_m.data()) != CMSBWT_OK) {
+        fprintf(stderr, "Error: no usable CUDA device 0 (cms_bwt has no CPU fallback)\n");
+        exit(1);
+      }
+      cmsbwt_stats s0{};
+      cmsbwt_get_stats(c0, &s0);
+      log << "Computed SA in " << s0.sa_build_ms << " ms (GPU prefix doubling)" << std::endl;
+      cmsbwt_ctx_destroy(c0);
+    }
+    std::vector<uint8_t> text_m((size_t)coll.size + 2);
+    int64_t nd_m = 0;
+    const int64_t N_m = cmsbwt_parse_collection_mt(coll.p, coll.size, arg.prefixLength, text_m.data(), &nd_m, T);
+    coll.close();
+    if (N_m <= 0) { fprintf(stderr, "Error: collection %s holds no document\n", collFileName.c_str()); exit(1); }
+    log << "Collection parsed: " << N_m << " symbols, " << nd_m << " documents" << std::endl;
+    std::cout << "==== Processing collection" << std::endl;
+    const int rc_m = run_multi_gpu(arg, x, n, sa_m.data(), text_m, N_m, log);
+    if (rc_m) exit(1);
+    std::cout << "==== Time elapsed: "
+              << std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::high_resolution_clock::now() - t1).count()
+              << " ms" << std::endl;
+    log.close();
+    return 0;
   }
 
   // ---- device ----

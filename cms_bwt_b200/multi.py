@@ -561,6 +561,63 @@ def run_sharded(ctx, device, d_text_ptr, N_local, ndocs_local, rank, world, grou
     return sp, out
 
 
+# ---- the C++ host layer (cms_bwt_b200/csrc/sharded.cu): the same path behind one call -----------------
+PHASES = ("sizes", "tails", "x_tails", "rank_owner", "x_ranks", "refine", "tiles_local", "x_tiles", "tiles_merge",
+          "x_cov", "emit", "x_placements", "apply", "rle")
+
+
+def comm_init(ctx, rank, world, device=None, group=None):
+    """NCCL communicator of the library for this rank's context: rank 0 makes the ncclUniqueId, the
+    process group (any backend) broadcasts it, every rank calls cmsbwt_comm_init (collective)."""
+    L = lib()
+    buf = (C.c_uint8 * 128)()
+    if rank == 0:
+        ctx._ck(L.cmsbwt_nccl_unique_id(buf))
+    if world > 1:
+        dev = device if (device is not None and dist.get_backend(group) == "nccl") else "cpu"
+        t = torch.tensor(list(buf), dtype=torch.uint8, device=dev)
+        dist.broadcast(t, 0, group=group)
+        buf = (C.c_uint8 * 128)(*t.cpu().tolist())
+    ctx._ck(L.cmsbwt_comm_init(ctx.h, buf, rank, world))
+
+
+class NativeRun:
+    """result of run_sharded_native: this rank's slice of the BWT (or its records) and the counters"""
+    pass
+
+
+def run_sharded_native(ctx, device, d_text_ptr, N_local, ndocs_local, mode=MODE_PLAIN):
+    """cmsbwt_run_sharded: stage 1 on this rank's documents, then stages 2-3 with the library's own
+    NCCL exchanges.  comm_init must have been called on ctx."""
+    L = lib()
+    ob, ol, tot = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    ctx.N = int(N_local)
+    ctx._ck(L.cmsbwt_run_sharded(ctx.h, C.c_void_p(int(d_text_ptr)), int(N_local), int(ndocs_local), mode,
+                                 C.byref(ob), C.byref(ol), C.byref(tot)))
+    r = NativeRun()
+    r.out_begin, r.out_len, r.N_total = ob.value, ol.value, tot.value
+    dev = torch.device(device)
+    p = L.cmsbwt_result_device(ctx.h)
+    if mode == MODE_PLAIN:
+        r.out = (torch.as_tensor(_DevArray(p, ol.value, "|u1"), device=dev) if ol.value
+                 else torch.empty(0, dtype=torch.uint8, device=dev))
+        r.records, r.first_record = None, 0
+    else:
+        rp, nrec, first = C.c_void_p(), C.c_uint64(), C.c_uint64()
+        ctx._ck(L.cmsbwt_sharded_rle(ctx.h, C.byref(rp), C.byref(nrec), C.byref(first)))
+        r.records = (torch.as_tensor(_DevArray(rp.value, nrec.value * 9, "|u1"), device=dev) if nrec.value
+                     else torch.empty(0, dtype=torch.uint8, device=dev))
+        r.first_record = first.value
+        r.out = None
+    coll, xb = C.c_uint64(), C.c_uint64()
+    ph = (C.c_double * 16)()
+    k = L.cmsbwt_sharded_stats(ctx.h, C.byref(coll), C.byref(xb), ph, 16)
+    r.collectives, r.comm_bytes = coll.value, xb.value
+    r.phase_ms = {PHASES[i]: ph[i] for i in range(min(k, len(PHASES)))}
+    r.rank_rounds = ctx.stats()["rank_rounds"]
+    return r
+
+
 # ---- the command line across GPUs -----------------------------------------------------------------
 def main(argv=None):
     """`cms_bwt` over all ranks of a torchrun launch: same options and files as the reference's

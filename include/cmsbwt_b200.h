@@ -253,6 +253,37 @@ int cmsbwt_shard_apply(cmsbwt_ctx *ctx, const void *d_plc, uint64_t count);
  * a run that straddles a device border is merged by the host layer (multi.rle_sharded). */
 int cmsbwt_shard_rle(cmsbwt_ctx *ctx, uint64_t *n_records);
 
+/* ---- the multi-GPU path behind ONE call (C++ host layer over NCCL, cms_bwt_b200/csrc/sharded.cu) ----
+ * One rank per context.  The shard steps above, with every collective (all-to-all = grouped
+ * ncclSend/ncclRecv, all-gather) issued by the library on the context's stream; NCCL is loaded at run
+ * time (libnccl.so.2, or CMSBWT_NCCL=<path>).  No reference counterpart (the reference is one thread);
+ * the stage order is the reference's (:1138-1213, :1359-1603, :1618-1777).
+ *   cmsbwt_nccl_unique_id   128-byte ncclUniqueId made on one rank; the caller hands it to every rank
+ *                           (torch.distributed / MPI broadcast, or shared memory between host threads)
+ *   cmsbwt_comm_init        ncclCommInitRank on the context's device (collective: every rank calls it)
+ *   cmsbwt_run_sharded      stage 1 on this rank's whole documents (d_text as in cmsbwt_ms_run_device,
+ *                           ndocs_local = its separators), then stages 2-3 with the exchanges.  PLAIN:
+ *                           this rank's slice of the BWT = bytes [*out_begin, *out_begin + *out_len) of
+ *                           the whole output (*total_bytes long), in cmsbwt_shard_buffer("result").
+ *                           RLE: additionally the slice's records with border-straddling runs merged,
+ *                           see cmsbwt_sharded_rle.  Collective: every rank must call it.
+ *   cmsbwt_sharded_after_ms the same for a text already run through cmsbwt_ms_run / _staged
+ *   cmsbwt_sharded_rle      device pointer / count of this rank's 9-byte records and the index of its
+ *                           first record in the concatenated .rl_bwt
+ *   cmsbwt_sharded_stats    collectives and exchanged bytes of the last job, wall time per phase (ms):
+ *                           sizes, tails, x_tails, rank_owner, x_ranks, refine, tiles_local, x_tiles,
+ *                           tiles_merge, x_cov, emit, x_placements, apply, rle; returns the phase count */
+int cmsbwt_nccl_unique_id(void *out128);
+int cmsbwt_comm_init(cmsbwt_ctx *ctx, const void *id128, uint32_t rank, uint32_t world);
+int cmsbwt_comm_destroy(cmsbwt_ctx *ctx);
+int cmsbwt_run_sharded(cmsbwt_ctx *ctx, const void *d_text, uint64_t N_local, uint64_t ndocs_local, int mode,
+                       uint64_t *out_begin, uint64_t *out_len, uint64_t *total_bytes);
+int cmsbwt_sharded_after_ms(cmsbwt_ctx *ctx, uint64_t ndocs_local, int mode, uint64_t *out_begin,
+                            uint64_t *out_len, uint64_t *total_bytes);
+int cmsbwt_sharded_rle(cmsbwt_ctx *ctx, const void **d_records, uint64_t *n_records, uint64_t *first_record);
+int cmsbwt_sharded_stats(const cmsbwt_ctx *ctx, uint64_t *collectives, uint64_t *exchange_bytes, double *phase_ms,
+                         uint32_t phase_cap);
+
 /* tuning knobs: "chunk_len" (text window of an MS lane; 0 = by text length, 1024..8192), "kmer_k"
  * (order of the k-mer table, 0 = largest k <= 14 with 4^k <= n; takes effect at the next
  * index_upload), "fast" (0: 8-bit warp kernel for every input), "tile_budget" (0: sort-based sweep

@@ -29,8 +29,16 @@ def main():
     ctx = P.Context(local)
     ctx.index_upload(x)
     t = torch.from_numpy(np.concatenate([shard, np.full(64, 2, np.uint8)])).to(dev)
-    sp, out = multi.run_sharded(ctx, dev, t.data_ptr(), len(shard), nd, rank, world)
-    np.savez(outp + ".%d.npz" % rank, out=out.cpu().numpy(), begin=sp.out_begin)
+    if os.environ.get("CMSBWT_TEST_PYTHON_HOST") == "1":        # the Python orchestration over torch.distributed
+        sp, out = multi.run_sharded(ctx, dev, t.data_ptr(), len(shard), nd, rank, world)
+        np.savez(outp + ".%d.npz" % rank, out=out.cpu().numpy(), begin=sp.out_begin)
+    else:                                                        # the C++ host layer over the library's own NCCL
+        multi.comm_init(ctx, rank, world, dev)
+        r = multi.run_sharded_native(ctx, dev, t.data_ptr(), len(shard), nd, P.MODE_PLAIN)
+        plain = r.out.cpu().numpy().copy()
+        r2 = multi.run_sharded_native(ctx, dev, t.data_ptr(), len(shard), nd, P.MODE_RLE)
+        np.savez(outp + ".%d.npz" % rank, out=plain, begin=r.out_begin, rle=r2.records.cpu().numpy(),
+                 rle_first=r2.first_record, collectives=r.collectives)
     dist.barrier()
     ctx.close()
     dist.destroy_process_group()

@@ -220,8 +220,72 @@ def test_sharded_nccl_all_gpus(workdir):
     logs = [p.communicate(timeout=600)[0].decode() for p in procs]
     for p, lg in zip(procs, logs):
         assert p.returncode == 0, lg[-3000:]
-    parts = [np.load(os.path.join(workdir, "nccl_out.%d.npz" % r))["out"] for r in range(world)]
-    assert np.array_equal(np.concatenate(parts), O.Oracle(x).bwt(text))
+    zs = [np.load(os.path.join(workdir, "nccl_out.%d.npz" % r)) for r in range(world)]
+    want = O.Oracle(x).bwt(text)
+    assert np.array_equal(np.concatenate([z["out"] for z in zs]), want)
+    assert np.array_equal(np.concatenate([z["rle"] for z in zs]), O.rle(want))
+    cnt = 0
+    for z in zs:
+        assert int(z["begin"]) == sum(len(q["out"]) for q in zs[:zs.index(z)]) and int(z["rle_first"]) == cnt
+        cnt += len(z["rle"]) // 9
+
+
+def test_native_host_layer_one_rank():
+    """cmsbwt_run_sharded (C++ host layer, NCCL communicator of one rank) on a single GPU: every
+    exchange runs as a self send/receive; BWT and RLBWT against the oracle"""
+    dev = torch.device("cuda:0")
+    cases = []
+    ref, copies = gen_synth.make_collection(30000, 9, 0.004, 21)
+    cases.append((P.augment(ref), O.docs_to_text([np.zeros(0, np.uint8)] + copies)))
+    rng = np.random.default_rng(8)
+    ref = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 20000)]
+    mut = ref.copy()
+    for q in rng.integers(100, 19900, 40):
+        mut[q] = ord("A") if mut[q] != ord("A") else ord("C")
+    cases.append((P.augment(ref), O.docs_to_text([mut.copy(), ref.copy(), mut.copy(), mut[5000:].copy(), mut.copy()])))
+    for seed in (3, 7, 11):
+        c = fuzz_cases.make_case(seed)
+        t, nd = P.parse_collection(c["coll_file"])
+        if len(t) >= 40:
+            cases.append((P.augment(P.read_reference(c["ref_file"])), t))
+    ctx = P.Context(0)
+    try:
+        multi.comm_init(ctx, 0, 1, dev)
+        for x, text in cases:
+            want = O.Oracle(x).bwt(text)
+            ctx.index_upload(x)
+            t = torch.from_numpy(np.concatenate([text, np.full(64, 2, np.uint8)])).to(dev)
+            nd = int((text == 2).sum())
+            r = multi.run_sharded_native(ctx, dev, t.data_ptr(), len(text), nd, P.MODE_PLAIN)
+            assert r.out_begin == 0 and r.out_len == len(text) == r.N_total
+            assert np.array_equal(r.out.cpu().numpy(), want)
+            r2 = multi.run_sharded_native(ctx, dev, t.data_ptr(), len(text), nd, P.MODE_RLE)
+            assert r2.first_record == 0 and np.array_equal(r2.records.cpu().numpy(), O.rle(want))
+            assert r.collectives >= 8
+    finally:
+        ctx.close()
+
+
+@pytest.mark.parametrize("rle_mode", [False, True])
+def test_cli_gpus_option_matches_golden(workdir, rle_mode):
+    """cms_bwt --gpus W (C++ host: one thread per GPU, NCCL inside the library) on every visible GPU
+    (W = 1 on a single-GPU box) against a golden .bwt of the reference binary"""
+    z = np.load(os.path.join(GOLDEN, "synth_20k_x8.npz"))
+    d = os.path.join(workdir, "cli_gpus_%d" % rle_mode)
+    os.makedirs(d, exist_ok=True)
+    z["ref_file"].tofile(os.path.join(d, "ref.fa"))
+    z["coll_file"].tofile(os.path.join(d, "coll.fa"))
+    with open(os.path.join(d, "list.txt"), "w") as f:
+        f.write(os.path.join(d, "ref.fa") + "\n" + os.path.join(d, "coll.fa") + "\n")
+    world = max(1, min(4, torch.cuda.device_count()))
+    exe = os.path.join(os.path.dirname(HERE), "cms_bwt_b200", "cms_bwt")
+    cmd = [exe, "--gpus", str(world), "-o", os.path.join(d, "out")] + (["-r"] if rle_mode else []) + [os.path.join(d, "list.txt")]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=600)
+    assert r.returncode == 0 and b"==== Time elapsed:" in r.stdout, r.stdout.decode()[-3000:]
+    got = np.fromfile(os.path.join(d, "out.rl_bwt" if rle_mode else "out.bwt"), dtype=np.uint8)
+    want = O.rle(z["bwt"]) if rle_mode else z["bwt"]
+    assert np.array_equal(got, want)
+    assert "Multi-GPU path on %d GPUs" % world in open(os.path.join(d, "out.log")).read()
 
 
 @pytest.mark.parametrize("rle_mode", [False, True])
