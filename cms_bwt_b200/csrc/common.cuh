@@ -191,6 +191,7 @@ struct cmsbwt_ctx {
   i64 use_slots = 1;         // fast path: k-mer slot table (one 64-byte read per search) on / off
   i64 nb_t[3] = {48, 160, 512};   // tile placement: most ranges per tile for 1 / 4 / 8 kappa buckets
   i64 scatter_mb = 64;       // random 4-byte scatters run in passes over target regions of this many MB (L2)
+  i64 tile_count_max = 1024;  // ranges of a tile ranked by counting; more: bitonic sort (tests lower it)
   i64 tile_budget = 1ll << 36; // stage 2: brute-force tile counting up to this many pair tests per job
 };
 

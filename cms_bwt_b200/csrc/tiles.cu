@@ -348,6 +348,127 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
   }
 }
 
+// ---- pass B of the pull emit, single GPU: bucket sizes AND within(h) in one kernel ----------------------
+// within(h) = mates with a smaller kappa + ranges covering pos_h with a smaller kappa.  The tile's ranges
+// are SORTED by kappa in shared memory (kappas are distinct: different phrases end in different tails);
+// a head finds idx = #ranges with a smaller kappa by bisection and then tests only the shorter side for
+// coverage: the idx ranges below it, or -- through cov(q) = all ranges covering q, which the bucket sizes
+// need anyway -- the rc - idx ranges above it.  Nearly all heads are the short ones in front of a
+// mutation, whose class (match end E next to the position, :23-33 of match.h) is smaller or larger
+// than that of almost every covering range, so the shorter side holds a handful of ranges where the
+// round-1 kernel tested a quarter of the tile (k_tile_place: 4 kappa buckets by sampled pivots, 37 % of
+// its instructions in the pair tests, 11 us per tile).  Ranges are ranked by counting when there are at
+// most TR_COUNT_MAX of them (no barriers), by an in-place bitonic sort otherwise.
+#define TR_COUNT_MAX 1024u
+#define TR_MAX_ENTRIES 8192u          // heads + ranges of one tile (dynamic shared memory, see tile_rank_smem)
+static size_t tile_rank_smem(u32 maxent, u32 count_max) {
+  const u32 cm = maxent < count_max ? maxent : count_max;
+  return (size_t)maxent * 24 + (size_t)cm * 12 + 64;      // worst split: all ranges, padded to a power of two
+}
+__global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restrict__ he, const TileEnt *__restrict__ re,
+                                                          const u32 *__restrict__ hoff, const u32 *__restrict__ roff,
+                                                          u32 n, u32 count_max, uint2 *__restrict__ pcov,
+                                                          u64 *__restrict__ hw, u32 *within_out) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W], s_cov[LT_W];
+  __shared__ int s_d[LT_W + 1];
+  typedef cub::BlockScan<u32, LT_THREADS> BS;
+  typedef cub::BlockScan<int, LT_THREADS> BSI;
+  __shared__ typename BS::TempStorage ts;
+  __shared__ typename BSI::TempStorage tsi;
+  const u32 t = blockIdx.x, tid = threadIdx.x;
+  const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
+  const u32 hc = h1 - h0, rc = r1 - r0;
+  const bool counting = rc <= count_max;
+  u32 rcp = rc;                                  // bitonic: padded to a power of two
+  if (!counting) { rcp = 1; while (rcp < rc) rcp <<= 1; }
+  TileEnt *s_he = (TileEnt *)smem;               // hc heads, grouped by position
+  u64 *s_rk = (u64 *)(s_he + hc);                // range kappas, ascending
+  u32 *s_rl = (u32 *)(s_rk + rcp);               // their lo | hi << 16
+  u64 *s_rk0 = (u64 *)(((uintptr_t)(s_rl + rcp) + 7) & ~(uintptr_t)7);   // unsorted copies (counting only)
+  u32 *s_rl0 = (u32 *)(s_rk0 + (counting ? rc : 0));
+  s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0;
+  if (tid == 0) s_d[LT_W] = 0;
+  TileEnt he0;
+  he0.a = he0.b = 0; he0.kappa = 0;
+  if (tid < hc) he0 = he[h0 + tid];
+  __syncthreads();
+  for (u32 j = tid; j < rc; j += LT_THREADS) {
+    const TileEnt e = re[r0 + j];
+    if (counting) { s_rk0[j] = e.kappa; s_rl0[j] = e.a; }
+    else { s_rk[j] = e.kappa; s_rl[j] = e.a; }
+    atomicAdd(&s_d[e.a & 0xFFFF], 1);
+    atomicAdd(&s_d[(e.a >> 16) + 1], -1);
+  }
+  if (!counting)
+    for (u32 j = rc + tid; j < rcp; j += LT_THREADS) { s_rk[j] = ~0ull; s_rl[j] = 0x0000FFFFu; }   // lo > hi: covers nothing
+  for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[(j == tid ? he0 : he[h0 + j]).b & (LT_W - 1)], 1u);
+  __syncthreads();
+  {
+    const u32 hq = s_cnt[tid];
+    u32 ex;
+    int incl;
+    BS(ts).ExclusiveSum(hq, ex);
+    BSI(tsi).InclusiveSum(s_d[tid], incl);
+    s_off[tid] = ex;
+    s_cov[tid] = (u32)incl;
+    if (tid == LT_THREADS - 1) s_off[LT_W] = ex + hq;
+    const u32 p = (t << LT_SHIFT) + tid;
+    if (p <= n) pcov[p] = make_uint2((u32)incl + hq, h0 + ex);
+  }
+  __syncthreads();
+  // ranges in kappa order
+  if (counting) {
+    for (u32 j = tid; j < rc; j += LT_THREADS) {
+      const u64 k = s_rk0[j];
+      u32 rk = 0;
+      for (u32 i = 0; i < rc; i++) rk += s_rk0[i] < k;
+      s_rk[rk] = k;
+      s_rl[rk] = s_rl0[j];
+    }
+  } else {
+    for (u32 k2 = 2; k2 <= rcp; k2 <<= 1)
+      for (u32 j2 = k2 >> 1; j2 > 0; j2 >>= 1) {
+        __syncthreads();
+        for (u32 i = tid; i < rcp; i += LT_THREADS) {
+          const u32 x = i ^ j2;
+          if (x > i) {
+            const u64 a = s_rk[i], b = s_rk[x];
+            if ((a > b) == ((i & k2) == 0)) {
+              s_rk[i] = b; s_rk[x] = a;
+              const u32 la = s_rl[i]; s_rl[i] = s_rl[x]; s_rl[x] = la;
+            }
+          }
+        }
+      }
+  }
+  for (u32 j = tid; j < hc; j += LT_THREADS) {
+    const TileEnt e = j == tid ? he0 : he[h0 + j];
+    const u32 q = e.b & (LT_W - 1);
+    s_he[s_off[q] + atomicAdd(&s_cur[q], 1u)] = e;
+  }
+  __syncthreads();
+  for (u32 j = tid; j < hc; j += LT_THREADS) {
+    const TileEnt e = s_he[j];
+    const u32 q = e.b & (LT_W - 1);
+    const u64 kap = e.kappa;
+    u32 mates = 0;
+    for (u32 jj = s_off[q]; jj < s_off[q + 1]; jj++) mates += s_he[jj].kappa < kap;
+    u32 lo = 0, hi = rc;                          // idx = number of ranges with a smaller kappa
+    while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (s_rk[mid] < kap) lo = mid + 1; else hi = mid; }
+    u32 c = 0, w;
+    if (lo <= rc - lo) {
+      for (u32 r = 0; r < lo; r++) { const u32 lh = s_rl[r]; c += ((lh & 0xFFFF) <= q) & (q <= (lh >> 16)); }
+      w = mates + c;
+    } else {
+      for (u32 r = lo; r < rc; r++) { const u32 lh = s_rl[r]; c += ((lh & 0xFFFF) <= q) & (q <= (lh >> 16)); }
+      w = mates + s_cov[q] - c;
+    }
+    hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);     // grouped by position, ascending within
+    if (within_out) within_out[e.a] = w;
+  }
+}
+
 // terminators: bucket of x[n-1..] (SA rank 0) holds one suffix per document, in document order
 __global__ void k_place_sentinels(const u32 *len, const u16 *cs, const u32 *sexcl, u64 H, u8 *out,
                                   u32 *within_out, u64 *off_out) {
@@ -359,7 +480,6 @@ __global__ void k_place_sentinels(const u32 *len, const u16 *cs, const u32 *sexc
 }
 
 // Builds the tile entries and cov[]; false = too heavy for the brute-force path (nothing kept).
-static bool tiles_finish(cmsbwt_ctx *c, DBuf &acc, u32 HE, u64 R, DBuf &sexcl);
 // histogram + scan + scatter of this device's heads over ntiles tiles -> t_he, t_re, t_hoff, t_roff
 __global__ void k_tile_deepest(const u32 *hcnt, const u32 *rcnt, u32 ntiles, u32 *mx) {
   u32 t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -413,6 +533,7 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   CK(cudaStreamSynchronize(st));
   c->launches += 5;
   if (R >= 0xFFFFFFF0ull) return false;
+  c->tile_maxent = deepest;
   if (depth_limit && deepest > depth_limit) return false;
   CK(cub::DeviceScan::ExclusiveSum(tmp.p, t1, rcnt.as<u32>(), c->t_roff.as<u32>(), (int)(ntiles + 1), st));
   u32 HE = 0;
@@ -441,40 +562,18 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
 }
 
 bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
-  cudaStream_t st = c->st;
   const u32 n = c->ix.n;
   const u32 ntiles = (n >> LT_SHIFT) + 1;
   c->light = false;
-  DBuf acc;
-  acc.alloc(16, st);
-  CK(cudaMemsetAsync(acc.p, 0, 16, st));
   u32 HE = 0;
   u64 R = 0;
-  if (!tiles_scatter(c, kappa, ntiles, &HE, &R, LT_MAX_ENTRIES)) return false;
-  c->d_cov.release();
-  c->d_pcov.alloc(((size_t)ntiles * LT_W + 1) * 8, st);
-  k_tile_cov<<<ntiles, LT_THREADS, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                            c->t_roff.as<u32>(), n, (u32)c->stats.n_docs, 0, nullptr,
-                                            c->d_pcov.as<uint2>(), acc.as<unsigned long long>(), acc.as<u32>() + 2);
-  LAUNCH(c);
-  CK(cudaGetLastError());
-  return tiles_finish(c, acc, HE, R, sexcl);
-}
-
-static bool tiles_finish(cmsbwt_ctx *c, DBuf &acc, u32 HE, u64 R, DBuf &sexcl) {
-  cudaStream_t st = c->st;
-  unsigned long long hacc[2] = {0, 0};
-  CK(cudaMemcpyAsync(hacc, acc.p, 16, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  const u64 work = hacc[0];
-  const u32 maxent = (u32)hacc[1];
-  c->stats.n_items = (u64)HE + R;
-  c->stats.pair_tests = work;
-  if (work > (u64)c->tile_budget || maxent > LT_MAX_ENTRIES) {
-    c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release(); c->d_pcov.release();
+  // a tile deeper than shared memory holds sends the whole job to the sort-based sweep (heads.cu)
+  if (!tiles_scatter(c, kappa, ntiles, &HE, &R, TR_MAX_ENTRIES)) {
+    c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release();
     return false;
   }
-  c->tile_maxent = maxent;
+  c->stats.n_items = (u64)HE + R;
+  c->stats.pair_tests = 0;
   c->n_hw = HE;
   c->h_sexcl.release();
   c->h_sexcl.swap(sexcl);
@@ -503,17 +602,14 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   u32 *wo = nullptr;
   if (c->dump) { c->h_within.alloc(H * 4, st); wo = c->h_within.as<u32>(); }
   c->d_hw.alloc(((size_t)c->n_hw + 1) * 8, st);
+  c->d_pcov.alloc(((size_t)ntiles * LT_W + 1) * 8, st);
   c->d_termsym.alloc((size_t)c->stats.n_docs + 16, st);
-  size_t sm = (size_t)c->tile_maxent * sizeof(TileEnt) + 64;
-  // static (24 KB of bucket rows) + dynamic shared memory above 48 KB needs the opt-in; a fresh
-  // process that starts with a tile of 1.6-2.5 K entries failed here before (threshold was 40 KB
-  // of dynamic memory alone)
-  if (sm > 16 * 1024)
-    CK(cudaFuncSetAttribute(k_tile_place, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  k_tile_place<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                               c->t_roff.as<u32>(), c->ix.isa, nullptr, n, 0, nullptr, nullptr, wo,
-                                               nullptr, make_int3((int)c->nb_t[0], (int)c->nb_t[1], (int)c->nb_t[2]),
-                                               c->d_hw.as<u64>());
+  u32 cm = (u32)c->tile_count_max;
+  if (cm > TR_COUNT_MAX) cm = TR_COUNT_MAX;
+  const size_t sm = tile_rank_smem(c->tile_maxent, cm);
+  if (sm > 32 * 1024) CK(cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_tile_rank<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+                                              c->t_roff.as<u32>(), n, cm, c->d_pcov.as<uint2>(), c->d_hw.as<u64>(), wo);
   k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
                                                      c->d_termsym.as<u8>(), wo);
   c->launches += 2;
