@@ -137,7 +137,7 @@ int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
     cudaSetDevice(c->dev);
     if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v) != cudaSuccess) { cudaGetLastError(); return CMSBWT_E_CUDA; }
   }
-  else if (!strcmp(name, "tile_count_max")) { if (v < 0) return CMSBWT_E_ARG; c->tile_count_max = v; }
+  else if (!strcmp(name, "tile_margin")) { if (v < 0 || v > (1 << 30)) return CMSBWT_E_ARG; c->tile_margin = v; }
   else if (!strcmp(name, "tile_budget")) { if (v < 0) return CMSBWT_E_ARG; c->tile_budget = v; }
   else return CMSBWT_E_ARG;
   return CMSBWT_OK;

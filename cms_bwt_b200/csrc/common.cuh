@@ -191,7 +191,7 @@ struct cmsbwt_ctx {
   i64 use_slots = 1;         // fast path: k-mer slot table (one 64-byte read per search) on / off
   i64 nb_t[3] = {48, 160, 512};   // tile placement: most ranges per tile for 1 / 4 / 8 kappa buckets
   i64 scatter_mb = 64;       // random 4-byte scatters run in passes over target regions of this many MB (L2)
-  i64 tile_count_max = 1024;  // ranges of a tile ranked by counting; more: bitonic sort (tests lower it)
+  i64 tile_margin = 48;       // k_tile_rank: heads / ranges with a match end below tile end + margin are "near"
   i64 tile_budget = 1ll << 36; // stage 2: brute-force tile counting up to this many pair tests per job
 };
 
@@ -257,6 +257,10 @@ void shard_emit(cmsbwt_ctx *c, const u32 *cov_full, u64 N_total, u32 world, u32 
 void shard_apply(cmsbwt_ctx *c, const u64 *plc, u64 cnt);
 void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N);
 void tiles_count_heads(cmsbwt_ctx *c);
+// product-owned LSD radix sort (rsort.cu): k / v = input and sorted output, k2 / v2 = scratch (swapped)
+void rsort_pairs32(cmsbwt_ctx *c, DBuf &k, DBuf &k2, DBuf &v, DBuf &v2, u64 n, int begin_bit, int end_bit);
+void rsort_pairs64(cmsbwt_ctx *c, DBuf &k, DBuf &k2, DBuf &v, DBuf &v2, u64 n, int begin_bit, int end_bit);
+void rsort_keys64(cmsbwt_ctx *c, DBuf &k, DBuf &k2, u64 n, int begin_bit, int end_bit);
 void emit_stage(cmsbwt_ctx *c, int mode);
 
 // ---------------------------------------------------------------------------------------------

@@ -293,21 +293,12 @@ void sweep_count(cmsbwt_ctx *c, u64 I, DBuf &it_tr, DBuf &it_key, DBuf &it_pay, 
   it_tr2.alloc(I * 4, st); it_key2.alloc(I * 8, st); idx.alloc(I * 4, st); idx2.alloc(I * 4, st);
   const u32 gI = (u32)((I + B - 1) / B);
   k_iota<<<gI, B, 0, st>>>(idx2.as<u32>(), I);
-  tb = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, it_tr.as<u32>(), it_tr2.as<u32>(), idx2.as<u32>(),
-                                  idx.as<u32>(), (int)I, 0, tbits, st);
-  tmp.need(tb, st);
-  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_tr.as<u32>(), it_tr2.as<u32>(),
-                                     idx2.as<u32>(), idx.as<u32>(), (int)I, 0, tbits, st));
+  rsort_pairs32(c, it_tr, it_tr2, idx2, idx, I, 0, tbits);
+  it_tr.swap(it_tr2); idx2.swap(idx);             // sorted by tail rank: it_tr2 / idx
   k_gather_keys<<<gI, B, 0, st>>>(idx.as<u32>(), it_key.as<u64>(), I, it_key2.as<u64>());
   int kb = cshift + 1; while ((1ull << (kb - cshift)) < (u64)ntiles + 1) kb++;
-  tb = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
-                                  idx2.as<u32>(), (int)I, 0, kb, st);
-  tmp.need(tb, st);
-  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, it_key2.as<u64>(), it_key.as<u64>(), idx.as<u32>(),
-                                     idx2.as<u32>(), (int)I, 0, kb, st));
-  c->launches += 12;
+  rsort_pairs64(c, it_key2, it_key, idx, idx2, I, 0, kb);       // stable: the tail-rank order survives inside (tile, cls)
+  it_key2.swap(it_key); idx.swap(idx2);           // sorted by (tile, cls): it_key / idx2
   DBuf tbeg, tend;
   tbeg.alloc(((size_t)ntiles + 1) * 4, st); tend.alloc(((size_t)ntiles + 1) * 4, st);
   CK(cudaMemsetAsync(tbeg.p, 0, ((size_t)ntiles + 1) * 4, st));

@@ -59,8 +59,6 @@ void sa_build_device(cmsbwt_ctx *c, const u8 *d_x, u32 n, i32 *d_sa) {
   rank.alloc((size_t)n * 4, st); gs.alloc((size_t)n * 4, st);
   cnt.alloc(4, st);
   size_t tb = 0, tb2 = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, key.as<u64>(), key2.as<u64>(), idx.as<u32>(),
-                                  idx2.as<u32>(), (int)n, 0, 64, st);
   cub::DeviceScan::InclusiveScan(nullptr, tb2, gs.as<u32>(), gs.as<u32>(), cub::Max(), (int)n, st);
   if (tb2 > tb) tb = tb2;
   tmp.alloc(tb, st);
@@ -70,8 +68,8 @@ void sa_build_device(cmsbwt_ctx *c, const u8 *d_x, u32 n, i32 *d_sa) {
   u32 h = 8;
   for (int round = 0; round < 40; round++) {
     size_t t = tb;
-    CK(cub::DeviceRadixSort::SortPairs(tmp.p, t, key.as<u64>(), key2.as<u64>(), idx.as<u32>(),
-                                       idx2.as<u32>(), (int)n, 0, 64, st));
+    rsort_pairs64(c, key, key2, idx, idx2, n, 0, 64);
+    key.swap(key2); idx.swap(idx2);               // sorted: key2 / idx2
     CK(cudaMemsetAsync(cnt.p, 0, 4, st));
     k_count_groups<<<g, B, 0, st>>>(key2.as<u64>(), n, cnt.as<u32>());
     u32 groups = 0;

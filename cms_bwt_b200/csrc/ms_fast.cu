@@ -246,16 +246,11 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   const u64 nseps = hsep;
   if (nseps >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 documents"};
   {                                   // sort the separator positions, add the sentinel
-    DBuf sorted;
-    sorted.alloc((nseps + 1) * 8, st);
+    DBuf alt;
+    alt.alloc((nseps + 1) * 8, st);
     int bits = 1; while (bits < 64 && (1ull << bits) < N) bits++;
-    size_t tb = 0;
-    cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_seps.as<u64>(), sorted.as<u64>(), (int)nseps, 0, bits, st);
-    tmp.alloc(tb, st);
-    CK(cub::DeviceRadixSort::SortKeys(tmp.p, tb, c->d_seps.as<u64>(), sorted.as<u64>(), (int)nseps, 0, bits, st));
-    CK(cudaMemsetAsync(sorted.as<u64>() + nseps, 0xFF, 8, st));
-    c->d_seps.swap(sorted);
-    c->launches += 2;
+    rsort_keys64(c, c->d_seps, alt, nseps, 0, bits);
+    CK(cudaMemsetAsync(c->d_seps.as<u64>() + nseps, 0xFF, 8, st));
   }
   DBuf wsep, wfirst, wcnt, wfp, wlp, wadj, woff, counter, nbused;
   wsep.alloc(nwin * 4, st); wfirst.alloc(nwin * 4, st); wcnt.alloc(nwin * 4, st);

@@ -130,11 +130,8 @@ void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32
   const int bits = key_bits > 32 ? 32 : key_bits;
   size_t tb = 0;
   if (tie_by_id) CK(cudaMemsetAsync(tie_by_id, 0, Tn, st));
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, key32.as<u32>(), key32s.as<u32>(), id.as<u32>(), ids.as<u32>(),
-                                  (int)Tn, 0, bits, st);
-  tmp.need(tb, st);
-  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, key32.as<u32>(), key32s.as<u32>(), id.as<u32>(),
-                                     ids.as<u32>(), (int)Tn, 0, bits, st));
+  rsort_pairs32(c, key32, key32s, id, ids, Tn, 0, bits);
+  key32.swap(key32s); id.swap(ids);             // sorted: key32s / ids; key32 / id are scratch from here on
   k_tr_gs32<<<gT, B, 0, st>>>(key32s.as<u32>(), Tn, gs.as<u32>());
   max_scan(tmp, gs.as<u32>(), Tn, st);
   {
@@ -161,6 +158,7 @@ void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32
     DBuf key, keys, sub2, grp, sg, jt;
     key.alloc((size_t)m * 8, st); keys.alloc((size_t)m * 8, st); sub2.alloc((size_t)m * 4, st);
     grp.alloc((size_t)m * 4, st); sg.alloc((size_t)m * 4, st); jt.alloc((size_t)m * 4, st);
+    if (id.bytes < (size_t)m * 4) id.alloc((size_t)m * 4, st);      // (after the swap id may be the smaller buffer)
     u32 *sub = id.as<u32>(), *subs = sub2.as<u32>();
     int tbits = 1;
     while (tbits < 32 && (1ull << tbits) < (u64)Tn) tbits++;
@@ -169,12 +167,9 @@ void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32
       const u32 gM = (m + B - 1) / B;
       if (first) k_tr_key_cls<<<gM, B, 0, st>>>(sub, m, trank, label, cls32, key.as<u64>());
       else k_tr_key_next<<<gM, B, 0, st>>>(sub, m, trank, nexth, key.as<u64>());
-      tb = 0;
-      cub::DeviceRadixSort::SortPairs(nullptr, tb, key.as<u64>(), keys.as<u64>(), sub, subs, (int)m, 0,
-                                      32 + tbits, st);
-      tmp.need(tb, st);
-      CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, key.as<u64>(), keys.as<u64>(), sub, subs, (int)m, 0,
-                                         32 + tbits, st));
+      rsort_pairs64(c, key, keys, id, sub2, m, 0, 32 + tbits);
+      key.swap(keys); id.swap(sub2);              // sorted: keys / sub2
+      sub = id.as<u32>(); subs = sub2.as<u32>();
       k_tr_gs64<<<gM, B, 0, st>>>(keys.as<u64>(), m, grp.as<u32>(), sg.as<u32>());
       max_scan(tmp, grp.as<u32>(), m, st);
       max_scan(tmp, sg.as<u32>(), m, st);
@@ -243,11 +238,8 @@ void shard_tails_sort(cmsbwt_ctx *c) {
   c->sh_cs.alloc((size_t)Tn * 4 + 16, st);
   const int bits = c->s_key_bits > 32 ? 32 : c->s_key_bits;
   size_t tb = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, c->s_key32.as<u32>(), c->sh_ks.as<u32>(), c->s_tid.as<u32>(),
-                                  c->sh_perm.as<u32>(), (int)Tn, 0, bits, st);
-  tmp.need(tb, st);
-  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, c->s_key32.as<u32>(), c->sh_ks.as<u32>(), c->s_tid.as<u32>(),
-                                     c->sh_perm.as<u32>(), (int)Tn, 0, bits, st));
+  rsort_pairs32(c, c->s_key32, c->sh_ks, c->s_tid, c->sh_perm, Tn, 0, bits);
+  c->s_key32.swap(c->sh_ks); c->s_tid.swap(c->sh_perm);      // sorted: sh_ks / sh_perm
   k_sh_gather_cls<<<gT, B, 0, st>>>(c->sh_perm.as<u32>(), c->s_label.as<u64>(), Tn, c->sh_cs.as<u32>());
   c->launches += 6;
   CK(cudaGetLastError());
@@ -314,11 +306,13 @@ u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off)
   const u32 gM = (m_total + B - 1) / B;
   k_sh_iota<<<gM, B, 0, st>>>(ids0.as<u32>(), m_total);
   size_t tb = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, tb, allkeys, keys.as<u64>(), ids0.as<u32>(), ids.as<u32>(), (int)m_total,
-                                  0, 64, st);
-  tmp.need(tb, st);
-  CK(cub::DeviceRadixSort::SortPairs(tmp.b.p, tb, allkeys, keys.as<u64>(), ids0.as<u32>(), ids.as<u32>(),
-                                     (int)m_total, 0, 64, st));
+  {
+    DBuf kin;
+    kin.alloc((size_t)m_total * 8, st);
+    CK(cudaMemcpyAsync(kin.p, allkeys, (size_t)m_total * 8, cudaMemcpyDeviceToDevice, st));
+    rsort_pairs64(c, kin, keys, ids0, ids, m_total, 0, 64);
+    kin.swap(keys); ids0.swap(ids);               // sorted: keys / ids
+  }
   k_tr_gs64<<<gM, B, 0, st>>>(keys.as<u64>(), m_total, grp.as<u32>(), sg.as<u32>());
   max_scan(tmp, grp.as<u32>(), m_total, st);
   max_scan(tmp, sg.as<u32>(), m_total, st);

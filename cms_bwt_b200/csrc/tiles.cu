@@ -349,59 +349,62 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
 }
 
 // ---- pass B of the pull emit, single GPU: bucket sizes AND within(h) in one kernel ----------------------
-// within(h) = mates with a smaller kappa + ranges covering pos_h with a smaller kappa.  The tile's ranges
-// are SORTED by kappa in shared memory (kappas are distinct: different phrases end in different tails);
-// a head finds idx = #ranges with a smaller kappa by bisection and then tests only the shorter side for
-// coverage: the idx ranges below it, or -- through cov(q) = all ranges covering q, which the bucket sizes
-// need anyway -- the rc - idx ranges above it.  Nearly all heads are the short ones in front of a
-// mutation, whose class (match end E next to the position, :23-33 of match.h) is smaller or larger
-// than that of almost every covering range, so the shorter side holds a handful of ranges where the
-// round-1 kernel tested a quarter of the tile (k_tile_place: 4 kappa buckets by sampled pivots, 37 % of
-// its instructions in the pair tests, 11 us per tile).  Ranges are ranked by counting when there are at
-// most TR_COUNT_MAX of them (no barriers), by an in-place bitonic sort otherwise.
-#define TR_COUNT_MAX 1024u
-#define TR_MAX_ENTRIES 8192u          // heads + ranges of one tile (dynamic shared memory, see tile_rank_smem)
-static size_t tile_rank_smem(u32 maxent, u32 count_max) {
-  const u32 cm = maxent < count_max ? maxent : count_max;
-  return (size_t)maxent * 24 + (size_t)cm * 12 + 64;      // worst split: all ranges, padded to a power of two
-}
+// within(h) = mates with a smaller kappa + ranges covering pos_h with a smaller kappa (:1517-1603).
+// kappa = (cls, tail rank) with cls = smaller ? E : ~E (match.h:23-33): every "smaller" phrase precedes
+// every other one, by ascending / descending match end E.  With X = end of the tile + TR_MARGIN, a range
+// or head is NEAR when its E < X.  Then, exactly:
+//   near head, smaller:      only near smaller ranges can have a lower kappa
+//                            within = mates + #{near smaller ranges: kappa < kappa_h, covers q}
+//   near head, not smaller:  only near not-smaller ranges can have a higher kappa
+//                            within = mates + cov(q) - #{near not-smaller ranges: kappa > kappa_h, covers q}
+//   far head:                all ranges are tested, by a whole warp (32 ranges per step)
+// cov(q) = ranges covering q comes from the difference array the bucket sizes need anyway.  Nearly all
+// heads are the short ones in front of a mutation (near); the near lists hold the few phrases that end
+// around the tile, so a head tests ~15 ranges instead of a quarter of the tile (round 1: 4 kappa buckets
+// by sampled pivots, per-bucket coverage rows; 37 % of the instructions in divergent pair tests), no
+// sorting, no pivots, and lanes of a warp walk the same list.
+#define TR_MARGIN 48u
+#define TR_MAX_ENTRIES 8192u          // heads + ranges of one tile (dynamic shared memory: 24 bytes per entry)
+static size_t tile_rank_smem(u32 maxent) { return (size_t)maxent * 24 + 64; }
+__device__ __forceinline__ u32 tr_covers(u32 lh, u32 q) { return ((lh & 0xFFFF) <= q) & (q <= (lh >> 16)); }
 __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restrict__ he, const TileEnt *__restrict__ re,
                                                           const u32 *__restrict__ hoff, const u32 *__restrict__ roff,
-                                                          u32 n, u32 count_max, uint2 *__restrict__ pcov,
+                                                          u32 n, u32 margin, uint2 *__restrict__ pcov,
                                                           u64 *__restrict__ hw, u32 *within_out) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W], s_cov[LT_W];
   __shared__ int s_d[LT_W + 1];
+  __shared__ u32 s_c1, s_c0, s_cf, s_nfar;
   typedef cub::BlockScan<u32, LT_THREADS> BS;
   typedef cub::BlockScan<int, LT_THREADS> BSI;
   __shared__ typename BS::TempStorage ts;
   __shared__ typename BSI::TempStorage tsi;
-  const u32 t = blockIdx.x, tid = threadIdx.x;
+  const u32 t = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
   const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
   const u32 hc = h1 - h0, rc = r1 - r0;
-  const bool counting = rc <= count_max;
-  u32 rcp = rc;                                  // bitonic: padded to a power of two
-  if (!counting) { rcp = 1; while (rcp < rc) rcp <<= 1; }
   TileEnt *s_he = (TileEnt *)smem;               // hc heads, grouped by position
-  u64 *s_rk = (u64 *)(s_he + hc);                // range kappas, ascending
-  u32 *s_rl = (u32 *)(s_rk + rcp);               // their lo | hi << 16
-  u64 *s_rk0 = (u64 *)(((uintptr_t)(s_rl + rcp) + 7) & ~(uintptr_t)7);   // unsorted copies (counting only)
-  u32 *s_rl0 = (u32 *)(s_rk0 + (counting ? rc : 0));
+  u64 *s_nk = (u64 *)(s_he + hc);                // near ranges: smaller ones from the front, the others from the back
+  u64 *s_fk = s_nk + rc;                         // far ranges
+  u32 *s_nl = (u32 *)(s_fk + rc);                // lo | hi << 16 of the near / far ranges
+  u32 *s_fl = s_nl + rc;
+  u32 *s_far = s_fl + rc;                        // far heads (indices into s_he)
+  const u64 Xl = (u64)((t + 1) << LT_SHIFT) + margin;
+  const u32 X = Xl > 0x7FFFFFFFull ? 0x7FFFFFFFu : (u32)Xl;
   s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0;
-  if (tid == 0) s_d[LT_W] = 0;
+  if (tid == 0) { s_d[LT_W] = 0; s_c1 = 0; s_c0 = 0; s_cf = 0; s_nfar = 0; }
   TileEnt he0;
   he0.a = he0.b = 0; he0.kappa = 0;
   if (tid < hc) he0 = he[h0 + tid];
   __syncthreads();
   for (u32 j = tid; j < rc; j += LT_THREADS) {
     const TileEnt e = re[r0 + j];
-    if (counting) { s_rk0[j] = e.kappa; s_rl0[j] = e.a; }
-    else { s_rk[j] = e.kappa; s_rl[j] = e.a; }
+    const u32 cls = (u32)(e.kappa >> 32);
+    if (cls < X) { const u32 k = atomicAdd(&s_c1, 1u); s_nk[k] = e.kappa; s_nl[k] = e.a; }
+    else if (cls > 0xFFFFFFFFu - X) { const u32 k = rc - 1 - atomicAdd(&s_c0, 1u); s_nk[k] = e.kappa; s_nl[k] = e.a; }
+    else { const u32 k = atomicAdd(&s_cf, 1u); s_fk[k] = e.kappa; s_fl[k] = e.a; }
     atomicAdd(&s_d[e.a & 0xFFFF], 1);
     atomicAdd(&s_d[(e.a >> 16) + 1], -1);
   }
-  if (!counting)
-    for (u32 j = rc + tid; j < rcp; j += LT_THREADS) { s_rk[j] = ~0ull; s_rl[j] = 0x0000FFFFu; }   // lo > hi: covers nothing
   for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[(j == tid ? he0 : he[h0 + j]).b & (LT_W - 1)], 1u);
   __syncthreads();
   {
@@ -417,55 +420,51 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     if (p <= n) pcov[p] = make_uint2((u32)incl + hq, h0 + ex);
   }
   __syncthreads();
-  // ranges in kappa order
-  if (counting) {
-    for (u32 j = tid; j < rc; j += LT_THREADS) {
-      const u64 k = s_rk0[j];
-      u32 rk = 0;
-      for (u32 i = 0; i < rc; i++) rk += s_rk0[i] < k;
-      s_rk[rk] = k;
-      s_rl[rk] = s_rl0[j];
-    }
-  } else {
-    for (u32 k2 = 2; k2 <= rcp; k2 <<= 1)
-      for (u32 j2 = k2 >> 1; j2 > 0; j2 >>= 1) {
-        __syncthreads();
-        for (u32 i = tid; i < rcp; i += LT_THREADS) {
-          const u32 x = i ^ j2;
-          if (x > i) {
-            const u64 a = s_rk[i], b = s_rk[x];
-            if ((a > b) == ((i & k2) == 0)) {
-              s_rk[i] = b; s_rk[x] = a;
-              const u32 la = s_rl[i]; s_rl[i] = s_rl[x]; s_rl[x] = la;
-            }
-          }
-        }
-      }
-  }
   for (u32 j = tid; j < hc; j += LT_THREADS) {
     const TileEnt e = j == tid ? he0 : he[h0 + j];
     const u32 q = e.b & (LT_W - 1);
     s_he[s_off[q] + atomicAdd(&s_cur[q], 1u)] = e;
   }
   __syncthreads();
+  const u32 c1 = s_c1, c0 = s_c0, cf = s_cf;
   for (u32 j = tid; j < hc; j += LT_THREADS) {
     const TileEnt e = s_he[j];
     const u32 q = e.b & (LT_W - 1);
     const u64 kap = e.kappa;
+    const u32 cls = (u32)(kap >> 32);
     u32 mates = 0;
     for (u32 jj = s_off[q]; jj < s_off[q + 1]; jj++) mates += s_he[jj].kappa < kap;
-    u32 lo = 0, hi = rc;                          // idx = number of ranges with a smaller kappa
-    while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (s_rk[mid] < kap) lo = mid + 1; else hi = mid; }
     u32 c = 0, w;
-    if (lo <= rc - lo) {
-      for (u32 r = 0; r < lo; r++) { const u32 lh = s_rl[r]; c += ((lh & 0xFFFF) <= q) & (q <= (lh >> 16)); }
+    if (cls < X) {
+      for (u32 r = 0; r < c1; r++) c += (s_nk[r] < kap) & tr_covers(s_nl[r], q);
       w = mates + c;
-    } else {
-      for (u32 r = lo; r < rc; r++) { const u32 lh = s_rl[r]; c += ((lh & 0xFFFF) <= q) & (q <= (lh >> 16)); }
+    } else if (cls > 0xFFFFFFFFu - X) {
+      for (u32 r = rc - c0; r < rc; r++) c += (s_nk[r] > kap) & tr_covers(s_nl[r], q);
       w = mates + s_cov[q] - c;
+    } else {
+      s_far[atomicAdd(&s_nfar, 1u)] = j | (mates << 16);      // hc, mates <= 8192
+      continue;
     }
     hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);     // grouped by position, ascending within
     if (within_out) within_out[e.a] = w;
+  }
+  __syncthreads();
+  const u32 nfar = s_nfar;
+  for (u32 f = tid >> 5; f < nfar; f += LT_THREADS / 32) {
+    const u32 fj = s_far[f], j = fj & 0xFFFF, mates = fj >> 16;
+    const TileEnt e = s_he[j];
+    const u32 q = e.b & (LT_W - 1);
+    const u64 kap = e.kappa;
+    u32 c = 0;
+    for (u32 r = lane; r < c1; r += 32) c += (s_nk[r] < kap) & tr_covers(s_nl[r], q);
+    for (u32 r = rc - c0 + lane; r < rc; r += 32) c += (s_nk[r] < kap) & tr_covers(s_nl[r], q);
+    for (u32 r = lane; r < cf; r += 32) c += (s_fk[r] < kap) & tr_covers(s_fl[r], q);
+    c = __reduce_add_sync(0xffffffffu, c);
+    if (lane == 0) {
+      const u32 w = mates + c;
+      hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);
+      if (within_out) within_out[e.a] = w;
+    }
   }
 }
 
@@ -604,12 +603,11 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   c->d_hw.alloc(((size_t)c->n_hw + 1) * 8, st);
   c->d_pcov.alloc(((size_t)ntiles * LT_W + 1) * 8, st);
   c->d_termsym.alloc((size_t)c->stats.n_docs + 16, st);
-  u32 cm = (u32)c->tile_count_max;
-  if (cm > TR_COUNT_MAX) cm = TR_COUNT_MAX;
-  const size_t sm = tile_rank_smem(c->tile_maxent, cm);
+  const size_t sm = tile_rank_smem(c->tile_maxent);
   if (sm > 32 * 1024) CK(cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_rank<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                              c->t_roff.as<u32>(), n, cm, c->d_pcov.as<uint2>(), c->d_hw.as<u64>(), wo);
+                                              c->t_roff.as<u32>(), n, (u32)c->tile_margin, c->d_pcov.as<uint2>(),
+                                              c->d_hw.as<u64>(), wo);
   k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
                                                      c->d_termsym.as<u8>(), wo);
   c->launches += 2;

@@ -29,8 +29,9 @@ def _inputs(ref_file, coll_file, prefix=P.UINT64_MAX):
 
 
 MODES = {                       # which kernels run (DESIGN.md sections 3-5)
-    "fast+tiles": dict(fast=1, tile_budget=1 << 36, tile_count_max=1024),     # 2-bit lane kernel + tile kernels
-    "fast+tiles/bitonic": dict(fast=1, tile_budget=1 << 36, tile_count_max=3),   # ranges of a tile sorted by the bitonic network
+    "fast+tiles": dict(fast=1, tile_budget=1 << 36, tile_margin=48),     # 2-bit lane kernel + tile kernels
+    "fast+tiles/far": dict(fast=1, tile_budget=1 << 36, tile_margin=0),  # same, nearly every head takes the "far" path
+    "fast+tiles/near": dict(fast=1, tile_budget=1 << 36, tile_margin=1 << 30),   # same, every head and range is "near"
     "general+sweep": dict(fast=0, tile_budget=0),        # 8-bit warp kernel + sort-based sweep
     "fast+sweep": dict(fast=1, tile_budget=0),
 }
@@ -102,7 +103,7 @@ def test_fuzz_vs_oracle(ctx, block):
         x, text = _inputs(c["ref_file"], c["coll_file"])
         if len(text) == 0:
             continue
-        for mode in ("fast+tiles", "general+sweep") + (("fast+tiles/bitonic",) if seed % 5 == 0 else ()):
+        for mode in ("fast+tiles", "general+sweep") + (("fast+tiles/far", "fast+tiles/near") if seed % 5 == 0 else ()):
             _check_case(ctx, x, text, None, c["desc"], chunk=[64, 100, 8192][seed % 3], mode=mode)
 
 
