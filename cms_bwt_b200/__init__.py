@@ -45,7 +45,7 @@ class Stats(C.Structure):
                 ("rank_rounds", C.c_uint32), ("kmer_k", C.c_uint32),
                 ("kernel_launches", C.c_uint64), ("pack_ms", C.c_double),
                 ("fast_path", C.c_uint32), ("light_tiles", C.c_uint32), ("pair_tests", C.c_uint64),
-                ("rank_tied", C.c_uint64), ("group_ms", C.c_double * 12)]
+                ("rank_tied", C.c_uint64), ("group_ms", C.c_double * 12), ("n_escapes", C.c_uint64)]
 
     GROUPS = ("pack", "ms", "gather", "rank", "tiles", "offsets", "fill", "place", "rle")
 

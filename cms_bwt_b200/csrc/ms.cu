@@ -313,6 +313,7 @@ __global__ void k_compact(const u64 *pg, const u32 *pp, const u32 *pl, const u16
 void ms_stage(cmsbwt_ctx *c) {
   cudaStream_t st = c->st;
   c->stats.fast_path = 0;
+  c->stats.n_escapes = 0;
   c->stats.pack_ms = 0;
   if (c->fast && c->pure && c->chunk_len <= 0x7FFFFFFF && ms_stage_fast(c)) return;
   const u64 N = c->N;

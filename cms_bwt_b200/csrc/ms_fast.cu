@@ -45,9 +45,10 @@ __global__ void __launch_bounds__(256) k_pack(const u8 *src, u64 len, u64 *dst, 
             u32 ch = (w >> (8 * bb)) & 0xFF;
             if (pb + bb >= len) continue;
             if (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') c8 |= msf_code_of(ch) << (2 * bb);
-            else if (ch == 2 && seps) {
+            else if (seps && (ch == 2 || (ch >= 3 && ch <= 127))) {     // separator, or an escape (any other legal symbol)
               unsigned long long k = atomicAdd(nsep, 1ull);
-              if (k < sepcap) seps[k] = pb + bb;
+              if (k < sepcap) seps[k] = ((pb + bb) << 1) | (ch != 2 ? 1ull : 0ull);
+              if (ch != 2) atomicAdd(nsep + 1, 1ull);
             } else bad = true;
           }
         }
@@ -59,91 +60,23 @@ __global__ void __launch_bounds__(256) k_pack(const u8 *src, u64 len, u64 *dst, 
   }
 }
 
-// Experiment (not the default): the same packing with one 16-byte load and one
-// 4-byte store per thread and iteration -- consecutive lanes read consecutive 16-byte vectors
-// (k_pack's lanes are 32 bytes apart, so each of its two loads touches every sector of a 1 KB span
-// for half of its bytes), four independent loads in flight.  Same bytes out (a 64-bit word is its
-// two little-endian halves), bit-exact in the parity tests, but 1.78 ms against k_pack's 1.58 ms at
-// config 3: the second load of k_pack hits L1, and its 8-byte stores are half as many.
-__device__ __forceinline__ u32 pack16(uint4 a, u64 p0, u64 len, u64 *seps, u64 sepcap,
-                                      unsigned long long *nsep, bool &bad) {
-  u32 v[4] = {a.x, a.y, a.z, a.w};
-  u32 half = 0;
-#pragma unroll
-  for (int t = 0; t < 4; t++) {
-    u32 w = v[t];
-    bool clean;
-    u32 c8 = pack4(w, clean);
-    if (!clean || p0 + 4 * t + 4 > len) {
-      const u64 pb = p0 + 4 * t;
-      c8 = 0;
-#pragma unroll
-      for (int bb = 0; bb < 4; bb++) {
-        u32 ch = (w >> (8 * bb)) & 0xFF;
-        if (pb + bb >= len) continue;
-        if (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') c8 |= msf_code_of(ch) << (2 * bb);
-        else if (ch == 2 && seps) {
-          unsigned long long k = atomicAdd(nsep, 1ull);
-          if (k < sepcap) seps[k] = pb + bb;
-        } else bad = true;
-      }
-    }
-    half |= c8 << (8 * t);
-  }
-  return half;
-}
-
-__global__ void __launch_bounds__(256) k_pack16(const u8 *src, u64 len, u32 *dst, u64 nhalf, u64 *seps,
-                                                u64 sepcap, unsigned long long *nsep, u32 *flags) {
-  const u64 S = (u64)gridDim.x * blockDim.x;
-  bool bad = false;
-  for (u64 j0 = (u64)blockIdx.x * blockDim.x + threadIdx.x; j0 < nhalf; j0 += 4 * S) {
-    uint4 a[4];
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      const u64 j = j0 + u * S;
-      a[u] = (j < nhalf && j * 16 < len) ? __ldg((const uint4 *)(src + j * 16)) : make_uint4(0, 0, 0, 0);
-    }
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      const u64 j = j0 + u * S;
-      if (j >= nhalf) break;
-      dst[j] = j * 16 < len ? pack16(a[u], j * 16, len, seps, sepcap, nsep, bad) : 0u;
-    }
-  }
-  if (bad) flags[0] = 1;
-}
-
-static int pack_variant() {        // measurement switch: CMSBWT_PACK=1 selects k_pack16 (measured slower: 1.78 against 1.58 ms)
-  static int v = -1;
-  if (v < 0) { const char *e = getenv("CMSBWT_PACK"); v = e ? atoi(e) : 0; }
-  return v;
-}
-
 void pack_2bit(cmsbwt_ctx *c, const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps, u64 sepcap,
                unsigned long long *nsep, u32 *flags) {
   u64 blocks = (nwords + 255) / 256;
   if (blocks > 148 * 64) blocks = 148 * 64;
-  if (pack_variant() == 1) {
-    const u64 nhalf = nwords * 2;
-    u64 b16 = (nhalf + 1023) / 1024;
-    if (b16 > 148 * 32) b16 = 148 * 32;
-    if (b16 < 1) b16 = 1;
-    k_pack16<<<(u32)b16, 256, 0, c->st>>>(src, len, (u32 *)dst, nhalf, seps, sepcap, nsep, flags);
-  } else
   k_pack<<<(u32)blocks, 256, 0, c->st>>>(src, len, dst, nwords, seps, sepcap, nsep, flags);
   LAUNCH(c);
   CK(cudaGetLastError());
 }
 
-// index of the first separator >= window start
+// index of the first break (separator or escape, MSF_BRK_*) at or after the window start
 __global__ void k_wsep(const u64 *seps, u64 nseps, u32 WL, u64 nwin, u32 *wsep) {
   u64 w = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   if (w >= nwin) return;
   u64 key = w * WL, lo = 0, hi = nseps;
   while (lo < hi) {
     u64 mid = (lo + hi) >> 1;
-    if (seps[mid] < key) lo = mid + 1; else hi = mid;
+    if (MSF_BRK_POS(seps[mid]) < key) lo = mid + 1; else hi = mid;
   }
   wsep[w] = (u32)lo;
 }
@@ -220,9 +153,10 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   const u64 nwords = (N + 31) / 32 + MSF_PAD_WORDS;
   c->d_tp.alloc(nwords * 8, st);
   DBuf flags, nsep, tmp;
-  flags.alloc(8, st); nsep.alloc(8, st);
+  flags.alloc(8, st); nsep.alloc(16, st);
   u64 sepcap = c->sep_hint ? c->sep_hint + 16 : (N / 1024 + (1u << 16));
-  unsigned long long hsep = 0;
+  unsigned long long hsep2[2] = {0, 0};
+  unsigned long long &hsep = hsep2[0];
   u32 hf[2] = {0, 0};
   cudaEvent_t e0, e1, e2;
   cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
@@ -231,24 +165,27 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   for (int attempt = 0; attempt < 2; attempt++) {
     c->d_seps.alloc((sepcap + 1) * 8, st);
     CK(cudaMemsetAsync(flags.p, 0, 8, st));
-    CK(cudaMemsetAsync(nsep.p, 0, 8, st));
+    CK(cudaMemsetAsync(nsep.p, 0, 16, st));
     pack_2bit(c, c->text, N, c->d_tp.as<u64>(), nwords, c->d_seps.as<u64>(), sepcap,
               nsep.as<unsigned long long>(), flags.as<u32>());
-    CK(cudaMemcpyAsync(&hsep, nsep.p, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hsep2, nsep.p, 16, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hf, flags.p, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    if (hf[0]) { delete gpack; cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); return false; }
+    // a byte outside 2..127, or so many escapes (lower-case genomes: every other symbol) that the break
+    // list would outgrow the text: the general 8-bit kernel takes the job
+    if (hf[0] || hsep2[1] > N / 32 + 4096) { delete gpack; cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); return false; }
     if (hsep <= sepcap) break;
     if (attempt == 1) throw CmsErr{CMSBWT_E_INTERNAL, "separator list overflow on exact-size rerun"};
     sepcap = hsep;
   }
   c->sep_hint = hsep;
+  c->stats.n_escapes = hsep2[1];
   const u64 nseps = hsep;
   if (nseps >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 documents"};
   {                                   // sort the separator positions, add the sentinel
     DBuf alt;
     alt.alloc((nseps + 1) * 8, st);
-    int bits = 1; while (bits < 64 && (1ull << bits) < N) bits++;
+    int bits = 2; while (bits < 64 && (1ull << bits) < 2 * N) bits++;       // position << 1 | escape
     rsort_keys64(c, c->d_seps, alt, nseps, 0, bits);
     CK(cudaMemsetAsync(c->d_seps.as<u64>() + nseps, 0xFF, 8, st));
   }
@@ -281,7 +218,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     P.slots = c->d_slots.as<u64>();
     P.xp = c->xp; P.x8 = c->ix.x; P.sak = c->d_sak.as<u64>(); P.ktab = c->ix.ktab; P.G = c->ix.G;
     P.n = c->ix.n; P.n_acgt = c->n_acgt; P.k = c->ix.k;
-    P.tp = c->d_tp.as<u64>(); P.N = N; P.seps = c->d_seps.as<u64>(); P.nseps = nseps; P.wsep = wsep.as<u32>();
+    P.tp = c->d_tp.as<u64>(); P.t8 = c->text; P.N = N; P.seps = c->d_seps.as<u64>(); P.nseps = nseps; P.wsep = wsep.as<u32>();
     P.WL = WL; P.nwin = nwin; P.skip_min = (u32)c->skip_min; P.variant = (u32)c->ms_variant;
     P.pool = pool.as<u32>(); P.batch_next = bnext.as<u32>(); P.nb_cap = (u32)nb; P.nb_used = nbused.as<u32>();
     P.wfirst = wfirst.as<u32>(); P.wcnt = wcnt.as<u32>(); P.wfirstpos = wfp.as<u32>(); P.wlastpos = wlp.as<u32>();

@@ -17,6 +17,14 @@
 //   D  skip (warp-cooperative): after a long match, the first q in (pos, E) with G[q] >= E
 //      (:1176-1185 as a search) from one coalesced read of the 32 entries below E.
 //
+// Symbols other than A, C, G, T in the TEXT (N, IUPAC codes, lower case: the reference program takes any
+// byte 3..127 through its augmentation, :231-237) do not leave this path: the 2-bit stream holds an
+// arbitrary code at such a position and the position is listed, with the separators, in the sorted
+// BREAK list (position << 1 | escape).  A match that starts before a break is limited by it exactly as
+// by a separator, the byte that decides the order at the limit is read from the 8-bit text, and the
+// (rare) escape positions themselves -- and matches that run through an escape into the augmentation
+// -- take an exact byte-wise search (msf_escape_search).  MS is still the sequential definition.
+//
 // The neighbour rule is the one of :53-76 as restated in ms.cu: the successor wins ties
 // (smaller = 1).  This header is plain C++ when compiled without nvcc so that the same lane code
 // is run on the CPU by tests/harness (test infrastructure; the product only ever runs it inside
@@ -74,6 +82,9 @@ struct msf_rec4 { msf_u32 x, y, z, w; };
 #define MSF_PAD_WORDS 4             // zero words readable past the last packed word
 
 enum { MSF_S_FETCH = 0, MSF_S_POS, MSF_S_BIN, MSF_S_SCAN, MSF_S_EQ, MSF_S_DONE };
+// break list entries: position << 1 | (1 = escape: a symbol outside A,C,G,T; 0 = document separator)
+#define MSF_BRK_POS(v) ((msf_u64)(v) >> 1)
+#define MSF_BRK_ESC(v) ((msf_u32)((v) & 1ull))
 
 // ---- 2-bit helpers -----------------------------------------------------------------------------
 // Packed layout: base j lives in word j >> 5, bits [2 (j & 31), 2 (j & 31) + 2); A,C,G,T = 0,1,2,3.
@@ -170,11 +181,12 @@ struct MsfParams {
   msf_u32 n, n_acgt;
   int k;
   // text
-  const msf_u64 *tp;      // packed text (separators hold arbitrary codes)
+  const msf_u64 *tp;      // packed text (breaks hold arbitrary codes)
+  const msf_u8 *t8;       // the text as parsed (8-bit): read only at breaks
   msf_u64 N;
-  const msf_u64 *seps;    // sorted separator positions, seps[nseps] = ~0
+  const msf_u64 *seps;    // sorted break list (separators and escapes, MSF_BRK_*), seps[nseps] = ~0
   msf_u64 nseps;
-  const msf_u32 *wsep;    // per window: index of the first separator >= window start
+  const msf_u32 *wsep;    // per window: index of the first break >= window start
   msf_u32 WL;             // window length
   msf_u64 nwin;
   msf_u32 skip_min;       // try the G skip when len >= skip_min
@@ -195,6 +207,7 @@ struct MsfParams {
 struct MsfLane {
   msf_u64 i, w1, sepnext;
   msf_u32 sepidx, w;
+  msf_u32 sepesc, prevesc;   // the next break is an escape; the previous position was one
   msf_u32 state, prevpos, prevterm, first;
   msf_u32 curb, fill, cnt;
   msf_u32 limit;
@@ -302,8 +315,42 @@ MSF_HD bool msf_compare(const MsfParams &P, msf_u64 i, msf_u32 limit, msf_u32 s,
   msf_u32 maxl = limit < room ? limit : room;
   m = msf_lce(P.tp, i, P.xp, s, maxl);
   xb = MSF_LD8(P.x8 + s + m);
-  tb = m == limit ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, i + m));
+  tb = m == limit ? (msf_u32)MSF_LD8(P.t8 + i + m) : (msf_u32)msf_sym_of(msf_base(P.tp, i + m));
+  if (m == limit && xb == tb) {        // an escape that the reference (its augmentation) continues: bytes from here
+    do { m++; xb = MSF_LD8(P.x8 + s + m); tb = MSF_LD8(P.t8 + i + m); } while (xb == tb);
+  }
   return xb < tb;
+}
+
+// exact search of the text suffix at i on the 8-bit data (escape positions): same neighbour rule.
+// The separator 0x02 occurs nowhere in x and x[n-1] = 0 is its unique smallest symbol, so the byte
+// comparison stops by itself.
+MSF_HDN void msf_escape_search(const MsfParams &P, msf_u64 i, msf_u32 &pos, msf_u32 &len, msf_u32 &sm) {
+  msf_u32 lo = 0, hi = P.n;
+  const msf_u8 *t = P.t8 + i;
+  while (lo < hi) {
+    const msf_u32 mid = lo + ((hi - lo) >> 1);
+    const msf_u8 *x = P.x8 + (msf_u32)(MSF_LD64(P.sak + mid) >> 32);
+    msf_u32 m = 0;
+    while (MSF_LD8(x + m) == MSF_LD8(t + m)) m++;
+    if (MSF_LD8(x + m) < MSF_LD8(t + m)) lo = mid + 1; else hi = mid;
+  }
+  long long lp = -1, ls = -1;
+  msf_u32 ppos = 0, spos = 0;
+  if (lo > 0) {
+    ppos = (msf_u32)(MSF_LD64(P.sak + lo - 1) >> 32);
+    msf_u32 m = 0;
+    while (MSF_LD8(P.x8 + ppos + m) == MSF_LD8(t + m)) m++;
+    lp = m;
+  }
+  if (lo < P.n) {
+    spos = (msf_u32)(MSF_LD64(P.sak + lo) >> 32);
+    msf_u32 m = 0;
+    while (MSF_LD8(P.x8 + spos + m) == MSF_LD8(t + m)) m++;
+    ls = m;
+  }
+  if (ls >= lp) { pos = spos; len = (msf_u32)ls; sm = 1; }
+  else { pos = ppos; len = (msf_u32)lp; sm = 0; }
 }
 
 // exact search on packed data (rare cases); same result as lane_search()/warp_search() in ms.cu
@@ -352,24 +399,34 @@ MSF_HD void msf_dump(const MsfParams &P, msf_u64 p, msf_u32 pos, msf_u32 len, ms
 #define MSF_ACT_TERM 4u       // position L.i is a document terminator
 #define MSF_ACT_EXT 8u        // extend the candidate L.pos from L.len matched bases (phase B)
 #define MSF_ACT_SKIP 16u      // long match recorded: find the end of its non-head run (phase D)
+#define MSF_ACT_ESC 32u       // position L.i holds an escape symbol: exact byte-wise search, then FIN
 
+MSF_HD void msf_next_break(const MsfParams &P, MsfLane &L) {
+  const msf_u64 v = MSF_LD64(P.seps + L.sepidx);
+  L.sepnext = MSF_BRK_POS(v);
+  L.sepesc = MSF_BRK_ESC(v);
+}
 // phase C: head test (:1154), record, step.  term: L.i holds a separator (:1198-1212).
 // Returns MSF_ACT_SKIP when the non-head run after this head has to be looked up.
-MSF_HD msf_u32 msf_fin(const MsfParams &P, MsfLane &L, bool term) {
+// esc: L.i holds an escape symbol (its MS comes from msf_escape_search; no skip follows it)
+MSF_HD msf_u32 msf_fin(const MsfParams &P, MsfLane &L, bool term, bool esc = false) {
   const bool tent = !term && L.first && !L.prevterm;   // window starts inside a document
   const bool head = term || L.prevterm || L.pos != L.prevpos + 1;
   if (L.first) P.wfirstpos[L.w] = (term || L.prevterm) ? MSF_INVALID : L.pos;
   if (head || tent) {
-    msf_u32 ch = L.prevterm ? 2u : (msf_u32)msf_sym_of(L.chb < 4 ? L.chb : msf_base(P.tp, L.i - 1));
+    msf_u32 ch = L.prevterm ? 2u : L.prevesc ? (msf_u32)MSF_LD8(P.t8 + L.i - 1)
+                                             : (msf_u32)msf_sym_of(L.chb < 4 ? L.chb : msf_base(P.tp, L.i - 1));
     msf_emit(P, L, (msf_u32)(L.i - (msf_u64)L.w * P.WL), L.pos, L.len, ch | (L.sm << 8) | (tent ? 1u << 9 : 0u));
   }
   msf_dump(P, L.i, L.pos, L.len, L.sm, head || tent);
   L.first = 0;
   L.prevterm = term ? 1u : 0u;
+  L.prevesc = esc ? 1u : 0u;
   L.state = MSF_S_POS;
-  if (term) {
+  if (term || esc) {
     L.sepidx++;
-    L.sepnext = MSF_LD64(P.seps + L.sepidx);
+    msf_next_break(P, L);
+    if (esc) L.prevpos = L.pos;
     L.i++;
     return MSF_ACT_NONE;
   }
@@ -386,6 +443,11 @@ MSF_HD void msf_skip_to(const MsfParams &P, MsfLane &L, msf_u32 q) {
     for (msf_u32 k2 = 1; k2 <= skip; k2++) msf_dump(P, L.i + k2, L.pos + k2, L.len - k2, L.sm, 0);
   L.i += 1 + (msf_u64)skip;
   L.prevpos = L.pos + skip;
+  if (L.sepnext < L.i) {                 // the match ran through escapes: the run skipped over their breaks
+    msf_u64 pb = 0;
+    do { pb = MSF_LD64(P.seps + L.sepidx); L.sepidx++; msf_next_break(P, L); } while (L.sepnext < L.i);
+    L.prevesc = (MSF_BRK_POS(pb) == L.i - 1 && MSF_BRK_ESC(pb)) ? 1u : 0u;
+  }
 }
 
 // single candidate s whose key equals the text's: hand it to the warp (or to the exact search)
@@ -419,7 +481,12 @@ MSF_HD void msf_ext_done(const MsfParams &P, MsfLane &L, msf_u32 res, msf_u32 bm
   if (res != 0xFFFFFFFFu && (res >> 1) < bmax) { L.len = res >> 1; L.sm = res & 1u; return; }
   L.len = bmax;
   msf_u32 xb = MSF_LD8(P.x8 + L.pos + bmax);
-  msf_u32 tb = bmax == L.limit ? 2u : (msf_u32)msf_sym_of(msf_base(P.tp, L.i + bmax));
+  msf_u32 tb = bmax == L.limit ? (msf_u32)MSF_LD8(P.t8 + L.i + bmax) : (msf_u32)msf_sym_of(msf_base(P.tp, L.i + bmax));
+  if (bmax == L.limit && xb == tb) {   // the single candidate continues through an escape: bytes from here
+    msf_u32 m = bmax;
+    do { m++; xb = MSF_LD8(P.x8 + L.pos + m); tb = MSF_LD8(P.t8 + L.i + m); } while (xb == tb);
+    L.len = m;
+  }
   L.sm = xb > tb ? 1u : 0u;
 }
 
@@ -457,8 +524,13 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
       L.i = w * P.WL;
       L.w1 = L.i + P.WL < P.N ? L.i + P.WL : P.N;
       L.sepidx = MSF_LD32(P.wsep + w);
-      L.sepnext = MSF_LD64(P.seps + L.sepidx);
-      L.prevterm = (L.i == 0) || (L.sepidx > 0 && MSF_LD64(P.seps + L.sepidx - 1) == L.i - 1);
+      msf_next_break(P, L);
+      {
+        const msf_u64 pb = L.sepidx > 0 ? MSF_LD64(P.seps + L.sepidx - 1) : 0;
+        const bool adj = L.sepidx > 0 && MSF_BRK_POS(pb) == L.i - 1;
+        L.prevterm = (L.i == 0) || (adj && !MSF_BRK_ESC(pb));
+        L.prevesc = (L.i != 0 && adj && MSF_BRK_ESC(pb)) ? 1u : 0u;
+      }
       L.prevpos = MSF_INVALID;
       L.first = 1;
       MSF_TCW(L) = 0xFFFFFFFFu;
@@ -477,8 +549,9 @@ MSF_HD msf_u32 msf_search_step(const MsfParams &P, MsfLane &L) {
         break;
       }
       L.chb = 4;
-      if (L.i == L.sepnext) {                             // document terminator (:1198-1212)
-        L.pos = P.n - 1; L.len = 0; L.sm = 0;
+      if (L.i == L.sepnext) {
+        if (L.sepesc) { act = MSF_ACT_ESC; break; }       // a symbol outside A,C,G,T
+        L.pos = P.n - 1; L.len = 0; L.sm = 0;             // document terminator (:1198-1212)
         act = MSF_ACT_TERM;
         break;
       }
@@ -641,7 +714,8 @@ __device__ __forceinline__ void msf_warp_iter(const MsfParams &P, MsfLane &L) {
   }
   // phase C
   if (act & MSF_ACT_GENERIC) msf_generic_search(P, L.i, L.limit, L.pos, L.len, L.sm);
-  if (act) act = msf_fin(P, L, (act & MSF_ACT_TERM) != 0);
+  if (act & MSF_ACT_ESC) msf_escape_search(P, L.i, L.pos, L.len, L.sm);
+  if (act) act = msf_fin(P, L, (act & MSF_ACT_TERM) != 0, (act & MSF_ACT_ESC) != 0);
   // phase D: cooperative skip
   unsigned sk = __ballot_sync(FULL, act == MSF_ACT_SKIP);
   while (sk) {
@@ -706,7 +780,8 @@ inline void msf_warp_iter_host(const MsfParams &P, MsfLane *W, int nl) {
   for (int l = 0; l < nl; l++) {                          // phase C
     MsfLane &L = W[l];
     if (act[l] & MSF_ACT_GENERIC) msf_generic_search(P, L.i, L.limit, L.pos, L.len, L.sm);
-    if (act[l]) act[l] = msf_fin(P, L, (act[l] & MSF_ACT_TERM) != 0);
+    if (act[l] & MSF_ACT_ESC) msf_escape_search(P, L.i, L.pos, L.len, L.sm);
+    if (act[l]) act[l] = msf_fin(P, L, (act[l] & MSF_ACT_TERM) != 0, (act[l] & MSF_ACT_ESC) != 0);
   }
   for (int l = 0; l < nl; l++) {                          // phase D
     if (act[l] != MSF_ACT_SKIP) continue;

@@ -79,6 +79,7 @@ typedef struct {
   /* CUDA-event time of the kernel groups of the last job (single-GPU path), milliseconds; the sum is
    * ms_ms + sort_ms + emit_ms minus host gaps.  Indices: CMSBWT_G_* below. */
   double group_ms[12];
+  uint64_t n_escapes;       /* text symbols outside A,C,G,T that the 2-bit kernel took through its break list */
 } cmsbwt_stats;
 
 enum {

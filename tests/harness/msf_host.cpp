@@ -39,9 +39,9 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   for (u32 j = n_acgt; j < n; j++)
     if (x[j] == 'A' || x[j] == 'C' || x[j] == 'G' || x[j] == 'T') return -1;
   if (n_acgt == 0 || x[n_acgt] >= 'A') return -1;
-  for (u64 j = 0; j < N; j++) {
+  for (u64 j = 0; j < N; j++) {          // any legal symbol: the others are escapes in the break list
     u8 c = text[j];
-    if (!(c == 2 || c == 'A' || c == 'C' || c == 'G' || c == 'T')) return -1;
+    if (c < 2 || c > 127) return -1;
   }
   // ---- index ----
   std::vector<u64> xp, tp;
@@ -72,14 +72,20 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   for (u32 i = 0; i < n; i++) G[i] = i + (u32)plcp_prime[i];
   // ---- text ----
   pack(text, N, tp);
-  std::vector<u64> seps;
-  for (u64 j = 0; j < N; j++) if (text[j] == 2) seps.push_back(j);
+  std::vector<u64> seps;                 // break list: position << 1 | escape (ms_fast.cu: k_pack + sort)
+  for (u64 j = 0; j < N; j++) {
+    const u8 c = text[j];
+    if (c == 2) seps.push_back(j << 1);
+    else if (!(c == 'A' || c == 'C' || c == 'G' || c == 'T')) seps.push_back((j << 1) | 1);
+  }
   const u64 nseps = seps.size();
   seps.push_back(~0ull);
   const u64 nwin = (N + WL - 1) / WL;
   std::vector<u32> wsep(nwin);
   for (u64 w = 0; w < nwin; w++)
-    wsep[w] = (u32)(std::lower_bound(seps.begin(), seps.begin() + nseps, w * WL) - seps.begin());
+    wsep[w] = (u32)(std::lower_bound(seps.begin(), seps.begin() + nseps, (w * WL) << 1) - seps.begin());
+  std::vector<u8> t8(text, text + N);
+  t8.resize(N + 64, 2);
   // ---- run ----
   const u64 nb_cap = N / MSF_RB + 2 * nwin + 16;
   std::vector<u32> pool(nb_cap * MSF_RB * 4), bnext(nb_cap), wfirst(nwin), wcnt(nwin, 0), wfp(nwin), wlp(nwin);
@@ -89,7 +95,7 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   P.slots = use_slots ? slots.data() : nullptr;
   P.xp = xp.data(); P.x8 = x8.data(); P.sak = sak.data(); P.ktab = ktab.data(); P.G = G.data();
   P.n = n; P.n_acgt = n_acgt; P.k = k;
-  P.tp = tp.data(); P.N = N; P.seps = seps.data(); P.nseps = nseps; P.wsep = wsep.data();
+  P.tp = tp.data(); P.t8 = t8.data(); P.N = N; P.seps = seps.data(); P.nseps = nseps; P.wsep = wsep.data();
   P.WL = WL; P.nwin = nwin; P.skip_min = skip_min; P.variant = use_slots == 2 ? 2u | 16u : 2u;   // use_slots 2: empty-bucket slots too
   P.pool = pool.data(); P.batch_next = bnext.data(); P.nb_cap = (u32)nb_cap; P.nb_used = &nb_used;
   P.wfirst = wfirst.data(); P.wcnt = wcnt.data(); P.wfirstpos = wfp.data(); P.wlastpos = wlp.data();

@@ -131,3 +131,40 @@ def test_small_k_and_repeats(harness):
     ref, copies = gen_synth.make_collection(3000, 300, 0.003, 9)
     short = [c[a:a + ln] for c in copies for a, ln in ((5, 11), (40, 30), (100, 3))]
     assert run_case(harness, O.augment(ref), O.docs_to_text(short), 64, desc="short docs") is not None
+
+
+def _sprinkle(text, rng, rate, symbols=b"NnRYacgt\x03\x7f@B"):
+    """replaces symbols of the documents (never a separator) by symbols outside A,C,G,T"""
+    t = text.copy()
+    idx = np.flatnonzero(t != 2)
+    pick = idx[rng.random(len(idx)) < rate]
+    t[pick] = np.frombuffer(symbols, np.uint8)[rng.integers(0, len(symbols), len(pick))]
+    return t
+
+
+@pytest.mark.parametrize("WL", [64, 1000])
+def test_text_escapes(harness, WL):
+    """symbols outside A,C,G,T in the TEXT (N, IUPAC, lower case, the first and last augmentation symbols)
+    stay on the 2-bit path through the break list: per-position MS against the oracle"""
+    rng = np.random.default_rng(17)
+    ref, copies = gen_synth.make_collection(30000, 5, 0.003, 4)
+    x = O.augment(ref)
+    base = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    for rate in (0.0005, 0.01, 0.2):
+        assert run_case(harness, x, _sprinkle(base, rng, rate), WL, desc="escapes %g" % rate) is not None
+    # runs of escapes, escapes next to separators and at document starts, a run that copies the augmentation
+    t = base.copy()
+    ends = np.flatnonzero(t == 2)
+    for e in ends[1:4]:
+        t[e - 1] = ord("N"); t[e + 1] = ord("n")
+    t[100:140] = ord("N")
+    aug = x[len(ref):len(x) - 2]
+    t[2000:2000 + 30] = aug[:30]                      # matches the augmentation itself for 30 symbols
+    t[3000:3005] = aug[-5:]
+    t[5000 - 1] = ref[-1]; t[5000:5000 + 10] = aug[:10]  # reference end + augmentation: a match through an escape
+    k = len(ref) - 40
+    t[7000:7040] = ref[k:k + 40]; t[7040:7045] = aug[:5]
+    assert run_case(harness, x, t, WL, desc="escape runs") is not None
+    # short documents made of escapes only
+    docs = [np.frombuffer(b"NNNN", np.uint8), np.frombuffer(b"N", np.uint8), ref[50:90].copy(), np.frombuffer(b"ACNGT", np.uint8)]
+    assert run_case(harness, x, O.docs_to_text(docs), 64, desc="escape documents") is not None
