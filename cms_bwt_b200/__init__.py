@@ -31,6 +31,7 @@ EXPORTS = [
     "cmsbwt_shard_rle",
     "cmsbwt_nccl_unique_id", "cmsbwt_comm_init", "cmsbwt_comm_destroy", "cmsbwt_run_sharded",
     "cmsbwt_sharded_after_ms", "cmsbwt_sharded_rle", "cmsbwt_sharded_stats",
+    "cmsbwt_fm_build", "cmsbwt_fm_count", "cmsbwt_fm_free",
     "cmsbwt_parse_collection_mt", "cmsbwt_parse_piece", "cmsbwt_line_start",
     "cmsbwt_host_alloc", "cmsbwt_host_free", "cmsbwt_text_begin", "cmsbwt_text_append",
     "cmsbwt_ms_run_staged", "cmsbwt_result_read", "cmsbwt_copy_fence", "cmsbwt_copy_wait",
@@ -116,6 +117,9 @@ def lib():
         L.cmsbwt_result_read.argtypes = [vp, vp, u64, u64]
         L.cmsbwt_copy_fence.argtypes = [vp, C.c_int]
         L.cmsbwt_copy_wait.argtypes = [vp, C.c_int]
+        L.cmsbwt_fm_build.argtypes = [vp, C.POINTER(C.c_uint32)]
+        L.cmsbwt_fm_count.argtypes = [vp, vp, vp, C.c_uint32, vp]
+        L.cmsbwt_fm_free.argtypes = [vp]
         L.cmsbwt_nccl_unique_id.argtypes = [vp]
         L.cmsbwt_comm_init.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
         L.cmsbwt_comm_destroy.argtypes = [vp]
@@ -299,6 +303,24 @@ class Context:
             out = np.empty(self.out_bytes, np.uint8)
         self._ck(lib().cmsbwt_result_download(self.h, _p(out), out.nbytes))
         return out[:self.out_bytes]
+
+    def fm_build(self):
+        """FM-index over the plain BWT the last emit left on the device -> number of distinct symbols"""
+        k = C.c_uint32()
+        self._ck(lib().cmsbwt_fm_build(self.h, C.byref(k)))
+        return k.value
+
+    def fm_count(self, patterns):
+        """occurrences of every pattern (bytes / uint8 arrays) in the collection, by backward search on the GPU"""
+        pats = [np.frombuffer(p, np.uint8) if isinstance(p, (bytes, bytearray)) else np.ascontiguousarray(p, np.uint8)
+                for p in patterns]
+        off = np.zeros(len(pats) + 1, np.uint64)
+        off[1:] = np.cumsum([len(p) for p in pats])
+        flat = np.concatenate(pats) if pats else np.zeros(0, np.uint8)
+        flat = np.ascontiguousarray(np.concatenate([flat, np.zeros(1, np.uint8)]))
+        out = np.zeros(len(pats), np.uint64)
+        self._ck(lib().cmsbwt_fm_count(self.h, _p(flat), _p(off), len(pats), _p(out)))
+        return out
 
     def run(self, text, mode=MODE_PLAIN, out=None):
         """ms_run + heads_sort + emit + download on host buffers (the drop-in call)."""

@@ -85,6 +85,7 @@ void cmsbwt_ctx_destroy(cmsbwt_ctx *c) {
     cudaStreamDestroy(c->st_copy);
   }
   cmsbwt_comm_destroy(c);
+  fm_release(c);
   group_reset(c);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
   c->ev_pool.clear();

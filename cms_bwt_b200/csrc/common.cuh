@@ -173,6 +173,7 @@ struct cmsbwt_ctx {
   u32 comm_rank = 0, comm_world = 1;
   double sh_phase_ms[16] = {};
   u64 sh_collectives = 0, sh_comm_bytes = 0, sh_rle_first = 0, sh_rle_skip = 0;
+  void *fm = nullptr;        // FM-index built from the last plain result (fmindex.cu)
   // stage 3
   DBuf d_out, d_rle;
   u64 out_bytes = 0, rle_off = 0;   // rle_off: bytes of d_rle that belong to the rank on the left (sharded -r)
@@ -257,6 +258,7 @@ void shard_emit(cmsbwt_ctx *c, const u32 *cov_full, u64 N_total, u32 world, u32 
 void shard_apply(cmsbwt_ctx *c, const u64 *plc, u64 cnt);
 void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N);
 void tiles_count_heads(cmsbwt_ctx *c);
+void fm_release(cmsbwt_ctx *c);
 // product-owned LSD radix sort (rsort.cu): k / v = input and sorted output, k2 / v2 = scratch (swapped)
 void rsort_pairs32(cmsbwt_ctx *c, DBuf &k, DBuf &k2, DBuf &v, DBuf &v2, u64 n, int begin_bit, int end_bit);
 void rsort_pairs64(cmsbwt_ctx *c, DBuf &k, DBuf &k2, DBuf &v, DBuf &v2, u64 n, int begin_bit, int end_bit);

@@ -285,6 +285,18 @@ int cmsbwt_sharded_rle(cmsbwt_ctx *ctx, const void **d_records, uint64_t *n_reco
 int cmsbwt_sharded_stats(const cmsbwt_ctx *ctx, uint64_t *collectives, uint64_t *exchange_bytes, double *phase_ms,
                          uint32_t phase_cap);
 
+/* ---- consumer of the output, fed from device memory (the reference stops at the files it
+ * writes, :1631-1777) ----
+ * cmsbwt_fm_build: FM-index over the plain BWT the last cmsbwt_emit left on the device (symbol counts +
+ * one occurrence checkpoint per 256 symbols); *n_symbols = distinct symbols (at most 16).
+ * cmsbwt_fm_count: batched backward search: counts[k] = occurrences of pattern k (bytes
+ * patterns[offsets[k] .. offsets[k+1]), host arrays) in the whole collection; a pattern must not hold
+ * the separator.  The index is valid until the next cmsbwt_ms_run* on the context. */
+int cmsbwt_fm_build(cmsbwt_ctx *ctx, uint32_t *n_symbols);
+int cmsbwt_fm_count(cmsbwt_ctx *ctx, const uint8_t *patterns, const uint64_t *offsets, uint32_t npat,
+                    uint64_t *counts);
+int cmsbwt_fm_free(cmsbwt_ctx *ctx);
+
 /* tuning knobs: "chunk_len" (text window of an MS lane; 0 = by text length, 1024..8192), "kmer_k"
  * (order of the k-mer table, 0 = largest k <= 14 with 4^k <= n; takes effect at the next
  * index_upload), "fast" (0: 8-bit warp kernel for every input), "tile_budget" (0: sort-based sweep
