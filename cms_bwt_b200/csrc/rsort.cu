@@ -77,7 +77,7 @@ __device__ __forceinline__ void rs_rank(const K (&key)[RS_ITEMS], int shift, u32
 }
 
 template <class K, bool VALS>
-__global__ void __launch_bounds__(RS_THREADS) k_rs_pass(const K *__restrict__ kin, K *__restrict__ kout,
+__global__ void __launch_bounds__(RS_THREADS, sizeof(K) == 4 ? 3 : 2) k_rs_pass(const K *__restrict__ kin, K *__restrict__ kout,
                                                         const u32 *__restrict__ vin, u32 *__restrict__ vout, u64 n,
                                                         int shift, const unsigned long long *__restrict__ gbase,
                                                         volatile unsigned long long *status, u32 *ticket) {
@@ -103,9 +103,15 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_pass(const K *__restrict__ ki
   for (int r = 0; r < RS_ITEMS; r++) {
     const u32 li = w * (32 * RS_ITEMS) + r * 32 + l;
     key[r] = li < nvalid ? kin[base + li] : (K)~(K)0;     // padding sorts behind every key of the last digit
-    if (VALS) val[r] = li < nvalid ? vin[base + li] : 0u;
   }
   rs_rank<K>(key, shift, s_cnt, rank);
+  if (VALS) {                                             // values are not live while the keys are ranked
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; r++) {
+      const u32 li = w * (32 * RS_ITEMS) + r * 32 + l;
+      val[r] = li < nvalid ? vin[base + li] : 0u;
+    }
+  }
   __syncthreads();
   // exclusive prefix over the warps per digit; tile counts; their exclusive scan over the digits
   u32 tile_cnt = 0;

@@ -364,69 +364,92 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
 // by sampled pivots, per-bucket coverage rows; 37 % of the instructions in divergent pair tests), no
 // sorting, no pivots, and lanes of a warp walk the same list.
 #define TR_MARGIN 48u
+#define TR_SHORT 8u                   // near ranges covering at most this many positions are filed per position
 #define TR_MAX_ENTRIES 8192u          // heads + ranges of one tile (dynamic shared memory: 24 bytes per entry)
-static size_t tile_rank_smem(u32 maxent) { return (size_t)maxent * 24 + 64; }
+// Most near ranges are SHORT: the heads in front of a mutation that are followed by a few non-heads (ncu,
+// config 3: ~190 ranges per tile, ~100 of them near, while a head has ~2 of them over its position).
+// They are filed under every position they cover (at most TR_SHORT 16-bit indices each, room
+// permitting: 40 instead of 24 bytes per entry), so that a head walks its position's incidences like
+// its mates instead of the whole near list.
+static size_t tile_rank_smem(u32 maxent, bool with_short) { return (size_t)maxent * (with_short ? 40 : 24) + 64; }
 __device__ __forceinline__ u32 tr_covers(u32 lh, u32 q) { return ((lh & 0xFFFF) <= q) & (q <= (lh >> 16)); }
 __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restrict__ he, const TileEnt *__restrict__ re,
                                                           const u32 *__restrict__ hoff, const u32 *__restrict__ roff,
-                                                          u32 n, u32 margin, uint2 *__restrict__ pcov,
+                                                          u32 n, u32 margin, u32 smem_bytes, uint2 *__restrict__ pcov,
                                                           u64 *__restrict__ hw, u32 *within_out) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W], s_cov[LT_W];
+  __shared__ u32 s_icnt[LT_W], s_ioff[LT_W + 1];
   __shared__ int s_d[LT_W + 1];
-  __shared__ u32 s_c1, s_c0, s_cf, s_nfar;
+  __shared__ u32 s_c1, s_c0, s_cs, s_cf, s_nfar;
   typedef cub::BlockScan<u32, LT_THREADS> BS;
   typedef cub::BlockScan<int, LT_THREADS> BSI;
   __shared__ typename BS::TempStorage ts;
+  __shared__ typename BS::TempStorage ts2;
   __shared__ typename BSI::TempStorage tsi;
   const u32 t = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
   const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
   const u32 hc = h1 - h0, rc = r1 - r0;
+  const bool shorts = (size_t)hc * 20 + (size_t)rc * 40 + 64 <= smem_bytes;   // room for the incidence lists
   TileEnt *s_he = (TileEnt *)smem;               // hc heads, grouped by position
-  u64 *s_nk = (u64 *)(s_he + hc);                // near ranges: smaller ones from the front, the others from the back
-  u64 *s_fk = s_nk + rc;                         // far ranges
-  u32 *s_nl = (u32 *)(s_fk + rc);                // lo | hi << 16 of the near / far ranges
+  u64 *s_nk = (u64 *)(s_he + hc);                // near long ranges: smaller ones from the front, the others from the back
+  u64 *s_fk = s_nk + rc;                         // short near ranges from the front, far ranges from the back
+  u32 *s_nl = (u32 *)(s_fk + rc);                // lo | hi << 16 of the same
   u32 *s_fl = s_nl + rc;
   u32 *s_far = s_fl + rc;                        // far heads (indices into s_he)
+  u16 *s_inc = (u16 *)(s_far + hc);              // per position: indices (into s_fk) of the short ranges covering it
   const u64 Xl = (u64)((t + 1) << LT_SHIFT) + margin;
   const u32 X = Xl > 0x7FFFFFFFull ? 0x7FFFFFFFu : (u32)Xl;
-  s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0;
-  if (tid == 0) { s_d[LT_W] = 0; s_c1 = 0; s_c0 = 0; s_cf = 0; s_nfar = 0; }
+  s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0; s_icnt[tid] = 0;
+  if (tid == 0) { s_d[LT_W] = 0; s_c1 = 0; s_c0 = 0; s_cs = 0; s_cf = 0; s_nfar = 0; }
   TileEnt he0;
   he0.a = he0.b = 0; he0.kappa = 0;
   if (tid < hc) he0 = he[h0 + tid];
   __syncthreads();
   for (u32 j = tid; j < rc; j += LT_THREADS) {
     const TileEnt e = re[r0 + j];
-    const u32 cls = (u32)(e.kappa >> 32);
-    if (cls < X) { const u32 k = atomicAdd(&s_c1, 1u); s_nk[k] = e.kappa; s_nl[k] = e.a; }
-    else if (cls > 0xFFFFFFFFu - X) { const u32 k = rc - 1 - atomicAdd(&s_c0, 1u); s_nk[k] = e.kappa; s_nl[k] = e.a; }
-    else { const u32 k = atomicAdd(&s_cf, 1u); s_fk[k] = e.kappa; s_fl[k] = e.a; }
-    atomicAdd(&s_d[e.a & 0xFFFF], 1);
-    atomicAdd(&s_d[(e.a >> 16) + 1], -1);
+    const u32 cls = (u32)(e.kappa >> 32), lo = e.a & 0xFFFF, hi = e.a >> 16;
+    const bool near1 = cls < X, near0 = cls > 0xFFFFFFFFu - X;
+    if ((near1 || near0) && shorts && hi - lo < TR_SHORT) {
+      const u32 k = atomicAdd(&s_cs, 1u);
+      s_fk[k] = e.kappa; s_fl[k] = e.a;
+      for (u32 q = lo; q <= hi; q++) atomicAdd(&s_icnt[q], 1u);
+    } else if (near1) { const u32 k = atomicAdd(&s_c1, 1u); s_nk[k] = e.kappa; s_nl[k] = e.a; }
+    else if (near0) { const u32 k = rc - 1 - atomicAdd(&s_c0, 1u); s_nk[k] = e.kappa; s_nl[k] = e.a; }
+    else { const u32 k = rc - 1 - atomicAdd(&s_cf, 1u); s_fk[k] = e.kappa; s_fl[k] = e.a; }
+    atomicAdd(&s_d[lo], 1);
+    atomicAdd(&s_d[hi + 1], -1);
   }
   for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[(j == tid ? he0 : he[h0 + j]).b & (LT_W - 1)], 1u);
   __syncthreads();
   {
     const u32 hq = s_cnt[tid];
-    u32 ex;
+    u32 ex, iex;
     int incl;
     BS(ts).ExclusiveSum(hq, ex);
+    BS(ts2).ExclusiveSum(s_icnt[tid], iex);
     BSI(tsi).InclusiveSum(s_d[tid], incl);
     s_off[tid] = ex;
+    s_ioff[tid] = iex;
     s_cov[tid] = (u32)incl;
-    if (tid == LT_THREADS - 1) s_off[LT_W] = ex + hq;
+    if (tid == LT_THREADS - 1) { s_off[LT_W] = ex + hq; s_ioff[LT_W] = iex + s_icnt[tid]; }
     const u32 p = (t << LT_SHIFT) + tid;
     if (p <= n) pcov[p] = make_uint2((u32)incl + hq, h0 + ex);
   }
   __syncthreads();
+  s_icnt[tid] = 0;                               // reused as the cursors of the incidence lists
+  __syncthreads();
+  const u32 c1 = s_c1, c0 = s_c0, cs = s_cs, cf = s_cf;
+  for (u32 k = tid; k < cs; k += LT_THREADS) {
+    const u32 lh = s_fl[k], lo = lh & 0xFFFF, hi = lh >> 16;
+    for (u32 q = lo; q <= hi; q++) s_inc[s_ioff[q] + atomicAdd(&s_icnt[q], 1u)] = (u16)k;
+  }
   for (u32 j = tid; j < hc; j += LT_THREADS) {
     const TileEnt e = j == tid ? he0 : he[h0 + j];
     const u32 q = e.b & (LT_W - 1);
     s_he[s_off[q] + atomicAdd(&s_cur[q], 1u)] = e;
   }
   __syncthreads();
-  const u32 c1 = s_c1, c0 = s_c0, cf = s_cf;
   for (u32 j = tid; j < hc; j += LT_THREADS) {
     const TileEnt e = s_he[j];
     const u32 q = e.b & (LT_W - 1);
@@ -437,9 +460,11 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     u32 c = 0, w;
     if (cls < X) {
       for (u32 r = 0; r < c1; r++) c += (s_nk[r] < kap) & tr_covers(s_nl[r], q);
+      for (u32 r = s_ioff[q]; r < s_ioff[q + 1]; r++) c += s_fk[s_inc[r]] < kap;
       w = mates + c;
     } else if (cls > 0xFFFFFFFFu - X) {
       for (u32 r = rc - c0; r < rc; r++) c += (s_nk[r] > kap) & tr_covers(s_nl[r], q);
+      for (u32 r = s_ioff[q]; r < s_ioff[q + 1]; r++) c += s_fk[s_inc[r]] > kap;
       w = mates + s_cov[q] - c;
     } else {
       s_far[atomicAdd(&s_nfar, 1u)] = j | (mates << 16);      // hc, mates <= 8192
@@ -458,7 +483,8 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     u32 c = 0;
     for (u32 r = lane; r < c1; r += 32) c += (s_nk[r] < kap) & tr_covers(s_nl[r], q);
     for (u32 r = rc - c0 + lane; r < rc; r += 32) c += (s_nk[r] < kap) & tr_covers(s_nl[r], q);
-    for (u32 r = lane; r < cf; r += 32) c += (s_fk[r] < kap) & tr_covers(s_fl[r], q);
+    for (u32 r = lane; r < cs; r += 32) c += (s_fk[r] < kap) & tr_covers(s_fl[r], q);
+    for (u32 r = rc - cf + lane; r < rc; r += 32) c += (s_fk[r] < kap) & tr_covers(s_fl[r], q);
     c = __reduce_add_sync(0xffffffffu, c);
     if (lane == 0) {
       const u32 w = mates + c;
@@ -603,11 +629,13 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   c->d_hw.alloc(((size_t)c->n_hw + 1) * 8, st);
   c->d_pcov.alloc(((size_t)ntiles * LT_W + 1) * 8, st);
   c->d_termsym.alloc((size_t)c->stats.n_docs + 16, st);
-  const size_t sm = tile_rank_smem(c->tile_maxent);
+  // room for the per-position lists of short ranges where the deepest tile leaves it (else 24 bytes per entry)
+  size_t sm = tile_rank_smem(c->tile_maxent, c->tile_short != 0);
+  if (sm > 200 * 1024) sm = tile_rank_smem(c->tile_maxent, false);
   if (sm > 32 * 1024) CK(cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_rank<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                              c->t_roff.as<u32>(), n, (u32)c->tile_margin, c->d_pcov.as<uint2>(),
-                                              c->d_hw.as<u64>(), wo);
+                                              c->t_roff.as<u32>(), n, (u32)c->tile_margin,
+                                              c->tile_short ? (u32)sm : 0u, c->d_pcov.as<uint2>(), c->d_hw.as<u64>(), wo);
   k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
                                                      c->d_termsym.as<u8>(), wo);
   c->launches += 2;
