@@ -216,7 +216,7 @@ void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N) {
 // buckets it intersects into it and stores the finished block with one bulk copy (TMA,
 // cp.async.bulk.global.shared::cta) -- every output sector is written exactly once and nothing is
 // scattered into the cold output (round 1: one sector read-modify-write per head symbol).
-__global__ void k_vrank(const uint2 *__restrict__ pcov, const i32 *__restrict__ sa, const u8 *__restrict__ rbwt,
+__global__ void k_vrank(const uint4 *__restrict__ pcov, const i32 *__restrict__ sa, const u8 *__restrict__ rbwt,
                         const u8 *__restrict__ termsym, u32 nd, u32 nv, u32 *__restrict__ cnt,
                         u64 *__restrict__ hl, u8 *__restrict__ vsym) {
   const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
@@ -224,9 +224,9 @@ __global__ void k_vrank(const uint2 *__restrict__ pcov, const i32 *__restrict__ 
   if (v < nd) { cnt[v] = 1; hl[v] = 0; vsym[v] = termsym[v]; return; }
   const u32 r = v - nd + 1;
   const u32 p = (u32)sa[r];
-  const uint2 a = __ldg(pcov + p), b = __ldg(pcov + p + 1);
+  const uint4 a = __ldg(pcov + p);               // {bucket size, first head slot, heads, -}: one random 16-byte read
   cnt[v] = a.x;
-  hl[v] = ((u64)a.y << 32) | (u64)(b.y - a.y);
+  hl[v] = ((u64)a.y << 32) | (u64)a.z;
   vsym[v] = rbwt[r];
 }
 
@@ -484,7 +484,7 @@ static void emit_pull(cmsbwt_ctx *c, int mode) {
   hl.alloc(((size_t)nv + 1) * 8, st);
   vsym.alloc((size_t)nv + 16, st);
   GroupSpan *goff = new GroupSpan(c, CMSBWT_G_OFFSETS);
-  k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(c->d_pcov.as<uint2>(), c->ix.sa, c->ix.rbwt, c->d_termsym.as<u8>(), nd, nv,
+  k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(c->d_pcov.as<uint4>(), c->ix.sa, c->ix.rbwt, c->d_termsym.as<u8>(), nd, nv,
                                          cnt.as<u32>(), hl.as<u64>(), vsym.as<u8>());
   CK(cudaMemsetAsync(cnt.as<u32>() + nv, 0, 4, st));
   size_t tb = 0;

@@ -357,7 +357,9 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_place(const TileEnt *he, co
 //                            within = mates + #{near smaller ranges: kappa < kappa_h, covers q}
 //   near head, not smaller:  only near not-smaller ranges can have a higher kappa
 //                            within = mates + cov(q) - #{near not-smaller ranges: kappa > kappa_h, covers q}
-//   far head:                all ranges are tested, by a whole warp (32 ranges per step)
+//   far head:                every near smaller range covering q precedes it, no near not-smaller one does:
+//                            within = mates + cov_near_smaller(q) + #{far ranges: kappa < kappa_h, covers q},
+//                            the far ranges tested by a whole warp (32 per step)
 // cov(q) = ranges covering q comes from the difference array the bucket sizes need anyway.  Nearly all
 // heads are the short ones in front of a mutation (near); the near lists hold the few phrases that end
 // around the tile, so a head tests ~15 ranges instead of a quarter of the tile (round 1: 4 kappa buckets
@@ -375,18 +377,19 @@ static size_t tile_rank_smem(u32 maxent, bool with_short) { return (size_t)maxen
 __device__ __forceinline__ u32 tr_covers(u32 lh, u32 q) { return ((lh & 0xFFFF) <= q) & (q <= (lh >> 16)); }
 __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restrict__ he, const TileEnt *__restrict__ re,
                                                           const u32 *__restrict__ hoff, const u32 *__restrict__ roff,
-                                                          u32 n, u32 margin, u32 smem_bytes, uint2 *__restrict__ pcov,
+                                                          u32 n, u32 margin, u32 smem_bytes, uint4 *__restrict__ pcov,
                                                           u64 *__restrict__ hw, u32 *within_out) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W], s_cov[LT_W];
-  __shared__ u32 s_icnt[LT_W], s_ioff[LT_W + 1];
-  __shared__ int s_d[LT_W + 1];
+  __shared__ u32 s_icnt[LT_W], s_ioff[LT_W + 1], s_cov1[LT_W];
+  __shared__ int s_d[LT_W + 1], s_d1[LT_W + 1];
   __shared__ u32 s_c1, s_c0, s_cs, s_cf, s_nfar;
   typedef cub::BlockScan<u32, LT_THREADS> BS;
   typedef cub::BlockScan<int, LT_THREADS> BSI;
   __shared__ typename BS::TempStorage ts;
   __shared__ typename BS::TempStorage ts2;
   __shared__ typename BSI::TempStorage tsi;
+  __shared__ typename BSI::TempStorage tsi2;
   const u32 t = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
   const u32 h0 = hoff[t], h1 = hoff[t + 1], r0 = roff[t], r1 = roff[t + 1];
   const u32 hc = h1 - h0, rc = r1 - r0;
@@ -400,8 +403,8 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
   u16 *s_inc = (u16 *)(s_far + hc);              // per position: indices (into s_fk) of the short ranges covering it
   const u64 Xl = (u64)((t + 1) << LT_SHIFT) + margin;
   const u32 X = Xl > 0x7FFFFFFFull ? 0x7FFFFFFFu : (u32)Xl;
-  s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0; s_icnt[tid] = 0;
-  if (tid == 0) { s_d[LT_W] = 0; s_c1 = 0; s_c0 = 0; s_cs = 0; s_cf = 0; s_nfar = 0; }
+  s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0; s_d1[tid] = 0; s_icnt[tid] = 0;
+  if (tid == 0) { s_d[LT_W] = 0; s_d1[LT_W] = 0; s_c1 = 0; s_c0 = 0; s_cs = 0; s_cf = 0; s_nfar = 0; }
   TileEnt he0;
   he0.a = he0.b = 0; he0.kappa = 0;
   if (tid < hc) he0 = he[h0 + tid];
@@ -419,27 +422,31 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     else { const u32 k = rc - 1 - atomicAdd(&s_cf, 1u); s_fk[k] = e.kappa; s_fl[k] = e.a; }
     atomicAdd(&s_d[lo], 1);
     atomicAdd(&s_d[hi + 1], -1);
+    if (near1) { atomicAdd(&s_d1[lo], 1); atomicAdd(&s_d1[hi + 1], -1); }
   }
   for (u32 j = tid; j < hc; j += LT_THREADS) atomicAdd(&s_cnt[(j == tid ? he0 : he[h0 + j]).b & (LT_W - 1)], 1u);
   __syncthreads();
   {
     const u32 hq = s_cnt[tid];
     u32 ex, iex;
-    int incl;
+    int incl, incl1;
     BS(ts).ExclusiveSum(hq, ex);
     BS(ts2).ExclusiveSum(s_icnt[tid], iex);
     BSI(tsi).InclusiveSum(s_d[tid], incl);
+    BSI(tsi2).InclusiveSum(s_d1[tid], incl1);
     s_off[tid] = ex;
     s_ioff[tid] = iex;
     s_cov[tid] = (u32)incl;
+    s_cov1[tid] = (u32)incl1;
     if (tid == LT_THREADS - 1) { s_off[LT_W] = ex + hq; s_ioff[LT_W] = iex + s_icnt[tid]; }
     const u32 p = (t << LT_SHIFT) + tid;
-    if (p <= n) pcov[p] = make_uint2((u32)incl + hq, h0 + ex);
+    if (p <= n) pcov[p] = make_uint4((u32)incl + hq, h0 + ex, hq, 0u);     // one aligned 16-byte record per position
   }
   __syncthreads();
   s_icnt[tid] = 0;                               // reused as the cursors of the incidence lists
   __syncthreads();
   const u32 c1 = s_c1, c0 = s_c0, cs = s_cs, cf = s_cf;
+  (void)cs;
   for (u32 k = tid; k < cs; k += LT_THREADS) {
     const u32 lh = s_fl[k], lo = lh & 0xFFFF, hi = lh >> 16;
     for (u32 q = lo; q <= hi; q++) s_inc[s_ioff[q] + atomicAdd(&s_icnt[q], 1u)] = (u16)k;
@@ -481,13 +488,10 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     const u32 q = e.b & (LT_W - 1);
     const u64 kap = e.kappa;
     u32 c = 0;
-    for (u32 r = lane; r < c1; r += 32) c += (s_nk[r] < kap) & tr_covers(s_nl[r], q);
-    for (u32 r = rc - c0 + lane; r < rc; r += 32) c += (s_nk[r] < kap) & tr_covers(s_nl[r], q);
-    for (u32 r = lane; r < cs; r += 32) c += (s_fk[r] < kap) & tr_covers(s_fl[r], q);
     for (u32 r = rc - cf + lane; r < rc; r += 32) c += (s_fk[r] < kap) & tr_covers(s_fl[r], q);
     c = __reduce_add_sync(0xffffffffu, c);
     if (lane == 0) {
-      const u32 w = mates + c;
+      const u32 w = mates + s_cov1[q] + c;
       hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);
       if (within_out) within_out[e.a] = w;
     }
@@ -627,7 +631,7 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   u32 *wo = nullptr;
   if (c->dump) { c->h_within.alloc(H * 4, st); wo = c->h_within.as<u32>(); }
   c->d_hw.alloc(((size_t)c->n_hw + 1) * 8, st);
-  c->d_pcov.alloc(((size_t)ntiles * LT_W + 1) * 8, st);
+  c->d_pcov.alloc(((size_t)ntiles * LT_W + 1) * 16, st);
   c->d_termsym.alloc((size_t)c->stats.n_docs + 16, st);
   // room for the per-position lists of short ranges where the deepest tile leaves it (else 24 bytes per entry)
   size_t sm = tile_rank_smem(c->tile_maxent, c->tile_short != 0);
@@ -635,7 +639,7 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   if (sm > 32 * 1024) CK(cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_rank<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                               c->t_roff.as<u32>(), n, (u32)c->tile_margin,
-                                              c->tile_short ? (u32)sm : 0u, c->d_pcov.as<uint2>(), c->d_hw.as<u64>(), wo);
+                                              c->tile_short ? (u32)sm : 0u, c->d_pcov.as<uint4>(), c->d_hw.as<u64>(), wo);
   k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
                                                      c->d_termsym.as<u8>(), wo);
   c->launches += 2;
