@@ -22,6 +22,36 @@ __device__ __forceinline__ u32 pack4(u32 w, bool &clean) {
   return (p & 0xFu) | ((p >> 12) & 0xF0u);
 }
 
+// one 64-bit word = 32 symbols (a, b = their 32 bytes); breaks are appended, illegal bytes raise *bad
+__device__ __forceinline__ u64 pack_word(uint4 a, uint4 b, u64 p0, u64 len, u64 *seps, u64 sepcap,
+                                         unsigned long long *nsep, bool &bad) {
+  u32 v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  u64 word = 0;
+#pragma unroll
+  for (int t = 0; t < 8; t++) {
+    u32 w = v[t];
+    bool clean;
+    u32 c8 = pack4(w, clean);
+    if (!clean || p0 + 4 * t + 4 > len) {     // rare: separator, foreign symbol, end of the text
+      const u64 pb = p0 + 4 * t;
+      c8 = 0;
+#pragma unroll
+      for (int bb = 0; bb < 4; bb++) {
+        u32 ch = (w >> (8 * bb)) & 0xFF;
+        if (pb + bb >= len) continue;
+        if (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') c8 |= msf_code_of(ch) << (2 * bb);
+        else if (seps && (ch == 2 || (ch >= 3 && ch <= 127))) {     // separator, or an escape (any other legal symbol)
+          unsigned long long k = atomicAdd(nsep, 1ull);
+          if (k < sepcap) seps[k] = ((pb + bb) << 1) | (ch != 2 ? 1ull : 0ull);
+          if (ch != 2) atomicAdd(nsep + 1, 1ull);
+        } else bad = true;
+      }
+    }
+    word |= (u64)c8 << (8 * t);
+  }
+  return word;
+}
+
 __global__ void __launch_bounds__(256) k_pack(const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps,
                                               u64 sepcap, unsigned long long *nsep, u32 *flags) {
   for (u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x; j < nwords; j += (u64)gridDim.x * blockDim.x) {
@@ -29,41 +59,97 @@ __global__ void __launch_bounds__(256) k_pack(const u8 *src, u64 len, u64 *dst, 
     u64 word = 0;
     if (p0 < len) {
       const uint4 *q = (const uint4 *)(src + p0);
-      uint4 a = __ldg(q), b = __ldg(q + 1);
-      u32 v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
       bool bad = false;
-#pragma unroll
-      for (int t = 0; t < 8; t++) {
-        u32 w = v[t];
-        bool clean;
-        u32 c8 = pack4(w, clean);
-        if (!clean || p0 + 4 * t + 4 > len) {     // rare: separator, foreign symbol, end of the text
-          const u64 pb = p0 + 4 * t;
-          c8 = 0;
-#pragma unroll
-          for (int bb = 0; bb < 4; bb++) {
-            u32 ch = (w >> (8 * bb)) & 0xFF;
-            if (pb + bb >= len) continue;
-            if (ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T') c8 |= msf_code_of(ch) << (2 * bb);
-            else if (seps && (ch == 2 || (ch >= 3 && ch <= 127))) {     // separator, or an escape (any other legal symbol)
-              unsigned long long k = atomicAdd(nsep, 1ull);
-              if (k < sepcap) seps[k] = ((pb + bb) << 1) | (ch != 2 ? 1ull : 0ull);
-              if (ch != 2) atomicAdd(nsep + 1, 1ull);
-            } else bad = true;
-          }
-        }
-        word |= (u64)c8 << (8 * t);
-      }
+      word = pack_word(__ldg(q), __ldg(q + 1), p0, len, seps, sepcap, nsep, bad);
       if (bad) flags[0] = 1;
     }
     dst[j] = word;
   }
 }
 
+// The same packing with the text staged into shared memory by the TMA engine (north-star subsystem 1:
+// "2-bit-packed DNA text is staged into shared memory with TMA"): persistent CTAs, two 8 KB stages,
+// cp.async.bulk global -> shared completing on an mbarrier; a stage is one packed word per thread.
+// The text must be readable up to the next multiple of 16 bytes (CMS_PAD guarantees it).
+#define PK_CHUNK 8192u
+__device__ __forceinline__ void pk_mbar_init(u64 *bar) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((u32)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void pk_load(u8 *sdst, const u8 *gsrc, u32 bytes, u64 *bar) {
+  const u32 b = (u32)__cvta_generic_to_shared(bar);
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"((u32)__cvta_generic_to_shared(sdst)), "l"(gsrc), "r"(bytes), "r"(b) : "memory");
+}
+__device__ __forceinline__ void pk_wait(u64 *bar, u32 phase) {
+  const u32 b = (u32)__cvta_generic_to_shared(bar);
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(b), "r"(phase) : "memory");
+}
+__global__ void __launch_bounds__(256) k_pack_tma(const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps,
+                                                  u64 sepcap, unsigned long long *nsep, u32 *flags) {
+  __shared__ __align__(128) u8 s_buf[2][PK_CHUNK];
+  __shared__ __align__(8) u64 s_bar[2];
+  const u32 tid = threadIdx.x;
+  const u64 nchunks = (nwords * 32 + PK_CHUNK - 1) / PK_CHUNK;
+  const u64 padded = (len + 15) & ~15ull;                  // bytes that may be read
+  if (tid == 0) {
+    pk_mbar_init(&s_bar[0]); pk_mbar_init(&s_bar[1]);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto chunk_bytes = [&](u64 ch) -> u32 {
+    const u64 a = ch * PK_CHUNK;
+    return a >= padded ? 0u : (u32)min((u64)PK_CHUNK, padded - a);
+  };
+  u64 ch = blockIdx.x;
+  u32 stage = 0, phase[2] = {0, 0};
+  bool bad = false;
+  if (tid == 0 && ch < nchunks && chunk_bytes(ch)) pk_load(s_buf[0], src + ch * PK_CHUNK, chunk_bytes(ch), &s_bar[0]);
+  for (; ch < nchunks; ch += gridDim.x) {
+    const u64 nx = ch + gridDim.x;
+    // the other stage was consumed in the previous iteration (barrier at its end): refill it
+    if (tid == 0 && nx < nchunks && chunk_bytes(nx)) pk_load(s_buf[stage ^ 1], src + nx * PK_CHUNK, chunk_bytes(nx), &s_bar[stage ^ 1]);
+    const u32 nb = chunk_bytes(ch);
+    const u64 j = ch * (PK_CHUNK / 32) + tid, p0 = j * 32;
+    u64 word = 0;
+    if (nb) {
+      pk_wait(&s_bar[stage], phase[stage]);
+      phase[stage] ^= 1;
+      if (p0 < len) {
+        const uint4 *q = (const uint4 *)(s_buf[stage] + tid * 32);
+        uint4 a = q[0], b = make_uint4(0, 0, 0, 0);
+        if (tid * 32 + 16 < nb) b = q[1];                  // bytes past the copied ones are never symbols (>= len)
+        word = pack_word(a, b, p0, len, seps, sepcap, nsep, bad);
+      }
+    }
+    if (j < nwords) dst[j] = word;
+    __syncthreads();
+    stage ^= 1;
+  }
+  if (bad) flags[0] = 1;
+}
+
+static int pack_tma() {        // measurement switch: CMSBWT_PACK_TMA=0 selects the plain-load kernel
+  static int v = -1;
+  if (v < 0) { const char *e = getenv("CMSBWT_PACK_TMA"); v = e ? atoi(e) : 1; }
+  return v;
+}
+
 void pack_2bit(cmsbwt_ctx *c, const u8 *src, u64 len, u64 *dst, u64 nwords, u64 *seps, u64 sepcap,
                unsigned long long *nsep, u32 *flags) {
   u64 blocks = (nwords + 255) / 256;
   if (blocks > 148 * 64) blocks = 148 * 64;
+  if (pack_tma() && ((uintptr_t)src & 15) == 0) {
+    u64 nch = (nwords * 32 + PK_CHUNK - 1) / PK_CHUNK;
+    u32 grid = (u32)(nch < 148 * 8 ? nch : 148 * 8);       // persistent: 8 CTAs per SM, 16 KB of stages each
+    k_pack_tma<<<grid ? grid : 1, 256, 0, c->st>>>(src, len, dst, nwords, seps, sepcap, nsep, flags);
+  } else
   k_pack<<<(u32)blocks, 256, 0, c->st>>>(src, len, dst, nwords, seps, sepcap, nsep, flags);
   LAUNCH(c);
   CK(cudaGetLastError());
