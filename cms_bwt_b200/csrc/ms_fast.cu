@@ -135,9 +135,13 @@ __global__ void __launch_bounds__(256) k_pack_tma(const u8 *src, u64 len, u64 *d
   if (bad) flags[0] = 1;
 }
 
-static int pack_tma() {        // measurement switch: CMSBWT_PACK_TMA=0 selects the plain-load kernel
+// measurement switch: CMSBWT_PACK_TMA=1 selects the TMA-staged kernel.  Measured at
+// config 3 (profiles/r2_q5_bench_packtma*.json): 1.89 ms against 1.59 ms for the plain 16-byte loads --
+// the packing is bound by the PRMT/validation arithmetic and the separator test, not by load issue, and
+// the bulk copy adds the shared-memory round trip; the plain kernel stays the default.
+static int pack_tma() {
   static int v = -1;
-  if (v < 0) { const char *e = getenv("CMSBWT_PACK_TMA"); v = e ? atoi(e) : 1; }
+  if (v < 0) { const char *e = getenv("CMSBWT_PACK_TMA"); v = e ? atoi(e) : 0; }
   return v;
 }
 
