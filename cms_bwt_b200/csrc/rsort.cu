@@ -241,7 +241,7 @@ static void rsort_run(cmsbwt_ctx *c, DBuf &k, DBuf &k2, DBuf *v, DBuf *v2, u64 n
   status.alloc((size_t)ntiles * RS_RADIX * 8, st);
   ticket.alloc(4, st);
   CK(cudaMemsetAsync(ghist.p, 0, (size_t)npass * RS_RADIX * 8, st));
-  u64 hb = (n + (1u << 16) - 1) >> 16;            // contiguous slices (n < 2^40: 32-bit block counters are safe)
+  u64 hb = (n + (1u << 12) - 1) >> 12;            // contiguous slices (n < 2^40: 32-bit block counters are safe)
   if (hb > 148 * 8) hb = 148 * 8;
   k_rs_hist<K><<<(u32)hb, RS_THREADS, 0, st>>>(k.as<K>(), n, begin_bit, npass, ghist.as<unsigned long long>());
   k_rs_scan<<<npass, RS_RADIX, 0, st>>>(ghist.as<unsigned long long>());

@@ -84,8 +84,20 @@ __global__ void __launch_bounds__(256) k_tile_scatter(const u32 *pos, const u32 
   for (int k = 0; k < TS_ILP; k++) {
     const u32 ta = (p[k] + 1) >> LT_SHIFT, tb = (p[k] + tn[k]) >> LT_SHIFT;
     const u32 nt = (in[k] && tn[k]) ? tb - ta + 1 : 0;
-    if (nt && nt <= 8)
-      for (u32 t = ta; t <= tb; t++) put_range(re, roff, rcur, t, p[k], tn[k], kap[k]);
+    if (nt && nt <= 8) {
+      // all slot reservations of this phrase first, then its stores: one round trip instead of one per tile
+      u32 sl[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++)
+        if ((u32)j < nt) sl[j] = roff[ta + j] + atomicAdd(rcur + ta + j, 1u);
+#pragma unroll
+      for (int j = 0; j < 8; j++)
+        if ((u32)j < nt) {
+          const u32 a = (ta + j) << LT_SHIFT;
+          TileEnt e; e.a = (max(p[k] + 1, a) - a) | ((min(p[k] + tn[k], a + LT_W - 1) - a) << 16); e.b = 0; e.kappa = kap[k];
+          re[sl[j]] = e;
+        }
+    }
     unsigned big = __ballot_sync(0xffffffffu, nt > 8);
     while (big) {
       int src = __ffs(big) - 1;
