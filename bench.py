@@ -576,7 +576,9 @@ def main():
                                "(SNP/ins/del)%s, plain BWT" % (args.workload, w["ref_bp"], w["copies"], w["div"],
                                                                " + %d block SVs per copy" % w["svs"] if w.get("svs") else ""),
                    "N_symbols": int(nsym), "documents": int(ndocs), "n_ref_augmented": int(n),
-                   "heads": int(H), "cache": "inputs (%.1f GB) larger than L2" % (N / 1e9),
+                   "heads": int(H), "tails": int(s["n_tails"]), "tails_tied_after_radix_sort": int(s["rank_tied"]),
+                   "rank_rounds": int(s["rank_rounds"]), "tile_entries": int(s["n_items"]),
+                   "escapes": int(s["n_escapes"]), "cache": "inputs (%.1f GB) larger than L2" % (N / 1e9),
                    "device_ms_per_step": dev_ms,
                    "stage_ms": {k: v / args.steps for k, v in stage.items()},
                    "index_ms": {"sa_build_gpu": st0["sa_build_ms"], "index_build": st0["index_build_ms"]}},
