@@ -46,6 +46,35 @@ __global__ void k_tr_rank0(const u32 *key, const u32 *id, const u32 *gs, u32 n, 
   if (t >= lo && t < hi) rank[t] = base + g;
   if (first) tie[j] = (g != j) || (j + 1 < n && __ldcs(key + j + 1) == __ldcs(key + j));
 }
+// The (rank, cls) round for SMALL groups, inside the group: tails that share a key sit next to each other
+// after the radix sort (2.9 M of 48.8 M at config 3, in groups of 2-3), so the thread at the first
+// position of a group orders its members by cls itself instead of sending them through an 8-pass 64-bit
+// sort.  rank = group start + start of the member's equal-cls run; tie = the run has another member.
+// Groups of more than TR_GRP_MAX members are left to the sort-based round below.
+#define TR_GRP_MAX 16
+__global__ void k_tr_group_cls(const u32 *__restrict__ gs, const u32 *__restrict__ ids, const u64 *__restrict__ label,
+                               const u32 *__restrict__ cls32, u32 n, u32 base, u32 *rank, u8 *tie) {
+  const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n || !tie[j] || gs[j] != j) return;          // first position of a tied group only
+  u32 g = 1;
+  while (g <= TR_GRP_MAX && j + g < n && gs[j + g] == j) g++;
+  if (g > TR_GRP_MAX) return;
+  u32 cl[TR_GRP_MAX], at[TR_GRP_MAX];
+  for (u32 s = 0; s < g; s++) {
+    const u32 t = ids[j + s];
+    const u32 v = cls32 ? cls32[t] : (u32)label[t];
+    u32 k = s;                                          // insertion sort by cls, carrying the member's place
+    while (k > 0 && cl[k - 1] > v) { cl[k] = cl[k - 1]; at[k] = at[k - 1]; k--; }
+    cl[k] = v; at[k] = s;
+  }
+  u32 run = 0;
+  for (u32 s = 0; s < g; s++) {
+    if (s > 0 && cl[s] != cl[s - 1]) run = s;
+    const bool shared = (s > 0 && cl[s - 1] == cl[s]) || (s + 1 < g && cl[s + 1] == cl[s]);
+    rank[ids[j + at[s]]] = base + j + run;
+    tie[j + at[s]] = shared ? 1 : 0;
+  }
+}
 // subset keys: (current rank, secondary) with secondary = cls (round 0) or rank of the far tail
 __global__ void k_tr_key_cls(const u32 *sub, u32 m, const u32 *rank, const u64 *label, const u32 *cls32,
                              u64 *key) {
@@ -149,6 +178,10 @@ void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32
     }
   }
   c->launches += 8;
+  if (c->tie_local) {
+    k_tr_group_cls<<<gT, B, 0, st>>>(gs.as<u32>(), ids.as<u32>(), label, cls32, Tn, rank_base, trank, tie.as<u8>());
+    LAUNCH(c);
+  }
   // subset of tied tails (reuses id as the compacted list)
   u32 m = select_tied(tmp, ids.as<u32>(), tie.as<u8>(), Tn, id.as<u32>(), cnt, st);
   key32.release(); key32s.release(); gs.release();
@@ -158,7 +191,6 @@ void tail_rank_ex(cmsbwt_ctx *c, const u64 *label, const u32 *cls32, DBuf &key32
     DBuf key, keys, sub2, grp, sg, jt;
     key.alloc((size_t)m * 8, st); keys.alloc((size_t)m * 8, st); sub2.alloc((size_t)m * 4, st);
     grp.alloc((size_t)m * 4, st); sg.alloc((size_t)m * 4, st); jt.alloc((size_t)m * 4, st);
-    if (id.bytes < (size_t)m * 4) id.alloc((size_t)m * 4, st);      // (after the swap id may be the smaller buffer)
     u32 *sub = id.as<u32>(), *subs = sub2.as<u32>();
     int tbits = 1;
     while (tbits < 32 && (1ull << tbits) < (u64)Tn) tbits++;

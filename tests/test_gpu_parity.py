@@ -29,8 +29,8 @@ def _inputs(ref_file, coll_file, prefix=P.UINT64_MAX):
 
 
 MODES = {                       # which kernels run (DESIGN.md sections 3-5)
-    "fast+tiles": dict(fast=1, tile_budget=1 << 36, tile_margin=48, tile_short=1),     # 2-bit lane kernel + tile kernels
-    "fast+tiles/noshort": dict(fast=1, tile_budget=1 << 36, tile_margin=48, tile_short=0),   # short ranges walked with the near lists
+    "fast+tiles": dict(fast=1, tile_budget=1 << 36, tile_margin=48, tile_short=1, tie_local=1),     # 2-bit lane kernel + tile kernels
+    "fast+tiles/noshort": dict(fast=1, tile_budget=1 << 36, tile_margin=48, tile_short=0, tie_local=0),   # short ranges walked with the near lists
     "fast+tiles/far": dict(fast=1, tile_budget=1 << 36, tile_margin=0),  # same, nearly every head takes the "far" path
     "fast+tiles/near": dict(fast=1, tile_budget=1 << 36, tile_margin=1 << 30),   # same, every head and range is "near"
     "general+sweep": dict(fast=0, tile_budget=0),        # 8-bit warp kernel + sort-based sweep
