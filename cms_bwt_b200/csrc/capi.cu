@@ -138,7 +138,6 @@ int cmsbwt_set_param(cmsbwt_ctx *c, const char *name, int64_t v) {
     cudaSetDevice(c->dev);
     if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v) != cudaSuccess) { cudaGetLastError(); return CMSBWT_E_CUDA; }
   }
-  else if (!strcmp(name, "tile_two_level")) { if (v < 0 || v > 2) return CMSBWT_E_ARG; c->tile_two_level = v; }
   else if (!strcmp(name, "tie_local")) { c->tie_local = v != 0; }
   else if (!strcmp(name, "tile_short")) { c->tile_short = v != 0; }
   else if (!strcmp(name, "tile_margin")) { if (v < 0 || v > (1 << 30)) return CMSBWT_E_ARG; c->tile_margin = v; }

@@ -192,7 +192,6 @@ struct cmsbwt_ctx {
   i64 use_slots = 1;         // fast path: k-mer slot table (one 64-byte read per search) on / off
   i64 nb_t[3] = {48, 160, 512};   // tile placement: most ranges per tile for 1 / 4 / 8 kappa buckets
   i64 scatter_mb = 64;       // random 4-byte scatters run in passes over target regions of this many MB (L2)
-  i64 tile_two_level = 1;     // tile filing through coarse tiles (0: one global atomic + random store per entry)
   i64 tie_local = 1;          // tail ranking: small tied groups ordered by cls inside the group (0: by the 64-bit sort)
   i64 tile_short = 1;         // k_tile_rank: short near ranges filed per position (0: walked with the near lists)
   i64 tile_margin = 48;       // k_tile_rank: heads / ranges with a match end below tile end + margin are "near"

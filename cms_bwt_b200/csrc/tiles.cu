@@ -179,128 +179,6 @@ __global__ void __launch_bounds__(256) k_tile_scatter_few(const u32 *pos, const 
   }
 }
 
-// ---- two-level filing (single GPU, many tiles) -------------------------------------------------------
-// k_tile_scatter files 104 M entries (config 3) with one global atomic and one random 16-byte store each:
-// 81 % of its stall samples wait on the atomic's return, and every store is a partial sector of a cold
-// line.  Two levels instead: (1) heads are filed, block-aggregated (a block counts its slice in shared
-// memory and reserves once per coarse tile, like the FEW-tiles kernels above), under COARSE tiles of
-// 2^cshift positions (at most 4096 of them) -- head {pos, symbol, kappa}, and per coarse tile a phrase
-// touches one piece {pos, toNext, kappa}; entries of one (block, coarse tile) land next to each other;
-// (2) one CTA per coarse tile counts its fine tiles in shared memory (k_ct_count: the histogram
-// without a single global atomic) and, after the scan of the fine counts, files the entries under the
-// fine tiles with shared-memory cursors (k_ct_file): the random 16-byte stores stay inside the coarse
-// tile's few MB of output, which L2 holds until whole lines are written.
-template <bool COUNT>
-__device__ __forceinline__ void ct_pieces(u32 p, u32 tn, int cshift, u32 *s_r, const u32 *s_rb, const u32 *roff,
-                                          TileEnt *re, u64 kap) {
-  const u32 ca = (p + 1) >> cshift, cb = (p + tn) >> cshift;
-  for (u32 t = ca; t <= cb; t++) {
-    const u32 k = atomicAdd(&s_r[t], 1u);
-    if (!COUNT) { TileEnt e; e.a = p; e.b = tn; e.kappa = kap; re[roff[t] + s_rb[t] + k] = e; }
-  }
-}
-__global__ void __launch_bounds__(256) k_ct_hist(const u32 *pos, const u32 *len, const u32 *toNext, u64 H, int cshift,
-                                                 u32 nc, u32 *hcnt, u32 *rcnt) {
-  extern __shared__ u32 s_ta[];
-  u32 *s_h = s_ta, *s_r = s_ta + nc;
-  for (u32 k = threadIdx.x; k < 2 * nc; k += blockDim.x) s_ta[k] = 0;
-  __syncthreads();
-  const u64 i0 = (u64)blockIdx.x * TA_SLICE, i1 = min(H, i0 + TA_SLICE);
-  for (u64 i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
-    if (len[i] == 0) continue;
-    const u32 p = pos[i], tn = toNext[i];
-    atomicAdd(&s_h[p >> cshift], 1u);
-    if (tn) ct_pieces<true>(p, tn, cshift, s_r, nullptr, nullptr, nullptr, 0);
-  }
-  __syncthreads();
-  for (u32 k = threadIdx.x; k < nc; k += blockDim.x) {
-    if (s_h[k]) atomicAdd(hcnt + k, s_h[k]);
-    if (s_r[k]) atomicAdd(rcnt + k, s_r[k]);
-  }
-}
-__global__ void __launch_bounds__(256) k_ct_scatter(const u32 *pos, const u32 *len, const u16 *cs, const u32 *toNext,
-                                                    const u64 *kappa, u64 H, int cshift, u32 nc, const u32 *hoff,
-                                                    const u32 *roff, u32 *hcur, u32 *rcur, TileEnt *he, TileEnt *re) {
-  extern __shared__ u32 s_ta[];
-  u32 *s_h = s_ta, *s_r = s_ta + nc, *s_hb = s_ta + 2 * nc, *s_rb = s_ta + 3 * nc;
-  for (u32 k = threadIdx.x; k < 2 * nc; k += blockDim.x) s_ta[k] = 0;
-  __syncthreads();
-  const u64 i0 = (u64)blockIdx.x * TA_SLICE, i1 = min(H, i0 + TA_SLICE);
-  for (u64 i = i0 + threadIdx.x; i < i1; i += blockDim.x) {          // pass 1: the slice's counts
-    if (len[i] == 0) continue;
-    const u32 p = pos[i], tn = toNext[i];
-    atomicAdd(&s_h[p >> cshift], 1u);
-    if (tn) ct_pieces<true>(p, tn, cshift, s_r, nullptr, nullptr, nullptr, 0);
-  }
-  __syncthreads();
-  for (u32 k = threadIdx.x; k < nc; k += blockDim.x) {               // one reservation per coarse tile
-    s_hb[k] = s_h[k] ? atomicAdd(hcur + k, s_h[k]) : 0u;
-    s_rb[k] = s_r[k] ? atomicAdd(rcur + k, s_r[k]) : 0u;
-    s_h[k] = 0; s_r[k] = 0;
-  }
-  __syncthreads();
-  for (u64 i = i0 + threadIdx.x; i < i1; i += blockDim.x) {          // pass 2: the entries
-    if (len[i] == 0) continue;
-    const u32 p = pos[i], tn = toNext[i], t = p >> cshift;
-    const u64 kap = kappa[i];
-    TileEnt e; e.a = p; e.b = (u32)(cs[i] & 0xFF); e.kappa = kap;
-    he[hoff[t] + s_hb[t] + atomicAdd(&s_h[t], 1u)] = e;
-    if (tn) ct_pieces<false>(p, tn, cshift, s_r, s_rb, roff, re, kap);
-  }
-}
-// fine tiles [fa, fb] of coarse tile c that the piece {p, tn} touches
-__device__ __forceinline__ void ct_clip(u32 p, u32 tn, u32 c, int cshift, u32 &lo, u32 &hi) {
-  const u32 cb = c << cshift;
-  const u64 ce = (u64)cb + (1ull << cshift) - 1;
-  lo = max(p + 1, cb);
-  const u64 h = (u64)p + tn;
-  hi = (u32)(h < ce ? h : ce);
-}
-#define CT_THREADS 1024
-__global__ void __launch_bounds__(CT_THREADS) k_ct_count(const TileEnt *che, const TileEnt *cre, const u32 *choff,
-                                                        const u32 *croff, int cshift, u32 ntiles, u32 *hcnt, u32 *rcnt) {
-  extern __shared__ u32 s_ct[];
-  const u32 fpc = 1u << (cshift - LT_SHIFT), c = blockIdx.x, f0 = c * fpc;
-  u32 *s_h = s_ct, *s_r = s_ct + fpc;
-  for (u32 k = threadIdx.x; k < 2 * fpc; k += CT_THREADS) s_ct[k] = 0;
-  __syncthreads();
-  for (u32 j = choff[c] + threadIdx.x; j < choff[c + 1]; j += CT_THREADS) atomicAdd(&s_h[(che[j].a >> LT_SHIFT) - f0], 1u);
-  for (u32 j = croff[c] + threadIdx.x; j < croff[c + 1]; j += CT_THREADS) {
-    const TileEnt e = cre[j];
-    u32 lo, hi;
-    ct_clip(e.a, e.b, c, cshift, lo, hi);
-    for (u32 t = lo >> LT_SHIFT; t <= (hi >> LT_SHIFT); t++) atomicAdd(&s_r[t - f0], 1u);
-  }
-  __syncthreads();
-  for (u32 k = threadIdx.x; k < fpc; k += CT_THREADS)
-    if (f0 + k < ntiles) { hcnt[f0 + k] = s_h[k]; rcnt[f0 + k] = s_r[k]; }
-}
-__global__ void __launch_bounds__(CT_THREADS) k_ct_file(const TileEnt *che, const TileEnt *cre, const u32 *choff,
-                                                       const u32 *croff, int cshift, u32 ntiles, const u32 *hoff,
-                                                       const u32 *roff, TileEnt *he, TileEnt *re) {
-  extern __shared__ u32 s_ct[];
-  const u32 fpc = 1u << (cshift - LT_SHIFT), c = blockIdx.x, f0 = c * fpc;
-  u32 *s_h = s_ct, *s_r = s_ct + fpc;
-  for (u32 k = threadIdx.x; k < 2 * fpc; k += CT_THREADS) s_ct[k] = 0;
-  __syncthreads();
-  for (u32 j = choff[c] + threadIdx.x; j < choff[c + 1]; j += CT_THREADS) {
-    const TileEnt e = che[j];
-    const u32 t = e.a >> LT_SHIFT;
-    TileEnt o; o.a = 0; o.b = (e.a & (LT_W - 1)) | (e.b << 8); o.kappa = e.kappa;
-    he[hoff[t] + atomicAdd(&s_h[t - f0], 1u)] = o;
-  }
-  for (u32 j = croff[c] + threadIdx.x; j < croff[c + 1]; j += CT_THREADS) {
-    const TileEnt e = cre[j];
-    u32 lo, hi;
-    ct_clip(e.a, e.b, c, cshift, lo, hi);
-    for (u32 t = lo >> LT_SHIFT; t <= (hi >> LT_SHIFT); t++) {
-      const u32 a = t << LT_SHIFT;
-      TileEnt o; o.a = (max(lo, a) - a) | ((min(hi, a + LT_W - 1) - a) << 16); o.b = 0; o.kappa = e.kappa;
-      re[roff[t] + atomicAdd(&s_r[t - f0], 1u)] = o;
-    }
-  }
-}
-
 // ---- pass A: bucket sizes + cost of pass B -------------------------------------------------------
 // pcov != NULL (single-GPU pull emit, emit.cu): pcov[p] = {bucket size without the terminators, index of
 // the position's first head in the position-grouped head array hw[] that k_tile_place fills}, for p <= n.
@@ -653,7 +531,7 @@ __global__ void k_tile_deepest(const u32 *hcnt, const u32 *rcnt, u32 ntiles, u32
 // depth_limit > 0: give up (false) as soon as a tile is known to hold more entries than that --
 // before the histogram when even the average does, else right after it, before the scatter
 static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_out, u64 *R_out,
-                          u32 depth_limit = 0, bool two_level = false) {
+                          u32 depth_limit = 0) {
   cudaStream_t st = c->st;
   const u64 H = c->H;
   const int B = 256;
@@ -666,45 +544,6 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
   const bool few = ntiles <= TA_MAX_TILES;
   const u32 gS = (u32)((H + TA_SLICE - 1) / TA_SLICE);
-  // two-level filing: single GPU, more fine tiles than the block-aggregated kernels take, no head ids wanted
-  const bool two = two_level && !c->dump && (c->tile_two_level == 2 || (c->tile_two_level && !few));   // 2: forced (tests)
-  int cshift = 16;
-  while ((((u64)ntiles << LT_SHIFT) >> cshift) + 1 > TA_MAX_TILES) cshift++;
-  const u32 nc = (u32)((((u64)ntiles << LT_SHIFT) >> cshift) + 1), fpc = 1u << (cshift - LT_SHIFT);
-  DBuf chc, crc, choff, croff, che, cre;
-  if (two) {
-    chc.alloc(((size_t)nc + 1) * 4, st); crc.alloc(((size_t)nc + 1) * 4, st);
-    choff.alloc(((size_t)nc + 1) * 4, st); croff.alloc(((size_t)nc + 1) * 4, st);
-    CK(cudaMemsetAsync(chc.p, 0, ((size_t)nc + 1) * 4, st));
-    CK(cudaMemsetAsync(crc.p, 0, ((size_t)nc + 1) * 4, st));
-    if ((size_t)nc * 16 > 40 * 1024) {
-      CK(cudaFuncSetAttribute(k_ct_hist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(nc * 8)));
-      CK(cudaFuncSetAttribute(k_ct_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(nc * 16)));
-    }
-    k_ct_hist<<<gS, B, (size_t)nc * 8, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_toNext.as<u32>(), H, cshift, nc,
-                                            chc.as<u32>(), crc.as<u32>());
-    size_t tb0 = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tb0, chc.as<u32>(), choff.as<u32>(), (int)(nc + 1), st);
-    DBuf tmp0; tmp0.alloc(tb0, st);
-    size_t t0 = tb0;
-    CK(cub::DeviceScan::ExclusiveSum(tmp0.p, t0, chc.as<u32>(), choff.as<u32>(), (int)(nc + 1), st));
-    t0 = tb0;
-    CK(cub::DeviceScan::ExclusiveSum(tmp0.p, t0, crc.as<u32>(), croff.as<u32>(), (int)(nc + 1), st));
-    u32 CH = 0, CR = 0;
-    CK(cudaMemcpyAsync(&CH, choff.as<u32>() + nc, 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(&CR, croff.as<u32>() + nc, 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    che.alloc(((size_t)CH + 1) * sizeof(TileEnt), st); cre.alloc(((size_t)CR + 1) * sizeof(TileEnt), st);
-    CK(cudaMemsetAsync(chc.p, 0, ((size_t)nc + 1) * 4, st));      // reused as cursors
-    CK(cudaMemsetAsync(crc.p, 0, ((size_t)nc + 1) * 4, st));
-    k_ct_scatter<<<gS, B, (size_t)nc * 16, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
-                                                c->h_toNext.as<u32>(), kappa, H, cshift, nc, choff.as<u32>(), croff.as<u32>(),
-                                                chc.as<u32>(), crc.as<u32>(), che.as<TileEnt>(), cre.as<TileEnt>());
-    k_ct_count<<<nc, CT_THREADS, (size_t)fpc * 8, st>>>(che.as<TileEnt>(), cre.as<TileEnt>(), choff.as<u32>(), croff.as<u32>(),
-                                                       cshift, ntiles, hcnt.as<u32>(), rcnt.as<u32>());
-    c->launches += 5;
-    CK(cudaGetLastError());
-  } else
   if (few)
     k_tile_hist_few<<<gS, B, (size_t)ntiles * 8, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_toNext.as<u32>(), H,
                                                        ntiles, hcnt.as<u32>(), rcnt.as<u32>());
@@ -745,11 +584,6 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   c->t_re.alloc(((size_t)R + 1) * sizeof(TileEnt), st);
   CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));      // reused as cursors
   CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
-  if (two) {
-    k_ct_file<<<nc, CT_THREADS, (size_t)fpc * 8, st>>>(che.as<TileEnt>(), cre.as<TileEnt>(), choff.as<u32>(), croff.as<u32>(),
-                                                      cshift, ntiles, c->t_hoff.as<u32>(), c->t_roff.as<u32>(),
-                                                      c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>());
-  } else
   if (few) {
     if ((size_t)ntiles * 16 > 40 * 1024)
       CK(cudaFuncSetAttribute(k_tile_scatter_few, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ntiles * 16)));
@@ -775,7 +609,7 @@ bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
   u32 HE = 0;
   u64 R = 0;
   // a tile deeper than shared memory holds sends the whole job to the sort-based sweep (heads.cu)
-  if (!tiles_scatter(c, kappa, ntiles, &HE, &R, TR_MAX_ENTRIES, true)) {
+  if (!tiles_scatter(c, kappa, ntiles, &HE, &R, TR_MAX_ENTRIES)) {
     c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release();
     return false;
   }

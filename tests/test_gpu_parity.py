@@ -29,8 +29,7 @@ def _inputs(ref_file, coll_file, prefix=P.UINT64_MAX):
 
 
 MODES = {                       # which kernels run (DESIGN.md sections 3-5)
-    "fast+tiles": dict(fast=1, tile_budget=1 << 36, tile_margin=48, tile_short=1, tie_local=1, tile_two_level=1),
-    "fast+tiles/twolevel": dict(fast=1, tile_budget=1 << 36, tile_margin=48, tile_short=1, tie_local=1, tile_two_level=2),   # filing through coarse tiles forced     # 2-bit lane kernel + tile kernels
+    "fast+tiles": dict(fast=1, tile_budget=1 << 36, tile_margin=48, tile_short=1, tie_local=1),     # 2-bit lane kernel + tile kernels
     "fast+tiles/noshort": dict(fast=1, tile_budget=1 << 36, tile_margin=48, tile_short=0, tie_local=0),   # short ranges walked with the near lists
     "fast+tiles/far": dict(fast=1, tile_budget=1 << 36, tile_margin=0),  # same, nearly every head takes the "far" path
     "fast+tiles/near": dict(fast=1, tile_budget=1 << 36, tile_margin=1 << 30),   # same, every head and range is "near"
@@ -105,7 +104,7 @@ def test_fuzz_vs_oracle(ctx, block):
         x, text = _inputs(c["ref_file"], c["coll_file"])
         if len(text) == 0:
             continue
-        for mode in ("fast+tiles", "general+sweep") + (("fast+tiles/far", "fast+tiles/near", "fast+tiles/noshort", "fast+tiles/twolevel") if seed % 5 == 0 else ()):
+        for mode in ("fast+tiles", "general+sweep") + (("fast+tiles/far", "fast+tiles/near", "fast+tiles/noshort") if seed % 5 == 0 else ()):
             _check_case(ctx, x, text, None, c["desc"], chunk=[64, 100, 8192][seed % 3], mode=mode)
 
 
