@@ -12,6 +12,23 @@
 #include <cub/cub.cuh>
 #include <utility>
 
+// ---- linking (toNext :1373, coverage deltas :368-390, tail flags) -------------------------
+__global__ void k_link(const u64 *g, const u32 *pos, const u32 *len, u64 H, u32 *toNext,
+                       i32 *diff, u32 *tflag, u32 *sflag) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H) return;
+  u32 l = len[i];
+  u64 gi = g[i];
+  u32 tn = l == 0 ? 0 : (u32)(g[i + 1] - gi - 1);     // a sentinel always follows a real head
+  toNext[i] = tn;
+  if (diff) {                     // sort-based path only: coverage deltas by global atomics
+    u32 p = pos[i];
+    atomicAdd(diff + p, 1);
+    atomicAdd(diff + p + tn + 1, -1);
+  }
+  tflag[i] = (i == 0) || (gi + l != g[i - 1] + len[i - 1]);
+  sflag[i] = l == 0;
+}
 // coverage deltas of the sort-based path (:368-390): +1 at pos, -1 past the phrase
 __global__ void k_cov_diff(const u32 *pos, const u32 *toNext, u64 H, i32 *diff) {
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -20,85 +37,10 @@ __global__ void k_cov_diff(const u32 *pos, const u32 *toNext, u64 H, i32 *diff) 
   atomicAdd(diff + p, 1);
   atomicAdd(diff + p + toNext[i] + 1, -1);
 }
-// ---- linking, both scans and the first head of every tail in ONE pass (:1359-1385) ------------------
-// k_link + InclusiveSum(tail flags) + ExclusiveSum(sentinel flags) + k_tail_first read and wrote ~51 bytes
-// per head in five launches; here a tile of LS_TILE heads is loaded once (shared memory), the two counts
-// travel as one packed 64-bit sum (tails in bits 0-30, sentinels in bits 31-61: both < 2^31) through a
-// block scan and a decoupled look-back over the earlier tiles (tiles take their index from a ticket, so
-// a tile only waits for tiles that already run): ~28 bytes per head, one launch.
-#define LS_ITEMS 8
-#define LS_TILE (256 * LS_ITEMS)
-#define LS_FLAG_AGG (1ull << 62)
-#define LS_FLAG_INCL (1ull << 63)
-#define LS_MASK31 0x7FFFFFFFull
-__global__ void __launch_bounds__(256) k_link_scan(const u64 *__restrict__ g, const u32 *__restrict__ len, u64 H,
-                                                   u32 *__restrict__ toNext, u32 *__restrict__ tincl,
-                                                   u32 *__restrict__ sexcl, u32 *__restrict__ tfirst,
-                                                   volatile unsigned long long *status, u32 *ticket, u32 *totals) {
-  __shared__ u64 s_g[LS_TILE + 2];          // g[base - 1 .. base + LS_TILE]
-  __shared__ u32 s_len[LS_TILE + 1];        // len[base - 1 .. base + LS_TILE - 1]
-  __shared__ u32 s_tile;
-  __shared__ unsigned long long s_prev;
-  typedef cub::BlockScan<unsigned long long, 256> BS;
-  __shared__ typename BS::TempStorage ts;
-  const u32 tid = threadIdx.x;
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  __syncthreads();
-  const u32 tile = s_tile;
-  const u64 base = (u64)tile * LS_TILE;
-  for (u32 k = tid; k < LS_TILE + 2; k += 256) {
-    const u64 i = base + k;                 // element i - 1
-    s_g[k] = (i >= 1 && i - 1 <= H) ? g[i - 1] : 0;        // g[H] is readable (one spare entry)
-    if (k <= LS_TILE) s_len[k] = (i >= 1 && i - 1 < H) ? len[i - 1] : 0;
-  }
-  __syncthreads();
-  u32 tf[LS_ITEMS], sf[LS_ITEMS];
-  unsigned long long local = 0;
-#pragma unroll
-  for (int k = 0; k < LS_ITEMS; k++) {
-    const u32 j = tid * LS_ITEMS + k;       // element base + j = s_g[j + 1]
-    const u64 i = base + j;
-    tf[k] = sf[k] = 0;
-    if (i < H) {
-      const u32 l = s_len[j + 1];
-      const u64 gi = s_g[j + 1];
-      toNext[i] = l == 0 ? 0u : (u32)(s_g[j + 2] - gi - 1);     // a sentinel always follows a real head
-      tf[k] = (i == 0) || (gi + l != s_g[j] + s_len[j]);
-      sf[k] = l == 0;
-    }
-    local += (unsigned long long)tf[k] | ((unsigned long long)sf[k] << 31);
-  }
-  unsigned long long ex, agg;
-  BS(ts).ExclusiveSum(local, ex, agg);
-  if (tid == 0) {
-    unsigned long long prev = 0;
-    if (tile == 0) status[0] = LS_FLAG_INCL | agg;
-    else {
-      status[tile] = LS_FLAG_AGG | agg;
-      size_t t = (size_t)tile - 1;
-      for (;;) {
-        const unsigned long long v = status[t];
-        if (v & LS_FLAG_INCL) { prev += v & ~(LS_FLAG_INCL | LS_FLAG_AGG); break; }
-        if (v & LS_FLAG_AGG) { prev += v & ~(LS_FLAG_INCL | LS_FLAG_AGG); t--; }
-      }
-      status[tile] = LS_FLAG_INCL | (prev + agg);
-    }
-    s_prev = prev;
-    if (base + LS_TILE >= H) { totals[0] = (u32)((prev + agg) & LS_MASK31); totals[1] = (u32)(((prev + agg) >> 31) & LS_MASK31); }
-  }
-  __syncthreads();
-  unsigned long long run = s_prev + ex;
-#pragma unroll
-  for (int k = 0; k < LS_ITEMS; k++) {
-    const u64 i = base + tid * LS_ITEMS + k;
-    if (i < H) {
-      const u32 ti = (u32)(run & LS_MASK31) + tf[k];            // inclusive count of tails
-      tincl[i] = ti;
-      sexcl[i] = (u32)((run >> 31) & LS_MASK31);                // exclusive count of sentinels
-      if (tf[k]) tfirst[ti - 1] = (u32)i;
-    }
-    run += (unsigned long long)tf[k] | ((unsigned long long)sf[k] << 31);
-  }
+__global__ void k_tail_first(const u32 *tflag, const u32 *tail_incl, u64 H, u32 *tail_first) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H) return;
+  if (tflag[i]) tail_first[tail_incl[i] - 1] = (u32)i;
 }
 // label + next pointer of every tail
 __global__ void k_tail_label(const u64 *g, const u32 *pos, const u32 *len, const u16 *cs,
@@ -397,35 +339,41 @@ void sort_prepare(cmsbwt_ctx *c, u64 doc_base) {
   const u64 H = c->H;
   const u32 n = c->ix.n;
   const int B = 256;
+  const u32 gH = (u32)((H + B - 1) / B);
   const u64 *g = c->h_gstart.as<u64>();
   const u32 *pos = c->h_pos.as<u32>(), *len = c->h_len.as<u32>();
   const u16 *cs = c->h_cs.as<u16>();
+  Tmp tmp;
+  size_t tb;
   c->h_toNext.alloc(H * 4, st);
   c->light = false;
   c->stats.light_tiles = 0;
   c->stats.pair_tests = 0;
-  DBuf tfirst, lsstat, lsmisc;
-  c->s_tincl.alloc(H * 4, st); c->s_sexcl.alloc(H * 4, st);
-  tfirst.alloc((size_t)H * 4, st);                  // at most one tail per head
-  const u64 ltiles = (H + LS_TILE - 1) / LS_TILE;
-  lsstat.alloc(ltiles * 8, st); lsmisc.alloc(16, st);
-  CK(cudaMemsetAsync(lsstat.p, 0, ltiles * 8, st));
-  CK(cudaMemsetAsync(lsmisc.p, 0, 16, st));
-  k_link_scan<<<(u32)ltiles, 256, 0, st>>>(g, len, H, c->h_toNext.as<u32>(), c->s_tincl.as<u32>(), c->s_sexcl.as<u32>(),
-                                          tfirst.as<u32>(), lsstat.as<unsigned long long>(), lsmisc.as<u32>(),
-                                          lsmisc.as<u32>() + 1);
+  DBuf tflag, sflag, tfirst;
+  tflag.alloc(H * 4, st); sflag.alloc(H * 4, st); c->s_tincl.alloc(H * 4, st); c->s_sexcl.alloc(H * 4, st);
+  k_link<<<gH, B, 0, st>>>(g, pos, len, H, c->h_toNext.as<u32>(), nullptr, tflag.as<u32>(),
+                           sflag.as<u32>());
   LAUNCH(c);
-  u32 tot[2] = {0, 0};
-  CK(cudaMemcpyAsync(tot, lsmisc.as<u32>() + 1, 8, cudaMemcpyDeviceToHost, st));
+  tb = 0; cub::DeviceScan::InclusiveSum(nullptr, tb, tflag.as<u32>(), c->s_tincl.as<u32>(), (int)H, st);
+  tmp.need(tb, st);
+  CK(cub::DeviceScan::InclusiveSum(tmp.b.p, tb, tflag.as<u32>(), c->s_tincl.as<u32>(), (int)H, st));
+  tb = 0; cub::DeviceScan::ExclusiveSum(nullptr, tb, sflag.as<u32>(), c->s_sexcl.as<u32>(), (int)H, st);
+  tmp.need(tb, st);
+  CK(cub::DeviceScan::ExclusiveSum(tmp.b.p, tb, sflag.as<u32>(), c->s_sexcl.as<u32>(), (int)H, st));
+  c->launches += 2;
+  u32 Tn = 0, lastS = 0, lastF = 0;
+  CK(cudaMemcpyAsync(&Tn, c->s_tincl.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&lastS, c->s_sexcl.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&lastF, sflag.as<u32>() + (H - 1), 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  const u32 Tn = tot[0];
-  c->stats.n_docs = tot[1];
+  c->stats.n_docs = (u64)lastS + lastF;
   c->stats.n_tails = Tn;
   c->s_Tn = Tn;
   const u32 gT = (Tn + B - 1) / B;
-  c->s_label.alloc((size_t)Tn * 8, st);
+  tfirst.alloc((size_t)Tn * 4, st); c->s_label.alloc((size_t)Tn * 8, st);
   c->s_next.alloc((size_t)Tn * 4, st); c->s_tid.alloc((size_t)Tn * 4, st);
   c->s_trank.alloc((size_t)Tn * 4, st);
+  k_tail_first<<<gH, B, 0, st>>>(tflag.as<u32>(), c->s_tincl.as<u32>(), H, tfirst.as<u32>());
   int isa_bits = 1;
   while (isa_bits < 32 && (1ull << isa_bits) < (u64)n) isa_bits++;
   const int qb = 32 - isa_bits < 6 ? 32 - isa_bits : 6;
