@@ -526,7 +526,7 @@ def main():
                     "stage3_emit": ("offsets", "fill", "rle")}
     stage_alg = {"stage1_ms": nsym, "stage2_head_order": 48 * H, "stage3_emit": N + 30 * n}
     stage_kernels = {"stage1_ms": "k_pack + k_ms_fast + k_msf_gather" if s.get("fast_path") else "k_ms + k_compact",
-                     "stage2_head_order": "k_link, k_tail_label, tail radix sort + refinement, k_tile_hist/scatter/cov, k_tile_place",
+                     "stage2_head_order": "k_link, k_tail_label, tail radix sort + refinement, k_tile_hist/scatter, k_tile_rank",
                      "stage3_emit": "k_cnt_sa, offsets scan, k_fill_part, k_fill"}
     traffic_tab, traffic_capture = {}, None
     try:

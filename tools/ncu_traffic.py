@@ -12,7 +12,7 @@ import sys
 GROUPS = [("pack", ("k_pack",)), ("ms", ("k_ms_fast", "k_ms(")), ("gather", ("k_msf_gather", "k_msf_fix", "k_compact")),
           ("rank", ("k_link", "k_tail_", "Onesweep", "RadixSort", "k_tr_", "k_kappa", "k_rsort", "k_rs_")),
           ("tiles", ("k_tile_hist", "k_tile_scatter", "k_tile_cov", "k_tile_bin", "k_tile_deepest")),
-          ("place", ("k_tile_place", "k_term_syms", "k_place_sentinels")),
+          ("place", ("k_tile_place", "k_tile_rank", "k_term_syms", "k_place_sentinels")),
           ("offsets", ("k_vrank", "k_cnt_sa", "k_fill_part")), ("fill", ("k_fill",)), ("rle", ("k_rle",))]
 COLS = [("gpu__time_duration.sum", "ms"), ("dram__bytes_read.sum", "rdGB"), ("dram__bytes_write.sum", "wrGB"),
         ("lts__t_sector_hit_rate.pct", "L2hit%"), ("l1tex__t_sector_hit_rate.pct", "L1hit%"),

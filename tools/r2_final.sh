@@ -14,6 +14,6 @@ timeout 300 python bench.py --steps 2 --no-e2e --no-cpu-baseline > $O/r2_final_p
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file $O/r2_final_launches_config3.csv \
   env CMSBWT_PROFILE=1 python bench.py --steps 2 --no-e2e --no-cpu-baseline > $O/r2_final_ncu_list.log 2>&1
 ncu --set full --clock-control none --import-source on --profile-from-start off \
-  -k 'regex:k_ms_fast|k_tile_rank|k_tile_scatter|k_fill|k_pack|k_vrank|k_tail_label|k_tr_rank0|k_msf_gather|k_tile_hist|k_kappa|k_link|k_tail_first|k_rs_hist|k_rs_pass<unsigned int' \
-  -c 22 -o $O/r2_final_kernels_full env CMSBWT_PROFILE=1 python bench.py --steps 1 --no-e2e --no-cpu-baseline > $O/r2_final_ncu_full.log 2>&1
+  -k 'regex:k_ms_fast|k_tile_rank|k_tile_scatter|k_fill|k_pack|k_vrank|k_tail_label|k_tr_rank0|k_msf_gather|k_tile_hist|k_kappa|k_link|k_tail_first|k_rs_hist|k_rs_pass|k_term_syms|k_tr_group_cls' \
+  -c 48 -o $O/r2_final_kernels_full env CMSBWT_PROFILE=1 python bench.py --steps 1 --no-e2e --no-cpu-baseline > $O/r2_final_ncu_full.log 2>&1
 echo "ncu rc=$?"; ls -la $O | grep r2_final
