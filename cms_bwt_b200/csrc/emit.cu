@@ -210,24 +210,22 @@ void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N) {
 // Pull emit (single GPU, tile path).  The output is walked in "virtual rank" order: v < nd is the
 // terminator of document v (the bucket of SA rank 0 holds exactly one suffix per document, in document
 // order: the writers' "first D-1 head chars", :1640-1643), v >= nd is SA rank r = v - nd + 1.  Per
-// virtual rank: cnt[v] = bucket size (:1618-1628 bucket inversion as a gather), vsym[v] = reference
+// virtual rank: cnt[v] = bucket size (:1618-1628 bucket inversion: k_tile_rank stores every position's
+// record at its virtual rank, the scatter overlapping that kernel's arithmetic), vsym[v] = reference
 // BWT symbol, hl[v] = (first slot << 32 | number) of the bucket's heads in hw[] (tiles.cu).  The fill
 // kernel expands the runs of its 16 KB output block in SHARED memory, pulls the head symbols of the
 // buckets it intersects into it and stores the finished block with one bulk copy (TMA,
 // cp.async.bulk.global.shared::cta) -- every output sector is written exactly once and nothing is
 // scattered into the cold output (round 1: one sector read-modify-write per head symbol).
-__global__ void k_vrank(const uint4 *__restrict__ pcov, const i32 *__restrict__ sa, const u8 *__restrict__ rbwt,
-                        const u8 *__restrict__ termsym, u32 nd, u32 nv, u32 *__restrict__ cnt,
-                        u64 *__restrict__ hl, u8 *__restrict__ vsym) {
+__global__ void k_vrank(const uint4 *__restrict__ vrec, const u8 *__restrict__ rbwt, const u8 *__restrict__ termsym,
+                        u32 nd, u32 nv, u32 *__restrict__ cnt, u64 *__restrict__ hl, u8 *__restrict__ vsym) {
   const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= nv) return;
   if (v < nd) { cnt[v] = 1; hl[v] = 0; vsym[v] = termsym[v]; return; }
-  const u32 r = v - nd + 1;
-  const u32 p = (u32)sa[r];
-  const uint4 a = __ldg(pcov + p);               // {bucket size, first head slot, heads, -}: one random 16-byte read
+  const uint4 a = vrec[v];                       // {bucket size, first head slot, heads, -}, written by k_tile_rank
   cnt[v] = a.x;
   hl[v] = ((u64)a.y << 32) | (u64)a.z;
-  vsym[v] = rbwt[r];
+  vsym[v] = rbwt[v - nd + 1];
 }
 
 #define PULL_SERIAL 24          // heads of one bucket a single thread pulls; longer lists go to a warp
@@ -484,7 +482,7 @@ static void emit_pull(cmsbwt_ctx *c, int mode) {
   hl.alloc(((size_t)nv + 1) * 8, st);
   vsym.alloc((size_t)nv + 16, st);
   GroupSpan *goff = new GroupSpan(c, CMSBWT_G_OFFSETS);
-  k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(c->d_pcov.as<uint4>(), c->ix.sa, c->ix.rbwt, c->d_termsym.as<u8>(), nd, nv,
+  k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(c->d_pcov.as<uint4>(), c->ix.rbwt, c->d_termsym.as<u8>(), nd, nv,
                                          cnt.as<u32>(), hl.as<u64>(), vsym.as<u8>());
   CK(cudaMemsetAsync(cnt.as<u32>() + nv, 0, 4, st));
   size_t tb = 0;

@@ -389,8 +389,9 @@ static size_t tile_rank_smem(u32 maxent, bool with_short) { return (size_t)maxen
 __device__ __forceinline__ u32 tr_covers(u32 lh, u32 q) { return ((lh & 0xFFFF) <= q) & (q <= (lh >> 16)); }
 __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restrict__ he, const TileEnt *__restrict__ re,
                                                           const u32 *__restrict__ hoff, const u32 *__restrict__ roff,
-                                                          u32 n, u32 margin, u32 smem_bytes, uint4 *__restrict__ pcov,
-                                                          u64 *__restrict__ hw, u32 *within_out) {
+                                                          u32 n, u32 margin, u32 smem_bytes, const u32 *__restrict__ isa,
+                                                          u32 nd, uint4 *__restrict__ vrec, u64 *__restrict__ hw,
+                                                          u32 *within_out) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W], s_cov[LT_W];
   __shared__ u32 s_icnt[LT_W], s_ioff[LT_W + 1], s_cov1[LT_W];
@@ -420,6 +421,9 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
   TileEnt he0;
   he0.a = he0.b = 0; he0.kappa = 0;
   if (tid < hc) he0 = he[h0 + tid];
+  // SA rank of this thread's position (coalesced): its bucket record goes straight to virtual-rank order
+  const u32 p_own = (t << LT_SHIFT) + tid;
+  const u32 rank_own = p_own < n ? isa[p_own] : 0u;
   __syncthreads();
   for (u32 j = tid; j < rc; j += LT_THREADS) {
     const TileEnt e = re[r0 + j];
@@ -451,8 +455,10 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     s_cov[tid] = (u32)incl;
     s_cov1[tid] = (u32)incl1;
     if (tid == LT_THREADS - 1) { s_off[LT_W] = ex + hq; s_ioff[LT_W] = iex + s_icnt[tid]; }
-    const u32 p = (t << LT_SHIFT) + tid;
-    if (p <= n) pcov[p] = make_uint4((u32)incl + hq, h0 + ex, hq, 0u);     // one aligned 16-byte record per position
+    // {bucket size, first head slot, heads}: one aligned 16-byte record per position, stored at its virtual
+    // rank (the bucket inversion :1618-1628 as a scatter that overlaps this kernel's arithmetic); SA rank 0
+    // is the terminators' bucket, which the virtual ranks below nd replace
+    if (p_own < n && rank_own) vrec[nd + rank_own - 1] = make_uint4((u32)incl + hq, h0 + ex, hq, 0u);
   }
   __syncthreads();
   s_icnt[tid] = 0;                               // reused as the cursors of the incidence lists
@@ -643,7 +649,7 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   u32 *wo = nullptr;
   if (c->dump) { c->h_within.alloc(H * 4, st); wo = c->h_within.as<u32>(); }
   c->d_hw.alloc(((size_t)c->n_hw + 1) * 8, st);
-  c->d_pcov.alloc(((size_t)ntiles * LT_W + 1) * 16, st);
+  c->d_pcov.alloc(((size_t)c->stats.n_docs + n + 1) * 16, st);     // records in virtual-rank order
   c->d_termsym.alloc((size_t)c->stats.n_docs + 16, st);
   // room for the per-position lists of short ranges where the deepest tile leaves it (else 24 bytes per entry)
   size_t sm = tile_rank_smem(c->tile_maxent, c->tile_short != 0);
@@ -651,7 +657,8 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   if (sm > 32 * 1024) CK(cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   k_tile_rank<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                               c->t_roff.as<u32>(), n, (u32)c->tile_margin,
-                                              c->tile_short ? (u32)sm : 0u, c->d_pcov.as<uint4>(), c->d_hw.as<u64>(), wo);
+                                              c->tile_short ? (u32)sm : 0u, c->ix.isa, (u32)c->stats.n_docs, c->d_pcov.as<uint4>(),
+                                              c->d_hw.as<u64>(), wo);
   k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
                                                      c->d_termsym.as<u8>(), wo);
   c->launches += 2;
