@@ -739,7 +739,7 @@ int cmsbwt_shard_tiles_merge(cmsbwt_ctx *c, uint32_t world, uint32_t rank, const
   order_after_device(c);
   Timer t(c->st);
   u32 me = shard_tiles_merge(c, world, rank, d_he, d_re, (const u32 *)d_hoffs, (const u32 *)d_roffs, he_slab,
-                             re_slab, ndocs_total);
+                             re_slab, ndocs_total, true);
   c->stats.sort_ms += t.stop();
   if (max_entries) *max_entries = me;
   GUARD_END(c)

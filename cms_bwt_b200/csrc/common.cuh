@@ -164,6 +164,12 @@ struct cmsbwt_ctx {
   int s_key_bits = 32;
   // shard state (shard.cu / tailrank.cu): locally sorted tail keys, tied subset, merged tiles
   DBuf sh_ks, sh_cs, sh_perm, sh_sub, sh_tiekeys, sh_cov, sh_plc, sh_base;
+  // pull emit across devices: static routing table of this device's reference positions (slot in the send
+  // buffer, grouped by the owner of the position's SA rank), the records / head lists to send
+  DBuf sh_slot, sh_vsend, sh_hwsend;
+  u64 sh_slot_key[5] = {0, 0, 0, 0, 0};
+  std::vector<u64> sh_slot_edges, sh_v_hwcnt, sh_v_bytes;
+  u32 sh_rper = 0;                               // SA ranks per device
   u32 sh_m = 0, sh_round = 0;
   std::vector<u64> sh_plc_cnt;                   // placements per destination rank
   u32 sh_world = 1, sh_rank = 0, sh_tp = 0;      // tiles per rank
@@ -255,7 +261,12 @@ void shard_tie_keys(cmsbwt_ctx *c);
 u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off);
 void shard_tiles_local(cmsbwt_ctx *c, u32 world);
 u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const void *re, const u32 *hoffs,
-                      const u32 *roffs, const u64 *he_slab, const u64 *re_slab, u64 ndocs_total);
+                      const u32 *roffs, const u64 *he_slab, const u64 *re_slab, u64 ndocs_total, bool with_cov);
+void shard_tiles_cov(cmsbwt_ctx *c, u64 ndocs_total);
+// multi-GPU pull emit (tiles.cu / emit.cu): bucket records routed to the owners of the SA-rank ranges
+bool shard_rank_pull(cmsbwt_ctx *c, u32 world, u32 rank);
+void shard_emit_pull(cmsbwt_ctx *c, int mode, u32 world, u32 rank, u32 nd_total, const void *recs, u64 nrecs,
+                     const u64 *rec_base, const u64 *hw_base, const void *hw, const u8 *termsym, u64 expect_bytes);
 void shard_emit(cmsbwt_ctx *c, const u32 *cov_full, u64 N_total, u32 world, u32 rank, u64 doc_base);
 void shard_apply(cmsbwt_ctx *c, const u64 *plc, u64 cnt);
 void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N);

@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include <cub/cub.cuh>
 #include <stdlib.h>
+#include <algorithm>
 
 __global__ void k_cnt_sa(const i32 *cov, const i32 *sa, u32 n, u32 *cnt) {
   u32 r = blockIdx.x * blockDim.x + threadIdx.x;
@@ -217,15 +218,17 @@ void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N) {
 // buckets it intersects into it and stores the finished block with one bulk copy (TMA,
 // cp.async.bulk.global.shared::cta) -- every output sector is written exactly once and nothing is
 // scattered into the cold output (round 1: one sector read-modify-write per head symbol).
+// ndl = terminators in front of this device's SA ranks (multi-GPU: all of them on device 0, none elsewhere),
+// r0 = SA ranks before this device's range: entry i >= ndl is SA rank 1 + r0 + (i - ndl)
 __global__ void k_vrank(const uint4 *__restrict__ vrec, const u8 *__restrict__ rbwt, const u8 *__restrict__ termsym,
-                        u32 nd, u32 nv, u32 *__restrict__ cnt, u64 *__restrict__ hl, u8 *__restrict__ vsym) {
+                        u32 ndl, u32 r0, u32 nv, u32 *__restrict__ cnt, u64 *__restrict__ hl, u8 *__restrict__ vsym) {
   const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= nv) return;
-  if (v < nd) { cnt[v] = 1; hl[v] = 0; vsym[v] = termsym[v]; return; }
+  if (v < ndl) { cnt[v] = 1; hl[v] = 0; vsym[v] = termsym[v]; return; }
   const uint4 a = vrec[v];                       // {bucket size, first head slot, heads, -}, written by k_tile_rank
   cnt[v] = a.x;
   hl[v] = ((u64)a.y << 32) | (u64)a.z;
-  vsym[v] = rbwt[v - nd + 1];
+  vsym[v] = rbwt[r0 + (v - ndl) + 1];
 }
 
 #define PULL_SERIAL 24          // heads of one bucket a single thread pulls; longer lists go to a warp
@@ -464,26 +467,21 @@ static int fill_store_variant() {     // measurement switch: CMSBWT_FILL_STORE=0
   return v;
 }
 
-static void emit_pull(cmsbwt_ctx *c, int mode) {
+// Buckets of nv virtual ranks (records vrec[], head lists hw[], terminators termsym[]) -> d_out (plain) or
+// d_rle (records) of N bytes; throws unless the bucket sizes add up to N.  keep_base: the caller wants
+// base[] (parity hook).
+static void emit_from_vrec(cmsbwt_ctx *c, int mode, const uint4 *vrec, const u64 *hw, const u8 *termsym, u32 ndl,
+                           u32 r0, u32 nv, u64 N, DBuf *keep_base) {
   cudaStream_t st = c->st;
-  const u32 n = c->ix.n;
-  const u64 N = c->N, H = c->H;
   const int B = 256;
-  const u64 nd64 = c->stats.n_docs;
-  if (nd64 + n >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "documents + reference length exceed 2^32"};
-  const u32 nd = (u32)nd64, nv = nd + n - 1;
-  {
-    GroupSpan g(c, CMSBWT_G_PLACE);
-    tiles_count_heads(c);
-  }
   DBuf cnt, base, hl, vsym, tmp, bstart;
   cnt.alloc(((size_t)nv + 1) * 4, st);
   base.alloc(((size_t)nv + 2) * 8, st);
   hl.alloc(((size_t)nv + 1) * 8, st);
   vsym.alloc((size_t)nv + 16, st);
   GroupSpan *goff = new GroupSpan(c, CMSBWT_G_OFFSETS);
-  k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(c->d_pcov.as<uint4>(), c->ix.rbwt, c->d_termsym.as<u8>(), nd, nv,
-                                         cnt.as<u32>(), hl.as<u64>(), vsym.as<u8>());
+  if (nv) k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(vrec, c->ix.rbwt, termsym, ndl, r0, nv, cnt.as<u32>(), hl.as<u64>(),
+                                                 vsym.as<u8>());
   CK(cudaMemsetAsync(cnt.as<u32>() + nv, 0, 4, st));
   size_t tb = 0;
   EXSUM64(nullptr, tb, cnt.as<u32>(), base.as<u64>(), (int)(nv + 1), st);
@@ -506,25 +504,21 @@ static void emit_pull(cmsbwt_ctx *c, int mode) {
     snprintf(buf, sizeof buf, "coverage total %llu != N %llu", (unsigned long long)total, (unsigned long long)N);
     throw CmsErr{CMSBWT_E_INTERNAL, buf};
   }
-  if (c->dump) {
-    c->h_off.alloc(H * 8, st);
-    k_head_offsets<<<(u32)((H + B - 1) / B), B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_within.as<u32>(),
-                                                        c->ix.isa, base.as<u64>(), nd, H, c->h_off.as<u64>());
-    LAUNCH(c);
-  }
   c->out_mode = mode;
   c->stats.n_runs = 0;
   if (mode == CMSBWT_MODE_PLAIN) {
     GroupSpan g(c, CMSBWT_G_FILL);
     c->d_out.alloc(N + CMS_PAD, st);
     u8 *out = c->d_out.as<u8>();
-    if (fill_store_variant() == 1)
-      k_fill_pull<1><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(),
-                                                            bstart.as<u32>(), N, out);
-    else
-      k_fill_pull<0><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(),
-                                                            bstart.as<u32>(), N, out);
-    LAUNCH(c);
+    if (nblocks) {
+      if (fill_store_variant() == 1)
+        k_fill_pull<1><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), hl.as<u64>(), hw,
+                                                              bstart.as<u32>(), N, out);
+      else
+        k_fill_pull<0><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), hl.as<u64>(), hw,
+                                                              bstart.as<u32>(), N, out);
+      LAUNCH(c);
+    }
     c->out_bytes = N;
   } else {
     GroupSpan g(c, CMSBWT_G_RLE);
@@ -532,25 +526,26 @@ static void emit_pull(cmsbwt_ctx *c, int mode) {
     lastsym.alloc((size_t)nv + 16, st); prevsym.alloc((size_t)nv + 16, st);
     nstart.alloc(((size_t)nv + 1) * 4, st); soff.alloc(((size_t)nv + 2) * 8, st);
     const u32 gV = (nv + B - 1) / B;
-    k_rled_last<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(), nv, lastsym.as<u8>());
-    size_t t1 = 0, t2 = 0;
-    cub::DeviceScan::ExclusiveScan(nullptr, t1, lastsym.as<u8>(), prevsym.as<u8>(), LastValid(), (u8)RLE_NONE, (int)nv, st);
-    EXSUM64(nullptr, t2, nstart.as<u32>(), soff.as<u64>(), (int)(nv + 1), st);
-    DBuf tmp2; tmp2.alloc(t1 > t2 ? t1 : t2, st);
-    size_t tt = t1;
-    CK(cub::DeviceScan::ExclusiveScan(tmp2.p, tt, lastsym.as<u8>(), prevsym.as<u8>(), LastValid(), (u8)RLE_NONE, (int)nv, st));
-    k_rled_count<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(), prevsym.as<u8>(), nv,
-                                   nstart.as<u32>());
-    CK(cudaMemsetAsync(nstart.as<u32>() + nv, 0, 4, st));
-    tt = t2;
-    CK(EXSUM64(tmp2.p, tt, nstart.as<u32>(), soff.as<u64>(), (int)(nv + 1), st));
     u64 R = 0;
-    CK(cudaMemcpyAsync(&R, soff.as<u64>() + nv, 8, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    if (nv) {
+      k_rled_last<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), hw, nv, lastsym.as<u8>());
+      size_t t1 = 0, t2 = 0;
+      cub::DeviceScan::ExclusiveScan(nullptr, t1, lastsym.as<u8>(), prevsym.as<u8>(), LastValid(), (u8)RLE_NONE, (int)nv, st);
+      EXSUM64(nullptr, t2, nstart.as<u32>(), soff.as<u64>(), (int)(nv + 1), st);
+      DBuf tmp2; tmp2.alloc(t1 > t2 ? t1 : t2, st);
+      size_t tt = t1;
+      CK(cub::DeviceScan::ExclusiveScan(tmp2.p, tt, lastsym.as<u8>(), prevsym.as<u8>(), LastValid(), (u8)RLE_NONE, (int)nv, st));
+      k_rled_count<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), hw, prevsym.as<u8>(), nv, nstart.as<u32>());
+      CK(cudaMemsetAsync(nstart.as<u32>() + nv, 0, 4, st));
+      tt = t2;
+      CK(EXSUM64(tmp2.p, tt, nstart.as<u32>(), soff.as<u64>(), (int)(nv + 1), st));
+      CK(cudaMemcpyAsync(&R, soff.as<u64>() + nv, 8, cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+    }
     starts.alloc((R + 1) * 8, st); syms.alloc(R + 16, st);
     c->d_rle.alloc(R * 9 + CMS_PAD, st);
-    k_rled_write<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), c->d_hw.as<u64>(), prevsym.as<u8>(),
-                                   base.as<u64>(), soff.as<u64>(), nv, starts.as<u64>(), syms.as<u8>());
+    if (nv) k_rled_write<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), hw, prevsym.as<u8>(),
+                                           base.as<u64>(), soff.as<u64>(), nv, starts.as<u64>(), syms.as<u8>());
     if (R) k_rled_records<<<(u32)((R + B - 1) / B), B, 0, st>>>(starts.as<u64>(), syms.as<u8>(), R, N, c->d_rle.as<u8>());
     c->launches += 7;
     c->out_bytes = R * 9;
@@ -560,6 +555,32 @@ static void emit_pull(cmsbwt_ctx *c, int mode) {
   }
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(st));
+  if (keep_base) keep_base->swap(base);
+}
+
+static void emit_pull(cmsbwt_ctx *c, int mode) {
+  cudaStream_t st = c->st;
+  const u32 n = c->ix.n;
+  const u64 N = c->N, H = c->H;
+  const int B = 256;
+  const u64 nd64 = c->stats.n_docs;
+  if (nd64 + n >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "documents + reference length exceed 2^32"};
+  const u32 nd = (u32)nd64, nv = nd + n - 1;
+  {
+    GroupSpan g(c, CMSBWT_G_PLACE);
+    tiles_count_heads(c);
+  }
+  DBuf base;
+  emit_from_vrec(c, mode, c->d_pcov.as<uint4>(), c->d_hw.as<u64>(), c->d_termsym.as<u8>(), nd, 0, nv, N,
+                 c->dump ? &base : nullptr);
+  if (c->dump) {
+    c->h_off.alloc(H * 8, st);
+    k_head_offsets<<<(u32)((H + B - 1) / B), B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_within.as<u32>(),
+                                                        c->ix.isa, base.as<u64>(), nd, H, c->h_off.as<u64>());
+    LAUNCH(c);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(st));
+  }
   c->d_hw.release(); c->d_pcov.release(); c->d_termsym.release();
   c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release();
 }
@@ -699,4 +720,62 @@ void shard_apply(cmsbwt_ctx *c, const u64 *plc, u64 cnt) {
   CK(cudaStreamSynchronize(st));
   if (hb) throw CmsErr{CMSBWT_E_INTERNAL, "a head placement fell outside this device's output range"};
   c->sh_base.release(); c->sh_plc.release(); c->t_he.release(); c->t_re.release();
+}
+
+// ================================================================================================
+// Multi-GPU pull emit, receiver side (sender: shard_rank_pull in tiles.cu).  This device owns the SA
+// ranks [1 + R * rper, 1 + (R + 1) * rper) (device 0 also the terminators in front of them); the records
+// of its buckets arrived grouped by source, their head lists likewise.  Scatter the records to their
+// SA rank -- a region of 16 * n / world bytes, L2-sized from 8 devices on -- and run the single-GPU
+// emit on the local buckets: offsets, fill and run-length records are all local, the output slices
+// of the devices follow each other in rank order.
+__global__ void __launch_bounds__(256) k_sh_vscatter(const uint4 *__restrict__ rec, u64 nrec, const u64 *__restrict__ rec_base,
+                                                     const u64 *__restrict__ hw_base, u32 W, u32 ndl, u32 r0, u32 nvl,
+                                                     uint4 *vrec, u32 *bad) {
+  __shared__ u64 s_rb[65], s_hb[65];
+  if (threadIdx.x <= W) s_rb[threadIdx.x] = rec_base[threadIdx.x];
+  if (threadIdx.x < W) s_hb[threadIdx.x] = hw_base[threadIdx.x];
+  __syncthreads();
+  const u64 j = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nrec) return;
+  u32 s = 0;
+  while (s + 1 < W && j >= s_rb[s + 1]) s++;
+  uint4 a = rec[j];
+  a.y += (u32)s_hb[s];
+  const u32 idx = ndl + (a.w - r0);
+  if (a.w < r0 || idx >= nvl) { *bad = 1; return; }
+  a.w = 0;
+  vrec[idx] = a;
+}
+
+void shard_emit_pull(cmsbwt_ctx *c, int mode, u32 W, u32 R, u32 nd_total, const void *recs, u64 nrecs,
+                     const u64 *rec_base, const u64 *hw_base, const void *hw, const u8 *termsym, u64 expect_bytes) {
+  cudaStream_t st = c->st;
+  const u32 n = c->ix.n;
+  const u32 rper = c->sh_rper;
+  const u64 r0 = (u64)R * rper;
+  const u32 nranks = r0 >= (u64)n - 1 ? 0u : (u32)std::min<u64>(rper, (u64)n - 1 - r0);
+  const u32 ndl = R == 0 ? nd_total : 0u;
+  const u32 nvl = ndl + nranks;
+  if (nrecs != nranks) throw CmsErr{CMSBWT_E_INTERNAL, "bucket records received != SA ranks owned"};
+  DBuf vrec, rb, hb, bad;
+  vrec.alloc(((size_t)nvl + 1) * 16, st);
+  rb.alloc((size_t)(W + 1) * 8, st); hb.alloc((size_t)W * 8, st); bad.alloc(4, st);
+  CK(cudaMemsetAsync(bad.p, 0, 4, st));
+  CK(cudaMemcpyAsync(rb.p, rec_base, (size_t)(W + 1) * 8, cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(hb.p, hw_base, (size_t)W * 8, cudaMemcpyHostToDevice, st));
+  {
+    GroupSpan g(c, CMSBWT_G_OFFSETS);
+    if (nrecs) {
+      k_sh_vscatter<<<(u32)((nrecs + 255) / 256), 256, 0, st>>>((const uint4 *)recs, nrecs, rb.as<u64>(), hb.as<u64>(), W, ndl,
+                                                               (u32)r0, nvl, vrec.as<uint4>(), bad.as<u32>());
+      LAUNCH(c);
+    }
+  }
+  u32 hbad = 0;
+  CK(cudaMemcpyAsync(&hbad, bad.p, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (hbad) throw CmsErr{CMSBWT_E_INTERNAL, "a bucket record arrived at a device that does not own its SA rank"};
+  emit_from_vrec(c, mode, vrec.as<uint4>(), (const u64 *)hw, termsym, ndl, (u32)r0, nvl, expect_bytes, nullptr);
+  c->sh_olen = expect_bytes;
 }

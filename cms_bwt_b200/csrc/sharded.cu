@@ -172,9 +172,11 @@ u64 sum(const std::vector<u64> &v) { u64 s = 0; for (u64 x : v) s += x; return s
 }  // namespace
 
 enum { PH_SIZES = 0, PH_TAILS, PH_X_TAILS, PH_RANK_OWNER, PH_X_RANKS, PH_REFINE, PH_TILES_LOCAL, PH_X_TILES,
-       PH_TILES_MERGE, PH_X_COV, PH_EMIT, PH_X_PLC, PH_APPLY, PH_RLE, PH_COUNT };
+       PH_TILES_MERGE, PH_X_COV, PH_EMIT, PH_X_PLC, PH_APPLY, PH_RLE, PH_PLACE, PH_X_VREC, PH_COUNT };
+static_assert(PH_COUNT <= 16, "cmsbwt_ctx::sh_phase_ms holds 16 phases");
 
 void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base);
+void shard_term_syms(cmsbwt_ctx *c, u8 *termsym);
 
 static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mode) {
   cudaStream_t st = c->st;
@@ -332,50 +334,136 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
   { u64 a = 0, b = 0; for (u32 s = 0; s < W; s++) { he_slab[s] = a; re_slab[s] = b; a += hrecv[s]; b += rrecv[s]; } }
   {
     Timer t(st);
-    shard_tiles_merge(c, W, R, he.p, re.p, hoffs.as<u32>(), roffs.as<u32>(), he_slab.data(), re_slab.data(), ndocs_total);
+    shard_tiles_merge(c, W, R, he.p, re.p, hoffs.as<u32>(), roffs.as<u32>(), he_slab.data(), re_slab.data(), ndocs_total,
+                      false);
     c->stats.sort_ms += t.stop();
   }
   he.release(); re.release(); hoffs.release(); roffs.release();
   ph.mark(PH_TILES_MERGE);
-  DBuf cov_full;
-  cov_full.alloc((size_t)tp * 256 * 4 * W, st);
-  cm.all_gather(c->sh_cov.p, cov_full.p, (size_t)tp * 256 * 4);
-  CK(cudaStreamSynchronize(st));
-  ph.mark(PH_X_COV);
 
-  // ---- stage 3: own output range + placements to the owners of the output ranges (:1618-1694)
+  // ---- stage 3, pull emit by SA-rank range (:1618-1694): within(h) and the bucket records where the tiles
+  // are, records + head lists to the owners of the SA ranks, offsets / fill / run-length records local.
+  // One count exchange decides the path for everybody: a device whose tiles are deeper than
+  // k_tile_rank holds sends everyone to the byte-range emit with the sort-based counting.
+  bool pulled = false;
   {
-    Timer t(st);
-    shard_emit(c, cov_full.as<u32>(), N_total, W, R, doc_base);
-    c->stats.emit_ms = t.stop();
+    const int want = getenv("CMSBWT_SHARD_EMIT") ? atoi(getenv("CMSBWT_SHARD_EMIT")) : 1;   // 0: byte-range emit (A/B)
+    bool mine = false;
+    {
+      Timer t(st);
+      if (want && ndocs_total + c->ix.n < 0xFFFFFFF0ull) mine = shard_rank_pull(c, W, R);
+      c->stats.sort_ms += t.stop();
+    }
+    std::vector<u64> my(1 + 3 * (size_t)W, 0);
+    my[0] = mine ? 1 : 0;
+    if (mine)
+      for (u32 d = 0; d < W; d++) {
+        my[1 + d] = c->sh_slot_edges[d + 1] - c->sh_slot_edges[d];
+        my[1 + W + d] = c->sh_v_hwcnt[d];
+        my[1 + 2 * W + d] = c->sh_v_bytes[d];
+      }
+    const size_t per = my.size();
+    std::vector<u64> all = cm.gather_u64(my);
+    pulled = true;
+    for (u32 s = 0; s < W; s++) pulled = pulled && all[s * per] != 0;
+    ph.mark(PH_PLACE);
+    if (pulled) {
+      std::vector<u64> qsend(W), qrecv(W), hsend2(W), hrecv2(W), rbase(W + 1, 0), hbase(W + 1, 0), olen(W, 0);
+      for (u32 d = 0; d < W; d++) {
+        qsend[d] = my[1 + d]; hsend2[d] = my[1 + W + d];
+        for (u32 s2 = 0; s2 < W; s2++) olen[d] += all[s2 * per + 1 + 2 * W + d];
+      }
+      olen[0] += ndocs_total;                          // the terminators (one byte per document) lead the output
+      for (u32 s2 = 0; s2 < W; s2++) {
+        qrecv[s2] = all[s2 * per + 1 + R]; hrecv2[s2] = all[s2 * per + 1 + W + R];
+        rbase[s2 + 1] = rbase[s2] + qrecv[s2]; hbase[s2 + 1] = hbase[s2] + hrecv2[s2];
+      }
+      if (hbase[W] >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 heads in one device's SA-rank range"};
+      u64 tot = 0, obeg = 0;
+      for (u32 d = 0; d < W; d++) { if (d < R) obeg += olen[d]; tot += olen[d]; }
+      if (tot != N_total) {
+        char buf[128];
+        snprintf(buf, sizeof buf, "coverage total %llu != N %llu", (unsigned long long)tot, (unsigned long long)N_total);
+        throw CmsErr{CMSBWT_E_INTERNAL, buf};
+      }
+      c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release();
+      // terminator symbols of this rank's documents (document order) -> rank 0
+      DBuf term_mine, term_all, vrecv, hwrecv;
+      term_mine.alloc(ndocs_local + 16, st);
+      shard_term_syms(c, term_mine.as<u8>());
+      if (R == 0) term_all.alloc(ndocs_total + 16, st);
+      vrecv.alloc((rbase[W] + 1) * 16, st); hwrecv.alloc((hbase[W] + 1) * 8, st);
+      cm.group_begin();
+      cm.a2a(c->sh_vsend.p, qsend, vrecv.p, qrecv, 16);
+      cm.a2a(c->sh_hwsend.p, hsend2, hwrecv.p, hrecv2, 8);
+      if (ndocs_local) NK(nccl().Send(term_mine.p, ndocs_local, ncclUint8, 0, cm.comm, st));
+      if (R == 0) {
+        u64 off = 0;
+        for (u32 s2 = 0; s2 < W; s2++) {
+          const u64 nds = plan[2 * s2 + 1];
+          if (nds) NK(nccl().Recv(term_all.as<u8>() + off, nds, ncclUint8, (int)s2, cm.comm, st));
+          off += nds;
+        }
+      }
+      cm.group_end();
+      CK(cudaStreamSynchronize(st));
+      c->sh_vsend.release(); c->sh_hwsend.release();
+      ph.mark(PH_X_VREC);
+      {
+        Timer t(st);
+        shard_emit_pull(c, mode, W, R, (u32)ndocs_total, vrecv.p, rbase[W], rbase.data(), hbase.data(), hwrecv.p,
+                        term_all.as<u8>(), olen[R]);
+        c->stats.emit_ms = t.stop();
+      }
+      c->sh_obeg = obeg;
+      c->sh_Ntotal = N_total;
+      ph.mark(PH_EMIT);
+    } else {
+      c->sh_vsend.release(); c->sh_hwsend.release();
+    }
   }
-  cov_full.release();
-  ph.mark(PH_EMIT);
-  std::vector<u64> psend(W), precv(W);
-  for (u32 d = 0; d < W; d++) psend[d] = c->sh_plc_cnt[d];
-  {
-    std::vector<u64> all = cm.gather_u64(psend);
-    for (u32 s = 0; s < W; s++) precv[s] = all[(size_t)s * W + R];
+  if (!pulled) {
+    shard_tiles_cov(c, ndocs_total);
+    DBuf cov_full;
+    cov_full.alloc((size_t)tp * 256 * 4 * W, st);
+    cm.all_gather(c->sh_cov.p, cov_full.p, (size_t)tp * 256 * 4);
+    CK(cudaStreamSynchronize(st));
+    ph.mark(PH_X_COV);
+
+    // ---- stage 3: own output range + placements to the owners of the output ranges (:1618-1694)
+    {
+      Timer t(st);
+      shard_emit(c, cov_full.as<u32>(), N_total, W, R, doc_base);
+      c->stats.emit_ms = t.stop();
+    }
+    cov_full.release();
+    ph.mark(PH_EMIT);
+    std::vector<u64> psend(W), precv(W);
+    for (u32 d = 0; d < W; d++) psend[d] = c->sh_plc_cnt[d];
+    {
+      std::vector<u64> all = cm.gather_u64(psend);
+      for (u32 s = 0; s < W; s++) precv[s] = all[(size_t)s * W + R];
+    }
+    DBuf plc;
+    plc.alloc((sum(precv) + 1) * 8, st);
+    cm.group_begin();
+    cm.a2a(c->sh_plc.p, psend, plc.p, precv, 8);
+    cm.group_end();
+    CK(cudaStreamSynchronize(st));
+    ph.mark(PH_X_PLC);
+    {
+      Timer t(st);
+      shard_apply(c, plc.as<u64>(), sum(precv));
+      c->stats.emit_ms += t.stop();
+    }
+    ph.mark(PH_APPLY);
   }
-  DBuf plc;
-  plc.alloc((sum(precv) + 1) * 8, st);
-  cm.group_begin();
-  cm.a2a(c->sh_plc.p, psend, plc.p, precv, 8);
-  cm.group_end();
-  CK(cudaStreamSynchronize(st));
-  ph.mark(PH_X_PLC);
-  {
-    Timer t(st);
-    shard_apply(c, plc.as<u64>(), sum(precv));
-    c->stats.emit_ms += t.stop();
-  }
-  ph.mark(PH_APPLY);
   c->sh_rle_first = 0;
   c->sh_rle_skip = 0;
   if (mode == CMSBWT_MODE_RLE) {
     // -r: every rank encodes its slice; a run that straddles rank borders belongs to the leftmost rank
     // it touches (the concatenated records are then the maximal-run RLE of the whole BWT, :1695-1777)
-    rle_encode(c, c->d_out.as<u8>(), c->sh_olen);
+    if (!pulled) rle_encode(c, c->d_out.as<u8>(), c->sh_olen);       // the pull emit wrote this slice's records itself
     const u64 nrec = c->stats.n_runs;
     u8 edge[18] = {0};
     if (nrec) {
@@ -413,6 +501,7 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
   }
   c->out_mode = mode;
   if (mode == CMSBWT_MODE_PLAIN) c->out_bytes = c->sh_olen;
+  group_collect(c);
 }
 
 extern "C" {

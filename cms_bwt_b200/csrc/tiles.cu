@@ -15,6 +15,7 @@
 // fit shared memory, tiles_build returns false and the sort-based sweep of heads.cu is used.
 #include "common.cuh"
 #include <cub/cub.cuh>
+#include <string.h>
 
 #define LT_SHIFT 8
 #define LT_W (1u << LT_SHIFT)
@@ -391,7 +392,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
                                                           const u32 *__restrict__ hoff, const u32 *__restrict__ roff,
                                                           u32 n, u32 margin, u32 smem_bytes, const u32 *__restrict__ isa,
                                                           u32 nd, uint4 *__restrict__ vrec, u64 *__restrict__ hw,
-                                                          u32 *within_out) {
+                                                          u32 *within_out, u32 t0, const u32 *__restrict__ slot) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ u32 s_cnt[LT_W], s_off[LT_W + 1], s_cur[LT_W], s_cov[LT_W];
   __shared__ u32 s_icnt[LT_W], s_ioff[LT_W + 1], s_cov1[LT_W];
@@ -414,7 +415,7 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
   u32 *s_fl = s_nl + rc;
   u32 *s_far = s_fl + rc;                        // far heads (indices into s_he)
   u16 *s_inc = (u16 *)(s_far + hc);              // per position: indices (into s_fk) of the short ranges covering it
-  const u64 Xl = (u64)((t + 1) << LT_SHIFT) + margin;
+  const u64 Xl = ((u64)(t + t0 + 1) << LT_SHIFT) + margin;      // t0: first tile of this device's range (multi-GPU)
   const u32 X = Xl > 0x7FFFFFFFull ? 0x7FFFFFFFu : (u32)Xl;
   s_cnt[tid] = 0; s_cur[tid] = 0; s_d[tid] = 0; s_d1[tid] = 0; s_icnt[tid] = 0;
   if (tid == 0) { s_d[LT_W] = 0; s_d1[LT_W] = 0; s_c1 = 0; s_c0 = 0; s_cs = 0; s_cf = 0; s_nfar = 0; }
@@ -422,8 +423,10 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
   he0.a = he0.b = 0; he0.kappa = 0;
   if (tid < hc) he0 = he[h0 + tid];
   // SA rank of this thread's position (coalesced): its bucket record goes straight to virtual-rank order
-  const u32 p_own = (t << LT_SHIFT) + tid;
+  const u32 p_own = ((t + t0) << LT_SHIFT) + tid;
   const u32 rank_own = p_own < n ? isa[p_own] : 0u;
+  // multi-GPU: the record goes to its slot of the send buffer (grouped by the owner of its SA rank)
+  const u32 slot_own = slot ? slot[(t << LT_SHIFT) + tid] : 0u;
   __syncthreads();
   for (u32 j = tid; j < rc; j += LT_THREADS) {
     const TileEnt e = re[r0 + j];
@@ -458,7 +461,10 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     // {bucket size, first head slot, heads}: one aligned 16-byte record per position, stored at its virtual
     // rank (the bucket inversion :1618-1628 as a scatter that overlaps this kernel's arithmetic); SA rank 0
     // is the terminators' bucket, which the virtual ranks below nd replace
-    if (p_own < n && rank_own) vrec[nd + rank_own - 1] = make_uint4((u32)incl + hq, h0 + ex, hq, 0u);
+    if (p_own < n && rank_own) {
+      if (slot) vrec[slot_own] = make_uint4((u32)incl + hq, h0 + ex, hq, rank_own - 1);
+      else vrec[nd + rank_own - 1] = make_uint4((u32)incl + hq, h0 + ex, hq, 0u);
+    }
   }
   __syncthreads();
   s_icnt[tid] = 0;                               // reused as the cursors of the incidence lists
@@ -658,7 +664,7 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   k_tile_rank<<<ntiles, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
                                               c->t_roff.as<u32>(), n, (u32)c->tile_margin,
                                               c->tile_short ? (u32)sm : 0u, c->ix.isa, (u32)c->stats.n_docs, c->d_pcov.as<uint4>(),
-                                              c->d_hw.as<u64>(), wo);
+                                              c->d_hw.as<u64>(), wo, 0u, nullptr);
   k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
                                                      c->d_termsym.as<u8>(), wo);
   c->launches += 2;
@@ -725,11 +731,12 @@ __global__ void __launch_bounds__(256) k_sh_tile_merge_deep(const TileEnt *src, 
   for (u32 k = blockIdx.z * 256 + threadIdx.x; k < cnt; k += gridDim.z * 256) dst[d + k] = p[k];
 }
 
+void shard_tiles_cov(cmsbwt_ctx *c, u64 ndocs_total);
 // he/re: the received slabs (slab s starts at he_slab[s] / re_slab[s] entries); hoffs/roffs: the
 // senders' offset slices for this device's tile range.  Leaves the merged entries in t_he/t_re
 // (tile-local offsets t_hoff/t_roff) and the bucket sizes of the range in sh_cov (tp * 256 entries).
 u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const void *re, const u32 *hoffs,
-                      const u32 *roffs, const u64 *he_slab, const u64 *re_slab, u64 ndocs_total) {
+                      const u32 *roffs, const u64 *he_slab, const u64 *re_slab, u64 ndocs_total, bool with_cov) {
   cudaStream_t st = c->st;
   const u32 n = c->ix.n;
   const u32 tp = c->sh_tp;
@@ -750,9 +757,11 @@ u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const 
   CK(cub::DeviceScan::ExclusiveSum(tmp.p, t1, hc.as<u32>(), mh.as<u32>(), (int)(tp + 1), st));
   t1 = tb;
   CK(cub::DeviceScan::ExclusiveSum(tmp.p, t1, rc.as<u32>(), mr.as<u32>(), (int)(tp + 1), st));
-  u32 HE = 0, R = 0;
+  u32 HE = 0, R = 0, deepest = 0;
+  k_tile_deepest<<<(tp + B - 1) / B, B, 0, st>>>(hc.as<u32>(), rc.as<u32>(), tp, acc.as<u32>() + 3);
   CK(cudaMemcpyAsync(&HE, mh.as<u32>() + tp, 4, cudaMemcpyDeviceToHost, st));
   CK(cudaMemcpyAsync(&R, mr.as<u32>() + tp, 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(&deepest, acc.as<u32>() + 3, 4, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   DBuf mhe, mre;
   mhe.alloc(((size_t)HE + 1) * sizeof(TileEnt), st); mre.alloc(((size_t)R + 1) * sizeof(TileEnt), st);
@@ -776,20 +785,34 @@ u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const 
   c->t_roff.swap(mr);
   c->sh_he = HE;
   c->sh_re = R;
+  c->launches += 7;
+  CK(cudaGetLastError());
+  c->stats.n_items = (u64)HE + R;
+  c->stats.pair_tests = 0;
+  c->tile_maxent = deepest;
+  if (with_cov) shard_tiles_cov(c, ndocs_total);
+  return c->tile_maxent;
+}
+
+// bucket sizes of this device's tile range -> sh_cov (tp * 256 entries): the byte-range emit (shard_emit)
+void shard_tiles_cov(cmsbwt_ctx *c, u64 ndocs_total) {
+  cudaStream_t st = c->st;
+  const u32 tp = c->sh_tp;
+  DBuf acc;
+  acc.alloc(16, st);
+  CK(cudaMemsetAsync(acc.p, 0, 16, st));
   c->sh_cov.alloc((size_t)tp * LT_W * 4, st);
   CK(cudaMemsetAsync(c->sh_cov.p, 0, (size_t)tp * LT_W * 4, st));
   k_tile_cov<<<tp, LT_THREADS, 0, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
-                                        c->t_roff.as<u32>(), n, (u32)ndocs_total, rank * tp, c->sh_cov.as<u32>(),
-                                        nullptr, acc.as<unsigned long long>(), acc.as<u32>() + 2);
-  c->launches += 7;
+                                        c->t_roff.as<u32>(), c->ix.n, (u32)ndocs_total, c->sh_rank * tp,
+                                        c->sh_cov.as<u32>(), nullptr, acc.as<unsigned long long>(), acc.as<u32>() + 2);
+  LAUNCH(c);
   CK(cudaGetLastError());
   unsigned long long hacc[2] = {0, 0};
   CK(cudaMemcpyAsync(hacc, acc.p, 16, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  c->stats.n_items = (u64)HE + R;
   c->stats.pair_tests = hacc[0];
   c->tile_maxent = (u32)hacc[1];
-  return c->tile_maxent;
 }
 
 __global__ void k_sh_sentinel_plc(const u32 *len, const u16 *cs, const u32 *sexcl, u64 H, u64 doc_base, u64 *plc) {
@@ -945,4 +968,146 @@ void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
   c->sh_nplc = P;
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(st));
+}
+
+// ================================================================================================
+// Multi-GPU pull emit, sender side.  The output is owned by SA-RANK range (device D emits the buckets of
+// the SA ranks [1 + D * rper, 1 + (D + 1) * rper), device 0 the terminators in front of them), so nothing
+// n-sized is replicated: the owner of a reference-position range runs k_tile_rank over its merged tiles
+// and sends every position's 16-byte bucket record and its head list to the owner of the position's SA
+// rank.  Which record goes where depends on the index alone (ISA), so the slot of every position in
+// the send buffer -- grouped by destination -- is a table built once per (index, world) and the
+// records are stored into their slots by k_tile_rank itself (the bucket inversion :1618-1628 as a
+// scatter across devices).
+__global__ void k_sh_vdest(const u32 *__restrict__ isa, u32 n, u32 p0, u32 np, u32 rper, u32 W, u32 *key, u32 *pl) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= np) return;
+  const u32 p = p0 + i;
+  const u32 r = p < n ? isa[p] : 0u;           // SA rank 0 (the sentinel suffix) is the terminators' bucket
+  key[i] = r ? (r - 1) / rper : W;
+  pl[i] = i;
+}
+// sorted by destination: slot of every local position, edges[d] = first slot of destination d (edges[W] = records)
+__global__ void k_sh_vslot(const u32 *__restrict__ ks, const u32 *__restrict__ pls, u32 np, u32 W, u32 *slot, u32 *edges) {
+  const u32 s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= np) return;
+  const u32 k = ks[s];
+  slot[pls[s]] = k < W ? s : 0xFFFFFFFFu;
+  if (s == 0) { for (u32 d = 0; d <= k && d <= W; d++) edges[d] = 0; }
+  else { for (u32 d = ks[s - 1] + 1; d <= k && d <= W; d++) edges[d] = s; }
+  if (s == np - 1) for (u32 d = k + 1; d <= W; d++) edges[d] = np;
+}
+__global__ void k_sh_rec_fields(const uint4 *__restrict__ rec, u32 ns, u32 *hz, u32 *sz) {
+  const u32 s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s > ns) return;
+  const uint4 a = s < ns ? rec[s] : make_uint4(0, 0, 0, 0);
+  hz[s] = a.z; sz[s] = a.x;
+}
+// head lists into the send buffer in slot order; a record's "first head" becomes relative to its destination's slab
+__global__ void __launch_bounds__(256) k_sh_hw_route(uint4 *rec, const u32 *__restrict__ hoff, const u32 *__restrict__ edges,
+                                                     u32 W, u32 ns, const u64 *__restrict__ hw, u64 *hws) {
+  __shared__ u32 s_e[PLC_MAXW + 1];
+  if (threadIdx.x <= W) s_e[threadIdx.x] = edges[threadIdx.x];
+  __syncthreads();
+  const u32 s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= ns) return;
+  uint4 a = rec[s];
+  u32 d = 0;
+  while (d + 1 < W && s >= s_e[d + 1]) d++;
+  const u32 o = hoff[s];
+  for (u32 j = 0; j < a.z; j++) hws[o + j] = hw[a.y + j];
+  a.y = o - hoff[s_e[d]];
+  rec[s] = a;
+}
+__global__ void k_sh_edge_counts(const u32 *hoff, const u64 *boff, const u32 *edges, u32 W, u64 *out) {
+  const u32 d = threadIdx.x;
+  if (d >= W) return;
+  out[d] = hoff[edges[d + 1]] - hoff[edges[d]];
+  out[W + d] = boff[edges[d + 1]] - boff[edges[d]];
+}
+
+// false: a tile of this device's range is deeper than k_tile_rank holds (the caller falls back to the
+// byte-range emit with the sort-based counting).  Leaves sh_vsend (records by destination, edges in
+// sh_slot_edges), sh_hwsend (head lists by destination, counts in sh_v_hwcnt) and the output bytes this
+// device's records stand for, per destination (sh_v_bytes).
+bool shard_rank_pull(cmsbwt_ctx *c, u32 W, u32 R) {
+  cudaStream_t st = c->st;
+  const u32 n = c->ix.n;
+  const u32 tp = c->sh_tp;
+  const int B = 256;
+  if (W > PLC_MAXW) throw CmsErr{CMSBWT_E_LIMIT, "more than 64 devices"};
+  if (c->tile_maxent > TR_MAX_ENTRIES || c->tile_budget <= 0 || n < 2) return false;
+  const u32 rper = (n - 1 + W - 1) / W;          // SA ranks 1 .. n-1
+  const u32 np = tp * LT_W;
+  const u64 key[5] = {W, R, n, (u64)(uintptr_t)c->ix.isa, tp};
+  if (memcmp(key, c->sh_slot_key, sizeof key) != 0 || !c->sh_slot.p) {
+    DBuf k1, k2, v1, v2, ed;
+    k1.alloc((size_t)np * 4, st); k2.alloc((size_t)np * 4, st); v1.alloc((size_t)np * 4, st); v2.alloc((size_t)np * 4, st);
+    ed.alloc((size_t)(W + 1) * 4, st);
+    c->sh_slot.alloc((size_t)np * 4, st);
+    k_sh_vdest<<<(np + B - 1) / B, B, 0, st>>>(c->ix.isa, n, R * tp * LT_W, np, rper, W, k1.as<u32>(), v1.as<u32>());
+    int bits = 1;
+    while ((1u << bits) <= W) bits++;
+    rsort_pairs32(c, k1, k2, v1, v2, np, 0, bits);
+    k_sh_vslot<<<(np + B - 1) / B, B, 0, st>>>(k1.as<u32>(), v1.as<u32>(), np, W, c->sh_slot.as<u32>(), ed.as<u32>());
+    std::vector<u32> he(W + 1);
+    CK(cudaMemcpyAsync(he.data(), ed.p, (size_t)(W + 1) * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    c->sh_slot_edges.assign(he.begin(), he.end());
+    memcpy(c->sh_slot_key, key, sizeof key);
+    c->launches += 2;
+  }
+  c->sh_rper = rper;
+  const u32 ns = (u32)c->sh_slot_edges[W];
+  DBuf ed, hz, sz, hoff, boff, tmp, cnts;
+  ed.alloc((size_t)(W + 1) * 4, st);
+  {
+    std::vector<u32> he(c->sh_slot_edges.begin(), c->sh_slot_edges.end());
+    CK(cudaMemcpyAsync(ed.p, he.data(), (size_t)(W + 1) * 4, cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));             // he is a temporary
+  }
+  c->sh_vsend.alloc(((size_t)ns + 1) * 16, st);
+  c->d_hw.alloc(((size_t)c->sh_he + 1) * 8, st);
+  c->sh_hwsend.alloc(((size_t)c->sh_he + 1) * 8, st);
+  size_t sm = tile_rank_smem(c->tile_maxent, c->tile_short != 0);
+  if (sm > 200 * 1024) sm = tile_rank_smem(c->tile_maxent, false);
+  if (sm > 32 * 1024) CK(cudaFuncSetAttribute(k_tile_rank, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  k_tile_rank<<<tp, LT_THREADS, sm, st>>>(c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(), c->t_hoff.as<u32>(),
+                                          c->t_roff.as<u32>(), n, (u32)c->tile_margin, c->tile_short ? (u32)sm : 0u,
+                                          c->ix.isa, 0u, c->sh_vsend.as<uint4>(), c->d_hw.as<u64>(), nullptr, R * tp,
+                                          c->sh_slot.as<u32>());
+  hz.alloc(((size_t)ns + 1) * 4, st); sz.alloc(((size_t)ns + 1) * 4, st);
+  hoff.alloc(((size_t)ns + 1) * 4, st); boff.alloc(((size_t)ns + 1) * 8, st);
+  cnts.alloc((size_t)2 * W * 8, st);
+  k_sh_rec_fields<<<(ns + 1 + B - 1) / B, B, 0, st>>>(c->sh_vsend.as<uint4>(), ns, hz.as<u32>(), sz.as<u32>());
+  size_t t1 = 0, t2 = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, t1, hz.as<u32>(), hoff.as<u32>(), (int)(ns + 1), st);
+  EXSUM64(nullptr, t2, sz.as<u32>(), boff.as<u64>(), (int)(ns + 1), st);
+  tmp.alloc(t1 > t2 ? t1 : t2, st);
+  size_t tt = t1;
+  CK(cub::DeviceScan::ExclusiveSum(tmp.p, tt, hz.as<u32>(), hoff.as<u32>(), (int)(ns + 1), st));
+  tt = t2;
+  CK(EXSUM64(tmp.p, tt, sz.as<u32>(), boff.as<u64>(), (int)(ns + 1), st));
+  if (ns) k_sh_hw_route<<<(ns + B - 1) / B, B, 0, st>>>(c->sh_vsend.as<uint4>(), hoff.as<u32>(), ed.as<u32>(), W, ns,
+                                                         c->d_hw.as<u64>(), c->sh_hwsend.as<u64>());
+  k_sh_edge_counts<<<1, PLC_MAXW, 0, st>>>(hoff.as<u32>(), boff.as<u64>(), ed.as<u32>(), W, cnts.as<u64>());
+  c->launches += 6;
+  CK(cudaGetLastError());
+  std::vector<u64> hc(2 * W);
+  CK(cudaMemcpyAsync(hc.data(), cnts.p, (size_t)2 * W * 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  c->sh_v_hwcnt.assign(hc.begin(), hc.begin() + W);
+  c->sh_v_bytes.assign(hc.begin() + W, hc.end());
+  c->d_hw.release();
+  return true;
+}
+
+// terminator symbols of this device's documents, in document order (the receiver is device 0)
+void shard_term_syms(cmsbwt_ctx *c, u8 *termsym) {
+  const u64 H = c->H;
+  if (!H) return;
+  k_term_syms<<<(u32)((H + 255) / 256), 256, 0, c->st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->s_sexcl.as<u32>(), H,
+                                                        termsym, nullptr);
+  LAUNCH(c);
+  CK(cudaGetLastError());
 }

@@ -563,7 +563,7 @@ def run_sharded(ctx, device, d_text_ptr, N_local, ndocs_local, rank, world, grou
 
 # ---- the C++ host layer (cms_bwt_b200/csrc/sharded.cu): the same path behind one call -----------------
 PHASES = ("sizes", "tails", "x_tails", "rank_owner", "x_ranks", "refine", "tiles_local", "x_tiles", "tiles_merge",
-          "x_cov", "emit", "x_placements", "apply", "rle")
+          "x_cov", "emit", "x_placements", "apply", "rle", "place", "x_records")
 
 
 def comm_init(ctx, rank, world, device=None, group=None):
