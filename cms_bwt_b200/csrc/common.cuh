@@ -258,7 +258,8 @@ void shard_rank_owner(cmsbwt_ctx *c, const u32 *keys, const u32 *cls, u32 M, u32
                       u8 *tie_out);
 u32 shard_rank_apply(cmsbwt_ctx *c, const u32 *rk_sorted, const u8 *tie_sorted);
 void shard_tie_keys(cmsbwt_ctx *c);
-u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off);
+u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off, const u64 *slab_off = nullptr,
+                     u32 world = 0, u64 *next_counts = nullptr);
 void shard_tiles_local(cmsbwt_ctx *c, u32 world);
 u32 shard_tiles_merge(cmsbwt_ctx *c, u32 world, u32 rank, const void *he, const void *re, const u32 *hoffs,
                       const u32 *roffs, const u64 *he_slab, const u64 *re_slab, u64 ndocs_total, bool with_cov);

@@ -107,6 +107,47 @@ __global__ void k_shx_edges(const u32 *hoff, const u32 *roff, u32 tp, u32 W, u32
   out[W + 1 + d] = roff[(size_t)d * tp];
 }
 
+// tails -> destination = owner of the key's range (fixed ranges of the key space: keys are SA ranks of
+// random-looking reference positions, so equal ranges hold about equal numbers of tails, and equal keys
+// always meet on one owner).  Counts, then one reservation per (block, destination).
+#define SHX_MAXW 64
+__global__ void __launch_bounds__(256) k_shx_part_hist(const u32 *__restrict__ key, u32 Tn, u32 kper, u32 W,
+                                                       unsigned long long *cnt) {
+  __shared__ u32 s_c[SHX_MAXW];
+  if (threadIdx.x < SHX_MAXW) s_c[threadIdx.x] = 0;
+  __syncthreads();
+  for (u32 j = blockIdx.x * blockDim.x + threadIdx.x; j < Tn; j += gridDim.x * blockDim.x)
+    atomicAdd(&s_c[min(W - 1, key[j] / kper)], 1u);
+  __syncthreads();
+  if (threadIdx.x < W && s_c[threadIdx.x]) atomicAdd(cnt + threadIdx.x, (unsigned long long)s_c[threadIdx.x]);
+}
+__global__ void k_shx_part_offsets(const unsigned long long *cnt, u32 W, unsigned long long *cur) {
+  if (threadIdx.x == 0) { unsigned long long run = 0; for (u32 d = 0; d < W; d++) { cur[d] = run; run += cnt[d]; } }
+}
+__global__ void __launch_bounds__(256) k_shx_part_scatter(const u32 *__restrict__ key, const u64 *__restrict__ label, u32 Tn,
+                                                          u32 kper, u32 W, unsigned long long *cur, u64 *kc, u32 *perm) {
+  __shared__ u32 s_c[SHX_MAXW];
+  __shared__ unsigned long long s_b[SHX_MAXW];
+  const u32 per = (Tn + gridDim.x - 1) / gridDim.x;
+  const u32 a = blockIdx.x * per, b = min(Tn, a + per);
+  if (threadIdx.x < SHX_MAXW) s_c[threadIdx.x] = 0;
+  __syncthreads();
+  for (u32 j = a + threadIdx.x; j < b; j += blockDim.x) atomicAdd(&s_c[min(W - 1, key[j] / kper)], 1u);
+  __syncthreads();
+  if (threadIdx.x < W) {
+    s_b[threadIdx.x] = s_c[threadIdx.x] ? atomicAdd(cur + threadIdx.x, (unsigned long long)s_c[threadIdx.x]) : 0ull;
+    s_c[threadIdx.x] = 0;
+  }
+  __syncthreads();
+  for (u32 j = a + threadIdx.x; j < b; j += blockDim.x) {
+    const u32 k = key[j];
+    const u32 d = min(W - 1, k / kper);
+    const u64 o = s_b[d] + atomicAdd(&s_c[d], 1u);
+    kc[o] = ((u64)k << 32) | (u32)label[j];          // (key, cls): what the owner ranks by
+    perm[o] = j;
+  }
+}
+
 namespace {
 struct Phase {
   cmsbwt_ctx *c;
@@ -169,6 +210,7 @@ struct Comm {
 };
 
 u64 sum(const std::vector<u64> &v) { u64 s = 0; for (u64 x : v) s += x; return s; }
+int isa_bits_of(u32 n) { int b = 1; while (b < 32 && (1ull << b) < (u64)n) b++; return b; }
 }  // namespace
 
 enum { PH_SIZES = 0, PH_TAILS, PH_X_TAILS, PH_RANK_OWNER, PH_X_RANKS, PH_REFINE, PH_TILES_LOCAL, PH_X_TILES,
@@ -202,37 +244,33 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
   {
     Timer t(st);
     sort_prepare(c, doc_base);
-    shard_tails_sort(c);
     c->stats.sort_ms = t.stop();
   }
   const u32 Tn = c->s_Tn;
-  ph.mark(PH_TAILS);
-  const u32 S = 1024;
   std::vector<u64> send(W, 0), recv(W, 0);
   std::vector<u64> cmat;
+  DBuf kc;
+  kc.alloc((size_t)Tn * 8 + 16, st);
+  c->sh_perm.alloc((size_t)Tn * 4 + 16, st);
   {
-    // W-1 splitters from S evenly spaced samples per rank; slabs are cut at lower bounds of key VALUES,
-    // so equal keys always land on one owner
-    DBuf smp, all, spl, lb;
-    smp.alloc(S * 4, st); all.alloc((size_t)S * 4 * W, st); spl.alloc((size_t)W * 4 + 16, st); lb.alloc((size_t)W * 4 + 16, st);
-    k_shx_sample<<<(S + B - 1) / B, B, 0, st>>>(c->sh_ks.as<u32>(), Tn, S, smp.as<u32>());
-    LAUNCH(c);
-    cm.all_gather(smp.p, all.p, S * 4);
-    std::vector<u32> hs((size_t)S * W);
-    CK(cudaMemcpyAsync(hs.data(), all.p, (size_t)S * 4 * W, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    std::sort(hs.begin(), hs.end());
-    std::vector<u32> splitters(W > 1 ? W - 1 : 0), hb(W + 1, 0);
-    for (u32 d = 1; d < W; d++) splitters[d - 1] = hs[(size_t)d * S];
-    if (W > 1) {
-      CK(cudaMemcpyAsync(spl.p, splitters.data(), (size_t)(W - 1) * 4, cudaMemcpyHostToDevice, st));
-      k_shx_lb<<<(W - 1 + 63) / 64, 64, 0, st>>>(c->sh_ks.as<u32>(), Tn, spl.as<u32>(), W - 1, lb.as<u32>());
-      LAUNCH(c);
-      CK(cudaMemcpyAsync(hb.data() + 1, lb.p, (size_t)(W - 1) * 4, cudaMemcpyDeviceToHost, st));
-      CK(cudaStreamSynchronize(st));
+    if (W > SHX_MAXW) throw CmsErr{CMSBWT_E_LIMIT, "more than 64 devices"};
+    const int kb = c->s_key_bits > 32 ? 32 : c->s_key_bits;
+    const u64 kspan = kb >= 32 ? (1ull << 32) : std::min<u64>(1ull << kb, ((u64)c->ix.n + 1) << (kb - (int)isa_bits_of(c->ix.n)));
+    const u32 kper = (u32)std::max<u64>(1, (kspan + W - 1) / W);
+    DBuf cnt, cur;
+    cnt.alloc((size_t)W * 8, st); cur.alloc((size_t)W * 8, st);
+    CK(cudaMemsetAsync(cnt.p, 0, (size_t)W * 8, st));
+    const u32 gP = (u32)std::min<u64>(148 * 8, ((u64)Tn + 255) / 256);
+    if (Tn) {
+      k_shx_part_hist<<<gP, 256, 0, st>>>(c->s_key32.as<u32>(), Tn, kper, W, cnt.as<unsigned long long>());
+      k_shx_part_offsets<<<1, 32, 0, st>>>(cnt.as<unsigned long long>(), W, cur.as<unsigned long long>());
+      k_shx_part_scatter<<<gP, 256, 0, st>>>(c->s_key32.as<u32>(), c->s_label.as<u64>(), Tn, kper, W,
+                                             cur.as<unsigned long long>(), kc.as<u64>(), c->sh_perm.as<u32>());
+      c->launches += 3;
     }
-    hb[W] = Tn;
-    for (u32 d = 0; d < W; d++) send[d] = hb[d + 1] - hb[d];
+    CK(cudaMemcpyAsync(send.data(), cnt.p, (size_t)W * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    ph.mark(PH_TAILS);
     cmat = cm.gather_u64(send);                     // count matrix cmat[src * W + dst]
   }
   u64 M64 = 0, rank_base = 0, tails_total = 0;
@@ -241,10 +279,9 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
     for (u32 s = 0; s < W; s++) { tails_total += cmat[(size_t)s * W + d]; if (d < R) rank_base += cmat[(size_t)s * W + d]; }
   if (tails_total >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 tails in the collection"};
   const u32 M = (u32)M64;
-  DBuf kc, got, rk, rc, r_out, t_out, back, backr, rs, ts;
-  kc.alloc((size_t)Tn * 8 + 16, st); got.alloc((size_t)M * 8 + 16, st);
+  DBuf got, rk, rc, r_out, t_out, back, backr, rs, ts;
+  got.alloc((size_t)M * 8 + 16, st);
   rk.alloc((size_t)M * 4 + 16, st); rc.alloc((size_t)M * 4 + 16, st);
-  if (Tn) k_shx_pack2<<<(Tn + B - 1) / B, B, 0, st>>>(c->sh_ks.as<u32>(), c->sh_cs.as<u32>(), Tn, kc.as<u64>());
   cm.group_begin();
   cm.a2a(kc.p, send, got.p, recv, 8);
   cm.group_end();
@@ -270,8 +307,8 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
   rs.release(); ts.release();
   // refinement rounds on the all-gathered (rank, rank[next^(2^h)]) keys of the tied subset (:1480-1494)
   u32 rounds = 0;
+  std::vector<u64> ms = cm.gather_u64({(u64)m});     // later rounds: every rank derives the counts itself
   for (;;) {
-    std::vector<u64> ms = cm.gather_u64({(u64)m});
     const u64 mt = sum(ms);
     if (mt == 0) break;
     if (mt >= 0xFFFFFFF0ull) throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 tied tails"};
@@ -282,9 +319,11 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
     cm.a2a_same(c->sh_tiekeys.p, m, allk.p, ms, 8);
     cm.group_end();
     CK(cudaStreamSynchronize(st));
-    u64 my_off = 0;
-    for (u32 s = 0; s < R; s++) my_off += ms[s];
-    m = shard_tie_refine(c, allk.as<u64>(), (u32)mt, (u32)my_off);
+    std::vector<u64> off(W + 1, 0), nxt(W, 0);
+    for (u32 s = 0; s < W; s++) off[s + 1] = off[s] + ms[s];
+    m = shard_tie_refine(c, allk.as<u64>(), (u32)mt, (u32)off[R], off.data(), W, nxt.data());
+    if (nxt[R] != m) throw CmsErr{CMSBWT_E_INTERNAL, "tie refinement: slab count disagrees with the local subset"};
+    ms = nxt;
     rounds++;
   }
   c->stats.rank_rounds = rounds;

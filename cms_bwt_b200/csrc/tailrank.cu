@@ -324,8 +324,24 @@ void shard_tie_keys(cmsbwt_ctx *c) {
   CK(cudaStreamSynchronize(st));
 }
 
-// every rank refines the all-gathered keys; this shard's entries are [my_off, my_off + sh_m)
-u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off) {
+// still-tied entries per source slab (every rank refines all the keys, so every rank knows the next
+// round's counts of every other rank without asking)
+__global__ void __launch_bounds__(256) k_sh_slab_ties(const u8 *__restrict__ nt, const u64 *__restrict__ off, u64 *out) {
+  __shared__ u32 s_c;
+  if (threadIdx.x == 0) s_c = 0;
+  __syncthreads();
+  u32 k = 0;
+  for (u64 j = off[blockIdx.x] + threadIdx.x; j < off[blockIdx.x + 1]; j += blockDim.x) k += nt[j] != 0;
+  k = __reduce_add_sync(0xffffffffu, k);
+  if ((threadIdx.x & 31) == 0 && k) atomicAdd(&s_c, k);
+  __syncthreads();
+  if (threadIdx.x == 0) out[blockIdx.x] = s_c;
+}
+
+// every rank refines the all-gathered keys; this shard's entries are [my_off, my_off + sh_m).
+// slab_off (world + 1 offsets of the sources' slabs) != NULL: next_counts[s] = entries of source s still tied.
+u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off, const u64 *slab_off, u32 world,
+                     u64 *next_counts) {
   cudaStream_t st = c->st;
   const int B = 256;
   const u32 m = c->sh_m;
@@ -351,6 +367,14 @@ u32 shard_tie_refine(cmsbwt_ctx *c, const u64 *allkeys, u32 m_total, u32 my_off)
   k_sh_refine_scatter<<<gM, B, 0, st>>>(keys.as<u64>(), ids.as<u32>(), grp.as<u32>(), sg.as<u32>(), m_total,
                                         nr.as<u32>(), nt.as<u8>());
   c->launches += 14;
+  DBuf so, sc;
+  if (slab_off && world) {
+    so.alloc((size_t)(world + 1) * 8, st); sc.alloc((size_t)world * 8, st);
+    CK(cudaMemcpyAsync(so.p, slab_off, (size_t)(world + 1) * 8, cudaMemcpyHostToDevice, st));
+    k_sh_slab_ties<<<world, 256, 0, st>>>(nt.as<u8>(), so.as<u64>(), sc.as<u64>());
+    CK(cudaMemcpyAsync(next_counts, sc.p, (size_t)world * 8, cudaMemcpyDeviceToHost, st));
+    LAUNCH(c);
+  }
   u32 m2 = 0;
   if (m) {
     k_sh_apply_own<<<(m + B - 1) / B, B, 0, st>>>(c->sh_sub.as<u32>(), m, nr.as<u32>() + my_off, c->s_trank.as<u32>());

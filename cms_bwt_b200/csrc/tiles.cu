@@ -979,22 +979,26 @@ void shard_place(cmsbwt_ctx *c, const u64 *base, u64 doc_base) {
 // the send buffer -- grouped by destination -- is a table built once per (index, world) and the
 // records are stored into their slots by k_tile_rank itself (the bucket inversion :1618-1628 as a
 // scatter across devices).
-__global__ void k_sh_vdest(const u32 *__restrict__ isa, u32 n, u32 p0, u32 np, u32 rper, u32 W, u32 *key, u32 *pl) {
+__global__ void k_sh_vdest(const u32 *__restrict__ isa, u32 n, u32 p0, u32 np, u32 *key, u32 *pl) {
   const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= np) return;
   const u32 p = p0 + i;
   const u32 r = p < n ? isa[p] : 0u;           // SA rank 0 (the sentinel suffix) is the terminators' bucket
-  key[i] = r ? (r - 1) / rper : W;
-  pl[i] = i;
+  key[i] = r ? r - 1 : 0xFFFFFFFFu;            // sorted by SA rank: grouped by destination, and every destination
+  pl[i] = i;                                   // receives its records in the order it stores them
 }
 // sorted by destination: slot of every local position, edges[d] = first slot of destination d (edges[W] = records)
-__global__ void k_sh_vslot(const u32 *__restrict__ ks, const u32 *__restrict__ pls, u32 np, u32 W, u32 *slot, u32 *edges) {
+__global__ void k_sh_vslot(const u32 *__restrict__ ks, const u32 *__restrict__ pls, u32 np, u32 rper, u32 W, u32 *slot,
+                           u32 *edges) {
   const u32 s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= np) return;
-  const u32 k = ks[s];
+  const u32 k = ks[s] == 0xFFFFFFFFu ? W : ks[s] / rper;
   slot[pls[s]] = k < W ? s : 0xFFFFFFFFu;
   if (s == 0) { for (u32 d = 0; d <= k && d <= W; d++) edges[d] = 0; }
-  else { for (u32 d = ks[s - 1] + 1; d <= k && d <= W; d++) edges[d] = s; }
+  else {
+    const u32 kp = ks[s - 1] == 0xFFFFFFFFu ? W : ks[s - 1] / rper;
+    for (u32 d = kp + 1; d <= k && d <= W; d++) edges[d] = s;
+  }
   if (s == np - 1) for (u32 d = k + 1; d <= W; d++) edges[d] = np;
 }
 __global__ void k_sh_rec_fields(const uint4 *__restrict__ rec, u32 ns, u32 *hz, u32 *sz) {
@@ -1045,11 +1049,9 @@ bool shard_rank_pull(cmsbwt_ctx *c, u32 W, u32 R) {
     k1.alloc((size_t)np * 4, st); k2.alloc((size_t)np * 4, st); v1.alloc((size_t)np * 4, st); v2.alloc((size_t)np * 4, st);
     ed.alloc((size_t)(W + 1) * 4, st);
     c->sh_slot.alloc((size_t)np * 4, st);
-    k_sh_vdest<<<(np + B - 1) / B, B, 0, st>>>(c->ix.isa, n, R * tp * LT_W, np, rper, W, k1.as<u32>(), v1.as<u32>());
-    int bits = 1;
-    while ((1u << bits) <= W) bits++;
-    rsort_pairs32(c, k1, k2, v1, v2, np, 0, bits);
-    k_sh_vslot<<<(np + B - 1) / B, B, 0, st>>>(k1.as<u32>(), v1.as<u32>(), np, W, c->sh_slot.as<u32>(), ed.as<u32>());
+    k_sh_vdest<<<(np + B - 1) / B, B, 0, st>>>(c->ix.isa, n, R * tp * LT_W, np, k1.as<u32>(), v1.as<u32>());
+    rsort_pairs32(c, k1, k2, v1, v2, np, 0, 32);
+    k_sh_vslot<<<(np + B - 1) / B, B, 0, st>>>(k1.as<u32>(), v1.as<u32>(), np, rper, W, c->sh_slot.as<u32>(), ed.as<u32>());
     std::vector<u32> he(W + 1);
     CK(cudaMemcpyAsync(he.data(), ed.p, (size_t)(W + 1) * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
