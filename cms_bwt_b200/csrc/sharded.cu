@@ -100,6 +100,15 @@ __global__ void k_shx_unpack_rt(const u64 *in, u32 n, u32 *rk, u8 *tie) {
   u32 j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j < n) { u64 v = in[j]; rk[j] = (u32)v; tie[j] = (u8)(v >> 32); }
 }
+// ranks below 2^31: rank | tie << 31 in one word (halves the bytes of the exchange back to the tails' origins)
+__global__ void k_shx_pack_rt32(const u32 *rk, const u8 *tie, u32 n, u32 *out) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) out[j] = rk[j] | ((u32)(tie[j] != 0) << 31);
+}
+__global__ void k_shx_unpack_rt32(const u32 *in, u32 n, u32 *rk, u8 *tie) {
+  u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n) { u32 v = in[j]; rk[j] = v & 0x7FFFFFFFu; tie[j] = (u8)(v >> 31); }
+}
 __global__ void k_shx_edges(const u32 *hoff, const u32 *roff, u32 tp, u32 W, u32 *out) {
   u32 d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d > W) return;
@@ -255,7 +264,8 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
   {
     if (W > SHX_MAXW) throw CmsErr{CMSBWT_E_LIMIT, "more than 64 devices"};
     const int kb = c->s_key_bits > 32 ? 32 : c->s_key_bits;
-    const u64 kspan = kb >= 32 ? (1ull << 32) : std::min<u64>(1ull << kb, ((u64)c->ix.n + 1) << (kb - (int)isa_bits_of(c->ix.n)));
+    // keys are (SA rank << qb | quantised cls order): they span [0, n << qb), not the whole 2^kb
+    const u64 kspan = std::min<u64>(1ull << kb, ((u64)c->ix.n + 1) << (kb - isa_bits_of(c->ix.n)));
     const u32 kper = (u32)std::max<u64>(1, (kspan + W - 1) / W);
     DBuf cnt, cur;
     cnt.alloc((size_t)W * 8, st); cur.alloc((size_t)W * 8, st);
@@ -294,11 +304,18 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
   ph.mark(PH_RANK_OWNER);
   back.alloc((size_t)M * 8 + 16, st); backr.alloc((size_t)Tn * 8 + 16, st);
   rs.alloc((size_t)Tn * 4 + 16, st); ts.alloc((size_t)Tn + 16, st);
-  if (M) k_shx_pack_rt<<<(M + B - 1) / B, B, 0, st>>>(r_out.as<u32>(), t_out.as<u8>(), M, back.as<u64>());
+  const bool rt32 = tails_total < 0x7FFFFFF0ull;
+  if (M) {
+    if (rt32) k_shx_pack_rt32<<<(M + B - 1) / B, B, 0, st>>>(r_out.as<u32>(), t_out.as<u8>(), M, back.as<u32>());
+    else k_shx_pack_rt<<<(M + B - 1) / B, B, 0, st>>>(r_out.as<u32>(), t_out.as<u8>(), M, back.as<u64>());
+  }
   cm.group_begin();
-  cm.a2a(back.p, recv, backr.p, send, 8);
+  cm.a2a(back.p, recv, backr.p, send, rt32 ? 4 : 8);
   cm.group_end();
-  if (Tn) k_shx_unpack_rt<<<(Tn + B - 1) / B, B, 0, st>>>(backr.as<u64>(), Tn, rs.as<u32>(), ts.as<u8>());
+  if (Tn) {
+    if (rt32) k_shx_unpack_rt32<<<(Tn + B - 1) / B, B, 0, st>>>(backr.as<u32>(), Tn, rs.as<u32>(), ts.as<u8>());
+    else k_shx_unpack_rt<<<(Tn + B - 1) / B, B, 0, st>>>(backr.as<u64>(), Tn, rs.as<u32>(), ts.as<u8>());
+  }
   c->launches += 2;
   CK(cudaStreamSynchronize(st));
   ph.mark(PH_X_RANKS);
