@@ -16,6 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libcmsbwt_b200.so")
 
 MODE_PLAIN, MODE_RLE = 0, 1
 UINT64_MAX = 2 ** 64 - 1
+RLE_STATIC_MAX = 1 << 30          # cmsbwt_rle_encode_static: symbols per call (include/cmsbwt_b200.h)
 
 EXPORTS = [
     "cmsbwt_ctx_create", "cmsbwt_ctx_destroy", "cmsbwt_last_error", "cmsbwt_get_stats",
@@ -31,7 +32,7 @@ EXPORTS = [
     "cmsbwt_shard_rle",
     "cmsbwt_nccl_unique_id", "cmsbwt_comm_init", "cmsbwt_comm_destroy", "cmsbwt_run_sharded",
     "cmsbwt_sharded_after_ms", "cmsbwt_sharded_rle", "cmsbwt_sharded_stats",
-    "cmsbwt_fm_build", "cmsbwt_fm_count", "cmsbwt_fm_free",
+    "cmsbwt_fm_build", "cmsbwt_fm_count", "cmsbwt_fm_free", "cmsbwt_rle_encode_static",
     "cmsbwt_parse_collection_mt", "cmsbwt_parse_piece", "cmsbwt_line_start",
     "cmsbwt_host_alloc", "cmsbwt_host_free", "cmsbwt_text_begin", "cmsbwt_text_append",
     "cmsbwt_ms_run_staged", "cmsbwt_result_read", "cmsbwt_copy_fence", "cmsbwt_copy_wait",
@@ -120,6 +121,7 @@ def lib():
         L.cmsbwt_fm_build.argtypes = [vp, C.POINTER(C.c_uint32)]
         L.cmsbwt_fm_count.argtypes = [vp, vp, vp, C.c_uint32, vp]
         L.cmsbwt_fm_free.argtypes = [vp]
+        L.cmsbwt_rle_encode_static.argtypes = [vp, vp, u64, vp, u64, vp, C.POINTER(u64), vp]
         L.cmsbwt_nccl_unique_id.argtypes = [vp]
         L.cmsbwt_comm_init.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
         L.cmsbwt_comm_destroy.argtypes = [vp]
@@ -321,6 +323,15 @@ class Context:
         out = np.zeros(len(pats), np.uint64)
         self._ck(lib().cmsbwt_fm_count(self.h, _p(flat), _p(off), len(pats), _p(out)))
         return out
+
+    def rle_encode_static(self, d_bwt, N, d_records, cap_records, d_n_records=None, stream=None, wait=True):
+        """9-byte run-length records of the device buffer d_bwt[0, N) into the device buffer d_records, with no
+        allocation in the library (static scratch, N <= RLE_STATIC_MAX); device pointers as integers.
+        wait: also return the number of records (synchronises the stream); else the call only enqueues."""
+        k = C.c_uint64(0)
+        self._ck(lib().cmsbwt_rle_encode_static(self.h, d_bwt, N, d_records, cap_records, d_n_records,
+                                                C.byref(k) if wait else None, stream))
+        return k.value if wait else None
 
     def run(self, text, mode=MODE_PLAIN, out=None):
         """ms_run + heads_sort + emit + download on host buffers (the drop-in call)."""

@@ -297,6 +297,26 @@ int cmsbwt_fm_count(cmsbwt_ctx *ctx, const uint8_t *patterns, const uint64_t *of
                     uint64_t *counts);
 int cmsbwt_fm_free(cmsbwt_ctx *ctx);
 
+/* ---- run-length records of a device-resident BWT without any allocation ----
+ * No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Encodes d_bwt[0, N) (device memory) into maximal-run records (9 bytes each: little-endian u64 run
+ * length, u8 symbol -- the .rl_bwt record of cmsbwt_emit(CMSBWT_MODE_RLE)) at d_records (device memory
+ * of the caller, room for cap_records records; records past the capacity are dropped, the count is the
+ * true one).  The number of records goes to *d_n_records (device, may be NULL) and, if n_records is
+ * not NULL, to *n_records on the host -- that alone makes the call wait for the stream; with
+ * n_records == NULL the call only enqueues three kernels.  stream: a cudaStream_t, NULL = the
+ * context's own stream.  The call performs no cudaMalloc / cudaFree and calls no allocating library
+ * routine: its scratch is a file-scope __device__ array of CMSBWT_RLE_STATIC_SCRATCH bytes that every
+ * GPU which loads the library holds until exit, which bounds N at CMSBWT_RLE_STATIC_MAX symbols per
+ * call (larger N: CMSBWT_E_LIMIT, nothing is launched).  All calls on one GPU share that array: a call
+ * writes every entry it reads, so nothing has to be cleared in between, but calls that OVERLAP on
+ * the GPU (different streams or host threads) race on it -- serialise them. */
+#define CMSBWT_RLE_STATIC_MAX (1ull << 30)
+#define CMSBWT_RLE_STATIC_SCRATCH (2 * (CMSBWT_RLE_STATIC_MAX / 4096) * 8 + 64)
+int cmsbwt_rle_encode_static(cmsbwt_ctx *ctx, const void *d_bwt, uint64_t N, void *d_records,
+                             uint64_t cap_records, uint64_t *d_n_records, uint64_t *n_records, void *stream);
+
 /* tuning knobs: "chunk_len" (text window of an MS lane; 0 = by text length, 1024..8192), "kmer_k"
  * (order of the k-mer table, 0 = largest k <= 14 with 4^k <= n; takes effect at the next
  * index_upload), "fast" (0: 8-bit warp kernel for every input), "tile_budget" (0: sort-based sweep
