@@ -294,6 +294,19 @@ __device__ __forceinline__ u64 ld8u(const u8 *p) {
 // exclusive prefix sum of u32 counts into u64 offsets (64-bit accumulator)
 #define EXSUM64(tmp_ptr, tmp_bytes, in, out, num, stream) \
   cub::DeviceScan::ExclusiveScan(tmp_ptr, tmp_bytes, in, out, cub::Sum(), (u64)0, num, stream)
+// Bucket record of the pull emit, one uint4 per virtual rank (written by k_tile_rank, read by the fill and
+// run-length kernels): x = bucket size; z = number of heads (15 bits) | VREC_INLINE | sym0 << 16 | sym1 << 24.
+// A bucket with at most two heads carries them in the record (y = within of the first, w = within of
+// the second): the fill kernel then never touches hw[] for it -- buckets are walked in SA order, their
+// head lists lie in reference-position order, so each list costs a random sector (ncu r2 final: 5.2 GB
+// read by k_fill_pull against 1.5 GB of sequential inputs).  Else y = first slot of the list in hw[].
+#define VREC_INLINE 0x8000u
+__device__ __forceinline__ u32 vrec_heads(const uint4 &a) { return a.z & 0x7FFFu; }
+// head j of the bucket as (within << 8 | symbol)
+__device__ __forceinline__ u64 vrec_head(const uint4 &a, const u64 *__restrict__ hw, u32 j) {
+  if (a.z & VREC_INLINE) return j ? (((u64)a.w << 8) | (a.z >> 24)) : (((u64)a.y << 8) | ((a.z >> 16) & 0xFFu));
+  return __ldg(hw + a.y + j);
+}
 __device__ __forceinline__ u32 cls_of(u32 pos, u32 len, u32 sm) {
   u32 E = pos + len;
   return sm ? E : 0xFFFFFFFFu - E;

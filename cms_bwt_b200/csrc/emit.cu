@@ -213,21 +213,19 @@ void rle_encode(cmsbwt_ctx *c, const u8 *out, u64 N) {
 // order: the writers' "first D-1 head chars", :1640-1643), v >= nd is SA rank r = v - nd + 1.  Per
 // virtual rank: cnt[v] = bucket size (:1618-1628 bucket inversion: k_tile_rank stores every position's
 // record at its virtual rank, the scatter overlapping that kernel's arithmetic), vsym[v] = reference
-// BWT symbol, hl[v] = (first slot << 32 | number) of the bucket's heads in hw[] (tiles.cu).  The fill
+// BWT symbol, vrec[v] = the bucket's record: its heads, inside the record or as a list in hw[] (common.cuh).  The fill
 // kernel expands the runs of its 16 KB output block in SHARED memory, pulls the head symbols of the
 // buckets it intersects into it and stores the finished block with one bulk copy (TMA,
 // cp.async.bulk.global.shared::cta) -- every output sector is written exactly once and nothing is
 // scattered into the cold output (round 1: one sector read-modify-write per head symbol).
 // ndl = terminators in front of this device's SA ranks (multi-GPU: all of them on device 0, none elsewhere),
 // r0 = SA ranks before this device's range: entry i >= ndl is SA rank 1 + r0 + (i - ndl)
-__global__ void k_vrank(const uint4 *__restrict__ vrec, const u8 *__restrict__ rbwt, const u8 *__restrict__ termsym,
-                        u32 ndl, u32 r0, u32 nv, u32 *__restrict__ cnt, u64 *__restrict__ hl, u8 *__restrict__ vsym) {
+__global__ void k_vrank(uint4 *__restrict__ vrec, const u8 *__restrict__ rbwt, const u8 *__restrict__ termsym,
+                        u32 ndl, u32 r0, u32 nv, u32 *__restrict__ cnt, u8 *__restrict__ vsym) {
   const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= nv) return;
-  if (v < ndl) { cnt[v] = 1; hl[v] = 0; vsym[v] = termsym[v]; return; }
-  const uint4 a = vrec[v];                       // {bucket size, first head slot, heads, -}, written by k_tile_rank
-  cnt[v] = a.x;
-  hl[v] = ((u64)a.y << 32) | (u64)a.z;
+  if (v < ndl) { cnt[v] = 1; vrec[v] = make_uint4(1u, 0u, 0u, 0u); vsym[v] = termsym[v]; return; }
+  cnt[v] = vrec[v].x;                            // bucket records (common.cuh), written by k_tile_rank
   vsym[v] = rbwt[r0 + (v - ndl) + 1];
 }
 
@@ -243,7 +241,7 @@ __device__ __forceinline__ void bulk_store_block(u8 *gdst, const u8 *s_src, u32 
 
 template <int STORE>      // 1 = bulk copy (TMA), 0 = 16-byte stores from shared memory
 __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restrict__ base, const u8 *__restrict__ vsym,
-                                                            const u64 *__restrict__ hl, const u64 *__restrict__ hw,
+                                                            const uint4 *__restrict__ vrec, const u64 *__restrict__ hw,
                                                             const u32 *__restrict__ bstart, u64 N, u8 *out) {
   // run starts RELATIVE to the block's first byte (a block is 16 KB: 32 bits do; starts before the block
   // clamp to 0 -- only the first run can --, starts past it to 0xFFFFFFFE)
@@ -262,9 +260,10 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
   const u32 nr = r1 - r0 + 1;                 // runs r0..r1 intersect this block
   const bool use_s = nr <= FILL_SMEM_RUNS;
   // the head list of this thread's first run is requested before anything else: its two dependent
-  // reads (hl -> hw) are in flight while the block expands the runs
-  u64 h_pre = 0, e_pre0 = 0, e_pre1 = 0;
-  if (tid < nr) h_pre = __ldg(hl + r0 + tid);
+  // reads (record -> hw) are in flight while the block expands the runs
+  uint4 h_pre = make_uint4(0u, 0u, 0u, 0u);
+  u64 e_pre0 = 0, e_pre1 = 0;
+  if (tid < nr) h_pre = __ldg(vrec + r0 + tid);
   const u64 base_r0 = __ldg(base + r0);
   if (tid == 0) s_qn = 0;
   if (use_s) {
@@ -276,10 +275,9 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
     if (tid == 0) sb[nr + 1] = 0xFFFFFFFFu;    // the last block runs one entry past base[nv] = N
     for (u32 v = tid; v < FILL_VECS; v += FILL_THREADS) s_m[v] = 0;
   }
-  if ((u32)h_pre) {
-    const u64 *e = hw + (h_pre >> 32);
-    e_pre0 = __ldg(e);
-    if ((u32)h_pre > 1) e_pre1 = __ldg(e + 1);
+  if (vrec_heads(h_pre)) {                       // heads inside the record cost nothing here
+    e_pre0 = vrec_head(h_pre, hw, 0);
+    if (vrec_heads(h_pre) > 1) e_pre1 = vrec_head(h_pre, hw, 1);
   }
   if (use_s) {
     __syncthreads();
@@ -343,17 +341,16 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
   // offset of a head inside the block = (start of its run - o0) + within; only the first run can start
   // before the block (signed arithmetic on its true start)
   for (u32 k = tid; k < nr; k += FILL_THREADS) {
-    const u64 h = k == tid ? h_pre : __ldg(hl + r0 + k);
-    const u32 nh = (u32)h;
+    const uint4 h = k == tid ? h_pre : __ldg(vrec + r0 + k);
+    const u32 nh = vrec_heads(h);
     if (!nh) continue;
     if (nh > PULL_SERIAL) {
       const u32 q = atomicAdd(&s_qn, 1u);
       if (q < PULL_QCAP) { s_q[q] = k; continue; }
     }
     const i64 b0 = k == 0 ? (i64)(base_r0 - o0) : (i64)(use_s ? (u64)sb[k] : base[r0 + k] - o0);
-    const u64 *e = hw + (h >> 32);
     for (u32 j = 0; j < nh; j++) {
-      const u64 x = (k == tid && j < 2) ? (j ? e_pre1 : e_pre0) : __ldg(e + j);
+      const u64 x = (k == tid && j < 2) ? (j ? e_pre1 : e_pre0) : vrec_head(h, hw, j);
       const i64 off = b0 + (i64)(x >> 8);
       if (off >= (i64)olen) break;             // ascending within
       if (off >= 0) s_out[off] = (u8)x;
@@ -364,10 +361,10 @@ __global__ void __launch_bounds__(FILL_THREADS) k_fill_pull(const u64 *__restric
     const u32 qn = min(s_qn, (u32)PULL_QCAP), lane = tid & 31;
     for (u32 q = tid >> 5; q < qn; q += FILL_THREADS / 32) {
       const u32 k = s_q[q];
-      const u64 h = __ldg(hl + r0 + k);
-      const u32 nh = (u32)h;
+      const uint4 h = __ldg(vrec + r0 + k);
+      const u32 nh = vrec_heads(h);                // > PULL_SERIAL: never an inline record
       const i64 b0 = k == 0 ? (i64)(base_r0 - o0) : (i64)(use_s ? (u64)sb[k] : base[r0 + k] - o0);
-      const u64 *e = hw + (h >> 32);
+      const u64 *e = hw + h.y;
       for (u32 j = lane; j < nh; j += 32) {
         const u64 x = __ldg(e + j);
         const i64 off = b0 + (i64)(x >> 8);
@@ -401,16 +398,16 @@ __global__ void k_head_offsets(const u32 *pos, const u32 *len, const u32 *within
 // through the last symbol before each bucket (a scan), and a record's length is the distance to the
 // next run start.  Nothing here is O(N).
 #define RLE_NONE 0xFFu
-__global__ void k_rled_last(const u32 *cnt, const u8 *vsym, const u64 *hl, const u64 *hw, u32 nv, u8 *lastsym) {
+__global__ void k_rled_last(const u32 *cnt, const u8 *vsym, const uint4 *vrec, const u64 *hw, u32 nv, u8 *lastsym) {
   const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= nv) return;
   const u32 c = cnt[v];
   u8 s = RLE_NONE;
   if (c) {
     s = vsym[v];
-    const u64 h = hl[v];
-    const u32 nh = (u32)h;
-    if (nh) { const u64 x = hw[(h >> 32) + nh - 1]; if ((u32)(x >> 8) == c - 1) s = (u8)x; }
+    const uint4 h = vrec[v];
+    const u32 nh = vrec_heads(h);
+    if (nh) { const u64 x = vrec_head(h, hw, nh - 1); if ((u32)(x >> 8) == c - 1) s = (u8)x; }
   }
   lastsym[v] = s;
 }
@@ -419,13 +416,12 @@ struct LastValid {
 };
 // walks the segments of bucket v; F(offset in the bucket, symbol) is called at every run start
 template <class F>
-__device__ __forceinline__ void rled_walk(u32 c, u8 vs, u64 h, const u64 *hw, u8 prev, F f) {
+__device__ __forceinline__ void rled_walk(u32 c, u8 vs, const uint4 h, const u64 *hw, u8 prev, F f) {
   if (!c) return;
-  const u32 nh = (u32)h;
-  const u64 *e = hw + (h >> 32);
+  const u32 nh = vrec_heads(h);
   u32 at = 0;
   for (u32 j = 0; j < nh; j++) {
-    const u64 x = __ldg(e + j);
+    const u64 x = vrec_head(h, hw, j);
     const u32 w = (u32)(x >> 8);
     const u8 s = (u8)x;
     if (w > at) { if (vs != prev) f(at, vs); prev = vs; }
@@ -435,21 +431,21 @@ __device__ __forceinline__ void rled_walk(u32 c, u8 vs, u64 h, const u64 *hw, u8
   }
   if (at < c && vs != prev) f(at, vs);
 }
-__global__ void k_rled_count(const u32 *cnt, const u8 *vsym, const u64 *hl, const u64 *hw, const u8 *prevsym, u32 nv,
+__global__ void k_rled_count(const u32 *cnt, const u8 *vsym, const uint4 *vrec, const u64 *hw, const u8 *prevsym, u32 nv,
                              u32 *nstart) {
   const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= nv) return;
   u32 k = 0;
-  rled_walk(cnt[v], vsym[v], hl[v], hw, prevsym[v], [&](u32, u8) { k++; });
+  rled_walk(cnt[v], vsym[v], vrec[v], hw, prevsym[v], [&](u32, u8) { k++; });
   nstart[v] = k;
 }
-__global__ void k_rled_write(const u32 *cnt, const u8 *vsym, const u64 *hl, const u64 *hw, const u8 *prevsym,
+__global__ void k_rled_write(const u32 *cnt, const u8 *vsym, const uint4 *vrec, const u64 *hw, const u8 *prevsym,
                              const u64 *base, const u64 *soff, u32 nv, u64 *starts, u8 *syms) {
   const u32 v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= nv) return;
   u64 w = soff[v];
   const u64 b0 = base[v];
-  rled_walk(cnt[v], vsym[v], hl[v], hw, prevsym[v], [&](u32 at, u8 s) { starts[w] = b0 + at; syms[w] = s; w++; });
+  rled_walk(cnt[v], vsym[v], vrec[v], hw, prevsym[v], [&](u32 at, u8 s) { starts[w] = b0 + at; syms[w] = s; w++; });
 }
 __global__ void k_rled_records(const u64 *starts, const u8 *syms, u64 R, u64 N, u8 *rec) {
   u64 k = (u64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -470,18 +466,16 @@ static int fill_store_variant() {     // measurement switch: CMSBWT_FILL_STORE=0
 // Buckets of nv virtual ranks (records vrec[], head lists hw[], terminators termsym[]) -> d_out (plain) or
 // d_rle (records) of N bytes; throws unless the bucket sizes add up to N.  keep_base: the caller wants
 // base[] (parity hook).
-static void emit_from_vrec(cmsbwt_ctx *c, int mode, const uint4 *vrec, const u64 *hw, const u8 *termsym, u32 ndl,
+static void emit_from_vrec(cmsbwt_ctx *c, int mode, uint4 *vrec, const u64 *hw, const u8 *termsym, u32 ndl,
                            u32 r0, u32 nv, u64 N, DBuf *keep_base) {
   cudaStream_t st = c->st;
   const int B = 256;
-  DBuf cnt, base, hl, vsym, tmp, bstart;
+  DBuf cnt, base, vsym, tmp, bstart;
   cnt.alloc(((size_t)nv + 1) * 4, st);
   base.alloc(((size_t)nv + 2) * 8, st);
-  hl.alloc(((size_t)nv + 1) * 8, st);
   vsym.alloc((size_t)nv + 16, st);
   GroupSpan *goff = new GroupSpan(c, CMSBWT_G_OFFSETS);
-  if (nv) k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(vrec, c->ix.rbwt, termsym, ndl, r0, nv, cnt.as<u32>(), hl.as<u64>(),
-                                                 vsym.as<u8>());
+  if (nv) k_vrank<<<(nv + B - 1) / B, B, 0, st>>>(vrec, c->ix.rbwt, termsym, ndl, r0, nv, cnt.as<u32>(), vsym.as<u8>());
   CK(cudaMemsetAsync(cnt.as<u32>() + nv, 0, 4, st));
   size_t tb = 0;
   EXSUM64(nullptr, tb, cnt.as<u32>(), base.as<u64>(), (int)(nv + 1), st);
@@ -512,10 +506,10 @@ static void emit_from_vrec(cmsbwt_ctx *c, int mode, const uint4 *vrec, const u64
     u8 *out = c->d_out.as<u8>();
     if (nblocks) {
       if (fill_store_variant() == 1)
-        k_fill_pull<1><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), hl.as<u64>(), hw,
+        k_fill_pull<1><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), vrec, hw,
                                                               bstart.as<u32>(), N, out);
       else
-        k_fill_pull<0><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), hl.as<u64>(), hw,
+        k_fill_pull<0><<<(u32)nblocks, FILL_THREADS, 0, st>>>(base.as<u64>(), vsym.as<u8>(), vrec, hw,
                                                               bstart.as<u32>(), N, out);
       LAUNCH(c);
     }
@@ -528,14 +522,14 @@ static void emit_from_vrec(cmsbwt_ctx *c, int mode, const uint4 *vrec, const u64
     const u32 gV = (nv + B - 1) / B;
     u64 R = 0;
     if (nv) {
-      k_rled_last<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), hw, nv, lastsym.as<u8>());
+      k_rled_last<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), vrec, hw, nv, lastsym.as<u8>());
       size_t t1 = 0, t2 = 0;
       cub::DeviceScan::ExclusiveScan(nullptr, t1, lastsym.as<u8>(), prevsym.as<u8>(), LastValid(), (u8)RLE_NONE, (int)nv, st);
       EXSUM64(nullptr, t2, nstart.as<u32>(), soff.as<u64>(), (int)(nv + 1), st);
       DBuf tmp2; tmp2.alloc(t1 > t2 ? t1 : t2, st);
       size_t tt = t1;
       CK(cub::DeviceScan::ExclusiveScan(tmp2.p, tt, lastsym.as<u8>(), prevsym.as<u8>(), LastValid(), (u8)RLE_NONE, (int)nv, st));
-      k_rled_count<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), hw, prevsym.as<u8>(), nv, nstart.as<u32>());
+      k_rled_count<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), vrec, hw, prevsym.as<u8>(), nv, nstart.as<u32>());
       CK(cudaMemsetAsync(nstart.as<u32>() + nv, 0, 4, st));
       tt = t2;
       CK(EXSUM64(tmp2.p, tt, nstart.as<u32>(), soff.as<u64>(), (int)(nv + 1), st));
@@ -544,7 +538,7 @@ static void emit_from_vrec(cmsbwt_ctx *c, int mode, const uint4 *vrec, const u64
     }
     starts.alloc((R + 1) * 8, st); syms.alloc(R + 16, st);
     c->d_rle.alloc(R * 9 + CMS_PAD, st);
-    if (nv) k_rled_write<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), hl.as<u64>(), hw, prevsym.as<u8>(),
+    if (nv) k_rled_write<<<gV, B, 0, st>>>(cnt.as<u32>(), vsym.as<u8>(), vrec, hw, prevsym.as<u8>(),
                                            base.as<u64>(), soff.as<u64>(), nv, starts.as<u64>(), syms.as<u8>());
     if (R) k_rled_records<<<(u32)((R + B - 1) / B), B, 0, st>>>(starts.as<u64>(), syms.as<u8>(), R, N, c->d_rle.as<u8>());
     c->launches += 7;

@@ -458,18 +458,12 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     s_cov[tid] = (u32)incl;
     s_cov1[tid] = (u32)incl1;
     if (tid == LT_THREADS - 1) { s_off[LT_W] = ex + hq; s_ioff[LT_W] = iex + s_icnt[tid]; }
-    // {bucket size, first head slot, heads}: one aligned 16-byte record per position, stored at its virtual
-    // rank (the bucket inversion :1618-1628 as a scatter that overlaps this kernel's arithmetic); SA rank 0
-    // is the terminators' bucket, which the virtual ranks below nd replace
-    if (p_own < n && rank_own) {
-      if (slot) vrec[slot_own] = make_uint4((u32)incl + hq, h0 + ex, hq, rank_own - 1);
-      else vrec[nd + rank_own - 1] = make_uint4((u32)incl + hq, h0 + ex, hq, 0u);
-    }
   }
   __syncthreads();
   s_icnt[tid] = 0;                               // reused as the cursors of the incidence lists
   __syncthreads();
   const u32 c1 = s_c1, c0 = s_c0, cs = s_cs, cf = s_cf;
+  const bool inl = slot == nullptr;              // multi-GPU records keep their SA rank in .w: no inline heads
   (void)cs;
   for (u32 k = tid; k < cs; k += LT_THREADS) {
     const u32 lh = s_fl[k], lo = lh & 0xFFFF, hi = lh >> 16;
@@ -501,7 +495,9 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
       s_far[atomicAdd(&s_nfar, 1u)] = j | (mates << 16);      // hc, mates <= 8192
       continue;
     }
-    hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);     // grouped by position, ascending within
+    // at most two heads on the position: they travel inside the bucket record (s_d / s_d1 / s_cur are free by now)
+    if (inl && s_cnt[q] <= 2) { (mates ? s_d1 : s_d)[q] = (int)w; ((u8 *)s_cur)[q * 4 + mates] = (u8)(e.b >> 8); }
+    else hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);     // grouped by position, ascending within
     if (within_out) within_out[e.a] = w;
   }
   __syncthreads();
@@ -516,8 +512,23 @@ __global__ void __launch_bounds__(LT_THREADS) k_tile_rank(const TileEnt *__restr
     c = __reduce_add_sync(0xffffffffu, c);
     if (lane == 0) {
       const u32 w = mates + s_cov1[q] + c;
-      hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);
+      if (inl && s_cnt[q] <= 2) { (mates ? s_d1 : s_d)[q] = (int)w; ((u8 *)s_cur)[q * 4 + mates] = (u8)(e.b >> 8); }
+      else hw[h0 + s_off[q] + mates] = ((u64)w << 8) | ((e.b >> 8) & 0xFF);
       if (within_out) within_out[e.a] = w;
+    }
+  }
+  __syncthreads();
+  // {bucket size, heads}: one aligned 16-byte record per position (common.cuh), stored at its virtual rank (the
+  // bucket inversion :1618-1628 as a scatter; the other CTAs of the SM hide it); SA rank 0 is the
+  // terminators' bucket, which the virtual ranks below nd replace
+  if (p_own < n && rank_own) {
+    const u32 hq = s_cnt[tid], size = s_cov[tid] + hq;
+    if (slot) vrec[slot_own] = make_uint4(size, h0 + s_off[tid], hq, rank_own - 1);
+    else if (hq == 0 || hq > 2) vrec[nd + rank_own - 1] = make_uint4(size, h0 + s_off[tid], hq, 0u);
+    else {
+      const u32 sy = s_cur[tid];
+      vrec[nd + rank_own - 1] = make_uint4(size, (u32)s_d[tid], hq | VREC_INLINE | ((sy & 0xFFu) << 16) |
+                                           (hq > 1 ? ((sy >> 8) & 0xFFu) << 24 : 0u), hq > 1 ? (u32)s_d1[tid] : 0u);
     }
   }
 }
