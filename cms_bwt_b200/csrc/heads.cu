@@ -418,12 +418,14 @@ void sort_stage(cmsbwt_ctx *c) {
     Tn = c->s_Tn;
     tail_rank(c, c->s_label.as<u64>(), c->s_key32, c->s_tid, c->s_key_bits, c->s_next.as<u32>(), Tn,
               c->s_trank.as<u32>());
-    sort_kappa(c);
+    c->s_label.release(); c->s_next.release(); c->s_tid.release(); c->s_key32.release();
   }
   DBuf &kappa = c->s_kappa, &nitems = c->s_nitems, &sexcl = c->s_sexcl;
-  // ---- brute-force tile path (tiles.cu) unless the collection is too deep for it ----
+  // ---- brute-force tile path (tiles.cu) unless the collection is too deep for it; the tile scatter forms
+  // kappa itself, the array is only built (sort_kappa) for the paths that need it more than once ----
   bool light;
-  { GroupSpan g(c, CMSBWT_G_TILES); light = c->tile_budget > 0 && tiles_build(c, kappa.as<u64>(), sexcl); }
+  { GroupSpan g(c, CMSBWT_G_TILES); light = c->tile_budget > 0 && tiles_build(c, nullptr, sexcl); }
+  if (!light && !c->s_kappa.p) { GroupSpan g(c, CMSBWT_G_RANK); sort_kappa(c); }
   if (light) {
     c->stats.light_tiles = 1;
     c->s_kappa.release(); c->s_nitems.release(); c->s_tincl.release(); c->s_trank.release();

@@ -349,8 +349,8 @@ static void run_sharded_impl(cmsbwt_ctx *c, u64 N_local, u64 ndocs_local, int mo
   // ---- stage 2b: tile entries to the owners of the reference-position ranges (:1387-1416, :368-390)
   {
     Timer t(st);
-    sort_kappa(c);
-    shard_tiles_local(c, W);
+    c->s_label.release(); c->s_next.release(); c->s_tid.release(); c->s_key32.release();
+    shard_tiles_local(c, W);                      // the tile scatter forms kappa from the tail ranks itself
     c->stats.sort_ms += t.stop();
   }
   const u32 tp = c->sh_tp;

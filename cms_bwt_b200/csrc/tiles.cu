@@ -59,7 +59,11 @@ __device__ __forceinline__ void put_range(TileEnt *re, const u32 *roff, u32 *rcu
 __global__ void __launch_bounds__(256) k_tile_scatter(const u32 *pos, const u32 *len, const u16 *cs,
                                                       const u32 *toNext, const u64 *kappa, u64 H, const u32 *hoff,
                                                       const u32 *roff, u32 *hcur, u32 *rcur, TileEnt *he,
-                                                      TileEnt *re) {
+                                                      TileEnt *re, const u32 *__restrict__ tail_incl,
+                                                      const u32 *__restrict__ trank) {
+  // kappa == NULL: kappa = (cls, rank of the phrase's tail) is formed here (heads.cu k_kappa_count) instead of
+  // being written by one kernel and read back by this one; tail_incl is monotone, so the rank reads are
+  // nearly sequential
   const int lane = threadIdx.x & 31;
   const u64 i0 = (u64)blockIdx.x * (blockDim.x * TS_ILP) + threadIdx.x;
   u32 p[TS_ILP], tn[TS_ILP], c8[TS_ILP], slot[TS_ILP];
@@ -68,9 +72,13 @@ __global__ void __launch_bounds__(256) k_tile_scatter(const u32 *pos, const u32 
 #pragma unroll
   for (int k = 0; k < TS_ILP; k++) {
     const u64 i = i0 + (u64)k * blockDim.x;
-    in[k] = i < H && len[i] != 0;
+    const u32 ln = i < H ? len[i] : 0;
+    in[k] = ln != 0;
+    const u32 c16 = in[k] ? (u32)cs[i] : 0;
     p[k] = in[k] ? pos[i] : 0; tn[k] = in[k] ? toNext[i] : 0;
-    kap[k] = in[k] ? kappa[i] : 0; c8[k] = in[k] ? (u32)(cs[i] & 0xFF) : 0;
+    c8[k] = c16 & 0xFF;
+    if (kappa) kap[k] = in[k] ? kappa[i] : 0;
+    else kap[k] = in[k] ? ((u64)cls_of(p[k], ln, c16 >> 8) << 32) | trank[tail_incl[i] - 1] : 0;
   }
 #pragma unroll
   for (int k = 0; k < TS_ILP; k++)
@@ -608,6 +616,7 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));      // reused as cursors
   CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
   if (few) {
+    if (!kappa) { sort_kappa(c); kappa = c->s_kappa.as<u64>(); }
     if ((size_t)ntiles * 16 > 40 * 1024)
       CK(cudaFuncSetAttribute(k_tile_scatter_few, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ntiles * 16)));
     k_tile_scatter_few<<<gS, B, (size_t)ntiles * 16, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
@@ -617,7 +626,8 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   } else
   k_tile_scatter<<<(u32)((H + B * TS_ILP - 1) / (B * TS_ILP)), B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                    c->h_toNext.as<u32>(), kappa, H, c->t_hoff.as<u32>(), c->t_roff.as<u32>(),
-                                   hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>());
+                                   hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(),
+                                   c->s_tincl.as<u32>(), c->s_trank.as<u32>());
   c->launches += 2;
   CK(cudaGetLastError());
   *HE_out = HE;
@@ -695,7 +705,7 @@ void shard_tiles_local(cmsbwt_ctx *c, u32 world) {
   c->sh_tp = tp;
   u32 HE = 0;
   u64 R = 0;
-  if (!tiles_scatter(c, c->s_kappa.as<u64>(), tp * world, &HE, &R))
+  if (!tiles_scatter(c, c->s_kappa.p ? c->s_kappa.as<u64>() : nullptr, tp * world, &HE, &R))
     throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 tile ranges on one device"};
   c->sh_he = HE;
   c->sh_re = R;
