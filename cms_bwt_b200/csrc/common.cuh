@@ -156,6 +156,7 @@ struct cmsbwt_ctx {
   // pull emit (single GPU, light path): per position {bucket size, first head slot}; heads grouped by
   // position as (within << 8 | symbol); terminator symbols in document order
   DBuf d_pcov, d_hw, d_termsym;
+  bool termsym_done = false;  // d_termsym was filled by the tile scatter
   u64 n_hw = 0;
   // stage 2 working set (kept in the context so that the multi-GPU shard calls can interleave
   // collectives between the phases)

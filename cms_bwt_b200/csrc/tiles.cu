@@ -60,7 +60,8 @@ __global__ void __launch_bounds__(256) k_tile_scatter(const u32 *pos, const u32 
                                                       const u32 *toNext, const u64 *kappa, u64 H, const u32 *hoff,
                                                       const u32 *roff, u32 *hcur, u32 *rcur, TileEnt *he,
                                                       TileEnt *re, const u32 *__restrict__ tail_incl,
-                                                      const u32 *__restrict__ trank) {
+                                                      const u32 *__restrict__ trank, const u32 *__restrict__ sexcl,
+                                                      u8 *termsym) {
   // kappa == NULL: kappa = (cls, rank of the phrase's tail) is formed here (heads.cu k_kappa_count) instead of
   // being written by one kernel and read back by this one; tail_incl is monotone, so the rank reads are
   // nearly sequential
@@ -74,6 +75,8 @@ __global__ void __launch_bounds__(256) k_tile_scatter(const u32 *pos, const u32 
     const u64 i = i0 + (u64)k * blockDim.x;
     const u32 ln = i < H ? len[i] : 0;
     in[k] = ln != 0;
+    // a terminator (len 0): its symbol goes to the document's place in the bucket of SA rank 0 (:1640-1643)
+    if (termsym && i < H && ln == 0) termsym[sexcl[i]] = (u8)(cs[i] & 0xFF);
     const u32 c16 = in[k] ? (u32)cs[i] : 0;
     p[k] = in[k] ? pos[i] : 0; tn[k] = in[k] ? toNext[i] : 0;
     c8[k] = c16 & 0xFF;
@@ -627,7 +630,8 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   k_tile_scatter<<<(u32)((H + B * TS_ILP - 1) / (B * TS_ILP)), B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
                                    c->h_toNext.as<u32>(), kappa, H, c->t_hoff.as<u32>(), c->t_roff.as<u32>(),
                                    hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(),
-                                   c->s_tincl.as<u32>(), c->s_trank.as<u32>());
+                                   c->s_tincl.as<u32>(), c->s_trank.as<u32>(), c->s_sexcl.as<u32>(),
+                                   c->d_termsym.p ? c->d_termsym.as<u8>() : nullptr);
   c->launches += 2;
   CK(cudaGetLastError());
   *HE_out = HE;
@@ -641,11 +645,15 @@ bool tiles_build(cmsbwt_ctx *c, const u64 *kappa, DBuf &sexcl) {
   c->light = false;
   u32 HE = 0;
   u64 R = 0;
+  // the scatter also files the terminators' symbols (document order) unless it is the few-tiles variant
+  c->termsym_done = false;
+  if (ntiles > TA_MAX_TILES) c->d_termsym.alloc((size_t)c->stats.n_docs + 16, c->st);
   // a tile deeper than shared memory holds sends the whole job to the sort-based sweep (heads.cu)
   if (!tiles_scatter(c, kappa, ntiles, &HE, &R, TR_MAX_ENTRIES)) {
-    c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release();
+    c->t_he.release(); c->t_re.release(); c->t_hoff.release(); c->t_roff.release(); c->d_termsym.release();
     return false;
   }
+  c->termsym_done = ntiles > TA_MAX_TILES;
   c->stats.n_items = (u64)HE + R;
   c->stats.pair_tests = 0;
   c->n_hw = HE;
@@ -677,7 +685,7 @@ void tiles_count_heads(cmsbwt_ctx *c) {
   if (c->dump) { c->h_within.alloc(H * 4, st); wo = c->h_within.as<u32>(); }
   c->d_hw.alloc(((size_t)c->n_hw + 1) * 8, st);
   c->d_pcov.alloc(((size_t)c->stats.n_docs + n + 1) * 16, st);     // records in virtual-rank order
-  c->d_termsym.alloc((size_t)c->stats.n_docs + 16, st);
+  if (!c->termsym_done) c->d_termsym.alloc((size_t)c->stats.n_docs + 16, st);
   // room for the per-position lists of short ranges where the deepest tile leaves it (else 24 bytes per entry)
   size_t sm = tile_rank_smem(c->tile_maxent, c->tile_short != 0);
   if (sm > 200 * 1024) sm = tile_rank_smem(c->tile_maxent, false);
@@ -686,9 +694,12 @@ void tiles_count_heads(cmsbwt_ctx *c) {
                                               c->t_roff.as<u32>(), n, (u32)c->tile_margin,
                                               c->tile_short ? (u32)sm : 0u, c->ix.isa, (u32)c->stats.n_docs, c->d_pcov.as<uint4>(),
                                               c->d_hw.as<u64>(), wo, 0u, nullptr);
-  k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
-                                                     c->d_termsym.as<u8>(), wo);
-  c->launches += 2;
+  if (!c->termsym_done || wo) {
+    k_term_syms<<<(u32)((H + 255) / 256), 256, 0, st>>>(c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_sexcl.as<u32>(), H,
+                                                       c->d_termsym.as<u8>(), wo);
+    LAUNCH(c);
+  }
+  LAUNCH(c);
   CK(cudaGetLastError());
 }
 
@@ -705,6 +716,7 @@ void shard_tiles_local(cmsbwt_ctx *c, u32 world) {
   c->sh_tp = tp;
   u32 HE = 0;
   u64 R = 0;
+  c->d_termsym.release();                        // the terminators of a shard travel separately (shard_term_syms)
   if (!tiles_scatter(c, c->s_kappa.p ? c->s_kappa.as<u64>() : nullptr, tp * world, &HE, &R))
     throw CmsErr{CMSBWT_E_LIMIT, "more than 2^32 tile ranges on one device"};
   c->sh_he = HE;
