@@ -44,12 +44,14 @@ __global__ void k_tail_first(const u32 *tflag, const u32 *tail_incl, u64 H, u32 
 }
 // label + next pointer of every tail
 __global__ void k_tail_label(const u64 *g, const u32 *pos, const u32 *len, const u16 *cs,
-                             const u32 *tail_incl, const u32 *sent_excl, const u32 *tail_first,
+                             const u32 *tail_incl, const u32 *sent_excl, const u32 *tflag,
                              const u32 *isa, u64 H, u32 Tn, int qb, u32 doc_base, u64 *label, u32 *next,
                              u32 *tid, u32 *key32) {
-  u32 t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= Tn) return;
-  u32 f = tail_first[t];
+  // one thread per HEAD; the first head of a tail (tflag) does the tail's work -- no list of first heads is
+  // built (round 2 until q14: k_tail_first + a gather here), and g / len are read where the thread stands
+  const u64 f = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= H || !tflag[f]) return;
+  const u32 t = tail_incl[f] - 1;
   u64 e = g[f] + len[f];
   // j = last head with gstart <= e (gallop from f, then bisect)
   u64 lo = f, step = 1;
@@ -370,19 +372,18 @@ void sort_prepare(cmsbwt_ctx *c, u64 doc_base) {
   c->stats.n_tails = Tn;
   c->s_Tn = Tn;
   const u32 gT = (Tn + B - 1) / B;
-  tfirst.alloc((size_t)Tn * 4, st); c->s_label.alloc((size_t)Tn * 8, st);
+  c->s_label.alloc((size_t)Tn * 8, st);
   c->s_next.alloc((size_t)Tn * 4, st); c->s_tid.alloc((size_t)Tn * 4, st);
   c->s_trank.alloc((size_t)Tn * 4, st);
-  k_tail_first<<<gH, B, 0, st>>>(tflag.as<u32>(), c->s_tincl.as<u32>(), H, tfirst.as<u32>());
   int isa_bits = 1;
   while (isa_bits < 32 && (1ull << isa_bits) < (u64)n) isa_bits++;
   const int qb = 32 - isa_bits < 6 ? 32 - isa_bits : 6;
   c->s_key_bits = isa_bits + qb;
   c->s_key32.alloc((size_t)Tn * 4, st);
-  k_tail_label<<<gT, B, 0, st>>>(g, pos, len, cs, c->s_tincl.as<u32>(), c->s_sexcl.as<u32>(), tfirst.as<u32>(),
+  k_tail_label<<<gH, B, 0, st>>>(g, pos, len, cs, c->s_tincl.as<u32>(), c->s_sexcl.as<u32>(), tflag.as<u32>(),
                                  c->ix.isa, H, Tn, qb, (u32)doc_base, c->s_label.as<u64>(), c->s_next.as<u32>(),
                                  c->s_tid.as<u32>(), c->s_key32.as<u32>());
-  c->launches += 2;
+  c->launches += 1;
   CK(cudaGetLastError());
 }
 
