@@ -68,11 +68,14 @@ __device__ __forceinline__ void rs_rank(const K (&key)[RS_ITEMS], int shift, u32
     const u32 d = (u32)(key[r] >> shift) & 255u;
     const unsigned m = __match_any_sync(0xffffffffu, d);
     const int leader = __ffs(m) - 1;
+    // one shared-memory atomic per (round, digit): a warp's atomics on one address execute in program order,
+    // so the rounds need no barrier between them and their latencies overlap (until q15 a read-modify-
+    // write by the leader with __syncwarp per round: the 16 rounds were one serial chain; ncu: 15 of 25
+    // stall cycles per issue on the short scoreboard)
     u32 old = 0;
-    if ((int)l == leader) { old = s_cnt[w][d]; s_cnt[w][d] = old + __popc(m); }
+    if ((int)l == leader) old = atomicAdd(&s_cnt[w][d], (u32)__popc(m));
     old = __shfl_sync(0xffffffffu, old, leader);
     rank[r] = old + __popc(m & lt);
-    __syncwarp();
   }
 }
 

@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include <cub/cub.cuh>
 #include <string.h>
+#include <stdlib.h>
 
 #define LT_SHIFT 8
 #define LT_W (1u << LT_SHIFT)
@@ -55,8 +56,8 @@ __device__ __forceinline__ void put_range(TileEnt *re, const u32 *roff, u32 *rcu
 
 // TS_ILP heads per thread: the slot atomics of all of them are in flight together (the kernel is
 // bound by the latency of atomic -> dependent store, not by bandwidth)
-#define TS_ILP 4
-__global__ void __launch_bounds__(256) k_tile_scatter(const u32 *pos, const u32 *len, const u16 *cs,
+template <int TS_ILP, int MINB>
+__global__ void __launch_bounds__(256, MINB) k_tile_scatter(const u32 *pos, const u32 *len, const u16 *cs,
                                                       const u32 *toNext, const u64 *kappa, u64 H, const u32 *hoff,
                                                       const u32 *roff, u32 *hcur, u32 *rcur, TileEnt *he,
                                                       TileEnt *re, const u32 *__restrict__ tail_incl,
@@ -626,12 +627,22 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
                                                            c->h_toNext.as<u32>(), kappa, H, ntiles, c->t_hoff.as<u32>(),
                                                            c->t_roff.as<u32>(), hcnt.as<u32>(), rcnt.as<u32>(),
                                                            c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>());
-  } else
-  k_tile_scatter<<<(u32)((H + B * TS_ILP - 1) / (B * TS_ILP)), B, 0, st>>>(c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(),
-                                   c->h_toNext.as<u32>(), kappa, H, c->t_hoff.as<u32>(), c->t_roff.as<u32>(),
-                                   hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(),
-                                   c->s_tincl.as<u32>(), c->s_trank.as<u32>(), c->s_sexcl.as<u32>(),
-                                   c->d_termsym.p ? c->d_termsym.as<u8>() : nullptr);
+  } else {
+    static int variant = -1;                      // measurement switch (A/B under profiles/)
+    if (variant < 0) { const char *e = getenv("CMSBWT_SCATTER_VARIANT"); variant = e ? atoi(e) : 0; }
+#define TS_LAUNCH(ILP, MINB)                                                                                            \
+    k_tile_scatter<ILP, MINB><<<(u32)((H + B * ILP - 1) / (B * ILP)), B, 0, st>>>(                                      \
+        c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>(), c->h_toNext.as<u32>(), kappa, H, c->t_hoff.as<u32>(), \
+        c->t_roff.as<u32>(), hcnt.as<u32>(), rcnt.as<u32>(), c->t_he.as<TileEnt>(), c->t_re.as<TileEnt>(),              \
+        c->s_tincl.as<u32>(), c->s_trank.as<u32>(), c->s_sexcl.as<u32>(), c->d_termsym.p ? c->d_termsym.as<u8>() : nullptr)
+    // config 3, tiles group: 4 heads x 6 CTAs 3.74 ms | 4 x (5 by registers) 3.85 | 8 x 3 4.27 | 2 x 8 3.80 | 1 x 8 3.78
+    if (variant == 1) TS_LAUNCH(4, 1);
+    else if (variant == 2) TS_LAUNCH(8, 3);
+    else if (variant == 3) TS_LAUNCH(2, 8);
+    else if (variant == 4) TS_LAUNCH(1, 8);
+    else TS_LAUNCH(4, 6);
+#undef TS_LAUNCH
+  }
   c->launches += 2;
   CK(cudaGetLastError());
   *HE_out = HE;
