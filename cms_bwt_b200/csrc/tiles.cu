@@ -49,7 +49,7 @@ __device__ __forceinline__ void put_range(TileEnt *re, const u32 *roff, u32 *rcu
                                           u64 kap) {
   u32 a = t << LT_SHIFT;
   u32 lo = max(p + 1, a) - a, hi = min(p + tn, a + LT_W - 1) - a;
-  u32 slot = roff[t] + atomicAdd(rcur + t, 1u);
+  u32 slot = atomicAdd(rcur + t, 1u);            // cursors start at the tile's offset (tiles_scatter)
   TileEnt e; e.a = lo | (hi << 16); e.b = 0; e.kappa = kap;
   re[slot] = e;
 }
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256, MINB) k_tile_scatter(const u32 *pos, cons
   }
 #pragma unroll
   for (int k = 0; k < TS_ILP; k++)
-    if (in[k]) { const u32 t = p[k] >> LT_SHIFT; slot[k] = hoff[t] + atomicAdd(hcur + t, 1u); }
+    if (in[k]) { const u32 t = p[k] >> LT_SHIFT; slot[k] = atomicAdd(hcur + t, 1u); }
 #pragma unroll
   for (int k = 0; k < TS_ILP; k++)
     if (in[k]) {
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(256, MINB) k_tile_scatter(const u32 *pos, cons
       u32 sl[8];
 #pragma unroll
       for (int j = 0; j < 8; j++)
-        if ((u32)j < nt) sl[j] = roff[ta + j] + atomicAdd(rcur + ta + j, 1u);
+        if ((u32)j < nt) sl[j] = atomicAdd(rcur + ta + j, 1u);
 #pragma unroll
       for (int j = 0; j < 8; j++)
         if ((u32)j < nt) {
@@ -617,8 +617,15 @@ static bool tiles_scatter(cmsbwt_ctx *c, const u64 *kappa, u32 ntiles, u32 *HE_o
   CK(cudaStreamSynchronize(st));
   c->t_he.alloc(((size_t)HE + 1) * sizeof(TileEnt), st);
   c->t_re.alloc(((size_t)R + 1) * sizeof(TileEnt), st);
-  CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));      // reused as cursors
-  CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
+  // the counters become cursors: relative to the tile for the few-tiles variant, ABSOLUTE slots (starting at
+  // the tile's offset) for k_tile_scatter -- one L2 request less per entry than offset + relative cursor
+  if (few) {
+    CK(cudaMemsetAsync(hcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
+    CK(cudaMemsetAsync(rcnt.p, 0, ((size_t)ntiles + 1) * 4, st));
+  } else {
+    CK(cudaMemcpyAsync(hcnt.p, c->t_hoff.p, ((size_t)ntiles + 1) * 4, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(rcnt.p, c->t_roff.p, ((size_t)ntiles + 1) * 4, cudaMemcpyDeviceToDevice, st));
+  }
   if (few) {
     if (!kappa) { sort_kappa(c); kappa = c->s_kappa.as<u64>(); }
     if ((size_t)ntiles * 16 > 40 * 1024)
