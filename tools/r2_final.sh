@@ -13,7 +13,12 @@ timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $O/r2_final_
 timeout 300 python bench.py --steps 2 --no-e2e --no-cpu-baseline > $O/r2_final_plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file $O/r2_final_launches_config3.csv \
   env CMSBWT_PROFILE=1 python bench.py --steps 2 --no-e2e --no-cpu-baseline > $O/r2_final_ncu_list.log 2>&1
-ncu --set full --clock-control none --import-source on --profile-from-start off \
-  -k 'regex:k_ms_fast|k_tile_rank|k_tile_scatter|k_fill|k_pack|k_vrank|k_tail_label|k_tr_rank0|k_msf_gather|k_tile_hist|k_kappa|k_link|k_tail_first|k_rs_hist|k_rs_pass|k_term_syms|k_tr_group_cls' \
-  -c 48 -o $O/r2_final_kernels_full env CMSBWT_PROFILE=1 python bench.py --steps 1 --no-e2e --no-cpu-baseline > $O/r2_final_ncu_full.log 2>&1
-echo "ncu rc=$?"; ls -la $O | grep r2_final
+ncu --set full --clock-control none --profile-from-start off \
+  -k 'regex:k_ms_fast|k_tile_rank|k_tile_scatter|k_fill_pull|k_pack|k_vrank|k_tail_label|k_tr_rank0|k_msf_gather|k_tile_hist|k_link|k_rs_pass<unsigned int|k_tr_group_cls' \
+  -c 24 -o $O/r2_final_kernels_full env CMSBWT_PROFILE=1 python bench.py --steps 1 --no-e2e --no-cpu-baseline > $O/r2_final_ncu_full.log 2>&1
+echo "ncu rc=$?"
+# the table is made here too: gpurun brings back at most 64 MiB
+ncu -i $O/r2_final_kernels_full.ncu-rep --page raw --csv > $O/r2_final_kernels_raw.csv 2>/dev/null
+sz=$(du -sm $O | cut -f1); echo "gpurun_out: $sz MiB"
+if [ "$sz" -gt 58 ]; then rm -f $O/r2_final_kernels_full.ncu-rep; echo "dropped the .ncu-rep (too large to bring back)"; fi
+ls -la $O | grep r2_final
