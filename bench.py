@@ -401,7 +401,7 @@ def run_multi(args, rank, world, local, dev, dist):
                        "N_symbols": int(nsym), "documents": int(sp.ndocs_total), "n_ref_augmented": int(n),
                        "heads": int(H_total), "cache": "inputs (%.1f GB per GPU) larger than L2" % (N / 1e9),
                        "parallelism": "documents sharded (stage 1), tails by key range, tiles by reference-"
-                                      "position range, output by byte range; index replicated; host layer = "
+                                      "position range, output by SA-rank range (pull emit); index replicated; host layer = "
                                       "cmsbwt_run_sharded (C++, NCCL grouped send/recv + all-gather on the library's stream)",
                        "device_ms_per_step_rank0": dev_ms_local / args.steps,
                        "kernel_stage_ms_max": lib_ms_max,

@@ -6,12 +6,12 @@
 // collective wherever data changes owner:
 //
 //   stage 1   matching statistics of this rank's documents                 (no communication)
-//   stage 2a  tails -> owners by 32-bit key range          all-to-all      (sampled splitters)
+//   stage 2a  tails -> owners by 32-bit key range          all-to-all      (fixed ranges of the key space)
 //             ranks + tie flags back                       all-to-all
 //             refinement of the still tied tails           all-gather per round (small)
 //   stage 2b  tile entries -> owners by reference-position range           all-to-all
-//             bucket sizes of every position range         all-gather
-//   stage 3   head placements -> owners by output byte range               all-to-all
+//   stage 3   bucket records + head lists -> owners by SA-rank range       all-to-all (pull emit; by output
+//             byte range with head placements for collections whose tiles are too deep for k_tile_rank)
 //
 // All collectives are enqueued on the context's own stream, so they are ordered with the kernels
 // either side of them without host synchronisation; the host only waits where it needs a count.
