@@ -248,8 +248,12 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
   unsigned long long hsep2[2] = {0, 0};
   unsigned long long &hsep = hsep2[0];
   u32 hf[2] = {0, 0};
-  cudaEvent_t e0, e1, e2;
-  cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
+  struct Ev3 {                                   // destroyed on every way out, the throwing ones included
+    cudaEvent_t a = nullptr, b = nullptr, c = nullptr;
+    Ev3() { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventCreate(&c); }
+    ~Ev3() { cudaEventDestroy(a); cudaEventDestroy(b); cudaEventDestroy(c); }
+  } ev;
+  cudaEvent_t e0 = ev.a, e1 = ev.b, e2 = ev.c;
   cudaEventRecord(e0, st);
   GroupSpan *gpack = new GroupSpan(c, CMSBWT_G_PACK);
   for (int attempt = 0; attempt < 2; attempt++) {
@@ -263,7 +267,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     CK(cudaStreamSynchronize(st));
     // a byte outside 2..127, or so many escapes (lower-case genomes: every other symbol) that the break
     // list would outgrow the text: the general 8-bit kernel takes the job
-    if (hf[0] || hsep2[1] > N / 32 + 4096) { delete gpack; cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); return false; }
+    if (hf[0] || hsep2[1] > N / 32 + 4096) { delete gpack; return false; }
     if (hsep <= sepcap) break;
     if (attempt == 1) throw CmsErr{CMSBWT_E_INTERNAL, "separator list overflow on exact-size rerun"};
     sepcap = hsep;
@@ -373,7 +377,6 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     CK(cudaStreamSynchronize(st));
     break;
   }
-  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
   c->stats.n_heads = c->H;
   c->stats.fast_path = 1;
   return true;

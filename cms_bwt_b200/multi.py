@@ -668,7 +668,11 @@ def main(argv=None):
         d0, d1 = plan[rank]
         lo = int(starts[d0]) if d0 < len(ends) else len(text)
         hi = int(ends[d1 - 1]) + 1 if d1 > d0 else lo
-    if hi == lo:
+    # decided by all ranks together: a rank that left alone would leave the others waiting in a collective
+    empty = torch.tensor([1 if hi == lo else 0], dtype=torch.int64, device=dev if dist.get_backend() == "nccl" else "cpu")
+    dist.all_reduce(empty, op=dist.ReduceOp.MAX)
+    if int(empty.item()):
+        dist.destroy_process_group()
         raise SystemExit("cms_bwt_multi: more ranks than documents")
     shard = torch.from_numpy(np.concatenate([text[lo:hi], np.full(64, 2, np.uint8)])).to(dev)
     ctx = Context(local)
