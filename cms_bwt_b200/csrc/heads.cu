@@ -13,8 +13,8 @@
 #include <utility>
 
 // ---- linking (toNext :1373, coverage deltas :368-390, tail flags) -------------------------
-__global__ void k_link(const u64 *g, const u32 *pos, const u32 *len, u64 H, u32 *toNext,
-                       i32 *diff, u32 *tflag, u32 *sflag) {
+__global__ void k_link(const u64 *__restrict__ g, const u32 *__restrict__ pos, const u32 *__restrict__ len, u64 H,
+                       u32 *__restrict__ toNext, i32 *diff, u32 *__restrict__ tflag, u32 *__restrict__ sflag) {
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= H) return;
   u32 l = len[i];
@@ -43,10 +43,11 @@ __global__ void k_tail_first(const u32 *tflag, const u32 *tail_incl, u64 H, u32 
   if (tflag[i]) tail_first[tail_incl[i] - 1] = (u32)i;
 }
 // label + next pointer of every tail
-__global__ void k_tail_label(const u64 *g, const u32 *pos, const u32 *len, const u16 *cs,
-                             const u32 *tail_incl, const u32 *sent_excl, const u32 *tflag,
-                             const u32 *isa, u64 H, u32 Tn, int qb, u32 doc_base, u64 *label, u32 *next,
-                             u32 *tid, u32 *key32) {
+__global__ void k_tail_label(const u64 *__restrict__ g, const u32 *__restrict__ pos, const u32 *__restrict__ len,
+                             const u16 *__restrict__ cs, const u32 *__restrict__ tail_incl,
+                             const u32 *__restrict__ sent_excl, const u32 *__restrict__ tflag,
+                             const u32 *__restrict__ isa, u64 H, u32 Tn, int qb, u32 doc_base, u64 *__restrict__ label,
+                             u32 *__restrict__ next, u32 *__restrict__ tid, u32 *__restrict__ key32) {
   // one thread per HEAD; the first head of a tail (tflag) does the tail's work -- no list of first heads is
   // built (round 2 until q14: k_tail_first + a gather here), and g / len are read where the thread stands
   const u64 f = (u64)blockIdx.x * blockDim.x + threadIdx.x;

@@ -195,21 +195,24 @@ __global__ void k_msf_fix(const u32 *wcnt, const u32 *wfirstpos, const u32 *wlas
   if (drop && dhead) dhead[w * WL] = 0;
 }
 
-// 8 threads per window walk its batch list and write the text-order arrays
-__global__ void __launch_bounds__(256) k_msf_gather(const uint4 *pool, const u32 *batch_next,
-                                                    const u32 *wfirst, const u32 *wcnt, const u32 *wadj,
-                                                    const u64 *woff, u64 nwin, u32 WL, u64 *g, u32 *pos,
-                                                    u32 *len, u16 *cs) {
+// GL threads per window walk its batch list and write the text-order arrays (a batch is 32 records = 512
+// bytes: with 32 lanes a warp moves one batch per step and the steps of a window are independent loads)
+template <int GL>
+__global__ void __launch_bounds__(256) k_msf_gather(const uint4 *__restrict__ pool, const u32 *__restrict__ batch_next,
+                                                    const u32 *__restrict__ wfirst, const u32 *__restrict__ wcnt,
+                                                    const u32 *__restrict__ wadj, const u64 *__restrict__ woff, u64 nwin,
+                                                    u32 WL, u64 *g, u32 *pos, u32 *len, u16 *cs) {
+  static_assert(MSF_RB % GL == 0, "a step never straddles two batches");
   u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  u64 w = gid >> 3;
-  u32 l = (u32)gid & 7;
+  u64 w = gid / GL;
+  u32 l = (u32)(gid % GL);
   if (w >= nwin) return;
   u32 cnt = wcnt[w];
   if (cnt == 0) return;
   u32 drop = cnt - wadj[w];
   u64 off = woff[w];
   u32 b = wfirst[w];
-  for (u32 j0 = 0; j0 < cnt; j0 += 8) {
+  for (u32 j0 = 0; j0 < cnt; j0 += GL) {
     if (j0 && (j0 % MSF_RB) == 0) b = batch_next[b];
     u32 j = j0 + l;
     if (j < cnt && !(j == 0 && drop)) {
@@ -368,10 +371,14 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     c->head_hint = H;
     c->h_gstart.alloc((H + 1) * 8, st); c->h_pos.alloc((H + 1) * 4, st);
     c->h_len.alloc((H + 1) * 4, st); c->h_cs.alloc((H + 1) * 2, st);
-    u64 threads = nwin * 8;
-    k_msf_gather<<<(u32)((threads + 255) / 256), 256, 0, st>>>(
-        pool.as<uint4>(), bnext.as<u32>(), wfirst.as<u32>(), wcnt.as<u32>(), wadj.as<u32>(), woff.as<u64>(),
-        nwin, WL, c->h_gstart.as<u64>(), c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>());
+    static int gl = -1;                           // measurement switch: lanes per window (8, 16, 32)
+    if (gl < 0) { const char *e = getenv("CMSBWT_GATHER_LANES"); gl = e ? atoi(e) : 16; }   // gather group at config 3: 8 lanes 0.71, 16 0.69, 32 0.71 ms
+#define MSF_GATHER(GL)                                                                                              \
+    k_msf_gather<GL><<<(u32)((nwin * GL + 255) / 256), 256, 0, st>>>(                                               \
+        pool.as<uint4>(), bnext.as<u32>(), wfirst.as<u32>(), wcnt.as<u32>(), wadj.as<u32>(), woff.as<u64>(), nwin, WL, \
+        c->h_gstart.as<u64>(), c->h_pos.as<u32>(), c->h_len.as<u32>(), c->h_cs.as<u16>())
+    if (gl == 8) MSF_GATHER(8); else if (gl == 32) MSF_GATHER(32); else MSF_GATHER(16);
+#undef MSF_GATHER
     LAUNCH(c);
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(st));

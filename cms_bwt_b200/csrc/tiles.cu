@@ -26,7 +26,8 @@
 struct __align__(16) TileEnt { u32 a, b; u64 kappa; };   // head: a = id, b = q | ch << 8; range: a = lo | hi << 16
 
 // ---- histogram of entries per tile ---------------------------------------------------------------
-__global__ void k_tile_hist(const u32 *pos, const u32 *len, const u32 *toNext, u64 H, u32 *hcnt, u32 *rcnt) {
+__global__ void k_tile_hist(const u32 *__restrict__ pos, const u32 *__restrict__ len, const u32 *__restrict__ toNext, u64 H,
+                            u32 *hcnt, u32 *rcnt) {
   const int lane = threadIdx.x & 31;
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   bool in = i < H && len[i] != 0;                  // sentinels (len 0) are placed by document index
@@ -57,10 +58,11 @@ __device__ __forceinline__ void put_range(TileEnt *re, const u32 *roff, u32 *rcu
 // TS_ILP heads per thread: the slot atomics of all of them are in flight together (the kernel is
 // bound by the latency of atomic -> dependent store, not by bandwidth)
 template <int TS_ILP, int MINB>
-__global__ void __launch_bounds__(256, MINB) k_tile_scatter(const u32 *pos, const u32 *len, const u16 *cs,
-                                                      const u32 *toNext, const u64 *kappa, u64 H, const u32 *hoff,
-                                                      const u32 *roff, u32 *hcur, u32 *rcur, TileEnt *he,
-                                                      TileEnt *re, const u32 *__restrict__ tail_incl,
+__global__ void __launch_bounds__(256, MINB) k_tile_scatter(const u32 *__restrict__ pos, const u32 *__restrict__ len,
+                                                      const u16 *__restrict__ cs, const u32 *__restrict__ toNext,
+                                                      const u64 *__restrict__ kappa, u64 H, const u32 *hoff,
+                                                      const u32 *roff, u32 *hcur, u32 *rcur, TileEnt *__restrict__ he,
+                                                      TileEnt *__restrict__ re, const u32 *__restrict__ tail_incl,
                                                       const u32 *__restrict__ trank, const u32 *__restrict__ sexcl,
                                                       u8 *termsym) {
   // kappa == NULL: kappa = (cls, rank of the phrase's tail) is formed here (heads.cu k_kappa_count) instead of
