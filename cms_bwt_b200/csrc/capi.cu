@@ -62,6 +62,8 @@ int cmsbwt_ctx_create(int dev, cmsbwt_ctx **out) {
   cmsbwt_ctx *c = new cmsbwt_ctx();
   c->dev = dev;
   if (const char *e = getenv("CMSBWT_MS_VARIANT")) c->ms_variant = atoll(e);   // measurement switch (= set_param "ms_variant")
+  if (const char *e = getenv("CMSBWT_SCATTER_MB")) c->scatter_mb = atoll(e);   // measurement switch (= set_param "scatter_mb")
+  if (const char *e = getenv("CMSBWT_TILE_MARGIN")) c->tile_margin = atoll(e); // measurement switch (= set_param "tile_margin")
   GUARD_BEGIN
   CK(cudaSetDevice(dev));
   CK(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking));
