@@ -88,7 +88,7 @@ enum {
   CMSBWT_G_GATHER = 2,    /* head records -> text-order arrays (k_msf_fix, scan, k_msf_gather)           */
   CMSBWT_G_RANK = 3,      /* linking, tail labels, radix sort + tie refinement, kappa (:1359-1494)       */
   CMSBWT_G_TILES = 4,     /* tile filing + bucket sizes: histogram, scan, scatter, k_tile_cov (:1387-1416) */
-  CMSBWT_G_OFFSETS = 5,   /* bucket inversion to SA order + offsets (k_cnt_sa, scan, k_fill_part; :1618-1628) */
+  CMSBWT_G_OFFSETS = 5,   /* bucket sizes in SA order + offsets (k_vrank / k_cnt_sa, scan, k_fill_part; :1618-1628) */
   CMSBWT_G_FILL = 6,      /* run expansion of the reference symbols (k_fill; :1640-1688)                 */
   CMSBWT_G_PLACE = 7,     /* counterSmallerThanHead + head symbols (k_tile_place / sweep; :1517-1603)    */
   CMSBWT_G_RLE = 8,       /* 9-byte run records (:1695-1777)                                             */
@@ -265,7 +265,9 @@ int cmsbwt_shard_rle(cmsbwt_ctx *ctx, uint64_t *n_records);
  *   cmsbwt_run_sharded      stage 1 on this rank's whole documents (d_text as in cmsbwt_ms_run_device,
  *                           ndocs_local = its separators), then stages 2-3 with the exchanges.  PLAIN:
  *                           this rank's slice of the BWT = bytes [*out_begin, *out_begin + *out_len) of
- *                           the whole output (*total_bytes long), in cmsbwt_shard_buffer("result").
+ *                           the whole output (*total_bytes long), in cmsbwt_shard_buffer("result"); the
+ *                           slices follow each other in rank order and are NOT of equal length (a rank
+ *                           emits the buckets of its range of SA ranks).
  *                           RLE: additionally the slice's records with border-straddling runs merged,
  *                           see cmsbwt_sharded_rle.  Collective: every rank must call it.
  *   cmsbwt_sharded_after_ms the same for a text already run through cmsbwt_ms_run / _staged
@@ -273,7 +275,9 @@ int cmsbwt_shard_rle(cmsbwt_ctx *ctx, uint64_t *n_records);
  *                           first record in the concatenated .rl_bwt
  *   cmsbwt_sharded_stats    collectives and exchanged bytes of the last job, wall time per phase (ms):
  *                           sizes, tails, x_tails, rank_owner, x_ranks, refine, tiles_local, x_tiles,
- *                           tiles_merge, x_cov, emit, x_placements, apply, rle; returns the phase count */
+ *                           tiles_merge, x_cov, emit, x_placements, apply, rle, place, x_records (x_cov,
+ *                           x_placements and apply are 0 unless the byte-range emit ran: deep tiles);
+ *                           returns the phase count */
 int cmsbwt_nccl_unique_id(void *out128);
 int cmsbwt_comm_init(cmsbwt_ctx *ctx, const void *id128, uint32_t rank, uint32_t world);
 int cmsbwt_comm_destroy(cmsbwt_ctx *ctx);
