@@ -198,6 +198,7 @@ class ShardedPath:
         self.collectives = 0
         self.phase_ms = {}
         self._t = None
+        self.pull = True           # stage 3 by SA-rank range where the ops offer it (the numpy model); False: byte ranges
 
     def _mark(self, name):
         """wall time of the phase that just ended (every device step and collective is synchronous)"""
@@ -353,6 +354,8 @@ class ShardedPath:
         # is counted by its owner with the sort-based sweep instead of the tile kernel (tiles.cu)
         self.tile_max_entries = ops.tiles_merge(W, R, he, re, hoffs, roffs, he_slab, re_slab, ndocs_total)
         self._mark("d_tiles_merge")
+        if hasattr(ops, "rank_pull") and self.pull:
+            return self._emit_pull(N_total, ndocs_total, g)
         cov = ops.buffer("cov_slice")
         cov_full = ops.empty(cov.numel() * W, cov.dtype)
         self.comm.all_gather(cov_full, cov)
@@ -371,6 +374,34 @@ class ShardedPath:
         ops.apply(got, sum(precv))
         self._mark("d_apply")
         self.out_begin, self.out_len = obeg, olen
+        return ops.buffer("result")
+
+    def _emit_pull(self, N_total, ndocs_total, g):
+        """Stage 3 as the C++ host layer does it (csrc/sharded.cu): output owned by SA-RANK range.  The owner of a
+        tile range sends every position's bucket record and head list to the owner of the position's
+        SA rank; offsets, fill and run-length records are then local, the slices follow each other in
+        rank order.  Only the numpy model offers the two steps (the CUDA steps are behind
+        cmsbwt_run_sharded, not in the cmsbwt_shard_* API)."""
+        ops, W, R = self.ops, self.world, self.rank
+        rec_cnt, hw_cnt, byte_cnt = ops.rank_pull(W, R)
+        self._mark("d_place")
+        cm = self._allgather_ints(rec_cnt + hw_cnt + byte_cnt)
+        rrecv = [cm[s_][R] for s_ in range(W)]
+        hrecv = [cm[s_][W + R] for s_ in range(W)]
+        olen = [sum(cm[s_][2 * W + d] for s_ in range(W)) for d in range(W)]
+        olen[0] += ndocs_total                     # the terminators (one byte per document) lead the output
+        if sum(olen) != N_total:
+            raise CmsBwtError(-5, "coverage total %d != N %d" % (sum(olen), N_total))
+        recs = self._a2a(ops.buffer("vrec_send"), rec_cnt, rrecv, width=2)
+        hws = self._a2a(ops.buffer("hw_send"), hw_cnt, hrecv)
+        nd = [x[1] for x in g]
+        tsend = [nd[R] if d == 0 else 0 for d in range(W)]
+        trecv = nd if R == 0 else [0] * W
+        terms = self._a2a(ops.buffer("term_send"), tsend, trecv)
+        self._mark("x_records")
+        ops.emit_pull(W, R, ndocs_total, recs, rrecv, hws, hrecv, terms, olen[R])
+        self._mark("d_emit")
+        self.out_begin, self.out_len = sum(olen[:R]), olen[R]
         return ops.buffer("result")
 
     def rle(self):

@@ -256,6 +256,87 @@ class NumpyShardOps:
         dest = (plc >> np.uint64(8)).astype(np.int64) // max(chunk, 1)
         return obeg, olen, np.bincount(dest, minlength=world)[:world].astype(np.int64).tolist()
 
+    # ---- tiles.cu: shard_rank_pull (k_tile_rank with the routing table, k_sh_hw_route): bucket records and
+    # head lists of this rank's reference positions, grouped by the owner of the position's SA rank, in
+    # SA-rank order.  Record = two 64-bit words: size | first head (relative to the destination's
+    # slab) << 32, heads | (SA rank - 1) << 32.
+    def rank_pull(self, world, rank):
+        n, tp = self.n, self.tp
+        rper = (n - 1 + world - 1) // world
+        self.rper = rper
+        recs = []                                   # (sa rank - 1, size, [(within, sym)...])
+        for t, (th, tr) in enumerate(self.tiles):
+            hq = ((th[:, 0] >> np.uint64(32)) & np.uint64(LT_W - 1)).astype(np.int64)
+            hc = ((th[:, 0] >> np.uint64(40)) & np.uint64(0xFF)).astype(np.int64)
+            lo = (tr[:, 0].astype(np.int64)) & 0xFFFF
+            hi = (tr[:, 0].astype(np.int64)) >> 16
+            for q in range(LT_W):
+                p = (rank * tp + t) * LT_W + q
+                if p >= n or self.isa[p] == 0:
+                    continue                        # SA rank 0 is the terminators' bucket
+                at = np.flatnonzero(hq == q)
+                covq = int(np.sum((lo <= q) & (q <= hi)))
+                heads = []
+                for k in at:
+                    kap = th[k, 1]
+                    w = int(np.sum(th[at, 1] < kap)) + int(np.sum((tr[:, 1] < kap) & (lo <= q) & (q <= hi)))
+                    heads.append((w, int(hc[k])))
+                recs.append((int(self.isa[p]) - 1, covq + len(at), sorted(heads)))
+        recs.sort()
+        dest = [r // rper for r, _, _ in recs]
+        rec_cnt = np.bincount(dest, minlength=world).astype(np.int64)
+        hw_cnt = np.zeros(world, np.int64)
+        byte_cnt = np.zeros(world, np.int64)
+        words, hws = [], []
+        for (r, size, heads), d in zip(recs, dest):
+            words.append(size | (int(hw_cnt[d]) << 32))
+            words.append(len(heads) | (r << 32))
+            hws += [(w << 8) | sym for w, sym in heads]
+            hw_cnt[d] += len(heads)
+            byte_cnt[d] += size
+        self.buf["vrec_send"] = _i64(np.array(words, np.uint64))
+        self.buf["hw_send"] = _i64(np.array(hws, np.uint64))
+        h = self.h
+        term = np.zeros(int(np.sum(h["len"] == 0)), np.uint8)
+        for i in np.flatnonzero(h["len"] == 0):
+            term[int(self.sexcl[i])] = h["ch"][i]
+        self.buf["term_send"] = torch.from_numpy(term)
+        return rec_cnt.tolist(), hw_cnt.tolist(), byte_cnt.tolist()
+
+    # ---- emit.cu: shard_emit_pull (k_sh_vscatter, then the single-GPU emit on this rank's SA ranks)
+    def emit_pull(self, world, rank, ndocs_total, recs, rec_counts, hws, hw_counts, terms, expect_bytes):
+        n, rper = self.n, self.rper
+        r0 = rank * rper
+        nranks = 0 if r0 >= n - 1 else min(rper, n - 1 - r0)
+        assert sum(rec_counts) == nranks, (sum(rec_counts), nranks)
+        w = _u64(recs).reshape(-1, 2)
+        hw = _u64(hws)
+        hw_base = np.concatenate([[0], np.cumsum(hw_counts)])
+        src = np.repeat(np.arange(world), rec_counts)
+        size = np.zeros(nranks, np.int64); first = np.zeros(nranks, np.int64); nh = np.zeros(nranks, np.int64)
+        seen = np.zeros(nranks, bool)
+        for j in range(len(w)):
+            r = int(w[j, 1] >> np.uint64(32)) - r0
+            assert 0 <= r < nranks and not seen[r]
+            seen[r] = True
+            size[r] = int(w[j, 0] & np.uint64(U32))
+            first[r] = int(w[j, 0] >> np.uint64(32)) + int(hw_base[src[j]])
+            nh[r] = int(w[j, 1] & np.uint64(U32))
+        assert seen.all()
+        parts = []
+        if rank == 0:
+            t = terms.numpy()
+            assert len(t) == ndocs_total
+            parts.append(t.copy())
+        for r in range(nranks):
+            b = np.full(size[r], self.ref_bwt[r0 + r + 1], np.uint8)
+            for x in hw[first[r]:first[r] + nh[r]]:
+                b[int(x >> np.uint64(8))] = int(x & np.uint64(0xFF))
+            parts.append(b)
+        self.out = np.concatenate(parts) if parts else np.zeros(0, np.uint8)
+        assert len(self.out) == expect_bytes, (len(self.out), expect_bytes)
+        self.buf["result"] = torch.from_numpy(self.out)
+
     # ---- emit.cu: shard_apply
     def apply(self, plc, count):
         p = _u64(plc)[:count]

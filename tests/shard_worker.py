@@ -40,6 +40,7 @@ def main():
     orc = O.Oracle(x)
     ops = NumpyShardOps(orc, shard)
     sp = multi.ShardedPath(ops, rank, world)
+    sp.pull = os.environ.get("CMSBWT_MODEL_EMIT", "pull") == "pull"      # stage 3 by SA-rank range / by output byte range
     out = sp.run(len(shard), b - a)
     rl, rl_first = sp.rle()
     np.savez(outp + ".%d.npz" % rank, out=out.numpy(), begin=sp.out_begin, rounds=sp.rank_rounds,

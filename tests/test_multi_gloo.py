@@ -28,7 +28,7 @@ def _free_port():
     return p
 
 
-def _run_world(x, text, workdir, name, world=2, coll_file=None):
+def _run_world(x, text, workdir, name, world=2, coll_file=None, emit="pull"):
     case = os.path.join(workdir, name + ".npz")
     if coll_file is None:
         np.savez(case, x=x, text=text)
@@ -38,7 +38,7 @@ def _run_world(x, text, workdir, name, world=2, coll_file=None):
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
-                   MASTER_PORT=str(port), OMP_NUM_THREADS="1")
+                   MASTER_PORT=str(port), OMP_NUM_THREADS="1", CMSBWT_MODEL_EMIT=emit)
         procs.append(subprocess.Popen([sys.executable, os.path.join(HERE, "shard_worker.py"), case,
                                        os.path.join(workdir, name)], env=env, stdout=subprocess.PIPE,
                                       stderr=subprocess.STDOUT))
@@ -86,14 +86,21 @@ def test_merge_rle_borders():
         [(3, 65), (3, 67), (6, 71)]
 
 
+@pytest.mark.parametrize("emit", ["pull", "bytes"])
 @pytest.mark.parametrize("world", [2, 3])
-def test_sharded_path_synthetic(workdir, world):
+def test_sharded_path_synthetic(workdir, world, emit):
+    """emit = pull: stage 3 by SA-rank range as the C++ host layer does it (csrc/sharded.cu); bytes: by output
+    byte range with head placements (the path kept for tiles too deep for k_tile_rank)"""
     ref, copies = gen_synth.make_collection(3000, 7, 0.01, 5)
     x = O.augment(ref)
     text = O.docs_to_text([np.zeros(0, np.uint8)] + copies)      # leading empty document (FASTA)
-    got, parts = _run_world(x, text, workdir, "synth%d" % world, world)
+    got, parts = _run_world(x, text, workdir, "synth%d%s" % (world, emit), world, emit=emit)
     want = O.Oracle(x).bwt(text)
     assert np.array_equal(got, want)
+    if emit == "pull":
+        # slices are the buckets of contiguous SA-rank ranges: rank 0's starts with the terminators
+        nd = int(np.sum(text == 2))
+        assert np.array_equal(parts[0]["out"][:nd], want[:nd]) and len(parts[0]["out"]) >= nd
 
 
 def test_sharded_path_duplicates_and_short_documents(workdir):
