@@ -268,7 +268,13 @@ class ShardedPath:
         Tn = ops.tails(doc_base)
         self._mark("d_tails")
         ks, cs = ops.tail_keys(), ops.tail_cls()
-        splitters = self._splitters(ks, Tn)
+        if hasattr(ops, "key_span") and self.pull:
+            # as csrc/sharded.cu: FIXED ranges of the key space (keys are SA ranks of the reference << qb: equal
+            # ranges hold about equal shares); destination = min(W - 1, key // kper)
+            kper = max(1, (ops.key_span() + W - 1) // W)
+            splitters = [min(d * kper, 0xFFFFFFFF) for d in range(1, W)]
+        else:
+            splitters = self._splitters(ks, Tn)
         b = [0] + ops.lower_bound("tail_keys", splitters) + [Tn]
         send = [b[d + 1] - b[d] for d in range(W)]
         cm = self._allgather_ints(send)             # the whole count matrix: cm[src][dst]

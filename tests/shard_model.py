@@ -63,6 +63,14 @@ class NumpyShardOps:
     def tail_cls(self):
         return self.buf["tail_cls"]
 
+    # ---- sharded.cu: the span of the 32-bit tail keys (SA rank << qb | quantised cls order)
+    def key_span(self):
+        isa_bits = 1
+        while isa_bits < 32 and (1 << isa_bits) < self.n:
+            isa_bits += 1
+        kb = isa_bits + min(6, 32 - isa_bits)
+        return min(1 << kb, (self.n + 1) << (kb - isa_bits))
+
     def lower_bound(self, name, values):
         a = _u32(self.buf[name]) if name == "tail_keys" else _u64(self.buf[name])
         return [int(np.searchsorted(a, np.array(v, dtype=a.dtype), side="left")) for v in values]
