@@ -220,20 +220,49 @@ int64_t cmsbwt_parse_collection(const uint8_t *file, int64_t size, uint64_t pref
 }
 
 // ---- index ------------------------------------------------------------------------------------
-// fast-path eligibility: x = (A|C|G|T)+ followed by the augmentation only, and the first
-// augmentation symbol sorts before 'A' (true for every pure-ACGT reference: it is 0x03)
-static void classify_x(cmsbwt_ctx *c, const uint8_t *x, uint32_t n) {
+// fast-path eligibility: x = A/C/G/T segments between runs of other symbols (N blocks, IUPAC codes, lower case;
+// the last run is the augmentation, :231-237).  The 2-bit kernel handles the runs through a run list
+// (ms_fast.cuh: msf_room_at) as long as they are few: a reference that is mostly other symbols (lower-case
+// genomes) takes the general 8-bit kernel.
+static void classify_x(cmsbwt_ctx *c, const uint8_t *x, uint32_t n, std::vector<u64> &runs, std::vector<u32> &xbk) {
   auto acgt = [](uint8_t b) { return b == 'A' || b == 'C' || b == 'G' || b == 'T'; };
-  uint32_t m = 0;
-  while (m < n && acgt(x[m])) m++;
-  bool pure = m > 0 && m < n && x[m] < 'A';
-  for (uint32_t j = m; pure && j < n; j++) if (acgt(x[j])) pure = false;
-  c->pure = pure;
-  c->n_acgt = pure ? m : 0;
+  runs.clear(); xbk.clear();
+  const size_t max_runs = (size_t)n / 8 + 16;
+  u64 bases = 0;
+  bool few = true;
+  for (uint32_t j = 0; j < n && few;) {
+    if (acgt(x[j])) { j++; bases++; continue; }
+    uint32_t e = j;
+    while (e < n && !acgt(x[e])) e++;
+    runs.push_back((u64)j | ((u64)e << 32));
+    if (runs.size() > max_runs) few = false;
+    j = e;
+  }
+  // x ends with its augmentation (x[n-1] = 0), so the last run ends at n
+  c->pure = few && bases > 0 && !runs.empty() && (u32)(runs.back() >> 32) == n;
+  c->nruns = c->pure ? (u32)runs.size() : 0;
+  c->n_acgt = c->pure ? (u32)runs.back() : 0;
+  if (c->pure && c->nruns > 1) {
+    xbk.resize(((size_t)n >> 6) + 2);
+    u32 j = 0;
+    for (size_t b = 0; b < xbk.size(); b++) {
+      while (j + 1 < runs.size() && (u32)(runs[j] >> 32) <= (b << 6)) j++;
+      xbk[b] = j;
+    }
+  }
 }
 
 static void upload_x(cmsbwt_ctx *c, const uint8_t *x, uint32_t n) {
-  classify_x(c, x, n);
+  std::vector<u64> runs;
+  std::vector<u32> xbk;
+  classify_x(c, x, n, runs, xbk);
+  c->d_xruns.alloc((runs.size() + 2) * 8, c->st);
+  c->d_xbk.alloc((xbk.size() + 2) * 4, c->st);
+  if (c->pure) {
+    CK(cudaMemcpyAsync(c->d_xruns.p, runs.data(), runs.size() * 8, cudaMemcpyHostToDevice, c->st));
+    if (!xbk.empty()) CK(cudaMemcpyAsync(c->d_xbk.p, xbk.data(), xbk.size() * 4, cudaMemcpyHostToDevice, c->st));
+    CK(cudaStreamSynchronize(c->st));            // runs / xbk are locals
+  }
   c->d_x.alloc((size_t)n + CMS_PAD, c->st);
   CK(cudaMemsetAsync(c->d_x.p, 0xFF, (size_t)n + CMS_PAD, c->st));
   CK(cudaMemcpyAsync(c->d_x.p, x, n, cudaMemcpyHostToDevice, c->st));

@@ -121,8 +121,10 @@ struct cmsbwt_ctx {
   DBuf d_x, d_sa, d_isa, d_G, d_rbwt, d_ktab;
   bool have_sa = false, have_index = false;
   // fast path (pure-ACGT reference): packed reference, {key, sa} per rank
-  bool pure = false;         // x = ACGT* + augmentation, x[n_acgt] < 'A'
-  u32 n_acgt = 0;
+  bool pure = false;         // x = A/C/G/T segments between a bounded number of runs of other symbols (the last run
+                             // is the augmentation); n_acgt = start of the last run (all there is for a pure reference)
+  u32 n_acgt = 0, nruns = 0;
+  DBuf d_xruns, d_xbk;       // the runs (start | end << 32) and, per 64 positions, the first run ending after them
   DBuf d_sak, d_slots;       // {key, sa} per rank; k-mer slot table (64 B per k-mer)
   u64 *xp = nullptr;         // packed reference, inside d_ktab's allocation
   size_t hot_bytes = 0;      // k-mer table + packed reference (L2 persistence window)

@@ -144,20 +144,21 @@ __global__ void k_ktab_mark(const u8 *x, const i32 *sa, u32 n, int k, u32 *ktab)
 }
 
 // fast path: per SA rank the 16 bases after the k-mer (big-endian) and the suffix itself
-__global__ void k_sak(const i32 *sa, const u64 *xp, u32 n, u32 n_acgt, int k, u64 *sak) {
+__global__ void k_sak(const i32 *sa, const u64 *xp, const u8 *x8, u32 n, const u64 *xruns, const u32 *xbk, u32 nruns,
+                      u32 n_acgt, int k, u64 *sak) {
   u32 r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= n) return;
   u32 s = (u32)sa[r];
-  sak[r] = (u64)msf_make_key(xp, s, n_acgt, k) | ((u64)s << 32);
+  sak[r] = (u64)msf_make_key(xp, x8, s, msf_room_at(xruns, xbk, nruns, n_acgt, s), k) | ((u64)s << 32);
 }
 
 // k-mer slot table (ms_fast.cuh): one thread per k-mer writes its 64-byte slot
-__global__ void k_slots(const u64 *sak, const u32 *ktab, const u64 *xp, u32 n, u32 n_acgt, int k, u64 K,
-                        ulonglong2 *slots) {
+__global__ void k_slots(const u64 *sak, const u32 *ktab, const u64 *xp, u32 n, const u64 *xruns, const u32 *xbk,
+                        u32 nruns, u32 n_acgt, int k, u64 K, ulonglong2 *slots) {
   u64 code = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   if (code >= K) return;
   u64 e[8];
-  msf_slot_fill(sak, ktab, xp, n, n_acgt, k, code, e);
+  msf_slot_fill(sak, ktab, xp, n, xruns, xbk, nruns, n_acgt, k, code, e);
 #pragma unroll
   for (int j = 0; j < 4; j++) slots[code * 4 + j] = make_ulonglong2(e[2 * j], e[2 * j + 1]);
 }
@@ -222,12 +223,15 @@ void index_build(cmsbwt_ctx *c) {
     DBuf fl;
     fl.alloc(8, st);
     CK(cudaMemsetAsync(fl.p, 0, 8, st));
-    pack_2bit(c, x, c->n_acgt, c->xp, nwords, nullptr, 0, nullptr, fl.as<u32>());
-    k_sak<<<g, B, 0, st>>>(sa, c->xp, n, c->n_acgt, k, c->d_sak.as<u64>());
+    // the whole of x is packed: inside the runs of other symbols the codes are arbitrary and never compared
+    pack_2bit(c, x, n, c->xp, nwords, nullptr, 0, nullptr, fl.as<u32>());
+    k_sak<<<g, B, 0, st>>>(sa, c->xp, x, n, c->d_xruns.as<u64>(), c->d_xbk.as<u32>(), c->nruns, c->n_acgt, k,
+                           c->d_sak.as<u64>());
     if (c->use_slots) {
       c->d_slots.alloc(K * 64, st);
-      k_slots<<<(u32)((K + B - 1) / B), B, 0, st>>>(c->d_sak.as<u64>(), c->d_ktab.as<u32>(), c->xp, n, c->n_acgt,
-                                                    k, (u64)K, (ulonglong2 *)c->d_slots.p);
+      k_slots<<<(u32)((K + B - 1) / B), B, 0, st>>>(c->d_sak.as<u64>(), c->d_ktab.as<u32>(), c->xp, n,
+                                                    c->d_xruns.as<u64>(), c->d_xbk.as<u32>(), c->nruns, c->n_acgt, k,
+                                                    (u64)K, (ulonglong2 *)c->d_slots.p);
     } else {
       c->d_slots.release();
     }

@@ -315,6 +315,7 @@ bool ms_stage_fast(cmsbwt_ctx *c) {
     P.slots = c->d_slots.as<u64>();
     P.xp = c->xp; P.x8 = c->ix.x; P.sak = c->d_sak.as<u64>(); P.ktab = c->ix.ktab; P.G = c->ix.G;
     P.n = c->ix.n; P.n_acgt = c->n_acgt; P.k = c->ix.k;
+    P.xruns = c->d_xruns.as<u64>(); P.xbk = c->d_xbk.as<u32>(); P.nruns = c->nruns;
     P.tp = c->d_tp.as<u64>(); P.t8 = c->text; P.N = N; P.seps = c->d_seps.as<u64>(); P.nseps = nseps; P.wsep = wsep.as<u32>();
     P.WL = WL; P.nwin = nwin; P.skip_min = (u32)c->skip_min; P.variant = (u32)c->ms_variant;
     P.pool = pool.as<u32>(); P.batch_next = bnext.as<u32>(); P.nb_cap = (u32)nb; P.nb_used = nbused.as<u32>();

@@ -121,16 +121,39 @@ MSF_HD msf_u32 msf_lce(const msf_u64 *tp, msf_u64 i, const msf_u64 *xp, msf_u64 
   return m < maxl ? m : maxl;
 }
 
+// ---- the reference's symbols outside A,C,G,T ---------------------------------------------------
+// x = A/C/G/T segments between RUNS of other symbols (N blocks, IUPAC codes, lower case, and always the
+// augmentation at the end, :231-237).  The 2-bit reference holds an arbitrary code inside a run; a match
+// never enters one on 2-bit data: room(s) = number of A/C/G/T symbols from s up to the next run.
+// xruns[j] = start | end << 32 (sorted, the last run ends at n), xbk[b] = first run that ends after
+// position 64 b.  One run (the augmentation alone: every pure reference) needs no table at all.
+MSF_HD msf_u32 msf_room_at(const msf_u64 *xruns, const msf_u32 *xbk, msf_u32 nruns, msf_u32 n_acgt, msf_u32 s) {
+  if (nruns <= 1) return s < n_acgt ? n_acgt - s : 0u;
+  msf_u32 j = MSF_LD32(xbk + (s >> 6));
+  msf_u64 r = MSF_LD64(xruns + j);
+  while ((msf_u32)(r >> 32) <= s) { j++; r = MSF_LD64(xruns + j); }
+  const msf_u32 st = (msf_u32)r;
+  return st > s ? st - s : 0u;
+}
+
 // ---- index construction helpers (shared by index.cu and the CPU harness) ----------------------
-// key of the suffix s: the 16 bases after its first k, big-endian, bases past n_acgt as zeros;
-// suffixes with fewer than k pure bases get the largest key (they sort after every member of the
-// k-mer bucket they fall into).
-MSF_HD msf_u32 msf_make_key(const msf_u64 *xp, msf_u32 s, msf_u32 n_acgt, int k) {
-  if ((msf_u64)s + (msf_u32)k > n_acgt) return 0xFFFFFFFFu;
-  msf_u32 valid = n_acgt - (s + (msf_u32)k);
+// key of the suffix s (room = msf_room_at(s)): the 16 bases after its first k, big-endian; suffixes with
+// fewer than k pure bases get the largest key (they sort after every member of the k-mer bucket they
+// fall into).  A suffix whose run starts inside the 16 bases gets, from there on, the bases that keep the
+// keys of its bucket in suffix order: the largest of A,C,G,T below the run's first symbol and then T's
+// (A's when the symbol sorts before 'A', as the augmentation's 0x03 does).  Such a key is never used
+// for an LCE: every search that meets the suffix takes the exact path (room < k + 16).
+MSF_HD msf_u32 msf_make_key(const msf_u64 *xp, const msf_u8 *x8, msf_u32 s, msf_u32 room, int k) {
+  if (room < (msf_u32)k) return 0xFFFFFFFFu;
+  msf_u32 valid = room - (msf_u32)k;
   msf_u64 be = msf_be64(msf_get64(xp, (msf_u64)s + (msf_u32)k));
   msf_u32 key = (msf_u32)(be >> 32);
-  if (valid < 16) key = valid == 0 ? 0u : (key & (0xFFFFFFFFu << (2 * (16 - valid))));
+  if (valid < 16) {
+    const msf_u8 b = x8[s + room];
+    const msf_u32 dl = (msf_u32)(b > 'A') + (b > 'C') + (b > 'G') + (b > 'T');
+    key = valid == 0 ? 0u : (key & (0xFFFFFFFFu << (2 * (16 - valid))));
+    if (dl) key |= ((dl - 1u) << (2 * (15 - valid))) | ((1u << (2 * (15 - valid))) - 1u);
+  }
   return key;
 }
 
@@ -154,13 +177,14 @@ MSF_HD msf_u64 msf_slot_entry(const msf_u64 *sak, msf_u32 lb, msf_u32 cnt, int j
 // bisection (variant bit 16; measured at config 3: k_ms_fast 6.25 -> 5.63 ms).  Entry 0 stays MSF_SLOT_EMPTY.
 #define MSF_SLOT_NB 0xFFFFFFFDFFFFFFFFull
 MSF_HD void msf_slot_fill(const msf_u64 *sak, const msf_u32 *ktab, const msf_u64 *xp, msf_u32 n,
-                          msf_u32 n_acgt, int k, msf_u64 code, msf_u64 *e) {
+                          const msf_u64 *xruns, const msf_u32 *xbk, msf_u32 nruns, msf_u32 n_acgt, int k,
+                          msf_u64 code, msf_u64 *e) {
   const msf_u32 lb = ktab[code], cnt = ktab[code + 1] - lb;
 #pragma unroll
   for (int j = 0; j < 8; j++) e[j] = msf_slot_entry(sak, lb, cnt, j);
   if (cnt == 0 && lb > 0 && lb < n && xp) {
     const msf_u32 ps = (msf_u32)(sak[lb - 1] >> 32), ss = (msf_u32)(sak[lb] >> 32);
-    if ((msf_u64)ps + (msf_u32)k <= n_acgt && (msf_u64)ss + (msf_u32)k <= n_acgt) {
+    if (msf_room_at(xruns, xbk, nruns, n_acgt, ps) >= (msf_u32)k && msf_room_at(xruns, xbk, nruns, n_acgt, ss) >= (msf_u32)k) {
       const msf_u32 pc = (msf_u32)(msf_be64(msf_get64(xp, ps)) >> (64 - 2 * k));
       const msf_u32 sc = (msf_u32)(msf_be64(msf_get64(xp, ss)) >> (64 - 2 * k));
       e[1] = (msf_u64)pc | ((msf_u64)ps << 32);
@@ -173,7 +197,10 @@ MSF_HD void msf_slot_fill(const msf_u64 *sak, const msf_u32 *ktab, const msf_u64
 struct MsfParams {
   // reference index
   const msf_u64 *slots;   // k-mer slot table (NULL: every search goes through ktab + sak)
-  const msf_u64 *xp;      // packed pure prefix of x (n_acgt bases), zero padded
+  const msf_u64 *xp;      // 2-bit packed x (arbitrary codes inside the runs of other symbols), zero padded
+  const msf_u64 *xruns;   // runs of symbols outside A,C,G,T in x (msf_room_at); unused when nruns <= 1
+  const msf_u32 *xbk;
+  msf_u32 nruns;
   const msf_u8 *x8;       // augmented reference bytes
   const msf_u64 *sak;     // per SA rank: key (low 32 bits) | sa (high 32 bits)
   const msf_u32 *ktab;    // 4^k + 1 entries: number of suffixes smaller than k-mer m
@@ -305,13 +332,15 @@ MSF_HD void msf_emit(const MsfParams &P, MsfLane &L, msf_u32 rel, msf_u32 pos, m
   L.cnt++;
 }
 
+MSF_HD msf_u32 msf_room(const MsfParams &P, msf_u32 s) { return msf_room_at(P.xruns, P.xbk, P.nruns, P.n_acgt, s); }
+
 // order of the reference suffix s against the text suffix at i (limit symbols up to its separator):
 // m = LCE, returns true when the reference suffix is the smaller one.  Same semantics as probe()
 // in ms.cu on the 8-bit data: past n_acgt the reference holds no A/C/G/T, and the separator 0x02
 // is smaller than every reference symbol but x[n-2] = 1 and x[n-1] = 0.
 MSF_HD bool msf_compare(const MsfParams &P, msf_u64 i, msf_u32 limit, msf_u32 s, msf_u32 &m, msf_u32 &xb,
                         msf_u32 &tb) {
-  msf_u32 room = s < P.n_acgt ? P.n_acgt - s : 0u;
+  msf_u32 room = msf_room(P, s);
   msf_u32 maxl = limit < room ? limit : room;
   m = msf_lce(P.tp, i, P.xp, s, maxl);
   xb = MSF_LD8(P.x8 + s + m);
@@ -453,13 +482,13 @@ MSF_HD void msf_skip_to(const MsfParams &P, MsfLane &L, msf_u32 q) {
 // single candidate s whose key equals the text's: hand it to the warp (or to the exact search)
 MSF_HD msf_u32 msf_start_ext(const MsfParams &P, MsfLane &L, msf_u32 s) {
   const msf_u32 KL = (msf_u32)P.k + 16;
-  if ((msf_u64)s + KL > P.n_acgt) return MSF_ACT_GENERIC;
+  if (msf_room(P, s) < KL) return MSF_ACT_GENERIC;
   L.pos = s;
   L.len = KL;
   return MSF_ACT_EXT;
 }
 MSF_HD msf_u32 msf_ext_max(const MsfParams &P, msf_u32 limit, msf_u32 pos) {
-  msf_u32 room = P.n_acgt - pos;
+  msf_u32 room = msf_room(P, pos);
   return limit < room ? limit : room;
 }
 // phase B probe: the 32 bases at offset off of the two streams.  Returns 0xFFFFFFFF when they are
@@ -503,7 +532,7 @@ MSF_HD void msf_load_slot(const msf_u64 *sp, msf_u64 *e) {
 // predecessor (prevkey/prevsa, if any) and successor (skey/ssa, if found) are known by key only
 MSF_HD msf_u32 msf_decide(const MsfParams &P, MsfLane &L, bool found, msf_u32 skey, msf_u32 ssa) {
   const msf_u32 KL = (msf_u32)P.k + 16;
-  if ((found && (msf_u64)ssa + KL > P.n_acgt) || (L.haveprev && (msf_u64)L.prevsa + KL > P.n_acgt))
+  if ((found && msf_room(P, ssa) < KL) || (L.haveprev && msf_room(P, L.prevsa) < KL))
     return MSF_ACT_GENERIC;
   msf_u32 lp = 0, ls = 0;
   if (L.haveprev) lp = (msf_u32)P.k + (MSF_CLZ32(L.prevkey ^ L.tkey) >> 1);

@@ -33,19 +33,36 @@ void msf_host_steps(unsigned long long *out) {
 long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plcp_prime, const u8 *text,
                        u64 N, u32 WL, int k, u32 skip_min, u32 nlanes, int use_slots, u32 *dpos, u32 *dlen, u8 *dsm,
                        u8 *dhead, u64 *hg, u32 *hpos, u32 *hlen, uint16_t *hcs) {
-  // ---- eligibility (capi.cu: index purity) ----
-  u32 n_acgt = 0;
-  while (n_acgt < n && (x[n_acgt] == 'A' || x[n_acgt] == 'C' || x[n_acgt] == 'G' || x[n_acgt] == 'T')) n_acgt++;
-  for (u32 j = n_acgt; j < n; j++)
-    if (x[j] == 'A' || x[j] == 'C' || x[j] == 'G' || x[j] == 'T') return -1;
-  if (n_acgt == 0 || x[n_acgt] >= 'A') return -1;
+  // ---- eligibility (capi.cu: classify_x): A/C/G/T segments between a bounded number of runs of other symbols ----
+  auto acgt = [](u8 b) { return b == 'A' || b == 'C' || b == 'G' || b == 'T'; };
+  std::vector<u64> runs;
+  std::vector<u32> xbk;
+  u64 bases = 0;
+  for (u32 j = 0; j < n;) {
+    if (acgt(x[j])) { j++; bases++; continue; }
+    u32 e = j;
+    while (e < n && !acgt(x[e])) e++;
+    runs.push_back((u64)j | ((u64)e << 32));
+    j = e;
+  }
+  if (runs.size() > (size_t)n / 8 + 16 || bases == 0 || runs.empty() || (u32)(runs.back() >> 32) != n) return -1;
+  const u32 nruns = (u32)runs.size(), n_acgt = (u32)runs.back();
+  if (nruns > 1) {
+    xbk.resize(((size_t)n >> 6) + 2);
+    u32 j = 0;
+    for (size_t b = 0; b < xbk.size(); b++) {
+      while (j + 1 < runs.size() && (u32)(runs[j] >> 32) <= (b << 6)) j++;
+      xbk[b] = j;
+    }
+  }
+  runs.push_back(~0ull);
   for (u64 j = 0; j < N; j++) {          // any legal symbol: the others are escapes in the break list
     u8 c = text[j];
     if (c < 2 || c > 127) return -1;
   }
   // ---- index ----
   std::vector<u64> xp, tp;
-  pack(x, n_acgt, xp);
+  pack(x, n, xp);
   xp.resize((n + 31) / 32 + MSF_PAD_WORDS, 0);
   std::vector<u8> x8(x, x + n);
   x8.resize(n + 64, 0xFF);
@@ -64,10 +81,11 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   }
   std::vector<u64> sak(n);
   for (u32 r = 0; r < n; r++)
-    sak[r] = (u64)msf_make_key(xp.data(), (u32)sa[r], n_acgt, k) | ((u64)(u32)sa[r] << 32);
+    sak[r] = (u64)msf_make_key(xp.data(), x8.data(), (u32)sa[r],
+                               msf_room_at(runs.data(), xbk.data(), nruns, n_acgt, (u32)sa[r]), k) | ((u64)(u32)sa[r] << 32);
   std::vector<u64> slots(K * 8);
   for (u64 code = 0; code < K; code++)
-    msf_slot_fill(sak.data(), ktab.data(), xp.data(), n, n_acgt, k, code, &slots[code * 8]);
+    msf_slot_fill(sak.data(), ktab.data(), xp.data(), n, runs.data(), xbk.data(), nruns, n_acgt, k, code, &slots[code * 8]);
   std::vector<u32> G(n + 8);
   for (u32 i = 0; i < n; i++) G[i] = i + (u32)plcp_prime[i];
   // ---- text ----
@@ -95,6 +113,7 @@ long long msf_host_run(const u8 *x, u32 n, const int32_t *sa, const int32_t *plc
   P.slots = use_slots ? slots.data() : nullptr;
   P.xp = xp.data(); P.x8 = x8.data(); P.sak = sak.data(); P.ktab = ktab.data(); P.G = G.data();
   P.n = n; P.n_acgt = n_acgt; P.k = k;
+  P.xruns = runs.data(); P.xbk = xbk.data(); P.nruns = nruns;
   P.tp = tp.data(); P.t8 = t8.data(); P.N = N; P.seps = seps.data(); P.nseps = nseps; P.wsep = wsep.data();
   P.WL = WL; P.nwin = nwin; P.skip_min = skip_min; P.variant = use_slots == 2 ? 2u | 16u : 2u;   // use_slots 2: empty-bucket slots too
   P.pool = pool.data(); P.batch_next = bnext.data(); P.nb_cap = (u32)nb_cap; P.nb_used = &nb_used;

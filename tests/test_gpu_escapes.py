@@ -90,3 +90,48 @@ def test_golden_fixtures_with_other_symbols_run_fast(ctx):
         assert st["n_escapes"] == int(other.sum())
         ran += 1
     print("golden fixtures with escapes on the fast path:", ran)
+
+
+def test_reference_with_other_symbols_stays_on_the_fast_path(ctx):
+    """N blocks, IUPAC codes, lower case and symbols below 'A' / above 'T' in the REFERENCE (second
+    half): run list beside the 2-bit reference (ms_fast.cuh: msf_room_at), matches end at the runs or run
+    through them where the text carries the same symbols"""
+    rng = np.random.default_rng(29)
+    ref, copies = gen_synth.make_collection(200000, 5, 0.002, 14)
+    ref = ref.copy()
+    ref[0:7] = ord("N")
+    ref[50000:53000] = ord("N")
+    for q in (90000, 90001, 90040, 120000, 120017, 120018, 120019):
+        ref[q] = ord("N")
+    ref[150000] = ord("R"); ref[150003] = ord("y"); ref[150100] = ord("#"); ref[150200] = ord("B")
+    ref[150300] = ord("a"); ref[150400] = ord("|")
+    ref[-3:] = ord("N")
+    x = P.augment(ref)
+    base = O.docs_to_text([np.zeros(0, np.uint8)] + copies)
+    for chunk in (None, 100):
+        _check_case(ctx, x, base, None, "reference runs", chunk=chunk, expect_fast=True)
+    t = base.copy()
+    t[51000:51500] = ord("N"); t[90000] = ord("N"); t[120017:120020] = ord("N"); t[150000] = ord("R")
+    t, _ = _sprinkle(t, rng, 0.001)
+    _check_case(ctx, x, t, None, "reference runs + text escapes", expect_fast=True)
+    docs = [ref[49990:53010].copy(), ref[89990:90050].copy(), ref[149990:150410].copy(), ref[-40:].copy(), ref[:30].copy()]
+    _check_case(ctx, x, O.docs_to_text(docs), None, "documents with the reference's runs", chunk=64, expect_fast=True)
+
+
+def test_golden_fixtures_with_impure_references_run_fast(ctx):
+    """the fixtures of the reference binary whose REFERENCE carries N / lower case (VERDICT r1 item 10 names
+    fuzz_003, fuzz_077, fuzz_150, fuzz_199): identical bytes with fast_path == 1"""
+    ran = []
+    for f in sorted(glob.glob(os.path.join(GOLDEN, "*.npz"))):
+        z = np.load(f)
+        x, text = _inputs(z["ref_file"].tobytes(), z["coll_file"].tobytes(), int(z["prefix"]))
+        acgt = np.isin(x, np.frombuffer(b"ACGT", np.uint8))
+        na = ~acgt
+        runs = int(np.sum(na[1:] & ~na[:-1])) + int(na[0])
+        other = ~np.isin(text, np.frombuffer(b"ACGT\x02", np.uint8))
+        if runs < 2 or runs > len(x) // 8 + 16 or not acgt.any() or other.sum() > len(text) // 32 + 4096 or len(text) == 0:
+            continue
+        _check_case(ctx, x, text, z["bwt"], os.path.basename(f), expect_fast=True)
+        ran.append(os.path.basename(f))
+    print("golden fixtures with impure references on the fast path:", ran)
+    assert len(ran) >= 4

@@ -103,7 +103,7 @@ def test_golden_and_fuzz(harness):
             continue
         if run_case(harness, x, text, [64, 100, 4096][seed % 3], desc=c["desc"]) is not None:
             ran += 1
-    assert ran >= 20, "too few pure-ACGT cases exercised the fast path (%d)" % ran
+    assert ran >= 180, "too few cases exercised the fast path (%d)" % ran      # references with runs of other symbols included
 
 
 @pytest.mark.parametrize("WL", [37, 256, 4096])
@@ -168,3 +168,37 @@ def test_text_escapes(harness, WL):
     # short documents made of escapes only
     docs = [np.frombuffer(b"NNNN", np.uint8), np.frombuffer(b"N", np.uint8), ref[50:90].copy(), np.frombuffer(b"ACNGT", np.uint8)]
     assert run_case(harness, x, O.docs_to_text(docs), 64, desc="escape documents") is not None
+
+
+@pytest.mark.parametrize("WL", [64, 1000])
+def test_reference_runs(harness, WL):
+    """symbols outside A,C,G,T in the REFERENCE (N blocks, IUPAC codes, lower case, symbols that sort before 'A',
+    between the bases and after 'T') stay on the 2-bit path through the run list (ms_fast.cuh: msf_room_at):
+    per-position MS against the oracle, text with and without the same symbols"""
+    rng = np.random.default_rng(23)
+    ref, copies = gen_synth.make_collection(30000, 5, 0.003, 6)
+    ref = ref.copy()
+    ref[0:7] = ord("N")                                   # the reference starts inside a run
+    ref[5000:5400] = ord("N")                             # a long block
+    for q in (9000, 9001, 9040, 12000, 12017, 12018, 12019, 20000):
+        ref[q] = ord("N")                                 # single symbols closer than k + 16 to each other
+    ref[15000] = ord("R"); ref[15003] = ord("y"); ref[15100] = ord("#"); ref[15200] = ord("B")
+    ref[15300] = ord("D"); ref[15400] = ord("H"); ref[15500] = ord("a"); ref[15600] = ord("|")
+    ref[-3:] = ord("N")                                   # a run right in front of the augmentation
+    x = O.augment(ref)
+    base = O.docs_to_text([np.zeros(0, np.uint8)] + copies)   # copies of the clean reference: matches end at the runs
+    assert run_case(harness, x, base, WL, desc="reference runs") is not None
+    t = base.copy()
+    t[5100:5200] = ord("N")                               # the text has the block too: matches run through it
+    t[9000] = ord("N"); t[12017:12020] = ord("N"); t[15000] = ord("R"); t[15100] = ord("#")
+    assert run_case(harness, x, t, WL, desc="reference runs + text escapes") is not None
+    assert run_case(harness, x, _sprinkle(base, rng, 0.01), WL, desc="reference runs + sprinkled escapes") is not None
+    # documents cut from the impure reference itself (exact copies through every run)
+    docs = [ref[4990:5410].copy(), ref[8990:9050].copy(), ref[14990:15610].copy(), ref[-40:].copy(), ref[:30].copy()]
+    assert run_case(harness, x, O.docs_to_text(docs), 64, desc="documents with the reference's runs") is not None
+    # tiny k (runs closer than k) and a reference that is mostly runs
+    ref2 = gen_synth.ACGT[rng.integers(0, 4, 3000)].copy()
+    ref2[rng.random(3000) < 0.01] = ord("N")
+    docs2 = [ref2[a:a + 200].copy() for a in range(0, 2800, 150)]
+    for k in (2, 5):
+        assert run_case(harness, O.augment(ref2), O.docs_to_text(docs2), 64, k=k, skip_min=2, desc="dense runs") is not None
