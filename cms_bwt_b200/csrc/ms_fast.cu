@@ -1,4 +1,4 @@
-// Stage 1, fast path (pure-ACGT reference and text): 2-bit packing, the lane-per-window matching
+// Stage 1, fast path (2-bit data; other symbols through the text's break list and the reference's run list): 2-bit packing, the lane-per-window matching
 // statistics kernel (state machine in ms_fast.cuh) and the compaction of its head records into the
 // text-order arrays the rest of the pipeline reads.  Replaces CMS-BWT-functions.cpp:1138-1213
 // (small path :344-419) for such inputs; anything else goes through k_ms (ms.cu).
@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(256) k_msf_gather(const uint4 *__restrict__ po
   }
 }
 
-// Returns false (nothing changed) when the text is not pure ACGT + separators.
+// Returns false (nothing changed) when the text holds an illegal byte or is mostly symbols outside A,C,G,T.
 bool ms_stage_fast(cmsbwt_ctx *c) {
   cudaStream_t st = c->st;
   const u64 N = c->N;

@@ -1,4 +1,4 @@
-// Fast matching-statistics path for pure-ACGT inputs: one *lane* per text window.
+// Fast matching-statistics path (2-bit data): one *lane* per text window.
 //
 // Replaces the reference's per-document MS driver (CMS-BWT-functions.cpp:1138-1213; small path
 // :344-419) with computeMSFactorAt :45-88, binarySearchLB/RB :94-149 and the PLCP' skip loop
@@ -13,7 +13,8 @@
 //      warp, which compares 1024 packed bases per round (32 lanes x 32 bases, coalesced).
 //   C  head test + record (lane-local, one copy of the code); msf_generic_search(), an exact
 //      binary search on the packed data, serves everything rare (separator within k+16 bases,
-//      empty bucket, repeated key, suffixes that touch the augmentation).
+//      empty bucket, repeated key, suffixes within k+16 bases of a run of other symbols in the reference --
+//      an N block, an IUPAC code, the augmentation; msf_room_at).
 //   D  skip (warp-cooperative): after a long match, the first q in (pos, E) with G[q] >= E
 //      (:1176-1185 as a search) from one coalesced read of the 32 entries below E.
 //
@@ -24,6 +25,8 @@
 // by a separator, the byte that decides the order at the limit is read from the 8-bit text, and the
 // (rare) escape positions themselves -- and matches that run through an escape into the augmentation
 // -- take an exact byte-wise search (msf_escape_search).  MS is still the sequential definition.
+// Symbols other than A, C, G, T in the REFERENCE are runs between which the 2-bit comparisons stay
+// (msf_room_at, msf_make_key); a match continues through a run byte-wise where the text has the same symbols.
 //
 // The neighbour rule is the one of :53-76 as restated in ms.cu: the successor wins ties
 // (smaller = 1).  This header is plain C++ when compiled without nvcc so that the same lane code
