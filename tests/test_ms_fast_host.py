@@ -202,3 +202,39 @@ def test_reference_runs(harness, WL):
     docs2 = [ref2[a:a + 200].copy() for a in range(0, 2800, 150)]
     for k in (2, 5):
         assert run_case(harness, O.augment(ref2), O.docs_to_text(docs2), 64, k=k, skip_min=2, desc="dense runs") is not None
+
+
+def test_reference_runs_fuzz(harness):
+    """random references over A,C,G,T with symbols from the whole legal range 3..127 sprinkled in at several densities
+    (single symbols and blocks), documents cut from the reference (so matches run through the runs) and mutated
+    copies; small k so that runs fall inside k-mers and inside the 16 key bases; per-position MS against the oracle"""
+    ran = 0
+    for seed in range(48):
+        rng = np.random.default_rng(1000 + seed)
+        n = int(rng.integers(300, 2500))
+        ref = gen_synth.ACGT[rng.integers(0, 4, n)].copy()
+        pool = np.array([c for c in range(3, 128) if chr(c) not in "ACGT"], np.uint8)
+        if seed % 3 == 0:
+            pool = np.frombuffer(b"N", np.uint8)
+        rate = [0.002, 0.01, 0.04][seed % 3]
+        hit = rng.random(n) < rate
+        ref[hit] = pool[rng.integers(0, len(pool), int(hit.sum()))]
+        for _ in range(int(rng.integers(0, 3))):                       # blocks
+            a = int(rng.integers(0, n - 40)); ref[a:a + int(rng.integers(2, 40))] = pool[int(rng.integers(0, len(pool)))]
+        if not np.isin(ref, gen_synth.ACGT).any():
+            continue
+        docs = []
+        for _ in range(6):
+            a = int(rng.integers(0, n - 30)); b = min(n, a + int(rng.integers(20, 400)))
+            d = ref[a:b].copy()
+            if rng.random() < 0.6:
+                m = rng.random(len(d)) < 0.02
+                d[m] = gen_synth.ACGT[rng.integers(0, 4, int(m.sum()))]
+            docs.append(d)
+        x = O.augment(ref)
+        text = O.docs_to_text(docs)
+        k = [2, 3, 4, 5][seed % 4]
+        r = run_case(harness, x, text, [37, 64, 500][seed % 3], k=k, skip_min=[2, 8, 20][seed % 3], desc="runs fuzz %d" % seed)
+        if r is not None:
+            ran += 1
+    assert ran >= 30, ran
