@@ -335,6 +335,32 @@ MSF_HD void msf_emit(const MsfParams &P, MsfLane &L, msf_u32 rel, msf_u32 pos, m
   L.cnt++;
 }
 
+// number of leading bytes on which a and b agree, counted from m on (they are known to agree before m).  The
+// caller's streams always differ somewhere (0x02 occurs nowhere in x, x[n-1] = 0 is unique); eight bytes
+// per step -- a match that runs through an N block of the reference is tens of thousands of bytes long
+// -- both buffers are readable 64 bytes past their ends.
+MSF_HD msf_u64 msf_ld64u(const msf_u8 *p) {
+#if defined(__CUDA_ARCH__)
+  const unsigned long long a = (unsigned long long)p;
+  const msf_u32 sh = (msf_u32)(a & 7ull) * 8u;
+  const msf_u64 *q = (const msf_u64 *)(a & ~7ull);
+  const msf_u64 lo = MSF_LD64(q);
+  if (sh == 0) return lo;
+  return (lo >> sh) | (MSF_LD64(q + 1) << (64u - sh));
+#else
+  msf_u64 v;
+  __builtin_memcpy(&v, p, 8);
+  return v;
+#endif
+}
+MSF_HD msf_u32 msf_match_bytes(const msf_u8 *a, const msf_u8 *b, msf_u32 m) {
+  for (;;) {
+    const msf_u64 d = msf_ld64u(a + m) ^ msf_ld64u(b + m);
+    if (d) return m + (MSF_CTZ64(d) >> 3);
+    m += 8;
+  }
+}
+
 MSF_HD msf_u32 msf_room(const MsfParams &P, msf_u32 s) { return msf_room_at(P.xruns, P.xbk, P.nruns, P.n_acgt, s); }
 
 // order of the reference suffix s against the text suffix at i (limit symbols up to its separator):
@@ -348,8 +374,9 @@ MSF_HD bool msf_compare(const MsfParams &P, msf_u64 i, msf_u32 limit, msf_u32 s,
   m = msf_lce(P.tp, i, P.xp, s, maxl);
   xb = MSF_LD8(P.x8 + s + m);
   tb = m == limit ? (msf_u32)MSF_LD8(P.t8 + i + m) : (msf_u32)msf_sym_of(msf_base(P.tp, i + m));
-  if (m == limit && xb == tb) {        // an escape that the reference (its augmentation) continues: bytes from here
-    do { m++; xb = MSF_LD8(P.x8 + s + m); tb = MSF_LD8(P.t8 + i + m); } while (xb == tb);
+  if (m == limit && xb == tb) {        // an escape that the reference continues (a run of its own, its augmentation): bytes from here
+    m = msf_match_bytes(P.x8 + s, P.t8 + i, m + 1);
+    xb = MSF_LD8(P.x8 + s + m); tb = MSF_LD8(P.t8 + i + m);
   }
   return xb < tb;
 }
@@ -363,23 +390,18 @@ MSF_HDN void msf_escape_search(const MsfParams &P, msf_u64 i, msf_u32 &pos, msf_
   while (lo < hi) {
     const msf_u32 mid = lo + ((hi - lo) >> 1);
     const msf_u8 *x = P.x8 + (msf_u32)(MSF_LD64(P.sak + mid) >> 32);
-    msf_u32 m = 0;
-    while (MSF_LD8(x + m) == MSF_LD8(t + m)) m++;
+    const msf_u32 m = msf_match_bytes(x, t, 0);
     if (MSF_LD8(x + m) < MSF_LD8(t + m)) lo = mid + 1; else hi = mid;
   }
   long long lp = -1, ls = -1;
   msf_u32 ppos = 0, spos = 0;
   if (lo > 0) {
     ppos = (msf_u32)(MSF_LD64(P.sak + lo - 1) >> 32);
-    msf_u32 m = 0;
-    while (MSF_LD8(P.x8 + ppos + m) == MSF_LD8(t + m)) m++;
-    lp = m;
+    lp = msf_match_bytes(P.x8 + ppos, t, 0);
   }
   if (lo < P.n) {
     spos = (msf_u32)(MSF_LD64(P.sak + lo) >> 32);
-    msf_u32 m = 0;
-    while (MSF_LD8(P.x8 + spos + m) == MSF_LD8(t + m)) m++;
-    ls = m;
+    ls = msf_match_bytes(P.x8 + spos, t, 0);
   }
   if (ls >= lp) { pos = spos; len = (msf_u32)ls; sm = 1; }
   else { pos = ppos; len = (msf_u32)lp; sm = 0; }
@@ -440,7 +462,7 @@ MSF_HD void msf_next_break(const MsfParams &P, MsfLane &L) {
 }
 // phase C: head test (:1154), record, step.  term: L.i holds a separator (:1198-1212).
 // Returns MSF_ACT_SKIP when the non-head run after this head has to be looked up.
-// esc: L.i holds an escape symbol (its MS comes from msf_escape_search; no skip follows it)
+// esc: L.i holds an escape symbol (its MS comes from msf_escape_search; a long match is followed by its skip like any other)
 MSF_HD msf_u32 msf_fin(const MsfParams &P, MsfLane &L, bool term, bool esc = false) {
   const bool tent = !term && L.first && !L.prevterm;   // window starts inside a document
   const bool head = term || L.prevterm || L.pos != L.prevpos + 1;
@@ -455,6 +477,11 @@ MSF_HD msf_u32 msf_fin(const MsfParams &P, MsfLane &L, bool term, bool esc = fal
   L.prevterm = term ? 1u : 0u;
   L.prevesc = esc ? 1u : 0u;
   L.state = MSF_S_POS;
+  // a long match that starts AT an escape (a document or a window that begins inside an N block which the
+  // reference has too) is followed by its non-head run like any other: without the skip every symbol of
+  // the block would take its own exact search, each as long as the rest of the block.  msf_skip_to moves
+  // the break cursor over the breaks of the run.
+  if (esc && L.len >= P.skip_min && L.len > 1) return MSF_ACT_SKIP;
   if (term || esc) {
     L.sepidx++;
     msf_next_break(P, L);
@@ -515,8 +542,8 @@ MSF_HD void msf_ext_done(const MsfParams &P, MsfLane &L, msf_u32 res, msf_u32 bm
   msf_u32 xb = MSF_LD8(P.x8 + L.pos + bmax);
   msf_u32 tb = bmax == L.limit ? (msf_u32)MSF_LD8(P.t8 + L.i + bmax) : (msf_u32)msf_sym_of(msf_base(P.tp, L.i + bmax));
   if (bmax == L.limit && xb == tb) {   // the single candidate continues through an escape: bytes from here
-    msf_u32 m = bmax;
-    do { m++; xb = MSF_LD8(P.x8 + L.pos + m); tb = MSF_LD8(P.t8 + L.i + m); } while (xb == tb);
+    const msf_u32 m = msf_match_bytes(P.x8 + L.pos, P.t8 + L.i, bmax + 1);
+    xb = MSF_LD8(P.x8 + L.pos + m); tb = MSF_LD8(P.t8 + L.i + m);
     L.len = m;
   }
   L.sm = xb > tb ? 1u : 0u;

@@ -238,3 +238,31 @@ def test_reference_runs_fuzz(harness):
         if r is not None:
             ran += 1
     assert ran >= 30, ran
+
+
+def test_long_blocks_in_reference_and_text(harness):
+    """N blocks of tens of thousands of symbols that the reference AND the copies carry (haplotypes built from a
+    reference keep its gaps): a match crosses a block byte-wise once and its non-head run covers the block,
+    also when a document or a window starts inside one -- never one exact search per symbol of the block."""
+    import time
+    rng = np.random.default_rng(41)
+    ref = gen_synth.ACGT[rng.integers(0, 4, 90000)].copy()
+    ref[0:12000] = ord("N")                       # the reference starts with a block (a telomere gap)
+    ref[40000:60000] = ord("N")
+    ref[70000:70300] = ord("n")
+    copies = []
+    for c in range(3):
+        d = ref.copy()
+        snp = np.flatnonzero(np.isin(d, gen_synth.ACGT) & (rng.random(len(d)) < 0.002))
+        d[snp] = gen_synth.ACGT[rng.integers(0, 4, len(snp))]
+        copies.append(d)
+    copies.append(ref[5000:45000].copy())         # starts and ends inside blocks
+    copies.append(ref[41000:41050].copy())        # nothing but a piece of a block
+    shorter = ref.copy(); shorter = np.concatenate([shorter[:45000], shorter[52000:]])   # a block 7000 symbols shorter
+    copies.append(shorter)
+    x = O.augment(ref)
+    text = O.docs_to_text(copies)
+    t0 = time.time()
+    for WL in (1000, 8192):
+        assert run_case(harness, x, text, WL, desc="long blocks") is not None
+    assert time.time() - t0 < 120, "the block symbols are being searched one by one"
